@@ -1,0 +1,12 @@
+"""nlbac_b200 — B200 (sm_100a) drop-in for the NLBAC neural-ODE hot path.
+
+Host mirror of the reference's call surface over the C ABI in include/nlbac.h:
+``odeint`` (torchdiffeq-compatible), ``NeuralODEModel``, ``train_step``.  Import as ``nlbac_b200``
+(the repo-root shim) — the directory name carries the reference's full name.
+"""
+from . import _lib
+from ._lib import build
+from .odeint import odeint, describe
+from .model import NeuralODEModel, train_step
+
+__all__ = ["odeint", "NeuralODEModel", "train_step", "build", "describe"]

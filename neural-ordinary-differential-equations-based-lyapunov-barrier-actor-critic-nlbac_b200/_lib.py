@@ -1,0 +1,104 @@
+"""ctypes binding of the C ABI in include/nlbac.h (no torch types cross the boundary).
+
+The shared library is built in-tree by ``build()`` (nvcc, sm_100a) and loaded lazily.  There is no
+CPU fallback: if the library is missing or a call fails, a RuntimeError is raised.
+"""
+import ctypes
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB_PATH = os.path.join(HERE, "libnlbac_b200.so")
+SOURCES = ["node_abi.cu", "mlp_abi.cu", "tail_abi.cu"]
+NVCC_FLAGS = ["-std=c++20", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
+              "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC"]
+
+_lib = None
+
+
+class NodeDesc(ctypes.Structure):
+    _fields_ = [("kind", ctypes.c_int), ("n_s", ctypes.c_int), ("n_u", ctypes.c_int), ("n_c", ctypes.c_int),
+                ("hidden", ctypes.c_int), ("n_f_layers", ctypes.c_int), ("n_g_layers", ctypes.c_int)]
+
+
+def _newer(src_files, target):
+    if not os.path.exists(target):
+        return True
+    t = os.path.getmtime(target)
+    return any(os.path.getmtime(f) > t for f in src_files)
+
+
+def build(force=False, verbose=False):
+    """Compile every CUDA source for sm_100a into libnlbac_b200.so (in-tree)."""
+    srcs = [os.path.join(CSRC, s) for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
+    deps = [os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [os.path.join(ROOT, "include", "nlbac.h")]
+    if not force and not _newer(deps, LIB_PATH):
+        return LIB_PATH
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    objs = []
+    procs = []
+    for s in srcs:
+        o = s[:-3] + ".o"
+        objs.append(o)
+        cmd = [nvcc] + NVCC_FLAGS + ["-c", s, "-o", o]
+        if verbose:
+            cmd.insert(1, "-Xptxas=-v")
+        procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))
+    for cmd, p in procs:
+        out, _ = p.communicate()
+        if verbose or p.returncode != 0:
+            print(out.decode())
+        if p.returncode != 0:
+            raise RuntimeError("nvcc failed: " + " ".join(cmd))
+    cmd = [nvcc, "-shared", "-o", LIB_PATH] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
+    subprocess.check_call(cmd)
+    return LIB_PATH
+
+
+def _declare(lib):
+    c = ctypes
+    vp, ip, fp = c.c_void_p, c.POINTER(c.c_int), c.POINTER(c.c_float)
+    dp = c.POINTER(NodeDesc)
+    lib.nlbac_last_error.restype = c.c_char_p
+    lib.nlbac_abi_version.restype = c.c_int
+    lib.nlbac_node_supported.argtypes = [dp, c.c_int]
+    lib.nlbac_node_param_count.argtypes = [dp]
+    lib.nlbac_node_param_count.restype = c.c_int64
+    lib.nlbac_node_packed_floats.argtypes = [dp]
+    lib.nlbac_node_packed_floats.restype = c.c_int64
+    lib.nlbac_node_pack.argtypes = [dp, c.POINTER(vp), vp, vp]
+    lib.nlbac_node_workspace_bytes.argtypes = [dp, c.c_int64, c.c_int, c.c_int, c.c_int,
+                                               c.POINTER(c.c_size_t), c.POINTER(c.c_size_t), c.POINTER(c.c_size_t)]
+    lib.nlbac_node_solve_fwd.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, fp, c.c_int, c.c_int, c.c_int,
+                                         vp, vp, vp, vp]
+    lib.nlbac_node_solve_bwd.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, fp, c.c_int, c.c_int, c.c_int,
+                                         vp, vp, vp, vp, vp, vp]
+    lib.nlbac_fp32_peak_probe.argtypes = [c.c_int, vp, c.POINTER(c.c_double), vp]
+    return lib
+
+
+def lib():
+    """Load the CUDA library; fail loudly if it was never built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                "nlbac_b200: %s is missing — run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(there is no CPU fallback)" % LIB_PATH)
+        _lib = _declare(ctypes.CDLL(LIB_PATH))
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        raise RuntimeError("nlbac_b200 %s failed (rc=%d): %s" % (what, rc, lib().nlbac_last_error().decode()))
+
+
+def declared_symbols():
+    """Every function name declared in include/nlbac.h (used by the CPU export test)."""
+    import re
+    text = open(os.path.join(ROOT, "include", "nlbac.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(nlbac_[a-z0-9_]+)\s*\(", text)))

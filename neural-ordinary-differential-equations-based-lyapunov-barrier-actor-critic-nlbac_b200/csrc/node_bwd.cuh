@@ -1,0 +1,423 @@
+// K2 — fused fixed-grid NODE solve, backward (reverse sweep through the discrete steps), FP32-exact.
+//
+// Replaces autograd through torchdiffeq's fixed-grid solvers + NeuralODEModel.forward
+// (loss.backward() at U sac_cbf_clf/model.py:256 and policy_loss.backward() at U sac_cbf_clf.py:285).
+// For every (step, stage) in reverse order a tile of TB trajectories re-evaluates the stage from its
+// checkpointed input (activations kept in shared memory), back-propagates the stage cotangent to the
+// stage input, the action columns and the parameters, and the owner thread of each trajectory
+// advances the Runge–Kutta adjoint recurrences in registers.  Parameter gradients of the HxH layers
+// are register-tiled GEMMs over the tile (contraction over trajectories) reduced into one of NREP
+// global replicas with vector reductions; a final kernel folds the replicas into the flat gradient.
+#pragma once
+#include "node_fwd.cuh"
+
+namespace nlbac {
+
+constexpr int NREP = 8;  // gradient replicas (spreads L2 atomic traffic of the 148 CTAs)
+
+struct BwdArgs {
+  const float* packed;
+  const float* y0;        // [B, D]  (constants of the flow: action / time columns)
+  const float* ckpt;      // [n_steps, S, B, NS] stage inputs written by the forward
+  const float* grad_out;  // [n_t, B, D]
+  float* grad_y0;         // [B, D] or null
+  float* grad_rep;        // [NREP, NGRAD] zero-initialised, or null (skip parameter gradients)
+  const float* dts;
+  const int* out_step;
+  const float* out_w;
+  long long B;
+  int n_steps, n_t, method;
+};
+
+template <class C, int TB>
+struct BwdGeom {
+  static constexpr int TT = TB / 16;
+  static constexpr int TG = TB / TT;
+  static constexpr int NGRP = C::HP / 8;
+  static constexpr int NT = TG * NGRP;
+  static constexpr int CYC = 2 * C::NHID;  // packets per stage: forward (transposed) + backward (natural)
+  static constexpr int NSLOT = (CYC * C::HID_BYTES <= 64 * 1024) ? CYC : 2;
+  static constexpr int NBUF = C::NL_MAX - 1;  // stored activations per chain
+  static constexpr int OFF_ACT = 0;
+  static constexpr int OFF_X = OFF_ACT + NBUF * TB * C::RS;
+  static constexpr int OFF_D = OFF_X + TB * C::INP0;
+  static constexpr int OFF_RES = OFF_D + TB * C::OUTP_MAX;
+  static constexpr int OFF_RING = OFF_RES + C::RES_ALL;
+  static constexpr int OFF_BAR = OFF_RING + NSLOT * C::HID_FLOATS;
+  static constexpr size_t SMEM_BYTES = (size_t)OFF_BAR * 4 + (NSLOT + 1) * 8;
+  static_assert(NT >= TB && NT >= NGRP * NGRP && NT >= C::H + C::OUTP_MAX, "thread roles");
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+
+  // packet offset for ring sequence number s
+  __device__ static int pkt_off(uint32_t s) {
+    int q = s % CYC;
+    int c = 0;
+    if (C::NCH == 2 && q >= 2 * C::nhc(0)) { c = 1; q -= 2 * C::nhc(0); }
+    const int n = C::nhc(c);
+    return q < n ? C::off_hid_t(C::hid_base(c) + q) : C::off_hid_n(C::hid_base(c) + (n - 1 - (q - n)));
+  }
+};
+
+// dW[j0..j0+8)[k0..k0+8) = sum_t delta[t][j] * act[t][k]  -> vector reductions into grad (row stride ldg)
+template <int TB, int RS>
+__device__ __forceinline__ void dw_tile_reduce(const float* __restrict__ delta, const float* __restrict__ act,
+                                               int j0, int k0, int nvalid_j, int nvalid_k, float* __restrict__ grad,
+                                               int ldg) {
+  float acc[8][8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[j][k] = 0.f;
+#pragma unroll 2
+  for (int t = 0; t < TB; ++t) {
+    const float4 d0 = *reinterpret_cast<const float4*>(delta + t * RS + j0);
+    const float4 d1 = *reinterpret_cast<const float4*>(delta + t * RS + j0 + 4);
+    const float4 a0 = *reinterpret_cast<const float4*>(act + t * RS + k0);
+    const float4 a1 = *reinterpret_cast<const float4*>(act + t * RS + k0 + 4);
+    const float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+    const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[j][k] = fmaf(d[j], a[k], acc[j][k]);
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (j0 + j < nvalid_j) {
+      float* g = grad + (size_t)(j0 + j) * ldg + k0;
+      if (k0 < nvalid_k) red_add_v4(g, acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
+      if (k0 + 4 < nvalid_k) red_add_v4(g + 4, acc[j][4], acc[j][5], acc[j][6], acc[j][7]);
+    }
+  }
+}
+
+// One stage of the reverse sweep for the tile.  Owner threads pass the stage input x, the constants
+// and the cotangent dk of the stage output; they receive dx (cotangent of the stage input) and
+// accumulate dcst (cotangent of the action / constant columns).  Parameter gradients go to `grep`.
+template <class C, int TB, class Ring>
+__device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, float* smem, Ring& ring, float* grep,
+                                             const float (&x)[C::NS], const float (&cst)[C::NCONST],
+                                             const float (&dk)[C::NS], float (&dx)[C::NS], float (&dcst)[C::NCONST]) {
+  using G = BwdGeom<C, TB>;
+  constexpr int RS = C::RS, H = C::H, HP = C::HP, INP0 = C::INP0;
+  float* sAct = smem + G::OFF_ACT;
+  float* sX = smem + G::OFF_X;
+  float* sD = smem + G::OFF_D;
+  const float* sRes = smem + G::OFF_RES;
+  const int tid = threadIdx.x;
+  const bool owner = tid < TB;
+  const int tg = tid % G::TG, n0 = (tid / G::TG) * 8;
+  const int wj0 = (tid / G::NGRP) * 8, wk0 = (tid % G::NGRP) * 8;  // dW tile of this thread
+  const bool wactive = tid < G::NGRP * G::NGRP;
+  auto off = [](uint32_t s) { return G::pkt_off(s); };
+
+  if (owner) {
+    float* xr = sX + tid * INP0;
+#pragma unroll
+    for (int d = 0; d < INP0; ++d) {
+      float v = 0.f;
+      if (d < C::NS) v = x[d];
+      else if (C::KIND == KIND_BLACKBOX && d < C::D) v = cst[d - C::NS];
+      xr[d] = v;
+    }
+  }
+  float dxa[INP0];
+#pragma unroll
+  for (int d = 0; d < INP0; ++d) dxa[d] = 0.f;
+  __syncthreads();
+
+#pragma unroll
+  for (int c = 0; c < C::NCH; ++c) {
+    const int n = C::nhc(c);
+    const int OUT = C::out(c), OUTP = C::outp(c);
+    float acc[G::TT][8];
+    // ---------------- forward with stored activations ----------------
+    gemm_tile<G::TT, G::TG>(sX, INP0, sRes + C::off_wt0(c), HP, sRes + C::off_b0(c), INP0, tg, n0, acc);
+    store_relu<G::TT, G::TG>(sAct, RS, tg, n0, acc);
+    __syncthreads();
+#pragma unroll 1
+    for (int l = 1; l <= n; ++l) {
+      const float* W = ring.acquire();
+      gemm_tile<G::TT, G::TG>(sAct + (l - 1) * TB * RS, RS, W, HP, sRes + C::off_bh(c, l), H, tg, n0, acc);
+      store_relu<G::TT, G::TG>(sAct + l * TB * RS, RS, tg, n0, acc);
+      __syncthreads();
+      ring.release(packed, off);
+    }
+    float* aL = sAct + n * TB * RS;  // input of the last layer
+    // ---------------- cotangent of the chain output ----------------
+    if (owner) {
+      float* dr = sD + tid * C::OUTP_MAX;
+      if (c == 0) {
+#pragma unroll
+        for (int o = 0; o < C::outp(0); ++o) dr[o] = o < C::NS ? dk[o] : 0.f;
+      } else {
+        float go[C::outp(C::NCH - 1)];
+        thin_out<H, C::outp(C::NCH - 1)>(aL + tid * RS, sRes + C::off_wtl(C::NCH - 1), sRes + C::off_bl(C::NCH - 1), go);
+#pragma unroll
+        for (int i = 0; i < C::NS; ++i)
+#pragma unroll
+          for (int j = 0; j < C::NU; ++j) {
+            dr[i * C::NU + j] = dk[i] * cst[j];
+            dcst[j] = fmaf(go[i * C::NU + j], dk[i], dcst[j]);
+          }
+#pragma unroll
+        for (int o = C::NS * C::NU; o < C::outp(C::NCH - 1); ++o) dr[o] = 0.f;
+      }
+    }
+    __syncthreads();
+    // ---------------- last layer: dW, db (thin), delta into aL ----------------
+    if (grep != nullptr) {
+      if (tid < H) {
+        float s[C::OUTP_MAX];
+#pragma unroll
+        for (int o = 0; o < C::OUTP_MAX; ++o) s[o] = 0.f;
+#pragma unroll 2
+        for (int t = 0; t < TB; ++t) {
+          const float av = aL[t * RS + tid];
+#pragma unroll
+          for (int o = 0; o < C::OUTP_MAX; ++o)
+            if (o < OUTP) s[o] = fmaf(sD[t * C::OUTP_MAX + o], av, s[o]);
+        }
+#pragma unroll
+        for (int o = 0; o < C::OUTP_MAX; ++o)
+          if (o < OUT) atomicAdd(grep + C::goff_w(c, n + 1) + o * H + tid, s[o]);
+      } else if (tid < H + OUT) {
+        const int o = tid - H;
+        float s = 0.f;
+        for (int t = 0; t < TB; ++t) s += sD[t * C::OUTP_MAX + o];
+        atomicAdd(grep + C::goff_b(c, n + 1) + o, s);
+      }
+    }
+    gemm_tile<G::TT, G::TG>(sD, C::OUTP_MAX, sRes + C::off_wnl(c), HP, nullptr, OUTP, tg, n0, acc);
+    __syncthreads();
+    store_masked<G::TT, G::TG>(aL, RS, tg, n0, acc);
+    __syncthreads();
+    // ---------------- hidden layers, reverse ----------------
+#pragma unroll 1
+    for (int l = n; l >= 1; --l) {
+      const float* dl = sAct + l * TB * RS;        // delta (pre-activation cotangent) of layer l
+      float* ain = sAct + (l - 1) * TB * RS;       // its input activation
+      if (grep != nullptr) {
+        if (wactive) dw_tile_reduce<TB, RS>(dl, ain, wj0, wk0, H, H, grep + C::goff_w(c, l), H);
+        if (tid < H) {
+          float s = 0.f;
+#pragma unroll 4
+          for (int t = 0; t < TB; ++t) s += dl[t * RS + tid];
+          atomicAdd(grep + C::goff_b(c, l) + tid, s);
+        }
+      }
+      const float* W = ring.acquire();
+      gemm_tile<G::TT, G::TG>(dl, RS, W, HP, nullptr, H, tg, n0, acc);
+      __syncthreads();
+      ring.release(packed, off);
+      store_masked<G::TT, G::TG>(ain, RS, tg, n0, acc);
+      __syncthreads();
+    }
+    // ---------------- first layer: dW0, db0 (thin), dx ----------------
+    if (grep != nullptr && tid < H) {
+      float s[INP0], sb = 0.f;
+#pragma unroll
+      for (int k = 0; k < INP0; ++k) s[k] = 0.f;
+#pragma unroll 2
+      for (int t = 0; t < TB; ++t) {
+        const float dv = sAct[t * RS + tid];
+        sb += dv;
+#pragma unroll
+        for (int k = 0; k < INP0; ++k) s[k] = fmaf(dv, sX[t * INP0 + k], s[k]);
+      }
+#pragma unroll
+      for (int k = 0; k < INP0; ++k)
+        if (k < C::IN0) atomicAdd(grep + C::goff_w(c, 0) + tid * C::IN0 + k, s[k]);
+      atomicAdd(grep + C::goff_b(c, 0) + tid, sb);
+    }
+    if (owner) {
+      const float* drow = sAct + tid * RS;
+      const float* Wn0 = sRes + C::off_wn0(c);
+#pragma unroll 1
+      for (int j = 0; j < H; j += 4) {
+        const float4 dv = *reinterpret_cast<const float4*>(drow + j);
+        const float d4[4] = {dv.x, dv.y, dv.z, dv.w};
+#pragma unroll
+        for (int jj = 0; jj < 4; ++jj)
+#pragma unroll
+          for (int k = 0; k < INP0; k += 4) {
+            const float4 w = *reinterpret_cast<const float4*>(Wn0 + (j + jj) * INP0 + k);
+            dxa[k] = fmaf(d4[jj], w.x, dxa[k]); dxa[k + 1] = fmaf(d4[jj], w.y, dxa[k + 1]);
+            dxa[k + 2] = fmaf(d4[jj], w.z, dxa[k + 2]); dxa[k + 3] = fmaf(d4[jj], w.w, dxa[k + 3]);
+          }
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int d = 0; d < C::NS; ++d) dx[d] = dxa[d];
+  if constexpr (C::KIND == KIND_BLACKBOX) {
+#pragma unroll
+    for (int d = 0; d < C::NCONST; ++d) dcst[d] += dxa[C::NS + d];
+  }
+}
+
+// Butcher tableaux of the fixed-grid solvers (torchdiffeq fixed_grid.py / rk_common.py):
+//   x_i = y + dt * sum_{j<i} beta[i][j] k_j,   y1 = y + dt * sum_i csol[i] k_i
+struct Tableau {
+  float beta[4][4];
+  float csol[4];
+  int S;
+};
+__host__ __device__ inline Tableau make_tableau(int method) {
+  Tableau t = {};
+  if (method == METHOD_EULER) {
+    t.S = 1; t.csol[0] = 1.f;
+  } else if (method == METHOD_MIDPOINT) {
+    t.S = 2; t.beta[1][0] = 0.5f; t.csol[1] = 1.f;
+  } else {
+    t.S = 4;
+    t.beta[1][0] = 1.f / 3.f;
+    t.beta[2][0] = -1.f / 3.f; t.beta[2][1] = 1.f;
+    t.beta[3][0] = 1.f; t.beta[3][1] = -1.f; t.beta[3][2] = 1.f;
+    t.csol[0] = 0.125f; t.csol[1] = 0.375f; t.csol[2] = 0.375f; t.csol[3] = 0.125f;
+  }
+  return t;
+}
+
+template <class C, int TB>
+__global__ void __launch_bounds__(BwdGeom<C, TB>::NT, 1) node_bwd_kernel(BwdArgs a) {
+  using G = BwdGeom<C, TB>;
+  extern __shared__ __align__(16) float smem[];
+  float* sRes = smem + G::OFF_RES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G::OFF_BAR);
+  const int tid = threadIdx.x;
+  const Tableau tab = make_tableau(a.method);
+  const int S = tab.S;
+
+  const long long n_tiles = (a.B + TB - 1) / TB;
+  long long my_tiles = 0;
+  if ((long long)blockIdx.x < n_tiles) my_tiles = (n_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x;
+
+  WeightRing<G::NSLOT, G::CYC, C::HID_FLOATS> ring;
+  ring.slots = smem + G::OFF_RING;
+  ring.full = bars;
+  ring.seq = 0;
+  ring.total = (uint32_t)(my_tiles * a.n_steps * S * G::CYC);
+
+  if (tid == 0) {
+    for (int i = 0; i <= G::NSLOT; ++i) mbar_init(&bars[i], 1);
+    fence_barrier_init();
+  }
+  __syncthreads();
+  if (my_tiles == 0) return;
+  if (tid == 0) {
+    mbar_expect_tx(&bars[G::NSLOT], C::RES_ALL * 4);
+    tma_load_1d(sRes, a.packed, C::RES_ALL * 4, &bars[G::NSLOT]);
+  }
+  ring.start(a.packed, [](uint32_t s) { return G::pkt_off(s); });
+  mbar_wait(&bars[G::NSLOT], 0);
+
+  float* grep = a.grad_rep ? a.grad_rep + (size_t)(blockIdx.x % NREP) * C::NGRAD : nullptr;
+
+  for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const long long b = tile * TB + tid;
+    const bool live = tid < TB && b < a.B;
+    float adj[C::NS], cst[C::NCONST], dcst[C::NCONST];
+    float dks[4][C::NS];
+#pragma unroll
+    for (int d = 0; d < C::NS; ++d) adj[d] = 0.f;
+#pragma unroll
+    for (int d = 0; d < C::NCONST; ++d) { cst[d] = 0.f; dcst[d] = 0.f; }
+    if (live) {
+#pragma unroll
+      for (int d = 0; d < C::NCONST; ++d) cst[d] = a.y0[b * C::D + C::NS + d];
+    }
+    int jo = a.n_t - 1;
+    for (int step = a.n_steps - 1; step >= 0; --step) {
+      const float dt = a.dts[step];
+      float carry[C::NS];
+#pragma unroll
+      for (int d = 0; d < C::NS; ++d) carry[d] = 0.f;
+      // cotangents of the outputs interpolated inside this step
+      while (jo >= 1 && a.out_step[jo] == step) {
+        if (live) {
+          const float w = a.out_w[jo];
+          const float* g = a.grad_out + ((long long)jo * a.B + b) * C::D;
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) {
+            const float gv = g[d];
+            adj[d] = fmaf(w, gv, adj[d]);
+            carry[d] = fmaf(1.f - w, gv, carry[d]);
+          }
+#pragma unroll
+          for (int d = 0; d < C::NCONST; ++d) dcst[d] += g[C::NS + d];
+        }
+        --jo;
+      }
+      // y1 = y + dt * sum_i csol[i] k_i
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) dks[i][d] = dt * tab.csol[i] * adj[d];
+      float ay[C::NS];
+#pragma unroll
+      for (int d = 0; d < C::NS; ++d) ay[d] = adj[d] + carry[d];
+#pragma unroll 1
+      for (int i = S - 1; i >= 0; --i) {
+        float x[C::NS], dk[C::NS], dx[C::NS];
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) { x[d] = 0.f; dk[d] = dks[i][d]; }
+        if (live) {
+          const float* p = a.ckpt + (((long long)step * S + i) * a.B + b) * C::NS;
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) x[d] = p[d];
+        } else {
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) dk[d] = 0.f;
+        }
+        vjp_rhs_tile<C, TB>(a.packed, smem, ring, grep, x, cst, dk, dx, dcst);
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) ay[d] += dx[d];
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+          if (j < i) {
+            const float bij = dt * tab.beta[i][j];
+#pragma unroll
+            for (int d = 0; d < C::NS; ++d) dks[j][d] = fmaf(bij, dx[d], dks[j][d]);
+          }
+      }
+#pragma unroll
+      for (int d = 0; d < C::NS; ++d) adj[d] = ay[d];
+    }
+    if (live && a.grad_y0 != nullptr) {
+      const float* g = a.grad_out + b * C::D;  // cotangent of y_out[0] = y0
+      float* o = a.grad_y0 + b * C::D;
+#pragma unroll
+      for (int d = 0; d < C::NS; ++d) o[d] = adj[d] + g[d];
+#pragma unroll
+      for (int d = 0; d < C::NCONST; ++d) o[C::NS + d] = dcst[d] + g[C::NS + d];
+    }
+  }
+}
+
+// fold the NREP aligned gradient replicas into the flat state-dict-order gradient vector
+struct GradSeg { int goff, poff, n; };
+struct GradTable { GradSeg seg[2 * 16]; int n; };
+template <class C>
+GradTable build_grad_table() {
+  GradTable t;
+  t.n = 0;
+  for (int c = 0; c < C::NCH; ++c)
+    for (int l = 0; l < C::nl(c); ++l) {
+      t.seg[t.n++] = {C::goff_w(c, l), C::poff_w(c, l), C::lin(c, l) * C::lout(c, l)};
+      t.seg[t.n++] = {C::goff_b(c, l), C::poff_b(c, l), C::lout(c, l)};
+    }
+  return t;
+}
+__global__ void fold_grad_kernel(GradTable tab, const float* __restrict__ rep, int ngrad, float* __restrict__ flat) {
+  const GradSeg s = tab.seg[blockIdx.y];
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < s.n; i += gridDim.x * blockDim.x) {
+    float v = 0.f;
+#pragma unroll
+    for (int r = 0; r < NREP; ++r) v += rep[(size_t)r * ngrad + s.goff + i];
+    flat[s.poff + i] = v;
+  }
+}
+
+}  // namespace nlbac

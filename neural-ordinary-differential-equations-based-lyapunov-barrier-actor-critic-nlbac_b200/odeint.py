@@ -1,0 +1,203 @@
+"""Drop-in for ``torchdiffeq.odeint`` on the NLBAC path (surface S1).
+
+``odeint(func, y0, t, *, rtol, atol, method, options)`` keeps torchdiffeq's signature and result
+(``[len(t), *y0.shape]``, ``solution[0] == y0``) as the reference calls it (U sac_cbf_clf/model.py:252,
+U sac_cbf_clf/sac_cbf_clf.py:453,577; C sac_cbf_clf.py:437,458; P sac_cbf_clf.py:459,499,534), but the
+whole solve — every step and stage, the NeuralODEModel right-hand side included — is ONE fused CUDA
+kernel, and autograd through it is one mirrored backward kernel (``torch.autograd.Function``).
+
+``func`` must be a reference-shaped ``NeuralODEModel`` (``f_net``+``g_net`` or ``net`` Sequentials of
+Linear/ReLU, state-dict keys as in the reference); anything else raises — there is no CPU or eager
+fallback by design.
+"""
+import ctypes
+
+import numpy as np
+import torch
+import torch.nn as nn
+
+from . import _lib
+
+METHODS = {"euler": 0, "midpoint": 1, "rk4": 2, "dopri5": 3}
+PRECISIONS = {"fp32": 0, "bf16": 1}
+_FIXED = ("euler", "midpoint", "rk4")
+
+
+def _linears(seq):
+    mods = list(seq)
+    lin = [m for m in mods if isinstance(m, nn.Linear)]
+    ok = all(isinstance(m, (nn.Linear, nn.ReLU)) for m in mods) and len(mods) == 2 * len(lin) - 1
+    if not ok or not all(isinstance(mods[i], nn.Linear) == (i % 2 == 0) for i in range(len(mods))):
+        raise TypeError("nlbac_b200.odeint: network must be Linear/ReLU alternating, ending in Linear")
+    return lin
+
+
+def describe(func, D):
+    """Build the C descriptor + ordered parameter list from a reference-shaped NODE module."""
+    if hasattr(func, "f_net") and hasattr(func, "g_net"):
+        f, g = _linears(func.f_net), _linears(func.g_net)
+        n_s, hidden = f[0].in_features, f[0].out_features
+        if f[-1].out_features != n_s or g[0].in_features != n_s or g[-1].out_features % n_s:
+            raise TypeError("nlbac_b200.odeint: inconsistent control-affine NODE shapes")
+        n_u = g[-1].out_features // n_s
+        desc = _lib.NodeDesc(0, n_s, n_u, D - n_s - n_u, hidden, len(f), len(g))
+        layers = f + g
+    elif hasattr(func, "net"):
+        f = _linears(func.net)
+        n_s, hidden = f[-1].out_features, f[0].out_features
+        if f[0].in_features != D:
+            raise TypeError("nlbac_b200.odeint: black-box NODE input width %d != y0 width %d" % (f[0].in_features, D))
+        n_u = getattr(func, "n_u", None)
+        if n_u is None:
+            n_u = 1 if D - n_s == 2 else D - n_s   # cars: [x(10), u(1), t_k(1)]
+        desc = _lib.NodeDesc(1, n_s, n_u, D - n_s - n_u, hidden, len(f), 0)
+        layers = f
+    else:
+        raise TypeError("nlbac_b200.odeint: func must be a NeuralODEModel (f_net+g_net or net); "
+                        "got %s — no fallback path exists" % type(func).__name__)
+    params = []
+    for l in layers:
+        if l.bias is None:
+            raise TypeError("nlbac_b200.odeint: Linear layers must have a bias")
+        params += [l.weight, l.bias]
+    return desc, params
+
+
+def _packed(func, desc, params):
+    """Packed kernel image of the parameters, cached on the module until a parameter changes."""
+    key = tuple((p.data_ptr(), p._version) for p in params)
+    cache = func.__dict__.get("_nlbac_packed")
+    if cache is not None and cache[0] == key:
+        return cache[1]
+    L = _lib.lib()
+    n = L.nlbac_node_packed_floats(ctypes.byref(desc))
+    packed = torch.empty(n, dtype=torch.float32, device=params[0].device)
+    ptrs = (ctypes.c_void_p * len(params))(*[p.data_ptr() for p in params])
+    for p in params:
+        if p.dtype != torch.float32 or not p.is_contiguous():
+            raise TypeError("nlbac_b200.odeint: parameters must be contiguous float32")
+    _lib.check(L.nlbac_node_pack(ctypes.byref(desc), ptrs, packed.data_ptr(),
+                                 torch.cuda.current_stream().cuda_stream), "node_pack")
+    func.__dict__["_nlbac_packed"] = (key, packed)
+    return packed
+
+
+def _farr(x):
+    a = np.ascontiguousarray(x, dtype=np.float32)
+    return a, a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+
+
+def _grid_from_step_size(t, step_size):
+    """FixedGridODESolver._grid_constructor_from_step_size, in t's float32 arithmetic."""
+    tt = torch.as_tensor(t, dtype=torch.float32)
+    niters = int(torch.ceil((tt[-1] - tt[0]) / step_size + 1).item())
+    grid = torch.arange(0, niters, dtype=torch.float32) * step_size + tt[0]
+    grid[-1] = tt[-1]
+    return grid.numpy()
+
+
+class _FixedSolve(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y0, desc, packed, t_np, grid_np, method, precision, want_ckpt, *params):
+        L = _lib.lib()
+        B, D = y0.shape
+        n_t, n_grid = len(t_np), len(grid_np)
+        y0c = y0.detach().contiguous()
+        fwd, ck, bwd = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_size_t()
+        _lib.check(L.nlbac_node_workspace_bytes(ctypes.byref(desc), B, n_grid, n_t, method, ctypes.byref(fwd),
+                                                ctypes.byref(ck), ctypes.byref(bwd)), "workspace_bytes")
+        dev = y0.device
+        ws = torch.empty(max(fwd.value, 16), dtype=torch.uint8, device=dev)
+        ckpt = torch.empty(max(ck.value // 4, 1), dtype=torch.float32, device=dev) if want_ckpt else None
+        y_out = torch.empty((n_t, B, D), dtype=torch.float32, device=dev)
+        _, tp = _farr(t_np)
+        _, gp = _farr(grid_np)
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(L.nlbac_node_solve_fwd(ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, tp, n_t, gp,
+                                          n_grid, method, precision, y_out.data_ptr(),
+                                          ckpt.data_ptr() if want_ckpt else None, ws.data_ptr(), st), "node_solve_fwd")
+        if want_ckpt:
+            ctx.save_for_backward(y0c, packed, ckpt)
+            ctx.meta = (desc, t_np, grid_np, method, precision, bwd.value, [p.shape for p in params])
+        return y_out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        L = _lib.lib()
+        y0c, packed, ckpt = ctx.saved_tensors
+        desc, t_np, grid_np, method, precision, bwd_bytes, shapes = ctx.meta
+        B, D = y0c.shape
+        dev = y0c.device
+        need_y0 = ctx.needs_input_grad[0]
+        need_p = any(ctx.needs_input_grad[8:])
+        go = grad_out.contiguous()
+        ws = torch.empty(max(bwd_bytes, 16), dtype=torch.uint8, device=dev)
+        gy0 = torch.empty((B, D), dtype=torch.float32, device=dev) if need_y0 else None
+        n_param = L.nlbac_node_param_count(ctypes.byref(desc))
+        gflat = torch.empty(n_param, dtype=torch.float32, device=dev) if need_p else None
+        _, tp = _farr(t_np)
+        _, gp = _farr(grid_np)
+        st = torch.cuda.current_stream().cuda_stream
+        _lib.check(L.nlbac_node_solve_bwd(ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, tp, len(t_np), gp,
+                                          len(grid_np), method, precision, ckpt.data_ptr(), go.data_ptr(),
+                                          gy0.data_ptr() if need_y0 else None,
+                                          gflat.data_ptr() if need_p else None, ws.data_ptr(), st), "node_solve_bwd")
+        grads = []
+        if need_p:
+            off = 0
+            for shp in shapes:
+                n = int(np.prod(shp))
+                grads.append(gflat[off:off + n].view(shp))
+                off += n
+        else:
+            grads = [None] * len(shapes)
+        return (gy0, None, None, None, None, None, None, None, *grads)
+
+
+def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None, precision="fp32"):
+    """torchdiffeq.odeint for a NeuralODEModel right-hand side, fused on the GPU.
+
+    Same argument meaning and error behaviour as torchdiffeq 0.2.3 for what the reference uses:
+    unknown ``method`` -> ValueError; non-monotone ``t`` -> AssertionError; ``rtol``/``atol`` are
+    ignored by the fixed-grid solvers; ``options={'step_size': h}`` sub-steps the grid.
+    """
+    if event_fn is not None:
+        raise NotImplementedError("nlbac_b200.odeint: event handling is not on the NLBAC path")
+    if not torch.is_tensor(y0):
+        raise NotImplementedError("nlbac_b200.odeint: tuple state is not on the NLBAC path")
+    if method is None:
+        method = "dopri5"
+    if method not in METHODS:
+        raise ValueError('Invalid method "{}". Must be one of {}'.format(
+            method, '{"' + '", "'.join(METHODS) + '"}.'))
+    if precision not in PRECISIONS:
+        raise ValueError("precision must be one of %s" % list(PRECISIONS))
+    if not y0.is_cuda:
+        raise RuntimeError("nlbac_b200.odeint: y0 must be a CUDA tensor (no CPU fallback)")
+    if y0.dtype != torch.float32 or y0.ndim != 2:
+        raise TypeError("nlbac_b200.odeint: y0 must be float32 [batch, state]")
+    t_np = (t.detach().to("cpu", torch.float32).numpy() if torch.is_tensor(t)
+            else np.asarray(t, dtype=np.float32))
+    if t_np.ndim != 1:
+        raise ValueError("t must be one dimensional")
+    d = np.diff(t_np)
+    assert (d > 0).all() or (d < 0).all(), "t must be strictly increasing or decreasing"
+    if len(d) and (d < 0).all():
+        raise NotImplementedError("nlbac_b200.odeint: decreasing t is not on the NLBAC path")
+    options = dict(options or {})
+    desc, params = describe(func, y0.shape[1])
+    L = _lib.lib()
+    prec = PRECISIONS[precision]
+    _lib.check(L.nlbac_node_supported(ctypes.byref(desc), prec), "node_supported")
+    packed = _packed(func, desc, params)
+    if len(t_np) == 1:
+        return y0.unsqueeze(0).clone()
+    if y0.shape[0] == 0:
+        return y0.new_empty((len(t_np),) + tuple(y0.shape))
+    need_grad = torch.is_grad_enabled() and (y0.requires_grad or any(p.requires_grad for p in params))
+    if method in _FIXED:
+        step_size = options.pop("step_size", None)
+        grid_np = t_np if step_size is None else _grid_from_step_size(t_np, float(step_size))
+        return _FixedSolve.apply(y0, desc, packed, t_np, grid_np, METHODS[method], prec, need_grad, *params)
+    from .dopri5 import dopri5_solve
+    return dopri5_solve(func, y0, desc, packed, params, t_np, float(rtol), float(atol), prec, need_grad, options)

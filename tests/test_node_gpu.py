@@ -1,0 +1,218 @@
+"""GPU parity of the fused NODE solve (forward + backward) through the C ABI.
+
+Oracle: oracle/torchdiffeq_restated.odeint driving oracle/nlbac_ref models on CPU (fp32, with an fp64
+run as tie-breaker), plus the committed golden vectors produced by the reference's own classes.
+Tolerance (BASELINE.json north_star): rel 1e-5 in fp32, measured as max|a-b| / max|b| per tensor.
+"""
+import os
+
+import pytest
+import torch
+
+from oracle import nlbac_ref
+from oracle.torchdiffeq_restated import odeint as oracle_odeint
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def _rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+def _models(tag, seed=0):
+    import nlbac_b200
+    torch.manual_seed(seed)
+    if tag == "U":
+        ref = nlbac_ref.AffineNODE(3, 3, 6)
+        ours = nlbac_b200.NeuralODEModel(3, 3, 6)
+    elif tag == "P":
+        ref = nlbac_ref.AffineNODE(6, 6, 12)
+        ours = nlbac_b200.NeuralODEModel(6, 6, 12)
+    elif tag == "C":
+        ref = nlbac_ref.BlackBoxNODE(12, 10)
+        ours = nlbac_b200.NeuralODEModel(12, 10)
+    else:  # quadrotor-shaped (assumed hidden 64), black-box 8 -> 6 with two action columns
+        ref = nlbac_ref.BlackBoxNODE(8, 6)
+        ours = nlbac_b200.NeuralODEModel(8, 6, n_u=2)
+    # make the thin layers and biases matter
+    with torch.no_grad():
+        for p in ref.parameters():
+            p.mul_(1.5)
+    ours.load_state_dict(ref.state_dict())
+    return ref, ours.cuda()
+
+
+def _y0(tag, B, seed=1):
+    g = torch.Generator().manual_seed(seed)
+    D = {"U": 5, "P": 8, "C": 12, "Q": 8}[tag]
+    y = torch.randn(B, D, generator=g)
+    if tag == "C":
+        y[:, :10] = y[:, :10] * 3 + torch.tensor([42.0, 3, 34, 3, 26, 3, 18, 3, 10, 3])
+    return y
+
+
+def _run_pair(tag, B, method, t, options=None, seed=0):
+    import nlbac_b200
+    ref, ours = _models(tag, seed)
+    y0 = _y0(tag, B)
+    g = torch.Generator().manual_seed(5)
+    cot = torch.randn(len(t), B, y0.shape[1], generator=g)
+    # oracle, fp32 and fp64
+    outs = {}
+    for name, dt_ in (("f32", torch.float32), ("f64", torch.float64)):
+        m = ref.to(dt_)
+        y = y0.to(dt_).requires_grad_(True)
+        m.zero_grad()
+        sol = oracle_odeint(m, y, t.to(dt_), method=method, options=options)
+        (sol * cot.to(dt_)).sum().backward()
+        outs[name] = (sol.detach(), y.grad.clone(), [p.grad.clone() for p in m.parameters()])
+    ref.to(torch.float32)
+    yg = y0.cuda().requires_grad_(True)
+    ours.zero_grad()
+    sol = nlbac_b200.odeint(ours, yg, t.cuda(), method=method, options=options, atol=1e-7, rtol=1e-5)
+    (sol * cot.cuda()).sum().backward()
+    got = (sol.detach(), yg.grad, [p.grad for p in ours.parameters()])
+    return got, outs
+
+
+def _check(got, outs, what):
+    names = ["sol", "grad_y0"] + ["grad_p%d" % i for i in range(len(got[2]))]
+    flat_got = [got[0], got[1]] + list(got[2])
+    flat32 = [outs["f32"][0], outs["f32"][1]] + list(outs["f32"][2])
+    flat64 = [outs["f64"][0], outs["f64"][1]] + list(outs["f64"][2])
+    for n, a, b32, b64 in zip(names, flat_got, flat32, flat64):
+        e32 = _rel(a, b32)
+        if e32 <= TOL:
+            continue
+        # tie-breaker: the fp32 CPU oracle has its own round-off; judge both against fp64
+        e64, o64 = _rel(a, b64), _rel(b32, b64)
+        assert e64 <= max(TOL, 2 * o64), (what, n, e32, e64, o64)
+
+
+@pytest.mark.parametrize("tag", ["U", "P", "C", "Q"])
+@pytest.mark.parametrize("method", ["euler", "midpoint", "rk4"])
+@pytest.mark.parametrize("B", [1, 33, 128])
+def test_one_step_matches_oracle(tag, method, B):
+    t = torch.tensor([0.0, 0.02])
+    got, outs = _run_pair(tag, B, method, t)
+    _check(got, outs, (tag, method, B))
+
+
+@pytest.mark.parametrize("tag", ["U", "P", "C"])
+def test_rk4_20_steps_all_outputs(tag):
+    t = 0.02 * torch.arange(21, dtype=torch.float32)
+    got, outs = _run_pair(tag, 77, "rk4", t)
+    _check(got, outs, (tag, "rk4x20"))
+
+
+@pytest.mark.parametrize("method", ["euler", "rk4"])
+def test_step_size_option_interpolates(method):
+    t = torch.tensor([0.0, 0.05, 0.1])
+    got, outs = _run_pair("U", 50, method, t, options={"step_size": 0.02})
+    _check(got, outs, (method, "step_size"))
+
+
+@pytest.mark.parametrize("tag,B", [("U", 5000), ("P", 4800), ("C", 6000)])
+def test_medium_tiles(tag, B):
+    """B > 32*SMs selects the 128-trajectory forward tile and the 64-trajectory backward tile."""
+    got, outs = _run_pair(tag, B, "rk4", torch.tensor([0.0, 0.02, 0.04]))
+    _check(got, outs, (tag, B))
+
+
+def test_large_tiles_unicycle():
+    """B >= 2*256*SMs selects the 256-trajectory forward tile (ragged last tile)."""
+    got, outs = _run_pair("U", 2 * 256 * 148 + 37, "euler", torch.tensor([0.0, 0.02]))
+    _check(got, outs, "U large")
+
+
+@pytest.mark.parametrize("tag", ["U", "C", "P"])
+def test_golden_from_reference(tag, golden_dir):
+    import nlbac_b200
+    g = torch.load(os.path.join(golden_dir, "node_%s.pt" % tag), weights_only=False)
+    ours = (nlbac_b200.NeuralODEModel(3, 3, 6) if tag == "U" else
+            nlbac_b200.NeuralODEModel(6, 6, 12) if tag == "P" else nlbac_b200.NeuralODEModel(12, 10))
+    ours.load_state_dict(g["state_dict"])
+    ours.cuda()
+    for name, c in g["cases"].items():
+        if c["method"] == "dopri5":
+            continue
+        y0 = g["y0"].cuda().requires_grad_(True)
+        ours.zero_grad()
+        sol = nlbac_b200.odeint(ours, y0, c["t"], method=c["method"], options=c["options"], atol=1e-7, rtol=1e-5)
+        assert _rel(sol, c["sol"]) <= TOL, name
+        (sol * c["cot"].cuda()).sum().backward()
+        assert _rel(y0.grad, c["grad_y0"]) <= 2 * TOL, name
+        for k, p in ours.named_parameters():
+            assert _rel(p.grad, c["grad_params"][k]) <= 2 * TOL, (name, k)
+
+
+@pytest.mark.parametrize("tag", ["U", "C", "P"])
+def test_train_step_trace_golden(tag, golden_dir):
+    import nlbac_b200
+    g = torch.load(os.path.join(golden_dir, "node_%s.pt" % tag), weights_only=False)
+    ours = (nlbac_b200.NeuralODEModel(3, 3, 6) if tag == "U" else
+            nlbac_b200.NeuralODEModel(6, 6, 12) if tag == "P" else nlbac_b200.NeuralODEModel(12, 10))
+    ours.load_state_dict(g["state_dict"])
+    ours.cuda()
+    n_s = g["n_s"]
+    y0 = g["y0"].cuda()
+    x, u = y0[:, :n_s].contiguous(), y0[:, n_s:n_s + (1 if tag == "C" else 2)].contiguous()
+    opt = torch.optim.Adam(ours.parameters(), lr=1e-3)
+    tr = g["train"]
+    nxt = tr["next_state"].cuda()
+    for want in tr["losses"]:
+        if tag == "C":
+            got = nlbac_b200.train_step(ours, x, u, nxt, y0[:, 11:12].contiguous(), opt, torch.nn.MSELoss(),
+                                        tr["horizon"], "euler", 0.02)
+        else:
+            got = nlbac_b200.train_step(ours, x, u, nxt, opt, torch.nn.MSELoss(), tr["horizon"], "euler", 0.02)
+        assert abs(got - want) <= 1e-5 * abs(want) + 1e-9
+    for k, v in ours.state_dict().items():
+        assert _rel(v, tr["state_dict_after"][k]) <= 1e-4, k   # Adam's 1/sqrt(v) amplifies round-off
+
+
+def test_properties_at_full_size():
+    """BASELINE config-5 shape (2^20 Unicycle trajectories x 20 rk4 steps): size-independent checks."""
+    import nlbac_b200
+    _, ours = _models("U")
+    B = 1 << 20
+    g = torch.Generator(device="cuda").manual_seed(1234)
+    y0 = torch.rand(B, 5, generator=g, device="cuda") * 2 - 1
+    t20 = 0.02 * torch.arange(21, dtype=torch.float32)
+    with torch.no_grad():
+        full = nlbac_b200.odeint(ours, y0, t20, method="rk4")
+        half = nlbac_b200.odeint(ours, y0, t20[:11], method="rk4")
+        rest = nlbac_b200.odeint(ours, half[-1], t20[10:], method="rk4")
+    assert torch.equal(full[0], y0)
+    assert torch.equal(full[:, :, 3:], y0[None, :, 3:].expand(21, -1, -1))      # action columns are constants
+    assert torch.equal(full[:11], half)                                          # prefix property
+    assert _rel(rest[-1], full[-1]) <= TOL                                       # step-count additivity
+    # linearity of the backward in the cotangent, and agreement of a row subset with a small solve
+    sub = y0[:257].clone().requires_grad_(True)
+    s1 = nlbac_b200.odeint(ours, sub, t20, method="rk4")[-1]
+    assert torch.equal(s1.detach(), full[-1][:257]) or _rel(s1, full[-1][:257]) <= 1e-6
+    c = torch.randn_like(s1)
+    g1, = torch.autograd.grad((s1 * c).sum(), sub, retain_graph=True)
+    g2, = torch.autograd.grad((s1 * (2 * c)).sum(), sub)
+    assert _rel(g2, 2 * g1) <= 1e-6
+
+
+def test_empty_batch_and_errors():
+    import nlbac_b200
+    _, ours = _models("U")
+    out = nlbac_b200.odeint(ours, torch.empty(0, 5, device="cuda"), torch.tensor([0.0, 0.02]), method="euler")
+    assert out.shape == (2, 0, 5)
+    y0 = torch.randn(4, 5, device="cuda")
+    with pytest.raises(ValueError):
+        nlbac_b200.odeint(ours, y0, torch.tensor([0.0, 0.02]), method="rk45")
+    with pytest.raises(AssertionError):
+        nlbac_b200.odeint(ours, y0, torch.tensor([0.0, 0.02, 0.01]), method="euler")
+    with pytest.raises(TypeError):
+        nlbac_b200.odeint(torch.nn.Linear(5, 5).cuda(), y0, torch.tensor([0.0, 0.02]), method="euler")
+    with pytest.raises(RuntimeError):
+        nlbac_b200.odeint(ours, y0.cpu(), torch.tensor([0.0, 0.02]), method="euler")
+    odd = nlbac_b200.NeuralODEModel(4, 4, 8).cuda()          # no compiled instance for this shape
+    with pytest.raises(RuntimeError):
+        nlbac_b200.odeint(odd, torch.randn(4, 6, device="cuda"), torch.tensor([0.0, 0.02]), method="euler")
