@@ -63,13 +63,13 @@ def _run_pair(tag, B, method, t, options=None, seed=0):
     outs = {}
     for name, dt_ in (("f32", torch.float32), ("f64", torch.float64)):
         m = ref.to(dt_)
-        y = y0.to(dt_).requires_grad_(True)
+        y = y0.detach().clone().to(dt_).requires_grad_(True)
         m.zero_grad()
         sol = oracle_odeint(m, y, t.to(dt_), method=method, options=options)
         (sol * cot.to(dt_)).sum().backward()
         outs[name] = (sol.detach(), y.grad.clone(), [p.grad.clone() for p in m.parameters()])
     ref.to(torch.float32)
-    yg = y0.cuda().requires_grad_(True)
+    yg = y0.detach().clone().cuda().requires_grad_(True)
     ours.zero_grad()
     sol = nlbac_b200.odeint(ours, yg, t.cuda(), method=method, options=options, atol=1e-7, rtol=1e-5)
     (sol * cot.cuda()).sum().backward()
