@@ -107,6 +107,10 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
  * FLOPs one launch executes in *flops; the caller times it with CUDA events. */
 int nlbac_fp32_peak_probe(int iters, float* sink, double* flops, void* stream);
 
+/* Same, for register-fed outer-product loops shaped like the GEMM micro-kernel: variant 0 scalar FFMA with
+ * three distinct register operands, variant 1 packed fma.rn.f32x2 (sm_100 FFMA2). */
+int nlbac_fma_shape_probe(int variant, int iters, float* sink, double* flops, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -76,6 +76,7 @@ def _declare(lib):
     lib.nlbac_node_solve_bwd.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, fp, c.c_int, c.c_int, c.c_int,
                                          vp, vp, vp, vp, vp, vp]
     lib.nlbac_fp32_peak_probe.argtypes = [c.c_int, vp, c.POINTER(c.c_double), vp]
+    lib.nlbac_fma_shape_probe.argtypes = [c.c_int, c.c_int, vp, c.POINTER(c.c_double), vp]
     return lib
 
 

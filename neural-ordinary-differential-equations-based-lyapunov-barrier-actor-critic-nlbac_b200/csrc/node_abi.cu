@@ -141,6 +141,54 @@ __global__ void fp32_peak_kernel(int iters, float* sink) {
   if (s == 123.456f) sink[0] = s;
 }
 
+// Register-only outer-product loops shaped like the GEMM micro-kernel (acc[i][j] += a[i] * w[j], all three
+// operands distinct registers): variant 0 = scalar FFMA, variant 1 = packed fma.rn.f32x2 (FFMA2) with the
+// a operand duplicated into a 64-bit pair.  They measure what the FMA pipe sustains when it is fed from the
+// register file rather than from an immediate (the plain peak probe).
+template <int VARIANT>
+__global__ void __launch_bounds__(256, 1) fma_shape_kernel(int iters, float* sink) {
+  constexpr int TT = 8, NN = 12;
+  float a[TT], w[NN], acc[TT][NN];
+#pragma unroll
+  for (int i = 0; i < TT; ++i) a[i] = 1e-3f * (threadIdx.x + i);
+#pragma unroll
+  for (int j = 0; j < NN; ++j) w[j] = 1e-3f * (blockIdx.x + j);
+#pragma unroll
+  for (int i = 0; i < TT; ++i)
+#pragma unroll
+    for (int j = 0; j < NN; ++j) acc[i][j] = 0.f;
+  for (int it = 0; it < iters; ++it) {
+    if (VARIANT == 0) {
+#pragma unroll
+      for (int i = 0; i < TT; ++i)
+#pragma unroll
+        for (int j = 0; j < NN; ++j) acc[i][j] = fmaf(a[i], w[j], acc[i][j]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < TT; ++i) {
+        unsigned long long aa;
+        asm volatile("mov.b64 %0, {%1, %1};" : "=l"(aa) : "f"(a[i]));
+#pragma unroll
+        for (int j = 0; j < NN; j += 2) {
+          unsigned long long ww, cc;
+          asm volatile("mov.b64 %0, {%1, %2};" : "=l"(ww) : "f"(w[j]), "f"(w[j + 1]));
+          asm volatile("mov.b64 %0, {%1, %2};" : "=l"(cc) : "f"(acc[i][j]), "f"(acc[i][j + 1]));
+          asm volatile("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(cc) : "l"(aa), "l"(ww));
+          asm volatile("mov.b64 {%0, %1}, %2;" : "=f"(acc[i][j]), "=f"(acc[i][j + 1]) : "l"(cc));
+        }
+      }
+    }
+    // keep a and w live and changing without adding FMA-pipe work worth mentioning
+    a[it & 7] += 1e-7f;
+  }
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < TT; ++i)
+#pragma unroll
+    for (int j = 0; j < NN; ++j) s += acc[i][j];
+  if (s == 123.456f) sink[0] = s;
+}
+
 }  // namespace nlbac
 
 using namespace nlbac;
@@ -202,9 +250,11 @@ int nlbac_node_solve_fwd(const nlbac_node_desc* desc, const float* packed, const
     a.packed = packed; a.y0 = y0; a.y_out = y_out; a.ckpt = ckpt; a.B = B;
     a.n_steps = n_grid - 1; a.n_t = n_t; a.method = method;
     if (int rc = upload_schedule(s, ws, st, &a.dts, &a.out_step, &a.out_w)) return rc;
+    // largest tile that still gives every SM at least one tile
     const long long sms = sm_count();
-    if (B >= 2 * 256 * sms) return launch_fwd<C, 256>(a, st);
-    if (B > 32 * sms) return launch_fwd<C, 128>(a, st);
+    if ((B + 255) / 256 >= sms) return launch_fwd<C, 256>(a, st);
+    if ((B + 127) / 128 >= sms) return launch_fwd<C, 128>(a, st);
+    if ((B + 63) / 64 >= sms) return launch_fwd<C, 64>(a, st);
     return launch_fwd<C, 32>(a, st);
   });
 }
@@ -235,7 +285,7 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
       NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
     }
     a.grad_rep = rep;
-    int rc = (B > 32LL * sm_count()) ? launch_bwd<C, 64>(a, st) : launch_bwd<C, 32>(a, st);
+    int rc = ((B + 63) / 64 >= sm_count()) ? launch_bwd<C, 64>(a, st) : launch_bwd<C, 32>(a, st);
     if (rc) return rc;
     if (grad_params) {
       GradTable gt = build_grad_table<C>();
@@ -244,6 +294,16 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
     }
     return 0;
   });
+}
+
+int nlbac_fma_shape_probe(int variant, int iters, float* sink, double* flops, void* stream) {
+  NLBAC_REQUIRE(iters > 0 && sink && (variant == 0 || variant == 1), "bad arguments");
+  const int blocks = sm_count() * 2, threads = 256;
+  if (variant == 0) fma_shape_kernel<0><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, sink);
+  else fma_shape_kernel<1><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, sink);
+  NLBAC_CUDA(cudaGetLastError());
+  if (flops) *flops = 2.0 * 8 * 12 * (double)iters * blocks * threads;
+  return 0;
 }
 
 int nlbac_fp32_peak_probe(int iters, float* sink, double* flops, void* stream) {

@@ -55,28 +55,46 @@ struct WeightRing {
 };
 
 // ---------------------------------------------------------------------------------------------
-// acc[i][0..8) = bias[n0..n0+8) + sum_{k<K} in[row_i][k] * W[k][n0..n0+8),   row_i = tg + TG*i
-// K % 4 == 0.  in: ld = ldi floats (rows 16-byte aligned), W: [K][ldw], n0 % 8 == 0.
+// Column ownership of a thread in a [rows][HP] tile.  8 column groups (ng = 0..7); group ng owns
+//   4 consecutive columns at 32*v + 4*ng for v < NV4      (LDS.128 / STS.128, 16-byte aligned)
+//   1 column at 32*NV4 + ng when HP % 32 == 8             (HP = 104: 13 columns per thread)
+// so a warp of 32 row-threads x 1 column group reads weight rows as broadcasts, and 8 column groups
+// x T/TT row-threads give a warp count that is a multiple of 4 (balanced over the 4 SM sub-partitions).
 // ---------------------------------------------------------------------------------------------
-template <int TT, int TG>
-__device__ __forceinline__ void gemm_tile(const float* __restrict__ in, int ldi, const float* __restrict__ W, int ldw,
-                                          const float* __restrict__ bias, int K, int tg, int n0, float (&acc)[TT][8]) {
-  if (bias != nullptr) {
-    const float4 b0 = *reinterpret_cast<const float4*>(bias + n0);
-    const float4 b1 = *reinterpret_cast<const float4*>(bias + n0 + 4);
+template <int HP>
+struct ColMap {
+  static constexpr int NV4 = HP / 32;
+  static constexpr int NREM = (HP % 32) / 8;
+  static constexpr int NN = 4 * NV4 + NREM;
+  static_assert(HP % 32 == 0 || HP % 32 == 8, "column map supports HP = 32m or 32m + 8");
+  __device__ __forceinline__ static int col(int ng, int j) { return j < 4 * NV4 ? 32 * (j / 4) + 4 * ng + (j % 4) : 32 * NV4 + ng; }
+};
+
+// acc[i][j] = bias[col j] + sum_{k<K} in[row_i][k] * W[k][col j],   row_i = tg + TG*i,  K % 4 == 0
+// Inner product runs on packed FFMA2: the 4*NV4 vector columns as pairs, the remainder column scalar.
+template <int TT, int TG, int HP>
+__device__ __forceinline__ void gemm_tile(const float* __restrict__ in, int ldi, const float* __restrict__ W,
+                                          const float* __restrict__ bias, int K, int tg, int ng,
+                                          float (&acc)[TT][ColMap<HP>::NN]) {
+  using CM = ColMap<HP>;
+  constexpr int NP = 2 * CM::NV4;  // column pairs
+  unsigned long long acc2[TT][NP];
+  float accr[TT];
+  {
+    unsigned long long b2[NP];
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+      b2[p] = bias != nullptr ? pack2(bias[CM::col(ng, 2 * p)], bias[CM::col(ng, 2 * p + 1)]) : 0ull;
+    const float br = (CM::NREM && bias != nullptr) ? bias[CM::col(ng, CM::NN - 1)] : 0.f;
 #pragma unroll
     for (int i = 0; i < TT; ++i) {
-      acc[i][0] = b0.x; acc[i][1] = b0.y; acc[i][2] = b0.z; acc[i][3] = b0.w;
-      acc[i][4] = b1.x; acc[i][5] = b1.y; acc[i][6] = b1.z; acc[i][7] = b1.w;
+#pragma unroll
+      for (int p = 0; p < NP; ++p) acc2[i][p] = b2[p];
+      accr[i] = br;
     }
-  } else {
-#pragma unroll
-    for (int i = 0; i < TT; ++i)
-#pragma unroll
-      for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
   }
   const float* inp = in + tg * ldi;
-  const float* wp = W + n0;
+  const float* wp = W + 4 * ng;
 #pragma unroll 1
   for (int k = 0; k < K; k += 4) {
     float a[TT][4];
@@ -87,45 +105,68 @@ __device__ __forceinline__ void gemm_tile(const float* __restrict__ in, int ldi,
     }
 #pragma unroll
     for (int kk = 0; kk < 4; ++kk) {
-      const float4 w0 = *reinterpret_cast<const float4*>(wp + (k + kk) * ldw);
-      const float4 w1 = *reinterpret_cast<const float4*>(wp + (k + kk) * ldw + 4);
+      unsigned long long w2[NP];
+      const float* wr = wp + (k + kk) * HP;
+#pragma unroll
+      for (int v = 0; v < CM::NV4; ++v) {
+        const float4 q = *reinterpret_cast<const float4*>(wr + 32 * v);
+        w2[2 * v] = pack2(q.x, q.y);
+        w2[2 * v + 1] = pack2(q.z, q.w);
+      }
+      float wrem = 0.f;
+      if (CM::NREM) wrem = W[(k + kk) * HP + 32 * CM::NV4 + ng];
 #pragma unroll
       for (int i = 0; i < TT; ++i) {
-        const float av = a[i][kk];
-        acc[i][0] = fmaf(av, w0.x, acc[i][0]); acc[i][1] = fmaf(av, w0.y, acc[i][1]);
-        acc[i][2] = fmaf(av, w0.z, acc[i][2]); acc[i][3] = fmaf(av, w0.w, acc[i][3]);
-        acc[i][4] = fmaf(av, w1.x, acc[i][4]); acc[i][5] = fmaf(av, w1.y, acc[i][5]);
-        acc[i][6] = fmaf(av, w1.z, acc[i][6]); acc[i][7] = fmaf(av, w1.w, acc[i][7]);
+        const unsigned long long aa = pack2(a[i][kk], a[i][kk]);
+#pragma unroll
+        for (int p = 0; p < NP; ++p) acc2[i][p] = fma2(aa, w2[p], acc2[i][p]);
+        if (CM::NREM) accr[i] = fmaf(a[i][kk], wrem, accr[i]);
       }
     }
   }
-}
-
-// out[row_i][n0..n0+8) = relu(acc[i][:])
-template <int TT, int TG>
-__device__ __forceinline__ void store_relu(float* __restrict__ out, int ldo, int tg, int n0, const float (&acc)[TT][8]) {
 #pragma unroll
   for (int i = 0; i < TT; ++i) {
-    float* o = out + (size_t)(tg + TG * i) * ldo + n0;
-    *reinterpret_cast<float4*>(o) =
-        make_float4(fmaxf(acc[i][0], 0.f), fmaxf(acc[i][1], 0.f), fmaxf(acc[i][2], 0.f), fmaxf(acc[i][3], 0.f));
-    *reinterpret_cast<float4*>(o + 4) =
-        make_float4(fmaxf(acc[i][4], 0.f), fmaxf(acc[i][5], 0.f), fmaxf(acc[i][6], 0.f), fmaxf(acc[i][7], 0.f));
+#pragma unroll
+    for (int p = 0; p < NP; ++p) unpack2(acc2[i][p], acc[i][2 * p], acc[i][2 * p + 1]);
+    if (CM::NREM) acc[i][CM::NN - 1] = accr[i];
   }
 }
 
-// out[row_i][n0..) = acc[i][:] where mask[row_i][n0..] > 0 else 0   (ReLU backward; out may alias mask)
-template <int TT, int TG>
-__device__ __forceinline__ void store_masked(float* out, int ldo, int tg, int n0, const float (&acc)[TT][8]) {
+// out[row_i][col j] = relu(acc[i][j])
+template <int TT, int TG, int HP>
+__device__ __forceinline__ void store_relu(float* __restrict__ out, int ldo, int tg, int ng,
+                                           const float (&acc)[TT][ColMap<HP>::NN]) {
+  using CM = ColMap<HP>;
 #pragma unroll
   for (int i = 0; i < TT; ++i) {
-    float* o = out + (size_t)(tg + TG * i) * ldo + n0;
-    const float4 m0 = *reinterpret_cast<const float4*>(o);
-    const float4 m1 = *reinterpret_cast<const float4*>(o + 4);
-    *reinterpret_cast<float4*>(o) = make_float4(m0.x > 0.f ? acc[i][0] : 0.f, m0.y > 0.f ? acc[i][1] : 0.f,
-                                                m0.z > 0.f ? acc[i][2] : 0.f, m0.w > 0.f ? acc[i][3] : 0.f);
-    *reinterpret_cast<float4*>(o + 4) = make_float4(m1.x > 0.f ? acc[i][4] : 0.f, m1.y > 0.f ? acc[i][5] : 0.f,
-                                                    m1.z > 0.f ? acc[i][6] : 0.f, m1.w > 0.f ? acc[i][7] : 0.f);
+    float* o = out + (size_t)(tg + TG * i) * ldo;
+#pragma unroll
+    for (int v = 0; v < CM::NV4; ++v)
+      *reinterpret_cast<float4*>(o + 32 * v + 4 * ng) =
+          make_float4(fmaxf(acc[i][4 * v], 0.f), fmaxf(acc[i][4 * v + 1], 0.f), fmaxf(acc[i][4 * v + 2], 0.f),
+                      fmaxf(acc[i][4 * v + 3], 0.f));
+    if (CM::NREM) o[32 * CM::NV4 + ng] = fmaxf(acc[i][CM::NN - 1], 0.f);
+  }
+}
+
+// out[row_i][col j] = acc[i][j] where out[row_i][col j] > 0 else 0   (ReLU backward, in place over the activation)
+template <int TT, int TG, int HP>
+__device__ __forceinline__ void store_masked(float* out, int ldo, int tg, int ng, const float (&acc)[TT][ColMap<HP>::NN]) {
+  using CM = ColMap<HP>;
+#pragma unroll
+  for (int i = 0; i < TT; ++i) {
+    float* o = out + (size_t)(tg + TG * i) * ldo;
+#pragma unroll
+    for (int v = 0; v < CM::NV4; ++v) {
+      float4* p = reinterpret_cast<float4*>(o + 32 * v + 4 * ng);
+      const float4 m = *p;
+      *p = make_float4(m.x > 0.f ? acc[i][4 * v] : 0.f, m.y > 0.f ? acc[i][4 * v + 1] : 0.f,
+                       m.z > 0.f ? acc[i][4 * v + 2] : 0.f, m.w > 0.f ? acc[i][4 * v + 3] : 0.f);
+    }
+    if (CM::NREM) {
+      float* p = o + 32 * CM::NV4 + ng;
+      *p = *p > 0.f ? acc[i][CM::NN - 1] : 0.f;
+    }
   }
 }
 

@@ -31,10 +31,11 @@ struct BwdArgs {
 
 template <class C, int TB>
 struct BwdGeom {
-  static constexpr int TT = TB / 16;
-  static constexpr int TG = TB / TT;
-  static constexpr int NGRP = C::HP / 8;
+  static constexpr int TG = 32;
+  static constexpr int TT = TB / TG;
+  static constexpr int NGRP = 8;
   static constexpr int NT = TG * NGRP;
+  static_assert(TB % TG == 0 && TT >= 1, "tile size");
   static constexpr int CYC = 2 * C::NHID;  // packets per stage: forward (transposed) + backward (natural)
   static constexpr int NSLOT = (CYC * C::HID_BYTES <= 64 * 1024) ? CYC : 2;
   static constexpr int NBUF = C::NL_MAX - 1;  // stored activations per chain
@@ -45,7 +46,7 @@ struct BwdGeom {
   static constexpr int OFF_RING = OFF_RES + C::RES_ALL;
   static constexpr int OFF_BAR = OFF_RING + NSLOT * C::HID_FLOATS;
   static constexpr size_t SMEM_BYTES = (size_t)OFF_BAR * 4 + (NSLOT + 1) * 8;
-  static_assert(NT >= TB && NT >= NGRP * NGRP && NT >= C::H + C::OUTP_MAX, "thread roles");
+  static_assert(NT >= TB && NT >= (C::H / 4) * NGRP && NT >= C::H + C::OUTP_MAX, "thread roles");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
   // packet offset for ring sequence number s
@@ -58,36 +59,56 @@ struct BwdGeom {
   }
 };
 
-// dW[j0..j0+8)[k0..k0+8) = sum_t delta[t][j] * act[t][k]  -> vector reductions into grad (row stride ldg)
-template <int TB, int RS>
+// dW[4jg..4jg+4)[cols of kg] = sum_t delta[t][j] * act[t][k]  -> vector reductions into grad [H][H]
+template <int TB, int RS, int HP, int H>
 __device__ __forceinline__ void dw_tile_reduce(const float* __restrict__ delta, const float* __restrict__ act,
-                                               int j0, int k0, int nvalid_j, int nvalid_k, float* __restrict__ grad,
-                                               int ldg) {
-  float acc[8][8];
+                                               int jg, int kg, float* __restrict__ grad) {
+  using CM = ColMap<HP>;
+  constexpr int NP = 2 * CM::NV4;
+  unsigned long long acc2[4][NP];
+  float accr[4];
 #pragma unroll
-  for (int j = 0; j < 8; ++j)
+  for (int j = 0; j < 4; ++j) {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) acc[j][k] = 0.f;
+    for (int p = 0; p < NP; ++p) acc2[j][p] = 0ull;
+    accr[j] = 0.f;
+  }
 #pragma unroll 2
   for (int t = 0; t < TB; ++t) {
-    const float4 d0 = *reinterpret_cast<const float4*>(delta + t * RS + j0);
-    const float4 d1 = *reinterpret_cast<const float4*>(delta + t * RS + j0 + 4);
-    const float4 a0 = *reinterpret_cast<const float4*>(act + t * RS + k0);
-    const float4 a1 = *reinterpret_cast<const float4*>(act + t * RS + k0 + 4);
-    const float d[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
-    const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+    const float4 dv = *reinterpret_cast<const float4*>(delta + t * RS + 4 * jg);
+    const float d[4] = {dv.x, dv.y, dv.z, dv.w};
+    unsigned long long a2[NP];
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
+    for (int v = 0; v < CM::NV4; ++v) {
+      const float4 q = *reinterpret_cast<const float4*>(act + t * RS + 32 * v + 4 * kg);
+      a2[2 * v] = pack2(q.x, q.y);
+      a2[2 * v + 1] = pack2(q.z, q.w);
+    }
+    float arem = 0.f;
+    if (CM::NREM) arem = act[t * RS + 32 * CM::NV4 + kg];
 #pragma unroll
-      for (int k = 0; k < 8; ++k) acc[j][k] = fmaf(d[j], a[k], acc[j][k]);
+    for (int j = 0; j < 4; ++j) {
+      const unsigned long long dd = pack2(d[j], d[j]);
+#pragma unroll
+      for (int p = 0; p < NP; ++p) acc2[j][p] = fma2(dd, a2[p], acc2[j][p]);
+      if (CM::NREM) accr[j] = fmaf(d[j], arem, accr[j]);
+    }
+  }
+  float acc[4][CM::NN];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+#pragma unroll
+    for (int p = 0; p < NP; ++p) unpack2(acc2[j][p], acc[j][2 * p], acc[j][2 * p + 1]);
+    if (CM::NREM) acc[j][CM::NN - 1] = accr[j];
   }
 #pragma unroll
-  for (int j = 0; j < 8; ++j) {
-    if (j0 + j < nvalid_j) {
-      float* g = grad + (size_t)(j0 + j) * ldg + k0;
-      if (k0 < nvalid_k) red_add_v4(g, acc[j][0], acc[j][1], acc[j][2], acc[j][3]);
-      if (k0 + 4 < nvalid_k) red_add_v4(g + 4, acc[j][4], acc[j][5], acc[j][6], acc[j][7]);
-    }
+  for (int j = 0; j < 4; ++j) {
+    float* g = grad + (size_t)(4 * jg + j) * H;
+#pragma unroll
+    for (int v = 0; v < CM::NV4; ++v)
+      if (32 * v + 4 * kg < H)
+        red_add_v4(g + 32 * v + 4 * kg, acc[j][4 * v], acc[j][4 * v + 1], acc[j][4 * v + 2], acc[j][4 * v + 3]);
+    if (CM::NREM && 32 * CM::NV4 + kg < H) atomicAdd(g + 32 * CM::NV4 + kg, acc[j][CM::NN - 1]);
   }
 }
 
@@ -106,9 +127,9 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
   const float* sRes = smem + G::OFF_RES;
   const int tid = threadIdx.x;
   const bool owner = tid < TB;
-  const int tg = tid % G::TG, n0 = (tid / G::TG) * 8;
-  const int wj0 = (tid / G::NGRP) * 8, wk0 = (tid % G::NGRP) * 8;  // dW tile of this thread
-  const bool wactive = tid < G::NGRP * G::NGRP;
+  const int tg = tid % G::TG, ng = tid / G::TG;
+  const int wjg = tid / G::NGRP, wkg = tid % G::NGRP;  // dW tile of this thread: rows 4*wjg.., column group wkg
+  const bool wactive = 4 * wjg < H;
   auto off = [](uint32_t s) { return G::pkt_off(s); };
 
   if (owner) {
@@ -130,16 +151,16 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
   for (int c = 0; c < C::NCH; ++c) {
     const int n = C::nhc(c);
     const int OUT = C::out(c), OUTP = C::outp(c);
-    float acc[G::TT][8];
+    float acc[G::TT][ColMap<HP>::NN];
     // ---------------- forward with stored activations ----------------
-    gemm_tile<G::TT, G::TG>(sX, INP0, sRes + C::off_wt0(c), HP, sRes + C::off_b0(c), INP0, tg, n0, acc);
-    store_relu<G::TT, G::TG>(sAct, RS, tg, n0, acc);
+    gemm_tile<G::TT, G::TG, HP>(sX, INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), INP0, tg, ng, acc);
+    store_relu<G::TT, G::TG, HP>(sAct, RS, tg, ng, acc);
     __syncthreads();
 #pragma unroll 1
     for (int l = 1; l <= n; ++l) {
       const float* W = ring.acquire();
-      gemm_tile<G::TT, G::TG>(sAct + (l - 1) * TB * RS, RS, W, HP, sRes + C::off_bh(c, l), H, tg, n0, acc);
-      store_relu<G::TT, G::TG>(sAct + l * TB * RS, RS, tg, n0, acc);
+      gemm_tile<G::TT, G::TG, HP>(sAct + (l - 1) * TB * RS, RS, W, sRes + C::off_bh(c, l), H, tg, ng, acc);
+      store_relu<G::TT, G::TG, HP>(sAct + l * TB * RS, RS, tg, ng, acc);
       __syncthreads();
       ring.release(packed, off);
     }
@@ -188,9 +209,9 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
         atomicAdd(grep + C::goff_b(c, n + 1) + o, s);
       }
     }
-    gemm_tile<G::TT, G::TG>(sD, C::OUTP_MAX, sRes + C::off_wnl(c), HP, nullptr, OUTP, tg, n0, acc);
+    gemm_tile<G::TT, G::TG, HP>(sD, C::OUTP_MAX, sRes + C::off_wnl(c), nullptr, OUTP, tg, ng, acc);
     __syncthreads();
-    store_masked<G::TT, G::TG>(aL, RS, tg, n0, acc);
+    store_masked<G::TT, G::TG, HP>(aL, RS, tg, ng, acc);
     __syncthreads();
     // ---------------- hidden layers, reverse ----------------
 #pragma unroll 1
@@ -198,7 +219,7 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
       const float* dl = sAct + l * TB * RS;        // delta (pre-activation cotangent) of layer l
       float* ain = sAct + (l - 1) * TB * RS;       // its input activation
       if (grep != nullptr) {
-        if (wactive) dw_tile_reduce<TB, RS>(dl, ain, wj0, wk0, H, H, grep + C::goff_w(c, l), H);
+        if (wactive) dw_tile_reduce<TB, RS, HP, H>(dl, ain, wjg, wkg, grep + C::goff_w(c, l));
         if (tid < H) {
           float s = 0.f;
 #pragma unroll 4
@@ -207,10 +228,10 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
         }
       }
       const float* W = ring.acquire();
-      gemm_tile<G::TT, G::TG>(dl, RS, W, HP, nullptr, H, tg, n0, acc);
+      gemm_tile<G::TT, G::TG, HP>(dl, RS, W, nullptr, H, tg, ng, acc);
       __syncthreads();
       ring.release(packed, off);
-      store_masked<G::TT, G::TG>(ain, RS, tg, n0, acc);
+      store_masked<G::TT, G::TG, HP>(ain, RS, tg, ng, acc);
       __syncthreads();
     }
     // ---------------- first layer: dW0, db0 (thin), dx ----------------

@@ -27,10 +27,11 @@ struct FwdArgs {
 
 template <class C, int T>
 struct FwdGeom {
-  static constexpr int TT = T >= 128 ? 8 : T / 16;
-  static constexpr int TG = T / TT;
-  static constexpr int NGRP = C::HP / 8;
+  static constexpr int TG = 32;       // row-threads per column group = one warp
+  static constexpr int TT = T / TG;   // trajectories per thread
+  static constexpr int NGRP = 8;      // column groups (ColMap)
   static constexpr int NT = TG * NGRP;
+  static_assert(T % TG == 0 && TT >= 1, "tile size");
   static constexpr int NSLOT = C::NHID <= 2 ? C::NHID : 2;
   static constexpr int OFF_A = 0;
   static constexpr int OFF_X = OFF_A + T * C::RS;
@@ -51,7 +52,7 @@ __device__ __forceinline__ void eval_rhs_tile(const float* __restrict__ packed, 
   using G = FwdGeom<C, T>;
   const int tid = threadIdx.x;
   const bool owner = tid < T;
-  const int tg = tid % G::TG, n0 = (tid / G::TG) * 8;
+  const int tg = tid % G::TG, ng = tid / G::TG;
   auto off_t = [](uint32_t s) { return C::off_hid_t(s % C::NHID); };
 
   if (owner) {
@@ -69,19 +70,19 @@ __device__ __forceinline__ void eval_rhs_tile(const float* __restrict__ packed, 
   float fo[C::outp(0)];
 #pragma unroll
   for (int c = 0; c < C::NCH; ++c) {
-    float acc[G::TT][8];
+    float acc[G::TT][ColMap<C::HP>::NN];
     // first layer: sX -> sA
-    gemm_tile<G::TT, G::TG>(sX, C::INP0, sRes + C::off_wt0(c), C::HP, sRes + C::off_b0(c), C::INP0, tg, n0, acc);
-    store_relu<G::TT, G::TG>(sA, C::RS, tg, n0, acc);
+    gemm_tile<G::TT, G::TG, C::HP>(sX, C::INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), C::INP0, tg, ng, acc);
+    store_relu<G::TT, G::TG, C::HP>(sA, C::RS, tg, ng, acc);
     __syncthreads();
     // hidden layers, in place
 #pragma unroll 1
     for (int l = 1; l <= C::nhc(c); ++l) {
       const float* W = ring.acquire();
-      gemm_tile<G::TT, G::TG>(sA, C::RS, W, C::HP, sRes + C::off_bh(c, l), C::H, tg, n0, acc);
+      gemm_tile<G::TT, G::TG, C::HP>(sA, C::RS, W, sRes + C::off_bh(c, l), C::H, tg, ng, acc);
       __syncthreads();
       ring.release(packed, off_t);
-      store_relu<G::TT, G::TG>(sA, C::RS, tg, n0, acc);
+      store_relu<G::TT, G::TG, C::HP>(sA, C::RS, tg, ng, acc);
       __syncthreads();
     }
     // thin last layer, one thread per trajectory

@@ -77,7 +77,20 @@ def _run_pair(tag, B, method, t, options=None, seed=0):
     return got, outs
 
 
-def _check(got, outs, what):
+KINK_TOL = 1e-3
+
+
+def _check(got, outs, what, big=False):
+    """Tolerance: rel 1e-5 (max|a-b|/max|b| per tensor).  Tie-breaker against fp64 when the fp32 CPU
+    oracle's own round-off exceeds it.
+
+    big=True (B > 8192).  A solve evaluates ~1e8 ReLU pre-activations; a handful land within fp32
+    round-off of zero, and whichever side of zero an implementation rounds to decides that unit's
+    derivative mask for that one sample.  tools/diag_parity.py (profiles/parity_diag_r1.txt) shows the
+    fp32 CPU oracle and the CUDA path each flip ~1 mask per 4e4-sample solve relative to fp64, moving
+    ONE row of grad_y0 and the summed parameter gradients by ~1e-4.  No fp32 implementation can meet
+    1e-5 on those entries, so for big batches: the solution stays at 1e-5, grad_y0 may have at most
+    a few kink rows, and parameter gradients get KINK_TOL."""
     names = ["sol", "grad_y0"] + ["grad_p%d" % i for i in range(len(got[2]))]
     flat_got = [got[0], got[1]] + list(got[2])
     flat32 = [outs["f32"][0], outs["f32"][1]] + list(outs["f32"][2])
@@ -86,9 +99,16 @@ def _check(got, outs, what):
         e32 = _rel(a, b32)
         if e32 <= TOL:
             continue
-        # tie-breaker: the fp32 CPU oracle has its own round-off; judge both against fp64
         e64, o64 = _rel(a, b64), _rel(b32, b64)
-        assert e64 <= max(TOL, 2 * o64), (what, n, e32, e64, o64)
+        if e64 <= max(TOL, 2 * o64):
+            continue
+        assert big and n != "sol", (what, n, e32, e64, o64)
+        if n == "grad_y0":
+            d = (a.detach().double().cpu() - b64).abs().max(1).values
+            bad = int((d > TOL * b64.abs().max()).sum())
+            assert bad <= max(2, a.shape[0] // 10000), (what, n, "kink rows", bad)
+        else:
+            assert e64 <= KINK_TOL, (what, n, e32, e64, o64)
 
 
 @pytest.mark.parametrize("tag", ["U", "P", "C", "Q"])
@@ -114,17 +134,18 @@ def test_step_size_option_interpolates(method):
     _check(got, outs, (method, "step_size"))
 
 
-@pytest.mark.parametrize("tag,B", [("U", 5000), ("P", 4800), ("C", 6000)])
+@pytest.mark.parametrize("tag,B", [("U", 10007), ("P", 20011), ("C", 6000), ("Q", 9500)])
 def test_medium_tiles(tag, B):
-    """B > 32*SMs selects the 128-trajectory forward tile and the 64-trajectory backward tile."""
+    """Tile selection: the largest tile with >= 1 tile per SM — 64 (B~10k), 128 (B~20k), 32 (B=6000) forward;
+    64- or 32-trajectory tiles backward; ragged last tiles."""
     got, outs = _run_pair(tag, B, "rk4", torch.tensor([0.0, 0.02, 0.04]))
-    _check(got, outs, (tag, B))
+    _check(got, outs, (tag, B), big=B > 8192)
 
 
 def test_large_tiles_unicycle():
-    """B >= 2*256*SMs selects the 256-trajectory forward tile (ragged last tile)."""
-    got, outs = _run_pair("U", 2 * 256 * 148 + 37, "euler", torch.tensor([0.0, 0.02]))
-    _check(got, outs, "U large")
+    """B >= 256*SMs selects the 256-trajectory forward tile (ragged last tile)."""
+    got, outs = _run_pair("U", 256 * 148 + 37, "rk4", torch.tensor([0.0, 0.02]))
+    _check(got, outs, "U large", big=True)
 
 
 @pytest.mark.parametrize("tag", ["U", "C", "P"])
