@@ -103,6 +103,23 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
                          const float* ckpt, const float* grad_out, float* grad_y0, float* grad_params,
                          void* ws, void* stream);
 
+/* Adaptive dopri5 with torchdiffeq semantics (one step size for the whole batch from an RMS norm over all
+ * of [B, D]; FSAL; 4th-order dense output at the requested times).  The forward SYNCHRONISES the stream once
+ * per attempted step (accept/reject is a host decision, as in torchdiffeq).  `t` host, strictly increasing.
+ *   ckpt      NULL or ckpt_bytes: stage inputs of every accepted step (needed by the backward)
+ *   step_dt   host out [max_steps]; out_step / out_x host out [n_t]: which accepted step and which fraction of
+ *             it produced each output (inputs of the backward). */
+int nlbac_node_dopri5_workspace_bytes(const nlbac_node_desc* desc, int64_t B, int n_t, int max_steps,
+                                      size_t* fwd_bytes, size_t* ckpt_bytes, size_t* bwd_bytes);
+int nlbac_node_dopri5_fwd(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B,
+                          const float* t, int n_t, float rtol, float atol, int max_steps, int precision,
+                          float* y_out, float* ckpt, void* ws, int* n_accepted, int* n_rejected, float* step_dt,
+                          int* out_step, float* out_x, void* stream);
+int nlbac_node_dopri5_bwd(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B, int n_t,
+                          int n_accepted, const float* step_dt, const int* out_step, const float* out_x,
+                          int precision, const float* ckpt, const float* grad_out, float* grad_y0,
+                          float* grad_params, void* ws, void* stream);
+
 /* Measured-peak helper for the roofline: register-resident FP32 FMA loop.  Returns the number of
  * FLOPs one launch executes in *flops; the caller times it with CUDA events. */
 int nlbac_fp32_peak_probe(int iters, float* sink, double* flops, void* stream);

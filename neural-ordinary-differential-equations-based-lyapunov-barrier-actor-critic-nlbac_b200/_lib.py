@@ -75,6 +75,12 @@ def _declare(lib):
                                          vp, vp, vp, vp]
     lib.nlbac_node_solve_bwd.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, fp, c.c_int, c.c_int, c.c_int,
                                          vp, vp, vp, vp, vp, vp]
+    szp = c.POINTER(c.c_size_t)
+    lib.nlbac_node_dopri5_workspace_bytes.argtypes = [dp, c.c_int64, c.c_int, c.c_int, szp, szp, szp]
+    lib.nlbac_node_dopri5_fwd.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, c.c_float, c.c_float, c.c_int, c.c_int,
+                                          vp, vp, vp, ip, ip, fp, ip, fp, vp]
+    lib.nlbac_node_dopri5_bwd.argtypes = [dp, vp, vp, c.c_int64, c.c_int, c.c_int, fp, ip, fp, c.c_int,
+                                          vp, vp, vp, vp, vp, vp]
     lib.nlbac_fp32_peak_probe.argtypes = [c.c_int, vp, c.POINTER(c.c_double), vp]
     lib.nlbac_fma_shape_probe.argtypes = [c.c_int, c.c_int, vp, c.POINTER(c.c_double), vp]
     return lib

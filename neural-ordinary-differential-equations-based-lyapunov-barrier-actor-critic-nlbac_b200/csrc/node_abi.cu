@@ -4,7 +4,8 @@
 #include <vector>
 
 #include "../../include/nlbac.h"
-#include "node_bwd.cuh"
+#include "node_dopri5.cuh"
+#include <cmath>
 #include "node_pack.cuh"
 
 namespace nlbac {
@@ -121,6 +122,45 @@ static int launch_bwd(const BwdArgs& a, cudaStream_t st) {
   const long long n_tiles = (a.B + TB - 1) / TB;
   const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());
   node_bwd_kernel<C, TB><<<grid, G::NT, G::SMEM_BYTES, st>>>(a);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <class C, int T>
+static int launch_dp5(const Dp5Args& a, cudaStream_t st) {
+  using G = FwdGeom<C, T>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    NLBAC_CUDA(cudaFuncSetAttribute(dopri5_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)G::SMEM_BYTES));
+    attr_done = true;
+  }
+  const long long n_tiles = (a.B + T - 1) / T;
+  const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());
+  dopri5_kernel<C, T><<<grid, G::NT, G::SMEM_BYTES, st>>>(a);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+template <class C>
+static int launch_dp5_any(const Dp5Args& a, cudaStream_t st) {
+  const long long sms = sm_count();
+  if ((a.B + 255) / 256 >= sms) return launch_dp5<C, 256>(a, st);
+  if ((a.B + 127) / 128 >= sms) return launch_dp5<C, 128>(a, st);
+  if ((a.B + 63) / 64 >= sms) return launch_dp5<C, 64>(a, st);
+  return launch_dp5<C, 32>(a, st);
+}
+template <class C, int TB>
+static int launch_dp5_bwd(const Dp5BwdArgs& a, cudaStream_t st) {
+  using G = BwdGeom<C, TB>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    NLBAC_CUDA(cudaFuncSetAttribute(dopri5_bwd_kernel<C, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)G::SMEM_BYTES));
+    attr_done = true;
+  }
+  const long long n_tiles = (a.B + TB - 1) / TB;
+  const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());
+  dopri5_bwd_kernel<C, TB><<<grid, G::NT, G::SMEM_BYTES, st>>>(a);
   NLBAC_CUDA(cudaGetLastError());
   return 0;
 }
@@ -286,6 +326,151 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
     }
     a.grad_rep = rep;
     int rc = ((B + 63) / 64 >= sm_count()) ? launch_bwd<C, 64>(a, st) : launch_bwd<C, 32>(a, st);
+    if (rc) return rc;
+    if (grad_params) {
+      GradTable gt = build_grad_table<C>();
+      fold_grad_kernel<<<dim3(8, gt.n), 256, 0, st>>>(gt, rep, C::NGRAD, grad_params);
+      NLBAC_CUDA(cudaGetLastError());
+    }
+    return 0;
+  });
+}
+
+// ------------------------------------------------------------------------------------------------
+// dopri5
+// ------------------------------------------------------------------------------------------------
+static size_t dp5_fwd_ws_bytes(int64_t B, int ns) { return (size_t)11 * B * ns * 4 + 64; }
+
+int nlbac_node_dopri5_workspace_bytes(const nlbac_node_desc* desc, int64_t B, int n_t, int max_steps,
+                                      size_t* fwd_bytes, size_t* ckpt_bytes, size_t* bwd_bytes) {
+  NLBAC_REQUIRE(B >= 0 && n_t >= 1 && max_steps >= 1, "bad sizes");
+  return dispatch(desc, [&]<class C>() {
+    if (fwd_bytes) *fwd_bytes = dp5_fwd_ws_bytes(B, C::NS);
+    if (ckpt_bytes) *ckpt_bytes = (size_t)max_steps * 6 * (size_t)B * C::NS * 4;
+    if (bwd_bytes) *bwd_bytes = (size_t)round_up(max_steps * 4 + n_t * 8, 16) + (size_t)NREP * C::NGRAD * 4;
+    return 0;
+  });
+}
+
+int nlbac_node_dopri5_fwd(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B,
+                          const float* t, int n_t, float rtol, float atol, int max_steps, int precision,
+                          float* y_out, float* ckpt, void* ws, int* n_accepted, int* n_rejected, float* step_dt,
+                          int* out_step, float* out_x, void* stream) {
+  NLBAC_REQUIRE(packed && y0 && t && y_out && ws && n_accepted && n_rejected && step_dt && out_step && out_x,
+                "null pointer");
+  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32, "precision %d not compiled", precision);
+  NLBAC_REQUIRE(B > 0 && n_t >= 2 && max_steps >= 1, "bad sizes");
+  for (int j = 1; j < n_t; ++j) NLBAC_REQUIRE(t[j] > t[j - 1], "t must be strictly increasing");
+  cudaStream_t st = (cudaStream_t)stream;
+  return dispatch(desc, [&]<class C>() {
+    const size_t n = (size_t)B * C::NS;
+    float* base = static_cast<float*>(ws);
+    float* ybuf[2] = {base, base + n};
+    float* kbuf[2] = {base + 2 * n, base + 3 * n};
+    float* krec = base + 4 * n;
+    double* acc = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + ((11 * n * 4 + 15) / 16) * 16);
+    const double cnt = (double)B * C::D;
+    double h_acc[3];
+    auto read_acc = [&]() -> int {
+      NLBAC_CUDA(cudaMemcpyAsync(h_acc, acc, sizeof(h_acc), cudaMemcpyDeviceToHost, st));
+      NLBAC_CUDA(cudaStreamSynchronize(st));
+      return 0;
+    };
+    // y_out[0] = y0; state columns -> ybuf[0]
+    NLBAC_CUDA(cudaMemcpyAsync(y_out, y0, (size_t)B * C::D * 4, cudaMemcpyDeviceToDevice, st));
+    NLBAC_CUDA(cudaMemcpy2DAsync(ybuf[0], C::NS * 4, y0, C::D * 4, C::NS * 4, B, cudaMemcpyDeviceToDevice, st));
+    Dp5Args a;
+    a.packed = packed; a.y0 = y0; a.B = B; a.rtol = rtol; a.atol = atol; a.krec = krec; a.acc = acc;
+    int cur = 0;
+    // f0 and the norms of _select_initial_step
+    NLBAC_CUDA(cudaMemsetAsync(acc, 0, 3 * sizeof(double), st));
+    a.mode = 0; a.y = ybuf[0]; a.k1 = nullptr; a.y1 = nullptr; a.k7 = kbuf[0]; a.xrec = nullptr; a.dt = 0.f;
+    if (int rc = launch_dp5_any<C>(a, st)) return rc;
+    if (int rc = read_acc()) return rc;
+    const double d0 = std::sqrt(h_acc[0] / cnt), d1 = std::sqrt(h_acc[1] / cnt);
+    const double h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+    a.mode = 1; a.k1 = kbuf[0]; a.k7 = nullptr; a.dt = (float)h0;
+    if (int rc = launch_dp5_any<C>(a, st)) return rc;
+    if (int rc = read_acc()) return rc;
+    const double d2 = std::sqrt(h_acc[2] / cnt) / h0;
+    const double h1 = (d1 <= 1e-15 && d2 <= 1e-15) ? std::fmax(1e-6, h0 * 1e-3)
+                                                   : std::pow(0.01 / std::fmax(d1, d2), 1.0 / 5.0);
+    double dt = std::fmin(100.0 * h0, h1);
+    double t_cur = t[0], t_prev = t[0];
+    int n_acc = 0, n_rej = 0;
+    float dt_last = 0.f;
+    a.mode = 2;
+    for (int j = 1; j < n_t; ++j) {
+      const double next_t = t[j];
+      while (next_t > t_cur) {
+        NLBAC_REQUIRE(n_acc < max_steps, "dopri5 exceeded max_steps=%d accepted steps", max_steps);
+        NLBAC_REQUIRE(n_acc + n_rej < 100 * max_steps, "dopri5 stalled (%d rejected steps)", n_rej);
+        const double t1 = t_cur + dt;
+        NLBAC_REQUIRE(t1 > t_cur, "underflow in dt %g", dt);
+        NLBAC_CUDA(cudaMemsetAsync(acc, 0, sizeof(double), st));
+        a.y = ybuf[cur]; a.k1 = kbuf[cur]; a.y1 = ybuf[cur ^ 1]; a.k7 = kbuf[cur ^ 1]; a.dt = (float)dt;
+        a.xrec = ckpt ? ckpt + (size_t)n_acc * 6 * n : nullptr;
+        if (int rc = launch_dp5_any<C>(a, st)) return rc;
+        if (int rc = read_acc()) return rc;
+        const double ratio = std::sqrt(h_acc[0] / cnt);
+        NLBAC_REQUIRE(std::isfinite(ratio), "non-finite error ratio in dopri5");
+        if (ratio <= 1.0) {
+          step_dt[n_acc] = (float)dt;
+          dt_last = (float)dt;
+          ++n_acc;
+          t_prev = t_cur; t_cur = t1; cur ^= 1;
+        } else {
+          ++n_rej;
+        }
+        // _optimal_step_size(safety 0.9, ifactor 10, dfactor 0.2, order 5)
+        if (ratio == 0.0) dt *= 10.0;
+        else {
+          const double dfactor = ratio < 1.0 ? 1.0 : 0.2;
+          dt *= std::fmin(10.0, std::fmax(0.9 / std::pow(ratio, 0.2), dfactor));
+        }
+      }
+      // dense output of the last accepted step at next_t
+      Dp5InterpArgs ia;
+      ia.y0 = y0; ia.ya = ybuf[cur ^ 1]; ia.yb = ybuf[cur]; ia.krec = krec; ia.out = y_out + (size_t)j * B * C::D;
+      ia.B = B; ia.dt = dt_last; ia.xf = (float)((next_t - t_prev) / (t_cur - t_prev)); ia.ns = C::NS; ia.d = C::D;
+      const long long tot = (long long)B * C::D;
+      dopri5_interp_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(ia);
+      NLBAC_CUDA(cudaGetLastError());
+      out_step[j] = n_acc - 1;
+      out_x[j] = ia.xf;
+    }
+    out_step[0] = -1; out_x[0] = 0.f;
+    *n_accepted = n_acc; *n_rejected = n_rej;
+    return 0;
+  });
+}
+
+int nlbac_node_dopri5_bwd(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B, int n_t,
+                          int n_accepted, const float* step_dt, const int* out_step, const float* out_x,
+                          int precision, const float* ckpt, const float* grad_out, float* grad_y0,
+                          float* grad_params, void* ws, void* stream) {
+  NLBAC_REQUIRE(packed && y0 && step_dt && out_step && out_x && ckpt && grad_out && ws, "null pointer");
+  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32, "precision %d not compiled", precision);
+  NLBAC_REQUIRE(B > 0 && n_t >= 2 && n_accepted >= 1, "bad sizes");
+  cudaStream_t st = (cudaStream_t)stream;
+  return dispatch(desc, [&]<class C>() {
+    char* p = static_cast<char*>(ws);
+    NLBAC_CUDA(cudaMemcpyAsync(p, step_dt, n_accepted * 4, cudaMemcpyHostToDevice, st));
+    NLBAC_CUDA(cudaMemcpyAsync(p + n_accepted * 4, out_step, n_t * 4, cudaMemcpyHostToDevice, st));
+    NLBAC_CUDA(cudaMemcpyAsync(p + n_accepted * 4 + n_t * 4, out_x, n_t * 4, cudaMemcpyHostToDevice, st));
+    Dp5BwdArgs a;
+    a.packed = packed; a.y0 = y0; a.xrec = ckpt; a.grad_out = grad_out; a.grad_y0 = grad_y0; a.B = B;
+    a.n_acc = n_accepted; a.n_t = n_t;
+    a.dts = reinterpret_cast<const float*>(p);
+    a.out_step = reinterpret_cast<const int*>(p + n_accepted * 4);
+    a.out_x = reinterpret_cast<const float*>(p + n_accepted * 4 + n_t * 4);
+    float* rep = nullptr;
+    if (grad_params) {
+      rep = reinterpret_cast<float*>(p + round_up(n_accepted * 4 + n_t * 8, 16));
+      NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
+    }
+    a.grad_rep = rep;
+    int rc = ((B + 63) / 64 >= sm_count()) ? launch_dp5_bwd<C, 64>(a, st) : launch_dp5_bwd<C, 32>(a, st);
     if (rc) return rc;
     if (grad_params) {
       GradTable gt = build_grad_table<C>();

@@ -1,0 +1,86 @@
+"""Adaptive dopri5 behind ``odeint(..., method='dopri5')`` (torchdiffeq's default method).
+
+torchdiffeq semantics kept: batch-global RMS error norm -> ONE step size for the
+whole batch, ``_select_initial_step``, ``_optimal_step_size`` (safety 0.9, ifactor 10, dfactor 0.2), FSAL,
+no clipping of the last step, 4th-order dense output.  Accept/reject is a host decision per attempted step
+(one scalar read-back), exactly where torchdiffeq itself synchronises; each attempt is one fused launch.
+The step sizes are constants of the backward pass.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+DEFAULT_STEP_CAPACITY = 128
+
+
+class _Dopri5Solve(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, y0, desc, packed, t_np, rtol, atol, precision, want_ckpt, max_steps, stats, *params):
+        L = _lib.lib()
+        B, D = y0.shape
+        n_t = len(t_np)
+        dev = y0.device
+        y0c = y0.detach().contiguous()
+        fwd, ck, bwd = ctypes.c_size_t(), ctypes.c_size_t(), ctypes.c_size_t()
+        _lib.check(L.nlbac_node_dopri5_workspace_bytes(ctypes.byref(desc), B, n_t, max_steps, ctypes.byref(fwd),
+                                                       ctypes.byref(ck), ctypes.byref(bwd)), "dopri5_workspace_bytes")
+        ws = torch.empty(fwd.value, dtype=torch.uint8, device=dev)
+        ckpt = torch.empty(max(ck.value // 4, 1), dtype=torch.float32, device=dev) if want_ckpt else None
+        y_out = torch.empty((n_t, B, D), dtype=torch.float32, device=dev)
+        t_arr = np.ascontiguousarray(t_np, dtype=np.float32)
+        step_dt = np.zeros(max_steps, dtype=np.float32)
+        out_step = np.zeros(n_t, dtype=np.int32)
+        out_x = np.zeros(n_t, dtype=np.float32)
+        n_acc, n_rej = ctypes.c_int(), ctypes.c_int()
+        fp, ip = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int)
+        _lib.check(L.nlbac_node_dopri5_fwd(
+            ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, t_arr.ctypes.data_as(fp), n_t, rtol, atol,
+            max_steps, precision, y_out.data_ptr(), ckpt.data_ptr() if want_ckpt else None, ws.data_ptr(),
+            ctypes.byref(n_acc), ctypes.byref(n_rej), step_dt.ctypes.data_as(fp), out_step.ctypes.data_as(ip),
+            out_x.ctypes.data_as(fp), torch.cuda.current_stream().cuda_stream), "node_dopri5_fwd")
+        if stats is not None:
+            stats.update(n_accepted=n_acc.value, n_rejected=n_rej.value, nfe=2 + 6 * (n_acc.value + n_rej.value),
+                         step_dt=step_dt[:n_acc.value].copy())
+        if want_ckpt:
+            ctx.save_for_backward(y0c, packed, ckpt)
+            ctx.meta = (desc, n_t, n_acc.value, step_dt, out_step, out_x, precision, bwd.value,
+                        [p.shape for p in params])
+        return y_out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        L = _lib.lib()
+        y0c, packed, ckpt = ctx.saved_tensors
+        desc, n_t, n_acc, step_dt, out_step, out_x, precision, bwd_bytes, shapes = ctx.meta
+        B, D = y0c.shape
+        dev = y0c.device
+        need_y0 = ctx.needs_input_grad[0]
+        need_p = any(ctx.needs_input_grad[10:])
+        go = grad_out.contiguous()
+        ws = torch.empty(max(bwd_bytes, 16), dtype=torch.uint8, device=dev)
+        gy0 = torch.empty((B, D), dtype=torch.float32, device=dev) if need_y0 else None
+        n_param = L.nlbac_node_param_count(ctypes.byref(desc))
+        gflat = torch.empty(n_param, dtype=torch.float32, device=dev) if need_p else None
+        fp, ip = ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int)
+        _lib.check(L.nlbac_node_dopri5_bwd(
+            ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, n_t, n_acc, step_dt.ctypes.data_as(fp),
+            out_step.ctypes.data_as(ip), out_x.ctypes.data_as(fp), precision, ckpt.data_ptr(), go.data_ptr(),
+            gy0.data_ptr() if need_y0 else None, gflat.data_ptr() if need_p else None, ws.data_ptr(),
+            torch.cuda.current_stream().cuda_stream), "node_dopri5_bwd")
+        grads = [None] * len(shapes)
+        if need_p:
+            off = 0
+            for i, shp in enumerate(shapes):
+                n = int(np.prod(shp))
+                grads[i] = gflat[off:off + n].view(shp)
+                off += n
+        return (gy0, None, None, None, None, None, None, None, None, None, *grads)
+
+
+def dopri5_solve(func, y0, desc, packed, params, t_np, rtol, atol, precision, need_grad, options):
+    cap = int(options.pop("max_num_steps", DEFAULT_STEP_CAPACITY))
+    stats = options.pop("_stats", None)
+    return _Dopri5Solve.apply(y0, desc, packed, t_np, rtol, atol, precision, need_grad, cap, stats, *params)

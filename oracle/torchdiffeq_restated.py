@@ -204,7 +204,11 @@ def _interp_evaluate(coeffs, t0, t1, t):
     return total
 
 
-def _integrate_dopri5(func, y0, t, rtol, atol, stats=None, max_num_steps=2 ** 31 - 1):
+def _integrate_dopri5(func, y0, t, rtol, atol, stats=None, max_num_steps=2 ** 31 - 1, replay_dt=None):
+    """`replay_dt` (test hook): a recorded list of accepted step sizes; every step is then taken with the
+    recorded size and accepted, which separates arithmetic parity from step-size selection (the error
+    estimate is a difference of nearly equal fp32 numbers, so two fp32 implementations legitimately pick
+    step sizes that differ in the 3rd digit)."""
     norm = _rms_norm
     t = t.to(torch.float64)
     f0 = func(t[0].to(y0.dtype), y0)
@@ -213,6 +217,10 @@ def _integrate_dopri5(func, y0, t, rtol, atol, stats=None, max_num_steps=2 ** 31
     interp = [y0] * 5
     sol = [y0]
     n_acc = n_rej = 0
+    dts = []
+    if replay_dt is not None:
+        replay_dt = [torch.tensor(float(v), dtype=torch.float64) for v in replay_dt]
+        dt = replay_dt[0]
     for i in range(1, len(t)):
         next_t = t[i]
         n_steps = 0
@@ -224,8 +232,9 @@ def _integrate_dopri5(func, y0, t, rtol, atol, stats=None, max_num_steps=2 ** 31
             with torch.no_grad():
                 tol = atol + rtol * torch.max(y.abs(), y1.abs())
                 ratio = norm(err / tol).abs()
-            accept = bool(ratio <= 1)
+            accept = bool(ratio <= 1) or replay_dt is not None
             if accept:
+                dts.append(float(dt))
                 dt32 = dt.to(y.dtype)
                 acc = 0
                 for c, kj in zip(DP_C_MID, k):
@@ -237,13 +246,17 @@ def _integrate_dopri5(func, y0, t, rtol, atol, stats=None, max_num_steps=2 ** 31
                 n_acc += 1
             else:
                 n_rej += 1
-            dt = _optimal_step_size(dt, ratio)
+            if replay_dt is None:
+                dt = _optimal_step_size(dt, ratio)
+            elif n_acc < len(replay_dt):
+                dt = replay_dt[n_acc]
             n_steps += 1
         sol.append(_interp_evaluate(interp, t_prev, t_cur, next_t))
     if stats is not None:
         stats["n_accepted"] = n_acc
         stats["n_rejected"] = n_rej
         stats["nfe"] = 2 + 6 * (n_acc + n_rej)
+        stats["step_dt"] = dts
     return torch.stack(sol, 0)
 
 
@@ -280,5 +293,5 @@ def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, even
     user = func
     func = lambda tt, y: user(tt.to(y.dtype), y)  # noqa: E731  (_PerturbFunc casts t)
     if method == "dopri5":
-        return _integrate_dopri5(func, y0, t, rtol, atol, stats=_stats)
+        return _integrate_dopri5(func, y0, t, rtol, atol, stats=_stats, replay_dt=options.get("_replay_dt"))
     return _integrate_fixed(func, y0, t, method, options.get("step_size"))
