@@ -95,7 +95,7 @@ def test_dopri5_golden_from_reference(tag, golden_dir):
         (sol * c["cot"].cuda()).sum().backward()
         # gradients of the golden run used the oracle's own fp32 step-size sequence: exact for the one-step
         # case, step-size-conditioned (see _pair) for the long one
-        gtol = 5 * TOL if c["stats"]["n_accepted"] == 1 else 1e-2
+        gtol = 5 * TOL if c["stats"]["n_accepted"] == 1 else 3e-2
         assert _rel(y0.grad, c["grad_y0"]) <= gtol, name
         for k, p in ours.named_parameters():
             assert _rel(p.grad, c["grad_params"][k]) <= gtol, (name, k)
