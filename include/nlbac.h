@@ -120,6 +120,88 @@ int nlbac_node_dopri5_bwd(const nlbac_node_desc* desc, const float* packed, cons
                           int precision, const float* ckpt, const float* grad_out, float* grad_y0,
                           float* grad_params, void* ws, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Actor / critic / Lyapunov / barrier MLPs: in -> hidden -> hidden -> out, ReLU (QNetwork is two of
+ * them, U sac_cbf_clf/model.py:37-64; LyaNetwork :67-83; BarrierNetwork BU model.py:67-86;
+ * GaussianPolicy :86-115 with out = [mean | log_std]).
+ *   params   HOST array of 6 DEVICE pointers W1,b1,W2,b2,W3,b3 (nn.Linear layout, W is [out,in])
+ *   act      [2,B,hidden] post-ReLU activations written by the forward for the backward (or NULL)
+ *   ws       bwd_bytes of scratch;  grad_params HOST array of 6 DEVICE pointers (overwritten) or NULL
+ * ------------------------------------------------------------------------------------------------ */
+typedef struct nlbac_mlp_desc {
+  int n_in;    /* <= 32 */
+  int hidden;  /* multiple of 32, <= 1024 (reference: 256) */
+  int n_out;   /* <= 8 */
+} nlbac_mlp_desc;
+
+int nlbac_mlp_workspace_bytes(const nlbac_mlp_desc* desc, int64_t B, size_t* act_bytes, size_t* bwd_bytes);
+int nlbac_mlp_fwd(const nlbac_mlp_desc* desc, const float* const* params, const float* x, int64_t B, float* out,
+                  float* act, void* stream);
+int nlbac_mlp_bwd(const nlbac_mlp_desc* desc, const float* const* params, const float* x, int64_t B, const float* act,
+                  const float* grad_out, float* grad_x, float* const* grad_params, void* ws, void* stream);
+
+/* tanh-squashed Gaussian head of GaussianPolicy.sample (U model.py:117-128) with the N(0,1) draw `eps`
+ * injected: mean_logstd [B, 2*n_u] -> action [B,n_u], log_prob [B,1], mean_out [B,n_u]. */
+int nlbac_policy_head_fwd(const float* mean_logstd, const float* eps, const float* action_scale,
+                          const float* action_bias, int64_t B, int n_u, float* action, float* log_prob,
+                          float* mean_out, void* stream);
+int nlbac_policy_head_bwd(const float* mean_logstd, const float* eps, const float* action_scale, int64_t B, int n_u,
+                          const float* grad_action, const float* grad_log_prob, const float* grad_mean_out,
+                          float* grad_mean_logstd, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * CBF / CLF constraint block of get_policy_loss_2: rows -> where(>0) -> batch sum / batch_size -> req[m]
+ * (U sac_cbf_clf.py:472-504; C :474-523; BU :424-460).  One fused elementwise + reduction kernel.
+ *   UNICYCLE  a = p(x_t) [B,2], b = p(x_{t+1}) [B,2] (grad);  rows: n_hazards CBF rows, then the CLF row
+ *   CARS      a = x_t [B,10], b = x_{t+1} [B,10] (grad), c = x_{t+2} [B,10] (grad); rows: cbf23, cbf34, CLF
+ *   BARRIER   a = B(x_t,u_t) detached [B], b = B(x_{t+1},u_{t+1}) [B] (grad); rows: barrier, CLF
+ * CLF row = (Vnext - V) * lya_inv_dt + gamma_l * V;  V [B] detached, Vnext [B] (grad).
+ * ------------------------------------------------------------------------------------------------ */
+#define NLBAC_CONSTRAINT_UNICYCLE 0
+#define NLBAC_CONSTRAINT_CARS     1
+#define NLBAC_CONSTRAINT_BARRIER  2
+#define NLBAC_MAX_HAZARDS 15
+typedef struct nlbac_constraint_desc {
+  int kind;
+  int m;                  /* rows: n_hazards+1 (UNICYCLE), 3 (CARS), 2 (BARRIER) */
+  int n_hazards;
+  float dt;               /* env.dt (0.02) */
+  float gamma_b;
+  float gamma_l;
+  float lya_inv_dt;       /* 1/dt for U/BU (U :474), 1 for C (:474) and P/BP (P :478) */
+  float batch_size;       /* args.batch_size, the divisor the reference uses (U :503-504) */
+  float collision_radius; /* U: 1.05 * hazards_radius; C: 4.5 */
+  float hazards[2 * NLBAC_MAX_HAZARDS];
+} nlbac_constraint_desc;
+
+int nlbac_constraints_fwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
+                          const float* V, const float* Vnext, int64_t B, float* req, void* stream);
+int nlbac_constraints_bwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
+                          const float* V, const float* Vnext, int64_t B, const float* grad_req, float* grad_b,
+                          float* grad_c, float* grad_Vnext, void* stream);
+
+/* lookahead point p(x) = [x + l_p cos(theta), y + l_p sin(theta)] of a [B, n_s] state (theta = column 2)
+ * (U sac_cbf_clf.py:429-437, 455-469). */
+int nlbac_lookahead_fwd(const float* state, int n_s, float l_p, int64_t B, float* p, void* stream);
+int nlbac_lookahead_bwd(const float* state, int n_s, float l_p, int64_t B, const float* grad_p, float* grad_state,
+                        void* stream);
+
+/* DynamicsModel.get_state / get_obs (U dynamics.py:27-69; C :25-96; P :25-153; BU :73-198).
+ *   UNICYCLE obs[B,7]  <-> state[B,3];  CARS obs[B,10] <-> state[B,10];  PVTOL obs[B,11] <-> state[B,7]
+ * get_state does its arithmetic in float64 like the reference's numpy round trip; state_dyn (PVTOL, [B,6]) may be NULL. */
+#define NLBAC_ENV_UNICYCLE 0
+#define NLBAC_ENV_CARS     1
+#define NLBAC_ENV_PVTOL    2
+int nlbac_get_state(int env, const float* obs, int64_t B, float* state, float* state_dyn, void* stream);
+int nlbac_get_obs_fwd(int env, const float* state, int64_t B, float* obs, void* stream);
+int nlbac_get_obs_bwd(int env, const float* state, int64_t B, const float* grad_obs, float* grad_state, void* stream);
+
+/* torch.optim.Adam.step (defaults, as used at U model.py:257 / sac_cbf_clf.py:249-290) on one flat tensor;
+ * `step` is the 1-based step count.  utils.soft_update (U utils.py:75-79): target = target*(1-tau) + source*tau. */
+int nlbac_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, int step, float lr,
+                    float beta1, float beta2, float eps, void* stream);
+int nlbac_soft_update(float* target, const float* source, int64_t n, float tau, void* stream);
+
 /* Measured-peak helper for the roofline: register-resident FP32 FMA loop.  Returns the number of
  * FLOPs one launch executes in *flops; the caller times it with CUDA events. */
 int nlbac_fp32_peak_probe(int iters, float* sink, double* flops, void* stream);

@@ -8,5 +8,10 @@ from . import _lib
 from ._lib import build
 from .odeint import odeint, describe
 from .model import NeuralODEModel, train_step
+from .mlp import QNetwork, LyaNetwork, BarrierNetwork, GaussianPolicy, weights_init_
+from .tail import DynamicsModel, FusedAdam, soft_update, hard_update, constraint_sums, lookahead, make_constraint_desc
+from . import constraints
 
-__all__ = ["odeint", "NeuralODEModel", "train_step", "build", "describe"]
+__all__ = ["odeint", "NeuralODEModel", "train_step", "build", "describe", "QNetwork", "LyaNetwork", "BarrierNetwork",
+           "GaussianPolicy", "weights_init_", "DynamicsModel", "FusedAdam", "soft_update", "hard_update",
+           "constraint_sums", "lookahead", "make_constraint_desc", "constraints"]

@@ -18,6 +18,20 @@ NVCC_FLAGS = ["-std=c++20", "-O3", "-gencode", "arch=compute_100a,code=sm_100a",
 _lib = None
 
 
+class MlpDesc(ctypes.Structure):
+    _fields_ = [("n_in", ctypes.c_int), ("hidden", ctypes.c_int), ("n_out", ctypes.c_int)]
+
+
+MAX_HAZARDS = 15
+
+
+class ConstraintDesc(ctypes.Structure):
+    _fields_ = [("kind", ctypes.c_int), ("m", ctypes.c_int), ("n_hazards", ctypes.c_int), ("dt", ctypes.c_float),
+                ("gamma_b", ctypes.c_float), ("gamma_l", ctypes.c_float), ("lya_inv_dt", ctypes.c_float),
+                ("batch_size", ctypes.c_float), ("collision_radius", ctypes.c_float),
+                ("hazards", ctypes.c_float * (2 * MAX_HAZARDS))]
+
+
 class NodeDesc(ctypes.Structure):
     _fields_ = [("kind", ctypes.c_int), ("n_s", ctypes.c_int), ("n_u", ctypes.c_int), ("n_c", ctypes.c_int),
                 ("hidden", ctypes.c_int), ("n_f_layers", ctypes.c_int), ("n_g_layers", ctypes.c_int)]
@@ -81,6 +95,21 @@ def _declare(lib):
                                           vp, vp, vp, ip, ip, fp, ip, fp, vp]
     lib.nlbac_node_dopri5_bwd.argtypes = [dp, vp, vp, c.c_int64, c.c_int, c.c_int, fp, ip, fp, c.c_int,
                                           vp, vp, vp, vp, vp, vp]
+    mp, cp, i64 = c.POINTER(MlpDesc), c.POINTER(ConstraintDesc), c.c_int64
+    lib.nlbac_mlp_workspace_bytes.argtypes = [mp, i64, szp, szp]
+    lib.nlbac_mlp_fwd.argtypes = [mp, c.POINTER(vp), vp, i64, vp, vp, vp]
+    lib.nlbac_mlp_bwd.argtypes = [mp, c.POINTER(vp), vp, i64, vp, vp, vp, c.POINTER(vp), vp, vp]
+    lib.nlbac_policy_head_fwd.argtypes = [vp, vp, vp, vp, i64, c.c_int, vp, vp, vp, vp]
+    lib.nlbac_policy_head_bwd.argtypes = [vp, vp, vp, i64, c.c_int, vp, vp, vp, vp, vp]
+    lib.nlbac_constraints_fwd.argtypes = [cp, vp, vp, vp, vp, vp, i64, vp, vp]
+    lib.nlbac_constraints_bwd.argtypes = [cp, vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, vp]
+    lib.nlbac_lookahead_fwd.argtypes = [vp, c.c_int, c.c_float, i64, vp, vp]
+    lib.nlbac_lookahead_bwd.argtypes = [vp, c.c_int, c.c_float, i64, vp, vp, vp]
+    lib.nlbac_get_state.argtypes = [c.c_int, vp, i64, vp, vp, vp]
+    lib.nlbac_get_obs_fwd.argtypes = [c.c_int, vp, i64, vp, vp]
+    lib.nlbac_get_obs_bwd.argtypes = [c.c_int, vp, i64, vp, vp, vp]
+    lib.nlbac_adam_step.argtypes = [vp, vp, vp, vp, i64, c.c_int, c.c_float, c.c_float, c.c_float, c.c_float, vp]
+    lib.nlbac_soft_update.argtypes = [vp, vp, i64, c.c_float, vp]
     lib.nlbac_fp32_peak_probe.argtypes = [c.c_int, vp, c.POINTER(c.c_double), vp]
     lib.nlbac_fma_shape_probe.argtypes = [c.c_int, c.c_int, vp, c.POINTER(c.c_double), vp]
     return lib

@@ -1,0 +1,108 @@
+"""``get_policy_loss_2`` — the CBF/CLF augmented-Lagrangian part of the actor loss — on the fused kernels.
+
+Mirrors the bodies of ``SAC_CBF_CLF.get_policy_loss_2`` for Unicycle (U sac_cbf_clf.py:408-530), SimulatedCars
+(C :412-555) and the learned-barrier variants (BU :359-477, BP :360-472): one fused NODE prediction per rollout
+step (``odeint``), the fused Lyapunov / barrier / policy MLPs, and ONE fused kernel for the constraint rows,
+the ``where(>0)`` filter and the batch reduction.  The multiplier / rho bookkeeping is the reference's, kept on
+the host exactly as written there (python floats, App. D.3).
+"""
+import torch
+
+from .odeint import odeint
+from .tail import constraint_sums, lookahead, make_constraint_desc
+
+
+class ConstraintState:
+    """The agent attributes the reference's method reads and mutates (U sac_cbf_clf.py:55-62)."""
+
+    def __init__(self, num_constraints, batch_size, *, lambda_max=400.0, cost_limit=0.0, augmented_term=1.0,
+                 augmented_ratio=1.0005, update_interval=8, ratio_floor=None, use_ratio=True):
+        self.num_constraints = num_constraints
+        self.batch_size = batch_size
+        self.lambda_values = [0.0] * num_constraints
+        self.lambda_max = lambda_max
+        self.cost_limit = cost_limit
+        self.augmented_term = augmented_term
+        self.augmented_ratio = augmented_ratio
+        self.Lagrangian_multiplier_update_interval = update_interval
+        self.ratio_floor = ratio_floor
+        self.use_ratio = use_ratio
+
+
+def augmented_lagrangian(required_matrix, st, updates):
+    """U sac_cbf_clf.py:506-530 (C :525-555 adds the 0.002 floor; BU :462-477 has no ratio)."""
+    ratio = 1.0
+    if st.use_ratio:
+        other = required_matrix[:-1, :] - st.cost_limit
+        other_mean = torch.abs(torch.mean(other))
+        lya_component = torch.abs(required_matrix[-1, :] - st.cost_limit)
+        ratio = float(other_mean / lya_component)
+        if st.ratio_floor is not None and ratio < st.ratio_floor:
+            ratio = st.ratio_floor
+    req_copy = required_matrix.detach()
+    if updates % st.Lagrangian_multiplier_update_interval == 0:
+        for i in range(st.num_constraints):
+            new_lambda = st.lambda_values[i] + st.augmented_term * req_copy[i]
+            st.lambda_values[i] = torch.clamp(new_lambda, 0.01, st.lambda_max)
+    st.augmented_term = min(st.augmented_term * st.augmented_ratio, 200)
+    rho, cl = st.augmented_term, st.cost_limit
+    loss = 0.0
+    m = required_matrix.shape[0]
+    for i in range(m - 1):
+        c = required_matrix[i] - cl
+        loss = loss + float(st.lambda_values[i]) * c + rho / 2.0 * c * c
+    c = required_matrix[-1] - cl
+    loss = loss + float(st.lambda_values[-1]) * ratio * c + ratio * ratio * rho / 2.0 * c * c
+    return loss
+
+
+def unicycle_required_matrix(neural_ode_model, lyapunovNet, state_batch, action_batch, lyapunov_value, *, dt,
+                             gamma_b, hazards_locations, hazards_radius, l_p, batch_size, solver="euler",
+                             gamma_l=1.0):
+    """U sac_cbf_clf.py:420-504: returns ``required_matrix`` [num_cbfs + 1, 1]."""
+    assert state_batch.ndim == 2 and action_batch.ndim == 2, (state_batch.shape, action_batch.shape)
+    ps = lookahead(state_batch, l_p)
+    model_input_t = torch.cat((state_batch, action_batch), dim=-1)
+    next_state_t = odeint(neural_ode_model, model_input_t, [0.0, dt], method=solver, atol=1e-7, rtol=1e-5)[-1]
+    ps_next = lookahead(next_state_t[:, :3], l_p)
+    lyapunov_value_next = lyapunovNet(ps_next)
+    desc = make_constraint_desc("unicycle", dt=dt, gamma_b=gamma_b, gamma_l=gamma_l, batch_size=batch_size,
+                                collision_radius=1.05 * hazards_radius, hazards=hazards_locations)
+    return constraint_sums(desc, ps, ps_next, None, lyapunov_value.detach(), lyapunov_value_next)
+
+
+def cars_required_matrix(neural_ode_model, lyapunovNet, policy, dynamics_model, state_batch, action_batch,
+                         lyapunov_value, t_batch, next_time_batch, *, dt, gamma_b, batch_size, solver="euler",
+                         gamma_l=0.15, eps_next=None):
+    """C sac_cbf_clf.py:424-523: two chained NODE predictions with the policy re-sampled on the detached
+    predicted observation in between; returns ``required_matrix`` [3, 1]."""
+    model_input_t = torch.cat((state_batch, action_batch, t_batch), dim=-1)
+    next_state_pred = odeint(neural_ode_model, model_input_t, [0.0, dt], method=solver, atol=1e-7, rtol=1e-5)[-1][:, :10]
+    next_obs_pred = dynamics_model.get_obs(next_state_pred.detach())
+    pi_next, _, _ = policy.sample(next_obs_pred, eps_next)
+    pi_next = pi_next.detach()
+    next_model_input_t = torch.cat((next_state_pred, pi_next, next_time_batch), dim=-1)
+    next_next_state_pred = odeint(neural_ode_model, next_model_input_t, [0.0, dt], method=solver, atol=1e-7,
+                                  rtol=1e-5)[-1][:, :10]
+    lyapunov_value_next = lyapunovNet(next_state_pred[:, 4:8])
+    desc = make_constraint_desc("cars", dt=dt, gamma_b=gamma_b, gamma_l=gamma_l, batch_size=batch_size,
+                                lya_inv_dt=1.0, collision_radius=4.5)
+    return constraint_sums(desc, state_batch, next_state_pred, next_next_state_pred, lyapunov_value.detach(),
+                           lyapunov_value_next)
+
+
+def barrier_unicycle_required_matrix(neural_ode_model, lyapunovNet, BarrierNet, policy, dynamics_model, obs_batch,
+                                     state_batch, action_batch, lyapunov_value, *, dt, gamma_b, l_p, batch_size,
+                                     solver="euler", gamma_l=1.0, eps_next=None):
+    """BU sac_cbf_clf.py:368-446: learned barrier certificate instead of closed-form CBFs; ``required_matrix`` [2, 1]."""
+    model_input_t = torch.cat((state_batch, action_batch), dim=-1)
+    next_state_t = odeint(neural_ode_model, model_input_t, [0.0, dt], method=solver, atol=1e-7, rtol=1e-5)[-1]
+    predicted = next_state_t[:, :3]
+    ps_next = lookahead(predicted, l_p)
+    lyapunov_value_next = lyapunovNet(ps_next)
+    barrier_value = BarrierNet(obs_batch, action_batch).detach()
+    next_obs = dynamics_model.get_obs(predicted)
+    pi_next, _, _ = policy.sample(next_obs.detach(), eps_next)
+    barrier_next = BarrierNet(next_obs, pi_next.detach())
+    desc = make_constraint_desc("barrier", dt=dt, gamma_b=gamma_b, gamma_l=gamma_l, batch_size=batch_size)
+    return constraint_sums(desc, barrier_value, barrier_next, None, lyapunov_value.detach(), lyapunov_value_next)

@@ -1,0 +1,237 @@
+// K3/K4 — fused 2-hidden-layer ReLU MLP (in -> H -> H -> out), forward and backward, FP32.
+//
+// Replaces QNetwork / LyaNetwork / BarrierNetwork / GaussianPolicy.forward of the reference
+// (U sac_cbf_clf/model.py:37-64, :67-83, :86-115; BU model.py:67-86) and autograd through them.
+// The real minibatches are B = 128 / 256 rows: the whole forward is ONE launch
+// of ceil(B/TM) CTAs that keep the row tile's activations in shared memory; weights (<= 0.27 MB)
+// are read through L1/L2.  The backward is one row-tile kernel (deltas, dX) + one batched
+// A^T B kernel for the three weight gradients + one column-sum kernel for the biases; no atomics,
+// so gradients are bit-reproducible run to run.
+#pragma once
+#include "common.cuh"
+
+namespace nlbac {
+
+constexpr int MLP_TM = 8;         // rows per CTA
+constexpr int MLP_NT = 256;       // threads per CTA
+constexpr int MLP_MAX_OUT = 8;    // output columns (twin-Q: 1, policy: 2*n_u <= 4)
+constexpr int MLP_MAX_IN = 32;
+
+struct MlpArgs {
+  const float *W1, *b1, *W2, *b2, *W3, *b3;  // nn.Linear layout: W [out, in]
+  const float* x;    // [B, n_in]
+  float* out;        // [B, n_out]
+  float* act;        // [2, B, H] post-ReLU activations (saved for the backward) or null
+  long long B;
+  int n_in, H, n_out;
+};
+
+// dynamic smem: x[TM][n_in] | h1[TM][H] | h2[TM][H]
+__global__ void __launch_bounds__(MLP_NT) mlp_fwd_kernel(MlpArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  const int H = a.H, NI = a.n_in, NO = a.n_out;
+  float* sx = sm;
+  float* h1 = sx + MLP_TM * MLP_MAX_IN;
+  float* h2 = h1 + MLP_TM * H;
+  const int tid = threadIdx.x;
+  const long long row0 = (long long)blockIdx.x * MLP_TM;
+  const int rows = (int)min((long long)MLP_TM, a.B - row0);
+  for (int i = tid; i < MLP_TM * NI; i += MLP_NT) {
+    const int r = i / NI, c = i - r * NI;
+    sx[r * MLP_MAX_IN + c] = r < rows ? a.x[(row0 + r) * NI + c] : 0.f;
+  }
+  __syncthreads();
+  // layer 1: one hidden unit per thread, all rows of the tile
+  for (int j = tid; j < H; j += MLP_NT) {
+    float acc[MLP_TM];
+    const float bj = a.b1[j];
+#pragma unroll
+    for (int r = 0; r < MLP_TM; ++r) acc[r] = bj;
+    const float* w = a.W1 + (size_t)j * NI;
+    for (int k = 0; k < NI; ++k) {
+      const float wv = w[k];
+#pragma unroll
+      for (int r = 0; r < MLP_TM; ++r) acc[r] = fmaf(sx[r * MLP_MAX_IN + k], wv, acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < MLP_TM; ++r) h1[r * H + j] = fmaxf(acc[r], 0.f);
+  }
+  __syncthreads();
+  // layer 2: thread j walks row j of W2 (each 128-byte line is fetched once and consumed from L1)
+  for (int j = tid; j < H; j += MLP_NT) {
+    float acc[MLP_TM];
+    const float bj = a.b2[j];
+#pragma unroll
+    for (int r = 0; r < MLP_TM; ++r) acc[r] = bj;
+    const float4* w = reinterpret_cast<const float4*>(a.W2 + (size_t)j * H);
+    for (int k4 = 0; k4 < H / 4; ++k4) {
+      const float4 wv = w[k4];
+#pragma unroll
+      for (int r = 0; r < MLP_TM; ++r) {
+        const float4 hv = *reinterpret_cast<const float4*>(h1 + r * H + 4 * k4);
+        acc[r] = fmaf(hv.x, wv.x, acc[r]);
+        acc[r] = fmaf(hv.y, wv.y, acc[r]);
+        acc[r] = fmaf(hv.z, wv.z, acc[r]);
+        acc[r] = fmaf(hv.w, wv.w, acc[r]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < MLP_TM; ++r) h2[r * H + j] = fmaxf(acc[r], 0.f);
+  }
+  __syncthreads();
+  if (a.act != nullptr) {
+    for (int i = tid; i < rows * H; i += MLP_NT) {
+      const int r = i / H, c = i - r * H;
+      a.act[(row0 + r) * H + c] = h1[i];
+      a.act[((size_t)a.B + row0 + r) * H + c] = h2[i];
+    }
+  }
+  // layer 3: one warp per (row, output) dot product
+  const int warp = tid / 32, lane = tid % 32;
+  for (int p = warp; p < rows * NO; p += MLP_NT / 32) {
+    const int r = p / NO, o = p - r * NO;
+    float s = 0.f;
+    for (int k = lane; k < H; k += 32) s = fmaf(h2[r * H + k], a.W3[(size_t)o * H + k], s);
+    s = warp_sum(s);
+    if (lane == 0) a.out[(row0 + r) * NO + o] = s + a.b3[o];
+  }
+}
+
+struct MlpBwdArgs {
+  const float *W1, *W2, *W3;
+  const float* act;       // [2, B, H]
+  const float* grad_out;  // [B, n_out]
+  float* d1;              // [B, H] pre-activation cotangent of layer 1 (workspace)
+  float* d2;              // [B, H] pre-activation cotangent of layer 2 (workspace)
+  float* grad_x;          // [B, n_in] or null
+  long long B;
+  int n_in, H, n_out;
+};
+
+// dynamic smem: g[TM][MAX_OUT] | d2[TM][H] | d1[TM][H]
+__global__ void __launch_bounds__(MLP_NT) mlp_bwd_rows_kernel(MlpBwdArgs a) {
+  extern __shared__ __align__(16) float sm[];
+  const int H = a.H, NI = a.n_in, NO = a.n_out;
+  float* sg = sm;
+  float* s2 = sg + MLP_TM * MLP_MAX_OUT;
+  float* s1 = s2 + MLP_TM * H;
+  const int tid = threadIdx.x;
+  const long long row0 = (long long)blockIdx.x * MLP_TM;
+  const int rows = (int)min((long long)MLP_TM, a.B - row0);
+  for (int i = tid; i < MLP_TM * NO; i += MLP_NT) {
+    const int r = i / NO, o = i - r * NO;
+    sg[r * MLP_MAX_OUT + o] = r < rows ? a.grad_out[(row0 + r) * NO + o] : 0.f;
+  }
+  __syncthreads();
+  const float* h1 = a.act;
+  const float* h2 = a.act + (size_t)a.B * H;
+  // d2[r][j] = relu'(h2) * sum_o g[r][o] W3[o][j]
+  for (int j = tid; j < H; j += MLP_NT) {
+    float acc[MLP_TM];
+#pragma unroll
+    for (int r = 0; r < MLP_TM; ++r) acc[r] = 0.f;
+    for (int o = 0; o < NO; ++o) {
+      const float wv = a.W3[(size_t)o * H + j];
+#pragma unroll
+      for (int r = 0; r < MLP_TM; ++r) acc[r] = fmaf(sg[r * MLP_MAX_OUT + o], wv, acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < MLP_TM; ++r) {
+      float v = 0.f;
+      if (r < rows) {
+        v = h2[(row0 + r) * H + j] > 0.f ? acc[r] : 0.f;
+        a.d2[(row0 + r) * H + j] = v;
+      }
+      s2[r * H + j] = v;
+    }
+  }
+  __syncthreads();
+  // d1[r][k] = relu'(h1) * sum_j d2[r][j] W2[j][k]   (W2 rows read coalesced across threads k)
+  for (int k = tid; k < H; k += MLP_NT) {
+    float acc[MLP_TM];
+#pragma unroll
+    for (int r = 0; r < MLP_TM; ++r) acc[r] = 0.f;
+    for (int j = 0; j < H; ++j) {
+      const float wv = a.W2[(size_t)j * H + k];
+#pragma unroll
+      for (int r = 0; r < MLP_TM; ++r) acc[r] = fmaf(s2[r * H + j], wv, acc[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < MLP_TM; ++r) {
+      float v = 0.f;
+      if (r < rows) {
+        v = h1[(row0 + r) * H + k] > 0.f ? acc[r] : 0.f;
+        a.d1[(row0 + r) * H + k] = v;
+      }
+      s1[r * H + k] = v;
+    }
+  }
+  __syncthreads();
+  if (a.grad_x != nullptr) {
+    const int warp = tid / 32, lane = tid % 32;
+    for (int p = warp; p < rows * NI; p += MLP_NT / 32) {
+      const int r = p / NI, i = p - r * NI;
+      float s = 0.f;
+      for (int k = lane; k < H; k += 32) s = fmaf(s1[r * H + k], a.W1[(size_t)k * NI + i], s);
+      s = warp_sum(s);
+      if (lane == 0) a.grad_x[(row0 + r) * NI + i] = s;
+    }
+  }
+}
+
+// C[M,N] = A^T B over the batch:  C[m][n] = sum_b A[b][m] * Bm[b][n];  three problems per launch (blockIdx.z)
+struct AtbProb { const float* A; const float* Bm; float* C; int M, N; };
+struct AtbArgs { AtbProb p[3]; long long B; };
+__global__ void __launch_bounds__(256) mlp_atb_kernel(AtbArgs a) {
+  const AtbProb p = a.p[blockIdx.z];
+  const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
+  if (m0 >= p.M || n0 >= p.N) return;
+  __shared__ float sA[32][33], sB[32][33];
+  const int tx = threadIdx.x % 32, ty = threadIdx.x / 32;  // 32 x 8; each thread 4 rows of the 32x32 tile
+  float acc[4] = {0.f, 0.f, 0.f, 0.f};
+  for (long long b0 = 0; b0 < a.B; b0 += 32) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int bb = ty + 8 * i;
+      const long long b = b0 + bb;
+      sA[bb][tx] = (b < a.B && m0 + tx < p.M) ? p.A[b * p.M + m0 + tx] : 0.f;
+      sB[bb][tx] = (b < a.B && n0 + tx < p.N) ? p.Bm[b * p.N + n0 + tx] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int bb = 0; bb < 32; ++bb) {
+      const float bv = sB[bb][tx];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[i] = fmaf(sA[bb][ty + 8 * i], bv, acc[i]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty + 8 * i, n = n0 + tx;
+    if (m < p.M && n < p.N) p.C[(size_t)m * p.N + n] = acc[i];
+  }
+}
+
+// db[c] = sum_b D[b][c]; three problems per launch (blockIdx.y)
+struct ColSumProb { const float* D; float* out; int N; };
+struct ColSumArgs { ColSumProb p[3]; long long B; };
+__global__ void __launch_bounds__(256) mlp_colsum_kernel(ColSumArgs a) {
+  const ColSumProb p = a.p[blockIdx.y];
+  const int c = blockIdx.x * 32 + threadIdx.x % 32;
+  const int part = threadIdx.x / 32;
+  __shared__ float red[8][33];
+  float s = 0.f;
+  if (c < p.N)
+    for (long long b = part; b < a.B; b += 8) s += p.D[b * p.N + c];
+  red[part][threadIdx.x % 32] = s;
+  __syncthreads();
+  if (part == 0 && c < p.N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+    p.out[c] = t;
+  }
+}
+
+}  // namespace nlbac

@@ -1,0 +1,364 @@
+// C ABI of the element-wise / reduction tail of the update step (include/nlbac.h):
+//   nlbac_constraints_*  K5  CBF/CLF constraint rows -> filter -> batch sums   (U sac_cbf_clf.py:472-504,
+//                            C :474-523, BU :424-460)
+//   nlbac_lookahead_*    K6  p(x) = [x, y] + l_p [cos th, sin th]              (U sac_cbf_clf.py:429-437,455-469)
+//   nlbac_get_state / nlbac_get_obs_*  K6  DynamicsModel.get_state / get_obs   (U dynamics.py:27-69, C :25-96,
+//                            P :25-153, BU :27-198)
+//   nlbac_adam_step / nlbac_soft_update  torch.optim.Adam.step (U model.py:257) / utils.soft_update (U utils.py:75-79)
+// All are HBM-streaming kernels: one pass over the rows, coalesced, grid sized to the SM count.
+#include "../../include/nlbac.h"
+#include "common.cuh"
+
+namespace nlbac {
+
+static int tail_grid(long long n, int threads) {
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  long long g = (n + threads - 1) / threads;
+  const long long cap = (long long)sms * 8;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+// ------------------------------------------------------------------------------------------------
+// constraint rows.  MAXM rows per sample, kept in registers; block reduction; one atomicAdd per
+// (CTA, row).  For B <= 256 (the real minibatches) the grid is one CTA and the sums are deterministic.
+// ------------------------------------------------------------------------------------------------
+constexpr int MAXM = 16;
+constexpr int CNT = 256;
+
+template <bool BWD>
+__device__ __forceinline__ int constraint_rows(const nlbac_constraint_desc& d, const float* a, const float* b,
+                                               const float* c, const float* V, const float* Vn, long long i,
+                                               float (&row)[MAXM], const float* g /*[m] scaled*/, float* gb, float* gc,
+                                               float* gVn) {
+  const float v = V[i], vn = Vn[i];
+  if (d.kind == NLBAC_CONSTRAINT_UNICYCLE) {
+    // a = p(x_t) [B,2], b = p(x_{t+1}) [B,2]
+    const float px = a[2 * i], py = a[2 * i + 1], qx = b[2 * i], qy = b[2 * i + 1];
+    const float rc2 = d.collision_radius * d.collision_radius;
+    float gqx = 0.f, gqy = 0.f;
+    for (int h = 0; h < d.n_hazards; ++h) {
+      const float cx = d.hazards[2 * h], cy = d.hazards[2 * h + 1];
+      const float hs = 0.5f * ((px - cx) * (px - cx) + (py - cy) * (py - cy) - rc2);
+      const float hn = 0.5f * ((qx - cx) * (qx - cx) + (qy - cy) * (qy - cy) - rc2);
+      row[h] = -((hn - hs) / d.dt) - d.gamma_b * hs;
+      if (BWD && row[h] > 0.f) {   // d row / d hn = -1/dt ; d hn / d q = (q - c)
+        const float s = -g[h] / d.dt;
+        gqx = fmaf(s, qx - cx, gqx);
+        gqy = fmaf(s, qy - cy, gqy);
+      }
+    }
+    const int m = d.n_hazards;
+    row[m] = ((vn - v) * d.lya_inv_dt) + d.gamma_l * v;
+    if (BWD) {
+      gb[2 * i] = gqx; gb[2 * i + 1] = gqy;
+      gVn[i] = row[m] > 0.f ? g[m] * d.lya_inv_dt : 0.f;
+    }
+    return m + 1;
+  }
+  if (d.kind == NLBAC_CONSTRAINT_CARS) {
+    // a = x_t [B,10], b = x_{t+1} [B,10], c = x_{t+2} [B,10];  h23 = x3 - x4 - r, h34 = x4 - x5 - r (positions at 4,6,8)
+    const float r = d.collision_radius, gb_ = d.gamma_b;
+    const float* x0 = a + 10 * i; const float* x1 = b + 10 * i; const float* x2 = c + 10 * i;
+    float g1[10], g2[10];
+#pragma unroll
+    for (int k = 0; k < 10; ++k) g1[k] = g2[k] = 0.f;
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+      const int ia = 4 + 2 * p, ib = 6 + 2 * p;
+      const float h0 = x0[ia] - x0[ib] - r, h1 = x1[ia] - x1[ib] - r, h2 = x2[ia] - x2[ib] - r;
+      const float l1 = h1 - h0 + gb_ * h0;
+      const float l2 = h2 - h1 + gb_ * h1;
+      row[p] = -(l2 - l1) - gb_ * l1;
+      if (BWD && row[p] > 0.f) {
+        // d row/d h2 = -1 ; d row/d h1 = -(-1 + gb) + (1 - gb) = 2 - 2 gb   [l2: -1+gb, l1: +1 then *(1-gb)]
+        const float dh2 = -g[p];
+        const float dh1 = g[p] * ((1.f - gb_) + (1.f - gb_));
+        g2[ia] += dh2; g2[ib] -= dh2;
+        g1[ia] += dh1; g1[ib] -= dh1;
+      }
+    }
+    row[2] = (vn - v) * d.lya_inv_dt + d.gamma_l * v;
+    if (BWD) {
+#pragma unroll
+      for (int k = 0; k < 10; ++k) { gb[10 * i + k] = g1[k]; gc[10 * i + k] = g2[k]; }
+      gVn[i] = row[2] > 0.f ? g[2] * d.lya_inv_dt : 0.f;
+    }
+    return 3;
+  }
+  // NLBAC_CONSTRAINT_BARRIER: a = B(x_t,u_t) (detached) [B], b = B(x_{t+1},u_{t+1}) [B]
+  const float bv = a[i], bn = b[i];
+  row[0] = -(bn - bv) - d.gamma_b * bv;
+  row[1] = (vn - v) * d.lya_inv_dt + d.gamma_l * v;
+  if (BWD) {
+    gb[i] = row[0] > 0.f ? -g[0] : 0.f;
+    gVn[i] = row[1] > 0.f ? g[1] * d.lya_inv_dt : 0.f;
+  }
+  return 2;
+}
+
+__global__ void __launch_bounds__(CNT) constraints_fwd_kernel(nlbac_constraint_desc d, const float* a, const float* b,
+                                                              const float* c, const float* V, const float* Vn,
+                                                              long long B, float* req) {
+  __shared__ float red[CNT / 32][MAXM];
+  float acc[MAXM];
+#pragma unroll
+  for (int k = 0; k < MAXM; ++k) acc[k] = 0.f;
+  int m = 0;
+  for (long long i = (long long)blockIdx.x * CNT + threadIdx.x; i < B; i += (long long)gridDim.x * CNT) {
+    float row[MAXM];
+    m = constraint_rows<false>(d, a, b, c, V, Vn, i, row, nullptr, nullptr, nullptr, nullptr);
+#pragma unroll
+    for (int k = 0; k < MAXM; ++k)
+      if (k < m && row[k] > 0.f) acc[k] += row[k];   // torch.where(matr > 0, matr, 0)
+  }
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+#pragma unroll
+  for (int k = 0; k < MAXM; ++k) {
+    const float s = warp_sum(acc[k]);
+    if (lane == 0) red[warp][k] = s;
+  }
+  __syncthreads();
+  if (threadIdx.x < d.m) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < CNT / 32; ++w) s += red[w][threadIdx.x];
+    atomicAdd(req + threadIdx.x, s / d.batch_size);
+  }
+}
+
+__global__ void __launch_bounds__(CNT) constraints_bwd_kernel(nlbac_constraint_desc d, const float* a, const float* b,
+                                                              const float* c, const float* V, const float* Vn,
+                                                              long long B, const float* grad_req, float* gb, float* gc,
+                                                              float* gVn) {
+  __shared__ float g[MAXM];
+  if (threadIdx.x < MAXM) g[threadIdx.x] = threadIdx.x < d.m ? grad_req[threadIdx.x] / d.batch_size : 0.f;
+  __syncthreads();
+  for (long long i = (long long)blockIdx.x * CNT + threadIdx.x; i < B; i += (long long)gridDim.x * CNT) {
+    float row[MAXM];
+    constraint_rows<true>(d, a, b, c, V, Vn, i, row, g, gb, gc, gVn);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// lookahead point and obs/state maps
+// ------------------------------------------------------------------------------------------------
+__global__ void lookahead_fwd_kernel(const float* state, int ld, float l_p, long long B, float* p) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < B; i += (long long)gridDim.x * blockDim.x) {
+    const float th = state[i * ld + 2];
+    float s, c;
+    sincosf(th, &s, &c);
+    p[2 * i] = fmaf(l_p, c, state[i * ld]);
+    p[2 * i + 1] = fmaf(l_p, s, state[i * ld + 1]);
+  }
+}
+__global__ void lookahead_bwd_kernel(const float* state, int ld, float l_p, long long B, const float* gp, float* gs) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < B; i += (long long)gridDim.x * blockDim.x) {
+    const float th = state[i * ld + 2];
+    float s, c;
+    sincosf(th, &s, &c);
+    const float gx = gp[2 * i], gy = gp[2 * i + 1];
+    gs[i * ld] = gx;
+    gs[i * ld + 1] = gy;
+    gs[i * ld + 2] = l_p * (gy * c - gx * s);
+    for (int k = 3; k < ld; ++k) gs[i * ld + k] = 0.f;
+  }
+}
+
+// get_state: the reference does the arithmetic in float64 numpy and rounds back
+__global__ void get_state_kernel(int kind, const float* obs, long long B, float* state, float* state_dyn) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < B; i += (long long)gridDim.x * blockDim.x) {
+    if (kind == NLBAC_ENV_UNICYCLE) {
+      const float* o = obs + 7 * i;
+      state[3 * i] = o[0]; state[3 * i + 1] = o[1];
+      state[3 * i + 2] = (float)atan2((double)o[3], (double)o[2]);
+    } else if (kind == NLBAC_ENV_CARS) {
+      for (int k = 0; k < 10; ++k) state[10 * i + k] = (float)((double)obs[10 * i + k] * ((k & 1) ? 30.0 : 100.0));
+    } else {  // PVTOL: obs[11] -> state7 and its first 6
+      const float* o = obs + 11 * i;
+      const float th = (float)atan2((double)o[3], (double)o[2]);
+      const float s7[7] = {o[0], o[1], th, o[4], o[5], o[6], o[7]};
+      for (int k = 0; k < 7; ++k) state[7 * i + k] = s7[k];
+      if (state_dyn)
+        for (int k = 0; k < 6; ++k) state_dyn[6 * i + k] = s7[k];
+    }
+  }
+}
+
+struct ObsGeom { int n_s, n_o; float gx, gy; };
+__device__ __forceinline__ ObsGeom obs_geom(int kind) {
+  if (kind == NLBAC_ENV_UNICYCLE) return {3, 7, 2.5f, 2.5f};   // BU dynamics.py:106-107
+  if (kind == NLBAC_ENV_CARS) return {10, 10, 0.f, 0.f};
+  return {7, 11, 4.5f, 4.5f};                                    // P dynamics.py:115-116
+}
+// obs = [x, y, cos, sin, (pass-through), compass_x, compass_y, exp(-dist)]
+template <bool BWD>
+__global__ void get_obs_kernel(int kind, const float* state, long long B, float* obs, const float* gobs, float* gstate) {
+  const ObsGeom G = obs_geom(kind);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < B; i += (long long)gridDim.x * blockDim.x) {
+    const float* s = state + (long long)G.n_s * i;
+    if (kind == NLBAC_ENV_CARS) {
+      for (int k = 0; k < 10; ++k) {
+        const float div = (k & 1) ? 30.0f : 100.0f;
+        if (!BWD) obs[10 * i + k] = s[k] / div;
+        else gstate[10 * i + k] = gobs[10 * i + k] / div;
+      }
+      continue;
+    }
+    const int np = G.n_s - 3;   // pass-through columns after theta
+    float st, ct;
+    sincosf(s[2], &st, &ct);
+    const float rx = G.gx - s[0], ry = G.gy - s[1];
+    const float dist = sqrtf(rx * rx + ry * ry);
+    const float vx = ct * rx + st * ry, vy = -st * rx + ct * ry;   // Rs = [[c, s], [-s, c]]
+    const float nv = sqrtf(vx * vx + vy * vy);
+    const float den = nv + 0.001f;
+    const float e = expf(-dist);
+    if (!BWD) {
+      float* o = obs + (long long)G.n_o * i;
+      o[0] = s[0]; o[1] = s[1]; o[2] = ct; o[3] = st;
+      for (int k = 0; k < np; ++k) o[4 + k] = s[3 + k];
+      o[4 + np] = vx / den; o[5 + np] = vy / den; o[6 + np] = e;
+    } else {
+      const float* g = gobs + (long long)G.n_o * i;
+      float* gs = gstate + (long long)G.n_s * i;
+      const float gcx = g[4 + np], gcy = g[5 + np], ge = g[6 + np];
+      // compass = v / (|v| + 1e-3):  dL/dv = g/den - v (g.v) / (|v| den^2)
+      const float gv_dot = gcx * vx + gcy * vy;
+      const float k2 = nv > 0.f ? gv_dot / (nv * den * den) : 0.f;
+      const float gvx = gcx / den - vx * k2, gvy = gcy / den - vy * k2;
+      // v = R r:  dL/dr = R^T gv ;  dL/dtheta = gv . (dR/dtheta r) = gvx * vy - gvy * vx
+      float grx = ct * gvx - st * gvy, gry = st * gvx + ct * gvy;
+      // exp(-dist): d/dr = -e * r / dist
+      if (dist > 0.f) { grx -= ge * e * rx / dist; gry -= ge * e * ry / dist; }
+      gs[0] = g[0] - grx;   // r = goal - p
+      gs[1] = g[1] - gry;
+      gs[2] = -g[2] * st + g[3] * ct + gvx * vy - gvy * vx;
+      for (int k = 0; k < np; ++k) gs[3 + k] = g[4 + k];
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Adam (torch.optim.Adam defaults: no weight decay, no amsgrad) and Polyak averaging, flat tensors
+// ------------------------------------------------------------------------------------------------
+__global__ void adam_kernel(float* p, const float* g, float* m, float* v, long long n, float lr, float b1, float b2,
+                            float eps, float bc1, float bc2_sqrt) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float mi = m[i] + (gi - m[i]) * (1.f - b1);      // exp_avg.lerp_(grad, 1 - beta1)
+    const float vi = fmaf(v[i], b2, (1.f - b2) * gi * gi);  // exp_avg_sq.mul_(b2).addcmul_(g, g, 1 - b2)
+    m[i] = mi; v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = p[i] - (lr / bc1) * (mi / denom);
+  }
+}
+__global__ void soft_update_kernel(float* target, const float* src, long long n, float tau) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    target[i] = target[i] * (1.0f - tau) + src[i] * tau;
+}
+
+static int check_constraint(const nlbac_constraint_desc* d) {
+  NLBAC_REQUIRE(d != nullptr, "null constraint descriptor");
+  NLBAC_REQUIRE(d->kind >= NLBAC_CONSTRAINT_UNICYCLE && d->kind <= NLBAC_CONSTRAINT_BARRIER, "unknown constraint kind %d", d->kind);
+  const int want = d->kind == NLBAC_CONSTRAINT_UNICYCLE ? d->n_hazards + 1 : (d->kind == NLBAC_CONSTRAINT_CARS ? 3 : 2);
+  NLBAC_REQUIRE(d->m == want && d->m <= MAXM, "constraint rows m=%d, expected %d (<= %d)", d->m, want, MAXM);
+  NLBAC_REQUIRE(d->n_hazards >= 0 && d->n_hazards <= NLBAC_MAX_HAZARDS, "n_hazards=%d", d->n_hazards);
+  NLBAC_REQUIRE(d->batch_size > 0.f && d->dt > 0.f, "batch_size and dt must be positive");
+  return 0;
+}
+
+}  // namespace nlbac
+
+using namespace nlbac;
+
+extern "C" {
+
+int nlbac_constraints_fwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
+                          const float* V, const float* Vnext, int64_t B, float* req, void* stream) {
+  if (int rc = check_constraint(desc)) return rc;
+  NLBAC_REQUIRE(a && b && V && Vnext && req, "null pointer");
+  NLBAC_REQUIRE(desc->kind != NLBAC_CONSTRAINT_CARS || c, "cars constraints need x_{t+2}");
+  NLBAC_REQUIRE(B >= 0, "negative batch");
+  cudaStream_t st = (cudaStream_t)stream;
+  NLBAC_CUDA(cudaMemsetAsync(req, 0, desc->m * 4, st));
+  if (B == 0) return 0;
+  constraints_fwd_kernel<<<tail_grid(B, CNT), CNT, 0, st>>>(*desc, a, b, c, V, Vnext, B, req);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_constraints_bwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
+                          const float* V, const float* Vnext, int64_t B, const float* grad_req, float* grad_b,
+                          float* grad_c, float* grad_Vnext, void* stream) {
+  if (int rc = check_constraint(desc)) return rc;
+  NLBAC_REQUIRE(a && b && V && Vnext && grad_req && grad_b && grad_Vnext, "null pointer");
+  NLBAC_REQUIRE(desc->kind != NLBAC_CONSTRAINT_CARS || (c && grad_c), "cars constraints need x_{t+2} and its gradient");
+  if (B <= 0) return 0;
+  constraints_bwd_kernel<<<tail_grid(B, CNT), CNT, 0, (cudaStream_t)stream>>>(*desc, a, b, c, V, Vnext, B, grad_req,
+                                                                              grad_b, grad_c, grad_Vnext);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_lookahead_fwd(const float* state, int n_s, float l_p, int64_t B, float* p, void* stream) {
+  NLBAC_REQUIRE(state && p && n_s >= 3 && B >= 0, "bad arguments");
+  if (B == 0) return 0;
+  lookahead_fwd_kernel<<<tail_grid(B, 256), 256, 0, (cudaStream_t)stream>>>(state, n_s, l_p, B, p);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+int nlbac_lookahead_bwd(const float* state, int n_s, float l_p, int64_t B, const float* grad_p, float* grad_state,
+                        void* stream) {
+  NLBAC_REQUIRE(state && grad_p && grad_state && n_s >= 3 && B >= 0, "bad arguments");
+  if (B == 0) return 0;
+  lookahead_bwd_kernel<<<tail_grid(B, 256), 256, 0, (cudaStream_t)stream>>>(state, n_s, l_p, B, grad_p, grad_state);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_get_state(int env, const float* obs, int64_t B, float* state, float* state_dyn, void* stream) {
+  NLBAC_REQUIRE(env >= NLBAC_ENV_UNICYCLE && env <= NLBAC_ENV_PVTOL, "unknown env %d", env);
+  NLBAC_REQUIRE(obs && state && B >= 0, "bad arguments");
+  if (B == 0) return 0;
+  get_state_kernel<<<tail_grid(B, 256), 256, 0, (cudaStream_t)stream>>>(env, obs, B, state, state_dyn);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+int nlbac_get_obs_fwd(int env, const float* state, int64_t B, float* obs, void* stream) {
+  NLBAC_REQUIRE(env >= NLBAC_ENV_UNICYCLE && env <= NLBAC_ENV_PVTOL, "unknown env %d", env);
+  NLBAC_REQUIRE(state && obs && B >= 0, "bad arguments");
+  if (B == 0) return 0;
+  get_obs_kernel<false><<<tail_grid(B, 256), 256, 0, (cudaStream_t)stream>>>(env, state, B, obs, nullptr, nullptr);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+int nlbac_get_obs_bwd(int env, const float* state, int64_t B, const float* grad_obs, float* grad_state, void* stream) {
+  NLBAC_REQUIRE(env >= NLBAC_ENV_UNICYCLE && env <= NLBAC_ENV_PVTOL, "unknown env %d", env);
+  NLBAC_REQUIRE(state && grad_obs && grad_state && B >= 0, "bad arguments");
+  if (B == 0) return 0;
+  get_obs_kernel<true><<<tail_grid(B, 256), 256, 0, (cudaStream_t)stream>>>(env, state, B, nullptr, grad_obs, grad_state);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, int step, float lr,
+                    float beta1, float beta2, float eps, void* stream) {
+  NLBAC_REQUIRE(param && grad && exp_avg && exp_avg_sq && n >= 0 && step >= 1, "bad arguments");
+  if (n == 0) return 0;
+  const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
+  adam_kernel<<<tail_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2,
+                                                                   eps, (float)bc1, (float)sqrt(bc2));
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+int nlbac_soft_update(float* target, const float* source, int64_t n, float tau, void* stream) {
+  NLBAC_REQUIRE(target && source && n >= 0, "bad arguments");
+  if (n == 0) return 0;
+  soft_update_kernel<<<tail_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(target, source, n, tau);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,247 @@
+"""Fused element-wise / reduction tail of the update step over the C ABI.
+
+* ``constraint_sums``  — CBF/CLF rows -> ``where(>0)`` -> batch sum / ``batch_size`` (U sac_cbf_clf.py:472-504,
+  C :474-523, BU :424-460), one kernel forward, one backward.
+* ``lookahead``        — ``p(x) = [x, y] + l_p [cos th, sin th]`` (U sac_cbf_clf.py:429-437).
+* ``DynamicsModel``    — ``get_state`` / ``get_obs`` with the reference's signatures (U dynamics.py:27-69,
+  C :25-96, P :25-153, BU :73-198); tensors never leave the device.
+* ``FusedAdam`` / ``soft_update`` — torch.optim.Adam.step on flat tensors and Polyak averaging (U utils.py:75-79).
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+
+CONSTRAINT_KINDS = {"unicycle": 0, "cars": 1, "barrier": 2}
+ENVS = {"Unicycle": 0, "SimulatedCars": 1, "Pvtol": 2}
+_OBS_DIMS = {0: (7, 3), 1: (10, 10), 2: (11, 7)}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _cuda32(*ts):
+    out = []
+    for t in ts:
+        if t is None:
+            out.append(None)
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("nlbac_b200: tensors must be CUDA tensors (no CPU fallback)")
+        out.append(t.detach().contiguous().float())
+    return out
+
+
+def _p(t):
+    return None if t is None else t.data_ptr()
+
+
+def make_constraint_desc(kind, *, dt, gamma_b, gamma_l, batch_size, lya_inv_dt=None, collision_radius=0.0,
+                         hazards=None):
+    d = _lib.ConstraintDesc()
+    d.kind = CONSTRAINT_KINDS[kind]
+    hz = np.zeros((0, 2), dtype=np.float32) if hazards is None else np.asarray(hazards, dtype=np.float32).reshape(-1, 2)
+    if len(hz) > _lib.MAX_HAZARDS:
+        raise ValueError("at most %d hazards" % _lib.MAX_HAZARDS)
+    d.n_hazards = len(hz) if kind == "unicycle" else 0
+    d.m = d.n_hazards + 1 if kind == "unicycle" else (3 if kind == "cars" else 2)
+    d.dt, d.gamma_b, d.gamma_l = float(dt), float(gamma_b), float(gamma_l)
+    d.lya_inv_dt = float(1.0 / dt if lya_inv_dt is None else lya_inv_dt)
+    d.batch_size = float(batch_size)
+    d.collision_radius = float(collision_radius)
+    for i, v in enumerate(hz.reshape(-1)):
+        d.hazards[i] = float(v)
+    return d
+
+
+class _ConstraintSums(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, desc, a, b, c, V, Vnext):
+        L = _lib.lib()
+        a_, b_, c_, V_, Vn_ = _cuda32(a, b, c, V, Vnext)
+        B = V_.shape[0]
+        req = torch.empty((desc.m, 1), dtype=torch.float32, device=V_.device)
+        _lib.check(L.nlbac_constraints_fwd(ctypes.byref(desc), _p(a_), _p(b_), _p(c_), _p(V_), _p(Vn_), B,
+                                           req.data_ptr(), _stream()), "constraints_fwd")
+        ctx.desc = desc
+        ctx.save_for_backward(a_, b_, V_, Vn_, *([c_] if c_ is not None else []))
+        ctx.shapes = (b.shape, None if c is None else c.shape, Vnext.shape)
+        return req
+
+    @staticmethod
+    def backward(ctx, g):
+        L = _lib.lib()
+        a_, b_, V_, Vn_, *rest = ctx.saved_tensors
+        c_ = rest[0] if rest else None
+        B = V_.shape[0]
+        gb = torch.empty_like(b_)
+        gc = torch.empty_like(c_) if c_ is not None else None
+        gV = torch.empty_like(Vn_)
+        gq = g.contiguous().float()
+        _lib.check(L.nlbac_constraints_bwd(ctypes.byref(ctx.desc), _p(a_), _p(b_), _p(c_), _p(V_), _p(Vn_), B,
+                                           gq.data_ptr(), gb.data_ptr(), _p(gc), gV.data_ptr(), _stream()),
+                   "constraints_bwd")
+        sb, sc, sv = ctx.shapes
+        return None, None, gb.view(sb), (gc.view(sc) if gc is not None else None), None, gV.view(sv)
+
+
+def constraint_sums(desc, a, b, c, V, Vnext):
+    """``required_matrix`` [m, 1] of the reference: filtered constraint rows summed over the batch and divided
+    by ``batch_size``.  Gradients flow to ``b`` (x_{t+1} quantities), ``c`` (x_{t+2}) and ``Vnext``."""
+    return _ConstraintSums.apply(desc, a, b, c, V, Vnext)
+
+
+class _Lookahead(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, state, l_p):
+        L = _lib.lib()
+        (s,) = _cuda32(state)
+        B, n_s = s.shape
+        p = torch.empty((B, 2), dtype=torch.float32, device=s.device)
+        _lib.check(L.nlbac_lookahead_fwd(s.data_ptr(), n_s, float(l_p), B, p.data_ptr(), _stream()), "lookahead_fwd")
+        ctx.save_for_backward(s)
+        ctx.l_p = float(l_p)
+        return p
+
+    @staticmethod
+    def backward(ctx, gp):
+        L = _lib.lib()
+        (s,) = ctx.saved_tensors
+        B, n_s = s.shape
+        gs = torch.empty_like(s)
+        g = gp.contiguous().float()
+        _lib.check(L.nlbac_lookahead_bwd(s.data_ptr(), n_s, ctx.l_p, B, g.data_ptr(), gs.data_ptr(), _stream()),
+                   "lookahead_bwd")
+        return gs, None
+
+
+def lookahead(state, l_p):
+    return _Lookahead.apply(state, l_p)
+
+
+class _GetObs(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, state, env):
+        L = _lib.lib()
+        (s,) = _cuda32(state)
+        B = s.shape[0]
+        obs = torch.empty((B, _OBS_DIMS[env][0]), dtype=torch.float32, device=s.device)
+        _lib.check(L.nlbac_get_obs_fwd(env, s.data_ptr(), B, obs.data_ptr(), _stream()), "get_obs_fwd")
+        ctx.save_for_backward(s)
+        ctx.env = env
+        return obs
+
+    @staticmethod
+    def backward(ctx, g):
+        L = _lib.lib()
+        (s,) = ctx.saved_tensors
+        gs = torch.empty_like(s)
+        gc = g.contiguous().float()
+        _lib.check(L.nlbac_get_obs_bwd(ctx.env, s.data_ptr(), s.shape[0], gc.data_ptr(), gs.data_ptr(), _stream()),
+                   "get_obs_bwd")
+        return gs, None
+
+
+class DynamicsModel:
+    """``DynamicsModel(env, args)`` with ``get_state`` / ``get_obs`` like the reference (U dynamics.py:10-76).
+
+    ``env`` needs only ``dynamics_mode`` ('Unicycle' | 'SimulatedCars' | 'Pvtol').  Tensor inputs stay on the
+    GPU (the reference round-trips through float64 numpy, App. D.1; the kernel does the same arithmetic in
+    float64 registers); ndarray inputs follow the reference's numpy path on the host, as in ``select_action``.
+    """
+
+    def __init__(self, env, args=None):
+        self.env = env
+        if env.dynamics_mode not in ENVS:
+            raise Exception('Unknown dynamics')
+        self.kind = ENVS[env.dynamics_mode]
+
+    def seed(self, s):
+        torch.manual_seed(s)
+
+    def get_state(self, obs):
+        if not torch.is_tensor(obs):
+            return self._get_state_numpy(np.asarray(obs))
+        expand = obs.ndim == 1
+        o = obs.unsqueeze(0) if expand else obs
+        (oc,) = _cuda32(o)
+        n_o, n_s = _OBS_DIMS[self.kind]
+        if oc.shape[1] != n_o:
+            raise ValueError("observation width %d != %d" % (oc.shape[1], n_o))
+        B = oc.shape[0]
+        L = _lib.lib()
+        state = torch.empty((B, n_s), dtype=torch.float32, device=oc.device)
+        dyn = torch.empty((B, 6), dtype=torch.float32, device=oc.device) if self.kind == 2 else None
+        _lib.check(L.nlbac_get_state(self.kind, oc.data_ptr(), B, state.data_ptr(), _p(dyn), _stream()), "get_state")
+        state = state.to(obs.dtype)
+        if self.kind == 2:
+            dyn = dyn.to(obs.dtype)
+            return (state.squeeze(0), dyn.squeeze(0)) if expand else (state, dyn)
+        return state.squeeze(0) if expand else state
+
+    def _get_state_numpy(self, obs):
+        expand = obs.ndim == 1
+        o = obs[None] if expand else obs
+        if self.kind == 0:
+            st = np.stack([o[:, 0], o[:, 1], np.arctan2(o[:, 3], o[:, 2])], 1)
+        elif self.kind == 1:
+            st = np.copy(o)
+            st[:, ::2] *= 100.0
+            st[:, 1::2] *= 30.0
+        else:
+            st = np.stack([o[:, 0], o[:, 1], np.arctan2(o[:, 3], o[:, 2]), o[:, 4], o[:, 5], o[:, 6], o[:, 7]], 1)
+            dyn = st[:, :6]
+            return (st[0], dyn[0]) if expand else (st, dyn)
+        return st[0] if expand else st
+
+    def get_obs(self, state_batch, device=None):
+        """``state_batch`` is ``[B, n_s, 1]`` like the reference (or ``[B, n_s]``); returns the same rank."""
+        col = state_batch.ndim == 3
+        s = state_batch.squeeze(-1) if col else state_batch
+        obs = _GetObs.apply(s, self.kind)
+        return obs.unsqueeze(-1) if col else obs
+
+
+class FusedAdam(torch.optim.Optimizer):
+    """torch.optim.Adam (default betas/eps, no weight decay) with the update run by ``nlbac_adam_step``."""
+
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        L = _lib.lib()
+        for group in self.param_groups:
+            b1, b2 = group["betas"]
+            for p in group["params"]:
+                if p.grad is None:
+                    continue
+                if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
+                    raise RuntimeError("FusedAdam: parameters must be contiguous float32 CUDA tensors")
+                st = self.state[p]
+                if not st:
+                    st["step"] = 0
+                    st["exp_avg"] = torch.zeros_like(p)
+                    st["exp_avg_sq"] = torch.zeros_like(p)
+                st["step"] += 1
+                g = p.grad.contiguous()
+                _lib.check(L.nlbac_adam_step(p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(),
+                                             st["exp_avg_sq"].data_ptr(), p.numel(), st["step"], group["lr"], b1, b2,
+                                             group["eps"], _stream()), "adam_step")
+
+
+@torch.no_grad()
+def soft_update(target, source, tau):
+    """``utils.soft_update(target, source, tau)`` (U utils.py:75-79)."""
+    L = _lib.lib()
+    for tp, sp in zip(target.parameters(), source.parameters()):
+        _lib.check(L.nlbac_soft_update(tp.data_ptr(), sp.data_ptr(), tp.numel(), float(tau), _stream()), "soft_update")
+
+
+@torch.no_grad()
+def hard_update(target, source):
+    for tp, sp in zip(target.parameters(), source.parameters()):
+        tp.copy_(sp)

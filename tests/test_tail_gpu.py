@@ -1,0 +1,168 @@
+"""GPU parity of the constraint block, obs/state maps, Adam and Polyak kernels (nlbac_constraints_*,
+nlbac_lookahead_*, nlbac_get_state, nlbac_get_obs_*, nlbac_adam_step, nlbac_soft_update) against the golden
+vectors produced by the reference's own get_policy_loss_2 / DynamicsModel and against the CPU oracle.
+Tolerance rel 1e-5 unless stated (max-norm per tensor)."""
+import os
+
+import pytest
+import torch
+
+from oracle import constraints as OC
+from oracle import nlbac_ref
+from constraint_cases import build, run_sequence
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+def _rel(a, b):
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+class _Env:
+    def __init__(self, mode):
+        self.dynamics_mode = mode
+
+
+@pytest.mark.parametrize("tag,env", [("U", "Unicycle"), ("C", "SimulatedCars"), ("BU", "Unicycle")])
+def test_policy_loss_2_matches_reference_and_oracle(tag, env, golden_dir):
+    import nlbac_b200
+    g = torch.load(os.path.join(golden_dir, "constraints_%s.pt" % tag), weights_only=False)
+    nets = build(g, nlbac_b200, "cuda")
+    dyn = nlbac_b200.DynamicsModel(_Env(env))
+    losses, grads, st = run_sequence(g, nets, nlbac_b200.constraints, "cuda", dyn)
+    o_losses, o_grads, _ = run_sequence(g, build(g, nlbac_ref, "cpu"), OC, "cpu")
+    for got, want, ow in zip(losses, g["losses"], o_losses):
+        assert _rel(got, want.reshape(-1)) <= 2 * TOL and _rel(got, ow) <= 2 * TOL
+    for got, want, ow in zip(grads, g["grad_action"], o_grads):
+        assert _rel(got, want) <= 5 * TOL and _rel(got, ow) <= 5 * TOL
+    lam = torch.tensor([float(v) for v in st.lambda_values])
+    assert _rel(lam, torch.tensor(g["lambda_after"])) <= 2 * TOL
+
+
+def test_get_state_and_get_obs(golden_dir):
+    import nlbac_b200
+    for tag, env in (("U", "Unicycle"), ("C", "SimulatedCars"), ("BU", "Unicycle")):
+        g = torch.load(os.path.join(golden_dir, "constraints_%s.pt" % tag), weights_only=False)
+        dm = nlbac_b200.DynamicsModel(_Env(env))
+        st = dm.get_state(g["obs"].cuda())
+        # float64 atan2 rounded to fp32, like the reference's numpy round trip: exact or 1 ulp (libm vs CUDA fp64 atan2)
+        assert _rel(st, g["state_from_obs"]) <= 2e-7
+        one = dm.get_state(g["obs"][0].cuda())
+        assert one.shape == g["state_from_obs"][0].shape
+    g = torch.load(os.path.join(golden_dir, "constraints_BU.pt"), weights_only=False)
+    dm = nlbac_b200.DynamicsModel(_Env("Unicycle"))
+    s = g["state"].cuda().requires_grad_(True)
+    obs = dm.get_obs(s.unsqueeze(-1))
+    assert obs.shape == (s.shape[0], 7, 1)
+    assert _rel(obs.squeeze(-1), g["obs"]) <= TOL
+    (obs.squeeze(-1) * g["obs_cot"].cuda()).sum().backward()
+    assert _rel(s.grad, g["grad_state_get_obs"]) <= 2 * TOL
+    p = torch.load(os.path.join(golden_dir, "constraints_Pmaps.pt"), weights_only=False)
+    dm = nlbac_b200.DynamicsModel(_Env("Pvtol"))
+    s = p["state7"].cuda().requires_grad_(True)
+    obs = dm.get_obs(s, "cuda")
+    assert _rel(obs, p["obs"]) <= TOL
+    (obs * p["obs_cot"].cuda()).sum().backward()
+    assert _rel(s.grad, p["grad_state_get_obs"]) <= 2 * TOL
+    st, dyn = dm.get_state(p["obs"].cuda())
+    assert _rel(st, p["state_from_obs"]) <= 2e-7 and _rel(dyn, p["state_dyn_from_obs"]) <= 2e-7
+    c = torch.load(os.path.join(golden_dir, "constraints_C.pt"), weights_only=False)
+    dm = nlbac_b200.DynamicsModel(_Env("SimulatedCars"))
+    assert _rel(dm.get_obs(c["state"].cuda()), c["obs"]) <= 1e-7
+    import numpy as np
+    assert np.allclose(dm.get_state(c["obs"].numpy()), c["state_from_obs"].numpy(), rtol=1e-6)
+
+
+@pytest.mark.parametrize("kind,B", [("unicycle", 1), ("unicycle", 100000), ("cars", 3), ("cars", 70001), ("barrier", 2), ("barrier", 65537)])
+def test_constraint_sums_vs_oracle_rows(kind, B):
+    """Kernel rows + filter + reduction (and gradients) on synthetic tensors, including B=1 and multi-CTA sizes."""
+    import nlbac_b200
+    g = torch.Generator().manual_seed(B)
+    r = lambda *s: torch.randn(*s, generator=g)  # noqa: E731
+    V, Vn = r(B, 1), r(B, 1).requires_grad_(True)
+    bs = 256.0
+    if kind == "unicycle":
+        hz = torch.tensor([[0., 0.], [0., 1.], [0., -1.], [-1., 1.], [-1., -1.], [1., -1.], [1., 1.]]) * 1.5
+        a, b = r(B, 2) * 1.5, (r(B, 2) * 1.5).requires_grad_(True)
+        desc = nlbac_b200.make_constraint_desc("unicycle", dt=0.02, gamma_b=50.0, gamma_l=1.0, batch_size=bs,
+                                               collision_radius=0.525, hazards=hz.numpy())
+        hs = 0.5 * (((a[:, None] - hz[None]) ** 2).sum(2) - 0.525 ** 2)
+        hn = 0.5 * (((b[:, None] - hz[None]) ** 2).sum(2) - 0.525 ** 2)
+        rows = torch.cat((-((hn - hs) / 0.02) - 50.0 * hs, (Vn - V) / 0.02 + V), 1)
+        c = None
+    elif kind == "cars":
+        base = torch.tensor([42.0, 3, 36, 3, 31, 3, 26, 3, 21, 3])
+        a, b, c = base + r(B, 10), (base + r(B, 10)).requires_grad_(True), (base + r(B, 10)).requires_grad_(True)
+        desc = nlbac_b200.make_constraint_desc("cars", dt=0.02, gamma_b=0.5, gamma_l=0.15, batch_size=bs,
+                                               lya_inv_dt=1.0, collision_radius=4.5)
+        rr = []
+        for ia, ib in ((4, 6), (6, 8)):
+            h0, h1, h2 = (x[:, ia:ia + 1] - x[:, ib:ib + 1] - 4.5 for x in (a, b, c))
+            l1, l2 = h1 - h0 + 0.5 * h0, h2 - h1 + 0.5 * h1
+            rr.append(-(l2 - l1) - 0.5 * l1)
+        rows = torch.cat(rr + [(Vn - V) + 0.15 * V], 1)
+    else:
+        a, b, c = r(B, 1), r(B, 1).requires_grad_(True), None
+        desc = nlbac_b200.make_constraint_desc("barrier", dt=0.02, gamma_b=5.0, gamma_l=1.0, batch_size=bs)
+        rows = torch.cat((-(b - a) - 5.0 * a, (Vn - V) / 0.02 + V), 1)
+    want = OC.required_matrix_from_rows(rows.double(), bs)
+    w = torch.arange(1, want.shape[0] + 1, dtype=torch.float64).unsqueeze(-1)
+    (want * w).sum().backward()
+    leaves = [t for t in (b, c, Vn) if t is not None]
+    want_g = [t.grad.clone() for t in leaves]
+    dev = [t.detach().cuda().requires_grad_(True) for t in leaves]
+    bb = dev[0]
+    cc = dev[1] if c is not None else None
+    got = nlbac_b200.constraint_sums(desc, a.cuda(), bb, cc, V.cuda(), dev[-1])
+    assert got.shape == want.shape
+    assert _rel(got, want) <= 2 * TOL     # fp32 atomics over up to 400 CTAs vs an fp64 reference
+    (got * w.float().cuda()).sum().backward()
+    for d_, wg in zip(dev, want_g):
+        assert _rel(d_.grad, wg) <= TOL
+
+
+def test_fused_adam_and_soft_update_match_torch():
+    import nlbac_b200
+    torch.manual_seed(0)
+    a = torch.nn.Linear(37, 53).cuda()
+    b = torch.nn.Linear(37, 53).cuda()
+    b.load_state_dict(a.state_dict())
+    oa = torch.optim.Adam(a.parameters(), lr=1e-3)
+    ob = nlbac_b200.FusedAdam(b.parameters(), lr=1e-3)
+    for i in range(5):
+        x = torch.randn(16, 37, device="cuda")
+        for net, opt in ((a, oa), (b, ob)):
+            opt.zero_grad()
+            net(x).pow(2).sum().backward()
+            opt.step()
+    for p, q in zip(a.parameters(), b.parameters()):
+        assert _rel(q, p) <= 1e-6
+    tgt_a, tgt_b = torch.nn.Linear(37, 53).cuda(), torch.nn.Linear(37, 53).cuda()
+    tgt_b.load_state_dict(tgt_a.state_dict())
+    for tp, sp in zip(tgt_a.parameters(), a.parameters()):
+        tp.data.copy_(tp.data * (1.0 - 0.005) + sp.data * 0.005)
+    nlbac_b200.soft_update(tgt_b, a, 0.005)
+    for p, q in zip(tgt_a.parameters(), tgt_b.parameters()):
+        assert _rel(q, p) <= 1e-7
+    nlbac_b200.hard_update(tgt_b, a)
+    assert all(torch.equal(p, q) for p, q in zip(tgt_b.parameters(), a.parameters()))
+
+
+def test_train_step_with_fused_adam_matches_golden(golden_dir):
+    """train_step (zero_grad -> fused solve -> MSE -> fused backward -> Adam) with the fused optimiser reproduces
+    the reference's own 3-step trace."""
+    import nlbac_b200
+    g = torch.load(os.path.join(golden_dir, "node_U.pt"), weights_only=False)
+    m = nlbac_b200.NeuralODEModel(3, 3, 6)
+    m.load_state_dict(g["state_dict"])
+    m.cuda()
+    opt = nlbac_b200.FusedAdam(m.parameters(), lr=1e-3)
+    y0, tr = g["y0"].cuda(), g["train"]
+    for want in tr["losses"]:
+        got = nlbac_b200.train_step(m, y0[:, :3], y0[:, 3:5], tr["next_state"].cuda(), opt, torch.nn.MSELoss(),
+                                    tr["horizon"], "euler", 0.02)
+        assert abs(got - want) <= 1e-5 * abs(want) + 1e-9
+    for k, v in m.state_dict().items():
+        assert _rel(v, tr["state_dict_after"][k]) <= 1e-4, k
