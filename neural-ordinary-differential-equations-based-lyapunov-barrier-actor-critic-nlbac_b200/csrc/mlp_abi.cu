@@ -102,9 +102,9 @@ int nlbac_mlp_workspace_bytes(const nlbac_mlp_desc* desc, int64_t B, size_t* act
 int nlbac_mlp_fwd(const nlbac_mlp_desc* desc, const float* const* params, const float* x, int64_t B, float* out,
                   float* act, void* stream) {
   if (int rc = check_mlp(desc)) return rc;
-  NLBAC_REQUIRE(params && x && out, "null pointer");
   NLBAC_REQUIRE(B >= 0, "negative batch");
   if (B == 0) return 0;
+  NLBAC_REQUIRE(params && x && out, "null pointer");
   MlpArgs a;
   a.W1 = params[0]; a.b1 = params[1]; a.W2 = params[2]; a.b2 = params[3]; a.W3 = params[4]; a.b3 = params[5];
   a.x = x; a.out = out; a.act = act; a.B = B; a.n_in = desc->n_in; a.H = desc->hidden; a.n_out = desc->n_out;
@@ -119,8 +119,8 @@ int nlbac_mlp_fwd(const nlbac_mlp_desc* desc, const float* const* params, const 
 int nlbac_mlp_bwd(const nlbac_mlp_desc* desc, const float* const* params, const float* x, int64_t B, const float* act,
                   const float* grad_out, float* grad_x, float* const* grad_params, void* ws, void* stream) {
   if (int rc = check_mlp(desc)) return rc;
-  NLBAC_REQUIRE(params && x && act && grad_out && ws, "null pointer");
   NLBAC_REQUIRE(B >= 0, "negative batch");
+  NLBAC_REQUIRE(B == 0 || (params && x && act && grad_out && ws), "null pointer");
   cudaStream_t st = (cudaStream_t)stream;
   const int H = desc->hidden, NI = desc->n_in, NO = desc->n_out;
   if (B == 0) {

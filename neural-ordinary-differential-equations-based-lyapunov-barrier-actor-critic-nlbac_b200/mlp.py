@@ -44,7 +44,7 @@ class _MLP3(torch.autograd.Function):
         xc = x.detach().contiguous().float()
         B = xc.shape[0]
         desc = _lib.MlpDesc(W1.shape[1], W1.shape[0], W3.shape[0])
-        need = torch.is_grad_enabled() and any(t.requires_grad for t in (x, W1, b1, W2, b2, W3, b3))
+        need = any(ctx.needs_input_grad)
         out = torch.empty((B, desc.n_out), dtype=torch.float32, device=x.device)
         act = torch.empty((2, B, desc.hidden), dtype=torch.float32, device=x.device) if need else None
         _lib.check(L.nlbac_mlp_fwd(ctypes.byref(desc), _ptrs(params), xc.data_ptr(), B, out.data_ptr(),

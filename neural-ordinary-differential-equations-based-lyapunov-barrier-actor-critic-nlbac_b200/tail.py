@@ -231,6 +231,7 @@ class FusedAdam(torch.optim.Optimizer):
                 _lib.check(L.nlbac_adam_step(p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(),
                                              st["exp_avg_sq"].data_ptr(), p.numel(), st["step"], group["lr"], b1, b2,
                                              group["eps"], _stream()), "adam_step")
+                torch.autograd.graph.increment_version(p)   # written through a raw pointer: invalidate caches
 
 
 @torch.no_grad()
@@ -239,6 +240,7 @@ def soft_update(target, source, tau):
     L = _lib.lib()
     for tp, sp in zip(target.parameters(), source.parameters()):
         _lib.check(L.nlbac_soft_update(tp.data_ptr(), sp.data_ptr(), tp.numel(), float(tau), _stream()), "soft_update")
+        torch.autograd.graph.increment_version(tp)
 
 
 @torch.no_grad()
