@@ -51,7 +51,9 @@ extern "C" {
 
 /* arithmetic of the hidden-layer contractions */
 #define NLBAC_PREC_FP32 0  /* FP32 FMA pipe; parity bar rel 1e-5 */
-#define NLBAC_PREC_BF16 1  /* bf16 tcgen05 tensor cores, fp32 accumulate; parity bar rel 1e-2 */
+#define NLBAC_PREC_BF16 1  /* reserved: bf16 operands measured at 2.7e-2 on d-theta -> not built */
+#define NLBAC_PREC_TF32 2  /* tcgen05 kind::tf32 hidden layers, fp32 accumulate (forward); parity bar rel 1e-2 */
+#define NLBAC_PREC_3XTF32 3 /* 3xTF32 split (hi*hi + lo*hi + hi*lo) on tcgen05 (forward); fp32-class, bar rel 1e-5 */
 
 typedef struct nlbac_node_desc {
   int kind;        /* NLBAC_KIND_* */
@@ -79,6 +81,12 @@ int64_t nlbac_node_packed_floats(const nlbac_node_desc* desc);
  * [out,in] like nn.Linear.weight) into the padded/transposed image the kernels stream through
  * shared memory.  `params` is a HOST array of DEVICE pointers. */
 int nlbac_node_pack(const nlbac_node_desc* desc, const float* const* params, float* packed, void* stream);
+
+/* Packed image for the tensor-core tiers (NLBAC_PREC_TF32 / NLBAC_PREC_3XTF32): thin layers + one UMMA K-major
+ * core-matrix image (hi and lo halves) per hidden matrix.  Pass THIS image as `packed` to nlbac_node_solve_fwd
+ * when precision is a tensor-core tier; the backward always takes the FP32 image of nlbac_node_pack. */
+int64_t nlbac_node_tc_packed_floats(const nlbac_node_desc* desc);
+int nlbac_node_tc_pack(const nlbac_node_desc* desc, const float* const* params, float* packed, void* stream);
 
 /* Workspace sizes in bytes for a solve over `n_grid` integration grid points (n_grid-1 steps). */
 int nlbac_node_workspace_bytes(const nlbac_node_desc* desc, int64_t B, int n_grid, int n_t, int method,
@@ -201,6 +209,11 @@ int nlbac_get_obs_bwd(int env, const float* state, int64_t B, const float* grad_
 int nlbac_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, int step, float lr,
                     float beta1, float beta2, float eps, void* stream);
 int nlbac_soft_update(float* target, const float* source, int64_t n, float tau, void* stream);
+
+/* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 TF32 tile.
+ * mode 0: D[t][j] = sum_k X[t][k] Y[j][k];  mode 1: D[t][k] = sum_j X[t][j] Y[j][k];  mode 2: D[j][k] = sum_t X[t][j] Y[t][k].
+ * X [128,104]; Y [104,104] (modes 0,1) or [128,104] (mode 2); D [128,112] (columns/rows >= 104 are padding). */
+int nlbac_umma_selftest(int mode, const float* X, const float* Y, float* D, void* stream);
 
 /* Measured-peak helper for the roofline: register-resident FP32 FMA loop.  Returns the number of
  * FLOPs one launch executes in *flops; the caller times it with CUDA events. */

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libnlbac_b200.so")
-SOURCES = ["node_abi.cu", "mlp_abi.cu", "tail_abi.cu"]
+SOURCES = ["node_abi.cu", "mlp_abi.cu", "tail_abi.cu", "tc_abi.cu"]
 NVCC_FLAGS = ["-std=c++20", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC"]
 
@@ -83,6 +83,9 @@ def _declare(lib):
     lib.nlbac_node_packed_floats.argtypes = [dp]
     lib.nlbac_node_packed_floats.restype = c.c_int64
     lib.nlbac_node_pack.argtypes = [dp, c.POINTER(vp), vp, vp]
+    lib.nlbac_node_tc_packed_floats.argtypes = [dp]
+    lib.nlbac_node_tc_packed_floats.restype = c.c_int64
+    lib.nlbac_node_tc_pack.argtypes = [dp, c.POINTER(vp), vp, vp]
     lib.nlbac_node_workspace_bytes.argtypes = [dp, c.c_int64, c.c_int, c.c_int, c.c_int,
                                                c.POINTER(c.c_size_t), c.POINTER(c.c_size_t), c.POINTER(c.c_size_t)]
     lib.nlbac_node_solve_fwd.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, fp, c.c_int, c.c_int, c.c_int,
@@ -110,6 +113,7 @@ def _declare(lib):
     lib.nlbac_get_obs_bwd.argtypes = [c.c_int, vp, i64, vp, vp, vp]
     lib.nlbac_adam_step.argtypes = [vp, vp, vp, vp, i64, c.c_int, c.c_float, c.c_float, c.c_float, c.c_float, vp]
     lib.nlbac_soft_update.argtypes = [vp, vp, i64, c.c_float, vp]
+    lib.nlbac_umma_selftest.argtypes = [c.c_int, vp, vp, vp, vp]
     lib.nlbac_fp32_peak_probe.argtypes = [c.c_int, vp, c.POINTER(c.c_double), vp]
     lib.nlbac_fma_shape_probe.argtypes = [c.c_int, c.c_int, vp, c.POINTER(c.c_double), vp]
     return lib

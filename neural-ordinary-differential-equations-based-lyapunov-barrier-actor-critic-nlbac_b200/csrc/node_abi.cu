@@ -5,6 +5,7 @@
 
 #include "../../include/nlbac.h"
 #include "node_dopri5.cuh"
+#include "node_tc.cuh"
 #include <cmath>
 #include "node_pack.cuh"
 
@@ -107,6 +108,44 @@ static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
   const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());
   node_fwd_kernel<C, T><<<grid, G::NT, G::SMEM_BYTES, st>>>(a);
   NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <class C, bool SPLIT>
+static int launch_tc_fwd(const FwdArgs& a, cudaStream_t st) {
+  using G = TcFwdGeom<C, SPLIT>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    NLBAC_CUDA(cudaFuncSetAttribute(node_tc_fwd_kernel<C, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    (int)G::SMEM_BYTES));
+    attr_done = true;
+  }
+  const long long n_tiles = (a.B + 127) / 128;
+  const long long n_pairs = (n_tiles + G::G - 1) / G::G;
+  const int grid = (int)(n_pairs < sm_count() ? n_pairs : sm_count());
+  node_tc_fwd_kernel<C, SPLIT><<<grid, G::NT, G::SMEM_BYTES, st>>>(a);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+template <class C>
+static int launch_pack_tc(const float* const* params, float* packed, cudaStream_t st) {
+  using T = TcCfg<C>;
+  // thin layers: the RES_FWD segments of the FP32 image
+  PackTable full = build_pack_table<C>(params), t;
+  t.n = 0;
+  for (int i = 0; i < full.n; ++i)
+    if (full.seg[i].dst_off + full.seg[i].rows * full.seg[i].cols <= C::RES_FWD) t.seg[t.n++] = full.seg[i];
+  pack_params_kernel<<<dim3(8, t.n), 256, 0, st>>>(t, packed);
+  NLBAC_CUDA(cudaGetLastError());
+  int pi = 0;
+  for (int c = 0; c < C::NCH; ++c)
+    for (int l = 0; l < C::nl(c); ++l, pi += 2)
+      if (l >= 1 && l <= C::nhc(c)) {
+        const int h = C::hid_base(c) + (l - 1);
+        pack_tc_kernel<C><<<16, 256, 0, st>>>(params[pi], packed + T::off_hi(h), packed + T::off_lo(h));
+        NLBAC_CUDA(cudaGetLastError());
+      }
   return 0;
 }
 
@@ -239,7 +278,10 @@ const char* nlbac_last_error(void) { return g_err; }
 int nlbac_abi_version(void) { return NLBAC_ABI_VERSION; }
 
 int nlbac_node_supported(const nlbac_node_desc* desc, int precision) {
-  if (precision != NLBAC_PREC_FP32) { set_error("precision %d not compiled", precision); return -3; }
+  if (precision != NLBAC_PREC_FP32 && precision != NLBAC_PREC_TF32 && precision != NLBAC_PREC_3XTF32) {
+    set_error("precision %d not compiled", precision);
+    return -3;
+  }
   return dispatch(desc, [&]<class C>() { return 0; });
 }
 
@@ -253,6 +295,17 @@ int64_t nlbac_node_packed_floats(const nlbac_node_desc* desc) {
   int64_t n = -1;
   dispatch(desc, [&]<class C>() { n = C::PACKED; return 0; });
   return n;
+}
+
+int64_t nlbac_node_tc_packed_floats(const nlbac_node_desc* desc) {
+  int64_t n = -1;
+  dispatch(desc, [&]<class C>() { n = TcCfg<C>::PACKED; return 0; });
+  return n;
+}
+
+int nlbac_node_tc_pack(const nlbac_node_desc* desc, const float* const* params, float* packed, void* stream) {
+  NLBAC_REQUIRE(params && packed, "null pointer");
+  return dispatch(desc, [&]<class C>() { return launch_pack_tc<C>(params, packed, (cudaStream_t)stream); });
 }
 
 int nlbac_node_pack(const nlbac_node_desc* desc, const float* const* params, float* packed, void* stream) {
@@ -278,7 +331,8 @@ int nlbac_node_solve_fwd(const nlbac_node_desc* desc, const float* packed, const
                          const float* t, int n_t, const float* grid, int n_grid, int method, int precision,
                          float* y_out, float* ckpt, void* ws, void* stream) {
   NLBAC_REQUIRE(packed && y0 && t && grid && y_out && ws, "null pointer");
-  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32, "precision %d not compiled", precision);
+  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32 || precision == NLBAC_PREC_TF32 || precision == NLBAC_PREC_3XTF32,
+                "precision %d not compiled", precision);
   NLBAC_REQUIRE(method >= NLBAC_EULER && method <= NLBAC_RK4, "fixed-grid methods only (got %d)", method);
   NLBAC_REQUIRE(B >= 0, "negative batch");
   Schedule s;
@@ -290,6 +344,8 @@ int nlbac_node_solve_fwd(const nlbac_node_desc* desc, const float* packed, const
     a.packed = packed; a.y0 = y0; a.y_out = y_out; a.ckpt = ckpt; a.B = B;
     a.n_steps = n_grid - 1; a.n_t = n_t; a.method = method;
     if (int rc = upload_schedule(s, ws, st, &a.dts, &a.out_step, &a.out_w)) return rc;
+    if (precision == NLBAC_PREC_TF32) return launch_tc_fwd<C, false>(a, st);     // `packed` is the TC image
+    if (precision == NLBAC_PREC_3XTF32) return launch_tc_fwd<C, true>(a, st);
     // largest tile that still gives every SM at least one tile
     const long long sms = sm_count();
     if ((B + 255) / 256 >= sms) return launch_fwd<C, 256>(a, st);

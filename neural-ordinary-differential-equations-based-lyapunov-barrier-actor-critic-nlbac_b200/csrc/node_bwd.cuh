@@ -431,7 +431,7 @@ GradTable build_grad_table() {
     }
   return t;
 }
-__global__ void fold_grad_kernel(GradTable tab, const float* __restrict__ rep, int ngrad, float* __restrict__ flat) {
+static __global__ void fold_grad_kernel(GradTable tab, const float* __restrict__ rep, int ngrad, float* __restrict__ flat) {
   const GradSeg s = tab.seg[blockIdx.y];
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < s.n; i += gridDim.x * blockDim.x) {
     float v = 0.f;

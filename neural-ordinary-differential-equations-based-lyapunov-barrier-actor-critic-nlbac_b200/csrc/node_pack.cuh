@@ -18,7 +18,7 @@ struct PackTable {
   int n;
 };
 
-__global__ void pack_params_kernel(PackTable tab, float* __restrict__ packed) {
+static __global__ void pack_params_kernel(PackTable tab, float* __restrict__ packed) {
   const PackSeg s = tab.seg[blockIdx.y];
   const int total = s.rows * s.cols;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {

@@ -1,0 +1,394 @@
+// K1-TC — fused fixed-grid NODE solve, forward, hidden layers on the 5th-generation tensor cores
+// (tcgen05.mma kind::tf32, accumulators in TMEM).  Same call sites as node_fwd.cuh (U model.py:252,
+// U sac_cbf_clf.py:453, ...); precision tiers:
+//   SPLIT = false  one TF32 pass per hidden layer            -> declared 1e-2 tier (measured ~3e-3 on d-theta)
+//   SPLIT = true   3xTF32 (hi*hi + lo*hi + hi*lo)            -> fp32-class
+//
+// One persistent CTA runs G independent "groups" of 128 threads; a group owns a tile of 128 trajectories:
+// thread = trajectory = TMEM lane.  Per right-hand-side evaluation the owner thread computes the thin first
+// layer on the FP32 pipe and writes its activation row straight into the K-major core-matrix image
+// (umma.cuh); ONE thread issues the 13 (39) MMAs of a hidden layer [128 x 112 x 104]; the owner reads its
+// accumulator row back with tcgen05.ld, applies bias + ReLU and either rewrites the activation image in
+// place or folds the thin last layer in registers.  The G groups share one TMA weight ring (one packet =
+// one hidden matrix image, 46.6 KB), so while one group is in its epilogue the other group's MMAs run.
+#pragma once
+#include "node_fwd.cuh"
+#include "umma.cuh"
+
+namespace nlbac {
+
+template <class C>
+struct TcCfg {
+  static constexpr int ROWS = 128;                 // trajectories per tile = MMA M
+  static constexpr int NP = round_up(C::H, 16);    // MMA N (100 -> 112, 64 -> 64)
+  static constexpr int KP = round_up(C::H, 8);     // MMA K extent (100 -> 104, 64 -> 64)
+  static constexpr int KSTEPS = KP / 8;
+  static constexpr int NCHUNK = KP / 4;            // 16-byte chunks along K
+  static constexpr int ACH = ROWS * 16;            // activation image: bytes per chunk
+  static constexpr int WCH = NP * 16;              // weight image: bytes per chunk
+  static constexpr int A_BYTES = NCHUNK * ACH;
+  static constexpr int W_FLOATS = NCHUNK * NP * 4;
+  static constexpr int W_BYTES = W_FLOATS * 4;
+  static constexpr int TCOLS = 128;                // TMEM columns reserved per group
+  static_assert(NP <= TCOLS && KP == C::HP, "tile shape");
+  // packed image: [RES_FWD (thin layers, node_cfg.cuh) | U_hi[NHID] | U_lo[NHID]]
+  static constexpr int off_hi(int h) { return C::RES_FWD + h * W_FLOATS; }
+  static constexpr int off_lo(int h) { return C::RES_FWD + (C::NHID + h) * W_FLOATS; }
+  static constexpr int PACKED = C::RES_FWD + 2 * C::NHID * W_FLOATS;
+};
+
+// weight image of one hidden matrix: W[j][k] (nn.Linear [out][in]) -> float index (k/4)*NP*4 + j*4 + k%4
+template <class C>
+__global__ void pack_tc_kernel(const float* __restrict__ W, float* __restrict__ hi, float* __restrict__ lo) {
+  using T = TcCfg<C>;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < T::W_FLOATS; i += gridDim.x * blockDim.x) {
+    const int c = i / (T::NP * 4), j = (i / 4) % T::NP, k = 4 * c + (i & 3);
+    const float w = (j < C::H && k < C::H) ? W[j * C::H + k] : 0.f;
+    const float h = __uint_as_float(__float_as_uint(w) & 0xFFFFE000u);   // exactly representable in TF32
+    hi[i] = h;
+    lo[i] = w - h;
+  }
+}
+
+template <class C, bool SPLIT>
+struct TcFwdGeom {
+  using T = TcCfg<C>;
+  static constexpr int G = SPLIT ? 1 : 2;          // groups (tiles in flight) per CTA
+  static constexpr int NT = G * 128 + 32;          // + one producer warp
+  static constexpr int NSLOT = 2;
+  static constexpr int NIMG = SPLIT ? 2 : 1;       // activation images per group (hi, lo)
+  static constexpr int OFF_A = 0;                                   // bytes
+  static constexpr int OFF_W = OFF_A + G * NIMG * T::A_BYTES;
+  static constexpr int OFF_RES = OFF_W + NSLOT * T::W_BYTES;
+  static constexpr int OFF_BAR = OFF_RES + C::RES_FWD * 4;
+  static constexpr int NBAR = 2 * NSLOT + G + 1;   // full[NSLOT], empty[NSLOT], done[G], res
+  static constexpr size_t SMEM_BYTES = OFF_BAR + NBAR * 8 + 16;
+  static constexpr int PKT_PER_EVAL = C::NHID * (SPLIT ? 2 : 1);
+  static_assert(OFF_W % 128 == 0 && OFF_RES % 16 == 0 && OFF_BAR % 8 == 0, "alignment");
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+  // global offset (floats) of ring packet p
+  __device__ static int pkt_off(uint32_t p) {
+    const int q = p % PKT_PER_EVAL;
+    if (SPLIT) return (q & 1) ? T::off_lo(q >> 1) : T::off_hi(q >> 1);
+    return T::off_hi(q);
+  }
+};
+
+__device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory"); }
+
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
+
+// store 4 consecutive features [c, c+4) of activation row r into the image(s)
+template <bool SPLIT, int ACH, int A_BYTES>
+__device__ __forceinline__ void store_act4(unsigned char* img, int r, int c, float v0, float v1, float v2, float v3) {
+  unsigned char* p = img + (c >> 2) * ACH + (r >> 3) * 128 + (r & 7) * 16;
+  if (SPLIT) {
+    const float h0 = tf32_hi(v0), h1 = tf32_hi(v1), h2 = tf32_hi(v2), h3 = tf32_hi(v3);
+    *reinterpret_cast<float4*>(p) = make_float4(h0, h1, h2, h3);
+    *reinterpret_cast<float4*>(p + A_BYTES) = make_float4(v0 - h0, v1 - h1, v2 - h2, v3 - h3);
+  } else {
+    *reinterpret_cast<float4*>(p) = make_float4(v0, v1, v2, v3);
+  }
+}
+
+// Shared-memory / barrier handles of one group
+struct TcGroupCtx {
+  unsigned char* sA;       // activation image(s) of this group
+  unsigned char* sW;       // weight ring base
+  const float* sRes;       // thin layers (RES_FWD layout)
+  uint64_t *full, *empty, *done;
+  uint32_t tacc;           // TMEM address of this thread's accumulator row (lane quadrant + group column base)
+  uint32_t tmma;           // TMEM address of the group's accumulator tile (lane 0)
+  uint32_t seq;            // ring packets consumed so far (uniform over the CTA's groups)
+  uint32_t nd;             // completed hidden layers of this group (phase of `done`)
+  int lt, g;
+};
+
+// Right-hand side for the group's tile: owner thread passes x / constants, receives k = dx/dt.
+template <class C, bool SPLIT>
+__device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::NS], const float (&cst)[C::NCONST],
+                                            float (&k)[C::NS]) {
+  using T = TcCfg<C>;
+  using G = TcFwdGeom<C, SPLIT>;
+  const int lt = cx.lt;
+  const uint32_t idesc = umma::make_idesc_tf32(128, T::NP, false, false);
+  float fo[C::outp(0)];
+#pragma unroll
+  for (int c = 0; c < C::NCH; ++c) {
+    // ---- thin first layer on the FP32 pipe -> activation image ----
+    {
+      const float* Wt0 = cx.sRes + C::off_wt0(c);
+      const float* b0 = cx.sRes + C::off_b0(c);
+#pragma unroll 2
+      for (int j4 = 0; j4 < T::NCHUNK; ++j4) {
+        float4 acc = *reinterpret_cast<const float4*>(b0 + 4 * j4);
+#pragma unroll
+        for (int d = 0; d < C::IN0; ++d) {
+          const float xv = d < C::NS ? x[d < C::NS ? d : 0] : cst[d >= C::NS ? d - C::NS : 0];
+          const float4 w = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 4 * j4);
+          acc.x = fmaf(xv, w.x, acc.x); acc.y = fmaf(xv, w.y, acc.y);
+          acc.z = fmaf(xv, w.z, acc.z); acc.w = fmaf(xv, w.w, acc.w);
+        }
+        store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, 4 * j4, fmaxf(acc.x, 0.f), fmaxf(acc.y, 0.f),
+                                              fmaxf(acc.z, 0.f), fmaxf(acc.w, 0.f));
+      }
+    }
+    fence_proxy_async();
+    umma::fence_before_sync();
+    group_sync(cx.g);
+    const int n = C::nhc(c);
+    float o[C::OUTP_MAX];
+#pragma unroll 1
+    for (int l = 1; l <= n; ++l) {
+      if (lt == 0) {  // ---- MMA issue: one thread per group ----
+        umma::fence_after_sync();
+        const uint32_t a0 = smem_u32(cx.sA);
+        {
+          const uint32_t slot = cx.seq % G::NSLOT;
+          mbar_wait(&cx.full[slot], (cx.seq / G::NSLOT) & 1);
+          umma::fence_after_sync();
+          const uint32_t b0 = smem_u32(cx.sW + slot * T::W_BYTES);
+#pragma unroll 1
+          for (int ks = 0; ks < T::KSTEPS; ++ks)
+            umma::mma_tf32(cx.tmma, umma::make_desc(a0 + ks * 2 * T::ACH, T::ACH, 128),
+                           umma::make_desc(b0 + ks * 2 * T::WCH, T::WCH, 128), idesc, ks > 0);
+          if (SPLIT) {
+#pragma unroll 1
+            for (int ks = 0; ks < T::KSTEPS; ++ks)
+              umma::mma_tf32(cx.tmma, umma::make_desc(a0 + T::A_BYTES + ks * 2 * T::ACH, T::ACH, 128),
+                             umma::make_desc(b0 + ks * 2 * T::WCH, T::WCH, 128), idesc, 1);
+          }
+          umma::commit(&cx.empty[slot]);
+        }
+        if (SPLIT) {
+          const uint32_t s2 = cx.seq + 1;
+          const uint32_t slot = s2 % G::NSLOT;
+          mbar_wait(&cx.full[slot], (s2 / G::NSLOT) & 1);
+          umma::fence_after_sync();
+          const uint32_t b0 = smem_u32(cx.sW + slot * T::W_BYTES);
+#pragma unroll 1
+          for (int ks = 0; ks < T::KSTEPS; ++ks)
+            umma::mma_tf32(cx.tmma, umma::make_desc(a0 + ks * 2 * T::ACH, T::ACH, 128),
+                           umma::make_desc(b0 + ks * 2 * T::WCH, T::WCH, 128), idesc, 1);
+          umma::commit(&cx.empty[slot]);
+        }
+        umma::commit(cx.done);
+      }
+      cx.seq += SPLIT ? 2 : 1;
+      mbar_wait(cx.done, cx.nd & 1);
+      ++cx.nd;
+      umma::fence_after_sync();
+      const float* bias = cx.sRes + C::off_bh(c, l);
+      if (l < n) {  // ---- epilogue: bias + ReLU -> activation image (in place) ----
+#pragma unroll 1
+        for (int c0 = 0; c0 < T::KP; c0 += 8) {
+          float v[8];
+          umma::ld8(cx.tacc + c0, v);
+          umma::wait_ld();
+          const float4 b0 = *reinterpret_cast<const float4*>(bias + c0);
+          const float4 b1 = *reinterpret_cast<const float4*>(bias + c0 + 4);
+          store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, c0, fmaxf(v[0] + b0.x, 0.f), fmaxf(v[1] + b0.y, 0.f),
+                                                fmaxf(v[2] + b0.z, 0.f), fmaxf(v[3] + b0.w, 0.f));
+          store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, c0 + 4, fmaxf(v[4] + b1.x, 0.f), fmaxf(v[5] + b1.y, 0.f),
+                                                fmaxf(v[6] + b1.z, 0.f), fmaxf(v[7] + b1.w, 0.f));
+        }
+        fence_proxy_async();
+        umma::fence_before_sync();
+        group_sync(cx.g);
+      } else {  // ---- last hidden layer: bias + ReLU, thin output layer folded in registers ----
+        const int OUTP = C::outp(c);
+        const float* WtL = cx.sRes + C::off_wtl(c);
+        const float* bL = cx.sRes + C::off_bl(c);
+#pragma unroll
+        for (int j = 0; j < C::OUTP_MAX; ++j) o[j] = j < OUTP ? bL[j] : 0.f;
+#pragma unroll 1
+        for (int c0 = 0; c0 < T::KP; c0 += 8) {
+          float v[8];
+          umma::ld8(cx.tacc + c0, v);
+          umma::wait_ld();
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int kk = c0 + i;
+            if (kk < C::H) {
+              const float h = fmaxf(v[i] + bias[kk], 0.f);
+#pragma unroll
+              for (int j = 0; j < C::OUTP_MAX; j += 4)
+                if (j < OUTP) {
+                  const float4 w = *reinterpret_cast<const float4*>(WtL + kk * OUTP + j);
+                  o[j] = fmaf(h, w.x, o[j]); o[j + 1] = fmaf(h, w.y, o[j + 1]);
+                  o[j + 2] = fmaf(h, w.z, o[j + 2]); o[j + 3] = fmaf(h, w.w, o[j + 3]);
+                }
+            }
+          }
+        }
+      }
+    }
+    if (c == 0) {
+#pragma unroll
+      for (int j = 0; j < C::outp(0); ++j) fo[j] = o[j];
+    } else {
+#pragma unroll
+      for (int i = 0; i < C::NS; ++i) {
+        float v = fo[i];
+#pragma unroll
+        for (int j = 0; j < C::NU; ++j) v = fmaf(o[i * C::NU + j], cst[j], v);
+        k[i] = v;
+      }
+    }
+  }
+  if (C::NCH == 1) {
+#pragma unroll
+    for (int i = 0; i < C::NS; ++i) k[i] = fo[i];
+  }
+}
+
+template <class C, bool SPLIT>
+__global__ void __launch_bounds__(TcFwdGeom<C, SPLIT>::NT, 1) node_tc_fwd_kernel(FwdArgs a) {
+  using T = TcCfg<C>;
+  using G = TcFwdGeom<C, SPLIT>;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  float* sRes = reinterpret_cast<float*>(smem_raw + G::OFF_RES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + G::OFF_BAR);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + G::NSLOT;
+  uint64_t* done = bars + 2 * G::NSLOT;
+  uint64_t* resbar = bars + 2 * G::NSLOT + G::G;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + G::NBAR);
+  const int tid = threadIdx.x, warp = tid / 32;
+  const bool is_prod = warp == G::G * 4;
+
+  const int S = method_stages(a.method);
+  const long long n_tiles = (a.B + T::ROWS - 1) / T::ROWS;
+  const long long n_pairs = (n_tiles + G::G - 1) / G::G;           // CTA-level work items (G tiles each)
+  long long my_iters = 0;
+  if ((long long)blockIdx.x < n_pairs) my_iters = (n_pairs - blockIdx.x + gridDim.x - 1) / gridDim.x;
+  const uint32_t total = (uint32_t)(my_iters * a.n_steps * S * G::PKT_PER_EVAL);
+
+  if (tid == 0) {
+    for (int i = 0; i < G::NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], G::G); }
+    for (int i = 0; i < G::G; ++i) mbar_init(&done[i], 1);
+    mbar_init(resbar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) umma::tmem_alloc(tslot, G::G * T::TCOLS);
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tbase = *tslot;
+
+  if (is_prod) {
+    // ---------------- TMA producer: thin layers once, then the weight ring ----------------
+    if (tid % 32 == 0 && my_iters > 0) {
+      mbar_expect_tx(resbar, C::RES_FWD * 4);
+      tma_load_1d(sRes, a.packed, C::RES_FWD * 4, resbar);
+      for (uint32_t p = 0; p < total; ++p) {
+        const uint32_t slot = p % G::NSLOT;
+        if (p >= (uint32_t)G::NSLOT) mbar_wait(&empty[slot], ((p / G::NSLOT) - 1) & 1);
+        mbar_expect_tx(&full[slot], T::W_BYTES);
+        tma_load_1d(smem_raw + G::OFF_W + slot * T::W_BYTES, a.packed + G::pkt_off(p), T::W_BYTES, &full[slot]);
+      }
+    }
+    __syncwarp();
+  } else if (my_iters > 0) {
+    TcGroupCtx cx;
+    cx.g = tid / 128;
+    cx.lt = tid % 128;
+    cx.sA = smem_raw + G::OFF_A + cx.g * G::NIMG * T::A_BYTES;
+    cx.sW = smem_raw + G::OFF_W;
+    cx.sRes = sRes;
+    cx.full = full; cx.empty = empty; cx.done = &done[cx.g];
+    cx.tmma = tbase + cx.g * T::TCOLS;
+    cx.tacc = cx.tmma + ((uint32_t)((warp % 4) * 32) << 16);
+    cx.seq = 0; cx.nd = 0;
+    mbar_wait(resbar, 0);
+
+    for (long long it = 0; it < my_iters; ++it) {
+      const long long tile = (it * gridDim.x + blockIdx.x) * G::G + cx.g;
+      const long long b = tile * T::ROWS + cx.lt;
+      const bool live = b < a.B;     // dead rows / dead tiles still run (the ring is shared by the groups)
+      float y[C::NS], cst[C::NCONST], k1[C::NS], k2[C::NS], k3[C::NS], k4[C::NS], x[C::NS];
+#pragma unroll
+      for (int d = 0; d < C::NS; ++d) k1[d] = k2[d] = k3[d] = k4[d] = y[d] = 0.f;
+#pragma unroll
+      for (int d = 0; d < C::NCONST; ++d) cst[d] = 0.f;
+      if (live) {
+        const float* yr = a.y0 + b * C::D;
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) y[d] = yr[d];
+#pragma unroll
+        for (int d = 0; d < C::NCONST; ++d) cst[d] = yr[C::NS + d];
+        float* o = a.y_out + b * C::D;
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) o[d] = y[d];
+#pragma unroll
+        for (int d = 0; d < C::NCONST; ++d) o[C::NS + d] = cst[d];
+      }
+      int jout = 1;
+      for (int step = 0; step < a.n_steps; ++step) {
+        const float dt = a.dts[step];
+        float y1[C::NS];
+#pragma unroll 1
+        for (int stage = 0; stage < S; ++stage) {
+          if (stage == 0) {
+#pragma unroll
+            for (int d = 0; d < C::NS; ++d) x[d] = y[d];
+          } else if (a.method == METHOD_MIDPOINT) {
+            const float half = 0.5f * dt;
+#pragma unroll
+            for (int d = 0; d < C::NS; ++d) x[d] = y[d] + k1[d] * half;
+          } else {
+            const float third = 1.0f / 3.0f;
+#pragma unroll
+            for (int d = 0; d < C::NS; ++d) {
+              if (stage == 1) x[d] = y[d] + dt * k1[d] * third;
+              else if (stage == 2) x[d] = y[d] + dt * (k2[d] - k1[d] * third);
+              else x[d] = y[d] + dt * (k1[d] - k2[d] + k3[d]);
+            }
+          }
+          if (a.ckpt != nullptr && live) {
+            float* p = a.ckpt + (((long long)step * S + stage) * a.B + b) * C::NS;
+#pragma unroll
+            for (int d = 0; d < C::NS; ++d) p[d] = x[d];
+          }
+          float kn[C::NS];
+          eval_rhs_tc<C, SPLIT>(cx, x, cst, kn);
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) {
+            if (stage == 0) k1[d] = kn[d];
+            else if (stage == 1) k2[d] = kn[d];
+            else if (stage == 2) k3[d] = kn[d];
+            else k4[d] = kn[d];
+          }
+        }
+        if (a.method == METHOD_EULER) {
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) y1[d] = y[d] + dt * k1[d];
+        } else if (a.method == METHOD_MIDPOINT) {
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) y1[d] = y[d] + dt * k2[d];
+        } else {
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) y1[d] = y[d] + (k1[d] + 3.f * (k2[d] + k3[d]) + k4[d]) * dt * 0.125f;
+        }
+        while (jout < a.n_t && a.out_step[jout] == step) {
+          if (live) {
+            const float w = a.out_w[jout];
+            float* o = a.y_out + ((long long)jout * a.B + b) * C::D;
+#pragma unroll
+            for (int d = 0; d < C::NS; ++d) o[d] = (w == 1.f) ? y1[d] : ((w == 0.f) ? y[d] : y[d] + w * (y1[d] - y[d]));
+#pragma unroll
+            for (int d = 0; d < C::NCONST; ++d) o[C::NS + d] = cst[d];
+          }
+          ++jout;
+        }
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) y[d] = y1[d];
+      }
+    }
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tbase, G::G * T::TCOLS);
+}
+
+}  // namespace nlbac

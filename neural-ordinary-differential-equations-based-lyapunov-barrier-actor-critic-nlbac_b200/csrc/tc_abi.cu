@@ -1,0 +1,149 @@
+// Tensor-core (tcgen05, kind::tf32) tier of the NODE solve: C ABI entry points + a UMMA layout self-test.
+#include "../../include/nlbac.h"
+#include "umma.cuh"
+#include <cstring>
+
+namespace nlbac {
+
+// ------------------------------------------------------------------------------------------------
+// Self-test of the three operand interpretations the NODE kernels rely on (umma.cuh):
+//   mode 0  D[t][j] = sum_k X[t][k] W[j][k]   A K-major,  B K-major   (forward hidden layer)
+//   mode 1  D[t][k] = sum_j X[t][j] W[j][k]   A K-major,  B MN-major  (dX: same weight image)
+//   mode 2  D[j][k] = sum_t X[t][j] Y[t][k]   A MN-major, B MN-major  (dW: same activation images)
+// X, Y: [128][104] row-major; W: [104][104] row-major; D: [128][112] row-major.
+// ------------------------------------------------------------------------------------------------
+constexpr int ST_ROWS = 128, ST_K = 104, ST_N = 112;
+constexpr int ST_XCH = ST_ROWS * 16, ST_WCH = ST_N * 16;
+constexpr int ST_SMEM = 32 * ST_XCH * 2 + 64;
+
+__global__ void __launch_bounds__(128, 1) umma_selftest_kernel(int mode, const float* __restrict__ X,
+                                                              const float* __restrict__ Y, float* __restrict__ D) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  unsigned char* bufA = sm;                    // 32 chunks x 2048 B
+  unsigned char* bufB = sm + 32 * ST_XCH;      // up to 32 chunks x 2048 B
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sm + 64 * ST_XCH);
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(sm + 64 * ST_XCH + 16);
+  const int tid = threadIdx.x, warp = tid / 32;
+  for (int i = tid; i < 64 * ST_XCH / 4; i += 128) reinterpret_cast<float*>(sm)[i] = 0.f;
+  __syncthreads();
+  // A: row-owner image of X (chunk stride 2048)
+  for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufA + umma::tile_off(tid, c, ST_XCH)) = X[tid * ST_K + c];
+  if (mode == 2) {
+    for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_XCH)) = Y[tid * ST_K + c];
+  } else if (tid < ST_K) {  // weight image: rows j (112 per chunk), columns k
+    for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_WCH)) = Y[tid * ST_K + c];
+  }
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) umma::tmem_alloc(tslot, 128);
+  fence_proxy_async();
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tbase = *tslot;
+  if (tid == 0) {
+    const uint32_t a0 = smem_u32(bufA), b0 = smem_u32(bufB);
+    if (mode == 0) {
+      const uint32_t idesc = umma::make_idesc_tf32(128, ST_N, false, false);
+      for (int ks = 0; ks < ST_K / 8; ++ks)
+        umma::mma_tf32(tbase, umma::make_desc(a0 + ks * 2 * ST_XCH, ST_XCH, 128),
+                       umma::make_desc(b0 + ks * 2 * ST_WCH, ST_WCH, 128), idesc, ks > 0);
+    } else if (mode == 1) {
+      const uint32_t idesc = umma::make_idesc_tf32(128, ST_N, false, true);
+      for (int ks = 0; ks < ST_K / 8; ++ks)
+        umma::mma_tf32(tbase, umma::make_desc(a0 + ks * 2 * ST_XCH, ST_XCH, 128),
+                       umma::make_desc(b0 + ks * 128, 128, ST_WCH), idesc, ks > 0);
+    } else {
+      const uint32_t idesc = umma::make_idesc_tf32(128, ST_N, true, true);
+      for (int ks = 0; ks < ST_ROWS / 8; ++ks)
+        umma::mma_tf32(tbase, umma::make_desc(a0 + ks * 128, 128, ST_XCH), umma::make_desc(b0 + ks * 128, 128, ST_XCH),
+                       idesc, ks > 0);
+    }
+    umma::commit(bar);
+  }
+  mbar_wait(bar, 0);
+  umma::fence_after_sync();
+  for (int c0 = 0; c0 < ST_N; c0 += 8) {
+    float v[8];
+    umma::ld8(umma::tmem_addr(tbase, warp * 32, c0), v);
+    umma::wait_ld();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) D[tid * ST_N + c0 + i] = v[i];
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tbase, 128);
+}
+
+struct ProbeArgs { int a_mn, b_mn, lboA, sboA, stepA, lboB, sboB, stepB, nsteps, b_is_weight; };
+__global__ void __launch_bounds__(128, 1) umma_probe_kernel(ProbeArgs p, const float* __restrict__ X,
+                                                           const float* __restrict__ Y, float* __restrict__ D) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  unsigned char* bufA = sm;
+  unsigned char* bufB = sm + 32 * ST_XCH;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sm + 64 * ST_XCH);
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(sm + 64 * ST_XCH + 16);
+  const int tid = threadIdx.x, warp = tid / 32;
+  for (int i = tid; i < 64 * ST_XCH / 4; i += 128) reinterpret_cast<float*>(sm)[i] = 0.f;
+  __syncthreads();
+  for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufA + umma::tile_off(tid, c, ST_XCH)) = X[tid * ST_K + c];
+  if (!p.b_is_weight) {
+    for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_XCH)) = Y[tid * ST_K + c];
+  } else if (tid < ST_K) {
+    for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_WCH)) = Y[tid * ST_K + c];
+  }
+  if (tid == 0) { mbar_init(bar, 1); fence_barrier_init(); }
+  if (warp == 0) umma::tmem_alloc(tslot, 128);
+  fence_proxy_async();
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tbase = *tslot;
+  if (tid == 0) {
+    const uint32_t a0 = smem_u32(bufA), b0 = smem_u32(bufB);
+    const uint32_t idesc = umma::make_idesc_tf32(128, ST_N, p.a_mn != 0, p.b_mn != 0);
+    for (int ks = 0; ks < p.nsteps; ++ks)
+      umma::mma_tf32(tbase, umma::make_desc(a0 + ks * p.stepA, p.lboA, p.sboA),
+                     umma::make_desc(b0 + ks * p.stepB, p.lboB, p.sboB), idesc, ks > 0);
+    umma::commit(bar);
+  }
+  mbar_wait(bar, 0);
+  umma::fence_after_sync();
+  for (int c0 = 0; c0 < ST_N; c0 += 8) {
+    float v[8];
+    umma::ld8(umma::tmem_addr(tbase, warp * 32, c0), v);
+    umma::wait_ld();
+#pragma unroll
+    for (int i = 0; i < 8; ++i) D[tid * ST_N + c0 + i] = v[i];
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tbase, 128);
+}
+
+}  // namespace nlbac
+
+using namespace nlbac;
+
+extern "C" {
+
+int nlbac_umma_selftest(int mode, const float* X, const float* Y, float* D, void* stream) {
+  NLBAC_REQUIRE(mode >= 0 && mode <= 2 && X && Y && D, "bad arguments");
+  NLBAC_CUDA(cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
+  umma_selftest_kernel<<<1, 128, ST_SMEM, (cudaStream_t)stream>>>(mode, X, Y, D);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_umma_probe(const int* params10, const float* X, const float* Y, float* D, void* stream) {
+  ProbeArgs p;
+  memcpy(&p, params10, sizeof(p));
+  NLBAC_CUDA(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
+  umma_probe_kernel<<<1, 128, ST_SMEM, (cudaStream_t)stream>>>(p, X, Y, D);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

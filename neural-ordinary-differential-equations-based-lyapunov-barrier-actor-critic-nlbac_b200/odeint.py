@@ -19,7 +19,7 @@ import torch.nn as nn
 from . import _lib
 
 METHODS = {"euler": 0, "midpoint": 1, "rk4": 2, "dopri5": 3}
-PRECISIONS = {"fp32": 0, "bf16": 1}
+PRECISIONS = {"fp32": 0, "tf32": 2, "3xtf32": 3}   # tensor-core tiers: forward on tcgen05, backward FP32
 _FIXED = ("euler", "midpoint", "rk4")
 
 
@@ -63,22 +63,24 @@ def describe(func, D):
     return desc, params
 
 
-def _packed(func, desc, params):
-    """Packed kernel image of the parameters, cached on the module until a parameter changes."""
+def _packed(func, desc, params, tc=False):
+    """Packed kernel image of the parameters (FP32 image, or the tensor-core image with ``tc``), cached on the
+    module until a parameter changes."""
     key = tuple((p.data_ptr(), p._version) for p in params)
-    cache = func.__dict__.get("_nlbac_packed")
+    slot = "_nlbac_packed_tc" if tc else "_nlbac_packed"
+    cache = func.__dict__.get(slot)
     if cache is not None and cache[0] == key:
         return cache[1]
     L = _lib.lib()
-    n = L.nlbac_node_packed_floats(ctypes.byref(desc))
+    n = (L.nlbac_node_tc_packed_floats if tc else L.nlbac_node_packed_floats)(ctypes.byref(desc))
     packed = torch.empty(n, dtype=torch.float32, device=params[0].device)
     ptrs = (ctypes.c_void_p * len(params))(*[p.data_ptr() for p in params])
     for p in params:
         if p.dtype != torch.float32 or not p.is_contiguous():
             raise TypeError("nlbac_b200.odeint: parameters must be contiguous float32")
-    _lib.check(L.nlbac_node_pack(ctypes.byref(desc), ptrs, packed.data_ptr(),
-                                 torch.cuda.current_stream().cuda_stream), "node_pack")
-    func.__dict__["_nlbac_packed"] = (key, packed)
+    _lib.check((L.nlbac_node_tc_pack if tc else L.nlbac_node_pack)(
+        ctypes.byref(desc), ptrs, packed.data_ptr(), torch.cuda.current_stream().cuda_stream), "node_pack")
+    func.__dict__[slot] = (key, packed)
     return packed
 
 
@@ -98,7 +100,7 @@ def _grid_from_step_size(t, step_size):
 
 class _FixedSolve(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, y0, desc, packed, t_np, grid_np, method, precision, want_ckpt, *params):
+    def forward(ctx, y0, desc, packed, packed_fwd, t_np, grid_np, method, precision, want_ckpt, *params):
         L = _lib.lib()
         B, D = y0.shape
         n_t, n_grid = len(t_np), len(grid_np)
@@ -113,12 +115,12 @@ class _FixedSolve(torch.autograd.Function):
         _, tp = _farr(t_np)
         _, gp = _farr(grid_np)
         st = torch.cuda.current_stream().cuda_stream
-        _lib.check(L.nlbac_node_solve_fwd(ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, tp, n_t, gp,
+        _lib.check(L.nlbac_node_solve_fwd(ctypes.byref(desc), packed_fwd.data_ptr(), y0c.data_ptr(), B, tp, n_t, gp,
                                           n_grid, method, precision, y_out.data_ptr(),
                                           ckpt.data_ptr() if want_ckpt else None, ws.data_ptr(), st), "node_solve_fwd")
         if want_ckpt:
             ctx.save_for_backward(y0c, packed, ckpt)
-            ctx.meta = (desc, t_np, grid_np, method, precision, bwd.value, [p.shape for p in params])
+            ctx.meta = (desc, t_np, grid_np, method, 0, bwd.value, [p.shape for p in params])   # backward is FP32
         return y_out
 
     @staticmethod
@@ -129,7 +131,7 @@ class _FixedSolve(torch.autograd.Function):
         B, D = y0c.shape
         dev = y0c.device
         need_y0 = ctx.needs_input_grad[0]
-        need_p = any(ctx.needs_input_grad[8:])
+        need_p = any(ctx.needs_input_grad[9:])
         go = grad_out.contiguous()
         ws = torch.empty(max(bwd_bytes, 16), dtype=torch.uint8, device=dev)
         gy0 = torch.empty((B, D), dtype=torch.float32, device=dev) if need_y0 else None
@@ -151,7 +153,7 @@ class _FixedSolve(torch.autograd.Function):
                 off += n
         else:
             grads = [None] * len(shapes)
-        return (gy0, None, None, None, None, None, None, None, *grads)
+        return (gy0, None, None, None, None, None, None, None, None, *grads)
 
 
 def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, event_fn=None, precision="fp32"):
@@ -189,7 +191,6 @@ def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, even
     L = _lib.lib()
     prec = PRECISIONS[precision]
     _lib.check(L.nlbac_node_supported(ctypes.byref(desc), prec), "node_supported")
-    packed = _packed(func, desc, params)
     if len(t_np) == 1:
         return y0.unsqueeze(0).clone()
     if y0.shape[0] == 0:
@@ -198,6 +199,11 @@ def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, even
     if method in _FIXED:
         step_size = options.pop("step_size", None)
         grid_np = t_np if step_size is None else _grid_from_step_size(t_np, float(step_size))
-        return _FixedSolve.apply(y0, desc, packed, t_np, grid_np, METHODS[method], prec, need_grad, *params)
+        packed = _packed(func, desc, params) if (need_grad or prec == 0) else None
+        packed_fwd = _packed(func, desc, params, tc=True) if prec != 0 else packed
+        return _FixedSolve.apply(y0, desc, packed, packed_fwd, t_np, grid_np, METHODS[method], prec, need_grad, *params)
+    if prec != 0:
+        raise NotImplementedError("nlbac_b200.odeint: dopri5 runs in fp32 only")
+    packed = _packed(func, desc, params)
     from .dopri5 import dopri5_solve
     return dopri5_solve(func, y0, desc, packed, params, t_np, float(rtol), float(atol), prec, need_grad, options)

@@ -237,3 +237,43 @@ def test_empty_batch_and_errors():
     odd = nlbac_b200.NeuralODEModel(4, 4, 8).cuda()          # no compiled instance for this shape
     with pytest.raises(RuntimeError):
         nlbac_b200.odeint(odd, torch.randn(4, 6, device="cuda"), torch.tensor([0.0, 0.02]), method="euler")
+
+
+# ------------------------------------------------------------------------------------------------
+# tensor-core tiers (tcgen05 kind::tf32 forward): 3xTF32 is fp32-class (1e-5), plain TF32 is the 1e-2 tier
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("tag,B", [("U", 128), ("U", 300), ("P", 256), ("C", 256), ("Q", 37), ("U", 40000)])
+@pytest.mark.parametrize("precision,tol", [("3xtf32", 1e-5), ("tf32", 1e-2)])
+def test_tensor_core_forward_tiers(tag, B, precision, tol):
+    import nlbac_b200
+    ref, ours = _models(tag)
+    y0 = _y0(tag, B)
+    t = 0.02 * torch.arange(6, dtype=torch.float32)
+    with torch.no_grad():
+        want = oracle_odeint(ref, y0, t, method="rk4")
+        got = nlbac_b200.odeint(ours, y0.cuda(), t, method="rk4", precision=precision)
+        got_e = nlbac_b200.odeint(ours, y0.cuda(), t[:2], method="euler", precision=precision)
+        want_e = oracle_odeint(ref, y0, t[:2], method="euler")
+    assert got.shape == want.shape
+    assert _rel(got, want) <= tol, _rel(got, want)
+    assert _rel(got_e, want_e) <= tol
+    # the increment y(t_end) - y0 is what the solver computes: hold it to the tier as well (looser for tf32)
+    inc_tol = 2e-4 if precision == "3xtf32" else 5e-2
+    assert _rel(got[-1].cpu() - y0, want[-1] - y0) <= inc_tol, _rel(got[-1].cpu() - y0, want[-1] - y0)
+
+
+def test_tensor_core_forward_with_fp32_backward():
+    """precision='tf32': forward on tcgen05, backward = FP32 reverse sweep from the forward's stage checkpoints."""
+    import nlbac_b200
+    ref, ours = _models("U")
+    y0 = _y0("U", 256)
+    t = 0.02 * torch.arange(4, dtype=torch.float32)
+    ya = y0.clone().requires_grad_(True)
+    oracle_odeint(ref, ya, t, method="rk4")[-1].pow(2).sum().backward()
+    for precision, tol in (("3xtf32", 2e-5), ("tf32", 1e-2)):
+        ours.zero_grad()
+        yb = y0.cuda().requires_grad_(True)
+        nlbac_b200.odeint(ours, yb, t, method="rk4", precision=precision)[-1].pow(2).sum().backward()
+        assert _rel(yb.grad, ya.grad) <= tol
+        for p, q in zip(ours.parameters(), ref.parameters()):
+            assert _rel(p.grad, q.grad) <= tol
