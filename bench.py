@@ -35,6 +35,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log2m", type=int, default=20, help="log2 of trajectories per GPU")
     ap.add_argument("--env", default="U", choices=["U", "P"])
+    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "3xtf32"],
+                    help="forward tier: fp32 FMA, tcgen05 TF32 (1e-2 tier) or 3xTF32 (fp32-class); backward is FP32")
     ap.add_argument("--cpu-sample", type=int, default=1024, help="trajectories in the CPU baseline sample")
     return ap.parse_args()
 
@@ -163,7 +165,7 @@ def run_ours(args):
     def fwd_bwd(y, timers=None):
         if timers is not None:
             timers[0].record()
-        sol = nlbac_b200.odeint(model, y, t, method="rk4", atol=1e-7, rtol=1e-5)
+        sol = nlbac_b200.odeint(model, y, t, method="rk4", atol=1e-7, rtol=1e-5, precision=args.precision)
         loss = sol[-1][:, :n_s].sum()
         if timers is not None:
             timers[1].record()
@@ -233,7 +235,7 @@ def run_ours(args):
             "config": {"workload": "config5: 2^%d %s-shaped trajectories per GPU x 20 rk4(3/8) steps, fwd+bwd, "
                                    "t=0.02*arange(21), cotangent ones on final state, d-theta all-reduced" % (
                                        args.log2m, "Unicycle" if env == "U" else "PVTOL"),
-                       "trajectories_per_gpu": M, "solver_steps": N_STEPS, "method": "rk4", "precision": "fp32",
+                       "trajectories_per_gpu": M, "solver_steps": N_STEPS, "method": "rk4", "precision": {"fp32": "fwd fp32 / bwd fp32", "tf32": "fwd tf32 / bwd tf32 (dW bf16 operands, fp32 accumulate)", "3xtf32": "fwd 3xtf32 / bwd fp32"}[args.precision],
                        "l2": "per-step working set (stage checkpoints + outputs, %.1f GB) exceeds the 126 MB L2; no explicit flush" % (
                            M * (N_STEPS * 4 * n_s + (N_STEPS + 1) * (n_s + 2) * 2) * 4 / 1e9)},
             "fwd_ms": fwd_ms, "bwd_ms": bwd_ms,

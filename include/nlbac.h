@@ -52,7 +52,7 @@ extern "C" {
 /* arithmetic of the hidden-layer contractions */
 #define NLBAC_PREC_FP32 0  /* FP32 FMA pipe; parity bar rel 1e-5 */
 #define NLBAC_PREC_BF16 1  /* reserved: bf16 operands measured at 2.7e-2 on d-theta -> not built */
-#define NLBAC_PREC_TF32 2  /* tcgen05 kind::tf32 hidden layers, fp32 accumulate (forward); parity bar rel 1e-2 */
+#define NLBAC_PREC_TF32 2  /* tcgen05 kind::tf32 hidden layers (forward and backward; dW on kind::f16 bf16), fp32 accumulate; bar rel 1e-2 */
 #define NLBAC_PREC_3XTF32 3 /* 3xTF32 split (hi*hi + lo*hi + hi*lo) on tcgen05 (forward); fp32-class, bar rel 1e-5 */
 
 typedef struct nlbac_node_desc {
@@ -87,6 +87,12 @@ int nlbac_node_pack(const nlbac_node_desc* desc, const float* const* params, flo
  * when precision is a tensor-core tier; the backward always takes the FP32 image of nlbac_node_pack. */
 int64_t nlbac_node_tc_packed_floats(const nlbac_node_desc* desc);
 int nlbac_node_tc_pack(const nlbac_node_desc* desc, const float* const* params, float* packed, void* stream);
+
+/* Workspace of the tensor-core backward (precision NLBAC_PREC_TF32 in nlbac_node_solve_bwd, `packed` = the
+ * tensor-core image): schedule tables + gradient replicas + (when parameter gradients are wanted) the bf16
+ * activation / cotangent images of one chunk of trajectories (<= 24 GB; the call loops over chunks). */
+int nlbac_node_tc_bwd_workspace_bytes(const nlbac_node_desc* desc, int64_t B, int n_grid, int n_t, int method,
+                                      int want_param_grads, size_t* bwd_bytes);
 
 /* Workspace sizes in bytes for a solve over `n_grid` integration grid points (n_grid-1 steps). */
 int nlbac_node_workspace_bytes(const nlbac_node_desc* desc, int64_t B, int n_grid, int n_t, int method,

@@ -5,7 +5,7 @@
 
 #include "../../include/nlbac.h"
 #include "node_dopri5.cuh"
-#include "node_tc.cuh"
+#include "node_tc_bwd.cuh"
 #include <cmath>
 #include "node_pack.cuh"
 
@@ -128,6 +128,50 @@ static int launch_tc_fwd(const FwdArgs& a, cudaStream_t st) {
   return 0;
 }
 
+// tiles per chunk of the tensor-core backward: a whole number of passes over the grid, images <= 24 GB
+template <class C>
+static long long tc_bwd_chunk_tiles(long long n_tiles, long long n_se) {
+  using G = TcBwdGeom<C>;
+  const long long per_pass = (long long)sm_count() * G::G;
+  const long long cap = 24LL << 30;
+  long long k = cap / (per_pass * n_se * ImgMap<C>::STRIDE);
+  if (k < 1) k = 1;
+  const long long chunk = k * per_pass;
+  return n_tiles < chunk ? n_tiles : chunk;
+}
+
+template <class C>
+static int run_tc_bwd(const BwdArgs& a, unsigned char* images, float* rep, cudaStream_t st) {
+  using G = TcBwdGeom<C>;
+  using DG = DwGeom<C>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    NLBAC_CUDA(cudaFuncSetAttribute(node_tc_bwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM_BYTES));
+    NLBAC_CUDA(cudaFuncSetAttribute(node_tc_dw_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DG::SMEM_BYTES));
+    attr_done = true;
+  }
+  const long long n_tiles = (a.B + 127) / 128;
+  const long long n_se = (long long)a.n_steps * method_stages(a.method);
+  const long long chunk = images ? tc_bwd_chunk_tiles<C>(n_tiles, n_se) : n_tiles;
+  for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
+    TcBwdArgs ta;
+    ta.b = a; ta.images = images; ta.tile0 = t0; ta.n_tiles = (n_tiles - t0 < chunk) ? n_tiles - t0 : chunk;
+    const long long n_pairs = (ta.n_tiles + G::G - 1) / G::G;
+    const int grid = (int)(n_pairs < sm_count() ? n_pairs : sm_count());
+    node_tc_bwd_kernel<C><<<grid, G::NT, G::SMEM_BYTES, st>>>(ta);
+    NLBAC_CUDA(cudaGetLastError());
+    if (images) {
+      const long long items = ta.n_tiles * n_se;
+      long long slabs = sm_count() / ImgMap<C>::NPAIR;
+      if (slabs < 1) slabs = 1;
+      if (slabs > items) slabs = items;
+      node_tc_dw_kernel<C><<<dim3((unsigned)slabs, ImgMap<C>::NPAIR), DG::NT, DG::SMEM_BYTES, st>>>(images, items, rep);
+      NLBAC_CUDA(cudaGetLastError());
+    }
+  }
+  return 0;
+}
+
 template <class C>
 static int launch_pack_tc(const float* const* params, float* packed, cudaStream_t st) {
   using T = TcCfg<C>;
@@ -135,7 +179,7 @@ static int launch_pack_tc(const float* const* params, float* packed, cudaStream_
   PackTable full = build_pack_table<C>(params), t;
   t.n = 0;
   for (int i = 0; i < full.n; ++i)
-    if (full.seg[i].dst_off + full.seg[i].rows * full.seg[i].cols <= C::RES_FWD) t.seg[t.n++] = full.seg[i];
+    if (full.seg[i].dst_off + full.seg[i].rows * full.seg[i].cols <= C::RES_ALL) t.seg[t.n++] = full.seg[i];
   pack_params_kernel<<<dim3(8, t.n), 256, 0, st>>>(t, packed);
   NLBAC_CUDA(cudaGetLastError());
   int pi = 0;
@@ -143,7 +187,8 @@ static int launch_pack_tc(const float* const* params, float* packed, cudaStream_
     for (int l = 0; l < C::nl(c); ++l, pi += 2)
       if (l >= 1 && l <= C::nhc(c)) {
         const int h = C::hid_base(c) + (l - 1);
-        pack_tc_kernel<C><<<16, 256, 0, st>>>(params[pi], packed + T::off_hi(h), packed + T::off_lo(h));
+        pack_tc_kernel<C><<<16, 256, 0, st>>>(params[pi], packed + T::off_hi(h), packed + T::off_lo(h),
+                                              packed + T::off_tr(h));
         NLBAC_CUDA(cudaGetLastError());
       }
   return 0;
@@ -355,12 +400,61 @@ int nlbac_node_solve_fwd(const nlbac_node_desc* desc, const float* packed, const
   });
 }
 
+int nlbac_node_tc_bwd_workspace_bytes(const nlbac_node_desc* desc, int64_t B, int n_grid, int n_t, int method,
+                                      int want_param_grads, size_t* bwd_bytes) {
+  NLBAC_REQUIRE(B >= 0 && n_grid >= 2 && n_t >= 1 && bwd_bytes, "bad sizes");
+  NLBAC_REQUIRE(method >= NLBAC_EULER && method <= NLBAC_RK4, "fixed-grid methods only (got %d)", method);
+  return dispatch(desc, [&]<class C>() {
+    const int n_steps = n_grid - 1;
+    const long long n_se = (long long)n_steps * method_stages(method);
+    const long long n_tiles = (B + 127) / 128;
+    size_t bytes = round_up((int)sched_bytes(n_steps, n_t), 1024) + (size_t)round_up(NREP * C::NGRAD * 4, 1024);
+    if (want_param_grads) bytes += (size_t)tc_bwd_chunk_tiles<C>(n_tiles, n_se) * n_se * ImgMap<C>::STRIDE;
+    *bwd_bytes = bytes;
+    return 0;
+  });
+}
+
 int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B,
                          const float* t, int n_t, const float* grid, int n_grid, int method, int precision,
                          const float* ckpt, const float* grad_out, float* grad_y0, float* grad_params,
                          void* ws, void* stream) {
   NLBAC_REQUIRE(packed && y0 && t && grid && ckpt && grad_out && ws, "null pointer");
-  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32, "precision %d not compiled", precision);
+  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32 || precision == NLBAC_PREC_TF32, "precision %d not compiled for the backward",
+                precision);
+  if (precision == NLBAC_PREC_TF32) {   // `packed` is the tensor-core image, `ws` sized by nlbac_node_tc_bwd_workspace_bytes
+    NLBAC_REQUIRE(method >= NLBAC_EULER && method <= NLBAC_RK4, "fixed-grid methods only (got %d)", method);
+    NLBAC_REQUIRE(B >= 0, "negative batch");
+    Schedule s;
+    if (int rc = build_schedule(t, n_t, grid, n_grid, &s)) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    return dispatch(desc, [&]<class C>() {
+      if (B == 0) {
+        if (grad_params) NLBAC_CUDA(cudaMemsetAsync(grad_params, 0, (size_t)C::NPARAM * 4, st));
+        return 0;
+      }
+      BwdArgs a;
+      a.packed = packed; a.y0 = y0; a.ckpt = ckpt; a.grad_out = grad_out; a.grad_y0 = grad_y0; a.B = B;
+      a.n_steps = n_grid - 1; a.n_t = n_t; a.method = method; a.grad_rep = nullptr;
+      if (int rc = upload_schedule(s, ws, st, &a.dts, &a.out_step, &a.out_w)) return rc;
+      char* base = static_cast<char*>(ws);
+      const size_t off_rep = round_up((int)sched_bytes(a.n_steps, n_t), 1024);
+      const size_t off_img = off_rep + (size_t)round_up(NREP * C::NGRAD * 4, 1024);
+      float* rep = reinterpret_cast<float*>(base + off_rep);
+      unsigned char* images = nullptr;
+      if (grad_params) {
+        NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
+        images = reinterpret_cast<unsigned char*>(base + off_img);
+      }
+      if (int rc = run_tc_bwd<C>(a, images, rep, st)) return rc;
+      if (grad_params) {
+        GradTable gt = build_grad_table<C>();
+        fold_grad_kernel<<<dim3(8, gt.n), 256, 0, st>>>(gt, rep, C::NGRAD, grad_params);
+        NLBAC_CUDA(cudaGetLastError());
+      }
+      return 0;
+    });
+  }
   NLBAC_REQUIRE(method >= NLBAC_EULER && method <= NLBAC_RK4, "fixed-grid methods only (got %d)", method);
   NLBAC_REQUIRE(B >= 0, "negative batch");
   Schedule s;

@@ -31,22 +31,39 @@ struct TcCfg {
   static constexpr int W_BYTES = W_FLOATS * 4;
   static constexpr int TCOLS = 128;                // TMEM columns reserved per group
   static_assert(NP <= TCOLS && KP == C::HP, "tile shape");
-  // packed image: [RES_FWD (thin layers, node_cfg.cuh) | U_hi[NHID] | U_lo[NHID]]
-  static constexpr int off_hi(int h) { return C::RES_FWD + h * W_FLOATS; }
-  static constexpr int off_lo(int h) { return C::RES_FWD + (C::NHID + h) * W_FLOATS; }
-  static constexpr int PACKED = C::RES_FWD + 2 * C::NHID * W_FLOATS;
+  // packed image: [RES_ALL (thin layers fwd + bwd, node_cfg.cuh) | U_hi[NHID] | U_lo[NHID] | U_T[NHID]]
+  //   U_hi / U_lo: B operand of the forward GEMM  (rows j = out, K = in);  U_T: B operand of dX (rows k = in, K = out)
+  __host__ __device__ static constexpr int off_hi(int h) { return C::RES_ALL + h * W_FLOATS; }
+  __host__ __device__ static constexpr int off_lo(int h) { return C::RES_ALL + (C::NHID + h) * W_FLOATS; }
+  __host__ __device__ static constexpr int off_tr(int h) { return C::RES_ALL + (2 * C::NHID + h) * W_FLOATS; }
+  static constexpr int PACKED = C::RES_ALL + 3 * C::NHID * W_FLOATS;
 };
+
+// round-to-nearest TF32 (the MMA itself truncates the low 13 mantissa bits: rounding first halves the error and
+// removes its bias); the result is exactly representable, so hi + (x - hi) == x for the 3xTF32 split
+__host__ __device__ __forceinline__ float tf32_hi(float x) {
+#ifdef __CUDA_ARCH__
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+#else
+  return x;
+#endif
+}
 
 // weight image of one hidden matrix: W[j][k] (nn.Linear [out][in]) -> float index (k/4)*NP*4 + j*4 + k%4
 template <class C>
-__global__ void pack_tc_kernel(const float* __restrict__ W, float* __restrict__ hi, float* __restrict__ lo) {
+__global__ void pack_tc_kernel(const float* __restrict__ W, float* __restrict__ hi, float* __restrict__ lo,
+                               float* __restrict__ tr) {
   using T = TcCfg<C>;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < T::W_FLOATS; i += gridDim.x * blockDim.x) {
     const int c = i / (T::NP * 4), j = (i / 4) % T::NP, k = 4 * c + (i & 3);
-    const float w = (j < C::H && k < C::H) ? W[j * C::H + k] : 0.f;
-    const float h = __uint_as_float(__float_as_uint(w) & 0xFFFFE000u);   // exactly representable in TF32
+    const bool in = j < C::H && k < C::H;
+    const float w = in ? W[j * C::H + k] : 0.f;
+    const float h = tf32_hi(w);
     hi[i] = h;
     lo[i] = w - h;
+    tr[i] = in ? tf32_hi(W[k * C::H + j]) : 0.f;                         // row j of the image = column j of W
   }
 }
 
@@ -76,7 +93,6 @@ struct TcFwdGeom {
 
 __device__ __forceinline__ void group_sync(int g) { asm volatile("bar.sync %0, 128;" ::"r"(g + 1) : "memory"); }
 
-__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xFFFFE000u); }
 
 // store 4 consecutive features [c, c+4) of activation row r into the image(s)
 template <bool SPLIT, int ACH, int A_BYTES>
@@ -87,7 +103,7 @@ __device__ __forceinline__ void store_act4(unsigned char* img, int r, int c, flo
     *reinterpret_cast<float4*>(p) = make_float4(h0, h1, h2, h3);
     *reinterpret_cast<float4*>(p + A_BYTES) = make_float4(v0 - h0, v1 - h1, v2 - h2, v3 - h3);
   } else {
-    *reinterpret_cast<float4*>(p) = make_float4(v0, v1, v2, v3);
+    *reinterpret_cast<float4*>(p) = make_float4(tf32_hi(v0), tf32_hi(v1), tf32_hi(v2), tf32_hi(v3));
   }
 }
 

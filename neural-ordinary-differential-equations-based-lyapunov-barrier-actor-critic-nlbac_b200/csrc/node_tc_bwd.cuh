@@ -1,0 +1,603 @@
+// K2-TC — backward of the fixed-grid NODE solve on the 5th-generation tensor cores, TF32 tier (1e-2).
+//
+// Two passes:
+//   pass A  node_tc_bwd_kernel: the reverse sweep of node_bwd.cuh with the hidden-layer GEMMs on tcgen05
+//           (kind::tf32): per (step, stage) the tile's activations are recomputed from the checkpointed stage
+//           input, the cotangent is pulled back through the layers (dX GEMMs against the transposed weight
+//           images), the owner thread advances the Runge-Kutta adjoint recurrences in registers.  Every
+//           activation a_i and every pre-activation cotangent d_i is ALSO written, rounded to bf16, to a
+//           global "image" that is already in the UMMA MN-major core-matrix layout (fully coalesced stores).
+//   pass B  node_tc_dw_kernel: parameter gradients as streaming GEMMs over those images,
+//           dW = sum over (trajectory, step, stage) of d^T a, on tcgen05 kind::f16 (bf16 operands, fp32
+//           accumulation in TMEM; tools/prec_emul.py: bf16 here adds 1e-4 to a 3.4e-3 tier).  A ones column in
+//           every activation image yields the bias gradients from the same GEMM.  HBM-bound by construction.
+#pragma once
+#include "node_bwd.cuh"
+#include "node_tc.cuh"
+#include <cuda_bf16.h>
+
+namespace nlbac {
+
+// Layout of the bf16 images of one (tile of 128 trajectories, stage evaluation), in bytes.
+//   big activation image  a_i   [128 x IMGW]  IMGW = round_up(H + 1, 16): features, a ones column at H, zeros
+//   big cotangent image   d_i   [128 x KP]
+//   thin images           xin [128 x 16] (stage input incl. constants for black-box nets, ones column at IN0),
+//                         dOut_c [128 x 16] (cotangent of the chain output)
+// element (t, c) of an image lives at (c / 8) * 2048 + (t / 8) * 128 + (t % 8) * 16 + (c % 8) * 2.
+template <class C>
+struct ImgMap {
+  using T = TcCfg<C>;
+  static constexpr int IMGW = round_up(C::H + 1, 16);
+  static constexpr int ACT_CH = IMGW / 8, DEL_CH = T::KP / 8, THIN_CH = 2;
+  static constexpr int ACT_B = ACT_CH * 2048, DEL_B = DEL_CH * 2048, THIN_B = THIN_CH * 2048;
+  static_assert(C::IN0 < 16 && C::OUTP_MAX <= 16, "thin images hold 16 columns");
+  __host__ __device__ static constexpr int nl1(int c) { return C::nhc(c) + 1; }   // activations / cotangents per chain
+  __host__ __device__ static constexpr int chain_bytes(int c) { return nl1(c) * (ACT_B + DEL_B) + THIN_B; }
+  __host__ __device__ static constexpr int off_xin() { return 0; }
+  __host__ __device__ static constexpr int chain_base(int c) { return THIN_B + (c == 0 ? 0 : chain_bytes(0)); }
+  __host__ __device__ static constexpr int off_act(int c, int i /*1..nl1*/) { return chain_base(c) + (i - 1) * ACT_B; }
+  __host__ __device__ static constexpr int off_del(int c, int i) { return chain_base(c) + nl1(c) * ACT_B + (i - 1) * DEL_B; }
+  __host__ __device__ static constexpr int off_dout(int c) { return chain_base(c) + nl1(c) * (ACT_B + DEL_B); }
+  static constexpr int STRIDE = THIN_B + chain_bytes(0) + (C::NCH == 2 ? chain_bytes(1) : 0);
+  // GEMM pairs of pass B: per chain  (d_1 | xin), (d_{l+1} | a_l) l = 1..nhc, (dOut | a_{nl1})
+  __host__ __device__ static constexpr int npairs(int c) { return C::nhc(c) + 2; }
+  static constexpr int NPAIR = npairs(0) + (C::NCH == 2 ? npairs(1) : 0);
+};
+
+struct __align__(16) Pack8 { __nv_bfloat162 a, b, c, d; };
+
+// 8 consecutive columns [c0, c0+8) of row t of a bf16 image (one 16-byte store; a warp writes 512 contiguous bytes)
+__device__ __forceinline__ void store_img8(unsigned char* img, int t, int c0, const float (&v)[8]) {
+  Pack8 p;
+  p.a = __floats2bfloat162_rn(v[0], v[1]); p.b = __floats2bfloat162_rn(v[2], v[3]);
+  p.c = __floats2bfloat162_rn(v[4], v[5]); p.d = __floats2bfloat162_rn(v[6], v[7]);
+  *reinterpret_cast<Pack8*>(img + (c0 >> 3) * 2048 + (t >> 3) * 128 + (t & 7) * 16) = p;
+}
+
+template <class C>
+struct TcBwdGeom {
+  using T = TcCfg<C>;
+  static constexpr int NSLOT = 2;
+  static constexpr int fixed_bytes = NSLOT * T::W_BYTES + C::RES_ALL * 4 + 256;
+  static constexpr int G = (fixed_bytes + 2 * T::A_BYTES <= 227 * 1024) ? 2 : 1;
+  static constexpr int NT = G * 128 + 32;
+  static constexpr int OFF_A = 0;
+  static constexpr int OFF_W = OFF_A + G * T::A_BYTES;
+  static constexpr int OFF_RES = OFF_W + NSLOT * T::W_BYTES;
+  static constexpr int OFF_BAR = OFF_RES + C::RES_ALL * 4;
+  static constexpr int NBAR = 2 * NSLOT + G + 1;
+  static constexpr size_t SMEM_BYTES = OFF_BAR + NBAR * 8 + 16;
+  static constexpr int PKT_PER_EVAL = 2 * C::NHID;   // every hidden matrix once forward, once transposed
+  static constexpr int NLAY = C::NL_MAX - 1;         // activations per chain (masks kept in registers)
+  static_assert(OFF_W % 128 == 0 && OFF_RES % 16 == 0 && OFF_BAR % 8 == 0, "alignment");
+  static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+  __device__ static int pkt_off(uint32_t p) {
+    int q = p % PKT_PER_EVAL, c = 0;
+    if (C::NCH == 2 && q >= 2 * C::nhc(0)) { c = 1; q -= 2 * C::nhc(0); }
+    const int n = C::nhc(c);
+    return q < n ? T::off_hi(C::hid_base(c) + q) : T::off_tr(C::hid_base(c) + (n - 1 - (q - n)));
+  }
+};
+
+// activation image store: 8 columns of row t; the ones column (bias gradients) sits at column H
+template <class C>
+__device__ __forceinline__ void store_act_img(unsigned char* img, int t, int c0, float (&v)[8]) {
+  if (C::H >= c0 && C::H < c0 + 8) v[C::H - c0] = 1.f;
+  store_img8(img, t, c0, v);
+}
+template <class C>
+__device__ __forceinline__ void finish_act_img(unsigned char* img, int t) {
+  if (C::H == TcCfg<C>::KP) {   // no padding column inside the K extent: the ones column opens a new chunk
+    float v[8] = {1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    store_img8(img, t, C::H, v);
+  }
+}
+
+// one hidden-layer GEMM of the group's tile: A = the group's activation image, B = next ring packet
+template <class C, int NSLOT>
+__device__ __forceinline__ void tc_layer_mma(TcGroupCtx& cx) {
+  using T = TcCfg<C>;
+  if (cx.lt == 0) {
+    umma::fence_after_sync();
+    const uint32_t slot = cx.seq % NSLOT;
+    mbar_wait(&cx.full[slot], (cx.seq / NSLOT) & 1);
+    umma::fence_after_sync();
+    const uint32_t a0 = smem_u32(cx.sA), b0 = smem_u32(cx.sW + slot * T::W_BYTES);
+    const uint32_t idesc = umma::make_idesc_tf32(128, T::NP, false, false);
+#pragma unroll 1
+    for (int ks = 0; ks < T::KSTEPS; ++ks)
+      umma::mma_tf32(cx.tmma, umma::make_desc(a0 + ks * 2 * T::ACH, T::ACH, 128),
+                     umma::make_desc(b0 + ks * 2 * T::WCH, T::WCH, 128), idesc, ks > 0);
+    umma::commit(&cx.empty[slot]);
+    umma::commit(cx.done);
+  }
+  ++cx.seq;
+  mbar_wait(cx.done, cx.nd & 1);
+  ++cx.nd;
+  umma::fence_after_sync();
+}
+
+__device__ __forceinline__ void tc_publish(TcGroupCtx& cx) {   // smem image written -> visible to the next MMA
+  fence_proxy_async();
+  umma::fence_before_sync();
+  group_sync(cx.g);
+}
+
+// One stage of the reverse sweep for the group's tile (mirrors vjp_rhs_tile of node_bwd.cuh).
+// img: global image block of this (tile, stage evaluation) or nullptr (no parameter gradients wanted).
+template <class C>
+__device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, const float (&x)[C::NS],
+                                           const float (&cst)[C::NCONST], const float (&dk)[C::NS],
+                                           float (&dx)[C::NS], float (&dcst)[C::NCONST]) {
+  using T = TcCfg<C>;
+  using G = TcBwdGeom<C>;
+  using IM = ImgMap<C>;
+  constexpr int NG8 = T::KP / 8;
+  const int lt = cx.lt;
+  float dxa[C::INP0];
+#pragma unroll
+  for (int d = 0; d < C::INP0; ++d) dxa[d] = 0.f;
+  if (img != nullptr) {   // stage input image (shared by the chains): [x | const | 1 | 0...]
+    float v0[8], v1[8];
+#pragma unroll
+    for (int d = 0; d < 16; ++d) {
+      float val = 0.f;
+      if (d < C::NS) val = x[d < C::NS ? d : 0];
+      else if (d < C::IN0) val = cst[(d >= C::NS && d < C::IN0) ? d - C::NS : 0];
+      else if (d == C::IN0) val = 1.f;
+      if (d < 8) v0[d] = val; else v1[d - 8] = val;
+    }
+    store_img8(img + IM::off_xin(), lt, 0, v0);
+    store_img8(img + IM::off_xin(), lt, 8, v1);
+  }
+#pragma unroll
+  for (int c = 0; c < C::NCH; ++c) {
+    const int n = C::nhc(c);
+    const int OUT = C::out(c), OUTP = C::outp(c);
+    uint32_t mk[G::NLAY][4];
+#pragma unroll
+    for (int i = 0; i < G::NLAY; ++i)
+#pragma unroll
+      for (int w = 0; w < 4; ++w) mk[i][w] = 0u;
+    // ---------------- thin first layer -> a_1 ----------------
+    {
+      const float* Wt0 = cx.sRes + C::off_wt0(c);
+      const float* b0 = cx.sRes + C::off_b0(c);
+#pragma unroll
+      for (int g8 = 0; g8 < NG8; ++g8) {
+        float v[8];
+        const float4 ba = *reinterpret_cast<const float4*>(b0 + 8 * g8);
+        const float4 bb = *reinterpret_cast<const float4*>(b0 + 8 * g8 + 4);
+        v[0] = ba.x; v[1] = ba.y; v[2] = ba.z; v[3] = ba.w; v[4] = bb.x; v[5] = bb.y; v[6] = bb.z; v[7] = bb.w;
+#pragma unroll
+        for (int d = 0; d < C::IN0; ++d) {
+          const float xv = d < C::NS ? x[d < C::NS ? d : 0] : cst[d >= C::NS ? d - C::NS : 0];
+          const float4 wa = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8);
+          const float4 wb = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8 + 4);
+          v[0] = fmaf(xv, wa.x, v[0]); v[1] = fmaf(xv, wa.y, v[1]); v[2] = fmaf(xv, wa.z, v[2]); v[3] = fmaf(xv, wa.w, v[3]);
+          v[4] = fmaf(xv, wb.x, v[4]); v[5] = fmaf(xv, wb.y, v[5]); v[6] = fmaf(xv, wb.z, v[6]); v[7] = fmaf(xv, wb.w, v[7]);
+        }
+        uint32_t bits = 0u;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { v[i] = fmaxf(v[i], 0.f); bits |= (v[i] > 0.f ? 1u : 0u) << i; }
+        mk[0][g8 >> 2] |= bits << ((g8 & 3) * 8);
+        store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
+        store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
+        if (img != nullptr) store_act_img<C>(img + IM::off_act(c, 1), lt, 8 * g8, v);
+      }
+      if (img != nullptr) finish_act_img<C>(img + IM::off_act(c, 1), lt);
+    }
+    tc_publish(cx);
+    // cotangent of the chain output
+    float dout[C::OUTP_MAX], go[C::OUTP_MAX];
+#pragma unroll
+    for (int o = 0; o < C::OUTP_MAX; ++o) { dout[o] = 0.f; go[o] = 0.f; }
+    if (c == 0) {
+#pragma unroll
+      for (int o = 0; o < C::NS; ++o) dout[o] = dk[o];
+    } else {
+#pragma unroll
+      for (int i = 0; i < C::NS; ++i)
+#pragma unroll
+        for (int j = 0; j < C::NU; ++j) dout[i * C::NU + j] = dk[i] * cst[j];
+    }
+    if (img != nullptr) {
+      float v0[8], v1[8];
+#pragma unroll
+      for (int o = 0; o < 16; ++o) {
+        const float val = o < C::OUTP_MAX ? dout[o < C::OUTP_MAX ? o : 0] : 0.f;
+        if (o < 8) v0[o] = val; else v1[o - 8] = val;
+      }
+      store_img8(img + IM::off_dout(c), lt, 0, v0);
+      store_img8(img + IM::off_dout(c), lt, 8, v1);
+    }
+    // ---------------- hidden layers forward: a_{l+1} = relu(H_l a_l + b_l) ----------------
+#pragma unroll
+    for (int l = 1; l <= G::NLAY - 1; ++l) {
+      if (l <= n) {
+        tc_layer_mma<C, G::NSLOT>(cx);
+        const float* bias = cx.sRes + C::off_bh(c, l);
+        const float* WnL = cx.sRes + C::off_wnl(c);
+        const float* WtL = cx.sRes + C::off_wtl(c);
+#pragma unroll
+        for (int g8 = 0; g8 < NG8; ++g8) {
+          float v[8];
+          umma::ld8(cx.tacc + 8 * g8, v);
+          umma::wait_ld();
+          const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
+          const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
+          v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
+          uint32_t bits = 0u;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { v[i] = fmaxf(v[i], 0.f); bits |= (v[i] > 0.f ? 1u : 0u) << i; }
+          mk[l][g8 >> 2] |= bits << ((g8 & 3) * 8);
+          if (l < n) {
+            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
+            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
+            if (img != nullptr) store_act_img<C>(img + IM::off_act(c, l + 1), lt, 8 * g8, v);
+          } else {
+            // last hidden activation: forward value of g(x) (action gradient) and d_{n+1} = relu' * WL^T dOut
+            float dl[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int kk = 8 * g8 + i;
+              float acc = 0.f;
+              if (kk < C::H) {
+                if (c == 1) {
+#pragma unroll
+                  for (int o = 0; o < C::OUTP_MAX; o += 4)
+                    if (o < OUTP) {
+                      const float4 w = *reinterpret_cast<const float4*>(WtL + kk * OUTP + o);
+                      go[o] = fmaf(v[i], w.x, go[o]); go[o + 1] = fmaf(v[i], w.y, go[o + 1]);
+                      go[o + 2] = fmaf(v[i], w.z, go[o + 2]); go[o + 3] = fmaf(v[i], w.w, go[o + 3]);
+                    }
+                }
+#pragma unroll
+                for (int o = 0; o < C::OUTP_MAX; ++o)
+                  if (o < OUT) acc = fmaf(dout[o], WnL[o * C::HP + kk], acc);
+              }
+              dl[i] = v[i] > 0.f ? acc : 0.f;
+            }
+            if (img != nullptr) {
+              store_act_img<C>(img + IM::off_act(c, n + 1), lt, 8 * g8, v);
+              store_img8(img + IM::off_del(c, n + 1), lt, 8 * g8, dl);
+            }
+            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, dl[0], dl[1], dl[2], dl[3]);
+            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, dl[4], dl[5], dl[6], dl[7]);
+          }
+        }
+        if (img != nullptr) finish_act_img<C>(img + IM::off_act(c, l + 1), lt);
+        tc_publish(cx);
+      }
+    }
+    if (c == 1) {   // dL/du_j += sum_i g(x)[i][j] dk[i]   (bias of the last layer included)
+      const float* bL = cx.sRes + C::off_bl(c);
+#pragma unroll
+      for (int i = 0; i < C::NS; ++i)
+#pragma unroll
+        for (int j = 0; j < C::NU; ++j) dcst[j] = fmaf(go[i * C::NU + j] + bL[i * C::NU + j], dk[i], dcst[j]);
+    }
+    // ---------------- hidden layers backward: d_l = relu'(a_l) * H_l^T d_{l+1} ----------------
+#pragma unroll
+    for (int l = G::NLAY - 1; l >= 1; --l) {
+      if (l <= n) {
+        tc_layer_mma<C, G::NSLOT>(cx);
+        const float* Wn0 = cx.sRes + C::off_wn0(c);
+#pragma unroll
+        for (int g8 = 0; g8 < NG8; ++g8) {
+          float v[8];
+          umma::ld8(cx.tacc + 8 * g8, v);
+          umma::wait_ld();
+          const uint32_t bits = (mk[l - 1][g8 >> 2] >> ((g8 & 3) * 8)) & 0xFFu;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = ((bits >> i) & 1u) ? v[i] : 0.f;
+          if (img != nullptr) store_img8(img + IM::off_del(c, l), lt, 8 * g8, v);
+          if (l > 1) {
+            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
+            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
+          } else {   // d_1: thin first layer, dx = W0^T d_1
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int j = 8 * g8 + i;
+              if (j < C::H) {
+#pragma unroll
+                for (int d = 0; d < C::INP0; d += 4) {
+                  const float4 w = *reinterpret_cast<const float4*>(Wn0 + j * C::INP0 + d);
+                  dxa[d] = fmaf(v[i], w.x, dxa[d]); dxa[d + 1] = fmaf(v[i], w.y, dxa[d + 1]);
+                  dxa[d + 2] = fmaf(v[i], w.z, dxa[d + 2]); dxa[d + 3] = fmaf(v[i], w.w, dxa[d + 3]);
+                }
+              }
+            }
+          }
+        }
+        if (l > 1) tc_publish(cx);
+      }
+    }
+  }
+#pragma unroll
+  for (int d = 0; d < C::NS; ++d) dx[d] = dxa[d];
+  if constexpr (C::KIND == KIND_BLACKBOX) {
+#pragma unroll
+    for (int d = 0; d < C::NCONST; ++d) dcst[d] += dxa[C::NS + d];
+  }
+}
+
+struct TcBwdArgs {
+  BwdArgs b;              // same meaning as node_bwd.cuh (grad_rep unused here)
+  unsigned char* images;  // [n_tiles_in_chunk][n_steps * S][ImgMap::STRIDE] or null
+  long long tile0;        // first tile of this chunk (rows tile0 * 128 ...)
+  long long n_tiles;      // tiles in this chunk
+};
+
+template <class C>
+__global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdArgs ta) {
+  using T = TcCfg<C>;
+  using G = TcBwdGeom<C>;
+  using IM = ImgMap<C>;
+  const BwdArgs& a = ta.b;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  float* sRes = reinterpret_cast<float*>(smem_raw + G::OFF_RES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + G::OFF_BAR);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + G::NSLOT;
+  uint64_t* done = bars + 2 * G::NSLOT;
+  uint64_t* resbar = bars + 2 * G::NSLOT + G::G;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + G::NBAR);
+  const int tid = threadIdx.x, warp = tid / 32;
+  const bool is_prod = warp == G::G * 4;
+  const Tableau tab = make_tableau(a.method);
+  const int S = tab.S;
+
+  const long long n_pairs = (ta.n_tiles + G::G - 1) / G::G;
+  long long my_iters = 0;
+  if ((long long)blockIdx.x < n_pairs) my_iters = (n_pairs - blockIdx.x + gridDim.x - 1) / gridDim.x;
+  const uint32_t total = (uint32_t)(my_iters * a.n_steps * S * G::PKT_PER_EVAL);
+
+  if (tid == 0) {
+    for (int i = 0; i < G::NSLOT; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], G::G); }
+    for (int i = 0; i < G::G; ++i) mbar_init(&done[i], 1);
+    mbar_init(resbar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) umma::tmem_alloc(tslot, G::G * T::TCOLS);
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tbase = *tslot;
+
+  if (is_prod) {
+    if (tid % 32 == 0 && my_iters > 0) {
+      mbar_expect_tx(resbar, C::RES_ALL * 4);
+      tma_load_1d(sRes, a.packed, C::RES_ALL * 4, resbar);
+      for (uint32_t p = 0; p < total; ++p) {
+        const uint32_t slot = p % G::NSLOT;
+        if (p >= (uint32_t)G::NSLOT) mbar_wait(&empty[slot], ((p / G::NSLOT) - 1) & 1);
+        mbar_expect_tx(&full[slot], T::W_BYTES);
+        tma_load_1d(smem_raw + G::OFF_W + slot * T::W_BYTES, a.packed + G::pkt_off(p), T::W_BYTES, &full[slot]);
+      }
+    }
+    __syncwarp();
+  } else if (my_iters > 0) {
+    TcGroupCtx cx;
+    cx.g = tid / 128;
+    cx.lt = tid % 128;
+    cx.sA = smem_raw + G::OFF_A + cx.g * T::A_BYTES;
+    cx.sW = smem_raw + G::OFF_W;
+    cx.sRes = sRes;
+    cx.full = full; cx.empty = empty; cx.done = &done[cx.g];
+    cx.tmma = tbase + cx.g * T::TCOLS;
+    cx.tacc = cx.tmma + ((uint32_t)((warp % 4) * 32) << 16);
+    cx.seq = 0; cx.nd = 0;
+    mbar_wait(resbar, 0);
+    const long long n_se = (long long)a.n_steps * S;
+
+    for (long long it = 0; it < my_iters; ++it) {
+      const long long ltile = (it * gridDim.x + blockIdx.x) * G::G + cx.g;   // tile within the chunk
+      const bool tile_live = ltile < ta.n_tiles;
+      const long long b = (ta.tile0 + ltile) * T::ROWS + cx.lt;
+      const bool live = tile_live && b < a.B;
+      unsigned char* timg = (ta.images != nullptr && tile_live) ? ta.images + (size_t)ltile * n_se * IM::STRIDE : nullptr;
+      float adj[C::NS], cst[C::NCONST], dcst[C::NCONST];
+      float dks[4][C::NS];
+#pragma unroll
+      for (int d = 0; d < C::NS; ++d) adj[d] = 0.f;
+#pragma unroll
+      for (int d = 0; d < C::NCONST; ++d) { cst[d] = 0.f; dcst[d] = 0.f; }
+      if (live) {
+#pragma unroll
+        for (int d = 0; d < C::NCONST; ++d) cst[d] = a.y0[b * C::D + C::NS + d];
+      }
+      int jo = a.n_t - 1;
+      for (int step = a.n_steps - 1; step >= 0; --step) {
+        const float dt = a.dts[step];
+        float carry[C::NS];
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) carry[d] = 0.f;
+        while (jo >= 1 && a.out_step[jo] == step) {
+          if (live) {
+            const float w = a.out_w[jo];
+            const float* g = a.grad_out + ((long long)jo * a.B + b) * C::D;
+#pragma unroll
+            for (int d = 0; d < C::NS; ++d) {
+              const float gv = g[d];
+              adj[d] = fmaf(w, gv, adj[d]);
+              carry[d] = fmaf(1.f - w, gv, carry[d]);
+            }
+#pragma unroll
+            for (int d = 0; d < C::NCONST; ++d) dcst[d] += g[C::NS + d];
+          }
+          --jo;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) dks[i][d] = dt * tab.csol[i] * adj[d];
+        float ay[C::NS];
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) ay[d] = adj[d] + carry[d];
+#pragma unroll 1
+        for (int i = S - 1; i >= 0; --i) {
+          float x[C::NS], dk[C::NS], dx[C::NS];
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) { x[d] = 0.f; dk[d] = dks[i][d]; }
+          if (live) {
+            const float* p = a.ckpt + (((long long)step * S + i) * a.B + b) * C::NS;
+#pragma unroll
+            for (int d = 0; d < C::NS; ++d) x[d] = p[d];
+          } else {
+#pragma unroll
+            for (int d = 0; d < C::NS; ++d) dk[d] = 0.f;
+          }
+          unsigned char* img = timg ? timg + (size_t)((long long)step * S + i) * IM::STRIDE : nullptr;
+          vjp_rhs_tc<C>(cx, img, x, cst, dk, dx, dcst);
+#pragma unroll
+          for (int d = 0; d < C::NS; ++d) ay[d] += dx[d];
+#pragma unroll
+          for (int j = 0; j < 3; ++j)
+            if (j < i) {
+              const float bij = dt * tab.beta[i][j];
+#pragma unroll
+              for (int d = 0; d < C::NS; ++d) dks[j][d] = fmaf(bij, dx[d], dks[j][d]);
+            }
+        }
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) adj[d] = ay[d];
+      }
+      if (live && a.grad_y0 != nullptr) {
+        const float* g = a.grad_out + b * C::D;
+        float* o = a.grad_y0 + b * C::D;
+#pragma unroll
+        for (int d = 0; d < C::NS; ++d) o[d] = adj[d] + g[d];
+#pragma unroll
+        for (int d = 0; d < C::NCONST; ++d) o[C::NS + d] = dcst[d] + g[C::NS + d];
+      }
+    }
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tbase, G::G * T::TCOLS);
+}
+
+// ------------------------------------------------------------------------------------------------
+// pass B: parameter gradients as streaming bf16 GEMMs over the images (one GEMM pair per blockIdx.y)
+// ------------------------------------------------------------------------------------------------
+struct DwPair {
+  int offD, bytesD;   // cotangent image (A operand, M = its feature columns)
+  int offA, bytesA;   // activation image (B operand, N = its columns)
+  int N;              // MMA N
+  int rows, cols;     // valid extent of the result: rows of W, input columns of W
+  int goff_w, goff_b, ldw;
+};
+template <class C>
+__host__ __device__ inline DwPair dw_pair(int pr) {
+  using IM = ImgMap<C>;
+  int c = 0;
+  if (C::NCH == 2 && pr >= IM::npairs(0)) { c = 1; pr -= IM::npairs(0); }
+  const int n = C::nhc(c);
+  DwPair p;
+  if (pr == 0) {
+    p = {IM::off_del(c, 1), IM::DEL_B, IM::off_xin(), IM::THIN_B, 16, C::H, C::IN0, C::goff_w(c, 0), C::goff_b(c, 0), C::IN0};
+  } else if (pr <= n) {
+    p = {IM::off_del(c, pr + 1), IM::DEL_B, IM::off_act(c, pr), IM::ACT_B, IM::IMGW, C::H, C::H, C::goff_w(c, pr),
+         C::goff_b(c, pr), C::H};
+  } else {
+    p = {IM::off_dout(c), IM::THIN_B, IM::off_act(c, n + 1), IM::ACT_B, IM::IMGW, C::out(c), C::H, C::goff_w(c, n + 1),
+         C::goff_b(c, n + 1), C::H};
+  }
+  return p;
+}
+
+template <class C>
+struct DwGeom {
+  using IM = ImgMap<C>;
+  static constexpr int NST = 3;
+  static constexpr int DBUF = 16 * 2048;            // M = 128 feature rows are addressed (13 or 2 chunks are loaded)
+  static constexpr int ABUF = IM::ACT_B;
+  static constexpr int STAGE = DBUF + ABUF;
+  static constexpr int OFF_BAR = NST * STAGE;
+  static constexpr size_t SMEM_BYTES = OFF_BAR + (2 * NST + 1) * 8 + 16;
+  static constexpr int NT = 160;
+  static_assert(STAGE % 128 == 0 && SMEM_BYTES <= 227 * 1024, "pass-B staging");
+};
+
+template <class C>
+__global__ void __launch_bounds__(DwGeom<C>::NT, 1) node_tc_dw_kernel(const unsigned char* __restrict__ images,
+                                                                      long long n_items, float* __restrict__ grad_rep) {
+  using G = DwGeom<C>;
+  using IM = ImgMap<C>;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + G::OFF_BAR);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + G::NST;
+  uint64_t* done = bars + 2 * G::NST;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 2 * G::NST + 1);
+  const int tid = threadIdx.x, warp = tid / 32;
+  const DwPair pr = dw_pair<C>(blockIdx.y);
+  long long my_items = 0;
+  if ((long long)blockIdx.x < n_items) my_items = (n_items - blockIdx.x + gridDim.x - 1) / gridDim.x;
+
+  if (tid == 0) {
+    for (int i = 0; i < G::NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) umma::tmem_alloc(tslot, 128);
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tbase = *tslot;
+
+  if (my_items > 0) {
+    if (warp == 4) {
+      if (tid % 32 == 0) {   // TMA producer
+        for (long long i = 0; i < my_items; ++i) {
+          const int s = (int)(i % G::NST);
+          if (i >= G::NST) mbar_wait(&empty[s], (uint32_t)((i / G::NST) - 1) & 1);
+          const unsigned char* blk = images + (size_t)(blockIdx.x + i * gridDim.x) * IM::STRIDE;
+          mbar_expect_tx(&full[s], pr.bytesD + pr.bytesA);
+          tma_load_1d(smem_raw + s * G::STAGE, blk + pr.offD, pr.bytesD, &full[s]);
+          tma_load_1d(smem_raw + s * G::STAGE + G::DBUF, blk + pr.offA, pr.bytesA, &full[s]);
+        }
+      }
+      __syncwarp();
+    } else {
+      if (tid == 0) {        // MMA issuer: D[j][n] += sum_t d[t][j] a[t][n], K = 128 trajectories = 8 x 16
+        const uint32_t idesc = umma::make_idesc_bf16(128, pr.N, true, true);
+        for (long long i = 0; i < my_items; ++i) {
+          const int s = (int)(i % G::NST);
+          mbar_wait(&full[s], (uint32_t)(i / G::NST) & 1);
+          umma::fence_after_sync();
+          const uint32_t a0 = smem_u32(smem_raw + s * G::STAGE), b0 = a0 + G::DBUF;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma::mma_bf16(tbase, umma::make_desc(a0 + ks * 256, 128, 2048), umma::make_desc(b0 + ks * 256, 128, 2048),
+                           idesc, (i > 0 || ks > 0) ? 1u : 0u);
+          umma::commit(&empty[s]);
+        }
+        umma::commit(done);
+      }
+      mbar_wait(done, 0);
+      umma::fence_after_sync();
+      const int j = tid;   // result row = feature of the cotangent image
+      float* grep = grad_rep + (size_t)(blockIdx.x % NREP) * C::NGRAD;
+      for (int c0 = 0; c0 < pr.N; c0 += 8) {
+        float v[8];
+        umma::ld8(tbase + ((uint32_t)(warp * 32) << 16) + c0, v);
+        umma::wait_ld();
+        if (j < pr.rows) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int col = c0 + i;
+            if (col < pr.cols) atomicAdd(grep + pr.goff_w + j * pr.ldw + col, v[i]);
+            else if (col == pr.cols) atomicAdd(grep + pr.goff_b + j, v[i]);
+          }
+        }
+      }
+    }
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tbase, 128);
+}
+
+}  // namespace nlbac

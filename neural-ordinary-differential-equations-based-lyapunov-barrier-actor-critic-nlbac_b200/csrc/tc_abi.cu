@@ -2,6 +2,7 @@
 #include "../../include/nlbac.h"
 #include "umma.cuh"
 #include <cstring>
+#include <cuda_bf16.h>
 
 namespace nlbac {
 
@@ -88,8 +89,15 @@ __global__ void __launch_bounds__(128, 1) umma_probe_kernel(ProbeArgs p, const f
   const int tid = threadIdx.x, warp = tid / 32;
   for (int i = tid; i < 64 * ST_XCH / 4; i += 128) reinterpret_cast<float*>(sm)[i] = 0.f;
   __syncthreads();
+  if (p.b_is_weight == 2) {
+    for (int c = 0; c < ST_K; ++c) {
+      *reinterpret_cast<__nv_bfloat16*>(bufA + umma::tile_off16(tid, c, ST_XCH)) = __float2bfloat16(X[tid * ST_K + c]);
+      *reinterpret_cast<__nv_bfloat16*>(bufB + umma::tile_off16(tid, c, ST_XCH)) = __float2bfloat16(Y[tid * ST_K + c]);
+    }
+  } else
   for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufA + umma::tile_off(tid, c, ST_XCH)) = X[tid * ST_K + c];
-  if (!p.b_is_weight) {
+  if (p.b_is_weight == 2) {
+  } else if (!p.b_is_weight) {
     for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_XCH)) = Y[tid * ST_K + c];
   } else if (tid < ST_K) {
     for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_WCH)) = Y[tid * ST_K + c];
@@ -103,10 +111,17 @@ __global__ void __launch_bounds__(128, 1) umma_probe_kernel(ProbeArgs p, const f
   const uint32_t tbase = *tslot;
   if (tid == 0) {
     const uint32_t a0 = smem_u32(bufA), b0 = smem_u32(bufB);
+    if (p.b_is_weight == 2) {
+      const uint32_t idesc = umma::make_idesc_bf16(128, ST_N, p.a_mn != 0, p.b_mn != 0);
+      for (int ks = 0; ks < p.nsteps; ++ks)
+        umma::mma_bf16(tbase, umma::make_desc(a0 + ks * p.stepA, p.lboA, p.sboA),
+                       umma::make_desc(b0 + ks * p.stepB, p.lboB, p.sboB), idesc, ks > 0);
+    } else {
     const uint32_t idesc = umma::make_idesc_tf32(128, ST_N, p.a_mn != 0, p.b_mn != 0);
     for (int ks = 0; ks < p.nsteps; ++ks)
       umma::mma_tf32(tbase, umma::make_desc(a0 + ks * p.stepA, p.lboA, p.sboA),
                      umma::make_desc(b0 + ks * p.stepB, p.lboB, p.sboB), idesc, ks > 0);
+    }
     umma::commit(bar);
   }
   mbar_wait(bar, 0);

@@ -119,8 +119,10 @@ class _FixedSolve(torch.autograd.Function):
                                           n_grid, method, precision, y_out.data_ptr(),
                                           ckpt.data_ptr() if want_ckpt else None, ws.data_ptr(), st), "node_solve_fwd")
         if want_ckpt:
-            ctx.save_for_backward(y0c, packed, ckpt)
-            ctx.meta = (desc, t_np, grid_np, method, 0, bwd.value, [p.shape for p in params])   # backward is FP32
+            # backward tier: TF32 -> tensor-core reverse sweep (takes the tensor-core image); others -> FP32 sweep
+            bprec = 2 if precision == 2 else 0
+            ctx.save_for_backward(y0c, packed_fwd if bprec == 2 else packed, ckpt)
+            ctx.meta = (desc, t_np, grid_np, method, bprec, bwd.value, [p.shape for p in params])
         return y_out
 
     @staticmethod
@@ -133,12 +135,17 @@ class _FixedSolve(torch.autograd.Function):
         need_y0 = ctx.needs_input_grad[0]
         need_p = any(ctx.needs_input_grad[9:])
         go = grad_out.contiguous()
+        _, tp = _farr(t_np)
+        _, gp = _farr(grid_np)
+        if precision == 2:
+            nb = ctypes.c_size_t()
+            _lib.check(L.nlbac_node_tc_bwd_workspace_bytes(ctypes.byref(desc), B, len(grid_np), len(t_np), method,
+                                                           1 if need_p else 0, ctypes.byref(nb)), "tc_bwd_workspace")
+            bwd_bytes = nb.value
         ws = torch.empty(max(bwd_bytes, 16), dtype=torch.uint8, device=dev)
         gy0 = torch.empty((B, D), dtype=torch.float32, device=dev) if need_y0 else None
         n_param = L.nlbac_node_param_count(ctypes.byref(desc))
         gflat = torch.empty(n_param, dtype=torch.float32, device=dev) if need_p else None
-        _, tp = _farr(t_np)
-        _, gp = _farr(grid_np)
         st = torch.cuda.current_stream().cuda_stream
         _lib.check(L.nlbac_node_solve_bwd(ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, tp, len(t_np), gp,
                                           len(grid_np), method, precision, ckpt.data_ptr(), go.data_ptr(),
@@ -199,7 +206,7 @@ def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, even
     if method in _FIXED:
         step_size = options.pop("step_size", None)
         grid_np = t_np if step_size is None else _grid_from_step_size(t_np, float(step_size))
-        packed = _packed(func, desc, params) if (need_grad or prec == 0) else None
+        packed = _packed(func, desc, params) if (prec == 0 or (need_grad and prec == 3)) else None
         packed_fwd = _packed(func, desc, params, tc=True) if prec != 0 else packed
         return _FixedSolve.apply(y0, desc, packed, packed_fwd, t_np, grid_np, METHODS[method], prec, need_grad, *params)
     if prec != 0:

@@ -23,3 +23,9 @@ for lbo, sbo, step in [(128, WCH, 128), (WCH, 128, 128), (128, WCH, 256), (WCH, 
 print("mode2: both MN-major variants")
 for lbo, sbo, step in [(128, XCH, 128), (XCH, 128, 128), (128, XCH, 256), (XCH, 128, 256)]:
     print((lbo, sbo, step), err(run([1, 1, lbo, sbo, step, lbo, sbo, step, 16 if step == 128 else 8, 0], X.cuda(), Y.cuda()), want2))
+
+print("mode3: bf16 both MN-major interleave (lbo, sbo, step) K=16 per MMA")
+Xb, Yb = X.bfloat16().double(), Y.bfloat16().double()
+want3 = Xb.t() @ Yb
+for lbo, sbo, step in [(128, XCH, 256), (XCH, 128, 256)]:
+    print((lbo, sbo, step), err(run([1, 1, lbo, sbo, step, lbo, sbo, step, 8, 2], X.cuda(), Y.cuda()), want3))
