@@ -107,6 +107,25 @@ __device__ __forceinline__ void store_act4(unsigned char* img, int r, int c, flo
   }
 }
 
+// Visit the accumulator row in batches of 4 x 8 columns: up to four tcgen05.ld in flight, ONE wait per batch.
+// body(q, u, g8, v): q = batch (rolled loop), u = 0..3 (unrolled), g8 = 4q + u = column group, v = 8 columns.
+template <int NG8, bool LOAD, class F>
+__device__ __forceinline__ void tc_batches(uint32_t tacc, F&& body) {
+#pragma unroll 1
+  for (int q = 0; q < (NG8 + 3) / 4; ++q) {
+    float v[4][8];
+    if (LOAD) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (4 * q + u < NG8) umma::ld8(tacc + 8 * (4 * q + u), v[u]);
+      umma::wait_ld();
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (4 * q + u < NG8) body(q, u, 4 * q + u, v[u]);
+  }
+}
+
 // Shared-memory / barrier handles of one group
 struct TcGroupCtx {
   unsigned char* sA;       // activation image(s) of this group
@@ -195,19 +214,16 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
       ++cx.nd;
       umma::fence_after_sync();
       const float* bias = cx.sRes + C::off_bh(c, l);
+      constexpr int NG8 = T::KP / 8;
       if (l < n) {  // ---- epilogue: bias + ReLU -> activation image (in place) ----
-#pragma unroll 1
-        for (int c0 = 0; c0 < T::KP; c0 += 8) {
-          float v[8];
-          umma::ld8(cx.tacc + c0, v);
-          umma::wait_ld();
-          const float4 b0 = *reinterpret_cast<const float4*>(bias + c0);
-          const float4 b1 = *reinterpret_cast<const float4*>(bias + c0 + 4);
-          store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, c0, fmaxf(v[0] + b0.x, 0.f), fmaxf(v[1] + b0.y, 0.f),
+        tc_batches<NG8, true>(cx.tacc, [&](int, int, int g8, float (&v)[8]) {
+          const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * g8);
+          const float4 b1 = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
+          store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, fmaxf(v[0] + b0.x, 0.f), fmaxf(v[1] + b0.y, 0.f),
                                                 fmaxf(v[2] + b0.z, 0.f), fmaxf(v[3] + b0.w, 0.f));
-          store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, c0 + 4, fmaxf(v[4] + b1.x, 0.f), fmaxf(v[5] + b1.y, 0.f),
+          store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, fmaxf(v[4] + b1.x, 0.f), fmaxf(v[5] + b1.y, 0.f),
                                                 fmaxf(v[6] + b1.z, 0.f), fmaxf(v[7] + b1.w, 0.f));
-        }
+        });
         fence_proxy_async();
         umma::fence_before_sync();
         group_sync(cx.g);
@@ -217,16 +233,15 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
         const float* bL = cx.sRes + C::off_bl(c);
 #pragma unroll
         for (int j = 0; j < C::OUTP_MAX; ++j) o[j] = j < OUTP ? bL[j] : 0.f;
-#pragma unroll 1
-        for (int c0 = 0; c0 < T::KP; c0 += 8) {
-          float v[8];
-          umma::ld8(cx.tacc + c0, v);
-          umma::wait_ld();
+        tc_batches<NG8, true>(cx.tacc, [&](int, int, int g8, float (&v)[8]) {
+          const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * g8);
+          const float4 b1 = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
+          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const int kk = c0 + i;
+            const int kk = 8 * g8 + i;
             if (kk < C::H) {
-              const float h = fmaxf(v[i] + bias[kk], 0.f);
+              const float h = fmaxf(v[i] + bb[i], 0.f);
 #pragma unroll
               for (int j = 0; j < C::OUTP_MAX; j += 4)
                 if (j < OUTP) {
@@ -236,7 +251,7 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
                 }
             }
           }
-        }
+        });
       }
     }
     if (c == 0) {

@@ -123,6 +123,15 @@ __device__ __forceinline__ void tc_publish(TcGroupCtx& cx) {   // smem image wri
   group_sync(cx.g);
 }
 
+// ReLU masks: 8 bits per group of 8 columns, 4 groups per word, 4 words per layer -- kept in registers and
+// addressed with selects so that the column loops can stay rolled (instruction-cache footprint)
+__device__ __forceinline__ uint32_t sel4(const uint32_t (&m)[4], int q) {
+  return q == 0 ? m[0] : (q == 1 ? m[1] : (q == 2 ? m[2] : m[3]));
+}
+__device__ __forceinline__ void or4(uint32_t (&m)[4], int q, uint32_t w) {
+  m[0] |= q == 0 ? w : 0u; m[1] |= q == 1 ? w : 0u; m[2] |= q == 2 ? w : 0u; m[3] |= q == 3 ? w : 0u;
+}
+
 // One stage of the reverse sweep for the group's tile (mirrors vjp_rhs_tile of node_bwd.cuh).
 // img: global image block of this (tile, stage evaluation) or nullptr (no parameter gradients wanted).
 template <class C>
@@ -133,11 +142,13 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
   using G = TcBwdGeom<C>;
   using IM = ImgMap<C>;
   constexpr int NG8 = T::KP / 8;
+  static_assert(NG8 <= 16, "mask words");
   const int lt = cx.lt;
+  const bool wimg = img != nullptr;
   float dxa[C::INP0];
 #pragma unroll
   for (int d = 0; d < C::INP0; ++d) dxa[d] = 0.f;
-  if (img != nullptr) {   // stage input image (shared by the chains): [x | const | 1 | 0...]
+  if (wimg) {   // stage input image (shared by the chains): [x | const | 1 | 0...]
     float v0[8], v1[8];
 #pragma unroll
     for (int d = 0; d < 16; ++d) {
@@ -163,9 +174,8 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
     {
       const float* Wt0 = cx.sRes + C::off_wt0(c);
       const float* b0 = cx.sRes + C::off_b0(c);
-#pragma unroll
-      for (int g8 = 0; g8 < NG8; ++g8) {
-        float v[8];
+      unsigned char* ia = img + IM::off_act(c, 1);
+      tc_batches<NG8, false>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
         const float4 ba = *reinterpret_cast<const float4*>(b0 + 8 * g8);
         const float4 bb = *reinterpret_cast<const float4*>(b0 + 8 * g8 + 4);
         v[0] = ba.x; v[1] = ba.y; v[2] = ba.z; v[3] = ba.w; v[4] = bb.x; v[5] = bb.y; v[6] = bb.z; v[7] = bb.w;
@@ -180,12 +190,15 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
         uint32_t bits = 0u;
 #pragma unroll
         for (int i = 0; i < 8; ++i) { v[i] = fmaxf(v[i], 0.f); bits |= (v[i] > 0.f ? 1u : 0u) << i; }
-        mk[0][g8 >> 2] |= bits << ((g8 & 3) * 8);
+        or4(mk[0], q, bits << (8 * u));
         store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
         store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
-        if (img != nullptr) store_act_img<C>(img + IM::off_act(c, 1), lt, 8 * g8, v);
-      }
-      if (img != nullptr) finish_act_img<C>(img + IM::off_act(c, 1), lt);
+        if (wimg) {
+          if (C::H >= 8 * g8 && C::H < 8 * g8 + 8) v[C::H & 7] = 1.f;
+          store_img8(ia, lt, 8 * g8, v);
+        }
+      });
+      if (wimg) finish_act_img<C>(ia, lt);
     }
     tc_publish(cx);
     // cotangent of the chain output
@@ -201,7 +214,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
 #pragma unroll
         for (int j = 0; j < C::NU; ++j) dout[i * C::NU + j] = dk[i] * cst[j];
     }
-    if (img != nullptr) {
+    if (wimg) {
       float v0[8], v1[8];
 #pragma unroll
       for (int o = 0; o < 16; ++o) {
@@ -217,30 +230,37 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
       if (l <= n) {
         tc_layer_mma<C, G::NSLOT>(cx);
         const float* bias = cx.sRes + C::off_bh(c, l);
-        const float* WnL = cx.sRes + C::off_wnl(c);
-        const float* WtL = cx.sRes + C::off_wtl(c);
+        unsigned char* ia = img + IM::off_act(c, l + 1);
+        if (l < n) {
+          tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
+            const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
+            const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
+            v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
+            uint32_t bits = 0u;
 #pragma unroll
-        for (int g8 = 0; g8 < NG8; ++g8) {
-          float v[8];
-          umma::ld8(cx.tacc + 8 * g8, v);
-          umma::wait_ld();
-          const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
-          const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
-          v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
-          uint32_t bits = 0u;
-#pragma unroll
-          for (int i = 0; i < 8; ++i) { v[i] = fmaxf(v[i], 0.f); bits |= (v[i] > 0.f ? 1u : 0u) << i; }
-          mk[l][g8 >> 2] |= bits << ((g8 & 3) * 8);
-          if (l < n) {
+            for (int i = 0; i < 8; ++i) { v[i] = fmaxf(v[i], 0.f); bits |= (v[i] > 0.f ? 1u : 0u) << i; }
+            or4(mk[l], q, bits << (8 * u));
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
-            if (img != nullptr) store_act_img<C>(img + IM::off_act(c, l + 1), lt, 8 * g8, v);
-          } else {
-            // last hidden activation: forward value of g(x) (action gradient) and d_{n+1} = relu' * WL^T dOut
+            if (wimg) {
+              if (C::H >= 8 * g8 && C::H < 8 * g8 + 8) v[C::H & 7] = 1.f;
+              store_img8(ia, lt, 8 * g8, v);
+            }
+          });
+        } else {
+          // last hidden activation: forward value of g(x) (action gradient) and d_{n+1} = relu' * WL^T dOut
+          const float* WnL = cx.sRes + C::off_wnl(c);
+          const float* WtL = cx.sRes + C::off_wtl(c);
+          unsigned char* id = img + IM::off_del(c, n + 1);
+          tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
+            const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
+            const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
+            v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
             float dl[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               const int kk = 8 * g8 + i;
+              v[i] = fmaxf(v[i], 0.f);
               float acc = 0.f;
               if (kk < C::H) {
                 if (c == 1) {
@@ -258,15 +278,16 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
               }
               dl[i] = v[i] > 0.f ? acc : 0.f;
             }
-            if (img != nullptr) {
-              store_act_img<C>(img + IM::off_act(c, n + 1), lt, 8 * g8, v);
-              store_img8(img + IM::off_del(c, n + 1), lt, 8 * g8, dl);
-            }
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, dl[0], dl[1], dl[2], dl[3]);
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, dl[4], dl[5], dl[6], dl[7]);
-          }
+            if (wimg) {
+              store_img8(id, lt, 8 * g8, dl);
+              if (C::H >= 8 * g8 && C::H < 8 * g8 + 8) v[C::H & 7] = 1.f;
+              store_img8(ia, lt, 8 * g8, v);
+            }
+          });
         }
-        if (img != nullptr) finish_act_img<C>(img + IM::off_act(c, l + 1), lt);
+        if (wimg) finish_act_img<C>(ia, lt);
         tc_publish(cx);
       }
     }
@@ -283,15 +304,12 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
       if (l <= n) {
         tc_layer_mma<C, G::NSLOT>(cx);
         const float* Wn0 = cx.sRes + C::off_wn0(c);
-#pragma unroll
-        for (int g8 = 0; g8 < NG8; ++g8) {
-          float v[8];
-          umma::ld8(cx.tacc + 8 * g8, v);
-          umma::wait_ld();
-          const uint32_t bits = (mk[l - 1][g8 >> 2] >> ((g8 & 3) * 8)) & 0xFFu;
+        unsigned char* id = img + IM::off_del(c, l);
+        tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
+          const uint32_t bits = (sel4(mk[l - 1], q) >> (8 * u)) & 0xFFu;
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[i] = ((bits >> i) & 1u) ? v[i] : 0.f;
-          if (img != nullptr) store_img8(img + IM::off_del(c, l), lt, 8 * g8, v);
+          if (wimg) store_img8(id, lt, 8 * g8, v);
           if (l > 1) {
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
@@ -309,7 +327,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
               }
             }
           }
-        }
+        });
         if (l > 1) tc_publish(cx);
       }
     }
