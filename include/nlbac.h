@@ -216,10 +216,15 @@ int nlbac_adam_step(float* param, const float* grad, float* exp_avg, float* exp_
                     float beta1, float beta2, float eps, void* stream);
 int nlbac_soft_update(float* target, const float* source, int64_t n, float tau, void* stream);
 
-/* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 TF32 tile.
- * mode 0: D[t][j] = sum_k X[t][k] Y[j][k];  mode 1: D[t][k] = sum_j X[t][j] Y[j][k];  mode 2: D[j][k] = sum_t X[t][j] Y[t][k].
- * X [128,104]; Y [104,104] (modes 0,1) or [128,104] (mode 2); D [128,112] (columns/rows >= 104 are padding). */
+/* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 tile.
+ * mode 0 (kind::tf32, both operands K-major):   D[t][j] = sum_k X[t][k] Y[j][k],  X [128,104], Y [104,104];
+ * mode 1 (kind::f16 on bf16 images, MN-major):  D[j][k] = sum_t X[t][j] Y[t][k],  X, Y [128,104].
+ * D [128,112] fp32 (rows/columns >= 104 are padding). */
 int nlbac_umma_selftest(int mode, const float* X, const float* Y, float* D, void* stream);
+
+/* Diagnostic descriptor sweep (tools/umma_sweep.py): params10 = {a_mn, b_mn, lboA, sboA, stepA, lboB, sboB, stepB,
+ * nsteps, operand_kind (0 fp32 row-owner images, 1 fp32 weight image for B, 2 bf16 row-owner images)}. */
+int nlbac_umma_probe(const int* params10, const float* X, const float* Y, float* D, void* stream);
 
 /* Measured-peak helper for the roofline: register-resident FP32 FMA loop.  Returns the number of
  * FLOPs one launch executes in *flops; the caller times it with CUDA events. */

@@ -1,4 +1,4 @@
-// Tensor-core (tcgen05, kind::tf32) tier of the NODE solve: C ABI entry points + a UMMA layout self-test.
+// tcgen05 operand-layout self-test and descriptor probe (the tensor-core NODE entry points live in node_abi.cu).
 #include "../../include/nlbac.h"
 #include "umma.cuh"
 #include <cstring>
@@ -7,10 +7,12 @@
 namespace nlbac {
 
 // ------------------------------------------------------------------------------------------------
-// Self-test of the three operand interpretations the NODE kernels rely on (umma.cuh):
-//   mode 0  D[t][j] = sum_k X[t][k] W[j][k]   A K-major,  B K-major   (forward hidden layer)
-//   mode 1  D[t][k] = sum_j X[t][j] W[j][k]   A K-major,  B MN-major  (dX: same weight image)
-//   mode 2  D[j][k] = sum_t X[t][j] Y[t][k]   A MN-major, B MN-major  (dW: same activation images)
+// Self-test of the two operand interpretations the tensor-core NODE kernels rely on (umma.cuh):
+//   mode 0  kind::tf32  D[t][j] = sum_k X[t][k] W[j][k]   A K-major,  B K-major   (hidden layer; the dX product uses
+//                                                                                  the same form on a transposed image)
+//   mode 1  kind::f16   D[j][k] = sum_t X[t][j] Y[t][k]   A MN-major, B MN-major  (dW over bf16 row-owner images)
+// kind::tf32 has no MN-major form without the 128-byte swizzle (measured: all-zero accumulators for every LBO/SBO
+// assignment, tools/umma_sweep.py), which is why dX reads a transposed weight image and dW runs in bf16.
 // X, Y: [128][104] row-major; W: [104][104] row-major; D: [128][112] row-major.
 // ------------------------------------------------------------------------------------------------
 constexpr int ST_ROWS = 128, ST_K = 104, ST_N = 112;
@@ -27,12 +29,17 @@ __global__ void __launch_bounds__(128, 1) umma_selftest_kernel(int mode, const f
   const int tid = threadIdx.x, warp = tid / 32;
   for (int i = tid; i < 64 * ST_XCH / 4; i += 128) reinterpret_cast<float*>(sm)[i] = 0.f;
   __syncthreads();
-  // A: row-owner image of X (chunk stride 2048)
-  for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufA + umma::tile_off(tid, c, ST_XCH)) = X[tid * ST_K + c];
-  if (mode == 2) {
-    for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_XCH)) = Y[tid * ST_K + c];
-  } else if (tid < ST_K) {  // weight image: rows j (112 per chunk), columns k
-    for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_WCH)) = Y[tid * ST_K + c];
+  if (mode == 0) {
+    // A: row-owner fp32 image of X (chunk stride 2048); B: weight image, rows j (112 per chunk), columns k
+    for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufA + umma::tile_off(tid, c, ST_XCH)) = X[tid * ST_K + c];
+    if (tid < ST_K)
+      for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_WCH)) = Y[tid * ST_K + c];
+  } else {
+    // both operands: row-owner bf16 images (8 features per 16-byte chunk)
+    for (int c = 0; c < ST_K; ++c) {
+      *reinterpret_cast<__nv_bfloat16*>(bufA + umma::tile_off16(tid, c, ST_XCH)) = __float2bfloat16(X[tid * ST_K + c]);
+      *reinterpret_cast<__nv_bfloat16*>(bufB + umma::tile_off16(tid, c, ST_XCH)) = __float2bfloat16(Y[tid * ST_K + c]);
+    }
   }
   if (tid == 0) {
     mbar_init(bar, 1);
@@ -51,15 +58,10 @@ __global__ void __launch_bounds__(128, 1) umma_selftest_kernel(int mode, const f
       for (int ks = 0; ks < ST_K / 8; ++ks)
         umma::mma_tf32(tbase, umma::make_desc(a0 + ks * 2 * ST_XCH, ST_XCH, 128),
                        umma::make_desc(b0 + ks * 2 * ST_WCH, ST_WCH, 128), idesc, ks > 0);
-    } else if (mode == 1) {
-      const uint32_t idesc = umma::make_idesc_tf32(128, ST_N, false, true);
-      for (int ks = 0; ks < ST_K / 8; ++ks)
-        umma::mma_tf32(tbase, umma::make_desc(a0 + ks * 2 * ST_XCH, ST_XCH, 128),
-                       umma::make_desc(b0 + ks * 128, 128, ST_WCH), idesc, ks > 0);
     } else {
-      const uint32_t idesc = umma::make_idesc_tf32(128, ST_N, true, true);
-      for (int ks = 0; ks < ST_ROWS / 8; ++ks)
-        umma::mma_tf32(tbase, umma::make_desc(a0 + ks * 128, 128, ST_XCH), umma::make_desc(b0 + ks * 128, 128, ST_XCH),
+      const uint32_t idesc = umma::make_idesc_bf16(128, ST_N, true, true);
+      for (int ks = 0; ks < ST_ROWS / 16; ++ks)  // K = 16 rows (two 8-row core matrices, 256 B) per MMA
+        umma::mma_bf16(tbase, umma::make_desc(a0 + ks * 256, 128, ST_XCH), umma::make_desc(b0 + ks * 256, 128, ST_XCH),
                        idesc, ks > 0);
     }
     umma::commit(bar);
@@ -78,6 +80,7 @@ __global__ void __launch_bounds__(128, 1) umma_selftest_kernel(int mode, const f
   if (warp == 0) umma::tmem_dealloc(tbase, 128);
 }
 
+// Descriptor sweep used to establish the table above (tools/umma_sweep.py); diagnostic only.
 struct ProbeArgs { int a_mn, b_mn, lboA, sboA, stepA, lboB, sboB, stepB, nsteps, b_is_weight; };
 __global__ void __launch_bounds__(128, 1) umma_probe_kernel(ProbeArgs p, const float* __restrict__ X,
                                                            const float* __restrict__ Y, float* __restrict__ D) {
@@ -145,7 +148,7 @@ using namespace nlbac;
 extern "C" {
 
 int nlbac_umma_selftest(int mode, const float* X, const float* Y, float* D, void* stream) {
-  NLBAC_REQUIRE(mode >= 0 && mode <= 2 && X && Y && D, "bad arguments");
+  NLBAC_REQUIRE(mode >= 0 && mode <= 1 && X && Y && D, "bad arguments");
   NLBAC_CUDA(cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
   umma_selftest_kernel<<<1, 128, ST_SMEM, (cudaStream_t)stream>>>(mode, X, Y, D);
   NLBAC_CUDA(cudaGetLastError());

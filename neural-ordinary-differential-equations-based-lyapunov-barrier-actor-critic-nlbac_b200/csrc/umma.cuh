@@ -4,11 +4,13 @@
 // Operand layout used throughout (no swizzle, "interleave" canonical form, 32-bit elements):
 //   a tile X[r][c] (r = row held by its owner thread, c = feature) is stored as 16-byte chunks
 //       byte(r, c) = (c / 4) * CHUNK + (r / 8) * 128 + (r % 8) * 16 + (c % 4) * 4,     CHUNK = ROWS * 16
-//   so one "core matrix" (8 rows x 16 bytes) is 128 contiguous bytes.  The SAME bytes are
-//     * a K-major operand with  rows = M/N, c = K:   SBO = 128   (next 8 rows),   LBO = CHUNK (next 4 k)
-//       one MMA consumes K = 8 -> advance the start address by 2 * CHUNK per k-step;
-//     * an MN-major operand with c = M/N, rows = K:  SBO = CHUNK (next 4 m/n),    LBO = 128   (next 8 k)
-//       one MMA consumes K = 8 rows -> advance the start address by 128 per k-step.
+//   so one "core matrix" (8 rows x 16 bytes) is 128 contiguous bytes.  As a K-major kind::tf32 operand
+//   (rows = M/N, c = K): SBO = 128 (next 8 rows), LBO = CHUNK (next 4 k); one MMA consumes K = 8 -> advance the
+//   start address by 2 * CHUNK per k-step.  kind::tf32 has NO MN-major form in this layout (it needs the 128-byte
+//   swizzle; measured all-zero accumulators), so products that contract over the row index use 16-bit images:
+//       byte16(r, c) = (c / 8) * CHUNK + (r / 8) * 128 + (r % 8) * 16 + (c % 8) * 2
+//   read by kind::f16 as an MN-major operand (c = M/N, rows = K): LBO = 128 (next 8 k), SBO = CHUNK (next 8 m/n),
+//   one MMA consumes K = 16 rows -> advance by 256 per k-step.
 #pragma once
 #include "common.cuh"
 

@@ -35,7 +35,7 @@ def _worker(rank, world, port, q):
     flat = torch.cat([g.reshape(-1) for g in grads])
     dist.all_reduce(flat)                     # the one collective of the path
     if rank == 0:
-        q.put(flat)
+        q.put(flat.tolist())              # plain floats: a tensor would travel as an fd the exiting worker may close
     dist.barrier()
     dist.destroy_process_group()
 
@@ -60,7 +60,7 @@ def test_two_rank_allreduce_matches_single_rank_gradient():
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     for p in procs:
         p.start()
-    got = q.get(timeout=240)
+    got = torch.tensor(q.get(timeout=240))
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0

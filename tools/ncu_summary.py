@@ -1,0 +1,27 @@
+"""Summarise an .ncu-rep (raw page) into the handful of counters the roofline discussion uses."""
+import csv, subprocess, sys
+KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+        "launch__shared_mem_per_block_dynamic", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+        "smsp__issue_active.avg.pct_of_peak_sustained_active", "smsp__inst_executed.sum",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_elapsed",
+        "sm__ops_path_tensor_op_utchmma_src_tf32_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed",
+        "sm__ops_path_tensor_op_utchmma_src_bf16_dst_fp32_sparsity_off.avg.pct_of_peak_sustained_elapsed",
+        "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active",
+        "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum.pct_of_peak_sustained_elapsed",
+        "dram__bytes_read.sum", "dram__bytes_write.sum", "dram__throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_bytes.sum", "smsp__warps_active.avg.per_cycle_active"]
+def main(path):
+    raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(raw.splitlines()))
+    h, u, v = rows[0], rows[1], rows[2]
+    print("# %s" % path)
+    print("kernel:", v[h.index("Kernel Name")])
+    for i, n in enumerate(h):
+        if n in KEYS or ("issue_stalled" in n and n.endswith("per_issue_active.ratio")):
+            try:
+                if "issue_stalled" in n and float(v[i]) < 0.05: continue
+            except ValueError: pass
+            print("%-100s %-12s %s" % (n, u[i], v[i]))
+if __name__ == "__main__":
+    for p in sys.argv[1:]: main(p)
