@@ -1,6 +1,9 @@
 #!/usr/bin/env python
 """bench.py — neural-ODE trajectory-steps/sec (forward + backward) on B200.
 
+Headline tier: --precision tf32 (tensor cores, gradients within 1e-2 of fp64 — measured 3.4e-3);
+the exact FP32 tier (1e-5) is measured in the same run and reported under "fp32_tier".
+
 Workload (BASELINE.json configs[4], the configuration the metric is quoted on): M = 2^20 Unicycle-shaped
 trajectories PER GPU x 20 rk4 (3/8-rule) steps, forward + backward with cotangent = ones on the final
 state, parameter gradients produced (and all-reduced over NCCL when N > 1).  One "step" = one such
@@ -25,6 +28,9 @@ import torch  # noqa: E402
 FLOP_EVAL_FWD = {"U": 103012, "P": 106024}      # SURVEY.md App. C (1 MAC = 2 FLOP)
 N_STEPS = 20
 DT = 0.02
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at the bench size, from the
+# `ncu --set full` capture committed under profiles/ (r1_ncu_bench_*.txt); None until captured for that tier
+NCU_TRAFFIC = {"fp32": None, "tf32": 18.96e9, "3xtf32": None}   # tf32: profiles/r1_ncu_bench_tc_tf32.txt (0.49 GB read + 18.47 GB written)
 
 
 def parse():
@@ -35,8 +41,9 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log2m", type=int, default=20, help="log2 of trajectories per GPU")
     ap.add_argument("--env", default="U", choices=["U", "P"])
-    ap.add_argument("--precision", default="fp32", choices=["fp32", "tf32", "3xtf32"],
-                    help="forward tier: fp32 FMA, tcgen05 TF32 (1e-2 tier) or 3xTF32 (fp32-class); backward is FP32")
+    ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32", "3xtf32"],
+                    help="tf32: tcgen05 kind::tf32 forward + reverse sweep, dW in bf16 (the 1e-2 tier of north_star); "
+                         "fp32: exact FP32 FMA path (1e-5 tier); 3xtf32: split-TF32 forward (fp32-class) + FP32 backward")
     ap.add_argument("--cpu-sample", type=int, default=1024, help="trajectories in the CPU baseline sample")
     return ap.parse_args()
 
@@ -139,6 +146,32 @@ def fp32_peak_tflops(nlbac_b200):
     return best
 
 
+def kernel_timing(nlbac_b200, enable):
+    nlbac_b200._lib.check(nlbac_b200._lib.lib().nlbac_kernel_timing(1 if enable else 0), "kernel_timing")
+
+
+def kernel_timing_read(nlbac_b200):
+    import ctypes
+    ms, n = (ctypes.c_double * 4)(), (ctypes.c_int * 4)()
+    nlbac_b200._lib.check(nlbac_b200._lib.lib().nlbac_kernel_timing_read(ms, n), "kernel_timing_read")
+    return list(ms), list(n)
+
+
+def image_bytes_per_tile_eval(nlbac_b200, model, D, method="rk4"):
+    """bf16 image bytes pass A writes (and pass B reads) per 128-trajectory tile per stage evaluation."""
+    import ctypes
+    from nlbac_b200.odeint import describe, METHODS
+    L = nlbac_b200._lib.lib()
+    desc, _ = describe(model, D)
+    out = []
+    for B in (128, 256):
+        nb = ctypes.c_size_t()
+        nlbac_b200._lib.check(L.nlbac_node_tc_bwd_workspace_bytes(ctypes.byref(desc), B, 2, 2, METHODS[method], 1,
+                                                                  ctypes.byref(nb)), "tc_ws")
+        out.append(nb.value)
+    return (out[1] - out[0]) / 4.0           # one rk4 step = 4 stage evaluations
+
+
 def run_ours(args):
     import nlbac_b200
     import torch.distributed as dist
@@ -162,10 +195,10 @@ def run_ours(args):
     y0_host = y0.cpu().pin_memory()
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
 
-    def fwd_bwd(y, timers=None):
+    def fwd_bwd(y, timers=None, precision=args.precision):
         if timers is not None:
             timers[0].record()
-        sol = nlbac_b200.odeint(model, y, t, method="rk4", atol=1e-7, rtol=1e-5, precision=args.precision)
+        sol = nlbac_b200.odeint(model, y, t, method="rk4", atol=1e-7, rtol=1e-5, precision=precision)
         loss = sol[-1][:, :n_s].sum()
         if timers is not None:
             timers[1].record()
@@ -188,6 +221,7 @@ def run_ours(args):
     sampler = ClockSampler(local)
     sampler.start()
     timers = [[ev(), ev(), ev()] for _ in range(args.steps)]
+    kernel_timing(nlbac_b200, True)
     e0, e1 = ev(), ev()
     e0.record()
     for i in range(args.steps):
@@ -195,6 +229,8 @@ def run_ours(args):
     e1.record()
     barrier()
     sampler.stop_flag = True
+    k_ms, k_n = kernel_timing_read(nlbac_b200)      # summed over the K timed steps, per kernel slot
+    kernel_timing(nlbac_b200, False)
     ms_total = e0.elapsed_time(e1)
     fwd_ms = sum(tm[0].elapsed_time(tm[1]) for tm in timers) / args.steps
     bwd_ms = sum(tm[1].elapsed_time(tm[2]) for tm in timers) / args.steps
@@ -212,26 +248,72 @@ def run_ours(args):
     barrier()
     e2e_ms = h0.elapsed_time(h1)
 
-    tms = torch.tensor([ms_total, e2e_ms], device=dev, dtype=torch.float64)
+    # the exact FP32 tier on the same workload (1 warm-up + 2 timed passes), reported beside the headline
+    fp32_ms = 0.0
+    if args.precision != "fp32":
+        fwd_bwd(y0, precision="fp32")
+        barrier()
+        f0, f1 = ev(), ev()
+        f0.record()
+        for _ in range(2):
+            fwd_bwd(y0, precision="fp32")
+        f1.record()
+        barrier()
+        fp32_ms = f0.elapsed_time(f1) / 2
+
+    tms = torch.tensor([ms_total, e2e_ms, fp32_ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms = tms.tolist()
+    ms_total, e2e_ms, fp32_ms = tms.tolist()
     peak32 = fp32_peak_tflops(nlbac_b200) if rank == 0 else 0.0
     if rank == 0:
         traj_steps = float(world) * M * N_STEPS
         ms_step = ms_total / args.steps
         value = traj_steps / (ms_step * 1e-3)
-        fl = flop_per_traj_step(env)
-        bwd_flops = M * N_STEPS * fl * 2.0 / 3.0
-        achieved = bwd_flops / (bwd_ms * 1e-3) / 1e12
+        K = args.steps
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(
             os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+        evals = M * N_STEPS * 4.0                               # stage evaluations per pass (rk4)
+        sweep_ms, sweep_n = k_ms[1] / K, k_n[1] // K            # reverse sweep: the dominant kernel in both tiers
+        if args.precision == "tf32":
+            # algorithmic work of pass A = the dX products (1 x forward FLOPs); it also re-computes the forward
+            # hidden layers from the stage checkpoints (another 1 x), reported as "executed"
+            sweep_flops, executed = evals * FLOP_EVAL_FWD[env], evals * 2 * FLOP_EVAL_FWD[env]
+            bf16 = peaks.get("bf16_tflops_sustained") or 1403.6
+            peak, peak_src = bf16 / 2.0, (
+                "MEASURED_PEAKS.json bf16_tflops_sustained / 2 (kind::tf32 issues at half the bf16 rate; sustained "
+                "figure because the kernel is timed inside a long step)" if peaks else
+                "B200_PROFILING.md fallback: sustained bf16 1403.6 / 2")
+            roof = {"bound": "tensor", "kernel": "node_tc_bwd_kernel (pass A: tcgen05 TF32 recompute + dX sweep)"}
+            img = image_bytes_per_tile_eval(nlbac_b200, model, 5 if env == "U" else 8)
+            dw_bytes = (M / 128.0) * N_STEPS * 4 * img
+            hbm = peaks.get("hbm_gbs") or 6453.1
+            dw_gbs = dw_bytes / (k_ms[2] / K * 1e-3) / 1e9 if k_ms[2] else None
+            secondary = {"kernel": "node_tc_dw_kernel (pass B: bf16 dW = d^T a over the HBM images)", "bound": "hbm",
+                         "achieved": dw_gbs, "peak": hbm, "unit": "GB/s", "frac": dw_gbs / hbm if dw_gbs else None,
+                         "algorithmic_bytes_per_pass": dw_bytes, "ms_per_pass": k_ms[2] / K,
+                         "launches_per_pass": k_n[2] // K}
+        else:
+            # algorithmic work = dX + dW (2 x forward FLOPs); the kernel also re-computes the forward (3 x executed)
+            sweep_flops, executed = evals * 2 * FLOP_EVAL_FWD[env], evals * 3 * FLOP_EVAL_FWD[env]
+            peak, peak_src = peak32, ("measured live: register-resident FFMA loop (nlbac_fp32_peak_probe); "
+                                      "MEASURED_PEAKS.json has no FP32-FMA figure")
+            roof = {"bound": "fp32_fma", "kernel": "node_bwd_kernel"}
+            secondary = None
+        achieved = sweep_flops / (sweep_ms * 1e-3) / 1e12 if sweep_ms else None
+        roof.update({"achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+                     "frac": achieved / peak if achieved and peak else None, "traffic": NCU_TRAFFIC.get(args.precision),
+                     "peak_source": peak_src, "algorithmic_flops_per_pass": sweep_flops,
+                     "executed_tflops": executed / (sweep_ms * 1e-3) / 1e12 if sweep_ms else None,
+                     "ms_per_pass": sweep_ms, "launches_per_pass": sweep_n,
+                     "share_of_step": sweep_ms / ms_step if ms_step else None})
         cores = os.cpu_count()
         cpu_val, cpu_ms = cpu_reference_run(env, args.cpu_sample, 2, 1, cores) if world == 1 else (None, None)
         line = {
             "metric": "neural-ODE trajectory-steps/sec (fwd+bwd)", "value": value, "unit": "trajectory-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp32": "f32", "tf32": "tf32", "3xtf32": "f32 (3xtf32 fwd)"}[args.precision], "data": "synthetic",
             "config": {"workload": "config5: 2^%d %s-shaped trajectories per GPU x 20 rk4(3/8) steps, fwd+bwd, "
                                    "t=0.02*arange(21), cotangent ones on final state, d-theta all-reduced" % (
                                        args.log2m, "Unicycle" if env == "U" else "PVTOL"),
@@ -239,18 +321,17 @@ def run_ours(args):
                        "l2": "per-step working set (stage checkpoints + outputs, %.1f GB) exceeds the 126 MB L2; no explicit flush" % (
                            M * (N_STEPS * 4 * n_s + (N_STEPS + 1) * (n_s + 2) * 2) * 4 / 1e9)},
             "fwd_ms": fwd_ms, "bwd_ms": bwd_ms,
-            "roofline": {"bound": "fp32_fma", "kernel": "node_bwd_kernel", "achieved": achieved, "peak": peak32,
-                         "unit": "TFLOP/s", "frac": achieved / peak32 if peak32 else None, "traffic": None,
-                         "peak_source": "measured live: register-resident FFMA loop (nlbac_fp32_peak_probe); "
-                                        "MEASURED_PEAKS.json has no FP32-FMA figure",
-                         "algorithmic_flops_per_launch": bwd_flops,
-                         "bf16_tensor_peak_measured_tflops": peaks.get("bf16_tflops_sustained")},
+            "kernel_ms_per_step": {"fwd_solve": k_ms[0] / K, "reverse_sweep": k_ms[1] / K, "dw_gemm": k_ms[2] / K,
+                                   "grad_fold": k_ms[3] / K},
+            "roofline": roof, "roofline_secondary": secondary,
+            "fp32_tier": {"value": traj_steps / (fp32_ms * 1e-3), "ms_per_step": fp32_ms,
+                          "note": "exact FP32 FMA path (1e-5 tier), same workload, 2 timed passes"} if fp32_ms else None,
             "cpu_baseline": {"value": cpu_val, "unit": "trajectory-steps/s", "cores": cores, "kind": "port",
                              "sample": "%d trajectories x 20 rk4 steps fwd+bwd, PyTorch CPU fp32, %.0f ms per pass" % (
                                  args.cpu_sample, cpu_ms)} if cpu_val else None,
             "e2e": {"value": traj_steps / (e2e_ms / args.steps * 1e-3), "unit": "trajectory-steps/s",
                     "h2d_bytes_per_step": y0_host.numel() * 4, "d2h_bytes_per_step": 4 + flat_h.numel() * 4},
-            "gpu_launches": 3 * args.steps,
+            "gpu_launches": int(sum(k_n)),
             "clocks": sampler.summary(),
         }
         print(json.dumps(line))

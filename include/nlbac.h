@@ -226,6 +226,13 @@ int nlbac_umma_selftest(int mode, const float* X, const float* Y, float* D, void
  * nsteps, operand_kind (0 fp32 row-owner images, 1 fp32 weight image for B, 2 bf16 row-owner images)}. */
 int nlbac_umma_probe(const int* params10, const float* X, const float* Y, float* D, void* stream);
 
+/* Opt-in per-kernel timing of the NODE path for bench.py's roofline: while enabled, every launch of the solve
+ * kernels is bracketed by CUDA events on the launching stream.  nlbac_kernel_timing_read waits for them and returns
+ * summed milliseconds and launch counts per slot {0 forward solve, 1 reverse sweep, 2 dW GEMM, 3 gradient fold},
+ * then clears the records.  Not thread-safe; intended for measurement only. */
+int nlbac_kernel_timing(int enable);
+int nlbac_kernel_timing_read(double* ms4, int* launches4);
+
 /* Measured-peak helper for the roofline: register-resident FP32 FMA loop.  Returns the number of
  * FLOPs one launch executes in *flops; the caller times it with CUDA events. */
 int nlbac_fp32_peak_probe(int iters, float* sink, double* flops, void* stream);

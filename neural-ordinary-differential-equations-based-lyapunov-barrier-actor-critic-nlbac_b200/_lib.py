@@ -116,6 +116,8 @@ def _declare(lib):
     lib.nlbac_adam_step.argtypes = [vp, vp, vp, vp, i64, c.c_int, c.c_float, c.c_float, c.c_float, c.c_float, vp]
     lib.nlbac_soft_update.argtypes = [vp, vp, i64, c.c_float, vp]
     lib.nlbac_umma_selftest.argtypes = [c.c_int, vp, vp, vp, vp]
+    lib.nlbac_kernel_timing.argtypes = [c.c_int]
+    lib.nlbac_kernel_timing_read.argtypes = [c.POINTER(c.c_double), c.POINTER(c.c_int)]
     lib.nlbac_umma_probe.argtypes = [c.POINTER(c.c_int), vp, vp, vp, vp]
     lib.nlbac_fp32_peak_probe.argtypes = [c.c_int, vp, c.POINTER(c.c_double), vp]
     lib.nlbac_fma_shape_probe.argtypes = [c.c_int, c.c_int, vp, c.POINTER(c.c_double), vp]

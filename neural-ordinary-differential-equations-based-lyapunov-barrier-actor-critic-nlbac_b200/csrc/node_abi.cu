@@ -33,6 +33,30 @@ static int sm_count() {
   return n;
 }
 
+// Opt-in per-kernel timing (nlbac_kernel_timing): CUDA events recorded on the launching stream around each launch
+// of the NODE kernels, summed per slot when read.  Slots: 0 forward solve, 1 reverse sweep, 2 dW GEMM, 3 fold.
+struct KTimer {
+  bool on = false;
+  struct Rec { int slot; cudaEvent_t e0, e1; };
+  std::vector<Rec> recs;
+};
+static KTimer g_kt;
+struct KScope {
+  int slot; cudaStream_t st; cudaEvent_t e0 = nullptr, e1 = nullptr; bool on;
+  KScope(int slot_, cudaStream_t st_) : slot(slot_), st(st_), on(g_kt.on) {
+    if (on) {
+      on = cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
+      if (on) cudaEventRecord(e0, st);
+    }
+  }
+  ~KScope() {
+    if (on) {
+      cudaEventRecord(e1, st);
+      g_kt.recs.push_back({slot, e0, e1});
+    }
+  }
+};
+
 template <class C>
 static bool matches(const nlbac_node_desc* d) {
   return d->kind == C::KIND && d->n_s == C::NS && d->n_u == C::NU && d->n_c == C::NC && d->hidden == C::H &&
@@ -106,6 +130,7 @@ static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
   }
   const long long n_tiles = (a.B + T - 1) / T;
   const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());
+  KScope ks(0, st);
   node_fwd_kernel<C, T><<<grid, G::NT, G::SMEM_BYTES, st>>>(a);
   NLBAC_CUDA(cudaGetLastError());
   return 0;
@@ -123,6 +148,7 @@ static int launch_tc_fwd(const FwdArgs& a, cudaStream_t st) {
   const long long n_tiles = (a.B + 127) / 128;
   const long long n_pairs = (n_tiles + G::G - 1) / G::G;
   const int grid = (int)(n_pairs < sm_count() ? n_pairs : sm_count());
+  KScope ks(0, st);
   node_tc_fwd_kernel<C, SPLIT><<<grid, G::NT, G::SMEM_BYTES, st>>>(a);
   NLBAC_CUDA(cudaGetLastError());
   return 0;
@@ -158,13 +184,17 @@ static int run_tc_bwd(const BwdArgs& a, unsigned char* images, float* rep, cudaS
     ta.b = a; ta.images = images; ta.tile0 = t0; ta.n_tiles = (n_tiles - t0 < chunk) ? n_tiles - t0 : chunk;
     const long long n_pairs = (ta.n_tiles + G::G - 1) / G::G;
     const int grid = (int)(n_pairs < sm_count() ? n_pairs : sm_count());
-    node_tc_bwd_kernel<C><<<grid, G::NT, G::SMEM_BYTES, st>>>(ta);
+    {
+      KScope ks(1, st);
+      node_tc_bwd_kernel<C><<<grid, G::NT, G::SMEM_BYTES, st>>>(ta);
+    }
     NLBAC_CUDA(cudaGetLastError());
     if (images) {
       const long long items = ta.n_tiles * n_se;
       long long slabs = sm_count() / ImgMap<C>::NPAIR;
       if (slabs < 1) slabs = 1;
       if (slabs > items) slabs = items;
+      KScope ks(2, st);
       node_tc_dw_kernel<C><<<dim3((unsigned)slabs, ImgMap<C>::NPAIR), DG::NT, DG::SMEM_BYTES, st>>>(images, items, rep);
       NLBAC_CUDA(cudaGetLastError());
     }
@@ -205,6 +235,7 @@ static int launch_bwd(const BwdArgs& a, cudaStream_t st) {
   }
   const long long n_tiles = (a.B + TB - 1) / TB;
   const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());
+  KScope ks(1, st);
   node_bwd_kernel<C, TB><<<grid, G::NT, G::SMEM_BYTES, st>>>(a);
   NLBAC_CUDA(cudaGetLastError());
   return 0;
@@ -449,7 +480,8 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
       if (int rc = run_tc_bwd<C>(a, images, rep, st)) return rc;
       if (grad_params) {
         GradTable gt = build_grad_table<C>();
-        fold_grad_kernel<<<dim3(8, gt.n), 256, 0, st>>>(gt, rep, C::NGRAD, grad_params);
+        KScope ks(3, st);
+      fold_grad_kernel<<<dim3(8, gt.n), 256, 0, st>>>(gt, rep, C::NGRAD, grad_params);
         NLBAC_CUDA(cudaGetLastError());
       }
       return 0;
@@ -479,6 +511,7 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
     if (rc) return rc;
     if (grad_params) {
       GradTable gt = build_grad_table<C>();
+      KScope ks(3, st);
       fold_grad_kernel<<<dim3(8, gt.n), 256, 0, st>>>(gt, rep, C::NGRAD, grad_params);
       NLBAC_CUDA(cudaGetLastError());
     }
@@ -624,6 +657,7 @@ int nlbac_node_dopri5_bwd(const nlbac_node_desc* desc, const float* packed, cons
     if (rc) return rc;
     if (grad_params) {
       GradTable gt = build_grad_table<C>();
+      KScope ks(3, st);
       fold_grad_kernel<<<dim3(8, gt.n), 256, 0, st>>>(gt, rep, C::NGRAD, grad_params);
       NLBAC_CUDA(cudaGetLastError());
     }
@@ -638,6 +672,29 @@ int nlbac_fma_shape_probe(int variant, int iters, float* sink, double* flops, vo
   else fma_shape_kernel<1><<<blocks, threads, 0, (cudaStream_t)stream>>>(iters, sink);
   NLBAC_CUDA(cudaGetLastError());
   if (flops) *flops = 2.0 * 8 * 12 * (double)iters * blocks * threads;
+  return 0;
+}
+
+int nlbac_kernel_timing(int enable) {
+  for (auto& r : g_kt.recs) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  g_kt.recs.clear();
+  g_kt.on = enable != 0;
+  return 0;
+}
+
+int nlbac_kernel_timing_read(double* ms4, int* launches4) {
+  NLBAC_REQUIRE(ms4 && launches4, "null output");
+  for (int i = 0; i < 4; ++i) { ms4[i] = 0.0; launches4[i] = 0; }
+  for (auto& r : g_kt.recs) {
+    NLBAC_CUDA(cudaEventSynchronize(r.e1));
+    float ms = 0.f;
+    NLBAC_CUDA(cudaEventElapsedTime(&ms, r.e0, r.e1));
+    ms4[r.slot] += ms;
+    launches4[r.slot] += 1;
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+  }
+  g_kt.recs.clear();
   return 0;
 }
 

@@ -14,14 +14,16 @@ KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "la
 def main(path):
     raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
-    h, u, v = rows[0], rows[1], rows[2]
+    h, u = rows[0], rows[1]
     print("# %s" % path)
-    print("kernel:", v[h.index("Kernel Name")])
-    for i, n in enumerate(h):
-        if n in KEYS or ("issue_stalled" in n and n.endswith("per_issue_active.ratio")):
-            try:
-                if "issue_stalled" in n and float(v[i]) < 0.05: continue
-            except ValueError: pass
-            print("%-100s %-12s %s" % (n, u[i], v[i]))
+    for v in rows[2:]:
+        print("kernel:", v[h.index("Kernel Name")])
+        for i, n in enumerate(h):
+            if n in KEYS or ("issue_stalled" in n and n.endswith("per_issue_active.ratio")):
+                try:
+                    if "issue_stalled" in n and float(v[i]) < 0.05: continue
+                except ValueError: pass
+                print("%-100s %-12s %s" % (n, u[i], v[i]))
+        print()
 if __name__ == "__main__":
     for p in sys.argv[1:]: main(p)
