@@ -108,21 +108,31 @@ __device__ __forceinline__ void store_act4(unsigned char* img, int r, int c, flo
 }
 
 // Visit the accumulator row in batches of 4 x 8 columns: up to four tcgen05.ld in flight, ONE wait per batch.
-// body(q, u, g8, v): q = batch (rolled loop), u = 0..3 (unrolled), g8 = 4q + u = column group, v = 8 columns.
+// body(q, u, g8, v): q = batch (rolled loop over the full batches; the remainder is a separate, guard-free tail),
+// u = 0..3 (unrolled), g8 = 4q + u = column group, v = 8 columns.
 template <int NG8, bool LOAD, class F>
 __device__ __forceinline__ void tc_batches(uint32_t tacc, F&& body) {
+  constexpr int NFULL = NG8 / 4, REM = NG8 % 4;
 #pragma unroll 1
-  for (int q = 0; q < (NG8 + 3) / 4; ++q) {
+  for (int q = 0; q < NFULL; ++q) {
     float v[4][8];
     if (LOAD) {
 #pragma unroll
-      for (int u = 0; u < 4; ++u)
-        if (4 * q + u < NG8) umma::ld8(tacc + 8 * (4 * q + u), v[u]);
+      for (int u = 0; u < 4; ++u) umma::ld8(tacc + 8 * (4 * q + u), v[u]);
       umma::wait_ld();
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (4 * q + u < NG8) body(q, u, 4 * q + u, v[u]);
+    for (int u = 0; u < 4; ++u) body(q, u, 4 * q + u, v[u]);
+  }
+  if (REM > 0) {
+    float v[REM > 0 ? REM : 1][8];
+    if (LOAD) {
+#pragma unroll
+      for (int u = 0; u < REM; ++u) umma::ld8(tacc + 8 * (4 * NFULL + u), v[u]);
+      umma::wait_ld();
+    }
+#pragma unroll
+    for (int u = 0; u < REM; ++u) body(NFULL, u, 4 * NFULL + u, v[u]);
   }
 }
 
@@ -136,8 +146,22 @@ struct TcGroupCtx {
   uint32_t tmma;           // TMEM address of the group's accumulator tile (lane 0)
   uint32_t seq;            // ring packets consumed so far (uniform over the CTA's groups)
   uint32_t nd;             // completed hidden layers of this group (phase of `done`)
+  uint64_t adesc, wdesc;   // UMMA descriptors of the activation image and of ring slot 0 (k-step 0)
   int lt, g;
 };
+
+// The KSTEPS MMAs of one hidden layer.  Descriptors differ from k-step to k-step only in the 14-bit start address,
+// so they are formed by adding to the low word; one out-of-line copy keeps the (fully unrolled) issue sequence
+// short on the critical path without multiplying it over the call sites.
+template <class C>
+__device__ __noinline__ void tc_issue(uint32_t tmma, uint64_t ad, uint64_t wd, uint32_t acc0) {
+  using T = TcCfg<C>;
+  constexpr uint32_t idesc = umma::make_idesc_tf32(128, T::NP, false, false);
+#pragma unroll
+  for (int ks = 0; ks < T::KSTEPS; ++ks)
+    umma::mma_tf32(tmma, ad + (uint64_t)(ks * ((2 * T::ACH) >> 4)), wd + (uint64_t)(ks * ((2 * T::WCH) >> 4)), idesc,
+                   ks > 0 ? 1u : acc0);
+}
 
 // Right-hand side for the group's tile: owner thread passes x / constants, receives k = dx/dt.
 template <class C, bool SPLIT>
@@ -146,7 +170,6 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
   using T = TcCfg<C>;
   using G = TcFwdGeom<C, SPLIT>;
   const int lt = cx.lt;
-  const uint32_t idesc = umma::make_idesc_tf32(128, T::NP, false, false);
   float fo[C::outp(0)];
 #pragma unroll
   for (int c = 0; c < C::NCH; ++c) {
@@ -177,22 +200,13 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
     for (int l = 1; l <= n; ++l) {
       if (lt == 0) {  // ---- MMA issue: one thread per group ----
         umma::fence_after_sync();
-        const uint32_t a0 = smem_u32(cx.sA);
         {
           const uint32_t slot = cx.seq % G::NSLOT;
           mbar_wait(&cx.full[slot], (cx.seq / G::NSLOT) & 1);
           umma::fence_after_sync();
-          const uint32_t b0 = smem_u32(cx.sW + slot * T::W_BYTES);
-#pragma unroll 1
-          for (int ks = 0; ks < T::KSTEPS; ++ks)
-            umma::mma_tf32(cx.tmma, umma::make_desc(a0 + ks * 2 * T::ACH, T::ACH, 128),
-                           umma::make_desc(b0 + ks * 2 * T::WCH, T::WCH, 128), idesc, ks > 0);
-          if (SPLIT) {
-#pragma unroll 1
-            for (int ks = 0; ks < T::KSTEPS; ++ks)
-              umma::mma_tf32(cx.tmma, umma::make_desc(a0 + T::A_BYTES + ks * 2 * T::ACH, T::ACH, 128),
-                             umma::make_desc(b0 + ks * 2 * T::WCH, T::WCH, 128), idesc, 1);
-          }
+          const uint64_t wd = cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4));
+          tc_issue<C>(cx.tmma, cx.adesc, wd, 0u);
+          if (SPLIT) tc_issue<C>(cx.tmma, cx.adesc + (uint64_t)(T::A_BYTES >> 4), wd, 1u);
           umma::commit(&cx.empty[slot]);
         }
         if (SPLIT) {
@@ -200,11 +214,7 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
           const uint32_t slot = s2 % G::NSLOT;
           mbar_wait(&cx.full[slot], (s2 / G::NSLOT) & 1);
           umma::fence_after_sync();
-          const uint32_t b0 = smem_u32(cx.sW + slot * T::W_BYTES);
-#pragma unroll 1
-          for (int ks = 0; ks < T::KSTEPS; ++ks)
-            umma::mma_tf32(cx.tmma, umma::make_desc(a0 + ks * 2 * T::ACH, T::ACH, 128),
-                           umma::make_desc(b0 + ks * 2 * T::WCH, T::WCH, 128), idesc, 1);
+          tc_issue<C>(cx.tmma, cx.adesc, cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4)), 1u);
           umma::commit(&cx.empty[slot]);
         }
         umma::commit(cx.done);
@@ -331,6 +341,8 @@ __global__ void __launch_bounds__(TcFwdGeom<C, SPLIT>::NT, 1) node_tc_fwd_kernel
     cx.tmma = tbase + cx.g * T::TCOLS;
     cx.tacc = cx.tmma + ((uint32_t)((warp % 4) * 32) << 16);
     cx.seq = 0; cx.nd = 0;
+    cx.adesc = umma::make_desc(smem_u32(cx.sA), T::ACH, 128);
+    cx.wdesc = umma::make_desc(smem_u32(cx.sW), T::WCH, 128);
     mbar_wait(resbar, 0);
 
     for (long long it = 0; it < my_iters; ++it) {

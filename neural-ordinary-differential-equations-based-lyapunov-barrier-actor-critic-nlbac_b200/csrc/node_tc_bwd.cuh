@@ -102,12 +102,7 @@ __device__ __forceinline__ void tc_layer_mma(TcGroupCtx& cx) {
     const uint32_t slot = cx.seq % NSLOT;
     mbar_wait(&cx.full[slot], (cx.seq / NSLOT) & 1);
     umma::fence_after_sync();
-    const uint32_t a0 = smem_u32(cx.sA), b0 = smem_u32(cx.sW + slot * T::W_BYTES);
-    const uint32_t idesc = umma::make_idesc_tf32(128, T::NP, false, false);
-#pragma unroll 1
-    for (int ks = 0; ks < T::KSTEPS; ++ks)
-      umma::mma_tf32(cx.tmma, umma::make_desc(a0 + ks * 2 * T::ACH, T::ACH, 128),
-                     umma::make_desc(b0 + ks * 2 * T::WCH, T::WCH, 128), idesc, ks > 0);
+    tc_issue<C>(cx.tmma, cx.adesc, cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4)), 0u);
     umma::commit(&cx.empty[slot]);
     umma::commit(cx.done);
   }
@@ -130,6 +125,17 @@ __device__ __forceinline__ uint32_t sel4(const uint32_t (&m)[4], int q) {
 }
 __device__ __forceinline__ void or4(uint32_t (&m)[4], int q, uint32_t w) {
   m[0] |= q == 0 ? w : 0u; m[1] |= q == 1 ? w : 0u; m[2] |= q == 2 ? w : 0u; m[3] |= q == 3 ? w : 0u;
+}
+
+// bit i = (v[i] != 0) for eight ReLU outputs (v >= 0): the carry out of bits(v) + 0x7FFFFFFF, gathered by funnel shifts
+__device__ __forceinline__ uint32_t nz_bits8(const float (&v)[8]) {
+  uint32_t lo = 0u, hi = 0u;
+#pragma unroll
+  for (int i = 3; i >= 0; --i) {
+    lo = __funnelshift_l(__float_as_uint(v[i]) + 0x7FFFFFFFu, lo, 1);
+    hi = __funnelshift_l(__float_as_uint(v[i + 4]) + 0x7FFFFFFFu, hi, 1);
+  }
+  return lo | (hi << 4);
 }
 
 // One stage of the reverse sweep for the group's tile (mirrors vjp_rhs_tile of node_bwd.cuh).
@@ -187,10 +193,9 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
           v[0] = fmaf(xv, wa.x, v[0]); v[1] = fmaf(xv, wa.y, v[1]); v[2] = fmaf(xv, wa.z, v[2]); v[3] = fmaf(xv, wa.w, v[3]);
           v[4] = fmaf(xv, wb.x, v[4]); v[5] = fmaf(xv, wb.y, v[5]); v[6] = fmaf(xv, wb.z, v[6]); v[7] = fmaf(xv, wb.w, v[7]);
         }
-        uint32_t bits = 0u;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) { v[i] = fmaxf(v[i], 0.f); bits |= (v[i] > 0.f ? 1u : 0u) << i; }
-        or4(mk[0], q, bits << (8 * u));
+        for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+        or4(mk[0], q, nz_bits8(v) << (8 * u));
         store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
         store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
         if (wimg) {
@@ -236,10 +241,9 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
             const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
             const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
             v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
-            uint32_t bits = 0u;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { v[i] = fmaxf(v[i], 0.f); bits |= (v[i] > 0.f ? 1u : 0u) << i; }
-            or4(mk[l], q, bits << (8 * u));
+            for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+            or4(mk[l], q, nz_bits8(v) << (8 * u));
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
             if (wimg) {
@@ -406,6 +410,8 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
     cx.tmma = tbase + cx.g * T::TCOLS;
     cx.tacc = cx.tmma + ((uint32_t)((warp % 4) * 32) << 16);
     cx.seq = 0; cx.nd = 0;
+    cx.adesc = umma::make_desc(smem_u32(cx.sA), T::ACH, 128);
+    cx.wdesc = umma::make_desc(smem_u32(cx.sW), T::WCH, 128);
     mbar_wait(resbar, 0);
     const long long n_se = (long long)a.n_steps * S;
 
