@@ -30,7 +30,7 @@ N_STEPS = 20
 DT = 0.02
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at the bench size, from the
 # `ncu --set full` capture committed under profiles/ (r1_ncu_bench_*.txt); None until captured for that tier
-NCU_TRAFFIC = {"fp32": None, "tf32": 18.96e9, "3xtf32": None}   # tf32: profiles/r1_ncu_bench_tc_tf32.txt (0.49 GB read + 18.47 GB written)
+NCU_TRAFFIC = {"fp32": None, "tf32": 18.54e9, "3xtf32": None}   # tf32: profiles/r1_ncu_bench_tc_tf32.txt (0.18 GB read + 18.36 GB written)
 
 
 def parse():
