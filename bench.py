@@ -179,11 +179,13 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", 1))
     local = int(os.environ.get("LOCAL_RANK", 0))
     assert world == args.gpus, "launch with torchrun --nproc-per-node %d" % args.gpus
+    # stdout carries exactly ONE JSON line: anything libraries print on fd 1 (NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"        # keep stdout to the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     env, M = args.env, 1 << args.log2m
     n_s = 3 if env == "U" else 6
@@ -336,7 +338,7 @@ def run_ours(args):
             "gpu_launches": int(sum(k_n)),
             "clocks": sampler.summary(),
         }
-        print(json.dumps(line))
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     if world > 1:
         dist.destroy_process_group()
 

@@ -169,15 +169,19 @@ int nlbac_policy_head_bwd(const float* mean_logstd, const float* eps, const floa
  *   UNICYCLE  a = p(x_t) [B,2], b = p(x_{t+1}) [B,2] (grad);  rows: n_hazards CBF rows, then the CLF row
  *   CARS      a = x_t [B,10], b = x_{t+1} [B,10] (grad), c = x_{t+2} [B,10] (grad); rows: cbf23, cbf34, CLF
  *   BARRIER   a = B(x_t,u_t) detached [B], b = B(x_{t+1},u_{t+1}) [B] (grad); rows: barrier, CLF
+ *   PVTOL     a = x_t [B,7], b, c, e = x_{t+1}, x_{t+2}, x_{t+3} [B,7] (grad; columns 0 = x, 1 = y, 6 = safety operator's x);
+ *             rows: n_hazards third-order CBF rows, operator (two sides), y_max, y_min, CLF  (P sac_cbf_clf.py:556-697);
+ *             four states -> nlbac_constraints4_fwd/bwd
  * CLF row = (Vnext - V) * lya_inv_dt + gamma_l * V;  V [B] detached, Vnext [B] (grad).
  * ------------------------------------------------------------------------------------------------ */
 #define NLBAC_CONSTRAINT_UNICYCLE 0
 #define NLBAC_CONSTRAINT_CARS     1
 #define NLBAC_CONSTRAINT_BARRIER  2
+#define NLBAC_CONSTRAINT_PVTOL    3
 #define NLBAC_MAX_HAZARDS 15
 typedef struct nlbac_constraint_desc {
   int kind;
-  int m;                  /* rows: n_hazards+1 (UNICYCLE), 3 (CARS), 2 (BARRIER) */
+  int m;                  /* rows: n_hazards+1 (UNICYCLE), 3 (CARS), 2 (BARRIER), n_hazards+5 (PVTOL) */
   int n_hazards;
   float dt;               /* env.dt (0.02) */
   float gamma_b;
@@ -186,6 +190,8 @@ typedef struct nlbac_constraint_desc {
   float batch_size;       /* args.batch_size, the divisor the reference uses (U :503-504) */
   float collision_radius; /* U: 1.05 * hazards_radius; C: 4.5 */
   float hazards[2 * NLBAC_MAX_HAZARDS];
+  /* PVTOL only (P sac_cbf_clf.py:591, :633-636): 0.9 * env.operator_dist, env.y_max, env.y_min, delta_y (10) */
+  float operator_dist, y_max, y_min, delta_y;
 } nlbac_constraint_desc;
 
 int nlbac_constraints_fwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
@@ -193,6 +199,14 @@ int nlbac_constraints_fwd(const nlbac_constraint_desc* desc, const float* a, con
 int nlbac_constraints_bwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
                           const float* V, const float* Vnext, int64_t B, const float* grad_req, float* grad_b,
                           float* grad_c, float* grad_Vnext, void* stream);
+
+/* Same with a fourth state tensor e = x_{t+3} (and its gradient); e / grad_e may be NULL for the kinds that do not use
+ * them.  nlbac_constraints_fwd/bwd are these with e = NULL. */
+int nlbac_constraints4_fwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
+                           const float* e, const float* V, const float* Vnext, int64_t B, float* req, void* stream);
+int nlbac_constraints4_bwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
+                           const float* e, const float* V, const float* Vnext, int64_t B, const float* grad_req,
+                           float* grad_b, float* grad_c, float* grad_e, float* grad_Vnext, void* stream);
 
 /* lookahead point p(x) = [x + l_p cos(theta), y + l_p sin(theta)] of a [B, n_s] state (theta = column 2)
  * (U sac_cbf_clf.py:429-437, 455-469). */

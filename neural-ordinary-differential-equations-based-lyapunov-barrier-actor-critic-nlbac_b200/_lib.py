@@ -29,7 +29,9 @@ class ConstraintDesc(ctypes.Structure):
     _fields_ = [("kind", ctypes.c_int), ("m", ctypes.c_int), ("n_hazards", ctypes.c_int), ("dt", ctypes.c_float),
                 ("gamma_b", ctypes.c_float), ("gamma_l", ctypes.c_float), ("lya_inv_dt", ctypes.c_float),
                 ("batch_size", ctypes.c_float), ("collision_radius", ctypes.c_float),
-                ("hazards", ctypes.c_float * (2 * MAX_HAZARDS))]
+                ("hazards", ctypes.c_float * (2 * MAX_HAZARDS)),
+                ("operator_dist", ctypes.c_float), ("y_max", ctypes.c_float), ("y_min", ctypes.c_float),
+                ("delta_y", ctypes.c_float)]
 
 
 class NodeDesc(ctypes.Structure):
@@ -108,6 +110,8 @@ def _declare(lib):
     lib.nlbac_policy_head_bwd.argtypes = [vp, vp, vp, i64, c.c_int, vp, vp, vp, vp, vp]
     lib.nlbac_constraints_fwd.argtypes = [cp, vp, vp, vp, vp, vp, i64, vp, vp]
     lib.nlbac_constraints_bwd.argtypes = [cp, vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, vp]
+    lib.nlbac_constraints4_fwd.argtypes = [cp, vp, vp, vp, vp, vp, vp, i64, vp, vp]
+    lib.nlbac_constraints4_bwd.argtypes = [cp, vp, vp, vp, vp, vp, vp, i64, vp, vp, vp, vp, vp, vp]
     lib.nlbac_lookahead_fwd.argtypes = [vp, c.c_int, c.c_float, i64, vp, vp]
     lib.nlbac_lookahead_bwd.argtypes = [vp, c.c_int, c.c_float, i64, vp, vp, vp]
     lib.nlbac_get_state.argtypes = [c.c_int, vp, i64, vp, vp, vp]

@@ -1,7 +1,7 @@
 """``get_policy_loss_2`` — the CBF/CLF augmented-Lagrangian part of the actor loss — on the fused kernels.
 
 Mirrors the bodies of ``SAC_CBF_CLF.get_policy_loss_2`` for Unicycle (U sac_cbf_clf.py:408-530), SimulatedCars
-(C :412-555) and the learned-barrier variants (BU :359-477, BP :360-472): one fused NODE prediction per rollout
+(C :412-555), PVTOL (P :424-738) and the learned-barrier variants (BU :359-477, BP :360-472): one fused NODE prediction per rollout
 step (``odeint``), the fused Lyapunov / barrier / policy MLPs, and ONE fused kernel for the constraint rows,
 the ``where(>0)`` filter and the batch reduction.  The multiplier / rho bookkeeping is the reference's, kept on
 the host exactly as written there (python floats, App. D.3).
@@ -106,3 +106,34 @@ def barrier_unicycle_required_matrix(neural_ode_model, lyapunovNet, BarrierNet, 
     barrier_next = BarrierNet(next_obs, pi_next.detach())
     desc = make_constraint_desc("barrier", dt=dt, gamma_b=gamma_b, gamma_l=gamma_l, batch_size=batch_size)
     return constraint_sums(desc, barrier_value, barrier_next, None, lyapunov_value.detach(), lyapunov_value_next)
+
+
+def pvtol_required_matrix(neural_ode_model, lyapunovNet, policy, dynamics_model, state_batch, action_batch,
+                          lyapunov_value, state_dynamics_batch=None, *, dt, gamma_b, hazard_locations, hazards_radius,
+                          safety_operator_follow, operator_dist, y_max, y_min, batch_size, solver="euler",
+                          gamma_l=0.1, eps_next=None, eps_next_next=None):
+    """P sac_cbf_clf.py:424-697: three chained NODE predictions of the six dynamic states (the seventh state, the
+    safety operator's x, follows ``op + follow * (x_next - op)``, :461-464), the policy re-sampled on the detached
+    predicted observation between steps (:483-489, :520-527), then 5 hazard + 4 operator / altitude third-order CBF
+    rows and the CLF row in ONE fused kernel; returns ``required_matrix`` [10, 1]."""
+    assert state_batch.ndim == 2 and action_batch.ndim == 2, (state_batch.shape, action_batch.shape)
+    if state_dynamics_batch is None:
+        state_dynamics_batch = state_batch[:, :6]
+
+    def step(s7_prev, dyn_prev, u):
+        nxt = odeint(neural_ode_model, torch.cat((dyn_prev, u), dim=-1), [0.0, dt], method=solver, atol=1e-7,
+                     rtol=1e-5)[-1][:, :6]
+        op = s7_prev[:, 6] + safety_operator_follow * (nxt[:, 0] - s7_prev[:, 6])
+        return torch.cat((nxt, op[:, None]), dim=1), nxt
+
+    s1, d1 = step(state_batch, state_dynamics_batch, action_batch)
+    next_obs = dynamics_model.get_obs(s1)
+    lyapunov_value_next = lyapunovNet(next_obs)
+    pi_next = policy.sample(next_obs.detach(), eps_next)[0].detach()
+    s2, d2 = step(s1, d1, pi_next)
+    pi_next_next = policy.sample(dynamics_model.get_obs(s2.detach()), eps_next_next)[0].detach()
+    s3, _ = step(s2, d2, pi_next_next)
+    desc = make_constraint_desc("pvtol", dt=dt, gamma_b=gamma_b, gamma_l=gamma_l, batch_size=batch_size,
+                                lya_inv_dt=1.0, collision_radius=1.2 * hazards_radius, hazards=hazard_locations,
+                                operator_dist=0.9 * operator_dist, y_max=y_max, y_min=y_min, delta_y=10.0)
+    return constraint_sums(desc, state_batch, s1, s2, lyapunov_value.detach(), lyapunov_value_next, e=s3)

@@ -29,10 +29,82 @@ constexpr int CNT = 256;
 
 template <bool BWD>
 __device__ __forceinline__ int constraint_rows(const nlbac_constraint_desc& d, const float* a, const float* b,
-                                               const float* c, const float* V, const float* Vn, long long i,
-                                               float (&row)[MAXM], const float* g /*[m] scaled*/, float* gb, float* gc,
-                                               float* gVn) {
+                                               const float* c, const float* e, const float* V, const float* Vn,
+                                               long long i, float (&row)[MAXM], const float* g /*[m] scaled*/,
+                                               float* gb, float* gc, float* ge, float* gVn) {
   const float v = V[i], vn = Vn[i];
+  if (d.kind == NLBAC_CONSTRAINT_PVTOL) {
+    // a = s_t (data), b, c, e = s_{t+1..3} [B,7]: column 0 = x, 1 = y, 6 = safety operator's x  (P sac_cbf_clf.py:444-697)
+    const float* sp[4] = {a + 7 * i, b + 7 * i, c + 7 * i, e + 7 * i};
+    float X[4], Y[4], O[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { X[j] = sp[j][0]; Y[j] = sp[j][1]; O[j] = sp[j][6]; }
+    const float gm = d.gamma_b, am = d.gamma_b - 1.f;
+    // third-order discrete CBF expression, evaluated in the reference's order (P :581-587)
+    auto cbf3 = [gm](float h0, float h1, float h2, float h3) {
+      const float t1 = h3 - h2 + gm * h2, t2 = h2 - h1 + gm * h1, t3 = h1 - h0 + gm * h0;
+      const float y = t2 - t3 + gm * t3;
+      return -(t1 - t2 + gm * t2 - y + gm * y);
+    };
+    // d row / d h_j, j = 1..3:  row = -(h3 + 3a h2 + 3a^2 h1 + a^3 h0), a = gamma_b - 1
+    const float coef[4] = {0.f, -3.f * am * am, -3.f * am, -1.f};
+    float gx[4] = {0.f, 0.f, 0.f, 0.f}, gy[4] = {0.f, 0.f, 0.f, 0.f}, go[4] = {0.f, 0.f, 0.f, 0.f};
+    const float rc2 = d.collision_radius * d.collision_radius;
+    int k = 0;
+    for (int h = 0; h < d.n_hazards; ++h, ++k) {
+      const float cx = d.hazards[2 * h], cy = d.hazards[2 * h + 1];
+      float hv[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) hv[j] = 0.5f * ((X[j] - cx) * (X[j] - cx) + (Y[j] - cy) * (Y[j] - cy) - rc2);
+      row[k] = cbf3(hv[0], hv[1], hv[2], hv[3]);
+      if (BWD && row[k] > 0.f) {
+#pragma unroll
+        for (int j = 1; j < 4; ++j) {
+          const float s = g[k] * coef[j];
+          gx[j] = fmaf(s, X[j] - cx, gx[j]);
+          gy[j] = fmaf(s, Y[j] - cy, gy[j]);
+        }
+      }
+    }
+    const float od = d.operator_dist;
+    row[k] = cbf3(X[0] - O[0] + od, X[1] - O[1] + od, X[2] - O[2] + od, X[3] - O[3] + od);
+    if (BWD && row[k] > 0.f) {
+#pragma unroll
+      for (int j = 1; j < 4; ++j) { gx[j] += g[k] * coef[j]; go[j] -= g[k] * coef[j]; }
+    }
+    ++k;
+    row[k] = cbf3(-X[0] + O[0] + od, -X[1] + O[1] + od, -X[2] + O[2] + od, -X[3] + O[3] + od);
+    if (BWD && row[k] > 0.f) {
+#pragma unroll
+      for (int j = 1; j < 4; ++j) { gx[j] -= g[k] * coef[j]; go[j] += g[k] * coef[j]; }
+    }
+    ++k;
+    row[k] = cbf3(-Y[0] + d.y_max - d.delta_y, -Y[1] + d.y_max - d.delta_y, -Y[2] + d.y_max - d.delta_y,
+                  -Y[3] + d.y_max - d.delta_y);
+    if (BWD && row[k] > 0.f) {
+#pragma unroll
+      for (int j = 1; j < 4; ++j) gy[j] -= g[k] * coef[j];
+    }
+    ++k;
+    row[k] = cbf3(Y[0] - d.y_min - d.delta_y, Y[1] - d.y_min - d.delta_y, Y[2] - d.y_min - d.delta_y,
+                  Y[3] - d.y_min - d.delta_y);
+    if (BWD && row[k] > 0.f) {
+#pragma unroll
+      for (int j = 1; j < 4; ++j) gy[j] += g[k] * coef[j];
+    }
+    ++k;
+    row[k] = (vn - v) * d.lya_inv_dt + d.gamma_l * v;
+    if (BWD) {
+      float* gp[4] = {nullptr, gb + 7 * i, gc + 7 * i, ge + 7 * i};
+#pragma unroll
+      for (int j = 1; j < 4; ++j) {
+        gp[j][0] = gx[j]; gp[j][1] = gy[j]; gp[j][2] = 0.f; gp[j][3] = 0.f; gp[j][4] = 0.f; gp[j][5] = 0.f;
+        gp[j][6] = go[j];
+      }
+      gVn[i] = row[k] > 0.f ? g[k] * d.lya_inv_dt : 0.f;
+    }
+    return k + 1;
+  }
   if (d.kind == NLBAC_CONSTRAINT_UNICYCLE) {
     // a = p(x_t) [B,2], b = p(x_{t+1}) [B,2]
     const float px = a[2 * i], py = a[2 * i + 1], qx = b[2 * i], qy = b[2 * i + 1];
@@ -99,8 +171,8 @@ __device__ __forceinline__ int constraint_rows(const nlbac_constraint_desc& d, c
 }
 
 __global__ void __launch_bounds__(CNT) constraints_fwd_kernel(nlbac_constraint_desc d, const float* a, const float* b,
-                                                              const float* c, const float* V, const float* Vn,
-                                                              long long B, float* req) {
+                                                              const float* c, const float* e, const float* V,
+                                                              const float* Vn, long long B, float* req) {
   __shared__ float red[CNT / 32][MAXM];
   float acc[MAXM];
 #pragma unroll
@@ -108,7 +180,7 @@ __global__ void __launch_bounds__(CNT) constraints_fwd_kernel(nlbac_constraint_d
   int m = 0;
   for (long long i = (long long)blockIdx.x * CNT + threadIdx.x; i < B; i += (long long)gridDim.x * CNT) {
     float row[MAXM];
-    m = constraint_rows<false>(d, a, b, c, V, Vn, i, row, nullptr, nullptr, nullptr, nullptr);
+    m = constraint_rows<false>(d, a, b, c, e, V, Vn, i, row, nullptr, nullptr, nullptr, nullptr, nullptr);
 #pragma unroll
     for (int k = 0; k < MAXM; ++k)
       if (k < m && row[k] > 0.f) acc[k] += row[k];   // torch.where(matr > 0, matr, 0)
@@ -129,15 +201,15 @@ __global__ void __launch_bounds__(CNT) constraints_fwd_kernel(nlbac_constraint_d
 }
 
 __global__ void __launch_bounds__(CNT) constraints_bwd_kernel(nlbac_constraint_desc d, const float* a, const float* b,
-                                                              const float* c, const float* V, const float* Vn,
-                                                              long long B, const float* grad_req, float* gb, float* gc,
-                                                              float* gVn) {
+                                                              const float* c, const float* e, const float* V,
+                                                              const float* Vn, long long B, const float* grad_req,
+                                                              float* gb, float* gc, float* ge, float* gVn) {
   __shared__ float g[MAXM];
   if (threadIdx.x < MAXM) g[threadIdx.x] = threadIdx.x < d.m ? grad_req[threadIdx.x] / d.batch_size : 0.f;
   __syncthreads();
   for (long long i = (long long)blockIdx.x * CNT + threadIdx.x; i < B; i += (long long)gridDim.x * CNT) {
     float row[MAXM];
-    constraint_rows<true>(d, a, b, c, V, Vn, i, row, g, gb, gc, gVn);
+    constraint_rows<true>(d, a, b, c, e, V, Vn, i, row, g, gb, gc, ge, gVn);
   }
 }
 
@@ -261,8 +333,9 @@ __global__ void soft_update_kernel(float* target, const float* src, long long n,
 
 static int check_constraint(const nlbac_constraint_desc* d) {
   NLBAC_REQUIRE(d != nullptr, "null constraint descriptor");
-  NLBAC_REQUIRE(d->kind >= NLBAC_CONSTRAINT_UNICYCLE && d->kind <= NLBAC_CONSTRAINT_BARRIER, "unknown constraint kind %d", d->kind);
-  const int want = d->kind == NLBAC_CONSTRAINT_UNICYCLE ? d->n_hazards + 1 : (d->kind == NLBAC_CONSTRAINT_CARS ? 3 : 2);
+  NLBAC_REQUIRE(d->kind >= NLBAC_CONSTRAINT_UNICYCLE && d->kind <= NLBAC_CONSTRAINT_PVTOL, "unknown constraint kind %d", d->kind);
+  const int want = d->kind == NLBAC_CONSTRAINT_UNICYCLE ? d->n_hazards + 1
+                   : (d->kind == NLBAC_CONSTRAINT_CARS ? 3 : (d->kind == NLBAC_CONSTRAINT_PVTOL ? d->n_hazards + 5 : 2));
   NLBAC_REQUIRE(d->m == want && d->m <= MAXM, "constraint rows m=%d, expected %d (<= %d)", d->m, want, MAXM);
   NLBAC_REQUIRE(d->n_hazards >= 0 && d->n_hazards <= NLBAC_MAX_HAZARDS, "n_hazards=%d", d->n_hazards);
   NLBAC_REQUIRE(d->batch_size > 0.f && d->dt > 0.f, "batch_size and dt must be positive");
@@ -275,31 +348,48 @@ using namespace nlbac;
 
 extern "C" {
 
-int nlbac_constraints_fwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
-                          const float* V, const float* Vnext, int64_t B, float* req, void* stream) {
+int nlbac_constraints4_fwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
+                           const float* e, const float* V, const float* Vnext, int64_t B, float* req, void* stream) {
   if (int rc = check_constraint(desc)) return rc;
   NLBAC_REQUIRE(a && b && V && Vnext && req, "null pointer");
-  NLBAC_REQUIRE(desc->kind != NLBAC_CONSTRAINT_CARS || c, "cars constraints need x_{t+2}");
+  NLBAC_REQUIRE((desc->kind != NLBAC_CONSTRAINT_CARS && desc->kind != NLBAC_CONSTRAINT_PVTOL) || c,
+                "cars / pvtol constraints need x_{t+2}");
+  NLBAC_REQUIRE(desc->kind != NLBAC_CONSTRAINT_PVTOL || e, "pvtol constraints need x_{t+3}");
   NLBAC_REQUIRE(B >= 0, "negative batch");
   cudaStream_t st = (cudaStream_t)stream;
   NLBAC_CUDA(cudaMemsetAsync(req, 0, desc->m * 4, st));
   if (B == 0) return 0;
-  constraints_fwd_kernel<<<tail_grid(B, CNT), CNT, 0, st>>>(*desc, a, b, c, V, Vnext, B, req);
+  constraints_fwd_kernel<<<tail_grid(B, CNT), CNT, 0, st>>>(*desc, a, b, c, e, V, Vnext, B, req);
   NLBAC_CUDA(cudaGetLastError());
   return 0;
+}
+
+int nlbac_constraints4_bwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
+                           const float* e, const float* V, const float* Vnext, int64_t B, const float* grad_req,
+                           float* grad_b, float* grad_c, float* grad_e, float* grad_Vnext, void* stream) {
+  if (int rc = check_constraint(desc)) return rc;
+  NLBAC_REQUIRE(a && b && V && Vnext && grad_req && grad_b && grad_Vnext, "null pointer");
+  NLBAC_REQUIRE((desc->kind != NLBAC_CONSTRAINT_CARS && desc->kind != NLBAC_CONSTRAINT_PVTOL) || (c && grad_c),
+                "cars / pvtol constraints need x_{t+2} and its gradient");
+  NLBAC_REQUIRE(desc->kind != NLBAC_CONSTRAINT_PVTOL || (e && grad_e), "pvtol constraints need x_{t+3} and its gradient");
+  if (B <= 0) return 0;
+  constraints_bwd_kernel<<<tail_grid(B, CNT), CNT, 0, (cudaStream_t)stream>>>(*desc, a, b, c, e, V, Vnext, B, grad_req,
+                                                                              grad_b, grad_c, grad_e, grad_Vnext);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_constraints_fwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
+                          const float* V, const float* Vnext, int64_t B, float* req, void* stream) {
+  NLBAC_REQUIRE(desc == nullptr || desc->kind != NLBAC_CONSTRAINT_PVTOL, "pvtol constraints take four states: use nlbac_constraints4_fwd");
+  return nlbac_constraints4_fwd(desc, a, b, c, nullptr, V, Vnext, B, req, stream);
 }
 
 int nlbac_constraints_bwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
                           const float* V, const float* Vnext, int64_t B, const float* grad_req, float* grad_b,
                           float* grad_c, float* grad_Vnext, void* stream) {
-  if (int rc = check_constraint(desc)) return rc;
-  NLBAC_REQUIRE(a && b && V && Vnext && grad_req && grad_b && grad_Vnext, "null pointer");
-  NLBAC_REQUIRE(desc->kind != NLBAC_CONSTRAINT_CARS || (c && grad_c), "cars constraints need x_{t+2} and its gradient");
-  if (B <= 0) return 0;
-  constraints_bwd_kernel<<<tail_grid(B, CNT), CNT, 0, (cudaStream_t)stream>>>(*desc, a, b, c, V, Vnext, B, grad_req,
-                                                                              grad_b, grad_c, grad_Vnext);
-  NLBAC_CUDA(cudaGetLastError());
-  return 0;
+  NLBAC_REQUIRE(desc == nullptr || desc->kind != NLBAC_CONSTRAINT_PVTOL, "pvtol constraints take four states: use nlbac_constraints4_bwd");
+  return nlbac_constraints4_bwd(desc, a, b, c, nullptr, V, Vnext, B, grad_req, grad_b, grad_c, nullptr, grad_Vnext, stream);
 }
 
 int nlbac_lookahead_fwd(const float* state, int n_s, float l_p, int64_t B, float* p, void* stream) {

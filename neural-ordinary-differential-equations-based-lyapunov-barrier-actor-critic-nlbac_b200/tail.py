@@ -14,7 +14,7 @@ import torch
 
 from . import _lib
 
-CONSTRAINT_KINDS = {"unicycle": 0, "cars": 1, "barrier": 2}
+CONSTRAINT_KINDS = {"unicycle": 0, "cars": 1, "barrier": 2, "pvtol": 3}
 ENVS = {"Unicycle": 0, "SimulatedCars": 1, "Pvtol": 2}
 _OBS_DIMS = {0: (7, 3), 1: (10, 10), 2: (11, 7)}
 
@@ -40,14 +40,15 @@ def _p(t):
 
 
 def make_constraint_desc(kind, *, dt, gamma_b, gamma_l, batch_size, lya_inv_dt=None, collision_radius=0.0,
-                         hazards=None):
+                         hazards=None, operator_dist=0.0, y_max=0.0, y_min=0.0, delta_y=10.0):
     d = _lib.ConstraintDesc()
     d.kind = CONSTRAINT_KINDS[kind]
     hz = np.zeros((0, 2), dtype=np.float32) if hazards is None else np.asarray(hazards, dtype=np.float32).reshape(-1, 2)
     if len(hz) > _lib.MAX_HAZARDS:
         raise ValueError("at most %d hazards" % _lib.MAX_HAZARDS)
-    d.n_hazards = len(hz) if kind == "unicycle" else 0
-    d.m = d.n_hazards + 1 if kind == "unicycle" else (3 if kind == "cars" else 2)
+    d.n_hazards = len(hz) if kind in ("unicycle", "pvtol") else 0
+    d.m = {"unicycle": d.n_hazards + 1, "cars": 3, "barrier": 2, "pvtol": d.n_hazards + 5}[kind]
+    d.operator_dist, d.y_max, d.y_min, d.delta_y = float(operator_dist), float(y_max), float(y_min), float(delta_y)
     d.dt, d.gamma_b, d.gamma_l = float(dt), float(gamma_b), float(gamma_l)
     d.lya_inv_dt = float(1.0 / dt if lya_inv_dt is None else lya_inv_dt)
     d.batch_size = float(batch_size)
@@ -59,39 +60,43 @@ def make_constraint_desc(kind, *, dt, gamma_b, gamma_l, batch_size, lya_inv_dt=N
 
 class _ConstraintSums(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, desc, a, b, c, V, Vnext):
+    def forward(ctx, desc, a, b, c, e, V, Vnext):
         L = _lib.lib()
-        a_, b_, c_, V_, Vn_ = _cuda32(a, b, c, V, Vnext)
+        a_, b_, c_, e_, V_, Vn_ = _cuda32(a, b, c, e, V, Vnext)
         B = V_.shape[0]
         req = torch.empty((desc.m, 1), dtype=torch.float32, device=V_.device)
-        _lib.check(L.nlbac_constraints_fwd(ctypes.byref(desc), _p(a_), _p(b_), _p(c_), _p(V_), _p(Vn_), B,
-                                           req.data_ptr(), _stream()), "constraints_fwd")
+        _lib.check(L.nlbac_constraints4_fwd(ctypes.byref(desc), _p(a_), _p(b_), _p(c_), _p(e_), _p(V_), _p(Vn_), B,
+                                            req.data_ptr(), _stream()), "constraints_fwd")
         ctx.desc = desc
-        ctx.save_for_backward(a_, b_, V_, Vn_, *([c_] if c_ is not None else []))
-        ctx.shapes = (b.shape, None if c is None else c.shape, Vnext.shape)
+        ctx.has = (c_ is not None, e_ is not None)
+        ctx.save_for_backward(a_, b_, V_, Vn_, *[t for t in (c_, e_) if t is not None])
+        ctx.shapes = (b.shape, None if c is None else c.shape, None if e is None else e.shape, Vnext.shape)
         return req
 
     @staticmethod
     def backward(ctx, g):
         L = _lib.lib()
         a_, b_, V_, Vn_, *rest = ctx.saved_tensors
-        c_ = rest[0] if rest else None
+        c_ = rest.pop(0) if ctx.has[0] else None
+        e_ = rest.pop(0) if ctx.has[1] else None
         B = V_.shape[0]
         gb = torch.empty_like(b_)
         gc = torch.empty_like(c_) if c_ is not None else None
+        ge = torch.empty_like(e_) if e_ is not None else None
         gV = torch.empty_like(Vn_)
         gq = g.contiguous().float()
-        _lib.check(L.nlbac_constraints_bwd(ctypes.byref(ctx.desc), _p(a_), _p(b_), _p(c_), _p(V_), _p(Vn_), B,
-                                           gq.data_ptr(), gb.data_ptr(), _p(gc), gV.data_ptr(), _stream()),
+        _lib.check(L.nlbac_constraints4_bwd(ctypes.byref(ctx.desc), _p(a_), _p(b_), _p(c_), _p(e_), _p(V_), _p(Vn_), B,
+                                            gq.data_ptr(), gb.data_ptr(), _p(gc), _p(ge), gV.data_ptr(), _stream()),
                    "constraints_bwd")
-        sb, sc, sv = ctx.shapes
-        return None, None, gb.view(sb), (gc.view(sc) if gc is not None else None), None, gV.view(sv)
+        sb, sc, se, sv = ctx.shapes
+        return (None, None, gb.view(sb), (gc.view(sc) if gc is not None else None),
+                (ge.view(se) if ge is not None else None), None, gV.view(sv))
 
 
-def constraint_sums(desc, a, b, c, V, Vnext):
+def constraint_sums(desc, a, b, c, V, Vnext, e=None):
     """``required_matrix`` [m, 1] of the reference: filtered constraint rows summed over the batch and divided
-    by ``batch_size``.  Gradients flow to ``b`` (x_{t+1} quantities), ``c`` (x_{t+2}) and ``Vnext``."""
-    return _ConstraintSums.apply(desc, a, b, c, V, Vnext)
+    by ``batch_size``.  Gradients flow to ``b`` (x_{t+1} quantities), ``c`` (x_{t+2}), ``e`` (x_{t+3}) and ``Vnext``."""
+    return _ConstraintSums.apply(desc, a, b, c, e, V, Vnext)
 
 
 class _Lookahead(torch.autograd.Function):

@@ -127,6 +127,54 @@ def barrier_unicycle_required_matrix(node, lya, barrier, policy, obs, state, act
     return required_matrix_from_rows(torch.cat((barrier_term, lya_term), 1), batch_size)
 
 
+def third_order_cbf(h0, h1, h2, h3, gamma_b):
+    """P sac_cbf_clf.py:581-587 (same expression for every P row): a discrete third-order CBF condition."""
+    t1 = h3 - h2 + gamma_b * h2
+    t2 = h2 - h1 + gamma_b * h1
+    t3 = h1 - h0 + gamma_b * h0
+    return -(t1 - t2 + gamma_b * t2 - (t2 - t3 + gamma_b * t3) + gamma_b * (t2 - t3 + gamma_b * t3))
+
+
+def pvtol_rollout(node, policy, state, action, *, dt, follow, solver="euler", eps_next=None, eps_next_next=None):
+    """P sac_cbf_clf.py:452-552: three chained NODE predictions of the 6 dynamic states; the 7th state (the safety
+    operator's x) follows ``op + follow * (x_next - op)``; the policy is re-sampled on the detached predicted
+    observation between steps.  Returns the three 7-column states."""
+    tspan = torch.tensor([0.0, dt])
+
+    def step(s7_prev, dyn_prev, u):
+        nxt = odeint(node, torch.cat((dyn_prev, u), -1), tspan, method=solver, atol=1e-7, rtol=1e-5)[-1][:, :6]
+        op = s7_prev[:, 6] + follow * (nxt[:, 0] - s7_prev[:, 6])
+        return torch.cat((nxt, op[:, None]), 1), nxt
+
+    s1, d1 = step(state, state[:, :6], action)
+    u1 = policy.sample(get_obs("Pvtol", s1).detach(), eps_next)[0].detach()
+    s2, d2 = step(s1, d1, u1)
+    u2 = policy.sample(get_obs("Pvtol", s2).detach(), eps_next_next)[0].detach()
+    s3, _ = step(s2, d2, u2)
+    return s1, s2, s3
+
+
+def pvtol_required_matrix(node, lya, policy, state, action, V, *, dt, gamma_b, hazards, hazards_radius, follow,
+                          operator_dist, y_max, y_min, batch_size, solver="euler", gamma_l=0.1, eps_next=None,
+                          eps_next_next=None):
+    """P sac_cbf_clf.py:424-697: rows = 5 hazards, operator (two sides), y_max, y_min, CLF."""
+    rc = 1.2 * hazards_radius
+    od = 0.9 * operator_dist
+    delta_y = 10.0
+    hz = torch.as_tensor(hazards, dtype=state.dtype, device=state.device)
+    s1, s2, s3 = pvtol_rollout(node, policy, state, action, dt=dt, follow=follow, solver=solver, eps_next=eps_next,
+                               eps_next_next=eps_next_next)
+    V_next = lya(get_obs("Pvtol", s1))
+    lya_term = (V_next - V) / 1.0 + gamma_l * V
+    seq = (state, s1, s2, s3)
+    hs = [0.5 * (((s[:, None, :2] - hz[None]) ** 2).sum(2) - rc ** 2) for s in seq]
+    rows = [third_order_cbf(*hs, gamma_b)]
+    for f in (lambda s: s[:, 0:1] - s[:, 6:7] + od, lambda s: -s[:, 0:1] + s[:, 6:7] + od,
+              lambda s: -s[:, 1:2] + y_max - delta_y, lambda s: s[:, 1:2] - y_min - delta_y):
+        rows.append(third_order_cbf(*[f(s) for s in seq], gamma_b))
+    return required_matrix_from_rows(torch.cat(rows + [lya_term], 1), batch_size)
+
+
 class ConstraintState:
     """lambda / rho bookkeeping of the agent (U sac_cbf_clf.py:55-62)."""
 

@@ -10,6 +10,9 @@ def build(g, lib, device):
     if tag in ("U", "BU"):
         node = lib.AffineNODE(3, 3, 6) if is_oracle else lib.NeuralODEModel(3, 3, 6)
         lya = lib.LyaNetwork(2, 256)
+    elif tag == "P":
+        node = lib.AffineNODE(6, 6, 12) if is_oracle else lib.NeuralODEModel(6, 6, 12)
+        lya = lib.LyaNetwork(11, 256)
     else:
         node = lib.BlackBoxNODE(12, 10) if is_oracle else lib.NeuralODEModel(12, 10)
         lya = lib.LyaNetwork(4, 256)
@@ -17,7 +20,7 @@ def build(g, lib, device):
     lya.load_state_dict(g["lya"])
     nets = {"node": node.to(device), "lya": lya.to(device)}
     if "policy" in g:
-        n_o, n_u, hi = (10, 1, [3.0]) if tag == "C" else (7, 2, [3.5, 12.0])
+        n_o, n_u, hi = (10, 1, [3.0]) if tag == "C" else ((11, 2, [3.5, 15.0]) if tag == "P" else (7, 2, [3.5, 12.0]))
         if is_oracle:
             pol = lib.GaussianPolicy(n_o, n_u, 256, hi, [-h for h in hi])
         else:
@@ -48,6 +51,8 @@ def run_sequence(g, nets, C, device, dyn=None):
     elif tag == "C":
         st = (C.ConstraintState(3, lambda_max=300.0, ratio_floor=0.002) if is_oracle
               else C.ConstraintState(3, B, lambda_max=300.0, ratio_floor=0.002))
+    elif tag == "P":      # P sac_cbf_clf.py:707-708 (floor 0.002), :718 (clamp 400)
+        st = (C.ConstraintState(10, ratio_floor=0.002) if is_oracle else C.ConstraintState(10, B, ratio_floor=0.002))
     else:
         st = C.ConstraintState(2, use_ratio=False) if is_oracle else C.ConstraintState(2, B, use_ratio=False)
     eps = g["eps"].to(device) if "eps" in g else None
@@ -69,6 +74,17 @@ def run_sequence(g, nets, C, device, dyn=None):
             else:
                 req = C.cars_required_matrix(nets["node"], nets["lya"], nets["policy"], dyn, state, action, V, t, t1,
                                              dt=k["dt"], gamma_b=k["gamma_b"], batch_size=B, eps_next=eps)
+        elif tag == "P":
+            kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_radius=k["hazards_radius"],
+                      operator_dist=k["operator_dist"], y_max=k["y_max"], y_min=k["y_min"], batch_size=B,
+                      eps_next=eps, eps_next_next=eps)
+            if is_oracle:
+                req = C.pvtol_required_matrix(nets["node"], nets["lya"], nets["policy"], state, action, V,
+                                              hazards=k["hazards"], follow=k["safety_operator_follow"], **kw)
+            else:
+                req = C.pvtol_required_matrix(nets["node"], nets["lya"], nets["policy"], dyn, state, action, V,
+                                              hazard_locations=k["hazards"],
+                                              safety_operator_follow=k["safety_operator_follow"], **kw)
         else:
             obs = g["obs"].to(device)
             if is_oracle:

@@ -215,8 +215,59 @@ def case_P_maps(B=64):
             "state_from_obs": st, "state_dyn_from_obs": st_dyn}
 
 
+def case_P(B=256):
+    """PVTOL: 3-step NODE rollout with two policy re-samples, 5 hazard + 4 box/operator third-order CBF rows + CLF
+    (P sac_cbf_clf.py:424-738), run by the reference's own method."""
+    model, agent_mod, dyn_mod = import_variant("P")
+    gen = torch.Generator().manual_seed(325)
+    torch.manual_seed(6)
+    env = _Env()
+    env.dynamics_mode, env.dt, env.hazards_radius = "Pvtol", 0.02, 0.25
+    env.hazard_locations = np.array([[-2.5, -2.5], [-2.5, 2.5], [0.0, -3.5], [0.0, 3.5], [-4.5, 0.0]])
+    # the env's own operator_dist = 1.0 and y bounds = +-100 never activate on this state range (the operator
+    # closes 70 % of its gap every step): tighter values exercise the sign changes of those four rows
+    env.safety_operator_follow, env.operator_dist = 0.7, 0.001
+    env.y_max, env.y_min = 13.0, -13.0
+    node = model.NeuralODEModel(6, 6, 12)
+    lya = model.LyaNetwork(11, 256)
+    pol = model.GaussianPolicy(11, 2, 256, _Box([-3.5, -15.0], [3.5, 15.0]))
+    for n in (lya, pol):
+        _perturb_biases(n, gen)
+    a = _agent(agent_mod, env, gamma_b=0.6, batch_size=B, num_cbfs=9, num_constraints=10, neural_ode_model=node,
+               lyapunovNet=lya, policy=pol)
+    r = lambda *s: torch.rand(*s, generator=gen)  # noqa: E731
+    x, y = r(B) * 14 - 7, r(B) * 12 - 6
+    # a third of the batch sits inside / at the edge of a hazard so that the obstacle rows change sign
+    hz = torch.tensor(env.hazard_locations, dtype=torch.float32)
+    k = torch.randint(0, 5, (B,), generator=gen)
+    near = r(B) < 0.34
+    x = torch.where(near, hz[k, 0] + (r(B) * 0.7 - 0.35), x)
+    y = torch.where(near, hz[k, 1] + (r(B) * 0.7 - 0.35), y)
+    state = torch.stack([x, y, (r(B) * 2 - 1) * np.pi, r(B) * 4 - 2, r(B) * 4 - 2, r(B) * 2,
+                         x + (r(B) * 3 - 1.5)], 1)
+    action = torch.stack([r(B) * 7 - 3.5, r(B) * 30 - 15], 1).requires_grad_(True)
+    eps = torch.randn(B, 2, generator=gen)
+    dm = dyn_mod.DynamicsModel(env, _Args())
+    obs = dm.get_obs(state.unsqueeze(-1), torch.device("cpu")).squeeze(-1).detach()
+    lv = lya(obs).detach()
+    V = lv + 0.3 * lv.abs().mean() * torch.randn(B, 1, generator=gen)
+    losses, grads = [], []
+    for updates in (8, 9):
+        if action.grad is not None:
+            action.grad = None
+        loss = _with_eps(eps, lambda: a.get_policy_loss_2(dm, state, action, V, updates, state[:, :6]))
+        loss.backward()
+        losses.append(loss.detach().clone())
+        grads.append(action.grad.clone())
+    return {"tag": "P", "B": B, "node": _sd(node), "lya": _sd(lya), "policy": _sd(pol), "state": state,
+            "action": action.detach(), "V": V, "eps": eps, "obs": obs, "losses": losses, "grad_action": grads,
+            "lambda_after": [float(v) for v in a.lambda_values], "augmented_term_after": a.augmented_term,
+            "consts": {"dt": 0.02, "gamma_b": 0.6, "hazards": env.hazard_locations, "hazards_radius": 0.25,
+                       "safety_operator_follow": 0.7, "operator_dist": 0.001, "y_max": 13.0, "y_min": -13.0}}
+
+
 def main():
-    for name, fn in (("U", case_U), ("C", case_C), ("BU", case_BU), ("Pmaps", case_P_maps)):
+    for name, fn in (("U", case_U), ("C", case_C), ("BU", case_BU), ("Pmaps", case_P_maps), ("P", case_P)):
         torch.save(fn(), os.path.join(HERE, "constraints_%s.pt" % name))
         print("constraints", name, "ok")
 

@@ -25,7 +25,7 @@ class _Env:
         self.dynamics_mode = mode
 
 
-@pytest.mark.parametrize("tag,env", [("U", "Unicycle"), ("C", "SimulatedCars"), ("BU", "Unicycle")])
+@pytest.mark.parametrize("tag,env", [("U", "Unicycle"), ("C", "SimulatedCars"), ("BU", "Unicycle"), ("P", "Pvtol")])
 def test_policy_loss_2_matches_reference_and_oracle(tag, env, golden_dir):
     import nlbac_b200
     g = torch.load(os.path.join(golden_dir, "constraints_%s.pt" % tag), weights_only=False)
@@ -75,7 +75,8 @@ def test_get_state_and_get_obs(golden_dir):
     assert np.allclose(dm.get_state(c["obs"].numpy()), c["state_from_obs"].numpy(), rtol=1e-6)
 
 
-@pytest.mark.parametrize("kind,B", [("unicycle", 1), ("unicycle", 100000), ("cars", 3), ("cars", 70001), ("barrier", 2), ("barrier", 65537)])
+@pytest.mark.parametrize("kind,B", [("unicycle", 1), ("unicycle", 100000), ("cars", 3), ("cars", 70001), ("barrier", 2),
+                                    ("barrier", 65537), ("pvtol", 1), ("pvtol", 90001)])
 def test_constraint_sums_vs_oracle_rows(kind, B):
     """Kernel rows + filter + reduction (and gradients) on synthetic tensors, including B=1 and multi-CTA sizes."""
     import nlbac_b200
@@ -103,6 +104,19 @@ def test_constraint_sums_vs_oracle_rows(kind, B):
             l1, l2 = h1 - h0 + 0.5 * h0, h2 - h1 + 0.5 * h1
             rr.append(-(l2 - l1) - 0.5 * l1)
         rows = torch.cat(rr + [(Vn - V) + 0.15 * V], 1)
+    elif kind == "pvtol":
+        hz = torch.tensor([[-2.5, -2.5], [-2.5, 2.5], [0.0, -3.5], [0.0, 3.5], [-4.5, 0.0]])
+        a = r(B, 7) * 2.5
+        b, c, e = ((a + 0.3 * r(B, 7)).requires_grad_(True) for _ in range(3))
+        desc = nlbac_b200.make_constraint_desc("pvtol", dt=0.02, gamma_b=0.6, gamma_l=0.1, batch_size=bs, lya_inv_dt=1.0,
+                                               collision_radius=0.3, hazards=hz.numpy(), operator_dist=0.9, y_max=13.0,
+                                               y_min=-13.0)
+        seq = (a, b, c, e)
+        rr = [OC.third_order_cbf(*[0.5 * (((s[:, None, :2] - hz[None]) ** 2).sum(2) - 0.3 ** 2) for s in seq], 0.6)]
+        for f in (lambda s: s[:, 0:1] - s[:, 6:7] + 0.9, lambda s: -s[:, 0:1] + s[:, 6:7] + 0.9,
+                  lambda s: -s[:, 1:2] + 13.0 - 10.0, lambda s: s[:, 1:2] + 13.0 - 10.0):
+            rr.append(OC.third_order_cbf(*[f(s) for s in seq], 0.6))
+        rows = torch.cat(rr + [(Vn - V) + 0.1 * V], 1)
     else:
         a, b, c = r(B, 1), r(B, 1).requires_grad_(True), None
         desc = nlbac_b200.make_constraint_desc("barrier", dt=0.02, gamma_b=5.0, gamma_l=1.0, batch_size=bs)
@@ -110,12 +124,14 @@ def test_constraint_sums_vs_oracle_rows(kind, B):
     want = OC.required_matrix_from_rows(rows.double(), bs)
     w = torch.arange(1, want.shape[0] + 1, dtype=torch.float64).unsqueeze(-1)
     (want * w).sum().backward()
-    leaves = [t for t in (b, c, Vn) if t is not None]
+    e4 = e if kind == "pvtol" else None
+    leaves = [t for t in (b, c, e4, Vn) if t is not None]
     want_g = [t.grad.clone() for t in leaves]
     dev = [t.detach().cuda().requires_grad_(True) for t in leaves]
     bb = dev[0]
     cc = dev[1] if c is not None else None
-    got = nlbac_b200.constraint_sums(desc, a.cuda(), bb, cc, V.cuda(), dev[-1])
+    ee = dev[2] if e4 is not None else None
+    got = nlbac_b200.constraint_sums(desc, a.cuda(), bb, cc, V.cuda(), dev[-1], e=ee)
     assert got.shape == want.shape
     assert _rel(got, want) <= 2 * TOL     # fp32 atomics over up to 400 CTAs vs an fp64 reference
     (got * w.float().cuda()).sum().backward()
