@@ -16,10 +16,15 @@ class ConstraintState:
     """The agent attributes the reference's method reads and mutates (U sac_cbf_clf.py:55-62)."""
 
     def __init__(self, num_constraints, batch_size, *, lambda_max=400.0, cost_limit=0.0, augmented_term=1.0,
-                 augmented_ratio=1.0005, update_interval=8, ratio_floor=None, use_ratio=True):
+                 augmented_ratio=1.0005, update_interval=8, ratio_floor=None, use_ratio=True,
+                 backup_update_interval=1, separate_backup_rho=False):
         self.num_constraints = num_constraints
         self.batch_size = batch_size
         self.lambda_values = [0.0] * num_constraints
+        self.backup_lambda_values = [0.0] * (num_constraints - 1)      # backup policy: CBF rows only
+        self.backup_augmented_term = augmented_term                    # P keeps its own rho (P :1032-1034)
+        self.backup_update_interval = backup_update_interval           # P: args.backup_update_interval (:1025)
+        self.separate_backup_rho = separate_backup_rho
         self.lambda_max = lambda_max
         self.cost_limit = cost_limit
         self.augmented_term = augmented_term
@@ -56,18 +61,44 @@ def augmented_lagrangian(required_matrix, st, updates):
     return loss
 
 
+def backup_augmented_lagrangian(backup_required_matrix, st, updates):
+    """The tail of ``backup_get_policy_loss_2``: U sac_cbf_clf.py:611-640, C :657-681 (rho shared with the primary
+    loss); P :1022-1045 (its own rho; multipliers every ``interval * backup_update_interval`` updates)."""
+    rho_name = "backup_augmented_term" if st.separate_backup_rho else "augmented_term"
+    req_copy = backup_required_matrix.detach()
+    if updates % (st.Lagrangian_multiplier_update_interval * st.backup_update_interval) == 0:
+        for i in range(len(st.backup_lambda_values)):
+            new_lambda = st.backup_lambda_values[i] + getattr(st, rho_name) * req_copy[i]
+            st.backup_lambda_values[i] = torch.clamp(new_lambda, 0.01, st.lambda_max)
+    setattr(st, rho_name, min(getattr(st, rho_name) * st.augmented_ratio, 200))
+    rho, cl = getattr(st, rho_name), st.cost_limit
+    loss = 0.0
+    for i in range(backup_required_matrix.shape[0]):
+        c = backup_required_matrix[i] - cl
+        loss = loss + float(st.backup_lambda_values[i]) * c + rho / 2.0 * c * c
+    return loss
+
+
+def _zeros_like_rows(x):
+    return torch.zeros((x.shape[0], 1), dtype=torch.float32, device=x.device)
+
+
 def unicycle_required_matrix(neural_ode_model, lyapunovNet, state_batch, action_batch, lyapunov_value, *, dt,
                              gamma_b, hazards_locations, hazards_radius, l_p, batch_size, solver="euler",
                              gamma_l=1.0):
-    """U sac_cbf_clf.py:420-504: returns ``required_matrix`` [num_cbfs + 1, 1]."""
+    """U sac_cbf_clf.py:420-504: returns ``required_matrix`` [num_cbfs + 1, 1].  With ``lyapunovNet=None`` it is the
+    CBF-only matrix of ``backup_get_policy_loss_2`` (:544-608), [num_cbfs, 1]."""
     assert state_batch.ndim == 2 and action_batch.ndim == 2, (state_batch.shape, action_batch.shape)
     ps = lookahead(state_batch, l_p)
     model_input_t = torch.cat((state_batch, action_batch), dim=-1)
     next_state_t = odeint(neural_ode_model, model_input_t, [0.0, dt], method=solver, atol=1e-7, rtol=1e-5)[-1]
     ps_next = lookahead(next_state_t[:, :3], l_p)
-    lyapunov_value_next = lyapunovNet(ps_next)
     desc = make_constraint_desc("unicycle", dt=dt, gamma_b=gamma_b, gamma_l=gamma_l, batch_size=batch_size,
                                 collision_radius=1.05 * hazards_radius, hazards=hazards_locations)
+    if lyapunovNet is None:   # zero CLF row, dropped
+        z = _zeros_like_rows(ps)
+        return constraint_sums(desc, ps, ps_next, None, z, z)[:-1]
+    lyapunov_value_next = lyapunovNet(ps_next)
     return constraint_sums(desc, ps, ps_next, None, lyapunov_value.detach(), lyapunov_value_next)
 
 
@@ -75,7 +106,8 @@ def cars_required_matrix(neural_ode_model, lyapunovNet, policy, dynamics_model, 
                          lyapunov_value, t_batch, next_time_batch, *, dt, gamma_b, batch_size, solver="euler",
                          gamma_l=0.15, eps_next=None):
     """C sac_cbf_clf.py:424-523: two chained NODE predictions with the policy re-sampled on the detached
-    predicted observation in between; returns ``required_matrix`` [3, 1]."""
+    predicted observation in between; returns ``required_matrix`` [3, 1].  With ``lyapunovNet=None`` (and ``policy`` =
+    the backup policy) it is the CBF-only matrix of ``backup_get_policy_loss_2`` (:557-645), [2, 1]."""
     model_input_t = torch.cat((state_batch, action_batch, t_batch), dim=-1)
     next_state_pred = odeint(neural_ode_model, model_input_t, [0.0, dt], method=solver, atol=1e-7, rtol=1e-5)[-1][:, :10]
     next_obs_pred = dynamics_model.get_obs(next_state_pred.detach())
@@ -84,9 +116,12 @@ def cars_required_matrix(neural_ode_model, lyapunovNet, policy, dynamics_model, 
     next_model_input_t = torch.cat((next_state_pred, pi_next, next_time_batch), dim=-1)
     next_next_state_pred = odeint(neural_ode_model, next_model_input_t, [0.0, dt], method=solver, atol=1e-7,
                                   rtol=1e-5)[-1][:, :10]
-    lyapunov_value_next = lyapunovNet(next_state_pred[:, 4:8])
     desc = make_constraint_desc("cars", dt=dt, gamma_b=gamma_b, gamma_l=gamma_l, batch_size=batch_size,
                                 lya_inv_dt=1.0, collision_radius=4.5)
+    if lyapunovNet is None:
+        z = _zeros_like_rows(state_batch)
+        return constraint_sums(desc, state_batch, next_state_pred, next_next_state_pred, z, z)[:-1]
+    lyapunov_value_next = lyapunovNet(next_state_pred[:, 4:8])
     return constraint_sums(desc, state_batch, next_state_pred, next_next_state_pred, lyapunov_value.detach(),
                            lyapunov_value_next)
 
@@ -115,7 +150,8 @@ def pvtol_required_matrix(neural_ode_model, lyapunovNet, policy, dynamics_model,
     """P sac_cbf_clf.py:424-697: three chained NODE predictions of the six dynamic states (the seventh state, the
     safety operator's x, follows ``op + follow * (x_next - op)``, :461-464), the policy re-sampled on the detached
     predicted observation between steps (:483-489, :520-527), then 5 hazard + 4 operator / altitude third-order CBF
-    rows and the CLF row in ONE fused kernel; returns ``required_matrix`` [10, 1]."""
+    rows and the CLF row in ONE fused kernel; returns ``required_matrix`` [10, 1].  With ``lyapunovNet=None`` (and
+    ``policy`` = the backup policy) it is the CBF-only matrix of ``backup_get_policy_loss_2`` (:740-1010), [9, 1]."""
     assert state_batch.ndim == 2 and action_batch.ndim == 2, (state_batch.shape, action_batch.shape)
     if state_dynamics_batch is None:
         state_dynamics_batch = state_batch[:, :6]
@@ -128,7 +164,6 @@ def pvtol_required_matrix(neural_ode_model, lyapunovNet, policy, dynamics_model,
 
     s1, d1 = step(state_batch, state_dynamics_batch, action_batch)
     next_obs = dynamics_model.get_obs(s1)
-    lyapunov_value_next = lyapunovNet(next_obs)
     pi_next = policy.sample(next_obs.detach(), eps_next)[0].detach()
     s2, d2 = step(s1, d1, pi_next)
     pi_next_next = policy.sample(dynamics_model.get_obs(s2.detach()), eps_next_next)[0].detach()
@@ -136,4 +171,8 @@ def pvtol_required_matrix(neural_ode_model, lyapunovNet, policy, dynamics_model,
     desc = make_constraint_desc("pvtol", dt=dt, gamma_b=gamma_b, gamma_l=gamma_l, batch_size=batch_size,
                                 lya_inv_dt=1.0, collision_radius=1.2 * hazards_radius, hazards=hazard_locations,
                                 operator_dist=0.9 * operator_dist, y_max=y_max, y_min=y_min, delta_y=10.0)
+    if lyapunovNet is None:
+        z = _zeros_like_rows(state_batch)
+        return constraint_sums(desc, state_batch, s1, s2, z, z, e=s3)[:-1]
+    lyapunov_value_next = lyapunovNet(next_obs)
     return constraint_sums(desc, state_batch, s1, s2, lyapunov_value.detach(), lyapunov_value_next, e=s3)

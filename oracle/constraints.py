@@ -84,11 +84,13 @@ def unicycle_required_matrix(node, lya, state, action, V, *, dt, gamma_b, hazard
     y0 = torch.cat((state, action), -1)
     nxt = odeint(node, y0, torch.tensor([0.0, dt]), method=solver, atol=1e-7, rtol=1e-5)[-1]
     ps_next = lookahead(nxt[:, :3], l_p)
-    V_next = lya(ps_next)
-    lya_term = (V_next - V) / dt + gamma_l * V
     hs = 0.5 * (((ps[:, None, :] - hz[None]) ** 2).sum(2) - rc ** 2)
     hs_next = 0.5 * (((ps_next[:, None, :] - hz[None]) ** 2).sum(2) - rc ** 2)
     cbf = -((hs_next - hs) / dt) - gamma_b * hs
+    if lya is None:   # backup_get_policy_loss_2 (U :532-608): CBF rows only
+        return required_matrix_from_rows(cbf, batch_size)
+    V_next = lya(ps_next)
+    lya_term = (V_next - V) / dt + gamma_l * V
     return required_matrix_from_rows(torch.cat((cbf, lya_term), 1), batch_size)
 
 
@@ -101,14 +103,16 @@ def cars_required_matrix(node, lya, policy, state, action, V, t_batch, next_t_ba
     obs1 = get_obs("SimulatedCars", x1).detach()
     pi_next = policy.sample(obs1, eps_next)[0].detach()
     x2 = odeint(node, torch.cat((x1, pi_next, next_t_batch), -1), tspan, method=solver, atol=1e-7, rtol=1e-5)[-1][:, :10]
-    V_next = lya(x1[:, 4:8])
-    lya_term = (V_next - V) + gamma_l * V
     rows = []
     for ia, ib in ((4, 6), (6, 8)):
         h0, h1, h2 = (x[:, ia:ia + 1] - x[:, ib:ib + 1] - r for x in (state, x1, x2))
         l1 = h1 - h0 + gamma_b * h0
         l2 = h2 - h1 + gamma_b * h1
         rows.append(-(l2 - l1) - gamma_b * l1)
+    if lya is None:   # backup_get_policy_loss_2 (C :557-645): CBF rows only, `policy` is the backup policy
+        return required_matrix_from_rows(torch.cat(rows, 1), batch_size)
+    V_next = lya(x1[:, 4:8])
+    lya_term = (V_next - V) + gamma_l * V
     return required_matrix_from_rows(torch.cat(rows + [lya_term], 1), batch_size)
 
 
@@ -164,25 +168,49 @@ def pvtol_required_matrix(node, lya, policy, state, action, V, *, dt, gamma_b, h
     hz = torch.as_tensor(hazards, dtype=state.dtype, device=state.device)
     s1, s2, s3 = pvtol_rollout(node, policy, state, action, dt=dt, follow=follow, solver=solver, eps_next=eps_next,
                                eps_next_next=eps_next_next)
-    V_next = lya(get_obs("Pvtol", s1))
-    lya_term = (V_next - V) / 1.0 + gamma_l * V
     seq = (state, s1, s2, s3)
     hs = [0.5 * (((s[:, None, :2] - hz[None]) ** 2).sum(2) - rc ** 2) for s in seq]
     rows = [third_order_cbf(*hs, gamma_b)]
     for f in (lambda s: s[:, 0:1] - s[:, 6:7] + od, lambda s: -s[:, 0:1] + s[:, 6:7] + od,
               lambda s: -s[:, 1:2] + y_max - delta_y, lambda s: s[:, 1:2] - y_min - delta_y):
         rows.append(third_order_cbf(*[f(s) for s in seq], gamma_b))
+    if lya is None:   # backup_get_policy_loss_2 (P :740-1010): CBF rows only, `policy` is the backup policy
+        return required_matrix_from_rows(torch.cat(rows, 1), batch_size)
+    V_next = lya(get_obs("Pvtol", s1))
+    lya_term = (V_next - V) / 1.0 + gamma_l * V
     return required_matrix_from_rows(torch.cat(rows + [lya_term], 1), batch_size)
 
 
 class ConstraintState:
     """lambda / rho bookkeeping of the agent (U sac_cbf_clf.py:55-62)."""
 
-    def __init__(self, num_constraints, lambda_max=400.0, ratio_floor=None, use_ratio=True, interval=8):
+    def __init__(self, num_constraints, lambda_max=400.0, ratio_floor=None, use_ratio=True, interval=8,
+                 backup_update_interval=1, separate_backup_rho=False):
         self.lambda_values = [0.0] * num_constraints
+        self.backup_lambda_values = [0.0] * (num_constraints - 1)
         self.num_constraints = num_constraints
         self.augmented_term, self.augmented_ratio, self.cost_limit = 1.0, 1.0005, 0.0
+        self.backup_augmented_term = 1.0
         self.lambda_max, self.ratio_floor, self.use_ratio, self.interval = lambda_max, ratio_floor, use_ratio, interval
+        self.backup_update_interval, self.separate_backup_rho = backup_update_interval, separate_backup_rho
+
+
+def backup_augmented_lagrangian(req, st, updates):
+    """U sac_cbf_clf.py:611-640, C :657-681 (shared rho); P :1022-1045 (its own rho, multipliers updated every
+    ``interval * backup_update_interval`` steps).  No ratio: every row enters with its own multiplier."""
+    rho_name = "backup_augmented_term" if st.separate_backup_rho else "augmented_term"
+    rc = req.detach()
+    if updates % (st.interval * st.backup_update_interval) == 0:
+        for i in range(len(st.backup_lambda_values)):
+            st.backup_lambda_values[i] = torch.clamp(st.backup_lambda_values[i] + getattr(st, rho_name) * rc[i], 0.01,
+                                                     st.lambda_max)
+    setattr(st, rho_name, min(getattr(st, rho_name) * st.augmented_ratio, 200))
+    rho = getattr(st, rho_name)
+    loss = 0.0
+    for i in range(req.shape[0]):
+        c = req[i] - st.cost_limit
+        loss = loss + float(st.backup_lambda_values[i]) * c + rho / 2.0 * c * c
+    return loss
 
 
 def augmented_lagrangian(req, st, updates):

@@ -17,8 +17,10 @@ def build(g, lib, device):
         node = lib.BlackBoxNODE(12, 10) if is_oracle else lib.NeuralODEModel(12, 10)
         lya = lib.LyaNetwork(4, 256)
     node.load_state_dict(g["node"])
-    lya.load_state_dict(g["lya"])
-    nets = {"node": node.to(device), "lya": lya.to(device)}
+    nets = {"node": node.to(device)}
+    if "lya" in g:        # the backup-loss goldens have no Lyapunov net
+        lya.load_state_dict(g["lya"])
+        nets["lya"] = lya.to(device)
     if "policy" in g:
         n_o, n_u, hi = (10, 1, [3.0]) if tag == "C" else ((11, 2, [3.5, 15.0]) if tag == "P" else (7, 2, [3.5, 12.0]))
         if is_oracle:
@@ -96,6 +98,53 @@ def run_sequence(g, nets, C, device, dyn=None):
                                                          obs, state, action, V, dt=k["dt"], gamma_b=k["gamma_b"],
                                                          l_p=k["l_p"], batch_size=B, eps_next=eps)
         loss = C.augmented_lagrangian(req, st, updates)
+        loss.backward()
+        losses.append(loss.detach().reshape(-1).cpu())
+        grads.append(action.grad.detach().cpu().clone())
+    return losses, grads, st
+
+
+def run_backup_sequence(g, nets, C, device, dyn=None):
+    """backup_get_policy_loss_2 twice (updates 8, 9) as the constraints_backup_*.pt goldens recorded it: CBF rows
+    only, the backup policy re-samples, separate multipliers (P: separate rho)."""
+    tag, B, k = g["tag"], g["B"], g["consts"]
+    is_oracle = "batch_size" not in C.ConstraintState.__init__.__code__.co_varnames
+    state = g["state"].to(device)
+    action = g["action"].clone().to(device).requires_grad_(True)
+    n_con = {"U": 8, "C": 3, "P": 10}[tag]
+    kw_st = {"C": dict(lambda_max=300.0), "P": dict(separate_backup_rho=True, backup_update_interval=1)}.get(tag, {})
+    st = C.ConstraintState(n_con, **kw_st) if is_oracle else C.ConstraintState(n_con, B, **kw_st)
+    eps = g["eps"].to(device) if "eps" in g else None
+    losses, grads = [], []
+    for updates in (8, 9):
+        action.grad = None
+        if tag == "U":
+            kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_radius=k["hazards_radius"], l_p=k["l_p"], batch_size=B)
+            if is_oracle:
+                req = C.unicycle_required_matrix(nets["node"], None, state, action, None, hazards=k["hazards"], **kw)
+            else:
+                req = C.unicycle_required_matrix(nets["node"], None, state, action, None,
+                                                 hazards_locations=k["hazards"], **kw)
+        elif tag == "C":
+            t, t1 = g["t"].to(device), g["t_next"].to(device)
+            args = (state, action, None, t, t1)
+            kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], batch_size=B, eps_next=eps)
+            if is_oracle:
+                req = C.cars_required_matrix(nets["node"], None, nets["policy"], *args, **kw)
+            else:
+                req = C.cars_required_matrix(nets["node"], None, nets["policy"], dyn, *args, **kw)
+        else:
+            kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_radius=k["hazards_radius"],
+                      operator_dist=k["operator_dist"], y_max=k["y_max"], y_min=k["y_min"], batch_size=B,
+                      eps_next=eps, eps_next_next=eps)
+            if is_oracle:
+                req = C.pvtol_required_matrix(nets["node"], None, nets["policy"], state, action, None,
+                                              hazards=k["hazards"], follow=k["safety_operator_follow"], **kw)
+            else:
+                req = C.pvtol_required_matrix(nets["node"], None, nets["policy"], dyn, state, action, None,
+                                              hazard_locations=k["hazards"],
+                                              safety_operator_follow=k["safety_operator_follow"], **kw)
+        loss = C.backup_augmented_lagrangian(req, st, updates)
         loss.backward()
         losses.append(loss.detach().reshape(-1).cpu())
         grads.append(action.grad.detach().cpu().clone())

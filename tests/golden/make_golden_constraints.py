@@ -77,7 +77,19 @@ def _sd(m):
     return {k: v.clone() for k, v in m.state_dict().items()}
 
 
-def case_U(B=128):
+def _run_twice(action, call):
+    losses, grads = [], []
+    for updates in (8, 9):
+        if action.grad is not None:
+            action.grad = None
+        loss = call(updates)
+        loss.backward()
+        losses.append(loss.detach().clone())
+        grads.append(action.grad.clone())
+    return losses, grads
+
+
+def case_U(B=128, backup=False):
     model, agent_mod, dyn_mod = import_variant("U")
     gen = torch.Generator().manual_seed(321)
     torch.manual_seed(3)
@@ -97,6 +109,14 @@ def case_U(B=128):
     dm = dyn_mod.DynamicsModel(env, _Args())
     state_from_obs = dm.get_state(obs)
     V = lya(agent_mod.l_p * torch.stack([torch.cos(state[:, 2]), torch.sin(state[:, 2])], 1) + state[:, :2]).detach()
+    if backup:   # U sac_cbf_clf.py:532-640: CBF rows only, separate multipliers
+        a.backup_lambda_values = [0.0] * a.num_cbfs
+        losses, grads = _run_twice(action, lambda u: a.backup_get_policy_loss_2(state, action, u))
+        return {"tag": "U", "B": B, "node": _sd(node), "state": state, "action": action.detach(), "losses": losses,
+                "grad_action": grads, "lambda_after": [float(v) for v in a.backup_lambda_values],
+                "augmented_term_after": a.augmented_term,
+                "consts": {"dt": 0.02, "gamma_b": 50.0, "hazards": env.hazards_locations, "hazards_radius": 0.5,
+                           "l_p": 0.03}}
     losses, grads = [], []
     for updates in (8, 9):
         if action.grad is not None:
@@ -112,7 +132,7 @@ def case_U(B=128):
                        "l_p": 0.03}}
 
 
-def case_C(B=256):
+def case_C(B=256, backup=False):
     model, agent_mod, dyn_mod = import_variant("C")
     gen = torch.Generator().manual_seed(322)
     torch.manual_seed(4)
@@ -140,6 +160,16 @@ def case_C(B=256):
     # all-inactive CLF row the reference's own ratio is inf and its loss NaN)
     lv = lya(state[:, 4:8]).detach()
     V = lv + 0.3 * lv.abs().mean() * torch.randn(B, 1, generator=gen)
+    if backup:   # C sac_cbf_clf.py:557-681: CBF rows only, the BACKUP policy re-samples u_{t+1}
+        bpol = model.GaussianPolicy(10, 1, 256, _Box([-3.0], [3.0]))
+        _perturb_biases(bpol, gen)
+        a.backup_policy, a.backup_lambda_values = bpol, [0.0] * a.num_cbfs
+        losses, grads = _run_twice(action, lambda u: _with_eps(
+            eps, lambda: a.backup_get_policy_loss_2(dm, state, action, tk, tk1, u)))
+        return {"tag": "C", "B": B, "node": _sd(node), "policy": _sd(bpol), "state": state, "action": action.detach(),
+                "t": tk, "t_next": tk1, "eps": eps, "losses": losses, "grad_action": grads,
+                "lambda_after": [float(v) for v in a.backup_lambda_values], "augmented_term_after": a.augmented_term,
+                "consts": {"dt": 0.02, "gamma_b": 0.5}}
     losses, grads = [], []
     for updates in (8, 9):
         if action.grad is not None:
@@ -215,7 +245,7 @@ def case_P_maps(B=64):
             "state_from_obs": st, "state_dyn_from_obs": st_dyn}
 
 
-def case_P(B=256):
+def case_P(B=256, backup=False):
     """PVTOL: 3-step NODE rollout with two policy re-samples, 5 hazard + 4 box/operator third-order CBF rows + CLF
     (P sac_cbf_clf.py:424-738), run by the reference's own method."""
     model, agent_mod, dyn_mod = import_variant("P")
@@ -251,6 +281,21 @@ def case_P(B=256):
     obs = dm.get_obs(state.unsqueeze(-1), torch.device("cpu")).squeeze(-1).detach()
     lv = lya(obs).detach()
     V = lv + 0.3 * lv.abs().mean() * torch.randn(B, 1, generator=gen)
+    consts = {"dt": 0.02, "gamma_b": 0.6, "hazards": env.hazard_locations, "hazards_radius": 0.25,
+              "safety_operator_follow": 0.7, "operator_dist": 0.001, "y_max": 13.0, "y_min": -13.0}
+    if backup:   # P sac_cbf_clf.py:740-1045: CBF rows only, the BACKUP policy re-samples u_{t+1}, u_{t+2}
+        bpol = model.GaussianPolicy(11, 2, 256, _Box([-3.5, -15.0], [3.5, 15.0]))
+        _perturb_biases(bpol, gen)
+        a.backup_policy, a.backup_lambda_values = bpol, [0.0] * a.num_cbfs
+        # P keeps a separate rho for the backup loss and updates its multipliers every
+        # Lagrangian_multiplier_update_interval * backup_update_interval steps (:1025-1034)
+        a.backup_update_interval, a.backup_augmented_term = 1, 1.0
+        losses, grads = _run_twice(action, lambda u: _with_eps(
+            eps, lambda: a.backup_get_policy_loss_2(dm, state, action, u, state[:, :6])))
+        return {"tag": "P", "B": B, "node": _sd(node), "policy": _sd(bpol), "state": state, "action": action.detach(),
+                "eps": eps, "losses": losses, "grad_action": grads,
+                "lambda_after": [float(v) for v in a.backup_lambda_values],
+                "augmented_term_after": a.backup_augmented_term, "consts": consts}
     losses, grads = [], []
     for updates in (8, 9):
         if action.grad is not None:
@@ -270,6 +315,9 @@ def main():
     for name, fn in (("U", case_U), ("C", case_C), ("BU", case_BU), ("Pmaps", case_P_maps), ("P", case_P)):
         torch.save(fn(), os.path.join(HERE, "constraints_%s.pt" % name))
         print("constraints", name, "ok")
+    for name, fn in (("U", case_U), ("C", case_C), ("P", case_P)):
+        torch.save(fn(backup=True), os.path.join(HERE, "constraints_backup_%s.pt" % name))
+        print("backup constraints", name, "ok")
 
 
 if __name__ == "__main__":

@@ -7,7 +7,7 @@ import torch
 
 from oracle import constraints as OC
 from oracle import nlbac_ref
-from constraint_cases import build, run_sequence
+from constraint_cases import build, run_backup_sequence, run_sequence
 
 
 def _close(a, b, rtol=2e-5, atol=1e-6):
@@ -26,6 +26,20 @@ def test_policy_loss_2_matches_reference(tag, golden_dir):
         assert _close(got, want, rtol=1e-4), (got - want).abs().max()
     assert torch.allclose(torch.tensor([float(v) for v in st.lambda_values]), torch.tensor(g["lambda_after"]), rtol=1e-5)
     assert abs(st.augmented_term - g["augmented_term_after"]) < 1e-12
+
+
+@pytest.mark.parametrize("tag", ["U", "C", "P"])
+def test_backup_policy_loss_2_matches_reference(tag, golden_dir):
+    g = torch.load(os.path.join(golden_dir, "constraints_backup_%s.pt" % tag), weights_only=False)
+    losses, grads, st = run_backup_sequence(g, build(g, nlbac_ref, "cpu"), OC, "cpu")
+    for got, want in zip(losses, g["losses"]):
+        assert _close(got, want.reshape(-1)), (got, want)
+    for got, want in zip(grads, g["grad_action"]):
+        assert _close(got, want, rtol=1e-4, atol=1e-10), (got - want).abs().max()
+    assert torch.allclose(torch.tensor([float(v) for v in st.backup_lambda_values]), torch.tensor(g["lambda_after"]),
+                          rtol=1e-5)
+    rho = st.backup_augmented_term if tag == "P" else st.augmented_term
+    assert abs(rho - g["augmented_term_after"]) < 1e-12
 
 
 @pytest.mark.parametrize("tag,env", [("U", "Unicycle"), ("C", "SimulatedCars"), ("BU", "Unicycle")])
