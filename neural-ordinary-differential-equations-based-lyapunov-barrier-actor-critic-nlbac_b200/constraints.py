@@ -143,6 +143,25 @@ def barrier_unicycle_required_matrix(neural_ode_model, lyapunovNet, BarrierNet, 
     return constraint_sums(desc, barrier_value, barrier_next, None, lyapunov_value.detach(), lyapunov_value_next)
 
 
+def barrier_pvtol_required_matrix(neural_ode_model, lyapunovNet, BarrierNet, policy, dynamics_model, obs_batch,
+                                  state_batch, action_batch, lyapunov_value, state_dynamics_batch=None, *, dt, gamma_b,
+                                  safety_operator_follow, batch_size, solver="euler", gamma_l=0.1, eps_next=None):
+    """BP sac_cbf_clf.py:373-438: PVTOL with a learned barrier certificate; ``required_matrix`` [2, 1]."""
+    if state_dynamics_batch is None:
+        state_dynamics_batch = state_batch[:, :6]
+    nxt = odeint(neural_ode_model, torch.cat((state_dynamics_batch, action_batch), dim=-1), [0.0, dt], method=solver,
+                 atol=1e-7, rtol=1e-5)[-1][:, :6]
+    op = state_batch[:, 6] + safety_operator_follow * (nxt[:, 0] - state_batch[:, 6])
+    next_obs = dynamics_model.get_obs(torch.cat((nxt, op[:, None]), dim=1))
+    lyapunov_value_next = lyapunovNet(next_obs)
+    pi_next, _, _ = policy.sample(next_obs.detach(), eps_next)
+    barrier_value = BarrierNet(obs_batch, action_batch).detach()
+    barrier_next = BarrierNet(next_obs, pi_next.detach())
+    desc = make_constraint_desc("barrier", dt=dt, gamma_b=gamma_b, gamma_l=gamma_l, batch_size=batch_size,
+                                lya_inv_dt=1.0)
+    return constraint_sums(desc, barrier_value, barrier_next, None, lyapunov_value.detach(), lyapunov_value_next)
+
+
 def pvtol_required_matrix(neural_ode_model, lyapunovNet, policy, dynamics_model, state_batch, action_batch,
                           lyapunov_value, state_dynamics_batch=None, *, dt, gamma_b, hazard_locations, hazards_radius,
                           safety_operator_follow, operator_dist, y_max, y_min, batch_size, solver="euler",

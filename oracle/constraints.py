@@ -131,6 +131,21 @@ def barrier_unicycle_required_matrix(node, lya, barrier, policy, obs, state, act
     return required_matrix_from_rows(torch.cat((barrier_term, lya_term), 1), batch_size)
 
 
+def barrier_pvtol_required_matrix(node, lya, barrier, policy, obs, state, action, V, *, dt, gamma_b, follow,
+                                  batch_size, solver="euler", gamma_l=0.1, eps_next=None):
+    """BP sac_cbf_clf.py:373-438."""
+    nxt = odeint(node, torch.cat((state[:, :6], action), -1), torch.tensor([0.0, dt]), method=solver, atol=1e-7,
+                 rtol=1e-5)[-1][:, :6]
+    op = state[:, 6] + follow * (nxt[:, 0] - state[:, 6])
+    next_obs = get_obs("Pvtol", torch.cat((nxt, op[:, None]), 1))
+    lya_term = (lya(next_obs) - V) / 1.0 + gamma_l * V
+    pi_next = policy.sample(next_obs.detach(), eps_next)[0].detach()
+    b_now = barrier(obs, action).detach()
+    b_next = barrier(next_obs, pi_next)
+    barrier_term = -(b_next - b_now) - gamma_b * b_now
+    return required_matrix_from_rows(torch.cat((barrier_term, lya_term), 1), batch_size)
+
+
 def third_order_cbf(h0, h1, h2, h3, gamma_b):
     """P sac_cbf_clf.py:581-587 (same expression for every P row): a discrete third-order CBF condition."""
     t1 = h3 - h2 + gamma_b * h2

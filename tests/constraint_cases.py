@@ -10,7 +10,7 @@ def build(g, lib, device):
     if tag in ("U", "BU"):
         node = lib.AffineNODE(3, 3, 6) if is_oracle else lib.NeuralODEModel(3, 3, 6)
         lya = lib.LyaNetwork(2, 256)
-    elif tag == "P":
+    elif tag in ("P", "BP"):
         node = lib.AffineNODE(6, 6, 12) if is_oracle else lib.NeuralODEModel(6, 6, 12)
         lya = lib.LyaNetwork(11, 256)
     else:
@@ -22,7 +22,7 @@ def build(g, lib, device):
         lya.load_state_dict(g["lya"])
         nets["lya"] = lya.to(device)
     if "policy" in g:
-        n_o, n_u, hi = (10, 1, [3.0]) if tag == "C" else ((11, 2, [3.5, 15.0]) if tag == "P" else (7, 2, [3.5, 12.0]))
+        n_o, n_u, hi = (10, 1, [3.0]) if tag == "C" else ((11, 2, [3.5, 15.0]) if tag in ("P", "BP") else (7, 2, [3.5, 12.0]))
         if is_oracle:
             pol = lib.GaussianPolicy(n_o, n_u, 256, hi, [-h for h in hi])
         else:
@@ -35,7 +35,7 @@ def build(g, lib, device):
         pol.load_state_dict(g["policy"])
         nets["policy"] = pol.to(device)
     if "barrier" in g:
-        bar = lib.BarrierNetwork(7, 2, 256)
+        bar = lib.BarrierNetwork(11 if tag == "BP" else 7, 2, 256)
         bar.load_state_dict(g["barrier"])
         nets["barrier"] = bar.to(device)
     return nets
@@ -55,13 +55,25 @@ def run_sequence(g, nets, C, device, dyn=None):
               else C.ConstraintState(3, B, lambda_max=300.0, ratio_floor=0.002))
     elif tag == "P":      # P sac_cbf_clf.py:707-708 (floor 0.002), :718 (clamp 400)
         st = (C.ConstraintState(10, ratio_floor=0.002) if is_oracle else C.ConstraintState(10, B, ratio_floor=0.002))
+    elif tag == "BP":     # BP sac_cbf_clf.py:441-447 (ratio with the 0.002 floor)
+        st = C.ConstraintState(2, ratio_floor=0.002) if is_oracle else C.ConstraintState(2, B, ratio_floor=0.002)
     else:
         st = C.ConstraintState(2, use_ratio=False) if is_oracle else C.ConstraintState(2, B, use_ratio=False)
     eps = g["eps"].to(device) if "eps" in g else None
     losses, grads = [], []
     for updates in (8, 9):
         action.grad = None
-        if tag == "U":
+        if tag == "BP":
+            obs = g["obs"].to(device)
+            kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], batch_size=B, eps_next=eps)
+            if is_oracle:
+                req = C.barrier_pvtol_required_matrix(nets["node"], nets["lya"], nets["barrier"], nets["policy"], obs,
+                                                      state, action, V, follow=k["safety_operator_follow"], **kw)
+            else:
+                req = C.barrier_pvtol_required_matrix(nets["node"], nets["lya"], nets["barrier"], nets["policy"], dyn,
+                                                      obs, state, action, V,
+                                                      safety_operator_follow=k["safety_operator_follow"], **kw)
+        elif tag == "U":
             kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_radius=k["hazards_radius"], l_p=k["l_p"], batch_size=B)
             if is_oracle:
                 req = C.unicycle_required_matrix(nets["node"], nets["lya"], state, action, V, hazards=k["hazards"], **kw)

@@ -311,8 +311,44 @@ def case_P(B=256, backup=False):
                        "safety_operator_follow": 0.7, "operator_dist": 0.001, "y_max": 13.0, "y_min": -13.0}}
 
 
+def case_BP(B=256):
+    """Learned-barrier PVTOL (BP sac_cbf_clf.py:360-472): one NODE step + operator follow, barrier net on the
+    predicted observation with the re-sampled action, CLF row; ratio floor 0.002."""
+    model, agent_mod, dyn_mod = import_variant("BP")
+    gen = torch.Generator().manual_seed(326)
+    torch.manual_seed(7)
+    env = _Env()
+    env.dynamics_mode, env.dt, env.safety_operator_follow = "Pvtol", 0.02, 0.7
+    node = model.NeuralODEModel(6, 6, 12)
+    lya = model.LyaNetwork(11, 256)
+    bar = model.BarrierNetwork(11, 2, 256)
+    pol = model.GaussianPolicy(11, 2, 256, _Box([-3.5, -15.0], [3.5, 15.0]))
+    for n in (lya, bar, pol):
+        _perturb_biases(n, gen)
+    a = _agent(agent_mod, env, gamma_b=0.6, batch_size=B, num_cbfs=1, num_constraints=2, neural_ode_model=node,
+               lyapunovNet=lya, BarrierNet=bar, policy=pol)
+    r = lambda *s: torch.rand(*s, generator=gen)  # noqa: E731
+    x = r(B) * 14 - 7
+    state = torch.stack([x, r(B) * 12 - 6, (r(B) * 2 - 1) * np.pi, r(B) * 4 - 2, r(B) * 4 - 2, r(B) * 2,
+                         x + (r(B) * 3 - 1.5)], 1)
+    action = torch.stack([r(B) * 7 - 3.5, r(B) * 30 - 15], 1).requires_grad_(True)
+    eps = torch.randn(B, 2, generator=gen)
+    dm = dyn_mod.DynamicsModel(env, _Args())
+    obs = dm.get_obs(state.unsqueeze(-1), torch.device("cpu")).squeeze(-1).detach()
+    lv = lya(obs).detach()
+    V = lv + 0.3 * lv.abs().mean() * torch.randn(B, 1, generator=gen)
+    losses, grads = _run_twice(action, lambda u: _with_eps(
+        eps, lambda: a.get_policy_loss_2(obs, dm, state, action, V, u, state[:, :6])))
+    return {"tag": "BP", "B": B, "node": _sd(node), "lya": _sd(lya), "barrier": _sd(bar), "policy": _sd(pol),
+            "state": state, "action": action.detach(), "V": V, "eps": eps, "obs": obs, "losses": losses,
+            "grad_action": grads, "lambda_after": [float(v) for v in a.lambda_values],
+            "augmented_term_after": a.augmented_term,
+            "consts": {"dt": 0.02, "gamma_b": 0.6, "safety_operator_follow": 0.7}}
+
+
 def main():
-    for name, fn in (("U", case_U), ("C", case_C), ("BU", case_BU), ("Pmaps", case_P_maps), ("P", case_P)):
+    for name, fn in (("U", case_U), ("C", case_C), ("BU", case_BU), ("Pmaps", case_P_maps), ("P", case_P),
+                     ("BP", case_BP)):
         torch.save(fn(), os.path.join(HERE, "constraints_%s.pt" % name))
         print("constraints", name, "ok")
     for name, fn in (("U", case_U), ("C", case_C), ("P", case_P)):

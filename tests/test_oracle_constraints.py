@@ -15,7 +15,7 @@ def _close(a, b, rtol=2e-5, atol=1e-6):
     return (a - b).abs().max().item() <= rtol * scale + atol
 
 
-@pytest.mark.parametrize("tag", ["U", "C", "BU", "P"])
+@pytest.mark.parametrize("tag", ["U", "C", "BU", "P", "BP"])
 def test_policy_loss_2_matches_reference(tag, golden_dir):
     g = torch.load(os.path.join(golden_dir, "constraints_%s.pt" % tag), weights_only=False)
     nets = build(g, nlbac_ref, "cpu")

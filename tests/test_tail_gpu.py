@@ -25,7 +25,8 @@ class _Env:
         self.dynamics_mode = mode
 
 
-@pytest.mark.parametrize("tag,env", [("U", "Unicycle"), ("C", "SimulatedCars"), ("BU", "Unicycle"), ("P", "Pvtol")])
+@pytest.mark.parametrize("tag,env", [("U", "Unicycle"), ("C", "SimulatedCars"), ("BU", "Unicycle"), ("P", "Pvtol"),
+                                     ("BP", "Pvtol")])
 def test_policy_loss_2_matches_reference_and_oracle(tag, env, golden_dir):
     import nlbac_b200
     g = torch.load(os.path.join(golden_dir, "constraints_%s.pt" % tag), weights_only=False)
