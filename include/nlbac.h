@@ -230,6 +230,16 @@ int nlbac_adam_step(float* param, const float* grad, float* exp_avg, float* exp_
                     float beta1, float beta2, float eps, void* stream);
 int nlbac_soft_update(float* target, const float* source, int64_t n, float tau, void* stream);
 
+/* Multi-tensor forms: ONE launch for all parameter tensors of an optimiser (same step count and hyper-parameters,
+ * as torch.optim.Adam keeps them per group) or of a target network (U sac_cbf_clf.py:249-290, 315-317).  The
+ * pointer arrays are HOST arrays of device pointers, n_tensors <= NLBAC_MAX_TENSORS. */
+#define NLBAC_MAX_TENSORS 32
+int nlbac_adam_step_multi(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
+                          float* const* exp_avg_sq, const int64_t* numels, int step, float lr, float beta1,
+                          float beta2, float eps, void* stream);
+int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* const* sources, const int64_t* numels,
+                            float tau, void* stream);
+
 /* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 tile.
  * mode 0 (kind::tf32, both operands K-major):   D[t][j] = sum_k X[t][k] Y[j][k],  X [128,104], Y [104,104];
  * mode 1 (kind::f16 on bf16 images, MN-major):  D[j][k] = sum_t X[t][j] Y[t][k],  X, Y [128,104].

@@ -23,6 +23,7 @@ class MlpDesc(ctypes.Structure):
 
 
 MAX_HAZARDS = 15
+MAX_TENSORS = 32
 
 
 class ConstraintDesc(ctypes.Structure):
@@ -119,6 +120,10 @@ def _declare(lib):
     lib.nlbac_get_obs_bwd.argtypes = [c.c_int, vp, i64, vp, vp, vp]
     lib.nlbac_adam_step.argtypes = [vp, vp, vp, vp, i64, c.c_int, c.c_float, c.c_float, c.c_float, c.c_float, vp]
     lib.nlbac_soft_update.argtypes = [vp, vp, i64, c.c_float, vp]
+    pvp, pi64 = c.POINTER(vp), c.POINTER(c.c_int64)
+    lib.nlbac_adam_step_multi.argtypes = [c.c_int, pvp, pvp, pvp, pvp, pi64, c.c_int, c.c_float, c.c_float, c.c_float,
+                                          c.c_float, vp]
+    lib.nlbac_soft_update_multi.argtypes = [c.c_int, pvp, pvp, pi64, c.c_float, vp]
     lib.nlbac_umma_selftest.argtypes = [c.c_int, vp, vp, vp, vp]
     lib.nlbac_kernel_timing.argtypes = [c.c_int]
     lib.nlbac_kernel_timing_read.argtypes = [c.POINTER(c.c_double), c.POINTER(c.c_int)]

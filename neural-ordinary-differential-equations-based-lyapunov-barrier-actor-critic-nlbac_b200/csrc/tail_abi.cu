@@ -331,6 +331,35 @@ __global__ void soft_update_kernel(float* target, const float* src, long long n,
     target[i] = target[i] * (1.0f - tau) + src[i] * tau;
 }
 
+// multi-tensor forms: one launch for every parameter tensor of an optimiser / of a target network
+// (blockIdx.y = tensor; the pointer table travels in the kernel parameters)
+struct AdamTable {
+  float* p[NLBAC_MAX_TENSORS]; const float* g[NLBAC_MAX_TENSORS]; float* m[NLBAC_MAX_TENSORS];
+  float* v[NLBAC_MAX_TENSORS]; long long n[NLBAC_MAX_TENSORS];
+};
+struct PolyakTable { float* t[NLBAC_MAX_TENSORS]; const float* s[NLBAC_MAX_TENSORS]; long long n[NLBAC_MAX_TENSORS]; };
+__global__ void adam_multi_kernel(const __grid_constant__ AdamTable tb, float lr, float b1, float b2, float eps,
+                                  float bc1, float bc2_sqrt) {
+  const int k = blockIdx.y;
+  float* p = tb.p[k]; const float* g = tb.g[k]; float* m = tb.m[k]; float* v = tb.v[k];
+  const long long n = tb.n[k];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float mi = m[i] + (gi - m[i]) * (1.f - b1);
+    const float vi = fmaf(v[i], b2, (1.f - b2) * gi * gi);
+    m[i] = mi; v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = p[i] - (lr / bc1) * (mi / denom);
+  }
+}
+__global__ void soft_update_multi_kernel(const __grid_constant__ PolyakTable tb, float tau) {
+  const int k = blockIdx.y;
+  float* t = tb.t[k]; const float* s = tb.s[k];
+  const long long n = tb.n[k];
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    t[i] = t[i] * (1.0f - tau) + s[i] * tau;
+}
+
 static int check_constraint(const nlbac_constraint_desc* d) {
   NLBAC_REQUIRE(d != nullptr, "null constraint descriptor");
   NLBAC_REQUIRE(d->kind >= NLBAC_CONSTRAINT_UNICYCLE && d->kind <= NLBAC_CONSTRAINT_PVTOL, "unknown constraint kind %d", d->kind);
@@ -440,6 +469,44 @@ int nlbac_adam_step(float* param, const float* grad, float* exp_avg, float* exp_
   const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
   adam_kernel<<<tail_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, lr, beta1, beta2,
                                                                    eps, (float)bc1, (float)sqrt(bc2));
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+int nlbac_adam_step_multi(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
+                          float* const* exp_avg_sq, const int64_t* numels, int step, float lr, float beta1,
+                          float beta2, float eps, void* stream) {
+  NLBAC_REQUIRE(n_tensors >= 0 && n_tensors <= NLBAC_MAX_TENSORS, "n_tensors=%d (max %d)", n_tensors, NLBAC_MAX_TENSORS);
+  NLBAC_REQUIRE(params && grads && exp_avg && exp_avg_sq && numels && step >= 1, "bad arguments");
+  if (n_tensors == 0) return 0;
+  AdamTable tb;
+  long long nmax = 0;
+  for (int k = 0; k < n_tensors; ++k) {
+    NLBAC_REQUIRE(numels[k] >= 0 && (numels[k] == 0 || (params[k] && grads[k] && exp_avg[k] && exp_avg_sq[k])),
+                  "tensor %d: null pointer", k);
+    tb.p[k] = params[k]; tb.g[k] = grads[k]; tb.m[k] = exp_avg[k]; tb.v[k] = exp_avg_sq[k]; tb.n[k] = numels[k];
+    if (numels[k] > nmax) nmax = numels[k];
+  }
+  if (nmax == 0) return 0;
+  const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
+  adam_multi_kernel<<<dim3(tail_grid(nmax, 256), n_tensors), 256, 0, (cudaStream_t)stream>>>(tb, lr, beta1, beta2, eps,
+                                                                                          (float)bc1, (float)sqrt(bc2));
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* const* sources, const int64_t* numels,
+                            float tau, void* stream) {
+  NLBAC_REQUIRE(n_tensors >= 0 && n_tensors <= NLBAC_MAX_TENSORS, "n_tensors=%d (max %d)", n_tensors, NLBAC_MAX_TENSORS);
+  NLBAC_REQUIRE(targets && sources && numels, "bad arguments");
+  if (n_tensors == 0) return 0;
+  PolyakTable tb;
+  long long nmax = 0;
+  for (int k = 0; k < n_tensors; ++k) {
+    NLBAC_REQUIRE(numels[k] >= 0 && (numels[k] == 0 || (targets[k] && sources[k])), "tensor %d: null pointer", k);
+    tb.t[k] = targets[k]; tb.s[k] = sources[k]; tb.n[k] = numels[k];
+    if (numels[k] > nmax) nmax = numels[k];
+  }
+  if (nmax == 0) return 0;
+  soft_update_multi_kernel<<<dim3(tail_grid(nmax, 256), n_tensors), 256, 0, (cudaStream_t)stream>>>(tb, tau);
   NLBAC_CUDA(cudaGetLastError());
   return 0;
 }

@@ -221,6 +221,7 @@ class FusedAdam(torch.optim.Optimizer):
         L = _lib.lib()
         for group in self.param_groups:
             b1, b2 = group["betas"]
+            by_step = {}
             for p in group["params"]:
                 if p.grad is None:
                     continue
@@ -232,20 +233,41 @@ class FusedAdam(torch.optim.Optimizer):
                     st["exp_avg"] = torch.zeros_like(p)
                     st["exp_avg_sq"] = torch.zeros_like(p)
                 st["step"] += 1
-                g = p.grad.contiguous()
-                _lib.check(L.nlbac_adam_step(p.data_ptr(), g.data_ptr(), st["exp_avg"].data_ptr(),
-                                             st["exp_avg_sq"].data_ptr(), p.numel(), st["step"], group["lr"], b1, b2,
-                                             group["eps"], _stream()), "adam_step")
-                torch.autograd.graph.increment_version(p)   # written through a raw pointer: invalidate caches
+                by_step.setdefault(st["step"], []).append((p, p.grad.contiguous(), st))
+            # one launch per (group, step count): normally ONE launch for the whole network
+            for step, items in by_step.items():
+                for lo in range(0, len(items), _lib.MAX_TENSORS):
+                    chunk = items[lo:lo + _lib.MAX_TENSORS]
+                    n = len(chunk)
+                    arr = lambda xs: (ctypes.c_void_p * n)(*xs)  # noqa: E731
+                    _lib.check(L.nlbac_adam_step_multi(
+                        n, arr([p.data_ptr() for p, _, _ in chunk]), arr([g.data_ptr() for _, g, _ in chunk]),
+                        arr([s["exp_avg"].data_ptr() for _, _, s in chunk]),
+                        arr([s["exp_avg_sq"].data_ptr() for _, _, s in chunk]),
+                        (ctypes.c_int64 * n)(*[p.numel() for p, _, _ in chunk]), step, group["lr"], b1, b2,
+                        group["eps"], _stream()), "adam_step_multi")
+                    for p, _, _ in chunk:
+                        torch.autograd.graph.increment_version(p)   # written through raw pointers: invalidate caches
 
 
 @torch.no_grad()
 def soft_update(target, source, tau):
-    """``utils.soft_update(target, source, tau)`` (U utils.py:75-79)."""
+    """``utils.soft_update(target, source, tau)`` (U utils.py:75-79): one launch for the whole network."""
     L = _lib.lib()
-    for tp, sp in zip(target.parameters(), source.parameters()):
-        _lib.check(L.nlbac_soft_update(tp.data_ptr(), sp.data_ptr(), tp.numel(), float(tau), _stream()), "soft_update")
-        torch.autograd.graph.increment_version(tp)
+    pairs = list(zip(target.parameters(), source.parameters()))
+    for lo in range(0, len(pairs), _lib.MAX_TENSORS):
+        chunk = pairs[lo:lo + _lib.MAX_TENSORS]
+        n = len(chunk)
+        for tp, sp in chunk:
+            if not (tp.is_cuda and sp.is_cuda and tp.is_contiguous() and sp.is_contiguous()
+                    and tp.dtype == sp.dtype == torch.float32 and tp.numel() == sp.numel()):
+                raise RuntimeError("soft_update: parameters must be matching contiguous float32 CUDA tensors")
+        _lib.check(L.nlbac_soft_update_multi(
+            n, (ctypes.c_void_p * n)(*[tp.data_ptr() for tp, _ in chunk]),
+            (ctypes.c_void_p * n)(*[sp.data_ptr() for _, sp in chunk]),
+            (ctypes.c_int64 * n)(*[tp.numel() for tp, _ in chunk]), float(tau), _stream()), "soft_update_multi")
+        for tp, _ in chunk:
+            torch.autograd.graph.increment_version(tp)
 
 
 @torch.no_grad()

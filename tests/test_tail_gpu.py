@@ -183,6 +183,25 @@ def test_fused_adam_and_soft_update_match_torch():
     assert all(torch.equal(p, q) for p, q in zip(tgt_b.parameters(), a.parameters()))
 
 
+def test_multi_tensor_adam_chunks_and_ragged_sizes():
+    """40 tensors of different sizes (two launches of <= 32), one of them empty, one without a gradient."""
+    import nlbac_b200
+    torch.manual_seed(1)
+    shapes = [(i % 7 + 1, 3 * i + 1) for i in range(38)] + [(0,), (5,)]
+    pa = [torch.nn.Parameter(torch.randn(*s, device="cuda")) for s in shapes]
+    pb = [torch.nn.Parameter(p.detach().clone()) for p in pa]
+    oa, ob = torch.optim.Adam(pa, lr=3e-4), nlbac_b200.FusedAdam(pb, lr=3e-4)
+    for it in range(3):
+        for ps, opt in ((pa, oa), (pb, ob)):
+            opt.zero_grad()
+            torch.manual_seed(10 + it)
+            sum((p * torch.randn_like(p)).sum() for p in ps[:-1]).backward()     # last tensor: grad None
+            opt.step()
+    for p, q in zip(pa, pb):
+        assert p.numel() == 0 or _rel(q, p) <= 1e-6
+    assert torch.equal(pa[-1], pb[-1])
+
+
 def test_train_step_with_fused_adam_matches_golden(golden_dir):
     """train_step (zero_grad -> fused solve -> MSE -> fused backward -> Adam) with the fused optimiser reproduces
     the reference's own 3-step trace."""
