@@ -45,6 +45,9 @@ def parse():
                     help="tf32: tcgen05 kind::tf32 forward + reverse sweep, dW in bf16 (the 1e-2 tier of north_star); "
                          "fp32: exact FP32 FMA path (1e-5 tier); 3xtf32: split-TF32 forward (fp32-class) + FP32 backward")
     ap.add_argument("--cpu-sample", type=int, default=1024, help="trajectories in the CPU baseline sample")
+    ap.add_argument("--suite", default="headline", choices=["headline", "configs"],
+                    help="configs: latencies of the reference's real small-batch configurations 1-3 (SURVEY.md §8d) "
+                         "next to the same code run eagerly by PyTorch on the GPU and on the host cores")
     return ap.parse_args()
 
 
@@ -360,9 +363,119 @@ def run_reference(args):
         "e2e": {"value": val, "unit": "trajectory-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
+def run_configs(args):
+    """BASELINE.json configs[0..2] as the reference runs them (B = 128 / 256, one solver call per update): median
+    latency of forward + backward through the public API, in microseconds, for this library, for the reference's
+    model classes + restated torchdiffeq run eagerly by PyTorch on the same GPU, and for the same on the host cores."""
+    import statistics
+    import nlbac_b200
+    from oracle import nlbac_ref
+    from oracle.torchdiffeq_restated import odeint as oracle_odeint
+    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(dev)
+
+    def lat_gpu(fn, iters=50, warm=10):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(iters):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            fn()
+            e1.record()
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1) * 1e3)
+        return statistics.median(ts)
+
+    def lat_cpu(fn, iters=7, warm=2):
+        for _ in range(warm):
+            fn()
+        ts = []
+        for _ in range(iters):
+            t0 = time.perf_counter()
+            fn()
+            ts.append((time.perf_counter() - t0) * 1e6)
+        return statistics.median(ts)
+
+    def node_case(name, mk_ref, mk_ours, B, D, n_s, method, steps=1):
+        torch.manual_seed(0)
+        ref = mk_ref()
+        ours = mk_ours()
+        ours.load_state_dict(ref.state_dict())
+        ours.to(dev)
+        ref_gpu = mk_ref()
+        ref_gpu.load_state_dict(ref.state_dict())
+        ref_gpu.to(dev)
+        y_cpu = torch.rand(B, D) * 2 - 1
+        y_gpu = y_cpu.to(dev)
+        t = [DT * i for i in range(steps + 1)]
+        tt = torch.tensor(t)
+
+        def ours_fn():
+            sol = nlbac_b200.odeint(ours, y_gpu, t, method=method, atol=1e-7, rtol=1e-5)
+            torch.autograd.grad(sol[-1][:, :n_s].sum(), list(ours.parameters()))
+
+        def eager_fn(model, y, tv):
+            def f():
+                sol = oracle_odeint(model, y, tv, method=method, atol=1e-7, rtol=1e-5)
+                torch.autograd.grad(sol[-1][:, :n_s].sum(), list(model.parameters()))
+            return f
+
+        o = lat_gpu(ours_fn)
+        e = lat_gpu(eager_fn(ref_gpu, y_gpu, tt.to(dev)), iters=20, warm=3)
+        c = lat_cpu(eager_fn(ref, y_cpu, tt))
+        return {"case": name, "batch": B, "method": method, "solver_steps": steps, "ours_us": o,
+                "torch_eager_gpu_us": e, "torch_cpu_us": c, "speedup_vs_eager_gpu": e / o, "speedup_vs_cpu": c / o}
+
+    U = (lambda: nlbac_ref.AffineNODE(3, 3, 6), lambda: nlbac_b200.NeuralODEModel(3, 3, 6))
+    P = (lambda: nlbac_ref.AffineNODE(6, 6, 12), lambda: nlbac_b200.NeuralODEModel(6, 6, 12))
+    Cc = (lambda: nlbac_ref.BlackBoxNODE(12, 10), lambda: nlbac_b200.NeuralODEModel(12, 10))
+    rows = [node_case("config1 Unicycle predict", *U, 128, 5, 3, "euler"),
+            node_case("config1 Unicycle predict", *U, 128, 5, 3, "rk4"),
+            node_case("config1 Unicycle NODE batch", *U, 32768, 5, 3, "euler"),
+            node_case("config2 SimulatedCars predict", *Cc, 256, 12, 10, "euler"),
+            node_case("config3 PVTOL predict", *P, 256, 8, 6, "dopri5"),
+            node_case("config3 PVTOL predict", *P, 256, 8, 6, "rk4", 20)]
+
+    def mlp_case(name, mk_ref, mk_ours, B, n_in):
+        torch.manual_seed(0)
+        ref = mk_ref()
+        ours = mk_ours()
+        ours.load_state_dict(ref.state_dict())
+        ours.to(dev)
+        ref_gpu = mk_ref()
+        ref_gpu.load_state_dict(ref.state_dict())
+        ref_gpu.to(dev)
+        xs_cpu = [torch.randn(B, n) for n in n_in]
+        xs_gpu = [x.to(dev) for x in xs_cpu]
+
+        def run(model, xs):
+            def f():
+                out = model(*xs)
+                out = out if isinstance(out, tuple) else (out,)
+                torch.autograd.grad(sum(o.sum() for o in out), list(model.parameters()))
+            return f
+        o, e, c = lat_gpu(run(ours, xs_gpu)), lat_gpu(run(ref_gpu, xs_gpu), iters=20, warm=3), lat_cpu(run(ref, xs_cpu))
+        return {"case": name, "batch": B, "ours_us": o, "torch_eager_gpu_us": e, "torch_cpu_us": c,
+                "speedup_vs_eager_gpu": e / o, "speedup_vs_cpu": c / o}
+
+    rows += [mlp_case("config1 twin-Q fwd+bwd", lambda: nlbac_ref.QNetwork(7, 2, 256), lambda: nlbac_b200.QNetwork(7, 2, 256),
+                      128, (7, 2)),
+             mlp_case("config1 Lyapunov fwd+bwd", lambda: nlbac_ref.LyaNetwork(2, 256), lambda: nlbac_b200.LyaNetwork(2, 256),
+                      128, (2,)),
+             mlp_case("config2 twin-Q fwd+bwd", lambda: nlbac_ref.QNetwork(10, 1, 256), lambda: nlbac_b200.QNetwork(10, 1, 256),
+                      256, (10, 1))]
+    print(json.dumps({"suite": "configs", "unit": "microseconds per forward+backward call (median)", "cores": os.cpu_count(),
+                      "note": "B = 128/256 calls are launch-latency bound: one fused launch per direction vs ~90 eager "
+                              "launches (SURVEY.md §8 a3)", "rows": rows}))
+
+
 if __name__ == "__main__":
     a = parse()
-    if a.impl == "reference":
+    if a.suite == "configs":
+        run_configs(a)
+    elif a.impl == "reference":
         run_reference(a)
     else:
         run_ours(a)

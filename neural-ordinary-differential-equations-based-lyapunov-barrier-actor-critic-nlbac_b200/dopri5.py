@@ -40,7 +40,7 @@ class _Dopri5Solve(torch.autograd.Function):
             ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, t_arr.ctypes.data_as(fp), n_t, rtol, atol,
             max_steps, precision, y_out.data_ptr(), ckpt.data_ptr() if want_ckpt else None, ws.data_ptr(),
             ctypes.byref(n_acc), ctypes.byref(n_rej), step_dt.ctypes.data_as(fp), out_step.ctypes.data_as(ip),
-            out_x.ctypes.data_as(fp), torch.cuda.current_stream().cuda_stream), "node_dopri5_fwd")
+            out_x.ctypes.data_as(fp), _lib.raw_stream()), "node_dopri5_fwd")
         if stats is not None:
             stats.update(n_accepted=n_acc.value, n_rejected=n_rej.value, nfe=2 + 6 * (n_acc.value + n_rej.value),
                          step_dt=step_dt[:n_acc.value].copy())
@@ -69,7 +69,7 @@ class _Dopri5Solve(torch.autograd.Function):
             ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, n_t, n_acc, step_dt.ctypes.data_as(fp),
             out_step.ctypes.data_as(ip), out_x.ctypes.data_as(fp), precision, ckpt.data_ptr(), go.data_ptr(),
             gy0.data_ptr() if need_y0 else None, gflat.data_ptr() if need_p else None, ws.data_ptr(),
-            torch.cuda.current_stream().cuda_stream), "node_dopri5_bwd")
+            _lib.raw_stream()), "node_dopri5_bwd")
         grads = [None] * len(shapes)
         if need_p:
             off = 0

@@ -29,7 +29,7 @@ def _ptrs(tensors):
 
 
 def _stream():
-    return torch.cuda.current_stream().cuda_stream
+    return _lib.raw_stream()
 
 
 class _MLP3(torch.autograd.Function):

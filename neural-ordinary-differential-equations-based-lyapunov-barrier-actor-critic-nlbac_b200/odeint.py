@@ -63,6 +63,17 @@ def describe(func, D):
     return desc, params
 
 
+def _plan(func, D):
+    """``describe`` cached on the module (keyed by the input width and the identity of its parameters)."""
+    key = (D,) + tuple(id(p) for p in func.parameters())
+    cache = func.__dict__.get("_nlbac_plan")
+    if cache is not None and cache[0] == key:
+        return cache[1], cache[2]
+    desc, params = describe(func, D)
+    func.__dict__["_nlbac_plan"] = (key, desc, params)
+    return desc, params
+
+
 def _packed(func, desc, params, tc=False):
     """Packed kernel image of the parameters (FP32 image, or the tensor-core image with ``tc``), cached on the
     module until a parameter changes."""
@@ -79,7 +90,7 @@ def _packed(func, desc, params, tc=False):
         if p.dtype != torch.float32 or not p.is_contiguous():
             raise TypeError("nlbac_b200.odeint: parameters must be contiguous float32")
     _lib.check((L.nlbac_node_tc_pack if tc else L.nlbac_node_pack)(
-        ctypes.byref(desc), ptrs, packed.data_ptr(), torch.cuda.current_stream().cuda_stream), "node_pack")
+        ctypes.byref(desc), ptrs, packed.data_ptr(), _lib.raw_stream()), "node_pack")
     func.__dict__[slot] = (key, packed)
     return packed
 
@@ -114,7 +125,7 @@ class _FixedSolve(torch.autograd.Function):
         y_out = torch.empty((n_t, B, D), dtype=torch.float32, device=dev)
         _, tp = _farr(t_np)
         _, gp = _farr(grid_np)
-        st = torch.cuda.current_stream().cuda_stream
+        st = _lib.raw_stream()
         _lib.check(L.nlbac_node_solve_fwd(ctypes.byref(desc), packed_fwd.data_ptr(), y0c.data_ptr(), B, tp, n_t, gp,
                                           n_grid, method, precision, y_out.data_ptr(),
                                           ckpt.data_ptr() if want_ckpt else None, ws.data_ptr(), st), "node_solve_fwd")
@@ -122,14 +133,15 @@ class _FixedSolve(torch.autograd.Function):
             # backward tier: TF32 -> tensor-core reverse sweep (takes the tensor-core image); others -> FP32 sweep
             bprec = 2 if precision == 2 else 0
             ctx.save_for_backward(y0c, packed_fwd if bprec == 2 else packed, ckpt)
-            ctx.meta = (desc, t_np, grid_np, method, bprec, bwd.value, [p.shape for p in params])
+            ctx.meta = (desc, t_np, grid_np, method, bprec, bwd.value, [p.shape for p in params],
+                        [p.numel() for p in params])
         return y_out
 
     @staticmethod
     def backward(ctx, grad_out):
         L = _lib.lib()
         y0c, packed, ckpt = ctx.saved_tensors
-        desc, t_np, grid_np, method, precision, bwd_bytes, shapes = ctx.meta
+        desc, t_np, grid_np, method, precision, bwd_bytes, shapes, sizes = ctx.meta
         B, D = y0c.shape
         dev = y0c.device
         need_y0 = ctx.needs_input_grad[0]
@@ -146,18 +158,13 @@ class _FixedSolve(torch.autograd.Function):
         gy0 = torch.empty((B, D), dtype=torch.float32, device=dev) if need_y0 else None
         n_param = L.nlbac_node_param_count(ctypes.byref(desc))
         gflat = torch.empty(n_param, dtype=torch.float32, device=dev) if need_p else None
-        st = torch.cuda.current_stream().cuda_stream
+        st = _lib.raw_stream()
         _lib.check(L.nlbac_node_solve_bwd(ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, tp, len(t_np), gp,
                                           len(grid_np), method, precision, ckpt.data_ptr(), go.data_ptr(),
                                           gy0.data_ptr() if need_y0 else None,
                                           gflat.data_ptr() if need_p else None, ws.data_ptr(), st), "node_solve_bwd")
-        grads = []
         if need_p:
-            off = 0
-            for shp in shapes:
-                n = int(np.prod(shp))
-                grads.append(gflat[off:off + n].view(shp))
-                off += n
+            grads = [g if len(shp) == 1 else g.view(shp) for g, shp in zip(gflat.split_with_sizes(sizes), shapes)]
         else:
             grads = [None] * len(shapes)
         return (gy0, None, None, None, None, None, None, None, None, *grads)
@@ -194,7 +201,7 @@ def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, even
     if len(d) and (d < 0).all():
         raise NotImplementedError("nlbac_b200.odeint: decreasing t is not on the NLBAC path")
     options = dict(options or {})
-    desc, params = describe(func, y0.shape[1])
+    desc, params = _plan(func, y0.shape[1])
     L = _lib.lib()
     prec = PRECISIONS[precision]
     _lib.check(L.nlbac_node_supported(ctypes.byref(desc), prec), "node_supported")

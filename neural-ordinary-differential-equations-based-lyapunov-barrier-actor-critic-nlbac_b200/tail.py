@@ -20,7 +20,7 @@ _OBS_DIMS = {0: (7, 3), 1: (10, 10), 2: (11, 7)}
 
 
 def _stream():
-    return torch.cuda.current_stream().cuda_stream
+    return _lib.raw_stream()
 
 
 def _cuda32(*ts):
