@@ -51,6 +51,17 @@ __host__ __device__ __forceinline__ float tf32_hi(float x) {
 #endif
 }
 
+// Activation-side rounding.  cvt.rna.tf32.f32 costs four instructions per element (add, |x| >= inf test, select,
+// mask); on the hot path two cheaper forms give the same rounding for finite values:
+//   tf32_bias: bits + 0x1000  -- the MMA then drops the low 13 bits itself, which completes round-to-nearest
+//              (ties away from zero).  ONE instruction.  Inf / NaN inputs come out as NaN (a solve that has
+//              already overflowed), which the exact form would have preserved as Inf.
+//   tf32_rn:   (bits + 0x1000) & ~0x1FFF  -- exactly representable, needed where hi is subtracted again (3xTF32).
+__device__ __forceinline__ float tf32_bias(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
+__device__ __forceinline__ float tf32_rn(float x) {
+  return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
+}
+
 // weight image of one hidden matrix: W[j][k] (nn.Linear [out][in]) -> float index (k/4)*NP*4 + j*4 + k%4
 template <class C>
 __global__ void pack_tc_kernel(const float* __restrict__ W, float* __restrict__ hi, float* __restrict__ lo,
@@ -99,11 +110,11 @@ template <bool SPLIT, int ACH, int A_BYTES>
 __device__ __forceinline__ void store_act4(unsigned char* img, int r, int c, float v0, float v1, float v2, float v3) {
   unsigned char* p = img + (c >> 2) * ACH + (r >> 3) * 128 + (r & 7) * 16;
   if (SPLIT) {
-    const float h0 = tf32_hi(v0), h1 = tf32_hi(v1), h2 = tf32_hi(v2), h3 = tf32_hi(v3);
+    const float h0 = tf32_rn(v0), h1 = tf32_rn(v1), h2 = tf32_rn(v2), h3 = tf32_rn(v3);
     *reinterpret_cast<float4*>(p) = make_float4(h0, h1, h2, h3);
     *reinterpret_cast<float4*>(p + A_BYTES) = make_float4(v0 - h0, v1 - h1, v2 - h2, v3 - h3);
   } else {
-    *reinterpret_cast<float4*>(p) = make_float4(tf32_hi(v0), tf32_hi(v1), tf32_hi(v2), tf32_hi(v3));
+    *reinterpret_cast<float4*>(p) = make_float4(tf32_bias(v0), tf32_bias(v1), tf32_bias(v2), tf32_bias(v3));
   }
 }
 

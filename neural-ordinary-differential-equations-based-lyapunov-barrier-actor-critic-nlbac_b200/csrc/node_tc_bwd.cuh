@@ -262,25 +262,31 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
             v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
             float dl[8];
 #pragma unroll
+            for (int i = 0; i < 8; ++i) { v[i] = fmaxf(v[i], 0.f); dl[i] = 0.f; }
+            // d_{n+1}[k] = sum_o dOut[o] WL[o][k]: two 16-byte weight loads per output row and column group
+#pragma unroll
+            for (int o = 0; o < C::OUTP_MAX; ++o)
+              if (o < OUT) {
+                const float4 wa = *reinterpret_cast<const float4*>(WnL + o * C::HP + 8 * g8);
+                const float4 wb = *reinterpret_cast<const float4*>(WnL + o * C::HP + 8 * g8 + 4);
+                dl[0] = fmaf(dout[o], wa.x, dl[0]); dl[1] = fmaf(dout[o], wa.y, dl[1]);
+                dl[2] = fmaf(dout[o], wa.z, dl[2]); dl[3] = fmaf(dout[o], wa.w, dl[3]);
+                dl[4] = fmaf(dout[o], wb.x, dl[4]); dl[5] = fmaf(dout[o], wb.y, dl[5]);
+                dl[6] = fmaf(dout[o], wb.z, dl[6]); dl[7] = fmaf(dout[o], wb.w, dl[7]);
+              }
+#pragma unroll
             for (int i = 0; i < 8; ++i) {
               const int kk = 8 * g8 + i;
-              v[i] = fmaxf(v[i], 0.f);
-              float acc = 0.f;
-              if (kk < C::H) {
-                if (c == 1) {
+              if (c == 1 && kk < C::H) {
 #pragma unroll
-                  for (int o = 0; o < C::OUTP_MAX; o += 4)
-                    if (o < OUTP) {
-                      const float4 w = *reinterpret_cast<const float4*>(WtL + kk * OUTP + o);
-                      go[o] = fmaf(v[i], w.x, go[o]); go[o + 1] = fmaf(v[i], w.y, go[o + 1]);
-                      go[o + 2] = fmaf(v[i], w.z, go[o + 2]); go[o + 3] = fmaf(v[i], w.w, go[o + 3]);
-                    }
-                }
-#pragma unroll
-                for (int o = 0; o < C::OUTP_MAX; ++o)
-                  if (o < OUT) acc = fmaf(dout[o], WnL[o * C::HP + kk], acc);
+                for (int o = 0; o < C::OUTP_MAX; o += 4)
+                  if (o < OUTP) {
+                    const float4 w = *reinterpret_cast<const float4*>(WtL + kk * OUTP + o);
+                    go[o] = fmaf(v[i], w.x, go[o]); go[o + 1] = fmaf(v[i], w.y, go[o + 1]);
+                    go[o + 2] = fmaf(v[i], w.z, go[o + 2]); go[o + 3] = fmaf(v[i], w.w, go[o + 3]);
+                  }
               }
-              dl[i] = v[i] > 0.f ? acc : 0.f;
+              dl[i] = (v[i] > 0.f && kk < C::H) ? dl[i] : 0.f;
             }
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, dl[0], dl[1], dl[2], dl[3]);
             store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, dl[4], dl[5], dl[6], dl[7]);
