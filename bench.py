@@ -314,6 +314,10 @@ def run_ours(args):
                      "executed_tflops": executed / (sweep_ms * 1e-3) / 1e12 if sweep_ms else None,
                      "ms_per_pass": sweep_ms, "launches_per_pass": sweep_n,
                      "share_of_step": sweep_ms / ms_step if ms_step else None})
+        # SURVEY.md 8(d)'s whole-path figure: trajectory-steps/s x algorithmic FLOPs per trajectory-step (fwd + bwd =
+        # 3 x forward, recompute not counted) against the same peak
+        whole = value / world * flop_per_traj_step(env) / 1e12
+        roof["whole_step"] = {"achieved": whole, "unit": "TFLOP/s", "frac": whole / peak if peak else None}
         cores = os.cpu_count()
         cpu_val, cpu_ms = cpu_reference_run(env, args.cpu_sample, 2, 1, cores) if world == 1 else (None, None)
         line = {
@@ -466,6 +470,27 @@ def run_configs(args):
                       128, (2,)),
              mlp_case("config2 twin-Q fwd+bwd", lambda: nlbac_ref.QNetwork(10, 1, 256), lambda: nlbac_b200.QNetwork(10, 1, 256),
                       256, (10, 1))]
+    # replay sampling: the reference's list-of-tuples memory + np.stack + H2D vs the device ring
+    from oracle.replay import ReplayMemory as RefReplay
+    import numpy as np
+    rng = np.random.default_rng(0)
+    trs = [(rng.normal(size=7), rng.normal(size=2), 0.1, 0.0, rng.normal(size=2), rng.normal(size=2),
+            rng.normal(size=7), 1.0) for _ in range(40000)]
+    ours_mem, ref_mem = nlbac_b200.ReplayMemory(40000, 0), RefReplay(40000, 0)
+    for tr in trs:
+        ours_mem.push(*tr)
+        ref_mem.push(*tr)
+
+    def ref_sample(bs):
+        def f():
+            batch = ref_mem.sample(bs)
+            return [torch.FloatTensor(a).to(dev) for a in batch[:8]]
+        return f
+    for bs in (128, 32768):
+        o = lat_gpu(lambda: ours_mem.sample(bs), iters=20, warm=3)
+        c = lat_cpu(lambda: (ref_sample(bs)(), torch.cuda.synchronize()), iters=5, warm=1)
+        rows.append({"case": "replay sample -> device batch", "batch": bs, "ours_us": o, "torch_eager_gpu_us": c,
+                     "torch_cpu_us": c, "speedup_vs_eager_gpu": c / o, "speedup_vs_cpu": c / o})
     print(json.dumps({"suite": "configs", "unit": "microseconds per forward+backward call (median)", "cores": os.cpu_count(),
                       "note": "B = 128/256 calls are launch-latency bound: one fused launch per direction vs ~90 eager "
                               "launches (SURVEY.md §8 a3)", "rows": rows}))

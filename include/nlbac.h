@@ -240,6 +240,11 @@ int nlbac_adam_step_multi(int n_tensors, float* const* params, const float* cons
 int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* const* sources, const int64_t* numels,
                             float tau, void* stream);
 
+/* Device-resident replay memory (U replay_memory.py:4-28, U sac_cbf_clf.py:201-229): transitions live
+ * as float32 rows [capacity, width] on the device; a minibatch is ONE gather launch, out[i] = ring[idx[i]].
+ * idx: DEVICE array of B row indices (int64), chosen by the host with the reference's own `random.sample`. */
+int nlbac_replay_gather(const float* ring, int width, const int64_t* idx, int64_t B, float* out, void* stream);
+
 /* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 tile.
  * mode 0 (kind::tf32, both operands K-major):   D[t][j] = sum_k X[t][k] Y[j][k],  X [128,104], Y [104,104];
  * mode 1 (kind::f16 on bf16 images, MN-major):  D[j][k] = sum_t X[t][j] Y[t][k],  X, Y [128,104].

@@ -11,7 +11,8 @@ from .model import NeuralODEModel, train_step
 from .mlp import QNetwork, LyaNetwork, BarrierNetwork, GaussianPolicy, weights_init_
 from .tail import DynamicsModel, FusedAdam, soft_update, hard_update, constraint_sums, lookahead, make_constraint_desc
 from . import constraints
+from .replay import ReplayMemory
 
 __all__ = ["odeint", "NeuralODEModel", "train_step", "build", "describe", "QNetwork", "LyaNetwork", "BarrierNetwork",
            "GaussianPolicy", "weights_init_", "DynamicsModel", "FusedAdam", "soft_update", "hard_update",
-           "constraint_sums", "lookahead", "make_constraint_desc", "constraints"]
+           "constraint_sums", "lookahead", "make_constraint_desc", "constraints", "ReplayMemory"]

@@ -131,6 +131,7 @@ def _declare(lib):
     lib.nlbac_adam_step_multi.argtypes = [c.c_int, pvp, pvp, pvp, pvp, pi64, c.c_int, c.c_float, c.c_float, c.c_float,
                                           c.c_float, vp]
     lib.nlbac_soft_update_multi.argtypes = [c.c_int, pvp, pvp, pi64, c.c_float, vp]
+    lib.nlbac_replay_gather.argtypes = [vp, c.c_int, vp, i64, vp, vp]
     lib.nlbac_umma_selftest.argtypes = [c.c_int, vp, vp, vp, vp]
     lib.nlbac_kernel_timing.argtypes = [c.c_int]
     lib.nlbac_kernel_timing_read.argtypes = [c.POINTER(c.c_double), c.POINTER(c.c_int)]

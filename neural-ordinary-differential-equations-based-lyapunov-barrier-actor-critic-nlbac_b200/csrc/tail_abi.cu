@@ -360,6 +360,17 @@ __global__ void soft_update_multi_kernel(const __grid_constant__ PolyakTable tb,
     t[i] = t[i] * (1.0f - tau) + s[i] * tau;
 }
 
+// replay ring gather: out[i][:] = ring[idx[i]][:]  (one thread per float; a warp reads / writes whole rows)
+__global__ void replay_gather_kernel(const float* __restrict__ ring, int width, const long long* __restrict__ idx,
+                                     long long B, float* __restrict__ out) {
+  const long long n = B * width;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const long long i = e / width;
+    const int c = (int)(e - i * width);
+    out[e] = ring[idx[i] * width + c];
+  }
+}
+
 static int check_constraint(const nlbac_constraint_desc* d) {
   NLBAC_REQUIRE(d != nullptr, "null constraint descriptor");
   NLBAC_REQUIRE(d->kind >= NLBAC_CONSTRAINT_UNICYCLE && d->kind <= NLBAC_CONSTRAINT_PVTOL, "unknown constraint kind %d", d->kind);
@@ -472,6 +483,16 @@ int nlbac_adam_step(float* param, const float* grad, float* exp_avg, float* exp_
   NLBAC_CUDA(cudaGetLastError());
   return 0;
 }
+int nlbac_replay_gather(const float* ring, int width, const int64_t* idx, int64_t B, float* out, void* stream) {
+  NLBAC_REQUIRE(width >= 1 && B >= 0, "bad sizes");
+  if (B == 0) return 0;
+  NLBAC_REQUIRE(ring && idx && out, "null pointer");
+  replay_gather_kernel<<<tail_grid(B * width, 256), 256, 0, (cudaStream_t)stream>>>(
+      ring, width, reinterpret_cast<const long long*>(idx), B, out);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int nlbac_adam_step_multi(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
                           float* const* exp_avg_sq, const int64_t* numels, int step, float lr, float beta1,
                           float beta2, float eps, void* stream) {
