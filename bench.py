@@ -470,6 +470,35 @@ def run_configs(args):
                       128, (2,)),
              mlp_case("config2 twin-Q fwd+bwd", lambda: nlbac_ref.QNetwork(10, 1, 256), lambda: nlbac_b200.QNetwork(10, 1, 256),
                       256, (10, 1))]
+    # one NODE model-fit step (train_step, U model.py:221-260): eager API, CUDA-graph replay, reference eager
+    def train_case(N):
+        torch.manual_seed(0)
+        ref = nlbac_ref.AffineNODE(3, 3, 6)
+        ref_gpu = nlbac_ref.AffineNODE(3, 3, 6).to(dev)
+        ref_gpu.load_state_dict(ref.state_dict())
+        ours = nlbac_b200.NeuralODEModel(3, 3, 6)
+        ours.load_state_dict(ref.state_dict())
+        ours.to(dev)
+        graphed_model = nlbac_b200.NeuralODEModel(3, 3, 6)
+        graphed_model.load_state_dict(ref.state_dict())
+        graphed_model.to(dev)
+        st, ac = torch.randn(N, 3), torch.randn(N, 2)
+        nx = st + 0.02 * torch.randn(N, 3)
+        std, acd, nxd = st.to(dev), ac.to(dev), nx.to(dev)
+        mse = torch.nn.MSELoss()
+        o_opt = nlbac_b200.FusedAdam(ours.parameters(), lr=1e-3)
+        r_opt = torch.optim.Adam(ref_gpu.parameters(), lr=1e-3)
+        c_opt = torch.optim.Adam(ref.parameters(), lr=1e-3)
+        gstep = nlbac_b200.GraphedTrainStep(graphed_model, N, 3, 2, solver="euler", time_interval=DT, lr=1e-3)
+        o = lat_gpu(lambda: nlbac_b200.train_step(ours, std, acd, nxd, o_opt, mse, N, "euler", DT))
+        gq = lat_gpu(lambda: gstep(std, acd, nxd))
+        e = lat_gpu(lambda: nlbac_ref.train_step(ref_gpu, std, acd, nxd, r_opt, mse, N, "euler", DT), iters=20, warm=3)
+        c = lat_cpu(lambda: nlbac_ref.train_step(ref, st, ac, nx, c_opt, mse, N, "euler", DT))
+        return {"case": "config1 train_step (fit + Adam)", "batch": N, "method": "euler", "ours_us": o,
+                "ours_cuda_graph_us": gq, "torch_eager_gpu_us": e, "torch_cpu_us": c, "speedup_vs_eager_gpu": e / o,
+                "speedup_vs_cpu": c / o, "graph_speedup_vs_eager_gpu": e / gq}
+    rows += [train_case(128), train_case(32768)]
+
     # replay sampling: the reference's list-of-tuples memory + np.stack + H2D vs the device ring
     from oracle.replay import ReplayMemory as RefReplay
     import numpy as np

@@ -237,6 +237,12 @@ int nlbac_soft_update(float* target, const float* source, int64_t n, float tau, 
 int nlbac_adam_step_multi(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
                           float* const* exp_avg_sq, const int64_t* numels, int step, float lr, float beta1,
                           float beta2, float eps, void* stream);
+/* Same update with the step counter kept ON THE DEVICE (*step_dev, int32; incremented first when `bump` != 0, then
+ * read by the update kernel, which forms the bias corrections itself): nothing depends on host state, so the call
+ * can be captured in a CUDA graph and replayed. */
+int nlbac_adam_step_multi_dev(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
+                              float* const* exp_avg_sq, const int64_t* numels, int* step_dev, int bump, float lr,
+                              float beta1, float beta2, float eps, void* stream);
 int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* const* sources, const int64_t* numels,
                             float tau, void* stream);
 

@@ -12,7 +12,8 @@ from .mlp import QNetwork, LyaNetwork, BarrierNetwork, GaussianPolicy, weights_i
 from .tail import DynamicsModel, FusedAdam, soft_update, hard_update, constraint_sums, lookahead, make_constraint_desc
 from . import constraints
 from .replay import ReplayMemory
+from .graphs import GraphedTrainStep
 
 __all__ = ["odeint", "NeuralODEModel", "train_step", "build", "describe", "QNetwork", "LyaNetwork", "BarrierNetwork",
            "GaussianPolicy", "weights_init_", "DynamicsModel", "FusedAdam", "soft_update", "hard_update",
-           "constraint_sums", "lookahead", "make_constraint_desc", "constraints", "ReplayMemory"]
+           "constraint_sums", "lookahead", "make_constraint_desc", "constraints", "ReplayMemory", "GraphedTrainStep"]

@@ -130,6 +130,8 @@ def _declare(lib):
     pvp, pi64 = c.POINTER(vp), c.POINTER(c.c_int64)
     lib.nlbac_adam_step_multi.argtypes = [c.c_int, pvp, pvp, pvp, pvp, pi64, c.c_int, c.c_float, c.c_float, c.c_float,
                                           c.c_float, vp]
+    lib.nlbac_adam_step_multi_dev.argtypes = [c.c_int, pvp, pvp, pvp, pvp, pi64, vp, c.c_int, c.c_float, c.c_float,
+                                              c.c_float, c.c_float, vp]
     lib.nlbac_soft_update_multi.argtypes = [c.c_int, pvp, pvp, pi64, c.c_float, vp]
     lib.nlbac_replay_gather.argtypes = [vp, c.c_int, vp, i64, vp, vp]
     lib.nlbac_umma_selftest.argtypes = [c.c_int, vp, vp, vp, vp]

@@ -106,13 +106,32 @@ static int build_schedule(const float* t, int n_t, const float* grid, int n_grid
 static size_t sched_bytes(int n_steps, int n_t) {
   return (size_t)round_up(n_steps * 4 + n_t * 8, 16);
 }
+// Short schedules (every real NLBAC call: <= 20 steps, <= 21 output times) reach the device inside the parameters of
+// a one-block kernel instead of three pageable-memory copies: cheaper for the launch-bound B = 128 / 256 calls, and
+// it keeps the whole solve capturable in a CUDA graph (a captured memcpy would keep a pointer into a dead vector).
+constexpr int SCHED_INLINE_WORDS = 512;
+struct SchedWords { uint32_t w[SCHED_INLINE_WORDS]; int n; };
+static __global__ void write_schedule_kernel(const __grid_constant__ SchedWords s, uint32_t* __restrict__ dst) {
+  for (int i = threadIdx.x; i < s.n; i += blockDim.x) dst[i] = s.w[i];
+}
+
 static int upload_schedule(const Schedule& s, void* ws, cudaStream_t st, const float** dts, const int** ostep,
                            const float** ow) {
   const int n_steps = (int)s.dts.size(), n_t = (int)s.out_step.size();
   char* p = static_cast<char*>(ws);
-  NLBAC_CUDA(cudaMemcpyAsync(p, s.dts.data(), n_steps * 4, cudaMemcpyHostToDevice, st));
-  NLBAC_CUDA(cudaMemcpyAsync(p + n_steps * 4, s.out_step.data(), n_t * 4, cudaMemcpyHostToDevice, st));
-  NLBAC_CUDA(cudaMemcpyAsync(p + n_steps * 4 + n_t * 4, s.out_w.data(), n_t * 4, cudaMemcpyHostToDevice, st));
+  if (n_steps + 2 * n_t <= SCHED_INLINE_WORDS) {
+    SchedWords sw;
+    sw.n = n_steps + 2 * n_t;
+    memcpy(sw.w, s.dts.data(), n_steps * 4);
+    memcpy(sw.w + n_steps, s.out_step.data(), n_t * 4);
+    memcpy(sw.w + n_steps + n_t, s.out_w.data(), n_t * 4);
+    write_schedule_kernel<<<1, 128, 0, st>>>(sw, reinterpret_cast<uint32_t*>(p));
+    NLBAC_CUDA(cudaGetLastError());
+  } else {
+    NLBAC_CUDA(cudaMemcpyAsync(p, s.dts.data(), n_steps * 4, cudaMemcpyHostToDevice, st));
+    NLBAC_CUDA(cudaMemcpyAsync(p + n_steps * 4, s.out_step.data(), n_t * 4, cudaMemcpyHostToDevice, st));
+    NLBAC_CUDA(cudaMemcpyAsync(p + n_steps * 4 + n_t * 4, s.out_w.data(), n_t * 4, cudaMemcpyHostToDevice, st));
+  }
   *dts = reinterpret_cast<const float*>(p);
   *ostep = reinterpret_cast<const int*>(p + n_steps * 4);
   *ow = reinterpret_cast<const float*>(p + n_steps * 4 + n_t * 4);

@@ -352,6 +352,26 @@ __global__ void adam_multi_kernel(const __grid_constant__ AdamTable tb, float lr
     p[i] = p[i] - (lr / bc1) * (mi / denom);
   }
 }
+// Adam with the step counter ON THE DEVICE (graph-capturable: nothing about the update depends on host state).
+// Launched after bump_step_kernel; every thread forms the two bias corrections from *step itself.
+__global__ void bump_step_kernel(int* step) { *step += 1; }
+__global__ void adam_multi_dev_kernel(const __grid_constant__ AdamTable tb, const int* __restrict__ step_ptr, float lr,
+                                      float b1, float b2, float eps) {
+  const int k = blockIdx.y;
+  float* p = tb.p[k]; const float* g = tb.g[k]; float* m = tb.m[k]; float* v = tb.v[k];
+  const long long n = tb.n[k];
+  const int step = *step_ptr;
+  const float bc1 = (float)(1.0 - pow((double)b1, (double)step));
+  const float bc2_sqrt = (float)sqrt(1.0 - pow((double)b2, (double)step));
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float mi = m[i] + (gi - m[i]) * (1.f - b1);
+    const float vi = fmaf(v[i], b2, (1.f - b2) * gi * gi);
+    m[i] = mi; v[i] = vi;
+    const float denom = sqrtf(vi) / bc2_sqrt + eps;
+    p[i] = p[i] - (lr / bc1) * (mi / denom);
+  }
+}
 __global__ void soft_update_multi_kernel(const __grid_constant__ PolyakTable tb, float tau) {
   const int k = blockIdx.y;
   float* t = tb.t[k]; const float* s = tb.s[k];
@@ -511,6 +531,30 @@ int nlbac_adam_step_multi(int n_tensors, float* const* params, const float* cons
   const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
   adam_multi_kernel<<<dim3(tail_grid(nmax, 256), n_tensors), 256, 0, (cudaStream_t)stream>>>(tb, lr, beta1, beta2, eps,
                                                                                           (float)bc1, (float)sqrt(bc2));
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+int nlbac_adam_step_multi_dev(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
+                              float* const* exp_avg_sq, const int64_t* numels, int* step_dev, int bump, float lr,
+                              float beta1, float beta2, float eps, void* stream) {
+  NLBAC_REQUIRE(n_tensors >= 0 && n_tensors <= NLBAC_MAX_TENSORS, "n_tensors=%d (max %d)", n_tensors, NLBAC_MAX_TENSORS);
+  NLBAC_REQUIRE(params && grads && exp_avg && exp_avg_sq && numels && step_dev, "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (bump) {
+    bump_step_kernel<<<1, 1, 0, st>>>(step_dev);
+    NLBAC_CUDA(cudaGetLastError());
+  }
+  if (n_tensors == 0) return 0;
+  AdamTable tb;
+  long long nmax = 0;
+  for (int k = 0; k < n_tensors; ++k) {
+    NLBAC_REQUIRE(numels[k] >= 0 && (numels[k] == 0 || (params[k] && grads[k] && exp_avg[k] && exp_avg_sq[k])),
+                  "tensor %d: null pointer", k);
+    tb.p[k] = params[k]; tb.g[k] = grads[k]; tb.m[k] = exp_avg[k]; tb.v[k] = exp_avg_sq[k]; tb.n[k] = numels[k];
+    if (numels[k] > nmax) nmax = numels[k];
+  }
+  if (nmax == 0) return 0;
+  adam_multi_dev_kernel<<<dim3(tail_grid(nmax, 256), n_tensors), 256, 0, st>>>(tb, step_dev, lr, beta1, beta2, eps);
   NLBAC_CUDA(cudaGetLastError());
   return 0;
 }
