@@ -211,16 +211,23 @@ class DynamicsModel:
 
 
 class FusedAdam(torch.optim.Optimizer):
-    """torch.optim.Adam (default betas/eps, no weight decay) with the update run by ``nlbac_adam_step``."""
+    """torch.optim.Adam (default betas/eps, no weight decay) with the update run by ``nlbac_adam_step_multi``: one
+    launch per parameter group.  ``capturable=True`` keeps the step counter on the device
+    (``nlbac_adam_step_multi_dev``) so that ``step()`` can be captured in a CUDA graph and replayed."""
 
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, capturable=False):
         super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+        self.capturable = bool(capturable)
+        self._step_dev = {}
 
     @torch.no_grad()
     def step(self, closure=None):
         L = _lib.lib()
         for group in self.param_groups:
             b1, b2 = group["betas"]
+            if self.capturable:
+                self._step_capturable(L, group, b1, b2)
+                continue
             by_step = {}
             for p in group["params"]:
                 if p.grad is None:
@@ -248,6 +255,40 @@ class FusedAdam(torch.optim.Optimizer):
                         group["eps"], _stream()), "adam_step_multi")
                     for p, _, _ in chunk:
                         torch.autograd.graph.increment_version(p)   # written through raw pointers: invalidate caches
+
+
+def _fused_adam_step_capturable(self, L, group, b1, b2):
+    items = []
+    for p in group["params"]:
+        if p.grad is None:
+            continue
+        if not p.is_cuda or p.dtype != torch.float32 or not p.is_contiguous():
+            raise RuntimeError("FusedAdam: parameters must be contiguous float32 CUDA tensors")
+        st = self.state[p]
+        if not st:
+            st["exp_avg"] = torch.zeros_like(p)
+            st["exp_avg_sq"] = torch.zeros_like(p)
+        items.append((p, p.grad.contiguous(), st))
+    if not items:
+        return
+    key = id(group)
+    if key not in self._step_dev:
+        self._step_dev[key] = torch.zeros(1, dtype=torch.int32, device=items[0][0].device)
+    step_dev = self._step_dev[key]
+    for lo in range(0, len(items), _lib.MAX_TENSORS):
+        chunk = items[lo:lo + _lib.MAX_TENSORS]
+        n = len(chunk)
+        arr = lambda xs: (ctypes.c_void_p * n)(*xs)  # noqa: E731
+        _lib.check(L.nlbac_adam_step_multi_dev(
+            n, arr([p.data_ptr() for p, _, _ in chunk]), arr([g.data_ptr() for _, g, _ in chunk]),
+            arr([s["exp_avg"].data_ptr() for _, _, s in chunk]), arr([s["exp_avg_sq"].data_ptr() for _, _, s in chunk]),
+            (ctypes.c_int64 * n)(*[p.numel() for p, _, _ in chunk]), step_dev.data_ptr(), 1 if lo == 0 else 0,
+            group["lr"], b1, b2, group["eps"], _stream()), "adam_step_multi_dev")
+        for p, _, _ in chunk:
+            torch.autograd.graph.increment_version(p)
+
+
+FusedAdam._step_capturable = _fused_adam_step_capturable
 
 
 @torch.no_grad()
