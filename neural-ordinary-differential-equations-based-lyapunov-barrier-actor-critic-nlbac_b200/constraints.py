@@ -79,6 +79,51 @@ def backup_augmented_lagrangian(backup_required_matrix, st, updates):
     return loss
 
 
+class DeviceConstraintState:
+    """The same bookkeeping as ``ConstraintState`` with every scalar ON THE DEVICE (float64, mirroring the Python
+    floats of the reference), so that ``augmented_lagrangian_device`` has no host read-back (the reference's
+    ``float(ratio)`` / ``float(lambda)`` at U sac_cbf_clf.py:510, 525-528) and the whole actor update can be captured
+    in a CUDA graph.  ``set_updates(updates)`` is the only per-call host input: it writes the
+    "multipliers are due" flag (``updates % interval == 0``) into a device scalar before the replay."""
+
+    def __init__(self, num_constraints, batch_size, device, *, lambda_max=400.0, cost_limit=0.0, augmented_term=1.0,
+                 augmented_ratio=1.0005, update_interval=8, ratio_floor=None, use_ratio=True):
+        f64 = dict(dtype=torch.float64, device=device)
+        self.num_constraints, self.batch_size = num_constraints, batch_size
+        self.lambda_values = torch.zeros(num_constraints, **f64)
+        self.augmented_term = torch.full((), float(augmented_term), **f64)
+        self.due = torch.zeros((), **f64)
+        self.lambda_max, self.cost_limit, self.augmented_ratio = lambda_max, cost_limit, augmented_ratio
+        self.Lagrangian_multiplier_update_interval = update_interval
+        self.ratio_floor, self.use_ratio = ratio_floor, use_ratio
+
+    def set_updates(self, updates):
+        self.due.fill_(1.0 if updates % self.Lagrangian_multiplier_update_interval == 0 else 0.0)
+
+
+def augmented_lagrangian_device(required_matrix, st):
+    """``augmented_lagrangian`` (U sac_cbf_clf.py:506-530) with the multipliers, rho and the ratio kept as device
+    tensors: same arithmetic (float64 scalars like the Python floats), no host synchronisation, capturable."""
+    req = required_matrix.reshape(-1)
+    c = req - st.cost_limit
+    cd = c.detach().double()
+    if st.use_ratio:
+        ratio = torch.abs(cd[:-1].mean()) / torch.abs(cd[-1])
+        if st.ratio_floor is not None:
+            ratio = torch.clamp(ratio, min=st.ratio_floor)
+    else:
+        ratio = torch.ones((), dtype=torch.float64, device=req.device)
+    new_lambda = torch.clamp(st.lambda_values + st.augmented_term * req.detach().double(), 0.01, st.lambda_max)
+    st.lambda_values.copy_(torch.where(st.due > 0, new_lambda, st.lambda_values))
+    st.augmented_term.copy_(torch.clamp(st.augmented_term * st.augmented_ratio, max=200.0))
+    rho = st.augmented_term
+    w = torch.ones_like(cd)
+    w[-1] = ratio
+    lin = (st.lambda_values * w).float()            # lambda_i (x ratio for the CLF row)
+    quad = (rho / 2.0 * w * w).float()              # rho / 2 (x ratio^2 for the CLF row)
+    return (lin * c + quad * c * c).sum().reshape(1)
+
+
 def _zeros_like_rows(x):
     return torch.zeros((x.shape[0], 1), dtype=torch.float32, device=x.device)
 

@@ -79,12 +79,7 @@ struct TcBwdGeom {
   }
 };
 
-// activation image store: 8 columns of row t; the ones column (bias gradients) sits at column H
-template <class C>
-__device__ __forceinline__ void store_act_img(unsigned char* img, int t, int c0, float (&v)[8]) {
-  if (C::H >= c0 && C::H < c0 + 8) v[C::H - c0] = 1.f;
-  store_img8(img, t, c0, v);
-}
+// the ones column of an activation image (bias gradients) sits at column H
 template <class C>
 __device__ __forceinline__ void finish_act_img(unsigned char* img, int t) {
   if (C::H == TcCfg<C>::KP) {   // no padding column inside the K extent: the ones column opens a new chunk

@@ -317,3 +317,82 @@ def test_critic_update_captured_in_a_cuda_graph():
         assert _rel(p, w) <= 1e-4
     for p, w in zip(qt.parameters(), rt.parameters()):
         assert _rel(p, w) <= 1e-5
+
+
+def test_device_side_lagrangian_and_graphed_actor_update(golden_dir):
+    """augmented_lagrangian_device (multipliers / rho / ratio on the device) against the host-float version over ten
+    updates, then the whole Unicycle CBF/CLF actor-loss update (NODE step, Lyapunov net, constraint kernel,
+    Lagrangian, backward to the action, Adam on a stand-in actor) captured in ONE CUDA graph and replayed."""
+    import nlbac_b200
+    C = nlbac_b200.constraints
+    g = torch.load(os.path.join(golden_dir, "constraints_U.pt"), weights_only=False)
+    nets = build(g, nlbac_b200, "cuda")
+    k, B = g["consts"], g["B"]
+    state, V = g["state"].cuda(), g["V"].cuda()
+    kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_locations=k["hazards"], hazards_radius=k["hazards_radius"],
+              l_p=k["l_p"], batch_size=B)
+    host, dev = C.ConstraintState(8, B), C.DeviceConstraintState(8, B, "cuda")
+    for updates in range(6, 16):
+        act = (g["action"].cuda() * (1.0 + 0.05 * (updates - 6))).requires_grad_(True)
+        req = C.unicycle_required_matrix(nets["node"], nets["lya"], state, act, V, **kw)
+        want = C.augmented_lagrangian(req, host, updates)
+        dev.set_updates(updates)
+        got = C.augmented_lagrangian_device(req, dev)
+        assert _rel(got, want) <= 1e-6
+        gw, = torch.autograd.grad(want, act, retain_graph=True)
+        gg, = torch.autograd.grad(got, act)
+        assert _rel(gg, gw) <= 1e-6
+    lam = torch.tensor([float(v) for v in host.lambda_values], dtype=torch.float64)
+    assert _rel(dev.lambda_values, lam) <= 1e-6 and abs(dev.augmented_term.item() - host.augmented_term) < 1e-12
+
+    # --- the same update as one CUDA graph: the actor is a stand-in linear map obs -> action with capturable Adam
+    torch.manual_seed(0)
+    actor = torch.nn.Linear(3, 2).cuda()
+    opt = nlbac_b200.FusedAdam(actor.parameters(), lr=3e-4, capturable=True)
+    ref_actor = torch.nn.Linear(3, 2).cuda()
+    ref_actor.load_state_dict(actor.state_dict())
+    ref_opt = torch.optim.Adam(ref_actor.parameters(), lr=3e-4)
+    st_g, st_h = C.DeviceConstraintState(8, B, "cuda"), C.ConstraintState(8, B)
+    s_in = torch.zeros_like(state)
+
+    def update():
+        pi = actor(s_in)
+        req = C.unicycle_required_matrix(nets["node"], nets["lya"], s_in, pi, V, **kw)
+        loss = C.augmented_lagrangian_device(req, st_g)
+        grads = torch.autograd.grad(loss, list(actor.parameters()))
+        for p, g_ in zip(actor.parameters(), grads):
+            p.grad = g_
+        opt.step()
+        return loss
+
+    snap = [p.detach().clone() for p in actor.parameters()]
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        s_in.copy_(state)
+        update()
+    torch.cuda.current_stream().wait_stream(side)
+    with torch.no_grad():
+        for p, v in zip(actor.parameters(), snap):
+            p.copy_(v)
+        for s_ in opt.state.values():
+            s_["exp_avg"].zero_(); s_["exp_avg_sq"].zero_()
+        for v in opt._step_dev.values():
+            v.zero_()
+        st_g.lambda_values.zero_(); st_g.augmented_term.fill_(1.0)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        loss_g = update()
+    for updates in range(8, 12):
+        s_now = state + 0.01 * (updates - 8)
+        s_in.copy_(s_now)
+        st_g.set_updates(updates)
+        graph.replay()
+        ref_opt.zero_grad()
+        req = C.unicycle_required_matrix(nets["node"], nets["lya"], s_now, ref_actor(s_now), V, **kw)
+        want = C.augmented_lagrangian(req, st_h, updates)
+        want.backward()
+        ref_opt.step()
+        assert _rel(loss_g, want) <= 1e-5
+    for p, w in zip(actor.parameters(), ref_actor.parameters()):
+        assert _rel(p, w) <= 1e-4
