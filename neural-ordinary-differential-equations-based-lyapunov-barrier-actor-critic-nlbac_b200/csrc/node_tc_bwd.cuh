@@ -27,18 +27,21 @@ namespace nlbac {
 template <class C>
 struct ImgMap {
   using T = TcCfg<C>;
-  static constexpr int IMGW = round_up(C::H + 1, 16);
-  static constexpr int ACT_CH = IMGW / 8, DEL_CH = T::KP / 8, THIN_CH = 2;
-  static constexpr int ACT_B = ACT_CH * 2048, DEL_B = DEL_CH * 2048, THIN_B = THIN_CH * 2048;
+  static constexpr int IMGW = round_up(C::H + 1, 16);              // MMA N of an activation image (multiple of 16)
+  // chunks (8 columns = 2048 B) actually written by pass A and streamed by pass B; the MMA addresses IMGW / 8 (or 2)
+  // chunks, the unloaded ones only feed result columns / rows that the epilogue drops
+  static constexpr int ACT_CH = round_up(C::H + 1, 8) / 8, DEL_CH = T::KP / 8;
+  static constexpr int XIN_CH = round_up(C::IN0 + 1, 8) / 8, DOUT_CH = round_up(C::OUTP_MAX, 8) / 8;
+  static constexpr int ACT_B = ACT_CH * 2048, DEL_B = DEL_CH * 2048, XIN_B = XIN_CH * 2048, DOUT_B = DOUT_CH * 2048;
   static_assert(C::IN0 < 16 && C::OUTP_MAX <= 16, "thin images hold 16 columns");
   __host__ __device__ static constexpr int nl1(int c) { return C::nhc(c) + 1; }   // activations / cotangents per chain
-  __host__ __device__ static constexpr int chain_bytes(int c) { return nl1(c) * (ACT_B + DEL_B) + THIN_B; }
+  __host__ __device__ static constexpr int chain_bytes(int c) { return nl1(c) * (ACT_B + DEL_B) + DOUT_B; }
   __host__ __device__ static constexpr int off_xin() { return 0; }
-  __host__ __device__ static constexpr int chain_base(int c) { return THIN_B + (c == 0 ? 0 : chain_bytes(0)); }
+  __host__ __device__ static constexpr int chain_base(int c) { return XIN_B + (c == 0 ? 0 : chain_bytes(0)); }
   __host__ __device__ static constexpr int off_act(int c, int i /*1..nl1*/) { return chain_base(c) + (i - 1) * ACT_B; }
   __host__ __device__ static constexpr int off_del(int c, int i) { return chain_base(c) + nl1(c) * ACT_B + (i - 1) * DEL_B; }
   __host__ __device__ static constexpr int off_dout(int c) { return chain_base(c) + nl1(c) * (ACT_B + DEL_B); }
-  static constexpr int STRIDE = THIN_B + chain_bytes(0) + (C::NCH == 2 ? chain_bytes(1) : 0);
+  static constexpr int STRIDE = XIN_B + chain_bytes(0) + (C::NCH == 2 ? chain_bytes(1) : 0);
   // GEMM pairs of pass B: per chain  (d_1 | xin), (d_{l+1} | a_l) l = 1..nhc, (dOut | a_{nl1})
   __host__ __device__ static constexpr int npairs(int c) { return C::nhc(c) + 2; }
   static constexpr int NPAIR = npairs(0) + (C::NCH == 2 ? npairs(1) : 0);
@@ -160,7 +163,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
       if (d < 8) v0[d] = val; else v1[d - 8] = val;
     }
     store_img8(img + IM::off_xin(), lt, 0, v0);
-    store_img8(img + IM::off_xin(), lt, 8, v1);
+    if (IM::XIN_CH > 1) store_img8(img + IM::off_xin(), lt, 8, v1);
   }
 #pragma unroll
   for (int c = 0; c < C::NCH; ++c) {
@@ -222,7 +225,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
         if (o < 8) v0[o] = val; else v1[o - 8] = val;
       }
       store_img8(img + IM::off_dout(c), lt, 0, v0);
-      store_img8(img + IM::off_dout(c), lt, 8, v1);
+      if (IM::DOUT_CH > 1) store_img8(img + IM::off_dout(c), lt, 8, v1);
     }
     // ---------------- hidden layers forward: a_{l+1} = relu(H_l a_l + b_l) ----------------
 #pragma unroll
@@ -521,12 +524,12 @@ __host__ __device__ inline DwPair dw_pair(int pr) {
   const int n = C::nhc(c);
   DwPair p;
   if (pr == 0) {
-    p = {IM::off_del(c, 1), IM::DEL_B, IM::off_xin(), IM::THIN_B, 16, C::H, C::IN0, C::goff_w(c, 0), C::goff_b(c, 0), C::IN0};
+    p = {IM::off_del(c, 1), IM::DEL_B, IM::off_xin(), IM::XIN_B, 16, C::H, C::IN0, C::goff_w(c, 0), C::goff_b(c, 0), C::IN0};
   } else if (pr <= n) {
     p = {IM::off_del(c, pr + 1), IM::DEL_B, IM::off_act(c, pr), IM::ACT_B, IM::IMGW, C::H, C::H, C::goff_w(c, pr),
          C::goff_b(c, pr), C::H};
   } else {
-    p = {IM::off_dout(c), IM::THIN_B, IM::off_act(c, n + 1), IM::ACT_B, IM::IMGW, C::out(c), C::H, C::goff_w(c, n + 1),
+    p = {IM::off_dout(c), IM::DOUT_B, IM::off_act(c, n + 1), IM::ACT_B, IM::IMGW, C::out(c), C::H, C::goff_w(c, n + 1),
          C::goff_b(c, n + 1), C::H};
   }
   return p;
@@ -537,7 +540,7 @@ struct DwGeom {
   using IM = ImgMap<C>;
   static constexpr int NST = 3;
   static constexpr int DBUF = 16 * 2048;            // M = 128 feature rows are addressed (13 or 2 chunks are loaded)
-  static constexpr int ABUF = IM::ACT_B;
+  static constexpr int ABUF = (IM::IMGW / 8) * 2048;   // the MMA addresses IMGW columns; ACT_B of them are loaded
   static constexpr int STAGE = DBUF + ABUF;
   static constexpr int OFF_BAR = NST * STAGE;
   static constexpr size_t SMEM_BYTES = OFF_BAR + (2 * NST + 1) * 8 + 16;
