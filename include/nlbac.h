@@ -254,6 +254,7 @@ int nlbac_replay_gather(const float* ring, int width, const int64_t* idx, int64_
 /* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 tile.
  * mode 0 (kind::tf32, both operands K-major):   D[t][j] = sum_k X[t][k] Y[j][k],  X [128,104], Y [104,104];
  * mode 1 (kind::f16 on bf16 images, MN-major):  D[j][k] = sum_t X[t][j] Y[t][k],  X, Y [128,104].
+ * mode 2 (kind::tf32, A operand in tensor memory written by tcgen05.st): same product as mode 0.
  * D [128,112] fp32 (rows/columns >= 104 are padding). */
 int nlbac_umma_selftest(int mode, const float* X, const float* Y, float* D, void* stream);
 

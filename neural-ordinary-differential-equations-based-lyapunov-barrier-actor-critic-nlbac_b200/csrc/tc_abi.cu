@@ -11,6 +11,7 @@ namespace nlbac {
 //   mode 0  kind::tf32  D[t][j] = sum_k X[t][k] W[j][k]   A K-major,  B K-major   (hidden layer; the dX product uses
 //                                                                                  the same form on a transposed image)
 //   mode 1  kind::f16   D[j][k] = sum_t X[t][j] Y[t][k]   A MN-major, B MN-major  (dW over bf16 row-owner images)
+//   mode 2  kind::tf32  as mode 0 with A in TENSOR MEMORY, written by its row-owner threads with tcgen05.st
 // kind::tf32 has no MN-major form without the 128-byte swizzle (measured: all-zero accumulators for every LBO/SBO
 // assignment, tools/umma_sweep.py), which is why dX reads a transposed weight image and dW runs in bf16.
 // X, Y: [128][104] row-major; W: [104][104] row-major; D: [128][112] row-major.
@@ -29,9 +30,10 @@ __global__ void __launch_bounds__(128, 1) umma_selftest_kernel(int mode, const f
   const int tid = threadIdx.x, warp = tid / 32;
   for (int i = tid; i < 64 * ST_XCH / 4; i += 128) reinterpret_cast<float*>(sm)[i] = 0.f;
   __syncthreads();
-  if (mode == 0) {
+  if (mode == 0 || mode == 2) {
     // A: row-owner fp32 image of X (chunk stride 2048); B: weight image, rows j (112 per chunk), columns k
-    for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufA + umma::tile_off(tid, c, ST_XCH)) = X[tid * ST_K + c];
+    if (mode == 0)
+      for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufA + umma::tile_off(tid, c, ST_XCH)) = X[tid * ST_K + c];
     if (tid < ST_K)
       for (int c = 0; c < ST_K; ++c) *reinterpret_cast<float*>(bufB + umma::tile_off(tid, c, ST_WCH)) = Y[tid * ST_K + c];
   } else {
@@ -45,15 +47,31 @@ __global__ void __launch_bounds__(128, 1) umma_selftest_kernel(int mode, const f
     mbar_init(bar, 1);
     fence_barrier_init();
   }
-  if (warp == 0) umma::tmem_alloc(tslot, 128);
+  if (warp == 0) umma::tmem_alloc(tslot, 256);
   fence_proxy_async();
   umma::fence_before_sync();
   __syncthreads();
   umma::fence_after_sync();
   const uint32_t tbase = *tslot;
+  if (mode == 2) {   // A operand: row tid -> lane tid, columns 128 .. 128 + ST_K
+    for (int c0 = 0; c0 < ST_K; c0 += 8) {
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = X[tid * ST_K + c0 + i];
+      umma::st8(umma::tmem_addr(tbase, warp * 32, 128 + c0), v);
+    }
+    umma::wait_st();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+  }
   if (tid == 0) {
     const uint32_t a0 = smem_u32(bufA), b0 = smem_u32(bufB);
-    if (mode == 0) {
+    if (mode == 2) {
+      const uint32_t idesc = umma::make_idesc_tf32(128, ST_N, false, false);
+      for (int ks = 0; ks < ST_K / 8; ++ks)
+        umma::mma_tf32_ts(tbase, tbase + 128 + ks * 8, umma::make_desc(b0 + ks * 2 * ST_WCH, ST_WCH, 128), idesc, ks > 0);
+    } else if (mode == 0) {
       const uint32_t idesc = umma::make_idesc_tf32(128, ST_N, false, false);
       for (int ks = 0; ks < ST_K / 8; ++ks)
         umma::mma_tf32(tbase, umma::make_desc(a0 + ks * 2 * ST_XCH, ST_XCH, 128),
@@ -77,7 +95,7 @@ __global__ void __launch_bounds__(128, 1) umma_selftest_kernel(int mode, const f
   }
   umma::fence_before_sync();
   __syncthreads();
-  if (warp == 0) umma::tmem_dealloc(tbase, 128);
+  if (warp == 0) umma::tmem_dealloc(tbase, 256);
 }
 
 // Descriptor sweep used to establish the table above (tools/umma_sweep.py); diagnostic only.
@@ -148,7 +166,7 @@ using namespace nlbac;
 extern "C" {
 
 int nlbac_umma_selftest(int mode, const float* X, const float* Y, float* D, void* stream) {
-  NLBAC_REQUIRE(mode >= 0 && mode <= 1 && X && Y && D, "bad arguments");
+  NLBAC_REQUIRE(mode >= 0 && mode <= 2 && X && Y && D, "bad arguments");
   NLBAC_CUDA(cudaFuncSetAttribute(umma_selftest_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
   umma_selftest_kernel<<<1, 128, ST_SMEM, (cudaStream_t)stream>>>(mode, X, Y, D);
   NLBAC_CUDA(cudaGetLastError());
