@@ -10,7 +10,10 @@
 // (umma.cuh); ONE thread issues the 13 (39) MMAs of a hidden layer [128 x 112 x 104]; the owner reads its
 // accumulator row back with tcgen05.ld, applies bias + ReLU and either rewrites the activation image in
 // place or folds the thin last layer in registers.  The G groups share one TMA weight ring (one packet =
-// one hidden matrix image, 46.6 KB), so while one group is in its epilogue the other group's MMAs run.
+// one hidden matrix image, 46.6 KB), so while one group is in its epilogue the other groups' MMAs run.
+// Shared memory holds two activation images; a THIRD group keeps its A operand in tensor memory instead (row = lane,
+// feature = column, written with tcgen05.st by the owner threads; self-test mode 2 in tc_abi.cu), which costs no
+// shared memory: 3 x 128 accumulator columns + 128 operand columns = all 512 TMEM columns of the SM.
 #pragma once
 #include "node_fwd.cuh"
 #include "umma.cuh"
@@ -78,15 +81,25 @@ __global__ void pack_tc_kernel(const float* __restrict__ W, float* __restrict__ 
   }
 }
 
+// TMEM columns of a CTA: one 128-column accumulator per group + one 128-column operand block per TMEM-operand group
+// (allocations are powers of two)
+__host__ __device__ constexpr int tmem_cols(int groups, int tmem_groups) {
+  const int need = (groups + tmem_groups) * 128;
+  return need <= 128 ? 128 : (need <= 256 ? 256 : 512);
+}
+
 template <class C, bool SPLIT>
 struct TcFwdGeom {
   using T = TcCfg<C>;
-  static constexpr int G = SPLIT ? 1 : 2;          // groups (tiles in flight) per CTA
-  static constexpr int NT = G * 128 + 32;          // + one producer warp
+  static constexpr int GS = SPLIT ? 1 : 2;         // groups whose activation image lives in shared memory
+  static constexpr int GT = SPLIT ? 0 : 1;         // groups whose activation operand lives in tensor memory
+  static constexpr int G = GS + GT;                // groups (tiles in flight) per CTA
+  static constexpr int NT = G * 128;               // no producer warp: see ring_prefetch
+  static constexpr int TMEM_COLS = tmem_cols(G, GT);
   static constexpr int NSLOT = 2;
   static constexpr int NIMG = SPLIT ? 2 : 1;       // activation images per group (hi, lo)
   static constexpr int OFF_A = 0;                                   // bytes
-  static constexpr int OFF_W = OFF_A + G * NIMG * T::A_BYTES;
+  static constexpr int OFF_W = OFF_A + GS * NIMG * T::A_BYTES;
   static constexpr int OFF_RES = OFF_W + NSLOT * T::W_BYTES;
   static constexpr int OFF_BAR = OFF_RES + C::RES_FWD * 4;
   static constexpr int NBAR = 2 * NSLOT + G + 1;   // full[NSLOT], empty[NSLOT], done[G], res
@@ -158,8 +171,37 @@ struct TcGroupCtx {
   uint32_t seq;            // ring packets consumed so far (uniform over the CTA's groups)
   uint32_t nd;             // completed hidden layers of this group (phase of `done`)
   uint64_t adesc, wdesc;   // UMMA descriptors of the activation image and of ring slot 0 (k-step 0)
+  uint32_t total;          // ring packets this CTA will consume in all
+  const float* packed;     // global weight image (ring source)
+  bool keeper;             // this thread re-fills the weight ring
+  uint32_t ta_row;         // TMEM address of this thread's activation row   (groups with the A operand in TMEM)
+  uint32_t ta_mma;         // TMEM address of the group's activation operand (lane 0)
+  bool tmemA;
   int lt, g;
 };
+
+// 8 consecutive features [8 g8, 8 g8 + 8) of the owner's activation row -> A operand of the group's next MMA
+template <class C, bool SPLIT>
+__device__ __forceinline__ void act_store8(const TcGroupCtx& cx, int g8, const float (&v)[8]) {
+  using T = TcCfg<C>;
+  if (!SPLIT && cx.tmemA) {
+    float r[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = tf32_bias(v[i]);
+    umma::st8(cx.ta_row + 8 * g8, r);
+  } else {
+    store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, cx.lt, 8 * g8, v[0], v[1], v[2], v[3]);
+    store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, cx.lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
+  }
+}
+// operand written -> visible to the MMA the group's elected thread issues next
+template <bool SPLIT>
+__device__ __forceinline__ void act_publish(const TcGroupCtx& cx) {
+  if (!SPLIT && cx.tmemA) umma::wait_st();
+  else fence_proxy_async();
+  umma::fence_before_sync();
+  group_sync(cx.g);
+}
 
 // The KSTEPS MMAs of one hidden layer.  Descriptors differ from k-step to k-step only in the 14-bit start address,
 // so they are formed by adding to the low word; one out-of-line copy keeps the (fully unrolled) issue sequence
@@ -172,6 +214,32 @@ __device__ __noinline__ void tc_issue(uint32_t tmma, uint64_t ad, uint64_t wd, u
   for (int ks = 0; ks < T::KSTEPS; ++ks)
     umma::mma_tf32(tmma, ad + (uint64_t)(ks * ((2 * T::ACH) >> 4)), wd + (uint64_t)(ks * ((2 * T::WCH) >> 4)), idesc,
                    ks > 0 ? 1u : acc0);
+}
+
+// The weight ring has no warp of its own: 12 warps leave 168 registers per thread, a 13th would put four warps on
+// one scheduler and cap every thread at 128.  Instead, at the top of each hidden layer one thread of group 0 (the
+// "ring keeper", lane 0 of the group's SECOND warp, so that it never delays the MMA issuer in the first) requests
+// packet p + NSLOT - 1, i.e. it re-fills the slot whose previous packet every group has finished multiplying
+// (empty barrier, armed by tcgen05.commit).
+template <class GEO>
+__device__ __forceinline__ void ring_prefetch(const TcGroupCtx& cx, uint32_t p) {
+  using T = typename GEO::T;
+  if (p < cx.total) {
+    const uint32_t slot = p % GEO::NSLOT;
+    if (p >= (uint32_t)GEO::NSLOT) mbar_wait(&cx.empty[slot], ((p / GEO::NSLOT) - 1) & 1);
+    mbar_expect_tx(&cx.full[slot], T::W_BYTES);
+    tma_load_1d(const_cast<unsigned char*>(cx.sW) + slot * T::W_BYTES, cx.packed + GEO::pkt_off(p), T::W_BYTES,
+                &cx.full[slot]);
+  }
+}
+
+template <class C>
+__device__ __noinline__ void tc_issue_ts(uint32_t tmma, uint32_t ta, uint64_t wd) {   // A operand in tensor memory
+  using T = TcCfg<C>;
+  constexpr uint32_t idesc = umma::make_idesc_tf32(128, T::NP, false, false);
+#pragma unroll
+  for (int ks = 0; ks < T::KSTEPS; ++ks)
+    umma::mma_tf32_ts(tmma, ta + 8 * ks, wd + (uint64_t)(ks * ((2 * T::WCH) >> 4)), idesc, ks > 0 ? 1u : 0u);
 }
 
 // Right-hand side for the group's tile: owner thread passes x / constants, receives k = dx/dt.
@@ -188,27 +256,33 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
     {
       const float* Wt0 = cx.sRes + C::off_wt0(c);
       const float* b0 = cx.sRes + C::off_b0(c);
-#pragma unroll 2
-      for (int j4 = 0; j4 < T::NCHUNK; ++j4) {
-        float4 acc = *reinterpret_cast<const float4*>(b0 + 4 * j4);
+#pragma unroll 1
+      for (int g8 = 0; g8 < T::KP / 8; ++g8) {
+        const float4 ba = *reinterpret_cast<const float4*>(b0 + 8 * g8);
+        const float4 bb = *reinterpret_cast<const float4*>(b0 + 8 * g8 + 4);
+        float v[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
         for (int d = 0; d < C::IN0; ++d) {
           const float xv = d < C::NS ? x[d < C::NS ? d : 0] : cst[d >= C::NS ? d - C::NS : 0];
-          const float4 w = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 4 * j4);
-          acc.x = fmaf(xv, w.x, acc.x); acc.y = fmaf(xv, w.y, acc.y);
-          acc.z = fmaf(xv, w.z, acc.z); acc.w = fmaf(xv, w.w, acc.w);
+          const float4 wa = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8);
+          const float4 wb = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8 + 4);
+          v[0] = fmaf(xv, wa.x, v[0]); v[1] = fmaf(xv, wa.y, v[1]); v[2] = fmaf(xv, wa.z, v[2]); v[3] = fmaf(xv, wa.w, v[3]);
+          v[4] = fmaf(xv, wb.x, v[4]); v[5] = fmaf(xv, wb.y, v[5]); v[6] = fmaf(xv, wb.z, v[6]); v[7] = fmaf(xv, wb.w, v[7]);
         }
-        store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, 4 * j4, fmaxf(acc.x, 0.f), fmaxf(acc.y, 0.f),
-                                              fmaxf(acc.z, 0.f), fmaxf(acc.w, 0.f));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+        act_store8<C, SPLIT>(cx, g8, v);
       }
     }
-    fence_proxy_async();
-    umma::fence_before_sync();
-    group_sync(cx.g);
+    act_publish<SPLIT>(cx);
     const int n = C::nhc(c);
     float o[C::OUTP_MAX];
 #pragma unroll 1
     for (int l = 1; l <= n; ++l) {
+      if (cx.keeper) {
+        ring_prefetch<G>(cx, cx.seq + G::NSLOT - 1);
+        if (SPLIT) ring_prefetch<G>(cx, cx.seq + G::NSLOT);
+      }
       if (lt == 0) {  // ---- MMA issue: one thread per group ----
         umma::fence_after_sync();
         {
@@ -216,7 +290,8 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
           mbar_wait(&cx.full[slot], (cx.seq / G::NSLOT) & 1);
           umma::fence_after_sync();
           const uint64_t wd = cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4));
-          tc_issue<C>(cx.tmma, cx.adesc, wd, 0u);
+          if (!SPLIT && cx.tmemA) tc_issue_ts<C>(cx.tmma, cx.ta_mma, wd);
+          else tc_issue<C>(cx.tmma, cx.adesc, wd, 0u);
           if (SPLIT) tc_issue<C>(cx.tmma, cx.adesc + (uint64_t)(T::A_BYTES >> 4), wd, 1u);
           umma::commit(&cx.empty[slot]);
         }
@@ -240,14 +315,12 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
         tc_batches<NG8, true>(cx.tacc, [&](int, int, int g8, float (&v)[8]) {
           const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * g8);
           const float4 b1 = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
-          store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, fmaxf(v[0] + b0.x, 0.f), fmaxf(v[1] + b0.y, 0.f),
-                                                fmaxf(v[2] + b0.z, 0.f), fmaxf(v[3] + b0.w, 0.f));
-          store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, fmaxf(v[4] + b1.x, 0.f), fmaxf(v[5] + b1.y, 0.f),
-                                                fmaxf(v[6] + b1.z, 0.f), fmaxf(v[7] + b1.w, 0.f));
+          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i] + bb[i], 0.f);
+          act_store8<C, SPLIT>(cx, g8, v);
         });
-        fence_proxy_async();
-        umma::fence_before_sync();
-        group_sync(cx.g);
+        act_publish<SPLIT>(cx);
       } else {  // ---- last hidden layer: bias + ReLU, thin output layer folded in registers ----
         const int OUTP = C::outp(c);
         const float* WtL = cx.sRes + C::off_wtl(c);
@@ -307,7 +380,6 @@ __global__ void __launch_bounds__(TcFwdGeom<C, SPLIT>::NT, 1) node_tc_fwd_kernel
   uint64_t* resbar = bars + 2 * G::NSLOT + G::G;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + G::NBAR);
   const int tid = threadIdx.x, warp = tid / 32;
-  const bool is_prod = warp == G::G * 4;
 
   const int S = method_stages(a.method);
   const long long n_tiles = (a.B + T::ROWS - 1) / T::ROWS;
@@ -322,38 +394,35 @@ __global__ void __launch_bounds__(TcFwdGeom<C, SPLIT>::NT, 1) node_tc_fwd_kernel
     mbar_init(resbar, 1);
     fence_barrier_init();
   }
-  if (warp == 0) umma::tmem_alloc(tslot, G::G * T::TCOLS);
+  if (warp == 0) umma::tmem_alloc(tslot, G::TMEM_COLS);
   umma::fence_before_sync();
   __syncthreads();
   umma::fence_after_sync();
   const uint32_t tbase = *tslot;
 
-  if (is_prod) {
-    // ---------------- TMA producer: thin layers once, then the weight ring ----------------
-    if (tid % 32 == 0 && my_iters > 0) {
-      mbar_expect_tx(resbar, C::RES_FWD * 4);
-      tma_load_1d(sRes, a.packed, C::RES_FWD * 4, resbar);
-      for (uint32_t p = 0; p < total; ++p) {
-        const uint32_t slot = p % G::NSLOT;
-        if (p >= (uint32_t)G::NSLOT) mbar_wait(&empty[slot], ((p / G::NSLOT) - 1) & 1);
-        mbar_expect_tx(&full[slot], T::W_BYTES);
-        tma_load_1d(smem_raw + G::OFF_W + slot * T::W_BYTES, a.packed + G::pkt_off(p), T::W_BYTES, &full[slot]);
-      }
-    }
-    __syncwarp();
-  } else if (my_iters > 0) {
+  if (my_iters > 0) {
     TcGroupCtx cx;
     cx.g = tid / 128;
     cx.lt = tid % 128;
-    cx.sA = smem_raw + G::OFF_A + cx.g * G::NIMG * T::A_BYTES;
+    cx.tmemA = cx.g >= G::GS;
+    cx.sA = smem_raw + G::OFF_A + (cx.tmemA ? 0 : cx.g) * G::NIMG * T::A_BYTES;
     cx.sW = smem_raw + G::OFF_W;
     cx.sRes = sRes;
     cx.full = full; cx.empty = empty; cx.done = &done[cx.g];
     cx.tmma = tbase + cx.g * T::TCOLS;
     cx.tacc = cx.tmma + ((uint32_t)((warp % 4) * 32) << 16);
+    cx.ta_mma = tbase + (G::G + (cx.tmemA ? cx.g - G::GS : 0)) * T::TCOLS;
+    cx.ta_row = cx.ta_mma + ((uint32_t)((warp % 4) * 32) << 16);
     cx.seq = 0; cx.nd = 0;
     cx.adesc = umma::make_desc(smem_u32(cx.sA), T::ACH, 128);
     cx.wdesc = umma::make_desc(smem_u32(cx.sW), T::WCH, 128);
+    cx.total = total; cx.packed = a.packed;
+    cx.keeper = tid == 32;
+    if (cx.keeper) {   // thin layers once, then the first packets of the weight ring
+      mbar_expect_tx(resbar, C::RES_FWD * 4);
+      tma_load_1d(sRes, a.packed, C::RES_FWD * 4, resbar);
+      for (uint32_t p = 0; p + 1 < (uint32_t)G::NSLOT; ++p) ring_prefetch<G>(cx, p);
+    }
     mbar_wait(resbar, 0);
 
     for (long long it = 0; it < my_iters; ++it) {
@@ -442,7 +511,7 @@ __global__ void __launch_bounds__(TcFwdGeom<C, SPLIT>::NT, 1) node_tc_fwd_kernel
   }
   umma::fence_before_sync();
   __syncthreads();
-  if (warp == 0) umma::tmem_dealloc(tbase, G::G * T::TCOLS);
+  if (warp == 0) umma::tmem_dealloc(tbase, G::TMEM_COLS);
 }
 
 }  // namespace nlbac

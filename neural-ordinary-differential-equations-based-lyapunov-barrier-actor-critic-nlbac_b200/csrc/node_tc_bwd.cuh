@@ -62,10 +62,13 @@ struct TcBwdGeom {
   using T = TcCfg<C>;
   static constexpr int NSLOT = 2;
   static constexpr int fixed_bytes = NSLOT * T::W_BYTES + C::RES_ALL * 4 + 256;
-  static constexpr int G = (fixed_bytes + 2 * T::A_BYTES <= 227 * 1024) ? 2 : 1;
-  static constexpr int NT = G * 128 + 32;
+  static constexpr int GS = (fixed_bytes + 2 * T::A_BYTES <= 227 * 1024) ? 2 : 1;   // operand image in shared memory
+  static constexpr int GT = 1;                                                        // operand in tensor memory
+  static constexpr int G = GS + GT;
+  static constexpr int NT = G * 128;
+  static constexpr int TMEM_COLS = tmem_cols(G, GT);
   static constexpr int OFF_A = 0;
-  static constexpr int OFF_W = OFF_A + G * T::A_BYTES;
+  static constexpr int OFF_W = OFF_A + GS * T::A_BYTES;
   static constexpr int OFF_RES = OFF_W + NSLOT * T::W_BYTES;
   static constexpr int OFF_BAR = OFF_RES + C::RES_ALL * 4;
   static constexpr int NBAR = 2 * NSLOT + G + 1;
@@ -92,15 +95,19 @@ __device__ __forceinline__ void finish_act_img(unsigned char* img, int t) {
 }
 
 // one hidden-layer GEMM of the group's tile: A = the group's activation image, B = next ring packet
-template <class C, int NSLOT>
+template <class C, class GEO>
 __device__ __forceinline__ void tc_layer_mma(TcGroupCtx& cx) {
   using T = TcCfg<C>;
+  constexpr int NSLOT = GEO::NSLOT;
+  if (cx.keeper) ring_prefetch<GEO>(cx, cx.seq + NSLOT - 1);
   if (cx.lt == 0) {
     umma::fence_after_sync();
     const uint32_t slot = cx.seq % NSLOT;
     mbar_wait(&cx.full[slot], (cx.seq / NSLOT) & 1);
     umma::fence_after_sync();
-    tc_issue<C>(cx.tmma, cx.adesc, cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4)), 0u);
+    const uint64_t wd = cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4));
+    if (cx.tmemA) tc_issue_ts<C>(cx.tmma, cx.ta_mma, wd);
+    else tc_issue<C>(cx.tmma, cx.adesc, wd, 0u);
     umma::commit(&cx.empty[slot]);
     umma::commit(cx.done);
   }
@@ -110,11 +117,7 @@ __device__ __forceinline__ void tc_layer_mma(TcGroupCtx& cx) {
   umma::fence_after_sync();
 }
 
-__device__ __forceinline__ void tc_publish(TcGroupCtx& cx) {   // smem image written -> visible to the next MMA
-  fence_proxy_async();
-  umma::fence_before_sync();
-  group_sync(cx.g);
-}
+__device__ __forceinline__ void tc_publish(TcGroupCtx& cx) { act_publish<false>(cx); }
 
 // ReLU masks: 8 bits per group of 8 columns, 4 groups per word, 4 words per layer -- kept in registers and
 // addressed with selects so that the column loops can stay rolled (instruction-cache footprint)
@@ -194,8 +197,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
         or4(mk[0], q, nz_bits8(v) << (8 * u));
-        store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
-        store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
+        act_store8<C, false>(cx, g8, v);
         if (wimg) {
           if (C::H >= 8 * g8 && C::H < 8 * g8 + 8) v[C::H & 7] = 1.f;
           store_img8(ia, lt, 8 * g8, v);
@@ -231,7 +233,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
 #pragma unroll
     for (int l = 1; l <= G::NLAY - 1; ++l) {
       if (l <= n) {
-        tc_layer_mma<C, G::NSLOT>(cx);
+        tc_layer_mma<C, G>(cx);
         const float* bias = cx.sRes + C::off_bh(c, l);
         unsigned char* ia = img + IM::off_act(c, l + 1);
         if (l < n) {
@@ -242,8 +244,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
 #pragma unroll
             for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
             or4(mk[l], q, nz_bits8(v) << (8 * u));
-            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
-            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
+            act_store8<C, false>(cx, g8, v);
             if (wimg) {
               if (C::H >= 8 * g8 && C::H < 8 * g8 + 8) v[C::H & 7] = 1.f;
               store_img8(ia, lt, 8 * g8, v);
@@ -286,8 +287,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
               }
               dl[i] = (v[i] > 0.f && kk < C::H) ? dl[i] : 0.f;
             }
-            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, dl[0], dl[1], dl[2], dl[3]);
-            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, dl[4], dl[5], dl[6], dl[7]);
+            act_store8<C, false>(cx, g8, dl);
             if (wimg) {
               store_img8(id, lt, 8 * g8, dl);
               if (C::H >= 8 * g8 && C::H < 8 * g8 + 8) v[C::H & 7] = 1.f;
@@ -310,7 +310,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
 #pragma unroll
     for (int l = G::NLAY - 1; l >= 1; --l) {
       if (l <= n) {
-        tc_layer_mma<C, G::NSLOT>(cx);
+        tc_layer_mma<C, G>(cx);
         const float* Wn0 = cx.sRes + C::off_wn0(c);
         unsigned char* id = img + IM::off_del(c, l);
         tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
@@ -319,8 +319,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
           for (int i = 0; i < 8; ++i) v[i] = ((bits >> i) & 1u) ? v[i] : 0.f;
           if (wimg) store_img8(id, lt, 8 * g8, v);
           if (l > 1) {
-            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8, v[0], v[1], v[2], v[3]);
-            store_act4<false, T::ACH, T::A_BYTES>(cx.sA, lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
+            act_store8<C, false>(cx, g8, v);
           } else {   // d_1: thin first layer, dx = W0^T d_1
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -370,7 +369,6 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
   uint64_t* resbar = bars + 2 * G::NSLOT + G::G;
   uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + G::NBAR);
   const int tid = threadIdx.x, warp = tid / 32;
-  const bool is_prod = warp == G::G * 4;
   const Tableau tab = make_tableau(a.method);
   const int S = tab.S;
 
@@ -385,37 +383,35 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
     mbar_init(resbar, 1);
     fence_barrier_init();
   }
-  if (warp == 0) umma::tmem_alloc(tslot, G::G * T::TCOLS);
+  if (warp == 0) umma::tmem_alloc(tslot, G::TMEM_COLS);
   umma::fence_before_sync();
   __syncthreads();
   umma::fence_after_sync();
   const uint32_t tbase = *tslot;
 
-  if (is_prod) {
-    if (tid % 32 == 0 && my_iters > 0) {
-      mbar_expect_tx(resbar, C::RES_ALL * 4);
-      tma_load_1d(sRes, a.packed, C::RES_ALL * 4, resbar);
-      for (uint32_t p = 0; p < total; ++p) {
-        const uint32_t slot = p % G::NSLOT;
-        if (p >= (uint32_t)G::NSLOT) mbar_wait(&empty[slot], ((p / G::NSLOT) - 1) & 1);
-        mbar_expect_tx(&full[slot], T::W_BYTES);
-        tma_load_1d(smem_raw + G::OFF_W + slot * T::W_BYTES, a.packed + G::pkt_off(p), T::W_BYTES, &full[slot]);
-      }
-    }
-    __syncwarp();
-  } else if (my_iters > 0) {
+  if (my_iters > 0) {
     TcGroupCtx cx;
     cx.g = tid / 128;
     cx.lt = tid % 128;
-    cx.sA = smem_raw + G::OFF_A + cx.g * T::A_BYTES;
+    cx.tmemA = cx.g >= G::GS;
+    cx.sA = smem_raw + G::OFF_A + (cx.tmemA ? 0 : cx.g) * T::A_BYTES;
     cx.sW = smem_raw + G::OFF_W;
     cx.sRes = sRes;
     cx.full = full; cx.empty = empty; cx.done = &done[cx.g];
     cx.tmma = tbase + cx.g * T::TCOLS;
     cx.tacc = cx.tmma + ((uint32_t)((warp % 4) * 32) << 16);
+    cx.ta_mma = tbase + (G::G + (cx.tmemA ? cx.g - G::GS : 0)) * T::TCOLS;
+    cx.ta_row = cx.ta_mma + ((uint32_t)((warp % 4) * 32) << 16);
     cx.seq = 0; cx.nd = 0;
     cx.adesc = umma::make_desc(smem_u32(cx.sA), T::ACH, 128);
     cx.wdesc = umma::make_desc(smem_u32(cx.sW), T::WCH, 128);
+    cx.total = total; cx.packed = a.packed;
+    cx.keeper = tid == 32;
+    if (cx.keeper) {
+      mbar_expect_tx(resbar, C::RES_ALL * 4);
+      tma_load_1d(sRes, a.packed, C::RES_ALL * 4, resbar);
+      for (uint32_t p = 0; p + 1 < (uint32_t)G::NSLOT; ++p) ring_prefetch<G>(cx, p);
+    }
     mbar_wait(resbar, 0);
     const long long n_se = (long long)a.n_steps * S;
 
@@ -503,7 +499,7 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
   }
   umma::fence_before_sync();
   __syncthreads();
-  if (warp == 0) umma::tmem_dealloc(tbase, G::G * T::TCOLS);
+  if (warp == 0) umma::tmem_dealloc(tbase, G::TMEM_COLS);
 }
 
 // ------------------------------------------------------------------------------------------------
