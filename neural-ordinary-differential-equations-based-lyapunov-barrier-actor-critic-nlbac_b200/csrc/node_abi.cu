@@ -236,8 +236,8 @@ static int launch_pack_tc(const float* const* params, float* packed, cudaStream_
     for (int l = 0; l < C::nl(c); ++l, pi += 2)
       if (l >= 1 && l <= C::nhc(c)) {
         const int h = C::hid_base(c) + (l - 1);
-        pack_tc_kernel<C><<<16, 256, 0, st>>>(params[pi], packed + T::off_hi(h), packed + T::off_lo(h),
-                                              packed + T::off_tr(h));
+        pack_tc_kernel<C><<<16, 256, 0, st>>>(params[pi], params[pi + 1], packed + T::off_hi(h), packed + T::off_lo(h),
+                                              packed + T::off_tr(h), l == 1 ? packed + C::off_b0(c) + C::H : nullptr);
         NLBAC_CUDA(cudaGetLastError());
       }
   return 0;

@@ -33,6 +33,10 @@ struct TcCfg {
   static constexpr int W_FLOATS = NCHUNK * NP * 4;
   static constexpr int W_BYTES = W_FLOATS * 4;
   static constexpr int TCOLS = 128;                // TMEM columns reserved per group
+  // Hidden biases ride inside the GEMM when the K extent has a spare column (H = 100 -> KP = 104): activation
+  // column H is a constant 1 (first-layer bias image b0[H] = 1, weight image W[H][H] = 1 keeps it alive from layer
+  // to layer) and weight column H holds the bias, so the epilogue is ReLU only.  H = 64 has no spare column.
+  static constexpr bool FOLD = KP > C::H;
   static_assert(NP <= TCOLS && KP == C::HP, "tile shape");
   // packed image: [RES_ALL (thin layers fwd + bwd, node_cfg.cuh) | U_hi[NHID] | U_lo[NHID] | U_T[NHID]]
   //   U_hi / U_lo: B operand of the forward GEMM  (rows j = out, K = in);  U_T: B operand of dX (rows k = in, K = out)
@@ -65,15 +69,23 @@ __device__ __forceinline__ float tf32_rn(float x) {
   return __uint_as_float((__float_as_uint(x) + 0x1000u) & 0xFFFFE000u);
 }
 
+// ReLU and the TF32 rounding bias in ONE integer instruction (VIADDMNMX): max(bits + 0x1000, 0) as signed integers
+// -- negative floats are negative integers and stay so after the add
+__device__ __forceinline__ float relu_tf32_bias(float x) {
+  return __int_as_float(__viaddmax_s32(__float_as_int(x), 0x1000, 0));
+}
+
 // weight image of one hidden matrix: W[j][k] (nn.Linear [out][in]) -> float index (k/4)*NP*4 + j*4 + k%4
 template <class C>
-__global__ void pack_tc_kernel(const float* __restrict__ W, float* __restrict__ hi, float* __restrict__ lo,
-                               float* __restrict__ tr) {
+__global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restrict__ b, float* __restrict__ hi,
+                               float* __restrict__ lo, float* __restrict__ tr, float* __restrict__ b0_one) {
   using T = TcCfg<C>;
+  if (T::FOLD && b0_one != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *b0_one = 1.f;   // a_1[H] = relu(1) = 1
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < T::W_FLOATS; i += gridDim.x * blockDim.x) {
     const int c = i / (T::NP * 4), j = (i / 4) % T::NP, k = 4 * c + (i & 3);
     const bool in = j < C::H && k < C::H;
-    const float w = in ? W[j * C::H + k] : 0.f;
+    float w = in ? W[j * C::H + k] : 0.f;
+    if (T::FOLD && k == C::H) w = j < C::H ? b[j] : (j == C::H ? 1.f : 0.f);
     const float h = tf32_hi(w);
     hi[i] = h;
     lo[i] = w - h;
@@ -194,6 +206,18 @@ __device__ __forceinline__ void act_store8(const TcGroupCtx& cx, int g8, const f
     store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, cx.lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
   }
 }
+// same for values that already carry their TF32 rounding (relu_tf32_bias)
+template <class C>
+__device__ __forceinline__ void act_store8_raw(const TcGroupCtx& cx, int g8, const float (&r)[8]) {
+  using T = TcCfg<C>;
+  if (cx.tmemA) {
+    umma::st8(cx.ta_row + 8 * g8, r);
+  } else {
+    unsigned char* p = cx.sA + (g8 * 2) * T::ACH + (cx.lt >> 3) * 128 + (cx.lt & 7) * 16;
+    *reinterpret_cast<float4*>(p) = make_float4(r[0], r[1], r[2], r[3]);
+    *reinterpret_cast<float4*>(p + T::ACH) = make_float4(r[4], r[5], r[6], r[7]);
+  }
+}
 // operand written -> visible to the MMA the group's elected thread issues next
 template <bool SPLIT>
 __device__ __forceinline__ void act_publish(const TcGroupCtx& cx) {
@@ -269,9 +293,15 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
           v[0] = fmaf(xv, wa.x, v[0]); v[1] = fmaf(xv, wa.y, v[1]); v[2] = fmaf(xv, wa.z, v[2]); v[3] = fmaf(xv, wa.w, v[3]);
           v[4] = fmaf(xv, wb.x, v[4]); v[5] = fmaf(xv, wb.y, v[5]); v[6] = fmaf(xv, wb.z, v[6]); v[7] = fmaf(xv, wb.w, v[7]);
         }
+        if (SPLIT) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
-        act_store8<C, SPLIT>(cx, g8, v);
+          for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+          act_store8<C, SPLIT>(cx, g8, v);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) v[i] = relu_tf32_bias(v[i]);
+          act_store8_raw<C>(cx, g8, v);
+        }
       }
     }
     act_publish<SPLIT>(cx);
@@ -313,12 +343,22 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
       constexpr int NG8 = T::KP / 8;
       if (l < n) {  // ---- epilogue: bias + ReLU -> activation image (in place) ----
         tc_batches<NG8, true>(cx.tacc, [&](int, int, int g8, float (&v)[8]) {
-          const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * g8);
-          const float4 b1 = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
-          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+          if (!T::FOLD) {
+            const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * g8);
+            const float4 b1 = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-          for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i] + bb[i], 0.f);
-          act_store8<C, SPLIT>(cx, g8, v);
+            for (int i = 0; i < 8; ++i) v[i] += bb[i];
+          }
+          if (SPLIT) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
+            act_store8<C, SPLIT>(cx, g8, v);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = relu_tf32_bias(v[i]);
+            act_store8_raw<C>(cx, g8, v);
+          }
         });
         act_publish<SPLIT>(cx);
       } else {  // ---- last hidden layer: bias + ReLU, thin output layer folded in registers ----
@@ -328,14 +368,18 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
 #pragma unroll
         for (int j = 0; j < C::OUTP_MAX; ++j) o[j] = j < OUTP ? bL[j] : 0.f;
         tc_batches<NG8, true>(cx.tacc, [&](int, int, int g8, float (&v)[8]) {
-          const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * g8);
-          const float4 b1 = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
-          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+          if (!T::FOLD) {
+            const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * g8);
+            const float4 b1 = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
+            const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] += bb[i];
+          }
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const int kk = 8 * g8 + i;
             if (kk < C::H) {
-              const float h = fmaxf(v[i] + bb[i], 0.f);
+              const float h = fmaxf(v[i], 0.f);
 #pragma unroll
               for (int j = 0; j < C::OUTP_MAX; j += 4)
                 if (j < OUTP) {

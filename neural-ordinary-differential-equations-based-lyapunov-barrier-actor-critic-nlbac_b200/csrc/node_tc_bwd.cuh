@@ -57,6 +57,19 @@ __device__ __forceinline__ void store_img8(unsigned char* img, int t, int c0, co
   *reinterpret_cast<Pack8*>(img + (c0 >> 3) * 2048 + (t >> 3) * 128 + (t & 7) * 16) = p;
 }
 
+// same with ReLU applied by the conversion itself (cvt.rn.relu.bf16x2.f32: negative inputs and NaN give +0)
+__device__ __forceinline__ uint32_t pack_relu_bf16x2(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ void store_img8_relu(unsigned char* img, int t, int c0, const float (&v)[8]) {
+  uint4 p;
+  p.x = pack_relu_bf16x2(v[0], v[1]); p.y = pack_relu_bf16x2(v[2], v[3]);
+  p.z = pack_relu_bf16x2(v[4], v[5]); p.w = pack_relu_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(img + (c0 >> 3) * 2048 + (t >> 3) * 128 + (t & 7) * 16) = p;
+}
+
 template <class C>
 struct TcBwdGeom {
   using T = TcCfg<C>;
@@ -128,15 +141,34 @@ __device__ __forceinline__ void or4(uint32_t (&m)[4], int q, uint32_t w) {
   m[0] |= q == 0 ? w : 0u; m[1] |= q == 1 ? w : 0u; m[2] |= q == 2 ? w : 0u; m[3] |= q == 3 ? w : 0u;
 }
 
-// bit i = (v[i] != 0) for eight ReLU outputs (v >= 0): the carry out of bits(v) + 0x7FFFFFFF, gathered by funnel shifts
-__device__ __forceinline__ uint32_t nz_bits8(const float (&v)[8]) {
+// ReLU mask of eight PRE-activations: bit i = !(sign bit of v[i]), gathered by funnel shifts (one instruction per
+// element).  An exactly-zero pre-activation therefore passes its cotangent (relu'(0) = 1 here, 0 in PyTorch): a
+// measure-zero set inside a tier whose operand rounding already moves pre-activations across zero; the padded
+// columns and dead rows where exact zeros do occur carry zero cotangents anyway.
+__device__ __forceinline__ uint32_t pos_bits8(const float (&v)[8]) {
   uint32_t lo = 0u, hi = 0u;
 #pragma unroll
   for (int i = 3; i >= 0; --i) {
-    lo = __funnelshift_l(__float_as_uint(v[i]) + 0x7FFFFFFFu, lo, 1);
-    hi = __funnelshift_l(__float_as_uint(v[i + 4]) + 0x7FFFFFFFu, hi, 1);
+    lo = __funnelshift_l(__float_as_uint(v[i]), lo, 1);
+    hi = __funnelshift_l(__float_as_uint(v[i + 4]), hi, 1);
   }
-  return lo | (hi << 4);
+  return (lo | (hi << 4)) ^ 0xFFu;
+}
+
+// Epilogue of a forward layer of the sweep for 8 pre-activations v (bias included): ReLU mask bits -> mk, the
+// activation -> the group's MMA operand (ReLU + TF32 rounding in one integer instruction) and, rounded to bf16 with
+// the ReLU folded into the conversion, -> the HBM image.  The ones column of the image (bias gradients, column H)
+// needs no special case where the bias is folded (TcCfg::FOLD): the pre-activation of column H is the constant 1.
+template <class C>
+__device__ __forceinline__ void relu_publish8(const TcGroupCtx& cx, uint32_t (&mk)[4], int q, int u, int g8,
+                                              float (&v)[8], unsigned char* ia) {
+  using T = TcCfg<C>;
+  or4(mk, q, pos_bits8(v) << (8 * u));
+  if (ia != nullptr) store_img8_relu(ia, cx.lt, 8 * g8, v);
+  float r[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) r[i] = relu_tf32_bias(v[i]);
+  act_store8_raw<C>(cx, g8, r);
 }
 
 // One stage of the reverse sweep for the group's tile (mirrors vjp_rhs_tile of node_bwd.cuh).
@@ -194,14 +226,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
           v[0] = fmaf(xv, wa.x, v[0]); v[1] = fmaf(xv, wa.y, v[1]); v[2] = fmaf(xv, wa.z, v[2]); v[3] = fmaf(xv, wa.w, v[3]);
           v[4] = fmaf(xv, wb.x, v[4]); v[5] = fmaf(xv, wb.y, v[5]); v[6] = fmaf(xv, wb.z, v[6]); v[7] = fmaf(xv, wb.w, v[7]);
         }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
-        or4(mk[0], q, nz_bits8(v) << (8 * u));
-        act_store8<C, false>(cx, g8, v);
-        if (wimg) {
-          if (C::H >= 8 * g8 && C::H < 8 * g8 + 8) v[C::H & 7] = 1.f;
-          store_img8(ia, lt, 8 * g8, v);
-        }
+        relu_publish8<C>(cx, mk[0], q, u, g8, v, wimg ? ia : nullptr);
       });
       if (wimg) finish_act_img<C>(ia, lt);
     }
@@ -238,17 +263,12 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
         unsigned char* ia = img + IM::off_act(c, l + 1);
         if (l < n) {
           tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
-            const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
-            const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
-            v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
-#pragma unroll
-            for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
-            or4(mk[l], q, nz_bits8(v) << (8 * u));
-            act_store8<C, false>(cx, g8, v);
-            if (wimg) {
-              if (C::H >= 8 * g8 && C::H < 8 * g8 + 8) v[C::H & 7] = 1.f;
-              store_img8(ia, lt, 8 * g8, v);
+            if (!T::FOLD) {
+              const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
+              const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
+              v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
             }
+            relu_publish8<C>(cx, mk[l], q, u, g8, v, wimg ? ia : nullptr);
           });
         } else {
           // last hidden activation: forward value of g(x) (action gradient) and d_{n+1} = relu' * WL^T dOut
@@ -256,12 +276,14 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
           const float* WtL = cx.sRes + C::off_wtl(c);
           unsigned char* id = img + IM::off_del(c, n + 1);
           tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
-            const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
-            const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
-            v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
+            if (!T::FOLD) {
+              const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
+              const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
+              v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
+            }
             float dl[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { v[i] = fmaxf(v[i], 0.f); dl[i] = 0.f; }
+            for (int i = 0; i < 8; ++i) { if (c == 1) v[i] = fmaxf(v[i], 0.f); dl[i] = 0.f; }
             // d_{n+1}[k] = sum_o dOut[o] WL[o][k]: two 16-byte weight loads per output row and column group
 #pragma unroll
             for (int o = 0; o < C::OUTP_MAX; ++o)
@@ -290,8 +312,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
             act_store8<C, false>(cx, g8, dl);
             if (wimg) {
               store_img8(id, lt, 8 * g8, dl);
-              if (C::H >= 8 * g8 && C::H < 8 * g8 + 8) v[C::H & 7] = 1.f;
-              store_img8(ia, lt, 8 * g8, v);
+                          store_img8_relu(ia, lt, 8 * g8, v);
             }
           });
         }

@@ -57,7 +57,15 @@ class EmuSeq(nn.Module):
         lin = [m for m in self.seq if isinstance(m, nn.Linear)]
         for i, l in enumerate(lin):
             hidden = 0 < i < len(lin) - 1
-            x = EmuLinear.apply(x, l.weight, l.bias, self.mode) if hidden else nn.functional.linear(x, l.weight, l.bias)
+            if hidden:
+                # csrc/node_tc.cuh TcCfg::FOLD: where the K extent has a spare column (H % 8 != 0) the hidden bias is a
+                # column of the weight image and is rounded with it (its gradient is unaffected)
+                b = l.bias
+                if self.mode.split("+")[0] == "tf32" and l.in_features % 8 != 0:
+                    b = b + (rtf32(b.detach()) - b.detach())
+                x = EmuLinear.apply(x, l.weight, b, self.mode)
+            else:
+                x = nn.functional.linear(x, l.weight, l.bias)
             if i < len(lin) - 1: x = torch.relu(x)
         return x
 

@@ -302,9 +302,17 @@ def test_tensor_core_tier_methods_and_interpolation(method, step_size):
     assert _rel(sb, sa) <= 1e-4, _rel(sb, sa)
     assert _rel(yb.grad, ya.grad) <= 2e-3, _rel(yb.grad, ya.grad)
     # the kernels and the emulation round the same operands but sum in different orders: a few ReLU decisions per
-    # matrix differ at B = 4500 (measured up to 4.5e-3 on one matrix for the 9-step euler case)
-    for (k, p), q in zip(ours.named_parameters(), emu.parameters()):
-        assert _rel(p.grad, q.grad) <= 6e-3, (k, _rel(p.grad, q.grad))
+    # matrix differ at B = 4500.  A single flipped decision moves a g_net gradient by ~1e-2 of its max-norm at this
+    # batch size (the emulation itself sits 1e-2..5e-2 from the fp32 oracle on those tensors,
+    # gpurun tools/diag_tc2.py), so the bar per tensor is 6e-3 or the emulation's own distance from fp32,
+    # whichever is larger -- the kernel may not be further from the emulation than the tier is from fp32.
+    ref.zero_grad()
+    yr = y0.clone().requires_grad_(True)
+    (oracle_odeint(ref, yr, t, method=method, **opts) * w).pow(2).sum().backward()
+    for (k, p), q, r in zip(ours.named_parameters(), emu.parameters(), ref.parameters()):
+        bar = max(6e-3, _rel(q.grad, r.grad))
+        assert _rel(p.grad, q.grad) <= bar, (k, _rel(p.grad, q.grad), bar)
+        assert _rel(p.grad, r.grad) <= 5e-2, (k, _rel(p.grad, r.grad))    # declared tier bar at small batch
 
 
 def test_tensor_core_tier_at_full_size():
