@@ -75,6 +75,24 @@ __device__ __forceinline__ float relu_tf32_bias(float x) {
   return __int_as_float(__viaddmax_s32(__float_as_int(x), 0x1000, 0));
 }
 
+// Eight fp32 accumulators as four packed pairs: the thin layers run on fma.rn.f32x2 (SASS FFMA2, one issue slot for
+// two IEEE FMAs -- common.cuh), which halves their share of the epilogue's instruction stream.
+struct Acc8 { unsigned long long p[4]; };
+__device__ __forceinline__ void acc8_init(Acc8& a, const float4& lo, const float4& hi) {
+  a.p[0] = pack2(lo.x, lo.y); a.p[1] = pack2(lo.z, lo.w); a.p[2] = pack2(hi.x, hi.y); a.p[3] = pack2(hi.z, hi.w);
+}
+__device__ __forceinline__ void acc8_zero(Acc8& a) { a.p[0] = a.p[1] = a.p[2] = a.p[3] = 0ull; }
+// a[0..8) += s * w[0..8)
+__device__ __forceinline__ void acc8_fma(Acc8& a, float s, const float4& wa, const float4& wb) {
+  const unsigned long long ss = pack2(s, s);
+  a.p[0] = fma2(ss, pack2(wa.x, wa.y), a.p[0]); a.p[1] = fma2(ss, pack2(wa.z, wa.w), a.p[1]);
+  a.p[2] = fma2(ss, pack2(wb.x, wb.y), a.p[2]); a.p[3] = fma2(ss, pack2(wb.z, wb.w), a.p[3]);
+}
+__device__ __forceinline__ void acc8_get(const Acc8& a, float (&v)[8]) {
+  unpack2(a.p[0], v[0], v[1]); unpack2(a.p[1], v[2], v[3]); unpack2(a.p[2], v[4], v[5]); unpack2(a.p[3], v[6], v[7]);
+}
+__device__ __forceinline__ float pair_sum(unsigned long long a) { float lo, hi; unpack2(a, lo, hi); return lo + hi; }
+
 // weight image of one hidden matrix: W[j][k] (nn.Linear [out][in]) -> float index (k/4)*NP*4 + j*4 + k%4
 template <class C>
 __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restrict__ b, float* __restrict__ hi,
@@ -282,17 +300,16 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
       const float* b0 = cx.sRes + C::off_b0(c);
 #pragma unroll 1
       for (int g8 = 0; g8 < T::KP / 8; ++g8) {
-        const float4 ba = *reinterpret_cast<const float4*>(b0 + 8 * g8);
-        const float4 bb = *reinterpret_cast<const float4*>(b0 + 8 * g8 + 4);
-        float v[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+        Acc8 acc;
+        acc8_init(acc, *reinterpret_cast<const float4*>(b0 + 8 * g8), *reinterpret_cast<const float4*>(b0 + 8 * g8 + 4));
 #pragma unroll
         for (int d = 0; d < C::IN0; ++d) {
           const float xv = d < C::NS ? x[d < C::NS ? d : 0] : cst[d >= C::NS ? d - C::NS : 0];
-          const float4 wa = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8);
-          const float4 wb = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8 + 4);
-          v[0] = fmaf(xv, wa.x, v[0]); v[1] = fmaf(xv, wa.y, v[1]); v[2] = fmaf(xv, wa.z, v[2]); v[3] = fmaf(xv, wa.w, v[3]);
-          v[4] = fmaf(xv, wb.x, v[4]); v[5] = fmaf(xv, wb.y, v[5]); v[6] = fmaf(xv, wb.z, v[6]); v[7] = fmaf(xv, wb.w, v[7]);
+          acc8_fma(acc, xv, *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8),
+                   *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8 + 4));
         }
+        float v[8];
+        acc8_get(acc, v);
         if (SPLIT) {
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[i] = fmaxf(v[i], 0.f);
@@ -365,8 +382,9 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
         const int OUTP = C::outp(c);
         const float* WtL = cx.sRes + C::off_wtl(c);
         const float* bL = cx.sRes + C::off_bl(c);
+        unsigned long long o2[C::OUTP_MAX / 2];
 #pragma unroll
-        for (int j = 0; j < C::OUTP_MAX; ++j) o[j] = j < OUTP ? bL[j] : 0.f;
+        for (int j = 0; j < C::OUTP_MAX; j += 2) o2[j / 2] = j < OUTP ? pack2(bL[j], bL[j + 1]) : 0ull;
         tc_batches<NG8, true>(cx.tacc, [&](int, int, int g8, float (&v)[8]) {
           if (!T::FOLD) {
             const float4 b0 = *reinterpret_cast<const float4*>(bias + 8 * g8);
@@ -380,16 +398,19 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
             const int kk = 8 * g8 + i;
             if (kk < C::H) {
               const float h = fmaxf(v[i], 0.f);
+              const unsigned long long hh = pack2(h, h);
 #pragma unroll
               for (int j = 0; j < C::OUTP_MAX; j += 4)
                 if (j < OUTP) {
                   const float4 w = *reinterpret_cast<const float4*>(WtL + kk * OUTP + j);
-                  o[j] = fmaf(h, w.x, o[j]); o[j + 1] = fmaf(h, w.y, o[j + 1]);
-                  o[j + 2] = fmaf(h, w.z, o[j + 2]); o[j + 3] = fmaf(h, w.w, o[j + 3]);
+                  o2[j / 2] = fma2(hh, pack2(w.x, w.y), o2[j / 2]);
+                  o2[j / 2 + 1] = fma2(hh, pack2(w.z, w.w), o2[j / 2 + 1]);
                 }
             }
           }
         });
+#pragma unroll
+        for (int j = 0; j < C::OUTP_MAX; j += 2) unpack2(o2[j / 2], o[j], o[j + 1]);
       }
     }
     if (c == 0) {

@@ -184,9 +184,9 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
   static_assert(NG8 <= 16, "mask words");
   const int lt = cx.lt;
   const bool wimg = img != nullptr;
-  float dxa[C::INP0];
+  unsigned long long dxa2[C::IN0];   // dL/d(stage input), even / odd hidden units in the two halves
 #pragma unroll
-  for (int d = 0; d < C::INP0; ++d) dxa[d] = 0.f;
+  for (int d = 0; d < C::IN0; ++d) dxa2[d] = 0ull;
   if (wimg) {   // stage input image (shared by the chains): [x | const | 1 | 0...]
     float v0[8], v1[8];
 #pragma unroll
@@ -215,26 +215,27 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
       const float* b0 = cx.sRes + C::off_b0(c);
       unsigned char* ia = img + IM::off_act(c, 1);
       tc_batches<NG8, false>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
-        const float4 ba = *reinterpret_cast<const float4*>(b0 + 8 * g8);
-        const float4 bb = *reinterpret_cast<const float4*>(b0 + 8 * g8 + 4);
-        v[0] = ba.x; v[1] = ba.y; v[2] = ba.z; v[3] = ba.w; v[4] = bb.x; v[5] = bb.y; v[6] = bb.z; v[7] = bb.w;
+        Acc8 acc;
+        acc8_init(acc, *reinterpret_cast<const float4*>(b0 + 8 * g8), *reinterpret_cast<const float4*>(b0 + 8 * g8 + 4));
 #pragma unroll
         for (int d = 0; d < C::IN0; ++d) {
           const float xv = d < C::NS ? x[d < C::NS ? d : 0] : cst[d >= C::NS ? d - C::NS : 0];
-          const float4 wa = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8);
-          const float4 wb = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8 + 4);
-          v[0] = fmaf(xv, wa.x, v[0]); v[1] = fmaf(xv, wa.y, v[1]); v[2] = fmaf(xv, wa.z, v[2]); v[3] = fmaf(xv, wa.w, v[3]);
-          v[4] = fmaf(xv, wb.x, v[4]); v[5] = fmaf(xv, wb.y, v[5]); v[6] = fmaf(xv, wb.z, v[6]); v[7] = fmaf(xv, wb.w, v[7]);
+          acc8_fma(acc, xv, *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8),
+                   *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8 + 4));
         }
+        acc8_get(acc, v);
         relu_publish8<C>(cx, mk[0], q, u, g8, v, wimg ? ia : nullptr);
       });
       if (wimg) finish_act_img<C>(ia, lt);
     }
     tc_publish(cx);
     // cotangent of the chain output
-    float dout[C::OUTP_MAX], go[C::OUTP_MAX];
+    float dout[C::OUTP_MAX];
+    unsigned long long dc2[C::NU > 0 ? C::NU : 1];   // chain 1: dL/du_j, even / odd hidden units in the two halves
 #pragma unroll
-    for (int o = 0; o < C::OUTP_MAX; ++o) { dout[o] = 0.f; go[o] = 0.f; }
+    for (int o = 0; o < C::OUTP_MAX; ++o) dout[o] = 0.f;
+#pragma unroll
+    for (int j = 0; j < (C::NU > 0 ? C::NU : 1); ++j) dc2[j] = 0ull;
     if (c == 0) {
 #pragma unroll
       for (int o = 0; o < C::NS; ++o) dout[o] = dk[o];
@@ -273,7 +274,6 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
         } else {
           // last hidden activation: forward value of g(x) (action gradient) and d_{n+1} = relu' * WL^T dOut
           const float* WnL = cx.sRes + C::off_wnl(c);
-          const float* WtL = cx.sRes + C::off_wtl(c);
           unsigned char* id = img + IM::off_del(c, n + 1);
           tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
             if (!T::FOLD) {
@@ -282,33 +282,41 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
               v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
             }
             float dl[8];
+            Acc8 da;
+            acc8_zero(da);
+            if (c == 0) {
+              // d_{n+1}[k] = sum_o dOut[o] WL[o][k]: two 16-byte weight loads per output row and column group
 #pragma unroll
-            for (int i = 0; i < 8; ++i) { if (c == 1) v[i] = fmaxf(v[i], 0.f); dl[i] = 0.f; }
-            // d_{n+1}[k] = sum_o dOut[o] WL[o][k]: two 16-byte weight loads per output row and column group
+              for (int o = 0; o < C::OUTP_MAX; ++o)
+                if (o < OUT)
+                  acc8_fma(da, dout[o], *reinterpret_cast<const float4*>(WnL + o * C::HP + 8 * g8),
+                           *reinterpret_cast<const float4*>(WnL + o * C::HP + 8 * g8 + 4));
+            } else {
+              // chain g, output (i, j) -> dOut = dk[i] u_j.  With q_j[k] = sum_i dk[i] WL[(i,j)][k]:
+              //   d_{n+1}[k] = sum_j u_j q_j[k]        and        dL/du_j += sum_k a_{n+1}[k] q_j[k]
+              // (the second is the forward value g(x) contracted with dk without ever forming g(x))
+              unsigned long long a2[4];
 #pragma unroll
-            for (int o = 0; o < C::OUTP_MAX; ++o)
-              if (o < OUT) {
-                const float4 wa = *reinterpret_cast<const float4*>(WnL + o * C::HP + 8 * g8);
-                const float4 wb = *reinterpret_cast<const float4*>(WnL + o * C::HP + 8 * g8 + 4);
-                dl[0] = fmaf(dout[o], wa.x, dl[0]); dl[1] = fmaf(dout[o], wa.y, dl[1]);
-                dl[2] = fmaf(dout[o], wa.z, dl[2]); dl[3] = fmaf(dout[o], wa.w, dl[3]);
-                dl[4] = fmaf(dout[o], wb.x, dl[4]); dl[5] = fmaf(dout[o], wb.y, dl[5]);
-                dl[6] = fmaf(dout[o], wb.z, dl[6]); dl[7] = fmaf(dout[o], wb.w, dl[7]);
+              for (int p = 0; p < 4; ++p) a2[p] = pack2(fmaxf(v[2 * p], 0.f), fmaxf(v[2 * p + 1], 0.f));
+#pragma unroll
+              for (int j = 0; j < C::NU; ++j) {
+                Acc8 qa;
+                acc8_zero(qa);
+#pragma unroll
+                for (int i = 0; i < C::NS; ++i)
+                  acc8_fma(qa, dk[i], *reinterpret_cast<const float4*>(WnL + (i * C::NU + j) * C::HP + 8 * g8),
+                           *reinterpret_cast<const float4*>(WnL + (i * C::NU + j) * C::HP + 8 * g8 + 4));
+                const unsigned long long uu = pack2(cst[j], cst[j]);
+#pragma unroll
+                for (int p = 0; p < 4; ++p) {
+                  da.p[p] = fma2(uu, qa.p[p], da.p[p]);
+                  dc2[j] = fma2(a2[p], qa.p[p], dc2[j]);
+                }
               }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int kk = 8 * g8 + i;
-              if (c == 1 && kk < C::H) {
-#pragma unroll
-                for (int o = 0; o < C::OUTP_MAX; o += 4)
-                  if (o < OUTP) {
-                    const float4 w = *reinterpret_cast<const float4*>(WtL + kk * OUTP + o);
-                    go[o] = fmaf(v[i], w.x, go[o]); go[o + 1] = fmaf(v[i], w.y, go[o + 1]);
-                    go[o + 2] = fmaf(v[i], w.z, go[o + 2]); go[o + 3] = fmaf(v[i], w.w, go[o + 3]);
-                  }
-              }
-              dl[i] = (v[i] > 0.f && kk < C::H) ? dl[i] : 0.f;
             }
+            acc8_get(da, dl);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) dl[i] = (v[i] > 0.f && 8 * g8 + i < C::H) ? dl[i] : 0.f;
             act_store8<C, false>(cx, g8, dl);
             if (wimg) {
               store_img8(id, lt, 8 * g8, dl);
@@ -323,16 +331,19 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
     if (c == 1) {   // dL/du_j += sum_i g(x)[i][j] dk[i]   (bias of the last layer included)
       const float* bL = cx.sRes + C::off_bl(c);
 #pragma unroll
-      for (int i = 0; i < C::NS; ++i)
+      for (int j = 0; j < C::NU; ++j) {
+        float acc = pair_sum(dc2[j]);
 #pragma unroll
-        for (int j = 0; j < C::NU; ++j) dcst[j] = fmaf(go[i * C::NU + j] + bL[i * C::NU + j], dk[i], dcst[j]);
+        for (int i = 0; i < C::NS; ++i) acc = fmaf(bL[i * C::NU + j], dk[i], acc);
+        dcst[j] += acc;
+      }
     }
     // ---------------- hidden layers backward: d_l = relu'(a_l) * H_l^T d_{l+1} ----------------
 #pragma unroll
     for (int l = G::NLAY - 1; l >= 1; --l) {
       if (l <= n) {
         tc_layer_mma<C, G>(cx);
-        const float* Wn0 = cx.sRes + C::off_wn0(c);
+        const float* Wt0 = cx.sRes + C::off_wt0(c);
         unsigned char* id = img + IM::off_del(c, l);
         tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
           const uint32_t bits = (sel4(mk[l - 1], q) >> (8 * u)) & 0xFFu;
@@ -341,18 +352,16 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
           if (wimg) store_img8(id, lt, 8 * g8, v);
           if (l > 1) {
             act_store8<C, false>(cx, g8, v);
-          } else {   // d_1: thin first layer, dx = W0^T d_1
+          } else {   // d_1: thin first layer, dx = W0^T d_1 (rows of the transposed image; padded columns are zero)
+            unsigned long long d2[4];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              const int j = 8 * g8 + i;
-              if (j < C::H) {
+            for (int p = 0; p < 4; ++p) d2[p] = pack2(v[2 * p], v[2 * p + 1]);
 #pragma unroll
-                for (int d = 0; d < C::INP0; d += 4) {
-                  const float4 w = *reinterpret_cast<const float4*>(Wn0 + j * C::INP0 + d);
-                  dxa[d] = fmaf(v[i], w.x, dxa[d]); dxa[d + 1] = fmaf(v[i], w.y, dxa[d + 1]);
-                  dxa[d + 2] = fmaf(v[i], w.z, dxa[d + 2]); dxa[d + 3] = fmaf(v[i], w.w, dxa[d + 3]);
-                }
-              }
+            for (int d = 0; d < C::IN0; ++d) {
+              const float4 wa = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8);
+              const float4 wb = *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8 + 4);
+              dxa2[d] = fma2(d2[0], pack2(wa.x, wa.y), dxa2[d]); dxa2[d] = fma2(d2[1], pack2(wa.z, wa.w), dxa2[d]);
+              dxa2[d] = fma2(d2[2], pack2(wb.x, wb.y), dxa2[d]); dxa2[d] = fma2(d2[3], pack2(wb.z, wb.w), dxa2[d]);
             }
           }
         });
@@ -361,10 +370,10 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
     }
   }
 #pragma unroll
-  for (int d = 0; d < C::NS; ++d) dx[d] = dxa[d];
+  for (int d = 0; d < C::NS; ++d) dx[d] = pair_sum(dxa2[d]);
   if constexpr (C::KIND == KIND_BLACKBOX) {
 #pragma unroll
-    for (int d = 0; d < C::NCONST; ++d) dcst[d] += dxa[C::NS + d];
+    for (int d = 0; d < C::NCONST; ++d) dcst[d] += pair_sum(dxa2[C::NS + d]);
   }
 }
 
