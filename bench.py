@@ -30,7 +30,7 @@ N_STEPS = 20
 DT = 0.02
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at the bench size, from the
 # `ncu --set full` capture committed under profiles/ (r1_ncu_bench_*.txt); None until captured for that tier
-NCU_TRAFFIC = {"fp32": None, "tf32": 18.54e9, "3xtf32": None}   # tf32: profiles/r1_ncu_bench_tc_tf32.txt (0.18 GB read + 18.36 GB written)
+NCU_TRAFFIC = {"fp32": None, "tf32": 13.75e9, "3xtf32": None}   # tf32: profiles/r1_ncu_bench_tc_tf32.txt, one pass-A chunk launch (0.21 GB read + 13.54 GB written; 19 launches per pass)
 
 
 def parse():

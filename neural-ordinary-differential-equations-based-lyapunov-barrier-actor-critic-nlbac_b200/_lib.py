@@ -66,7 +66,7 @@ def build(force=False, verbose=False):
     for s in srcs:
         o = s[:-3] + ".o"
         objs.append(o)
-        cmd = [nvcc] + NVCC_FLAGS + ["-c", s, "-o", o]
+        cmd = [nvcc] + NVCC_FLAGS + os.environ.get("NLBAC_NVCC_EXTRA", "").split() + ["-c", s, "-o", o]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
         procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT)))

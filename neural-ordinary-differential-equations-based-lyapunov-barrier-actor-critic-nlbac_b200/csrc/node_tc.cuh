@@ -164,8 +164,10 @@ __device__ __forceinline__ void store_act4(unsigned char* img, int r, int c, flo
 // Visit the accumulator row in batches of 4 x 8 columns: up to four tcgen05.ld in flight, ONE wait per batch.
 // body(q, u, g8, v): q = batch (rolled loop over the full batches; the remainder is a separate, guard-free tail),
 // u = 0..3 (unrolled), g8 = 4q + u = column group, v = 8 columns.
-template <int NG8, bool LOAD, class F>
-__device__ __forceinline__ void tc_batches(uint32_t tacc, F&& body) {
+struct NoPost { __device__ __forceinline__ void operator()(int) const {} };
+// post(q) runs once after the (up to four) column groups of batch q
+template <int NG8, bool LOAD, class F, class P = NoPost>
+__device__ __forceinline__ void tc_batches(uint32_t tacc, F&& body, P&& post = P()) {
   constexpr int NFULL = NG8 / 4, REM = NG8 % 4;
 #pragma unroll 1
   for (int q = 0; q < NFULL; ++q) {
@@ -177,6 +179,7 @@ __device__ __forceinline__ void tc_batches(uint32_t tacc, F&& body) {
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) body(q, u, 4 * q + u, v[u]);
+    post(q);
   }
   if (REM > 0) {
     float v[REM > 0 ? REM : 1][8];
@@ -187,6 +190,7 @@ __device__ __forceinline__ void tc_batches(uint32_t tacc, F&& body) {
     }
 #pragma unroll
     for (int u = 0; u < REM; ++u) body(NFULL, u, 4 * NFULL + u, v[u]);
+    post(NFULL);
   }
 }
 
@@ -208,6 +212,9 @@ struct TcGroupCtx {
   uint32_t ta_mma;         // TMEM address of the group's activation operand (lane 0)
   bool tmemA;
   int lt, g;
+#ifdef NLBAC_TC_PROF   // -DNLBAC_TC_PROF: cycle breakdown of the MMA round trip (tools/tc_roundtrip.py), debug builds only
+  long long pf_t, pf_epi, pf_full, pf_issue, pf_done, pf_n;
+#endif
 };
 
 // 8 consecutive features [8 g8, 8 g8 + 8) of the owner's activation row -> A operand of the group's next MMA

@@ -113,21 +113,35 @@ __device__ __forceinline__ void tc_layer_mma(TcGroupCtx& cx) {
   using T = TcCfg<C>;
   constexpr int NSLOT = GEO::NSLOT;
   if (cx.keeper) ring_prefetch<GEO>(cx, cx.seq + NSLOT - 1);
+#ifdef NLBAC_TC_PROF
+  long long p0 = clock64(), p1 = p0, p2 = p0;
+  cx.pf_epi += p0 - cx.pf_t;
+#endif
   if (cx.lt == 0) {
     umma::fence_after_sync();
     const uint32_t slot = cx.seq % NSLOT;
     mbar_wait(&cx.full[slot], (cx.seq / NSLOT) & 1);
     umma::fence_after_sync();
+#ifdef NLBAC_TC_PROF
+    p1 = clock64();
+#endif
     const uint64_t wd = cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4));
     if (cx.tmemA) tc_issue_ts<C>(cx.tmma, cx.ta_mma, wd);
     else tc_issue<C>(cx.tmma, cx.adesc, wd, 0u);
     umma::commit(&cx.empty[slot]);
     umma::commit(cx.done);
+#ifdef NLBAC_TC_PROF
+    p2 = clock64();
+#endif
   }
   ++cx.seq;
   mbar_wait(cx.done, cx.nd & 1);
   ++cx.nd;
   umma::fence_after_sync();
+#ifdef NLBAC_TC_PROF
+  cx.pf_t = clock64();
+  cx.pf_full += p1 - p0; cx.pf_issue += p2 - p1; cx.pf_done += cx.pf_t - p2; ++cx.pf_n;
+#endif
 }
 
 __device__ __forceinline__ void tc_publish(TcGroupCtx& cx) { act_publish<false>(cx); }
@@ -160,10 +174,10 @@ __device__ __forceinline__ uint32_t pos_bits8(const float (&v)[8]) {
 // the ReLU folded into the conversion, -> the HBM image.  The ones column of the image (bias gradients, column H)
 // needs no special case where the bias is folded (TcCfg::FOLD): the pre-activation of column H is the constant 1.
 template <class C>
-__device__ __forceinline__ void relu_publish8(const TcGroupCtx& cx, uint32_t (&mk)[4], int q, int u, int g8,
+__device__ __forceinline__ void relu_publish8(const TcGroupCtx& cx, uint32_t& mword, int u, int g8,
                                               float (&v)[8], unsigned char* ia) {
   using T = TcCfg<C>;
-  or4(mk, q, pos_bits8(v) << (8 * u));
+  mword |= pos_bits8(v) << (8 * u);     // the batch's mask word; the caller files it once per batch (or4)
   if (ia != nullptr) store_img8_relu(ia, cx.lt, 8 * g8, v);
   float r[8];
 #pragma unroll
@@ -209,6 +223,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
     for (int i = 0; i < G::NLAY; ++i)
 #pragma unroll
       for (int w = 0; w < 4; ++w) mk[i][w] = 0u;
+    uint32_t mword = 0u;
     // ---------------- thin first layer -> a_1 ----------------
     {
       const float* Wt0 = cx.sRes + C::off_wt0(c);
@@ -224,8 +239,8 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
                    *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8 + 4));
         }
         acc8_get(acc, v);
-        relu_publish8<C>(cx, mk[0], q, u, g8, v, wimg ? ia : nullptr);
-      });
+        relu_publish8<C>(cx, mword, u, g8, v, wimg ? ia : nullptr);
+      }, [&](int q) { or4(mk[0], q, mword); mword = 0u; });
       if (wimg) finish_act_img<C>(ia, lt);
     }
     tc_publish(cx);
@@ -269,8 +284,8 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
               const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
               v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
             }
-            relu_publish8<C>(cx, mk[l], q, u, g8, v, wimg ? ia : nullptr);
-          });
+            relu_publish8<C>(cx, mword, u, g8, v, wimg ? ia : nullptr);
+          }, [&](int q) { or4(mk[l], q, mword); mword = 0u; });
         } else {
           // last hidden activation: forward value of g(x) (action gradient) and d_{n+1} = relu' * WL^T dOut
           const float* WnL = cx.sRes + C::off_wnl(c);
@@ -444,6 +459,10 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
     }
     mbar_wait(resbar, 0);
     const long long n_se = (long long)a.n_steps * S;
+#ifdef NLBAC_TC_PROF
+    cx.pf_t = clock64(); cx.pf_epi = cx.pf_full = cx.pf_issue = cx.pf_done = cx.pf_n = 0;
+    const long long pf_start = cx.pf_t;
+#endif
 
     for (long long it = 0; it < my_iters; ++it) {
       const long long ltile = (it * gridDim.x + blockIdx.x) * G::G + cx.g;   // tile within the chunk
@@ -526,6 +545,12 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
         for (int d = 0; d < C::NCONST; ++d) o[C::NS + d] = dcst[d] + g[C::NS + d];
       }
     }
+#ifdef NLBAC_TC_PROF
+    if (blockIdx.x == 0 && cx.lt == 0)
+      printf("tc_prof pass A group %d: layers %lld  total %lld cyc  per layer: epilogue %lld  wait-weights %lld  issue %lld  "
+             "wait-done %lld\n", cx.g, cx.pf_n, clock64() - pf_start, cx.pf_epi / cx.pf_n, cx.pf_full / cx.pf_n,
+             cx.pf_issue / cx.pf_n, cx.pf_done / cx.pf_n);
+#endif
   }
   umma::fence_before_sync();
   __syncthreads();

@@ -29,4 +29,7 @@ def report(name, h, data, top):
     print("stall samples:", ", ".join("%s %.1f%%" % (k, 100.0 * v / tot) for k, v in st.most_common(10)))
     print()
 if __name__ == "__main__":
-    main(sys.argv[1], sys.argv[2] if len(sys.argv) > 2 else "")
+    try:
+        main(sys.argv[1], sys.argv[2] if len(sys.argv) > 2 else "")
+    except BrokenPipeError:
+        pass
