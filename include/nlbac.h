@@ -251,6 +251,20 @@ int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* c
  * idx: DEVICE array of B row indices (int64), chosen by the host with the reference's own `random.sample`. */
 int nlbac_replay_gather(const float* ring, int width, const int64_t* idx, int64_t B, float* out, void* stream);
 
+/* Vectorised environment stepping: E independent copies of the reference's UnicycleEnv advanced in
+ * one launch, float64 like the reference's numpy state.  Replaces, per environment, UnicycleEnv.reset
+ * (U envs/unicycle_env.py:166-184) and UnicycleEnv.step / _step / get_obs / obs_compass / goal_met (U :52-165,
+ * :263-279, :302-321).  Persistent per-environment state, owned by the caller: state [E,3], last_goal_dist [E],
+ * episode_step [E] (int32).  mask ([E] bytes, NULL = all) selects the environments to reset.  step outputs: obs [E,7],
+ * reward / constraint [E], center / next_center [E,2] (the Lyapunov inputs before / after the step), done / goal_met
+ * [E] bytes, and the reference's info dict as arrays: num_safety_violation [E] (int32, 0 = key absent), safety_cost [E]. */
+int nlbac_env_unicycle_reset(double* state, double* last_goal_dist, int32_t* episode_step, const uint8_t* mask,
+                             int64_t E, double* obs, void* stream);
+int nlbac_env_unicycle_step(double* state, double* last_goal_dist, int32_t* episode_step, const double* action,
+                            int64_t E, double* obs, double* reward, double* constraint, double* center,
+                            double* next_center, uint8_t* done, uint8_t* goal_met, int32_t* num_safety_violation,
+                            double* safety_cost, void* stream);
+
 /* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 tile.
  * mode 0 (kind::tf32, both operands K-major):   D[t][j] = sum_k X[t][k] Y[j][k],  X [128,104], Y [104,104];
  * mode 1 (kind::f16 on bf16 images, MN-major):  D[j][k] = sum_t X[t][j] Y[t][k],  X, Y [128,104].

@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libnlbac_b200.so")
-SOURCES = ["node_abi.cu", "mlp_abi.cu", "tail_abi.cu", "tc_abi.cu"]
+SOURCES = ["node_abi.cu", "mlp_abi.cu", "tail_abi.cu", "tc_abi.cu", "env_abi.cu"]
 NVCC_FLAGS = ["-std=c++20", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC"]
 
@@ -134,6 +134,8 @@ def _declare(lib):
                                               c.c_float, c.c_float, vp]
     lib.nlbac_soft_update_multi.argtypes = [c.c_int, pvp, pvp, pi64, c.c_float, vp]
     lib.nlbac_replay_gather.argtypes = [vp, c.c_int, vp, i64, vp, vp]
+    lib.nlbac_env_unicycle_reset.argtypes = [vp, vp, vp, vp, i64, vp, vp]
+    lib.nlbac_env_unicycle_step.argtypes = [vp, vp, vp, vp, i64] + [vp] * 10
     lib.nlbac_umma_selftest.argtypes = [c.c_int, vp, vp, vp, vp]
     lib.nlbac_kernel_timing.argtypes = [c.c_int]
     lib.nlbac_kernel_timing_read.argtypes = [c.POINTER(c.c_double), c.POINTER(c.c_int)]

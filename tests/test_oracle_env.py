@@ -1,0 +1,39 @@
+"""oracle/envs.py (numpy restatement of the reference's UnicycleEnv) against trajectories produced by the reference's
+own class (tests/golden/make_golden_env.py -> env_U.npz): goal bonus, hazard violations, plain motion."""
+import os
+import numpy as np
+import pytest
+
+from oracle import envs as oenv
+
+G = np.load(os.path.join(os.path.dirname(__file__), "golden", "env_U.npz"))
+NROLL = 4
+
+
+def _stack(key):
+    return np.stack([G["%s_%d" % (key, i)] for i in range(NROLL)], axis=1)      # [T, R, ...]
+
+
+def test_oracle_env_matches_reference_rollouts():
+    act = _stack("action")
+    T = act.shape[0]
+    state, last, step = oenv.reset(NROLL)
+    np.testing.assert_allclose(oenv.get_obs(state), np.stack([G["obs0_%d" % i] for i in range(NROLL)]), rtol=1e-13)
+    want = {k: _stack(k) for k in ("obs", "reward", "constraint", "center", "next_center", "done", "goal_met", "nviol", "cost", "state")}
+    for t in range(T):
+        obs, r, c, cen, ncen, done, met, nv, cost = oenv.step(state, last, step, act[t])
+        # float64 with the same operation order: agreement to a few ulp (numpy's small matmul may fuse differently)
+        for name, got in (("obs", obs), ("reward", r), ("constraint", c), ("center", cen), ("next_center", ncen),
+                          ("cost", cost), ("state", state)):
+            np.testing.assert_allclose(got, want[name][t], rtol=1e-11, atol=1e-12, err_msg="%s at step %d" % (name, t))
+        assert (done == want["done"][t]).all() and (met == want["goal_met"][t]).all(), t
+        assert (nv == want["nviol"][t]).all(), t
+    assert want["goal_met"].any() and want["nviol"].sum() > 100      # the goldens exercise both branches
+
+
+def test_oracle_env_time_limit():
+    state, last, step = oenv.reset(2)
+    step[:] = oenv.MAX_STEPS - 2
+    a = np.zeros((2, 2))
+    assert not oenv.step(state, last, step, a)[5].any()
+    assert oenv.step(state, last, step, a)[5].all()               # episode_step == max_episode_steps
