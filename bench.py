@@ -520,6 +520,19 @@ def run_configs(args):
         c = lat_cpu(lambda: (ref_sample(bs)(), torch.cuda.synchronize()), iters=5, warm=1)
         rows.append({"case": "replay sample -> device batch", "batch": bs, "ours_us": o, "torch_eager_gpu_us": c,
                      "torch_cpu_us": c, "speedup_vs_eager_gpu": c / o, "speedup_vs_cpu": c / o})
+    # vectorised environment stepping: E Unicycle environments per launch vs the numpy restatement of
+    # the reference's env (one python object per environment in the reference itself: E x ~25 us)
+    from oracle import envs as oenv
+    for E in (1, 4096, 1 << 20):
+        env = nlbac_b200.VecUnicycleEnv(E)
+        act = torch.rand(E, 2, dtype=torch.float64, device=dev) * 2 - 1
+        o = lat_gpu(lambda: env.step(act), iters=30, warm=5)
+        st, last, stp = oenv.reset(E)
+        a_np = act.cpu().numpy()
+        c = lat_cpu(lambda: oenv.step(st, last, stp, a_np), iters=5, warm=1)
+        rows.append({"case": "UnicycleEnv.step x E (float64)", "batch": E, "ours_us": o, "torch_eager_gpu_us": None,
+                     "torch_cpu_us": c, "speedup_vs_eager_gpu": None, "speedup_vs_cpu": c / o,
+                     "env_steps_per_s": E / (o * 1e-6), "hbm_gbs": E * 206 / (o * 1e-6) / 1e9})
     print(json.dumps({"suite": "configs", "unit": "microseconds per forward+backward call (median)", "cores": os.cpu_count(),
                       "note": "B = 128/256 calls are launch-latency bound: one fused launch per direction vs ~90 eager "
                               "launches (SURVEY.md §8 a3)", "rows": rows}))

@@ -265,6 +265,30 @@ int nlbac_env_unicycle_step(double* state, double* last_goal_dist, int32_t* epis
                             double* next_center, uint8_t* done, uint8_t* goal_met, int32_t* num_safety_violation,
                             double* safety_cost, void* stream);
 
+/* The same for SimulatedCarsEnv (C envs/simulated_cars_env.py: reset :158-177, step :42-146, _get_reward :148-155,
+ * _get_obs :197-213).  Per-environment state: state [E,10] = [x_1 v_1 ... x_5 v_5], t [E], episode_step [E].  reset draws
+ * ONE initial-velocity offset per environment (the reference: 3.0 + np.random.normal(0, 0.5), shared by the cars);
+ * the caller supplies it as vel_noise [E] so that runs are reproducible.  action [E] (car 4's acceleration).  step
+ * outputs: obs [E,10], reward / constraint [E], previous / next positions [E,4] (cars 3 and 4: x, v), done [E],
+ * info: reached [E] bytes, num_safety_violation [E], safety_cost [E] (goal_met is always False in the reference). */
+int nlbac_env_cars_reset(double* state, double* t, int32_t* episode_step, const double* vel_noise, const uint8_t* mask,
+                         int64_t E, double* obs, void* stream);
+int nlbac_env_cars_step(double* state, double* t, int32_t* episode_step, const double* action, int64_t E, double* obs,
+                        double* reward, double* constraint, double* previous_positions, double* next_positions,
+                        uint8_t* done, uint8_t* reached, int32_t* num_safety_violation, double* safety_cost,
+                        void* stream);
+
+/* The same for PvtolEnv (P envs/pvtol_env.py: reset :226-246, step / _step :66-216, get_obs :361-377, obs_compass
+ * :379-405).  state [E,7] = [x y theta vx vy thrust operator_x], episode_step [E], action [E,2] = (thrust rate, theta
+ * rate).  step outputs: obs [E,11] (the reference returns it twice), reward / constraint [E], lya_pre_term [E,11] (the
+ * observation BEFORE the step), done / goal_met [E] bytes, and the info dict as [E,4] arrays in the order (obstacles,
+ * safety operator, y_max, y_min): num_safety_violation (int32) and safety_cost. */
+int nlbac_env_pvtol_reset(double* state, int32_t* episode_step, const uint8_t* mask, int64_t E, double* obs,
+                          void* stream);
+int nlbac_env_pvtol_step(double* state, int32_t* episode_step, const double* action, int64_t E, double* obs,
+                         double* reward, double* constraint, double* lya_pre_term, uint8_t* done, uint8_t* goal_met,
+                         int32_t* num_safety_violation, double* safety_cost, void* stream);
+
 /* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 tile.
  * mode 0 (kind::tf32, both operands K-major):   D[t][j] = sum_k X[t][k] Y[j][k],  X [128,104], Y [104,104];
  * mode 1 (kind::f16 on bf16 images, MN-major):  D[j][k] = sum_t X[t][j] Y[t][k],  X, Y [128,104].

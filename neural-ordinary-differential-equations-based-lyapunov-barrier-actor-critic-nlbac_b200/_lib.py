@@ -136,6 +136,10 @@ def _declare(lib):
     lib.nlbac_replay_gather.argtypes = [vp, c.c_int, vp, i64, vp, vp]
     lib.nlbac_env_unicycle_reset.argtypes = [vp, vp, vp, vp, i64, vp, vp]
     lib.nlbac_env_unicycle_step.argtypes = [vp, vp, vp, vp, i64] + [vp] * 10
+    lib.nlbac_env_cars_reset.argtypes = [vp, vp, vp, vp, vp, i64, vp, vp]
+    lib.nlbac_env_cars_step.argtypes = [vp, vp, vp, vp, i64] + [vp] * 10
+    lib.nlbac_env_pvtol_reset.argtypes = [vp, vp, vp, i64, vp, vp]
+    lib.nlbac_env_pvtol_step.argtypes = [vp, vp, vp, i64] + [vp] * 9
     lib.nlbac_umma_selftest.argtypes = [c.c_int, vp, vp, vp, vp]
     lib.nlbac_kernel_timing.argtypes = [c.c_int]
     lib.nlbac_kernel_timing_read.argtypes = [c.POINTER(c.c_double), c.POINTER(c.c_int)]

@@ -51,3 +51,92 @@ if __name__ == "__main__":
             out["%s_%d" % (k, i)] = v
         print(mode, "goal_met", rec["goal_met"].any(), "violations", int(rec["nviol"].sum()), "done at", int(np.argmax(rec["done"])) if rec["done"].any() else None)
     np.savez_compressed(os.path.join(os.path.dirname(os.path.abspath(__file__)), "env_U.npz"), **out)
+
+
+def rollout_cars(seed, T, mode):
+    REFC = "/root/reference/NLBAC_SimulatedCarsFollowing_RL_training/Simulated_Car_Following_RL_training"
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("ref_cars_env", os.path.join(REFC, "envs", "simulated_cars_env.py"))
+    mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
+    env = mod.SimulatedCarsEnv(seed)
+    rng = np.random.RandomState(2000 + seed)
+    obs0 = env.reset()
+    state0 = env.state.copy()
+    keys = ("action", "obs", "reward", "constraint", "prev", "next", "done", "reached", "nviol", "cost", "state")
+    rec = {k: [] for k in keys}
+    for t in range(T):
+        if mode == "brake":     a = np.array([-3.0 + 0.2 * rng.randn()])      # falls back onto car 5
+        elif mode == "rush":    a = np.array([3.0 - 0.2 * rng.rand()])         # closes in on car 3
+        elif mode == "follow":  a = np.array([np.clip(2.0 * ((env.state[4] - env.state[6]) - 9.5) + 1.5 * (env.state[5] - env.state[7]), -3, 3)])
+        else:                   a = rng.uniform(-3.0, 3.0, size=1)
+        obs, r, c, prev, nxt, done, info = env.step(a)
+        rec["action"].append(a[0]); rec["obs"].append(obs); rec["reward"].append(float(r)); rec["constraint"].append(float(c))
+        rec["prev"].append(np.array(prev)); rec["next"].append(np.array(nxt)); rec["done"].append(bool(done))
+        rec["reached"].append(int(info["reached"])); rec["nviol"].append(int(info["num_safety_violation"]))
+        rec["cost"].append(float(info["safety_cost"])); rec["state"].append(env.state.copy())
+    return obs0, state0, {k: np.array(v) for k, v in rec.items()}
+
+
+if __name__ == "__main__":
+    out = {}
+    for i, (seed, mode) in enumerate([(0, "brake"), (1, "rush"), (2, "follow"), (3, "random")]):
+        obs0, state0, rec = rollout_cars(seed, 320, mode)
+        out["obs0_%d" % i], out["state0_%d" % i] = obs0, state0
+        for k, v in rec.items():
+            out["%s_%d" % (k, i)] = v
+        print("cars", mode, "reached", int(rec["reached"].sum()), "violations", int(rec["nviol"].sum()), "done at", int(np.argmax(rec["done"])))
+    np.savez_compressed(os.path.join(os.path.dirname(os.path.abspath(__file__)), "env_C.npz"), **out)
+
+
+def rollout_pvtol(seed, T, mode):
+    REFP = "/root/reference/NLBAC_pvtol_RL_training/Pvtol_RL_training"
+    import importlib.util
+    u = types.ModuleType("envs.utils"); u.to_pixel = lambda m, shift=0: 1.5 * 37.795 * m + shift
+    pk = types.ModuleType("Pvtol_RL_training"); pe = types.ModuleType("Pvtol_RL_training.envs"); pu = types.ModuleType("Pvtol_RL_training.envs.utils")
+    pu.to_pixel = u.to_pixel
+    for name, m in (("Pvtol_RL_training", pk), ("Pvtol_RL_training.envs", pe), ("Pvtol_RL_training.envs.utils", pu)):
+        sys.modules.setdefault(name, m)
+    spec = importlib.util.spec_from_file_location("ref_pvtol_env", os.path.join(REFP, "envs", "pvtol_env.py"))
+    mod = importlib.util.module_from_spec(spec); spec.loader.exec_module(mod)
+    env = mod.PvtolEnv(seed)
+    rng = np.random.RandomState(3000 + seed)
+    obs0 = env.reset()
+    keys = ("action", "obs", "reward", "constraint", "pre", "done", "goal_met", "nviol", "cost", "state")
+    rec = {k: [] for k in keys}
+    kinds = (("obstacles", "safety_cost_obstacles"), ("safety_operator", "safety_cost_operator_val"),
+             ("y_max", "safety_cost_y_max_val"), ("y_min", "safety_cost_y_min_val"))
+    for t in range(T):
+        s = env.state
+        if mode == "goal":       # PD attitude + thrust law flying up and right towards the goal disc
+            th_des = np.clip(-0.25 * (4.5 - s[0]) + 0.35 * s[3], -0.6, 0.6)
+            a = np.array([np.clip(4.0 * (1.25 + 0.4 * (4.5 - s[1]) - 0.8 * s[4] - s[5]), -3.5, 3.5), np.clip(8.0 * (th_des - s[2]), -15, 15)])
+        elif mode == "hazard":   # hover-climb straight up the x = -4.5 line into the hazard at (-4.5, 0)
+            a = np.array([np.clip(4.0 * (1.0 + 0.3 * (0.0 - s[1]) - 0.9 * s[4] - s[5]), -3.5, 3.5), np.clip(-8.0 * s[2], -15, 15)])
+        elif mode == "sideways": # tilt to -90 degrees, then full thrust rate: outruns the safety operator (|x - x_op| >= 1)
+            a = np.array([3.5, -15.0 if s[2] > -1.5 else 0.0])
+        elif mode == "climb":    # upright, full thrust rate: y > y_max
+            a = np.array([3.5, 0.0])
+        elif mode == "fall":     # thrust goes negative: y < y_min
+            a = np.array([-3.5, 0.0])
+        else:
+            a = rng.uniform([-3.5, -15.0], [3.5, 15.0])
+        obs, r, c, pre, obs2, done, info = env.step(a)
+        assert np.array_equal(obs, obs2)
+        rec["action"].append(a); rec["obs"].append(obs); rec["reward"].append(float(r)); rec["constraint"].append(float(c))
+        rec["pre"].append(np.array(pre)); rec["done"].append(bool(done)); rec["goal_met"].append(bool(info.get("goal_met", False)))
+        rec["nviol"].append([int(info.get("num_safety_violation_" + k, 0)) for k, _ in kinds])
+        rec["cost"].append([float(info.get(ck, 0.0)) for _, ck in kinds]); rec["state"].append(env.state.copy())
+    return obs0, {k: np.array(v) for k, v in rec.items()}
+
+
+if __name__ == "__main__":
+    out = {}
+    for i, (seed, mode) in enumerate([(0, "goal"), (1, "hazard"), (2, "sideways"), (3, "climb"), (4, "fall"), (5, "random")]):
+        obs0, rec = rollout_pvtol(seed, 520, mode)
+        assert np.array_equal(rec["pre"][1:], rec["obs"][:-1]) and np.array_equal(rec["pre"][0], obs0)
+        del rec["pre"]                     # lya_pre_term is the previous observation: checked here, not stored
+        out["obs0_%d" % i] = obs0
+        for k, v in rec.items():
+            out["%s_%d" % (k, i)] = v
+        print("pvtol", mode, "goal_met", bool(rec["goal_met"].any()), "violations", rec["nviol"].sum(0).tolist(), "final", np.round(rec["state"][-1], 2).tolist())
+    np.savez_compressed(os.path.join(os.path.dirname(os.path.abspath(__file__)), "env_P.npz"), **out)
