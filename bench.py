@@ -533,6 +533,21 @@ def run_configs(args):
         rows.append({"case": "UnicycleEnv.step x E (float64)", "batch": E, "ours_us": o, "torch_eager_gpu_us": None,
                      "torch_cpu_us": c, "speedup_vs_eager_gpu": None, "speedup_vs_cpu": c / o,
                      "env_steps_per_s": E / (o * 1e-6), "hbm_gbs": E * 206 / (o * 1e-6) / 1e9})
+    E = 1 << 20
+    cenv, penv = nlbac_b200.VecSimulatedCarsEnv(E), nlbac_b200.VecPvtolEnv(E)
+    ca = torch.rand(E, dtype=torch.float64, device=dev) * 2 - 1
+    pa = torch.rand(E, 2, dtype=torch.float64, device=dev) * 2 - 1
+    cst, ct, cstep = oenv.cars_reset(np.zeros(E))
+    pst, pstep = oenv.pvtol_reset(E)
+    ca_np, pa_np = ca.cpu().numpy(), pa.cpu().numpy()
+    for name, fn, ref_fn, nbytes in (
+            ("SimulatedCarsEnv.step x E (float64)", lambda: cenv.step(ca), lambda: oenv.cars_step(cst, ct, cstep, ca_np), 366),
+            ("PvtolEnv.step x E (float64)", lambda: penv.step(pa), lambda: oenv.pvtol_step(pst, pstep, pa_np), 378)):
+        o = lat_gpu(fn, iters=30, warm=5)
+        c = lat_cpu(ref_fn, iters=3, warm=1)
+        rows.append({"case": name, "batch": E, "ours_us": o, "torch_eager_gpu_us": None, "torch_cpu_us": c,
+                     "speedup_vs_eager_gpu": None, "speedup_vs_cpu": c / o, "env_steps_per_s": E / (o * 1e-6),
+                     "hbm_gbs": E * nbytes / (o * 1e-6) / 1e9})
     print(json.dumps({"suite": "configs", "unit": "microseconds per forward+backward call (median)", "cores": os.cpu_count(),
                       "note": "B = 128/256 calls are launch-latency bound: one fused launch per direction vs ~90 eager "
                               "launches (SURVEY.md §8 a3)", "rows": rows}))
