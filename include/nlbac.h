@@ -311,6 +311,13 @@ int nlbac_kernel_timing_read(double* ms4, int* launches4);
  * FLOPs one launch executes in *flops; the caller times it with CUDA events. */
 int nlbac_fp32_peak_probe(int iters, float* sink, double* flops, void* stream);
 
+/* Measured tensor-pipe peak: one CTA per SM, ONE thread issues tcgen05.mma back to back over operands
+ * resident in shared / tensor memory (no registers, no HBM), 13 k-steps per accumulator like a hidden layer.
+ * mode 0 kind::tf32 SS M=128 N=256; 1 kind::tf32 TS (A in tensor memory) N=256; 2 kind::tf32 SS N=112 (the NODE kernels'
+ * own tile); 3 kind::tf32 TS N=112; 4 kind::f16 on bf16 SS N=256 (cross-check against cuBLAS).  *flops = FLOPs of one
+ * launch (2 M N K per MMA); the caller times it with CUDA events (burst: one short launch; sustained: seconds). */
+int nlbac_umma_peak_probe(int mode, int iters, double* flops, void* stream);
+
 /* Same, for register-fed outer-product loops shaped like the GEMM micro-kernel: variant 0 scalar FFMA with
  * three distinct register operands, variant 1 packed fma.rn.f32x2 (sm_100 FFMA2). */
 int nlbac_fma_shape_probe(int variant, int iters, float* sink, double* flops, void* stream);

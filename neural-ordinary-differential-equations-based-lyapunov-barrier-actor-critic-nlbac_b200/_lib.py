@@ -144,6 +144,7 @@ def _declare(lib):
     lib.nlbac_kernel_timing.argtypes = [c.c_int]
     lib.nlbac_kernel_timing_read.argtypes = [c.POINTER(c.c_double), c.POINTER(c.c_int)]
     lib.nlbac_umma_probe.argtypes = [c.POINTER(c.c_int), vp, vp, vp, vp]
+    lib.nlbac_umma_peak_probe.argtypes = [c.c_int, c.c_int, c.POINTER(c.c_double), vp]
     lib.nlbac_fp32_peak_probe.argtypes = [c.c_int, vp, c.POINTER(c.c_double), vp]
     lib.nlbac_fma_shape_probe.argtypes = [c.c_int, c.c_int, vp, c.POINTER(c.c_double), vp]
     return lib

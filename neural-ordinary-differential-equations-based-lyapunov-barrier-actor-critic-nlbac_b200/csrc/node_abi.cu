@@ -173,7 +173,12 @@ static int launch_tc_fwd(const FwdArgs& a, cudaStream_t st) {
   return 0;
 }
 
-// tiles per chunk of the tensor-core backward: a whole number of passes over the grid, images <= 24 GB
+// tiles per chunk of the tensor-core backward: a whole number of passes over the grid, images <= 24 GB.
+// (Round 2 measured a software-pipelined variant -- the dW GEMMs of chunk k-1 riding along the sweep of chunk k on
+// 27 / 36 dedicated CTAs of the same launch -- at 151 / 134 ms per step against 127 ms for the two serial passes: a dW
+// CTA is latency-bound at ~65 GB/s with its 165 KB of TMA loads in flight, so it takes ~all SMs to drain the image
+// stream at HBM speed; and the longer TMEM accumulation chains raised the d-theta error from 3e-4 to 4e-3 -- the
+// tensor core accumulates with truncation, ~6e-8 relative bias per accumulate.  Dropped)
 template <class C>
 static long long tc_bwd_chunk_tiles(long long n_tiles, long long n_se) {
   using G = TcBwdGeom<C>;

@@ -166,9 +166,57 @@ __device__ __forceinline__ void store_act4(unsigned char* img, int r, int c, flo
 // u = 0..3 (unrolled), g8 = 4q + u = column group, v = 8 columns.
 struct NoPost { __device__ __forceinline__ void operator()(int) const {} };
 // post(q) runs once after the (up to four) column groups of batch q
+#ifndef NLBAC_TC_PIPE
+#define NLBAC_TC_PIPE 1     // 1: accumulator loads software-pipelined in half-batches of 16 columns (below)
+#endif
+#ifndef NLBAC_TC_BARWAIT
+#define NLBAC_TC_BARWAIT 0  // 1: one thread per group waits on the MMA-done mbarrier, the other 127 block in bar.sync
+                            // (measured on one box, round 2: sweep 68.2 -> 69.0 ms; the extra barrier hop costs more
+                            // than the polling instructions it removes, so the default stays 0)
+#endif
+
 template <int NG8, bool LOAD, class F, class P = NoPost>
 __device__ __forceinline__ void tc_batches(uint32_t tacc, F&& body, P&& post = P()) {
   constexpr int NFULL = NG8 / 4, REM = NG8 % 4;
+  if constexpr (LOAD && NLBAC_TC_PIPE) {
+    // Half-batches of 2 x 8 columns, double-buffered in registers: while the owner thread works on one half the
+    // tcgen05.ld of the next is in flight (same 32 live registers as four loads + one wait, but the TMEM read latency
+    // is hidden behind ~50 instructions of epilogue instead of being exposed four times per layer).
+    float va[2][8], vb[2][8];
+    if (NFULL > 0) { umma::ld8f(tacc, va[0]); umma::ld8f(tacc + 8, va[1]); }
+#pragma unroll 1
+    for (int q = 0; q < NFULL; ++q) {
+      umma::wait_ld16(va[0], va[1]);
+      umma::ld8f(tacc + 8 * (4 * q + 2), vb[0]);
+      umma::ld8f(tacc + 8 * (4 * q + 3), vb[1]);
+      body(q, 0, 4 * q, va[0]);
+      body(q, 1, 4 * q + 1, va[1]);
+      umma::wait_ld16(vb[0], vb[1]);
+      if (q + 1 < NFULL) {
+        umma::ld8f(tacc + 8 * (4 * q + 4), va[0]);
+        umma::ld8f(tacc + 8 * (4 * q + 5), va[1]);
+      } else if (REM > 0) {
+        umma::ld8f(tacc + 8 * (4 * NFULL), va[0]);
+        if (REM > 1) umma::ld8f(tacc + 8 * (4 * NFULL + 1), va[1]);
+      }
+      body(q, 2, 4 * q + 2, vb[0]);
+      body(q, 3, 4 * q + 3, vb[1]);
+      post(q);
+    }
+    if (REM > 0) {
+      if (NFULL == 0) {
+        umma::ld8f(tacc, va[0]);
+        if (REM > 1) umma::ld8f(tacc + 8, va[1]);
+      }
+      if (REM > 2) umma::ld8f(tacc + 8 * (4 * NFULL + 2), vb[0]);
+      umma::wait_ld16(va[0], vb[0]);
+      if (REM > 1) umma::wait_ld16(va[1], vb[0]);
+      body(NFULL, 0, 4 * NFULL, va[0]);
+      if (REM > 1) body(NFULL, 1, 4 * NFULL + 1, va[1]);
+      if (REM > 2) body(NFULL, 2, 4 * NFULL + 2, vb[0]);
+      post(NFULL);
+    }
+  } else {
 #pragma unroll 1
   for (int q = 0; q < NFULL; ++q) {
     float v[4][8];
@@ -191,6 +239,7 @@ __device__ __forceinline__ void tc_batches(uint32_t tacc, F&& body, P&& post = P
 #pragma unroll
     for (int u = 0; u < REM; ++u) body(NFULL, u, 4 * NFULL + u, v[u]);
     post(NFULL);
+  }
   }
 }
 
@@ -282,6 +331,24 @@ __device__ __forceinline__ void ring_prefetch(const TcGroupCtx& cx, uint32_t p) 
   }
 }
 
+// Wait for the group's MMAs: every thread on the mbarrier (default), or -- NLBAC_TC_BARWAIT -- the issuing thread alone
+// with the rest of the group blocked in the hardware barrier (no polling instructions: SYNCS + BRA + NANOSLEEP are 16 %
+// of the executed instructions of the reverse sweep, but they issue in otherwise idle slots; measured slower).
+__device__ __forceinline__ void tc_wait_done(TcGroupCtx& cx) {
+#if NLBAC_TC_BARWAIT
+  if (cx.lt == 0) {
+    mbar_wait(cx.done, cx.nd & 1);
+    umma::fence_after_sync();
+    umma::fence_before_sync();
+  }
+  group_sync(cx.g);
+#else
+  mbar_wait(cx.done, cx.nd & 1);
+#endif
+  ++cx.nd;
+  umma::fence_after_sync();
+}
+
 template <class C>
 __device__ __noinline__ void tc_issue_ts(uint32_t tmma, uint32_t ta, uint64_t wd) {   // A operand in tensor memory
   using T = TcCfg<C>;
@@ -360,9 +427,7 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
         umma::commit(cx.done);
       }
       cx.seq += SPLIT ? 2 : 1;
-      mbar_wait(cx.done, cx.nd & 1);
-      ++cx.nd;
-      umma::fence_after_sync();
+      tc_wait_done(cx);
       const float* bias = cx.sRes + C::off_bh(c, l);
       constexpr int NG8 = T::KP / 8;
       if (l < n) {  // ---- epilogue: bias + ReLU -> activation image (in place) ----

@@ -135,9 +135,7 @@ __device__ __forceinline__ void tc_layer_mma(TcGroupCtx& cx) {
 #endif
   }
   ++cx.seq;
-  mbar_wait(cx.done, cx.nd & 1);
-  ++cx.nd;
-  umma::fence_after_sync();
+  tc_wait_done(cx);
 #ifdef NLBAC_TC_PROF
   cx.pf_t = clock64();
   cx.pf_full += p1 - p0; cx.pf_issue += p2 - p1; cx.pf_done += cx.pf_t - p2; ++cx.pf_n;
@@ -392,6 +390,137 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// pass B: parameter gradients as streaming bf16 GEMMs over the images (one GEMM pair per blockIdx.y)
+// ------------------------------------------------------------------------------------------------
+struct DwPair {
+  int offD, bytesD;   // cotangent image (A operand, M = its feature columns)
+  int offA, bytesA;   // activation image (B operand, N = its columns)
+  int N;              // MMA N
+  int rows, cols;     // valid extent of the result: rows of W, input columns of W
+  int goff_w, goff_b, ldw;
+};
+template <class C>
+__host__ __device__ inline DwPair dw_pair(int pr) {
+  using IM = ImgMap<C>;
+  int c = 0;
+  if (C::NCH == 2 && pr >= IM::npairs(0)) { c = 1; pr -= IM::npairs(0); }
+  const int n = C::nhc(c);
+  DwPair p;
+  if (pr == 0) {
+    p = {IM::off_del(c, 1), IM::DEL_B, IM::off_xin(), IM::XIN_B, 16, C::H, C::IN0, C::goff_w(c, 0), C::goff_b(c, 0), C::IN0};
+  } else if (pr <= n) {
+    p = {IM::off_del(c, pr + 1), IM::DEL_B, IM::off_act(c, pr), IM::ACT_B, IM::IMGW, C::H, C::H, C::goff_w(c, pr),
+         C::goff_b(c, pr), C::H};
+  } else {
+    p = {IM::off_dout(c), IM::DOUT_B, IM::off_act(c, n + 1), IM::ACT_B, IM::IMGW, C::out(c), C::H, C::goff_w(c, n + 1),
+         C::goff_b(c, n + 1), C::H};
+  }
+  return p;
+}
+
+template <class C>
+struct DwGeom {
+  using IM = ImgMap<C>;
+  static constexpr int NST = 3;
+  static constexpr int DBUF = 16 * 2048;            // M = 128 feature rows are addressed (13 or 2 chunks are loaded)
+  static constexpr int ABUF = (IM::IMGW / 8) * 2048;   // the MMA addresses IMGW columns; ACT_B of them are loaded
+  static constexpr int STAGE = DBUF + ABUF;
+  static constexpr int OFF_BAR = NST * STAGE;
+  static constexpr size_t SMEM_BYTES = OFF_BAR + (2 * NST + 1) * 8 + 16;
+  static constexpr int NT = 160;
+  static_assert(STAGE % 128 == 0 && SMEM_BYTES <= 227 * 1024, "pass-B staging");
+};
+
+// The body of pass B for ONE GEMM pair: CTA `slab` of `nslab` streams blocks slab, slab + nslab, ... of `images`.
+// Called by every thread of the CTA (threads beyond DwGeom::NT only take part in the two block barriers), either from
+// node_tc_dw_kernel or from the dW-role CTAs of node_tc_bwd_kernel.
+template <class C>
+__device__ __forceinline__ void dw_role(unsigned char* smem_raw, const unsigned char* __restrict__ images, long long n_items,
+                                        float* __restrict__ grad_rep, int pair_idx, int slab, int nslab) {
+  using G = DwGeom<C>;
+  using IM = ImgMap<C>;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + G::OFF_BAR);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + G::NST;
+  uint64_t* done = bars + 2 * G::NST;
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 2 * G::NST + 1);
+  const int tid = threadIdx.x, warp = tid / 32;
+  const DwPair pr = dw_pair<C>(pair_idx);
+  long long my_items = 0;
+  if ((long long)slab < n_items && slab < nslab) my_items = (n_items - slab + nslab - 1) / nslab;
+
+  if (tid == 0) {
+    for (int i = 0; i < G::NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(done, 1);
+    fence_barrier_init();
+  }
+  if (warp == 0) umma::tmem_alloc(tslot, 128);
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tbase = *tslot;
+
+  if (my_items > 0 && tid < G::NT) {
+    if (warp == 4) {
+      if (tid % 32 == 0) {   // TMA producer
+        for (long long i = 0; i < my_items; ++i) {
+          const int s = (int)(i % G::NST);
+          if (i >= G::NST) mbar_wait(&empty[s], (uint32_t)((i / G::NST) - 1) & 1);
+          const unsigned char* blk = images + (size_t)(slab + i * nslab) * IM::STRIDE;
+          mbar_expect_tx(&full[s], pr.bytesD + pr.bytesA);
+          tma_load_1d(smem_raw + s * G::STAGE, blk + pr.offD, pr.bytesD, &full[s]);
+          tma_load_1d(smem_raw + s * G::STAGE + G::DBUF, blk + pr.offA, pr.bytesA, &full[s]);
+        }
+      }
+      __syncwarp();
+    } else {
+      if (tid == 0) {        // MMA issuer: D[j][n] += sum_t d[t][j] a[t][n], K = 128 trajectories = 8 x 16
+        const uint32_t idesc = umma::make_idesc_bf16(128, pr.N, true, true);
+        for (long long i = 0; i < my_items; ++i) {
+          const int s = (int)(i % G::NST);
+          mbar_wait(&full[s], (uint32_t)(i / G::NST) & 1);
+          umma::fence_after_sync();
+          const uint32_t a0 = smem_u32(smem_raw + s * G::STAGE), b0 = a0 + G::DBUF;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma::mma_bf16(tbase, umma::make_desc(a0 + ks * 256, 128, 2048), umma::make_desc(b0 + ks * 256, 128, 2048),
+                           idesc, (i > 0 || ks > 0) ? 1u : 0u);
+          umma::commit(&empty[s]);
+        }
+        umma::commit(done);
+      }
+      mbar_wait(done, 0);
+      umma::fence_after_sync();
+      const int j = tid;   // result row = feature of the cotangent image
+      float* grep = grad_rep + (size_t)(slab % NREP) * C::NGRAD;
+      for (int c0 = 0; c0 < pr.N; c0 += 8) {
+        float v[8];
+        umma::ld8(tbase + ((uint32_t)(warp * 32) << 16) + c0, v);
+        umma::wait_ld();
+        if (j < pr.rows) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int col = c0 + i;
+            if (col < pr.cols) atomicAdd(grep + pr.goff_w + j * pr.ldw + col, v[i]);
+            else if (col == pr.cols) atomicAdd(grep + pr.goff_b + j, v[i]);
+          }
+        }
+      }
+    }
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tbase, 128);
+}
+
+template <class C>
+__global__ void __launch_bounds__(DwGeom<C>::NT, 1) node_tc_dw_kernel(const unsigned char* __restrict__ images,
+                                                                      long long n_items, float* __restrict__ grad_rep) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  dw_role<C>(smem_raw, images, n_items, grad_rep, (int)blockIdx.y, (int)blockIdx.x, (int)gridDim.x);
+}
+
 struct TcBwdArgs {
   BwdArgs b;              // same meaning as node_bwd.cuh (grad_rep unused here)
   unsigned char* images;  // [n_tiles_in_chunk][n_steps * S][ImgMap::STRIDE] or null
@@ -417,9 +546,10 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
   const Tableau tab = make_tableau(a.method);
   const int S = tab.S;
 
+  const int n_cta = (int)gridDim.x;
   const long long n_pairs = (ta.n_tiles + G::G - 1) / G::G;
   long long my_iters = 0;
-  if ((long long)blockIdx.x < n_pairs) my_iters = (n_pairs - blockIdx.x + gridDim.x - 1) / gridDim.x;
+  if ((long long)blockIdx.x < n_pairs) my_iters = (n_pairs - blockIdx.x + n_cta - 1) / n_cta;
   const uint32_t total = (uint32_t)(my_iters * a.n_steps * S * G::PKT_PER_EVAL);
 
   if (tid == 0) {
@@ -465,7 +595,7 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
 #endif
 
     for (long long it = 0; it < my_iters; ++it) {
-      const long long ltile = (it * gridDim.x + blockIdx.x) * G::G + cx.g;   // tile within the chunk
+      const long long ltile = (it * n_cta + blockIdx.x) * G::G + cx.g;   // tile within the chunk
       const bool tile_live = ltile < ta.n_tiles;
       const long long b = (ta.tile0 + ltile) * T::ROWS + cx.lt;
       const bool live = tile_live && b < a.B;
@@ -555,128 +685,6 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
   umma::fence_before_sync();
   __syncthreads();
   if (warp == 0) umma::tmem_dealloc(tbase, G::TMEM_COLS);
-}
-
-// ------------------------------------------------------------------------------------------------
-// pass B: parameter gradients as streaming bf16 GEMMs over the images (one GEMM pair per blockIdx.y)
-// ------------------------------------------------------------------------------------------------
-struct DwPair {
-  int offD, bytesD;   // cotangent image (A operand, M = its feature columns)
-  int offA, bytesA;   // activation image (B operand, N = its columns)
-  int N;              // MMA N
-  int rows, cols;     // valid extent of the result: rows of W, input columns of W
-  int goff_w, goff_b, ldw;
-};
-template <class C>
-__host__ __device__ inline DwPair dw_pair(int pr) {
-  using IM = ImgMap<C>;
-  int c = 0;
-  if (C::NCH == 2 && pr >= IM::npairs(0)) { c = 1; pr -= IM::npairs(0); }
-  const int n = C::nhc(c);
-  DwPair p;
-  if (pr == 0) {
-    p = {IM::off_del(c, 1), IM::DEL_B, IM::off_xin(), IM::XIN_B, 16, C::H, C::IN0, C::goff_w(c, 0), C::goff_b(c, 0), C::IN0};
-  } else if (pr <= n) {
-    p = {IM::off_del(c, pr + 1), IM::DEL_B, IM::off_act(c, pr), IM::ACT_B, IM::IMGW, C::H, C::H, C::goff_w(c, pr),
-         C::goff_b(c, pr), C::H};
-  } else {
-    p = {IM::off_dout(c), IM::DOUT_B, IM::off_act(c, n + 1), IM::ACT_B, IM::IMGW, C::out(c), C::H, C::goff_w(c, n + 1),
-         C::goff_b(c, n + 1), C::H};
-  }
-  return p;
-}
-
-template <class C>
-struct DwGeom {
-  using IM = ImgMap<C>;
-  static constexpr int NST = 3;
-  static constexpr int DBUF = 16 * 2048;            // M = 128 feature rows are addressed (13 or 2 chunks are loaded)
-  static constexpr int ABUF = (IM::IMGW / 8) * 2048;   // the MMA addresses IMGW columns; ACT_B of them are loaded
-  static constexpr int STAGE = DBUF + ABUF;
-  static constexpr int OFF_BAR = NST * STAGE;
-  static constexpr size_t SMEM_BYTES = OFF_BAR + (2 * NST + 1) * 8 + 16;
-  static constexpr int NT = 160;
-  static_assert(STAGE % 128 == 0 && SMEM_BYTES <= 227 * 1024, "pass-B staging");
-};
-
-template <class C>
-__global__ void __launch_bounds__(DwGeom<C>::NT, 1) node_tc_dw_kernel(const unsigned char* __restrict__ images,
-                                                                      long long n_items, float* __restrict__ grad_rep) {
-  using G = DwGeom<C>;
-  using IM = ImgMap<C>;
-  extern __shared__ __align__(1024) unsigned char smem_raw[];
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + G::OFF_BAR);
-  uint64_t* full = bars;
-  uint64_t* empty = bars + G::NST;
-  uint64_t* done = bars + 2 * G::NST;
-  uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + 2 * G::NST + 1);
-  const int tid = threadIdx.x, warp = tid / 32;
-  const DwPair pr = dw_pair<C>(blockIdx.y);
-  long long my_items = 0;
-  if ((long long)blockIdx.x < n_items) my_items = (n_items - blockIdx.x + gridDim.x - 1) / gridDim.x;
-
-  if (tid == 0) {
-    for (int i = 0; i < G::NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    mbar_init(done, 1);
-    fence_barrier_init();
-  }
-  if (warp == 0) umma::tmem_alloc(tslot, 128);
-  umma::fence_before_sync();
-  __syncthreads();
-  umma::fence_after_sync();
-  const uint32_t tbase = *tslot;
-
-  if (my_items > 0) {
-    if (warp == 4) {
-      if (tid % 32 == 0) {   // TMA producer
-        for (long long i = 0; i < my_items; ++i) {
-          const int s = (int)(i % G::NST);
-          if (i >= G::NST) mbar_wait(&empty[s], (uint32_t)((i / G::NST) - 1) & 1);
-          const unsigned char* blk = images + (size_t)(blockIdx.x + i * gridDim.x) * IM::STRIDE;
-          mbar_expect_tx(&full[s], pr.bytesD + pr.bytesA);
-          tma_load_1d(smem_raw + s * G::STAGE, blk + pr.offD, pr.bytesD, &full[s]);
-          tma_load_1d(smem_raw + s * G::STAGE + G::DBUF, blk + pr.offA, pr.bytesA, &full[s]);
-        }
-      }
-      __syncwarp();
-    } else {
-      if (tid == 0) {        // MMA issuer: D[j][n] += sum_t d[t][j] a[t][n], K = 128 trajectories = 8 x 16
-        const uint32_t idesc = umma::make_idesc_bf16(128, pr.N, true, true);
-        for (long long i = 0; i < my_items; ++i) {
-          const int s = (int)(i % G::NST);
-          mbar_wait(&full[s], (uint32_t)(i / G::NST) & 1);
-          umma::fence_after_sync();
-          const uint32_t a0 = smem_u32(smem_raw + s * G::STAGE), b0 = a0 + G::DBUF;
-#pragma unroll
-          for (int ks = 0; ks < 8; ++ks)
-            umma::mma_bf16(tbase, umma::make_desc(a0 + ks * 256, 128, 2048), umma::make_desc(b0 + ks * 256, 128, 2048),
-                           idesc, (i > 0 || ks > 0) ? 1u : 0u);
-          umma::commit(&empty[s]);
-        }
-        umma::commit(done);
-      }
-      mbar_wait(done, 0);
-      umma::fence_after_sync();
-      const int j = tid;   // result row = feature of the cotangent image
-      float* grep = grad_rep + (size_t)(blockIdx.x % NREP) * C::NGRAD;
-      for (int c0 = 0; c0 < pr.N; c0 += 8) {
-        float v[8];
-        umma::ld8(tbase + ((uint32_t)(warp * 32) << 16) + c0, v);
-        umma::wait_ld();
-        if (j < pr.rows) {
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int col = c0 + i;
-            if (col < pr.cols) atomicAdd(grep + pr.goff_w + j * pr.ldw + col, v[i]);
-            else if (col == pr.cols) atomicAdd(grep + pr.goff_b + j, v[i]);
-          }
-        }
-      }
-    }
-  }
-  umma::fence_before_sync();
-  __syncthreads();
-  if (warp == 0) umma::tmem_dealloc(tbase, 128);
 }
 
 }  // namespace nlbac

@@ -159,6 +159,90 @@ __global__ void __launch_bounds__(128, 1) umma_probe_kernel(ProbeArgs p, const f
   if (warp == 0) umma::tmem_dealloc(tbase, 128);
 }
 
+// ------------------------------------------------------------------------------------------------
+// Tensor-pipe peak probe: one CTA per SM, ONE thread issues tcgen05.mma back to back
+// over operands that never leave shared / tensor memory (no registers, no HBM), K loop of 13 k-steps like a hidden
+// layer.  Modes:
+//   0  kind::tf32  SS  M=128 N=256   (the pipe's best case: 12 KB of operands per 128-cycle MMA)
+//   1  kind::tf32  TS  M=128 N=256   (A operand in tensor memory)
+//   2  kind::tf32  SS  M=128 N=112   (the NODE kernels' own tile: 7.6 KB per 56-cycle MMA -> shared-memory bound)
+//   3  kind::tf32  TS  M=128 N=112   (the NODE kernels' tensor-memory group)
+//   4  kind::f16 (bf16) SS M=128 N=256  (cross-check against MEASURED_PEAKS.json's cuBLAS figure)
+// ------------------------------------------------------------------------------------------------
+constexpr int PK_KSTEPS = 13;
+constexpr int PK_SMEM = PK_KSTEPS * (4096 + 8192) + 64;
+__global__ void __launch_bounds__(128, 1) umma_peak_kernel(int mode, int iters) {
+  extern __shared__ __align__(128) unsigned char sm[];
+  unsigned char* bufA = sm;                          // 13 k-steps x [128 rows x 8 k] fp32 (4 KB each)
+  unsigned char* bufB = sm + PK_KSTEPS * 4096;       // 13 k-steps x [256 rows x 8 k] fp32 (8 KB each)
+  uint64_t* bar = reinterpret_cast<uint64_t*>(sm + PK_KSTEPS * (4096 + 8192));
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(sm + PK_KSTEPS * (4096 + 8192) + 16);
+  const int tid = threadIdx.x, warp = tid / 32;
+  uint32_t h = 0x9E3779B9u * (tid + 1) + blockIdx.x;
+  for (int i = tid; i < PK_KSTEPS * (4096 + 8192) / 4; i += 128) {   // pseudo-random operands in [-1, 1)
+    h = h * 1664525u + 1013904223u;
+    reinterpret_cast<float*>(sm)[i] = __uint_as_float(0x3F800000u | (h >> 9)) * 2.f - 3.f;
+  }
+  if (mode == 4) {   // bf16 pairs: keep both halves finite
+    for (int i = tid; i < PK_KSTEPS * (4096 + 8192) / 4; i += 128)
+      reinterpret_cast<uint32_t*>(sm)[i] = (reinterpret_cast<uint32_t*>(sm)[i] & 0x0FFF0FFFu) | 0x30003000u;
+  }
+  if (tid == 0) { mbar_init(bar, 1); fence_barrier_init(); }
+  if (warp == 0) umma::tmem_alloc(tslot, 512);
+  fence_proxy_async();
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tbase = *tslot;
+  const bool ts = mode == 1 || mode == 3;
+  const int N = (mode == 2 || mode == 3) ? 112 : 256;
+  const uint32_t top = (N == 112) ? 384u : 256u;     // A operand block in tensor memory (TS modes)
+  if (ts) {
+    for (int c0 = 0; c0 < 8 * PK_KSTEPS; c0 += 8) {
+      float v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) v[i] = 1e-3f * (float)((tid * 31 + c0 + i) % 97) - 0.05f;
+      umma::st8(umma::tmem_addr(tbase, warp * 32, top + c0), v);
+    }
+    umma::wait_st();
+    umma::fence_before_sync();
+    __syncthreads();
+    umma::fence_after_sync();
+  }
+  if (tid == 0) {
+    const uint32_t a0 = smem_u32(bufA), b0 = smem_u32(bufB);
+    const int nacc = (N == 112) ? 3 : (ts ? 1 : 2);
+    const uint32_t astride = (N == 112) ? 128u : 256u;
+    if (mode == 4) {
+      const uint32_t idesc = umma::make_idesc_bf16(128, 256, false, false);   // K-major bf16: 16 k per MMA = 32 B = 2 chunks
+      for (int it = 0; it < iters; ++it) {
+        const uint32_t d = tbase + (uint32_t)(it % nacc) * astride;
+#pragma unroll
+        for (int ks = 0; ks < PK_KSTEPS; ++ks)
+          umma::mma_bf16(d, umma::make_desc(a0 + ks * 4096, 2048, 128), umma::make_desc(b0 + ks * 8192, 4096, 128), idesc,
+                         ks > 0 ? 1u : 0u);
+      }
+    } else {
+      const uint32_t idesc = umma::make_idesc_tf32(128, N, false, false);
+      for (int it = 0; it < iters; ++it) {
+        const uint32_t d = tbase + (uint32_t)(it % nacc) * astride;
+#pragma unroll
+        for (int ks = 0; ks < PK_KSTEPS; ++ks) {
+          const uint64_t bd = umma::make_desc(b0 + ks * 8192, 4096, 128);
+          if (ts) umma::mma_tf32_ts(d, tbase + top + 8 * ks, bd, idesc, ks > 0 ? 1u : 0u);
+          else umma::mma_tf32(d, umma::make_desc(a0 + ks * 4096, 2048, 128), bd, idesc, ks > 0 ? 1u : 0u);
+        }
+      }
+    }
+    umma::commit(bar);
+  }
+  mbar_wait(bar, 0);
+  umma::fence_after_sync();
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tbase, 512);
+}
+
 }  // namespace nlbac
 
 using namespace nlbac;
@@ -179,6 +263,19 @@ int nlbac_umma_probe(const int* params10, const float* X, const float* Y, float*
   NLBAC_CUDA(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ST_SMEM));
   umma_probe_kernel<<<1, 128, ST_SMEM, (cudaStream_t)stream>>>(p, X, Y, D);
   NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_umma_peak_probe(int mode, int iters, double* flops, void* stream) {
+  NLBAC_REQUIRE(mode >= 0 && mode <= 4 && iters > 0, "bad arguments");
+  int dev = 0, sms = 148;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  NLBAC_CUDA(cudaFuncSetAttribute(umma_peak_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PK_SMEM));
+  umma_peak_kernel<<<sms, 128, PK_SMEM, (cudaStream_t)stream>>>(mode, iters);
+  NLBAC_CUDA(cudaGetLastError());
+  const int N = (mode == 2 || mode == 3) ? 112 : 256, K = (mode == 4) ? 16 : 8;
+  if (flops) *flops = 2.0 * 128 * N * K * PK_KSTEPS * (double)iters * sms;
   return 0;
 }
 

@@ -109,6 +109,23 @@ __device__ __forceinline__ void ld8(uint32_t taddr, float (&v)[8]) {
   for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
 }
 __device__ __forceinline__ void wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// same load straight into float registers (a .b32 operand accepts .f32 registers): no move between the load and its
+// wait, which matters once loads are software-pipelined
+__device__ __forceinline__ void ld8f(uint32_t taddr, float (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=f"(v[0]), "=f"(v[1]), "=f"(v[2]), "=f"(v[3]), "=f"(v[4]), "=f"(v[5]), "=f"(v[6]), "=f"(v[7])
+               : "r"(taddr)
+               : "memory");
+}
+// wait::ld that NAMES the registers two earlier ld8 wrote: later reads of v0 / v1 cannot be scheduled above the wait
+// (needed once loads are software-pipelined: another tcgen05.ld is already in flight when these values are consumed)
+__device__ __forceinline__ void wait_ld16(float (&a)[8], float (&b)[8]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7]),
+                 "+f"(b[0]), "+f"(b[1]), "+f"(b[2]), "+f"(b[3]), "+f"(b[4]), "+f"(b[5]), "+f"(b[6]), "+f"(b[7])
+               :
+               : "memory");
+}
 
 // registers -> TMEM: the calling warp writes ITS 32 lanes, 8 consecutive columns
 __device__ __forceinline__ void st8(uint32_t taddr, const float (&v)[8]) {

@@ -1,0 +1,156 @@
+"""Golden trace of the REFERENCE's own ``SAC_CBF_CLF.update_parameters`` (U sac_cbf_clf/sac_cbf_clf.py:181-319) over 12
+consecutive updates, Unicycle variant.  Run here:  ``python tests/golden/make_golden_update.py`` -> update_U.pt
+
+The agent object is created with ``object.__new__`` (its constructor needs gym) and given the attributes the
+constructor would have set (U sac_cbf_clf.py:28-134): the reference's own network classes, ``torch.optim.Adam``
+optimisers with the reference's learning rates, multipliers, rho.  ``update_parameters`` itself, ``get_cbf_clf_part``,
+``get_policy_loss_2``, the backup variants, ``train_step``, ``soft_update`` and ``DynamicsModel.get_state`` run
+unmodified.  Two things are injected: the minibatches (a stand-in memory whose ``sample`` returns fixed arrays) and
+the Gaussian noise ``Normal.rsample`` draws (``torch.distributions.normal._standard_normal`` pops pre-generated
+tensors, recorded in the fixture), because PyTorch's RNG stream is not part of the contract.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+from make_golden import _Box  # noqa: E402
+from make_golden_constraints import import_variant, _Env, _Args, _perturb_biases, _sd  # noqa: E402
+
+N_UPDATES, B, NODE_N = 12, 128, 512
+
+
+class _Memory:
+    """Stand-in for ReplayMemory: ``sample`` returns the next prepared batch (10 fields like U replay_memory.py:21-25)."""
+
+    def __init__(self, batches, position):
+        self.batches, self.i, self.position = batches, 0, position
+
+    def sample(self, batch_size):
+        b = self.batches[self.i]
+        self.i += 1
+        assert len(b[0]) == batch_size, (len(b[0]), batch_size)
+        return b
+
+
+def _batch(gen, n):
+    r = lambda *s: torch.rand(*s, generator=gen, dtype=torch.float64)  # noqa: E731
+    l_p, goal = 0.03, torch.tensor([2.5, 2.5], dtype=torch.float64)
+
+    def obs_of(x, y, th):
+        rel = goal - torch.stack([x, y], 1)
+        d = rel.norm(dim=1)
+        c, s = torch.cos(th), torch.sin(th)
+        cx = (c * rel[:, 0] + s * rel[:, 1]) / (d + 1e-3)
+        cy = (-s * rel[:, 0] + c * rel[:, 1]) / (d + 1e-3)
+        return torch.stack([x, y, c, s, cx, cy, torch.exp(-d)], 1)
+
+    x, y, th = r(n) * 4 - 2, r(n) * 4 - 2, (r(n) * 2 - 1) * np.pi
+    act = torch.stack([r(n) * 7 - 3.5, r(n) * 24 - 12], 1)
+    x2 = x + 0.02 * act[:, 0] * torch.cos(th)
+    y2 = y + 0.02 * act[:, 0] * torch.sin(th)
+    th2 = th + 0.02 * act[:, 1]
+    obs, nobs = obs_of(x, y, th), obs_of(x2, y2, th2)
+    cp = torch.stack([x + l_p * torch.cos(th), y + l_p * torch.sin(th)], 1)
+    ncp = torch.stack([x2 + l_p * torch.cos(th2), y2 + l_p * torch.sin(th2)], 1)
+    reward = -(goal - torch.stack([x2, y2], 1)).norm(dim=1) * 0.1
+    cons = (goal - ncp).norm(dim=1)
+    mask = (r(n) > 0.02).double()
+    f32 = lambda t: t.float().double().numpy()  # noqa: E731  values exactly representable in float32
+    return (f32(obs), f32(act), f32(reward), f32(cons), f32(cp), f32(ncp), f32(nobs), f32(mask), None, None)
+
+
+def main():
+    model, agent_mod, dyn_mod = import_variant("U")
+    gen = torch.Generator().manual_seed(777)
+    torch.manual_seed(11)
+    env = _Env()
+    env.dynamics_mode, env.dt, env.hazards_radius = "Unicycle", 0.02, 0.5
+    env.hazards_locations = np.array([[0., 0.], [0., 1.], [0., -1.], [-1., 1.], [-1., -1.], [1., -1.], [1., 1.]]) * 1.5
+    space = _Box([-3.5, -12.0], [3.5, 12.0])
+    a = object.__new__(agent_mod.SAC_CBF_CLF)
+    dev = torch.device("cpu")
+    a.env, a.device, a.solver = env, dev, "euler"
+    a.gamma, a.gamma_b, a.tau, a.alpha, a.backup_alpha = 0.99, 50.0, 0.005, 0.2, 0.2
+    a.center_pos_num, a.policy_type, a.batch_size = 2, "Gaussian", B
+    a.target_update_interval, a.Lagrangian_multiplier_update_interval = 1, 8
+    a.automatic_entropy_tuning, a.critic_lyapunov_lr = True, 0.0004
+    a.critic = model.QNetwork(7, 2, 256)
+    a.critic_target = model.QNetwork(7, 2, 256)
+    a.lyapunovNet = model.LyaNetwork(2, 256)
+    a.lyapunovNet_target = model.LyaNetwork(2, 256)
+    a.policy = model.GaussianPolicy(7, 2, 256, space)
+    a.backup_policy = model.GaussianPolicy(7, 2, 256, space)
+    for net in (a.critic, a.lyapunovNet, a.policy, a.backup_policy):
+        _perturb_biases(net, gen)
+    agent_mod.hard_update(a.critic_target, a.critic)
+    agent_mod.hard_update(a.lyapunovNet_target, a.lyapunovNet)
+    a.critic_optim = torch.optim.Adam(a.critic.parameters(), lr=a.critic_lyapunov_lr)
+    a.lyaNet_optim = torch.optim.Adam(a.lyapunovNet.parameters(), lr=a.critic_lyapunov_lr)
+    a.policy_optim = torch.optim.Adam(a.policy.parameters(), lr=3e-4)
+    a.backup_policy_optim = torch.optim.Adam(a.backup_policy.parameters(), lr=3e-4)
+    a.target_entropy = -2.0
+    a.log_alpha = torch.zeros(1, requires_grad=True)
+    a.alpha_optim = torch.optim.Adam([a.log_alpha], lr=3e-4)
+    a.backup_log_alpha = torch.zeros(1, requires_grad=True)
+    a.backup_alpha_optim = torch.optim.Adam([a.backup_log_alpha], lr=3e-4)
+    a.cost_limit, a.augmented_term, a.augmented_ratio = 0.0, 1.0, 1.0005
+    a.num_cbfs, a.l_p, a.action_dim, a.num_constraints = 7, 0.03, 2, 8
+    a.lambda_values = [0.0] * 8
+    a.backup_lambda_values = [0.0] * 7
+    a.neural_ode_model = model.NeuralODEModel(3, 3, 6)
+    a.neural_ode_model_optimizer = torch.optim.Adam(a.neural_ode_model.parameters(), lr=1e-3)
+    a.model_loss_func = agent_mod.PoseLoss()
+    dm = dyn_mod.DynamicsModel(env, _Args())
+
+    init = {k: _sd(getattr(a, k)) for k in ("critic", "lyapunovNet", "policy", "backup_policy", "neural_ode_model")}
+    batches = [_batch(gen, B) for _ in range(N_UPDATES)]
+    updates_list = list(range(8, 8 + N_UPDATES))                      # 8, 16: multipliers due; 10: NODE fit due
+    node_batches = [_batch(gen, NODE_N) for u in updates_list if u % 10 == 0]
+    eps = [[torch.randn(B, 2, generator=gen) for _ in range(3)] for _ in range(N_UPDATES)]
+    mem, node_mem = _Memory(batches, B * 4), _Memory(node_batches, NODE_N)
+
+    import torch.distributions.normal as tdn
+    orig = tdn._standard_normal
+    queue = []
+
+    def pop_eps(shape, dtype, device):
+        e = queue.pop(0)
+        assert tuple(shape) == tuple(e.shape), (shape, e.shape)
+        return e.to(dtype)
+
+    tdn._standard_normal = pop_eps
+    returns = []
+    try:
+        for i, u in enumerate(updates_list):
+            queue.extend(eps[i])                                      # next_state sample, pi, backup_pi
+            returns.append(a.update_parameters(mem, B, u, dm, node_mem, 10))
+            assert not queue
+    finally:
+        tdn._standard_normal = orig
+
+    to_t = lambda b: [None if x is None else torch.tensor(x, dtype=torch.float32) for x in b]  # noqa: E731
+    out = {
+        "B": B, "node_N": NODE_N, "updates": updates_list, "init": init, "batches": [to_t(b) for b in batches],
+        "node_batches": [to_t(b) for b in node_batches], "eps": eps,
+        "returns": torch.tensor(returns, dtype=torch.float64),        # qf1, qf2, lf, policy_loss_1, alpha_loss, alpha
+        "final": {k: _sd(getattr(a, k)) for k in ("critic", "critic_target", "lyapunovNet", "lyapunovNet_target", "policy",
+                                                   "backup_policy", "neural_ode_model")},
+        "log_alpha": a.log_alpha.detach().clone(), "backup_log_alpha": a.backup_log_alpha.detach().clone(),
+        "lambda_values": [float(v) for v in a.lambda_values],
+        "backup_lambda_values": [float(v) for v in a.backup_lambda_values],
+        "augmented_term": float(a.augmented_term),
+        "consts": {"dt": 0.02, "gamma_b": 50.0, "hazards": env.hazards_locations, "hazards_radius": 0.5, "l_p": 0.03,
+                   "gamma": 0.99, "tau": 0.005, "alpha": 0.2, "target_entropy": -2.0, "lr": 3e-4, "critic_lr": 4e-4,
+                   "node_lr": 1e-3, "action_low": [-3.5, -12.0], "action_high": [3.5, 12.0]},
+    }
+    torch.save(out, os.path.join(HERE, "update_U.pt"))
+    print("update_U.pt: returns\n", out["returns"])
+    print("lambda", out["lambda_values"], "rho", out["augmented_term"])
+
+
+if __name__ == "__main__":
+    main()
