@@ -28,9 +28,29 @@ import torch  # noqa: E402
 FLOP_EVAL_FWD = {"U": 103012, "P": 106024}      # SURVEY.md App. C (1 MAC = 2 FLOP)
 N_STEPS = 20
 DT = 0.02
-# dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at the bench size, from the
-# `ncu --set full` capture committed under profiles/ (r1_ncu_bench_*.txt); None until captured for that tier
-NCU_TRAFFIC = {"fp32": None, "tf32": 13.75e9, "3xtf32": None}   # tf32: profiles/r1_ncu_bench_tc_tf32.txt, one pass-A chunk launch (0.21 GB read + 13.54 GB written; 19 launches per pass)
+
+
+def ncu_traffic(precision):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the dominant kernel at the bench size, read from
+    the `ncu --set full` summary committed under profiles/ (None when no capture exists for that tier)."""
+    import re
+    f, kern = {"tf32": ("r1_ncu_bench_tc_tf32.txt", "node_tc_bwd_kernel"),
+               "fp32": (None, None), "3xtf32": (None, None)}[precision]
+    path = os.path.join(ROOT, "profiles", f) if f else None
+    if not path or not os.path.exists(path):
+        return None, None
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot, inside = 0.0, False
+    for line in open(path):
+        if line.startswith("kernel:"):
+            if inside:
+                break
+            inside = kern in line
+        elif inside:
+            m = re.match(r"dram__bytes_(read|write)\.sum\s+(\w+)\s+([0-9.]+)", line)
+            if m:
+                tot += float(m.group(3)) * unit[m.group(2)]
+    return (tot or None), "profiles/" + f
 
 
 def parse():
@@ -44,7 +64,9 @@ def parse():
     ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32", "3xtf32"],
                     help="tf32: tcgen05 kind::tf32 forward + reverse sweep, dW in bf16 (the 1e-2 tier of north_star); "
                          "fp32: exact FP32 FMA path (1e-5 tier); 3xtf32: split-TF32 forward (fp32-class) + FP32 backward")
-    ap.add_argument("--cpu-sample", type=int, default=1024, help="trajectories in the CPU baseline sample")
+    ap.add_argument("--cpu-sample", type=int, default=16384,
+                    help="trajectories in the CPU baseline sample (2^20 x 25 passes does not fit a bench run: ~2.5 min "
+                         "per pass on 16 cores; the rate is flat in the sample size, see cpu_baseline.flatness)")
     ap.add_argument("--suite", default="headline", choices=["headline", "configs"],
                     help="configs: latencies of the reference's real small-batch configurations 1-3 (SURVEY.md §8d) "
                          "next to the same code run eagerly by PyTorch on the GPU and on the host cores")
@@ -55,10 +77,31 @@ def flop_per_traj_step(env):
     return 4 * 3 * FLOP_EVAL_FWD[env]            # rk4: 4 evaluations, fwd + bwd = 3x fwd
 
 
-def make_oracle_model(env):
-    from oracle import nlbac_ref
+REF_VARIANT = {"U": "NLBAC_Unicycle_RL_training/Unicycle_RL_training", "P": "NLBAC_pvtol_RL_training/Pvtol_RL_training"}
+
+
+def make_reference_model(env, device="cpu"):
+    """The NODE of the reference arm under torch.manual_seed(0), and what it is: the reference's OWN
+    ``sac_cbf_clf/model.py`` class imported by path (kind "reference": only where /root/reference exists, i.e. in the
+    build container -- its module-global ``device`` is patched, U model.py:11, and ``torchdiffeq`` is the restated
+    solver, not installable anywhere we run), else the oracle's restatement of that class (kind "port")."""
+    import importlib.util
+    import types
+    from oracle import nlbac_ref, torchdiffeq_restated
+    path = os.path.join("/root/reference", REF_VARIANT[env], "sac_cbf_clf", "model.py")
+    dims = (3, 3, 6) if env == "U" else (6, 6, 12)
+    if os.path.exists(path):
+        stub = types.ModuleType("torchdiffeq")
+        stub.odeint = torchdiffeq_restated.odeint
+        sys.modules.setdefault("torchdiffeq", stub)
+        spec = importlib.util.spec_from_file_location("nlbac_reference_model_" + env, path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        mod.device = torch.device(device)
+        torch.manual_seed(0)
+        return mod.NeuralODEModel(*dims).to(device), "reference"
     torch.manual_seed(0)
-    return nlbac_ref.AffineNODE(3, 3, 6) if env == "U" else nlbac_ref.AffineNODE(6, 6, 12)
+    return nlbac_ref.AffineNODE(*dims).to(device), "port"
 
 
 def synth_y0(env, M, seed, device):
@@ -67,15 +110,20 @@ def synth_y0(env, M, seed, device):
     return torch.rand(M, D, generator=g, device=device) * 2 - 1
 
 
-def cpu_reference_run(env, sample, steps, warmup, threads):
-    """The reference's CPU path (oracle restatement of torchdiffeq + the reference NODE forward),
-    PyTorch CPU fp32, on a bounded sample of the same workload.  Returns (traj-steps/s, ms per pass)."""
+def reference_run(env, sample, steps, warmup, threads=None, device="cpu"):
+    """The reference's path (its NODE class, see make_reference_model, + the restated torchdiffeq rk4), eager PyTorch
+    fp32 (TF32 off) on a bounded sample of the same workload; on the host cores (``threads``) or, with
+    device="cuda", run eagerly on the GPU -- SURVEY.md 8(d)'s like-for-like bar.
+    Returns (traj-steps/s, ms per pass, kind)."""
     from oracle.torchdiffeq_restated import odeint as oracle_odeint
-    torch.set_num_threads(threads)
-    model = make_oracle_model(env)
-    y0 = synth_y0(env, sample, 1234, "cpu")
-    t = DT * torch.arange(N_STEPS + 1, dtype=torch.float32)
+    if threads:
+        torch.set_num_threads(threads)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    model, kind = make_reference_model(env, device)
+    y0 = synth_y0(env, sample, 1234, device)
+    t = (DT * torch.arange(N_STEPS + 1, dtype=torch.float32)).to(device)
     n_s = 3 if env == "U" else 6
+    sync = torch.cuda.synchronize if device != "cpu" else (lambda: None)
 
     def one():
         model.zero_grad()
@@ -84,11 +132,13 @@ def cpu_reference_run(env, sample, steps, warmup, threads):
 
     for _ in range(warmup):
         one()
+    sync()
     t0 = time.perf_counter()
     for _ in range(steps):
         one()
+    sync()
     dt = (time.perf_counter() - t0) / steps
-    return sample * N_STEPS / dt, dt * 1e3
+    return sample * N_STEPS / dt, dt * 1e3, kind
 
 
 class ClockSampler(threading.Thread):
@@ -192,9 +242,8 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     env, M = args.env, 1 << args.log2m
     n_s = 3 if env == "U" else 6
-    ref = make_oracle_model(env)
+    torch.manual_seed(0)     # same nn.Linear construction order as the reference class -> same default init
     model = nlbac_b200.NeuralODEModel(3, 3, 6) if env == "U" else nlbac_b200.NeuralODEModel(6, 6, 12)
-    model.load_state_dict(ref.state_dict())
     model.to(dev)
     params = list(model.parameters())
     t = [DT * i for i in range(N_STEPS + 1)]
@@ -298,7 +347,9 @@ def run_ours(args):
             dw_gbs = dw_bytes / (k_ms[2] / K * 1e-3) / 1e9 if k_ms[2] else None
             secondary = {"kernel": "node_tc_dw_kernel (pass B: bf16 dW = d^T a over the HBM images)", "bound": "hbm",
                          "achieved": dw_gbs, "peak": hbm, "unit": "GB/s", "frac": dw_gbs / hbm if dw_gbs else None,
-                         "algorithmic_bytes_per_pass": dw_bytes, "ms_per_pass": k_ms[2] / K,
+                         "image_bytes_per_pass": dw_bytes,
+                         "algorithmic_bytes_per_pass": M * (20.0 + (N_STEPS + 1) * 20.0 + 2 * N_STEPS * 4 * 12.0 + 2 * 20.0)
+                         if env == "U" else None, "ms_per_pass": k_ms[2] / K,
                          "launches_per_pass": k_n[2] // K}
         else:
             # algorithmic work = dX + dW (2 x forward FLOPs); the kernel also re-computes the forward (3 x executed)
@@ -309,7 +360,7 @@ def run_ours(args):
             secondary = None
         achieved = sweep_flops / (sweep_ms * 1e-3) / 1e12 if sweep_ms else None
         roof.update({"achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": achieved / peak if achieved and peak else None, "traffic": NCU_TRAFFIC.get(args.precision),
+                     "frac": achieved / peak if achieved and peak else None, "traffic": ncu_traffic(args.precision)[0], "traffic_source": ncu_traffic(args.precision)[1],
                      "peak_source": peak_src, "algorithmic_flops_per_pass": sweep_flops,
                      "executed_tflops": executed / (sweep_ms * 1e-3) / 1e12 if sweep_ms else None,
                      "ms_per_pass": sweep_ms, "launches_per_pass": sweep_n,
@@ -319,7 +370,37 @@ def run_ours(args):
         whole = value / world * flop_per_traj_step(env) / 1e12
         roof["whole_step"] = {"achieved": whole, "unit": "TFLOP/s", "frac": whole / peak if peak else None}
         cores = os.cpu_count()
-        cpu_val, cpu_ms = cpu_reference_run(env, args.cpu_sample, 2, 1, cores) if world == 1 else (None, None)
+        cpu_base = eager_gpu = None
+        if world == 1:
+            del y_dev
+            torch.cuda.empty_cache()
+            cs = args.cpu_sample
+            cv, cms, kind = reference_run(env, cs, 2, 1, cores)
+            small = max(64, min(1024, cs // 16))
+            fv, fms, _ = reference_run(env, small, 2, 1, cores)
+            ov, oms, _ = reference_run(env, min(cs, 2048), 1, 1, 1)
+            cpu_base = {"value": cv, "unit": "trajectory-steps/s", "cores": cores, "kind": kind,
+                        "sample": "%d trajectories x 20 rk4 steps fwd+bwd (the reference's NeuralODEModel + restated "
+                                  "torchdiffeq rk4, PyTorch CPU fp32), %.0f ms per pass, 1 warm-up + 2 timed" % (cs, cms),
+                        "flatness": {"sample": small, "value": fv, "ms_per_pass": fms},
+                        "one_thread": {"sample": min(cs, 2048), "value": ov, "ms_per_pass": oms, "cores": 1}}
+            gs = min(M, 1 << 16)      # eager autograd keeps ~300 KB of activations per trajectory
+            gv, gms, gkind = reference_run(env, gs, 2, 1, None, device="cuda")
+            eager_gpu = {"value": gv, "unit": "trajectory-steps/s", "kind": gkind, "ms_per_pass": gms,
+                         "sample": "%d trajectories x 20 rk4 steps fwd+bwd: the same reference classes + restated "
+                                   "torchdiffeq run eagerly by PyTorch on this B200 (fp32, TF32 off)" % gs}
+        if args.precision == "tf32":
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import umma_peak
+            pk = umma_peak.measure(1.5, modes=(1, 3))
+            tf32_peak = {"pipe": pk["tf32_ts_n256"], "kernel_tile_n112": pk["tf32_ts_n112"],
+                         "how": "nlbac_umma_peak_probe: one thread per SM issues tcgen05.mma kind::tf32 back to back, "
+                                "A in tensor memory, B in shared memory, M=128, N=256 (pipe) / N=112 (the NODE tile); "
+                                "burst = best ~10 ms launch, sustained = 1.5 s of launches"}
+            roof["peak_measured_tf32"] = tf32_peak
+            mp = tf32_peak["pipe"]["sustained_tflops"]
+            roof["frac_of_measured_tf32"] = achieved / mp if achieved and mp else None
+            roof["whole_step"]["frac_of_measured_tf32"] = whole / mp if mp else None
         line = {
             "metric": "neural-ODE trajectory-steps/sec (fwd+bwd)", "value": value, "unit": "trajectory-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
@@ -337,9 +418,7 @@ def run_ours(args):
             "roofline": roof, "roofline_secondary": secondary,
             "fp32_tier": {"value": traj_steps / (fp32_ms * 1e-3), "ms_per_step": fp32_ms,
                           "note": "exact FP32 FMA path (1e-5 tier), same workload, 2 timed passes"} if fp32_ms else None,
-            "cpu_baseline": {"value": cpu_val, "unit": "trajectory-steps/s", "cores": cores, "kind": "port",
-                             "sample": "%d trajectories x 20 rk4 steps fwd+bwd, PyTorch CPU fp32, %.0f ms per pass" % (
-                                 args.cpu_sample, cpu_ms)} if cpu_val else None,
+            "cpu_baseline": cpu_base, "eager_gpu_baseline": eager_gpu,
             "e2e": {"value": traj_steps / (e2e_ms / args.steps * 1e-3), "unit": "trajectory-steps/s",
                     "h2d_bytes_per_step": y0_host.numel() * 4, "d2h_bytes_per_step": 4 + flat_h.numel() * 4},
             "gpu_launches": int(sum(k_n)),
@@ -355,15 +434,17 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count()
-    val, ms = cpu_reference_run(args.env, args.cpu_sample, args.steps, args.warmup, cores)
-    sample = "%d trajectories x 20 rk4 steps fwd+bwd per step, PyTorch CPU fp32" % args.cpu_sample
+    val, ms, kind = reference_run(args.env, args.cpu_sample, args.steps, args.warmup, cores)
+    sample = ("%d trajectories x 20 rk4 steps fwd+bwd per step (config5 is 2^20 per GPU: ~2.5 min per pass on 16 cores, "
+              "so the arm times a bounded sample; the rate is flat in the sample size), PyTorch CPU fp32, all %d host "
+              "threads" % (args.cpu_sample, cores))
     print(json.dumps({
         "impl": "reference", "metric": "neural-ODE trajectory-steps/sec (fwd+bwd)", "value": val,
         "unit": "trajectory-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": "config5 sample: %s" % sample, "method": "rk4", "solver_steps": N_STEPS},
-        "cpu_baseline": {"value": val, "unit": "trajectory-steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "trajectory-steps/s", "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": val, "unit": "trajectory-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
