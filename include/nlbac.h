@@ -117,6 +117,23 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
                          const float* ckpt, const float* grad_out, float* grad_y0, float* grad_params,
                          void* ws, void* stream);
 
+/* nlbac_node_solve_bwd for callers that may not allocate (CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as nlbac_node_solve_bwd with precision NLBAC_PREC_FP32, minus `ws`: the scratch (step
+ * schedule + the 8 gradient replicas the CTAs reduce into, ~1.7 MB for the shipped shapes) lives in a file-scope
+ * `static __device__` array of NLBAC_NOALLOC_SCRATCH_BYTES inside the library, which every GPU that loads the library
+ * holds until exit.  The entry point calls no cudaMalloc / cudaFree / allocating routine; the caller still passes every
+ * input and output.  A solve whose scratch (nlbac_node_workspace_bytes' bwd_bytes) exceeds the array, or any precision
+ * other than NLBAC_PREC_FP32 (the tensor-core tier needs GBs of operand images), is rejected with -1 and a message.
+ * The array is shared by every call on that device and keeps the last call's contents: the entry point clears what must
+ * start at zero on the caller's stream before use, and calls that overlap on one GPU (two streams, two threads) RACE --
+ * serialise them. */
+#define NLBAC_NOALLOC_SCRATCH_BYTES (2u << 20)
+int nlbac_node_solve_bwd_noalloc(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B,
+                                 const float* t, int n_t, const float* grid, int n_grid, int method,
+                                 const float* ckpt, const float* grad_out, float* grad_y0, float* grad_params,
+                                 void* stream);
+
 /* Adaptive dopri5 with torchdiffeq semantics (one step size for the whole batch from an RMS norm over all
  * of [B, D]; FSAL; 4th-order dense output at the requested times).  The forward SYNCHRONISES the stream once
  * per attempted step (accept/reject is a host decision, as in torchdiffeq).  `t` host, strictly increasing.

@@ -104,6 +104,8 @@ def _declare(lib):
                                          vp, vp, vp, vp]
     lib.nlbac_node_solve_bwd.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, fp, c.c_int, c.c_int, c.c_int,
                                          vp, vp, vp, vp, vp, vp]
+    lib.nlbac_node_solve_bwd_noalloc.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, fp, c.c_int, c.c_int,
+                                                 vp, vp, vp, vp, vp]
     szp = c.POINTER(c.c_size_t)
     lib.nlbac_node_dopri5_workspace_bytes.argtypes = [dp, c.c_int64, c.c_int, c.c_int, szp, szp, szp]
     lib.nlbac_node_dopri5_fwd.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, c.c_float, c.c_float, c.c_int, c.c_int,

@@ -1,6 +1,7 @@
 // C ABI of the NODE solve (include/nlbac.h): descriptor dispatch, schedule tables, launches.
 #include <cstdarg>
 #include <cstring>
+#include <mutex>
 #include <vector>
 
 #include "../../include/nlbac.h"
@@ -368,6 +369,33 @@ __global__ void __launch_bounds__(256, 1) fma_shape_kernel(int iters, float* sin
   if (s == 123.456f) sink[0] = s;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Scratch of nlbac_node_solve_bwd_noalloc (include/nlbac.h): held by every GPU that loads the library until exit.
+// In HOST code the name `g_noalloc_scratch` is a host-side stand-in, not a device address: the launch path must use
+// the pointer cudaGetSymbolAddress returns, taken once per device with that device current.
+// ------------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NLBAC_NOALLOC_SCRATCH_BYTES];
+
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static std::mutex g_noalloc_mu;
+static void* g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+static int noalloc_scratch(void** out) {
+  int dev = -1;
+  NLBAC_CUDA(cudaGetDevice(&dev));
+  NLBAC_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "device ordinal %d outside the no-alloc table (%d)", dev,
+                NOALLOC_MAX_DEVICES);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (g_noalloc_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    NLBAC_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    NLBAC_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null scratch address on device %d", dev);
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+
 }  // namespace nlbac
 
 using namespace nlbac;
@@ -541,6 +569,27 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
     }
     return 0;
   });
+}
+
+// No counterpart in the reference: the FP32 reverse sweep with its scratch
+// in the library's static device array instead of caller-supplied memory.  Allocates nothing; not re-entrant per device.
+int nlbac_node_solve_bwd_noalloc(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B,
+                                 const float* t, int n_t, const float* grid, int n_grid, int method,
+                                 const float* ckpt, const float* grad_out, float* grad_y0, float* grad_params,
+                                 void* stream) {
+  NLBAC_REQUIRE(n_grid >= 2 && n_t >= 1 && B >= 0, "bad sizes");
+  size_t need = 0;
+  if (int rc = nlbac_node_workspace_bytes(desc, B, n_grid, n_t, method, nullptr, nullptr, &need)) return rc;
+  NLBAC_REQUIRE(need <= (size_t)NLBAC_NOALLOC_SCRATCH_BYTES,
+                "nlbac_node_solve_bwd_noalloc: this solve needs %zu bytes of scratch (n_grid=%d, n_t=%d), the static "
+                "array holds %u; use nlbac_node_solve_bwd with caller-supplied workspace", need, n_grid, n_t,
+                (unsigned)NLBAC_NOALLOC_SCRATCH_BYTES);
+  void* ws = nullptr;
+  if (int rc = noalloc_scratch(&ws)) return rc;
+  // the array keeps the previous call's contents: the schedule words are rewritten and the gradient replicas are
+  // cleared (cudaMemsetAsync on the caller's stream) inside the shared path before the sweep reads them
+  return nlbac_node_solve_bwd(desc, packed, y0, B, t, n_t, grid, n_grid, method, NLBAC_PREC_FP32, ckpt, grad_out,
+                              grad_y0, grad_params, ws, stream);
 }
 
 // ------------------------------------------------------------------------------------------------
