@@ -64,9 +64,10 @@ def parse():
     ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32", "3xtf32"],
                     help="tf32: tcgen05 kind::tf32 forward + reverse sweep, dW in bf16 (the 1e-2 tier of north_star); "
                          "fp32: exact FP32 FMA path (1e-5 tier); 3xtf32: split-TF32 forward (fp32-class) + FP32 backward")
-    ap.add_argument("--cpu-sample", type=int, default=16384,
-                    help="trajectories in the CPU baseline sample (2^20 x 25 passes does not fit a bench run: ~2.5 min "
-                         "per pass on 16 cores; the rate is flat in the sample size, see cpu_baseline.flatness)")
+    ap.add_argument("--cpu-sample", type=int, default=65536,
+                    help="trajectories in the CPU baseline sample (2^20 x 25 passes does not fit a bench run: ~40 s per "
+                         "pass on 16 cores; the CPU rate still grows with the sample -- 1.5e5 at 2^10, 4.8e5 at 2^14 --, "
+                         "cpu_baseline.flatness reports a second point)")
     ap.add_argument("--suite", default="headline", choices=["headline", "configs"],
                     help="configs: latencies of the reference's real small-batch configurations 1-3 (SURVEY.md §8d) "
                          "next to the same code run eagerly by PyTorch on the GPU and on the host cores")
@@ -376,7 +377,7 @@ def run_ours(args):
             torch.cuda.empty_cache()
             cs = args.cpu_sample
             cv, cms, kind = reference_run(env, cs, 2, 1, cores)
-            small = max(64, min(1024, cs // 16))
+            small = max(64, cs // 4)
             fv, fms, _ = reference_run(env, small, 2, 1, cores)
             ov, oms, _ = reference_run(env, min(cs, 2048), 1, 1, 1)
             cpu_base = {"value": cv, "unit": "trajectory-steps/s", "cores": cores, "kind": kind,
@@ -435,9 +436,8 @@ def run_reference(args):
         return
     cores = os.cpu_count()
     val, ms, kind = reference_run(args.env, args.cpu_sample, args.steps, args.warmup, cores)
-    sample = ("%d trajectories x 20 rk4 steps fwd+bwd per step (config5 is 2^20 per GPU: ~2.5 min per pass on 16 cores, "
-              "so the arm times a bounded sample; the rate is flat in the sample size), PyTorch CPU fp32, all %d host "
-              "threads" % (args.cpu_sample, cores))
+    sample = ("%d trajectories x 20 rk4 steps fwd+bwd per step (config5 is 2^20 per GPU, ~40 s per pass on 16 cores: "
+              "the arm times a bounded sample), PyTorch CPU fp32, all %d host threads" % (args.cpu_sample, cores))
     print(json.dumps({
         "impl": "reference", "metric": "neural-ODE trajectory-steps/sec (fwd+bwd)", "value": val,
         "unit": "trajectory-steps/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
