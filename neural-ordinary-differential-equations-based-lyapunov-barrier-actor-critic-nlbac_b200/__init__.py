@@ -13,8 +13,9 @@ from .tail import DynamicsModel, FusedAdam, soft_update, hard_update, constraint
 from . import constraints
 from .replay import ReplayMemory
 from .graphs import GraphedTrainStep
+from .agent import GraphedUpdate
 from .envs import VecUnicycleEnv, VecSimulatedCarsEnv, VecPvtolEnv
 
 __all__ = ["odeint", "NeuralODEModel", "train_step", "build", "describe", "QNetwork", "LyaNetwork", "BarrierNetwork",
            "GaussianPolicy", "weights_init_", "DynamicsModel", "FusedAdam", "soft_update", "hard_update",
-           "constraint_sums", "lookahead", "make_constraint_desc", "constraints", "ReplayMemory", "GraphedTrainStep", "VecUnicycleEnv", "VecSimulatedCarsEnv", "VecPvtolEnv"]
+           "constraint_sums", "lookahead", "make_constraint_desc", "constraints", "ReplayMemory", "GraphedTrainStep", "GraphedUpdate", "VecUnicycleEnv", "VecSimulatedCarsEnv", "VecPvtolEnv"]

@@ -1,0 +1,256 @@
+"""``GraphedUpdate`` — one minibatch update of ``SAC_CBF_CLF.update_parameters`` as ONE CUDA-graph replay.
+
+Mirrors U ``sac_cbf_clf/sac_cbf_clf.py:181-319`` (C :177-319 with the cars constraint block): TD targets, critic +
+Lyapunov updates, actor and backup-actor losses = SAC term + CBF/CLF augmented Lagrangian (``get_cbf_clf_part`` /
+``backup_get_cbf_clf_part``, :364-406 -> ``constraints.*_required_matrix``), Adam steps, the temperature updates
+(:292-308), Polyak averaging (:315-317).  Everything the reference keeps as Python floats -- multipliers, rho, the
+CBF/CLF ratio, alpha, the update counter -- lives on the device, so the six ``.item()`` of :319 and the ``float()``
+read-backs of :510, :525-528 disappear: the update is captured once and replayed per call with zero host
+synchronisation.  The NODE model fit (:205-219, every ``NODE_model_update_interval`` updates) is a second graph
+(``GraphedTrainStep``) once the NODE batch has reached its steady size, the eager fused ``train_step`` before that.
+"""
+import torch
+
+from . import constraints as C
+from .odeint import odeint
+from .tail import FusedAdam, soft_update
+
+
+class GraphedUpdate:
+    """``upd = GraphedUpdate(critic, critic_target, lyapunovNet, lyapunovNet_target, policy, backup_policy,
+    neural_ode_model, dynamics_model, batch_size, primary=fn, backup=fn, ...)``
+
+    ``primary(state, pi, V) -> required_matrix [m, 1]`` and ``backup(state, backup_pi) -> [m - 1, 1]`` are the bodies
+    of ``get_policy_loss_2`` / ``backup_get_policy_loss_2`` up to the constraint sums (e.g. closures over
+    ``constraints.unicycle_required_matrix``); the augmented Lagrangians are applied here on the device.
+    ``update_parameters(memory, batch_size, updates, dynamics_model, NODE_memory, NODE_model_update_interval)`` keeps the
+    reference's signature; it returns a CUDA tensor with the reference's six values (qf1, qf2, lf, policy_loss_1,
+    alpha_loss, alpha) instead of six Python floats -- ``.tolist()`` it when the floats are wanted.
+    """
+
+    def __init__(self, critic, critic_target, lyapunovNet, lyapunovNet_target, policy, backup_policy, neural_ode_model,
+                 dynamics_model, batch_size, *, primary, backup, num_constraints, obs_dim, act_dim, center_pos_num,
+                 gamma=0.99, tau=0.005, alpha=0.2, lr=3e-4, critic_lyapunov_lr=4e-4, node_lr=1e-3,
+                 target_update_interval=1, automatic_entropy_tuning=True, multiplier_interval=8, lambda_max=400.0,
+                 ratio_floor=None, use_ratio=True, backup_update_interval=1, separate_backup_rho=False,
+                 node_solver="euler", dt=0.02, node_n_s=3, node_n_u=2, node_graph_batch=32768):
+        dev = next(critic.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("GraphedUpdate: the networks must live on a CUDA device (no CPU fallback)")
+        self.device, self.B = dev, int(batch_size)
+        self.critic, self.critic_target = critic, critic_target
+        self.lyapunovNet, self.lyapunovNet_target = lyapunovNet, lyapunovNet_target
+        self.policy, self.backup_policy = policy, backup_policy
+        self.neural_ode_model, self.dynamics_model = neural_ode_model, dynamics_model
+        self.primary, self.backup = primary, backup
+        self.gamma, self.tau, self.target_update_interval = gamma, tau, target_update_interval
+        self.automatic_entropy_tuning = automatic_entropy_tuning
+        self.target_entropy = -float(act_dim)                                   # U sac_cbf_clf.py:77
+        f32 = dict(dtype=torch.float32, device=dev)
+        self.alpha = torch.full((1,), float(alpha), **f32)                      # python float in the reference
+        self.backup_alpha = torch.full((1,), float(alpha), **f32)
+        self.log_alpha = torch.zeros(1, requires_grad=True, **f32)
+        self.backup_log_alpha = torch.zeros(1, requires_grad=True, **f32)
+        mk = lambda ps, lr_: FusedAdam(ps, lr=lr_, capturable=True)             # noqa: E731
+        self.critic_optim = mk(critic.parameters(), critic_lyapunov_lr)
+        self.lyaNet_optim = mk(lyapunovNet.parameters(), critic_lyapunov_lr)
+        self.policy_optim = mk(policy.parameters(), lr)
+        self.backup_policy_optim = mk(backup_policy.parameters(), lr)
+        self.alpha_optim = mk([self.log_alpha], lr)
+        self.backup_alpha_optim = mk([self.backup_log_alpha], lr)
+        self.cstate = C.DeviceConstraintState(num_constraints, batch_size, dev, lambda_max=lambda_max,
+                                              update_interval=multiplier_interval, ratio_floor=ratio_floor,
+                                              use_ratio=use_ratio, backup_update_interval=backup_update_interval,
+                                              separate_backup_rho=separate_backup_rho)
+        self.updates_dev = torch.zeros(1, dtype=torch.int64, device=dev)
+        B = self.B
+        z = lambda *s: torch.zeros(*s, **f32)                                   # noqa: E731
+        self.buf = {"state": z(B, obs_dim), "action": z(B, act_dim), "reward": z(B, 1), "constraint": z(B, 1),
+                    "center_pos": z(B, center_pos_num), "next_center_pos": z(B, center_pos_num),
+                    "next_state": z(B, obs_dim), "mask": z(B, 1)}
+        self.eps = [z(B, act_dim) for _ in range(3)]                            # next-state sample, pi, backup pi
+        self.out = z(6)
+        # NODE fit (its own optimiser state; eager fused step until the batch reaches node_graph_batch, a graph after)
+        self.node_optim = FusedAdam(neural_ode_model.parameters(), lr=node_lr, capturable=True)
+        self.node_lr, self.node_solver, self.dt = node_lr, node_solver, dt
+        self.node_n_s, self.node_n_u, self.node_graph_batch = node_n_s, node_n_u, node_graph_batch
+        self._node_graph = None
+        self.graph = None
+
+    # ------------------------------------------------------------------------------------------------
+    @staticmethod
+    def _step(optim, loss, params):
+        grads = torch.autograd.grad(loss, params, retain_graph=True)
+        for p, g in zip(params, grads):
+            p.grad = g
+        optim.step()
+
+    def _body(self):
+        """U sac_cbf_clf.py:221-319, statement for statement, on the static buffers."""
+        b, F = self.buf, torch.nn.functional
+        st = self.cstate
+        st.set_updates_device(self.updates_dev)
+        with torch.no_grad():                                                                    # :231-238
+            next_a, next_logp, _ = self.policy.sample(b["next_state"], self.eps[0])
+            q1t, q2t = self.critic_target(b["next_state"], next_a)
+            min_q = torch.min(q1t, q2t) - self.alpha * next_logp
+            next_q = b["reward"] + b["mask"] * self.gamma * min_q
+            next_l = b["constraint"] + b["mask"] * self.gamma * self.lyapunovNet_target(b["next_center_pos"])
+        qf1, qf2 = self.critic(b["state"], b["action"])                                          # :240-246
+        qf1_loss, qf2_loss = F.mse_loss(qf1, next_q), F.mse_loss(qf2, next_q)
+        lf_loss = F.mse_loss(self.lyapunovNet(b["center_pos"]), next_l)
+        self._step(self.critic_optim, qf1_loss + qf2_loss, list(self.critic.parameters()))       # :249-251
+        self._step(self.lyaNet_optim, lf_loss, list(self.lyapunovNet.parameters()))              # :253-255
+        pi, log_pi, _ = self.policy.sample(b["state"], self.eps[1])                              # :258-261
+        min_qf_pi = torch.min(*self.critic(b["state"], pi))
+        bpi, blog_pi, _ = self.backup_policy.sample(b["state"], self.eps[2])                     # :264-267
+        bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
+        policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                                 # :270
+        backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()                 # :273
+        state = self.dynamics_model.get_state(b["state"])                                        # :380 (get_cbf_clf_part)
+        if isinstance(state, tuple):
+            state = state[0]
+        V = self.lyapunovNet(b["center_pos"]).detach()                                           # :382-383
+        policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V), st)            # :384 -> :408-530
+        backup_loss_2 = C.backup_augmented_lagrangian_device(self.backup(state, bpi), st)        # :279 -> :532-640
+        self._step(self.policy_optim, policy_loss_1 + policy_loss_2, list(self.policy.parameters()))         # :284-286
+        self._step(self.backup_policy_optim, backup_policy_loss_1 + backup_loss_2,
+                   list(self.backup_policy.parameters()))                                                    # :288-290
+        if self.automatic_entropy_tuning:                                                        # :292-308
+            alpha_loss = -(self.log_alpha * (log_pi + self.target_entropy).detach()).mean()
+            self._step(self.alpha_optim, alpha_loss, [self.log_alpha])
+            balpha_loss = -(self.backup_log_alpha * (blog_pi + self.target_entropy).detach()).mean()
+            self._step(self.backup_alpha_optim, balpha_loss, [self.backup_log_alpha])
+            with torch.no_grad():
+                self.alpha.copy_(self.log_alpha.exp())
+                self.backup_alpha.copy_(self.backup_log_alpha.exp())
+        else:
+            alpha_loss = torch.zeros((), device=self.device)
+        if self.target_update_interval == 1:                                                     # :315-317
+            soft_update(self.critic_target, self.critic, self.tau)
+            soft_update(self.lyapunovNet_target, self.lyapunovNet, self.tau)
+        with torch.no_grad():
+            self.out.copy_(torch.stack([qf1_loss.reshape(()), qf2_loss.reshape(()), lf_loss.reshape(()),
+                                        policy_loss_1.reshape(()), alpha_loss.reshape(()), self.alpha.reshape(())]))
+            self.updates_dev.add_(1)
+        return self.out
+
+    # ------------------------------------------------------------------------------------------------
+    def _state_tensors(self):
+        ts = []
+        for net in (self.critic, self.critic_target, self.lyapunovNet, self.lyapunovNet_target, self.policy,
+                    self.backup_policy):
+            ts += list(net.parameters())
+        ts += [self.log_alpha, self.backup_log_alpha, self.alpha, self.backup_alpha, self.updates_dev,
+               self.cstate.lambda_values, self.cstate.backup_lambda_values, self.cstate.augmented_term,
+               self.cstate.backup_augmented_term, self.cstate.due, self.cstate.backup_due]
+        return ts
+
+    def _optims(self):
+        return (self.critic_optim, self.lyaNet_optim, self.policy_optim, self.backup_policy_optim, self.alpha_optim,
+                self.backup_alpha_optim)
+
+    def capture(self):
+        """Warm-up on a side stream (lazy kernel attributes, allocator, Adam state), restore every tensor the update
+        mutates, then capture ``_body`` as one CUDA graph."""
+        snap = [t.detach().clone() for t in self._state_tensors()]
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            self._body()
+        torch.cuda.current_stream().wait_stream(side)
+        with torch.no_grad():
+            for t, v in zip(self._state_tensors(), snap):
+                t.copy_(v)
+            for opt in self._optims():
+                for s_ in opt.state.values():
+                    s_["exp_avg"].zero_()
+                    s_["exp_avg_sq"].zero_()
+                for v in opt._step_dev.values():
+                    v.zero_()
+        for net in (self.critic, self.critic_target, self.lyapunovNet, self.lyapunovNet_target, self.policy,
+                    self.backup_policy):
+            for p in net.parameters():
+                torch.autograd.graph.increment_version(p)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._body()
+        return self
+
+    @torch.no_grad()
+    def load_batch(self, batch, eps=None):
+        """``batch`` = the reference's sampled tuple (state, action, reward, constraint, center_pos, next_center_pos,
+        next_state, mask, ...) as CUDA tensors or host arrays; ``eps`` = three [B, n_u] noise tensors or None (drawn
+        from torch's CUDA generator, like ``Normal.rsample`` in the reference)."""
+        names = ("state", "action", "reward", "constraint", "center_pos", "next_center_pos", "next_state", "mask")
+        for n, v in zip(names, batch):
+            t = v if torch.is_tensor(v) else torch.as_tensor(v, dtype=torch.float32)
+            self.buf[n].copy_(t.reshape(self.buf[n].shape), non_blocking=True)
+        for i in range(3):
+            if eps is None:
+                self.eps[i].normal_()
+            else:
+                self.eps[i].copy_(eps[i], non_blocking=True)
+
+    def step(self, batch=None, eps=None):
+        """One update: load the minibatch into the static buffers and replay the graph.  No host synchronisation."""
+        if batch is not None:
+            self.load_batch(batch, eps)
+        if self.graph is None:
+            self.capture()
+        self.graph.replay()
+        for net in (self.critic, self.critic_target, self.lyapunovNet, self.lyapunovNet_target, self.policy,
+                    self.backup_policy):
+            for p in net.parameters():          # written through raw pointers inside the graph
+                torch.autograd.graph.increment_version(p)
+        return self.out
+
+    # ------------------------------------------------------------------------------------------------
+    def _node_body(self, state, action, next_state):
+        y0 = torch.cat((state, action), dim=-1)
+        pred = odeint(self.neural_ode_model, y0, [0.0, self.dt], method=self.node_solver, atol=1e-7, rtol=1e-5)[-1]
+        loss = torch.nn.functional.mse_loss(pred[:, :state.shape[1]], next_state)
+        self._step(self.node_optim, loss, list(self.neural_ode_model.parameters()))
+        return loss
+
+    def node_fit(self, state, action, next_state):
+        """The NODE model fit of U sac_cbf_clf.py:205-219 (``train_step``): eager fused step, or -- once the batch has the
+        steady size ``node_graph_batch`` -- one graph replay.  One Adam state (device step counter) serves both."""
+        N = state.shape[0]
+        if N != self.node_graph_batch:
+            return self._node_body(state, action, next_state)
+        if self._node_graph is None:
+            self._nb = [torch.empty_like(state), torch.empty_like(action), torch.empty_like(next_state)]
+            for d, s_ in zip(self._nb, (state, action, next_state)):
+                d.copy_(s_)
+            self._node_body(*self._nb)          # eager: this update itself (also warms the allocator)
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._node_loss = self._node_body(*self._nb)
+            self._node_graph = g
+            return self._node_loss
+        for d, s_ in zip(self._nb, (state, action, next_state)):
+            d.copy_(s_, non_blocking=True)
+        self._node_graph.replay()
+        for p in self.neural_ode_model.parameters():
+            torch.autograd.graph.increment_version(p)
+        return self._node_loss
+
+    def update_parameters(self, memory, batch_size, updates, dynamics_model=None, NODE_memory=None,
+                          NODE_model_update_interval=10, eps=None):
+        """The reference's call (U sac_cbf_clf.py:181) on a device-resident ``nlbac_b200.ReplayMemory``."""
+        batch = memory.sample(batch_size=batch_size)
+        if NODE_memory is not None and updates % NODE_model_update_interval == 0:
+            n = min(NODE_memory.position, 32768)
+            nb = NODE_memory.sample(batch_size=n)
+            dm = dynamics_model or self.dynamics_model
+            to_dev = lambda v: v if torch.is_tensor(v) else torch.as_tensor(v, dtype=torch.float32, device=self.device)  # noqa: E731
+            s0, s1 = dm.get_state(to_dev(nb[0])), dm.get_state(to_dev(nb[6]))
+            if isinstance(s0, tuple):           # Pvtol: (state7, state6) -- the NODE is fitted on the six dynamic states
+                s0, s1 = s0[1], s1[1]
+            self.node_fit(s0, to_dev(nb[1]), s1)
+        with torch.no_grad():
+            self.updates_dev.fill_(int(updates))
+        return self.step(batch, eps)

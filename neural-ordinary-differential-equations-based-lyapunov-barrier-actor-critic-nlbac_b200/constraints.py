@@ -87,18 +87,33 @@ class DeviceConstraintState:
     "multipliers are due" flag (``updates % interval == 0``) into a device scalar before the replay."""
 
     def __init__(self, num_constraints, batch_size, device, *, lambda_max=400.0, cost_limit=0.0, augmented_term=1.0,
-                 augmented_ratio=1.0005, update_interval=8, ratio_floor=None, use_ratio=True):
+                 augmented_ratio=1.0005, update_interval=8, ratio_floor=None, use_ratio=True,
+                 backup_update_interval=1, separate_backup_rho=False):
         f64 = dict(dtype=torch.float64, device=device)
         self.num_constraints, self.batch_size = num_constraints, batch_size
         self.lambda_values = torch.zeros(num_constraints, **f64)
         self.augmented_term = torch.full((), float(augmented_term), **f64)
         self.due = torch.zeros((), **f64)
+        # backup policy: CBF rows only, its own multipliers; U / C share rho with the primary loss (advanced twice per
+        # update, SURVEY.md App. D.4), P keeps a separate one and a longer multiplier interval (P :1025-1034)
+        self.backup_lambda_values = torch.zeros(num_constraints - 1, **f64)
+        self.backup_augmented_term = torch.full((), float(augmented_term), **f64)
+        self.backup_due = torch.zeros((), **f64)
+        self.backup_update_interval, self.separate_backup_rho = backup_update_interval, separate_backup_rho
         self.lambda_max, self.cost_limit, self.augmented_ratio = lambda_max, cost_limit, augmented_ratio
         self.Lagrangian_multiplier_update_interval = update_interval
         self.ratio_floor, self.use_ratio = ratio_floor, use_ratio
 
     def set_updates(self, updates):
         self.due.fill_(1.0 if updates % self.Lagrangian_multiplier_update_interval == 0 else 0.0)
+        self.backup_due.fill_(1.0 if updates % (self.Lagrangian_multiplier_update_interval *
+                                                 self.backup_update_interval) == 0 else 0.0)
+
+    def set_updates_device(self, updates_dev):
+        """Same from a device-resident update counter (int64 tensor): no host input at all, capturable."""
+        k = self.Lagrangian_multiplier_update_interval
+        self.due.copy_((updates_dev % k == 0).reshape(()).double())
+        self.backup_due.copy_((updates_dev % (k * self.backup_update_interval) == 0).reshape(()).double())
 
 
 def augmented_lagrangian_device(required_matrix, st):
@@ -121,6 +136,19 @@ def augmented_lagrangian_device(required_matrix, st):
     w[-1] = ratio
     lin = (st.lambda_values * w).float()            # lambda_i (x ratio for the CLF row)
     quad = (rho / 2.0 * w * w).float()              # rho / 2 (x ratio^2 for the CLF row)
+    return (lin * c + quad * c * c).sum().reshape(1)
+
+
+def backup_augmented_lagrangian_device(backup_required_matrix, st):
+    """``backup_augmented_lagrangian`` (U sac_cbf_clf.py:611-640, C :657-681, P :1022-1045) on a DeviceConstraintState."""
+    req = backup_required_matrix.reshape(-1)
+    c = req - st.cost_limit
+    rho_t = st.backup_augmented_term if st.separate_backup_rho else st.augmented_term
+    new_lambda = torch.clamp(st.backup_lambda_values + rho_t * req.detach().double(), 0.01, st.lambda_max)
+    st.backup_lambda_values.copy_(torch.where(st.backup_due > 0, new_lambda, st.backup_lambda_values))
+    rho_t.copy_(torch.clamp(rho_t * st.augmented_ratio, max=200.0))
+    lin = st.backup_lambda_values.float()
+    quad = (rho_t / 2.0).float()
     return (lin * c + quad * c * c).sum().reshape(1)
 
 

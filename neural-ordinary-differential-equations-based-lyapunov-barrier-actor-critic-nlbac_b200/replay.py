@@ -1,7 +1,9 @@
 """Device-resident replay memory with the reference's interface (U sac_cbf_clf/replay_memory.py:4-28).
 
 ``ReplayMemory(capacity, seed)``, ``push(state, action, reward, constraint, center_pos, next_center_pos, next_state,
-mask, t=None, next_t=None)``, ``sample(batch_size)``, ``len()``, ``.position`` behave like the reference's class: the
+mask, t=None, next_t=None)`` -- or the 11-field form of the learned-barrier variants with ``barrier_signal`` after
+``constraint`` (BU / BP replay_memory.py:12); the field count of the first push fixes the layout --, ``batch_push``
+(P / BP :20-26), ``sample(batch_size)``, ``len()``, ``.position`` behave like the reference's class: the
 ring overwrites the oldest transition, ``random.seed(seed)`` seeds Python's global generator and ``sample`` draws the
 SAME indices ``random.sample(self.buffer, batch_size)`` would (``random.sample`` depends on the population's length
 only).  What changes is where the data lives: each transition is one float32 row of a ``[capacity, width]`` device
@@ -20,6 +22,9 @@ from . import _lib
 
 FIELDS = ("state", "action", "reward", "constraint", "center_pos", "next_center_pos", "next_state", "mask", "t",
           "next_t")
+# learned-barrier variants (BU / BP sac_cbf_clf/replay_memory.py:12): an extra ``barrier_signal`` after ``constraint``
+FIELDS_BARRIER = ("state", "action", "reward", "constraint", "barrier_signal", "lya_pre_term", "lya_next_term",
+                  "next_state", "mask", "t", "next_t")
 
 
 class ReplayMemory:
@@ -41,8 +46,9 @@ class ReplayMemory:
         return self._n
 
     def _init_layout(self, fields):
+        names = FIELDS_BARRIER if len(fields) == len(FIELDS_BARRIER) else FIELDS
         off, lay = 0, []
-        for name, v in zip(FIELDS, fields):
+        for name, v in zip(names, fields):
             if v is None:
                 lay.append((name, off, 0, None))
                 continue
@@ -53,11 +59,25 @@ class ReplayMemory:
         self._ring = torch.empty((self.capacity, off), dtype=torch.float32, device=self.device)
         self._stage = torch.empty((self.capacity, off), dtype=torch.float32).pin_memory()
 
-    def push(self, state, action, reward, constraint, center_pos, next_center_pos, next_state, mask, t=None,
-             next_t=None):
-        fields = (state, action, reward, constraint, center_pos, next_center_pos, next_state, mask, t, next_t)
+    def _fields(self, args, t, next_t):
+        """The reference's positional signatures: 8 (+ t, next_t) fields for U / C / P, 9 (+ t, next_t) with
+        ``barrier_signal`` for BU / BP; ``t`` / ``next_t`` may also come as keywords."""
+        n = len(args)
+        if n in (10, 11):
+            if t is not None or next_t is not None:
+                raise TypeError("ReplayMemory.push: t / next_t given twice")
+            return tuple(args)
+        if n in (8, 9):
+            return tuple(args) + (t, next_t)
+        raise TypeError("ReplayMemory.push takes 8 or 9 transition fields (+ t, next_t), got %d" % n)
+
+    def push(self, *args, t=None, next_t=None):
+        fields = self._fields(args, t, next_t)
         if self._layout is None:
             self._init_layout(fields)
+        if len(fields) != len(self._layout):
+            raise TypeError("ReplayMemory.push: %d fields, the memory was started with %d" % (len(fields),
+                                                                                               len(self._layout)))
         row = self._stage[self.position].numpy()
         for (name, off, w, shape), v in zip(self._layout, fields):
             if (v is None) != (w == 0):
@@ -71,6 +91,34 @@ class ReplayMemory:
         if self._n < self.capacity:
             self._n += 1
         self.position = (self.position + 1) % self.capacity
+
+    def batch_push(self, *batches, t_batch=None, next_t_batch=None):
+        """P / BP ``batch_push`` (P sac_cbf_clf/replay_memory.py:20-26): the rows of the batches, pushed in order --
+        here as whole-column copies into the staging ring instead of a Python loop over ``push``."""
+        fields = self._fields(batches, t_batch, next_t_batch)
+        n = len(np.asarray(fields[0]))
+        if n == 0:
+            return
+        if self._layout is None:
+            self._init_layout(tuple(None if f is None else np.asarray(f)[0] for f in fields))
+        if len(fields) != len(self._layout):
+            raise TypeError("ReplayMemory.batch_push: %d fields, the memory was started with %d" % (
+                len(fields), len(self._layout)))
+        idx = (self.position + np.arange(n)) % self.capacity
+        keep = slice(max(0, n - self.capacity), n)          # more rows than capacity: only the last `capacity` survive
+        stage = self._stage.numpy()
+        for (name, off, w, shape), v in zip(self._layout, fields):
+            if (v is None) != (w == 0):
+                raise ValueError("ReplayMemory.batch_push: field %r changed between None and a value" % name)
+            if w:
+                a = np.asarray(v, dtype=np.float32).reshape(n, -1)
+                if a.shape[1] != w:
+                    raise ValueError("ReplayMemory.batch_push: field %r has %d values per row, expected %d" % (
+                        name, a.shape[1], w))
+                stage[idx[keep], off:off + w] = a[keep]
+        self._dirty.extend(int(i) for i in idx[keep])
+        self._n = min(self.capacity, self._n + n)
+        self.position = int((self.position + n) % self.capacity)
 
     def _flush(self):
         if not self._dirty:

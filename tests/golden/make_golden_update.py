@@ -123,11 +123,17 @@ def main():
         return e.to(dtype)
 
     tdn._standard_normal = pop_eps
-    returns = []
+    returns, lam_trace, blam_trace, rho_trace = [], [], [], []
     try:
         for i, u in enumerate(updates_list):
             queue.extend(eps[i])                                      # next_state sample, pi, backup_pi
             returns.append(a.update_parameters(mem, B, u, dm, node_mem, 10))
+            lam_trace.append([float(v) for v in a.lambda_values])
+            blam_trace.append([float(v) for v in a.backup_lambda_values])
+            rho_trace.append(float(a.augmented_term))
+            if i == 0:
+                after_first = {k: _sd(getattr(a, k)) for k in ("critic", "critic_target", "lyapunovNet", "policy",
+                                                               "backup_policy")}
             assert not queue
     finally:
         tdn._standard_normal = orig
@@ -143,6 +149,9 @@ def main():
         "lambda_values": [float(v) for v in a.lambda_values],
         "backup_lambda_values": [float(v) for v in a.backup_lambda_values],
         "augmented_term": float(a.augmented_term),
+        "lambda_trace": torch.tensor(lam_trace, dtype=torch.float64),
+        "backup_lambda_trace": torch.tensor(blam_trace, dtype=torch.float64),
+        "rho_trace": torch.tensor(rho_trace, dtype=torch.float64), "after_first": after_first,
         "consts": {"dt": 0.02, "gamma_b": 50.0, "hazards": env.hazards_locations, "hazards_radius": 0.5, "l_p": 0.03,
                    "gamma": 0.99, "tau": 0.005, "alpha": 0.2, "target_entropy": -2.0, "lr": 3e-4, "critic_lr": 4e-4,
                    "node_lr": 1e-3, "action_low": [-3.5, -12.0], "action_high": [3.5, 12.0]},

@@ -21,7 +21,7 @@ def _rel(a, b):
     return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
 
 
-def _models(tag, seed=0):
+def _models(tag, seed=0, scale=1.5):
     import nlbac_b200
     torch.manual_seed(seed)
     if tag == "U":
@@ -39,7 +39,7 @@ def _models(tag, seed=0):
     # make the thin layers and biases matter
     with torch.no_grad():
         for p in ref.parameters():
-            p.mul_(1.5)
+            p.mul_(scale)
     ours.load_state_dict(ref.state_dict())
     return ref, ours.cuda()
 
@@ -388,3 +388,38 @@ def test_tensor_core_backward_tf32_tier(tag, B):
     oracle_odeint(ref, ya2, t[:2], method="euler")[-1].pow(2).sum().backward()
     nlbac_b200.odeint(ours, yb2, t[:2], method="euler", precision="tf32")[-1].pow(2).sum().backward()
     assert _rel(yb2.grad, ya2.grad) <= 1e-2
+
+
+# Declared bars of the TF32 tier against the FP32 ORACLE, on the reference's own
+# default-init weights (no scaling) at the BASELINE configurations.  Norms: max = max|a-b| / max|b| over one tensor;
+# flat = the same over the concatenation of ALL parameter gradients (what an optimiser step sees); l2 = relative L2.
+TF32_BARS = {"sol_max": 1e-4, "gy0_l2": 1e-3, "gy0_max": 1e-2, "dtheta_flat_small": 1e-2, "dtheta_flat_large": 1e-2,
+             "dtheta_tensor_l2": 5e-2}
+
+
+@pytest.mark.parametrize("tag,B,method,steps", [("U", 128, "euler", 1), ("U", 128, "rk4", 1), ("C", 256, "euler", 1),
+                                                ("P", 256, "euler", 1), ("P", 256, "rk4", 20), ("U", 32768, "euler", 1),
+                                                ("U", 8192, "rk4", 20)])
+def test_tf32_tier_declared_bars(tag, B, method, steps):
+    import nlbac_b200
+    ref, ours = _models(tag, scale=1.0)
+    y0 = _y0(tag, B)
+    t = 0.02 * torch.arange(steps + 1, dtype=torch.float32)
+    ya = y0.clone().requires_grad_(True)
+    sa = oracle_odeint(ref, ya, t, method=method)
+    sa.pow(2).sum().backward()
+    yb = y0.cuda().requires_grad_(True)
+    ours.zero_grad()
+    sb = nlbac_b200.odeint(ours, yb, t, method=method, precision="tf32")
+    sb.pow(2).sum().backward()
+    l2 = lambda a, b: ((a.detach().double().cpu() - b.detach().double()).norm() / b.detach().double().norm()).item()  # noqa: E731
+    got = torch.cat([p.grad.reshape(-1) for p in ours.parameters()])
+    want = torch.cat([p.grad.reshape(-1) for p in ref.parameters()])
+    m = {"sol_max": _rel(sb, sa), "gy0_l2": l2(yb.grad, ya.grad), "gy0_max": _rel(yb.grad, ya.grad),
+         "dtheta_flat": _rel(got, want),
+         "dtheta_tensor_l2": max(l2(p.grad, q.grad) for p, q in zip(ours.parameters(), ref.parameters()))}
+    print("tf32 bars", tag, B, method, steps, {k: "%.1e" % v for k, v in m.items()})
+    assert m["sol_max"] <= TF32_BARS["sol_max"], m
+    assert m["gy0_l2"] <= TF32_BARS["gy0_l2"] and m["gy0_max"] <= TF32_BARS["gy0_max"], m
+    assert m["dtheta_flat"] <= TF32_BARS["dtheta_flat_large" if B >= 4096 else "dtheta_flat_small"], m
+    assert m["dtheta_tensor_l2"] <= TF32_BARS["dtheta_tensor_l2"], m

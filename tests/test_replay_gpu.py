@@ -12,7 +12,7 @@ from test_oracle_replay import replay_sequence
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("tag", ["U", "C"])
+@pytest.mark.parametrize("tag", ["U", "C", "BP", "BPt", "Pbatch"])
 def test_replay_matches_reference_golden(tag, golden_dir):
     import nlbac_b200
     g = torch.load(os.path.join(golden_dir, "replay.pt"), weights_only=False)[tag]
@@ -20,7 +20,7 @@ def test_replay_matches_reference_golden(tag, golden_dir):
     got = replay_sequence(mem, g)
     assert mem.position == g["position"] and len(mem) == g["len"]
     for s, w in zip(got, g["samples"]):
-        assert len(s) == 10
+        assert len(s) == (11 if g.get("barrier") else 10)
         for a, b in zip(s, w):
             if b is None:
                 assert a is None
