@@ -61,6 +61,9 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--log2m", type=int, default=20, help="log2 of trajectories per GPU")
     ap.add_argument("--env", default="U", choices=["U", "P"])
+    ap.add_argument("--scaling", default="weak", choices=["weak", "strong"],
+                    help="weak: 2^log2m trajectories PER GPU; strong: 2^log2m-total trajectories sharded M/world per GPU")
+    ap.add_argument("--log2m-total", type=int, default=23, help="log2 of the total trajectories under --scaling strong")
     ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32", "3xtf32"],
                     help="tf32: tcgen05 kind::tf32 forward + reverse sweep, dW in bf16 (the 1e-2 tier of north_star); "
                          "fp32: exact FP32 FMA path (1e-5 tier); 3xtf32: split-TF32 forward (fp32-class) + FP32 backward")
@@ -241,7 +244,13 @@ def run_ours(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
-    env, M = args.env, 1 << args.log2m
+    env = args.env
+    if args.scaling == "strong":
+        lo_, hi_ = nlbac_b200.parallel.shard_rows(1 << args.log2m_total, world, rank)
+        M = hi_ - lo_
+    else:
+        M = 1 << args.log2m
+    comm = nlbac_b200.parallel.Comm(world, rank) if world > 1 else None      # the C ABI's NCCL communicator
     n_s = 3 if env == "U" else 6
     torch.manual_seed(0)     # same nn.Linear construction order as the reference class -> same default init
     model = nlbac_b200.NeuralODEModel(3, 3, 6) if env == "U" else nlbac_b200.NeuralODEModel(6, 6, 12)
@@ -260,11 +269,10 @@ def run_ours(args):
         if timers is not None:
             timers[1].record()
         grads = torch.autograd.grad(loss, params)
-        flat = grads[0]._base if grads[0]._base is not None else torch.cat([g.reshape(-1) for g in grads])
         if timers is not None:
             timers[2].record()
-        if world > 1:
-            dist.all_reduce(flat)
+        # ONE flat d-theta buffer (the backward kernel writes all gradients into one allocation), ONE all-reduce
+        flat = nlbac_b200.parallel.allreduce_grad_tensors(grads, comm)
         return loss, flat
 
     def barrier():
@@ -324,7 +332,7 @@ def run_ours(args):
     ms_total, e2e_ms, fp32_ms = tms.tolist()
     peak32 = fp32_peak_tflops(nlbac_b200) if rank == 0 else 0.0
     if rank == 0:
-        traj_steps = float(world) * M * N_STEPS
+        traj_steps = float((1 << args.log2m_total) if args.scaling == "strong" else world * M) * N_STEPS
         ms_step = ms_total / args.steps
         value = traj_steps / (ms_step * 1e-3)
         K = args.steps
@@ -405,11 +413,13 @@ def run_ours(args):
         line = {
             "metric": "neural-ODE trajectory-steps/sec (fwd+bwd)", "value": value, "unit": "trajectory-steps/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": {"fp32": "f32", "tf32": "tf32", "3xtf32": "f32 (3xtf32 fwd)"}[args.precision], "data": "synthetic",
-            "config": {"workload": "config5: 2^%d %s-shaped trajectories per GPU x 20 rk4(3/8) steps, fwd+bwd, "
+            "config": {"workload": "config5: %s %s-shaped trajectories x 20 rk4(3/8) steps, fwd+bwd, "
                                    "t=0.02*arange(21), cotangent ones on final state, d-theta all-reduced" % (
-                                       args.log2m, "Unicycle" if env == "U" else "PVTOL"),
+                                       ("2^%d in total, sharded M/world per GPU" % args.log2m_total)
+                                       if args.scaling == "strong" else ("2^%d per GPU" % args.log2m),
+                                       "Unicycle" if env == "U" else "PVTOL"),
                        "trajectories_per_gpu": M, "solver_steps": N_STEPS, "method": "rk4", "precision": {"fp32": "fwd fp32 / bwd fp32", "tf32": "fwd tf32 / bwd tf32 (dW bf16 operands, fp32 accumulate)", "3xtf32": "fwd 3xtf32 / bwd fp32"}[args.precision],
                        "l2": "per-step working set (stage checkpoints + outputs, %.1f GB) exceeds the 126 MB L2; no explicit flush" % (
                            M * (N_STEPS * 4 * n_s + (N_STEPS + 1) * (n_s + 2) * 2) * 4 / 1e9)},
@@ -426,6 +436,8 @@ def run_ours(args):
             "clocks": sampler.summary(),
         }
         os.write(json_fd, (json.dumps(line) + "\n").encode())
+    if comm is not None:
+        comm.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -579,6 +591,47 @@ def run_configs(args):
                 "ours_cuda_graph_us": gq, "torch_eager_gpu_us": e, "torch_cpu_us": c, "speedup_vs_eager_gpu": e / o,
                 "speedup_vs_cpu": c / o, "graph_speedup_vs_eager_gpu": e / gq}
     rows += [train_case(128), train_case(32768)]
+
+    # one full update_parameters (U sac_cbf_clf.py:181-319) at the reference's batch size: GraphedUpdate replay vs the
+    # restated update run eagerly by PyTorch on the GPU and on the host (inputs: the committed golden trace's batches)
+    def update_case():
+        import numpy as np
+        from oracle.update import UnicycleAgent
+        g = torch.load(os.path.join(ROOT, "tests", "golden", "update_U.pt"), weights_only=False)
+        k, B = g["consts"], g["B"]
+        C = nlbac_b200.constraints
+        sp = type("S", (), {"low": np.array(k["action_low"], dtype="float32"), "high": np.array(k["action_high"], dtype="float32")})
+        nets = {"critic": nlbac_b200.QNetwork(7, 2, 256), "critic_target": nlbac_b200.QNetwork(7, 2, 256),
+                "lya": nlbac_b200.LyaNetwork(2, 256), "lya_t": nlbac_b200.LyaNetwork(2, 256),
+                "policy": nlbac_b200.GaussianPolicy(7, 2, 256, sp), "backup": nlbac_b200.GaussianPolicy(7, 2, 256, sp),
+                "node": nlbac_b200.NeuralODEModel(3, 3, 6)}
+        for n, key in (("critic", "critic"), ("critic_target", "critic"), ("lya", "lyapunovNet"), ("lya_t", "lyapunovNet"),
+                       ("policy", "policy"), ("backup", "backup_policy"), ("node", "neural_ode_model")):
+            nets[n].load_state_dict(g["init"][key])
+            nets[n].to(dev)
+        kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_locations=k["hazards"], hazards_radius=k["hazards_radius"],
+                  l_p=k["l_p"], batch_size=B)
+        node, lya = nets["node"], nets["lya"]
+        env = type("E", (), {"dynamics_mode": "Unicycle"})
+        upd = nlbac_b200.GraphedUpdate(
+            nets["critic"], nets["critic_target"], lya, nets["lya_t"], nets["policy"], nets["backup"], node,
+            nlbac_b200.DynamicsModel(env), B,
+            primary=lambda s_, pi, V: C.unicycle_required_matrix(node, lya, s_, pi, V, **kw),
+            backup=lambda s_, pi: C.unicycle_required_matrix(node, None, s_, pi, None, **kw),
+            num_constraints=8, obs_dim=7, act_dim=2, center_pos_num=2)
+        batch = tuple(None if x is None else x.to(dev) for x in g["batches"][0])
+        upd.step(batch)                                                  # capture
+        o = lat_gpu(lambda: upd.step(batch))
+        o_replay = lat_gpu(lambda: upd.graph.replay())
+        ag_gpu, ag_cpu = UnicycleAgent(k, B, g["init"], "cuda"), UnicycleAgent(k, B, g["init"], "cpu")
+        e = lat_gpu(lambda: ag_gpu.update_parameters(batch, 9), iters=20, warm=3)
+        c = lat_cpu(lambda: ag_cpu.update_parameters(g["batches"][0], 9))
+        return {"case": "config1 full update_parameters (critic + Lyapunov + actor + backup actor + alpha + Polyak)",
+                "batch": B, "ours_us": o, "ours_graph_replay_only_us": o_replay, "torch_eager_gpu_us": e, "torch_cpu_us": c,
+                "speedup_vs_eager_gpu": e / o, "speedup_vs_cpu": c / o,
+                "note": "ours = load the minibatch into the static buffers + ONE CUDA-graph replay, no host sync; eager = "
+                        "the restated reference update (6 .item() + float() read-backs, numpy get_state round trip)"}
+    rows += [update_case()]
 
     # replay sampling: the reference's list-of-tuples memory + np.stack + H2D vs the device ring
     from oracle.replay import ReplayMemory as RefReplay

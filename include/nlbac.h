@@ -306,6 +306,19 @@ int nlbac_env_pvtol_step(double* state, int32_t* episode_step, const double* act
                          double* reward, double* constraint, double* lya_pre_term, uint8_t* done, uint8_t* goal_met,
                          int32_t* num_safety_violation, double* safety_cost, void* stream);
 
+/* Data-parallel plumbing (the reference's only analogue is the unused mpi4py scaffold,
+ * utils/mpi_pytorch.py:20-34).  One NCCL communicator per process (one process per GPU); nlbac_allreduce_grads is ONE
+ * in-place fp32 SUM all-reduce of a flat device buffer (the per-optimiser gradient buffer the backward kernels write, or
+ * the [m] constraint sums), enqueued on `stream` with no host synchronisation.  nlbac_comm_unique_id fills 128 bytes on
+ * rank 0 that the caller broadcasts to the other ranks (any transport) before nlbac_comm_init, with the rank's GPU
+ * current.  Returns 0, < 0 for bad arguments, 1000 + ncclResult_t for NCCL errors (text via nlbac_last_error).  NCCL is
+ * resolved at run time (dlopen of libnccl.so.2); the handle is the only state the library keeps. */
+typedef struct nlbac_comm nlbac_comm;
+int nlbac_comm_unique_id(void* id128);
+int nlbac_comm_init(int world, int rank, const void* id128, nlbac_comm** comm);
+int nlbac_allreduce_grads(nlbac_comm* comm, float* flat, size_t n, void* stream);
+int nlbac_comm_destroy(nlbac_comm* comm);
+
 /* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 tile.
  * mode 0 (kind::tf32, both operands K-major):   D[t][j] = sum_k X[t][k] Y[j][k],  X [128,104], Y [104,104];
  * mode 1 (kind::f16 on bf16 images, MN-major):  D[j][k] = sum_t X[t][j] Y[t][k],  X, Y [128,104].

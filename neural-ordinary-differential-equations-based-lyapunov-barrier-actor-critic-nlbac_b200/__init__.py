@@ -11,6 +11,7 @@ from .model import NeuralODEModel, train_step
 from .mlp import QNetwork, LyaNetwork, BarrierNetwork, GaussianPolicy, weights_init_
 from .tail import DynamicsModel, FusedAdam, soft_update, hard_update, constraint_sums, lookahead, make_constraint_desc
 from . import constraints
+from . import parallel
 from .replay import ReplayMemory
 from .graphs import GraphedTrainStep
 from .agent import GraphedUpdate
@@ -18,4 +19,4 @@ from .envs import VecUnicycleEnv, VecSimulatedCarsEnv, VecPvtolEnv
 
 __all__ = ["odeint", "NeuralODEModel", "train_step", "build", "describe", "QNetwork", "LyaNetwork", "BarrierNetwork",
            "GaussianPolicy", "weights_init_", "DynamicsModel", "FusedAdam", "soft_update", "hard_update",
-           "constraint_sums", "lookahead", "make_constraint_desc", "constraints", "ReplayMemory", "GraphedTrainStep", "GraphedUpdate", "VecUnicycleEnv", "VecSimulatedCarsEnv", "VecPvtolEnv"]
+           "constraint_sums", "lookahead", "make_constraint_desc", "constraints", "parallel", "ReplayMemory", "GraphedTrainStep", "GraphedUpdate", "VecUnicycleEnv", "VecSimulatedCarsEnv", "VecPvtolEnv"]

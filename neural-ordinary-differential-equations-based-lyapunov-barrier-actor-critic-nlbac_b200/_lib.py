@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 LIB_PATH = os.path.join(HERE, "libnlbac_b200.so")
-SOURCES = ["node_abi.cu", "mlp_abi.cu", "tail_abi.cu", "tc_abi.cu", "env_abi.cu"]
+SOURCES = ["node_abi.cu", "mlp_abi.cu", "tail_abi.cu", "tc_abi.cu", "env_abi.cu", "comm_abi.cu"]
 NVCC_FLAGS = ["-std=c++20", "-O3", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo",
               "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC"]
 
@@ -76,7 +76,7 @@ def build(force=False, verbose=False):
             print(out.decode())
         if p.returncode != 0:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
-    cmd = [nvcc, "-shared", "-o", LIB_PATH] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
+    cmd = [nvcc, "-shared", "-o", LIB_PATH] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-ldl"]
     subprocess.check_call(cmd)
     return LIB_PATH
 
@@ -142,6 +142,10 @@ def _declare(lib):
     lib.nlbac_env_cars_step.argtypes = [vp, vp, vp, vp, i64] + [vp] * 10
     lib.nlbac_env_pvtol_reset.argtypes = [vp, vp, vp, i64, vp, vp]
     lib.nlbac_env_pvtol_step.argtypes = [vp, vp, vp, i64] + [vp] * 9
+    lib.nlbac_comm_unique_id.argtypes = [vp]
+    lib.nlbac_comm_init.argtypes = [c.c_int, c.c_int, vp, c.POINTER(vp)]
+    lib.nlbac_allreduce_grads.argtypes = [vp, vp, c.c_size_t, vp]
+    lib.nlbac_comm_destroy.argtypes = [vp]
     lib.nlbac_umma_selftest.argtypes = [c.c_int, vp, vp, vp, vp]
     lib.nlbac_kernel_timing.argtypes = [c.c_int]
     lib.nlbac_kernel_timing_read.argtypes = [c.POINTER(c.c_double), c.POINTER(c.c_int)]

@@ -1,7 +1,9 @@
-"""World-size-2 gloo test of the trajectory sharding used by bench.py --gpus N: contiguous row
-blocks per rank, replicated weights, ONE all-reduce (sum) of the flat d-theta buffer.  Runs on CPU with the oracle
-standing in for the per-rank solve — what is under test is the host-side split / reduce logic, which must
-reproduce the single-rank gradient."""
+"""World-size-2 gloo tests of the PACKAGE's data-parallel host logic (nlbac_b200/parallel.py): the row
+sharding rule, the one-flat-buffer gradient all-reduce, and the differentiable all-reduce of the [m] constraint sums.
+On CPU a small torch network stands in for the fused kernels (they need a GPU); what is under test is that a
+mean-type loss scaled by shard_weight plus a loss that is NON-LINEAR in all-reduced row sums (the shape of the
+CBF/CLF augmented Lagrangian, U sac_cbf_clf.py:493-528) reproduces the single-rank gradient after allreduce_grads.
+The same identity on the CUDA path with the C ABI's NCCL communicator: tests/test_dp_gpu.py."""
 import os
 import sys
 
@@ -10,37 +12,46 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+N_ROWS = 37
 
 
-def shard_rows(n, world, rank):
-    """Contiguous block of rows for `rank` (same rule as bench.py: equal blocks, remainder to the last ranks)."""
-    base, rem = divmod(n, world)
-    start = rank * base + max(0, rank - (world - rem))
-    return start, start + base + (1 if rank >= world - rem else 0)
+def _net():
+    torch.manual_seed(0)
+    return torch.nn.Sequential(torch.nn.Linear(5, 16), torch.nn.ReLU(), torch.nn.Linear(16, 3))
+
+
+def _loss(net, x, rows_global, reduce_sum, weight):
+    """mean-type term + a term non-linear in batch sums of where(> 0)-filtered rows."""
+    out = net(x)
+    mean_term = out.pow(2).mean() * weight
+    rows = torch.where(out > 0, out, torch.zeros_like(out)).sum(0) / rows_global      # [m] local sums / global batch
+    s = reduce_sum(rows)
+    ratio = float(s[:-1].mean().abs() / s[-1].abs().clamp_min(1e-6))                  # detached, like the reference
+    return mean_term + (0.3 * s + 2.0 * s * s).sum() + ratio * s[-1]
 
 
 def _worker(rank, world, port, q):
     sys.path.insert(0, ROOT)
-    from oracle import nlbac_ref
-    from oracle.torchdiffeq_restated import odeint
+    from nlbac_b200 import parallel
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    torch.manual_seed(0)
-    model = nlbac_ref.AffineNODE(3, 3, 6)
-    y0 = torch.randn(37, 5, generator=torch.Generator().manual_seed(1))
-    t = 0.02 * torch.arange(4, dtype=torch.float32)
-    lo, hi = shard_rows(37, world, rank)
-    sol = odeint(model, y0[lo:hi], t, method="rk4")
-    grads = torch.autograd.grad(sol[-1][:, :3].sum(), list(model.parameters()))
-    flat = torch.cat([g.reshape(-1) for g in grads])
-    dist.all_reduce(flat)                     # the one collective of the path
+    net = _net()
+    x = torch.randn(N_ROWS, 5, generator=torch.Generator().manual_seed(1))
+    lo, hi = parallel.shard_rows(N_ROWS, world, rank)
+    loss = _loss(net, x[lo:hi], N_ROWS, parallel.all_reduce_sum, parallel.shard_weight(hi - lo, N_ROWS))
+    loss.backward()
+    flat = parallel.allreduce_grads(net)                       # the one collective per optimiser
+    got = torch.cat([p.grad.reshape(-1) for p in net.parameters()])
+    assert torch.equal(flat, got)
     if rank == 0:
-        q.put(flat.tolist())              # plain floats: a tensor would travel as an fd the exiting worker may close
+        q.put(got.tolist())               # plain floats: a tensor would travel as an fd the exiting worker may close
     dist.barrier()
     dist.destroy_process_group()
 
 
 def test_shard_rows_cover_and_balance():
+    sys.path.insert(0, ROOT)
+    from nlbac_b200.parallel import shard_rows
     for n in (1, 2, 37, 1 << 20):
         for w in (1, 2, 4, 8):
             spans = [shard_rows(n, w, r) for r in range(w)]
@@ -51,9 +62,6 @@ def test_shard_rows_cover_and_balance():
 
 
 def test_two_rank_allreduce_matches_single_rank_gradient():
-    sys.path.insert(0, ROOT)
-    from oracle import nlbac_ref
-    from oracle.torchdiffeq_restated import odeint
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29500 + os.getpid() % 2000
@@ -64,9 +72,8 @@ def test_two_rank_allreduce_matches_single_rank_gradient():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
-    torch.manual_seed(0)
-    model = nlbac_ref.AffineNODE(3, 3, 6)
-    y0 = torch.randn(37, 5, generator=torch.Generator().manual_seed(1))
-    sol = odeint(model, y0, 0.02 * torch.arange(4, dtype=torch.float32), method="rk4")
-    want = torch.cat([g.reshape(-1) for g in torch.autograd.grad(sol[-1][:, :3].sum(), list(model.parameters()))])
+    net = _net()
+    x = torch.randn(N_ROWS, 5, generator=torch.Generator().manual_seed(1))
+    _loss(net, x, N_ROWS, lambda r: r, 1.0).backward()
+    want = torch.cat([p.grad.reshape(-1) for p in net.parameters()])
     assert ((got - want).abs().max() / want.abs().max()) < 1e-5
