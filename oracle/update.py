@@ -33,6 +33,8 @@ class UnicycleAgent:
         for n in ("critic", "critic_target", "lyapunovNet", "lyapunovNet_target", "policy", "backup_policy",
                   "neural_ode_model"):
             getattr(self, n).to(dev)
+        for pol in (self.policy, self.backup_policy):       # plain tensor attributes (the reference overrides .to(), U model.py:130-133)
+            pol.action_scale, pol.action_bias = pol.action_scale.to(dev), pol.action_bias.to(dev)
         A = torch.optim.Adam
         self.critic_optim = A(self.critic.parameters(), lr=k["critic_lr"])            # :48
         self.lyaNet_optim = A(self.lyapunovNet.parameters(), lr=k["critic_lr"])       # :51
