@@ -592,6 +592,36 @@ def run_configs(args):
                 "speedup_vs_cpu": c / o, "graph_speedup_vs_eager_gpu": e / gq}
     rows += [train_case(128), train_case(32768)]
 
+    # BASELINE config 4: Quadrotor-shaped (8 -> 64 x3 -> 6, hidden 64 assumed) horizon-10 chained rollout with the policy
+    # re-sampled between steps (eps[9, 256, 2] injected), forward + backward to the first action and the NODE weights
+    def rollout_case():
+        from oracle import constraints as OC
+        torch.manual_seed(0)
+        B, H = 256, 10
+        ref_node, ref_pol = nlbac_ref.BlackBoxNODE(8, 6), nlbac_ref.GaussianPolicy(6, 2, 256)
+        node, pol = nlbac_b200.NeuralODEModel(8, 6), nlbac_b200.GaussianPolicy(6, 2, 256)
+        node.load_state_dict(ref_node.state_dict()); pol.load_state_dict(ref_pol.state_dict())
+        node, pol = node.to(dev), pol.to(dev)
+        gn, gp = nlbac_ref.BlackBoxNODE(8, 6).to(dev), nlbac_ref.GaussianPolicy(6, 2, 256).to(dev)
+        gn.load_state_dict(ref_node.state_dict()); gp.load_state_dict(ref_pol.state_dict())
+        gp.action_scale, gp.action_bias = gp.action_scale.to(dev), gp.action_bias.to(dev)
+        x0, eps, u0 = torch.randn(B, 6), torch.randn(H - 1, B, 2), torch.randn(B, 2)
+
+        def run(fn, n, p_, x, e, u):
+            def f():
+                uu = u.detach().requires_grad_(True)
+                out = fn(n, p_, x, uu, H, dt=DT, eps=e)
+                torch.autograd.grad(out.sum(), [uu] + list(n.parameters()))
+            return f
+        o = lat_gpu(run(nlbac_b200.constraints.chained_rollout, node, pol, x0.to(dev), eps.to(dev), u0.to(dev)))
+        e = lat_gpu(run(OC.chained_rollout, gn, gp, x0.to(dev), eps.to(dev), u0.to(dev)), iters=20, warm=3)
+        c = lat_cpu(run(OC.chained_rollout, ref_node, ref_pol, x0, eps, u0))
+        return {"case": "config4 Quadrotor-shaped rollout, horizon 10, policy re-sampled between steps (fwd+bwd)",
+                "batch": B, "method": "euler", "solver_steps": H, "ours_us": o, "torch_eager_gpu_us": e, "torch_cpu_us": c,
+                "speedup_vs_eager_gpu": e / o, "speedup_vs_cpu": c / o,
+                "note": "hidden width 64 ASSUMED (safe-control-gym submodule missing from the reference)"}
+    rows += [rollout_case()]
+
     # one full update_parameters (U sac_cbf_clf.py:181-319) at the reference's batch size: GraphedUpdate replay vs the
     # restated update run eagerly by PyTorch on the GPU and on the host (inputs: the committed golden trace's batches)
     def update_case():

@@ -268,3 +268,24 @@ def pvtol_required_matrix(neural_ode_model, lyapunovNet, policy, dynamics_model,
         return constraint_sums(desc, state_batch, s1, s2, z, z, e=s3)[:-1]
     lyapunov_value_next = lyapunovNet(next_obs)
     return constraint_sums(desc, state_batch, s1, s2, lyapunov_value.detach(), lyapunov_value_next, e=s3)
+
+
+def chained_rollout(neural_ode_model, policy, state_batch, action_batch, horizon, *, dt, eps=None, solver="euler",
+                    obs_fn=None, const_cols=None):
+    """Multi-step NODE rollout with the policy re-sampled on the DETACHED predicted observation between steps -- the
+    pattern of C sac_cbf_clf.py:437-459 (2 steps) and P :459-552 (3 steps) at an arbitrary horizon (BASELINE config 4:
+    the Quadrotor-shaped model, horizon 10, ``eps[horizon - 1, B, n_u]`` injected; README.md:190-192).
+    One fused solve per step; gradients flow through the chain of predicted states to ``action_batch`` and the NODE
+    parameters, not through the re-sampled actions.  ``obs_fn`` maps a predicted state to the policy's input (identity
+    by default); ``const_cols`` are extra constant columns of y0 after the action (the cars' time feature), one
+    tensor per step.  Returns the predicted states ``[horizon, B, n_s]``."""
+    n_s = state_batch.shape[1]
+    x, u, out = state_batch, action_batch, []
+    for k in range(horizon):
+        cols = (x, u) if const_cols is None else (x, u, const_cols[k])
+        x = odeint(neural_ode_model, torch.cat(cols, dim=-1), [0.0, dt], method=solver, atol=1e-7, rtol=1e-5)[-1][:, :n_s]
+        out.append(x)
+        if k + 1 < horizon:
+            obs = x.detach() if obs_fn is None else obs_fn(x.detach())
+            u = policy.sample(obs, None if eps is None else eps[k])[0].detach()
+    return torch.stack(out)

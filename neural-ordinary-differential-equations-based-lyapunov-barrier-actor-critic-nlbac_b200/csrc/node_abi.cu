@@ -24,15 +24,30 @@ int cuda_fail(cudaError_t e, const char* what) {
   return (int)e;
 }
 
-static int sm_count() {
-  static int n = 0;
-  if (n == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-  }
-  return n;
+// Per-device caches: cudaFuncSetAttribute and the SM count belong to a DEVICE, and one process may drive several.
+constexpr int MAX_DEVICES = 64;
+static int current_device() {
+  int dev = 0;
+  cudaGetDevice(&dev);
+  return (dev >= 0 && dev < MAX_DEVICES) ? dev : 0;
 }
+static int sm_count() {
+  static int n[MAX_DEVICES] = {};
+  const int dev = current_device();
+  if (n[dev] == 0) {
+    if (cudaDeviceGetAttribute(&n[dev], cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n[dev] <= 0) n[dev] = 148;
+  }
+  return n[dev];
+}
+struct DeviceOnce {          // `if (once.need()) { set attributes }` -- true the first time on each device
+  bool done[MAX_DEVICES] = {};
+  bool need() {
+    const int dev = current_device();
+    if (done[dev]) return false;
+    done[dev] = true;
+    return true;
+  }
+};
 
 // Opt-in per-kernel timing (nlbac_kernel_timing): CUDA events recorded on the launching stream around each launch
 // of the NODE kernels, summed per slot when read.  Slots: 0 forward solve, 1 reverse sweep, 2 dW GEMM, 3 fold.
@@ -142,11 +157,10 @@ static int upload_schedule(const Schedule& s, void* ws, cudaStream_t st, const f
 template <class C, int T>
 static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
   using G = FwdGeom<C, T>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
     NLBAC_CUDA(cudaFuncSetAttribute(node_fwd_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)G::SMEM_BYTES));
-    attr_done = true;
   }
   const long long n_tiles = (a.B + T - 1) / T;
   const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());
@@ -159,11 +173,10 @@ static int launch_fwd(const FwdArgs& a, cudaStream_t st) {
 template <class C, bool SPLIT>
 static int launch_tc_fwd(const FwdArgs& a, cudaStream_t st) {
   using G = TcFwdGeom<C, SPLIT>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
     NLBAC_CUDA(cudaFuncSetAttribute(node_tc_fwd_kernel<C, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)G::SMEM_BYTES));
-    attr_done = true;
   }
   const long long n_tiles = (a.B + 127) / 128;
   const long long n_pairs = (n_tiles + G::G - 1) / G::G;
@@ -195,11 +208,10 @@ template <class C>
 static int run_tc_bwd(const BwdArgs& a, unsigned char* images, float* rep, cudaStream_t st) {
   using G = TcBwdGeom<C>;
   using DG = DwGeom<C>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
     NLBAC_CUDA(cudaFuncSetAttribute(node_tc_bwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM_BYTES));
     NLBAC_CUDA(cudaFuncSetAttribute(node_tc_dw_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DG::SMEM_BYTES));
-    attr_done = true;
   }
   const long long n_tiles = (a.B + 127) / 128;
   const long long n_se = (long long)a.n_steps * method_stages(a.method);
@@ -252,11 +264,10 @@ static int launch_pack_tc(const float* const* params, float* packed, cudaStream_
 template <class C, int TB>
 static int launch_bwd(const BwdArgs& a, cudaStream_t st) {
   using G = BwdGeom<C, TB>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
     NLBAC_CUDA(cudaFuncSetAttribute(node_bwd_kernel<C, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)G::SMEM_BYTES));
-    attr_done = true;
   }
   const long long n_tiles = (a.B + TB - 1) / TB;
   const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());
@@ -269,11 +280,10 @@ static int launch_bwd(const BwdArgs& a, cudaStream_t st) {
 template <class C, int T>
 static int launch_dp5(const Dp5Args& a, cudaStream_t st) {
   using G = FwdGeom<C, T>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
     NLBAC_CUDA(cudaFuncSetAttribute(dopri5_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)G::SMEM_BYTES));
-    attr_done = true;
   }
   const long long n_tiles = (a.B + T - 1) / T;
   const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());
@@ -292,11 +302,10 @@ static int launch_dp5_any(const Dp5Args& a, cudaStream_t st) {
 template <class C, int TB>
 static int launch_dp5_bwd(const Dp5BwdArgs& a, cudaStream_t st) {
   using G = BwdGeom<C, TB>;
-  static bool attr_done = false;
-  if (!attr_done) {
+  static DeviceOnce attr_once;
+  if (attr_once.need()) {
     NLBAC_CUDA(cudaFuncSetAttribute(dopri5_bwd_kernel<C, TB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     (int)G::SMEM_BYTES));
-    attr_done = true;
   }
   const long long n_tiles = (a.B + TB - 1) / TB;
   const int grid = (int)(n_tiles < sm_count() ? n_tiles : sm_count());

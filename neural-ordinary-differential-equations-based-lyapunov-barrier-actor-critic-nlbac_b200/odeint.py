@@ -49,7 +49,18 @@ def describe(func, D):
             raise TypeError("nlbac_b200.odeint: black-box NODE input width %d != y0 width %d" % (f[0].in_features, D))
         n_u = getattr(func, "n_u", None)
         if n_u is None:
-            n_u = 1 if D - n_s == 2 else D - n_s   # cars: [x(10), u(1), t_k(1)]
+            # The trailing D - n_s columns are constants of the flow, split into actions and extra constants (the cars'
+            # time feature).  No guessing: take the split the library has a compiled instance for -- all of them
+            # actions first (Quadrotor shape 8 -> 6: n_u = 2), then one action + constants (cars 12 -> 10: u, t_k).
+            L = _lib.lib()
+            for cand in (D - n_s, 1):
+                if 1 <= cand <= D - n_s:
+                    trial = _lib.NodeDesc(1, n_s, cand, D - n_s - cand, hidden, len(f), 0)
+                    if L.nlbac_node_supported(ctypes.byref(trial), 0) == 0:
+                        n_u = cand
+                        break
+            if n_u is None:
+                n_u = D - n_s
         desc = _lib.NodeDesc(1, n_s, n_u, D - n_s - n_u, hidden, len(f), 0)
         layers = f
     else:

@@ -249,3 +249,17 @@ def augmented_lagrangian(req, st, updates):
         loss = loss + float(st.lambda_values[i]) * c + rho / 2.0 * c * c
     c = req[-1] - st.cost_limit
     return loss + float(st.lambda_values[-1]) * ratio * c + ratio * ratio * rho / 2.0 * c * c
+
+
+def chained_rollout(node, policy, state, action, horizon, *, dt, eps=None, solver="euler", obs_fn=None):
+    """Restatement of the chained-prediction pattern of C sac_cbf_clf.py:437-459 / P :459-552 at horizon H (config 4):
+    predict, re-sample the policy on the detached predicted observation, predict again."""
+    n_s = state.shape[1]
+    x, u, out = state, action, []
+    for k in range(horizon):
+        x = odeint(node, torch.cat((x, u), -1), torch.tensor([0.0, dt]), method=solver, atol=1e-7, rtol=1e-5)[-1][:, :n_s]
+        out.append(x)
+        if k + 1 < horizon:
+            obs = x.detach() if obs_fn is None else obs_fn(x.detach())
+            u = policy.sample(obs, None if eps is None else eps[k])[0].detach()
+    return torch.stack(out)

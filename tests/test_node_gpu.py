@@ -35,7 +35,7 @@ def _models(tag, seed=0, scale=1.5):
         ours = nlbac_b200.NeuralODEModel(12, 10)
     else:  # quadrotor-shaped (assumed hidden 64), black-box 8 -> 6 with two action columns
         ref = nlbac_ref.BlackBoxNODE(8, 6)
-        ours = nlbac_b200.NeuralODEModel(8, 6, n_u=2)
+        ours = nlbac_b200.NeuralODEModel(8, 6)      # n_u = 2 found by describe(): no heuristic, no keyword needed
     # make the thin layers and biases matter
     with torch.no_grad():
         for p in ref.parameters():

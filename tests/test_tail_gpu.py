@@ -396,3 +396,31 @@ def test_device_side_lagrangian_and_graphed_actor_update(golden_dir):
         assert _rel(loss_g, want) <= 1e-5
     for p, w in zip(actor.parameters(), ref_actor.parameters()):
         assert _rel(p, w) <= 1e-4
+
+
+def test_config4_quadrotor_shaped_horizon10_rollout():
+    """BASELINE config 4: Quadrotor-shaped black-box NODE (8 -> 64 -> 64 -> 64 -> 6, hidden 64 ASSUMED: the source is a
+    missing submodule), 10 chained Euler predictions with the policy re-sampled on the detached prediction between steps
+    (eps[9, 256, 2] injected), B = 256: states and gradients to the initial action / the NODE parameters vs the oracle.
+    Tolerance 5e-5: ten chained VJPs."""
+    import nlbac_b200
+    torch.manual_seed(0)
+    ref_node, ref_pol = nlbac_ref.BlackBoxNODE(8, 6), nlbac_ref.GaussianPolicy(6, 2, 256)
+    node, pol = nlbac_b200.NeuralODEModel(8, 6), nlbac_b200.GaussianPolicy(6, 2, 256)
+    node.load_state_dict(ref_node.state_dict()); pol.load_state_dict(ref_pol.state_dict())
+    node, pol = node.cuda(), pol.cuda()
+    g = torch.Generator().manual_seed(4)
+    B, H = 256, 10
+    x0, eps = torch.randn(B, 6, generator=g), torch.randn(H - 1, B, 2, generator=g)
+    cot = torch.randn(H, B, 6, generator=g)
+    ua = torch.randn(B, 2, generator=g).requires_grad_(True)
+    want = OC.chained_rollout(ref_node, ref_pol, x0, ua, H, dt=0.02, eps=eps)
+    (want * cot).sum().backward()
+    ub = ua.detach().clone().cuda().requires_grad_(True)
+    got = nlbac_b200.constraints.chained_rollout(node, pol, x0.cuda(), ub, H, dt=0.02, eps=eps.cuda())
+    (got * cot.cuda()).sum().backward()
+    assert got.shape == (H, B, 6)
+    assert _rel(got, want) <= 2e-5, _rel(got, want)
+    assert _rel(ub.grad, ua.grad) <= 5e-5, _rel(ub.grad, ua.grad)
+    for p, q in zip(node.parameters(), ref_node.parameters()):
+        assert _rel(p.grad, q.grad) <= 5e-5, _rel(p.grad, q.grad)
