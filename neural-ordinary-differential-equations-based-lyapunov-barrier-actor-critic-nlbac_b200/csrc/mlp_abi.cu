@@ -147,13 +147,31 @@ int nlbac_mlp_bwd(const nlbac_mlp_desc* desc, const float* const* params, const 
     g.p[0] = {a.d1, x, grad_params[0], H, NI};        // dW1 = d1^T x
     g.p[1] = {a.d2, h1, grad_params[2], H, H};        // dW2 = d2^T h1
     g.p[2] = {grad_out, h2, grad_params[4], NO, H};   // dW3 = g^T h2
-    mlp_atb_kernel<<<dim3((H + 31) / 32, (H + 31) / 32, 3), 256, 0, st>>>(g);
-    NLBAC_CUDA(cudaGetLastError());
     ColSumArgs c;
     c.B = B;
     c.p[0] = {a.d1, grad_params[1], H};
     c.p[1] = {a.d2, grad_params[3], H};
     c.p[2] = {grad_out, grad_params[5], NO};
+    if (B >= MLP_SPLIT_MIN_B) {   // split over the batch: chunks meet in pre-zeroed outputs (mlp_kernels.cuh)
+      const size_t sizes[6] = {(size_t)H * NI, (size_t)H, (size_t)H * H, (size_t)H, (size_t)NO * H, (size_t)NO};
+      for (int i = 0; i < 6; ++i) NLBAC_CUDA(cudaMemsetAsync(grad_params[i], 0, sizes[i] * 4, st));
+      int nsplit = (int)(B / 2048);
+      if (nsplit > 64) nsplit = 64;
+      if (nsplit < 1) nsplit = 1;
+      AtbSplitArgs gs;
+      gs.B = B; gs.nsplit = nsplit;
+      for (int i = 0; i < 3; ++i) gs.p[i] = g.p[i];
+      mlp_atb_split_kernel<<<dim3((H + 63) / 64, (H + 63) / 64, 3 * nsplit), 256, 0, st>>>(gs);
+      NLBAC_CUDA(cudaGetLastError());
+      ColSumSplitArgs cs;
+      cs.B = B; cs.nsplit = nsplit * 2;
+      for (int i = 0; i < 3; ++i) cs.p[i] = c.p[i];
+      mlp_colsum_split_kernel<<<dim3((H + 31) / 32, 3, cs.nsplit), 256, 0, st>>>(cs);
+      NLBAC_CUDA(cudaGetLastError());
+      return 0;
+    }
+    mlp_atb_kernel<<<dim3((H + 31) / 32, (H + 31) / 32, 3), 256, 0, st>>>(g);
+    NLBAC_CUDA(cudaGetLastError());
     mlp_colsum_kernel<<<dim3((H + 31) / 32, 3), 256, 0, st>>>(c);
     NLBAC_CUDA(cudaGetLastError());
   }

@@ -234,4 +234,80 @@ __global__ void __launch_bounds__(256) mlp_colsum_kernel(ColSumArgs a) {
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Large-batch forms of the two reductions above (B >= MLP_SPLIT_MIN_B: the vectorised environments of SURVEY 8f.4 feed
+// 10^4 .. 10^6-row batches).  The small-batch kernels loop over the WHOLE batch in 192 / 24 CTAs: at B = 2^20 ncu timed
+// them at 129 ms / 32 ms (profiles/r2_ncu_tail_kernels.txt).  Here the batch is cut into chunks (blockIdx.z / nsplit), a
+// CTA forms a 64 x 64 tile of C over its chunk with a 4 x 4 register tile per thread, and the chunks meet in a
+// pre-zeroed output through one atomicAdd per element per chunk (fp32 sums in a chunk-dependent order: 1e-6-level
+// differences from run to run, which is why the small-batch kernels, bit-reproducible, stay the default below it).
+// ------------------------------------------------------------------------------------------------
+constexpr long long MLP_SPLIT_MIN_B = 4096;
+struct AtbSplitArgs { AtbProb p[3]; long long B; int nsplit; };
+__global__ void __launch_bounds__(256) mlp_atb_split_kernel(AtbSplitArgs a) {
+  const AtbProb p = a.p[blockIdx.z / a.nsplit];
+  const int chunk = blockIdx.z % a.nsplit;
+  const int m0 = blockIdx.y * 64, n0 = blockIdx.x * 64;
+  if (m0 >= p.M || n0 >= p.N) return;
+  const long long per = ((a.B + a.nsplit - 1) / a.nsplit + 31) / 32 * 32;
+  const long long b_lo = (long long)chunk * per, b_hi = min(a.B, b_lo + per);
+  if (b_lo >= b_hi) return;
+  __shared__ __align__(16) float sA[32][64], sB[32][64];
+  const int tx = threadIdx.x % 16, ty = threadIdx.x / 16;      // thread tile: rows m0 + 4 ty .., columns n0 + 4 tx ..
+  const int lr = threadIdx.x / 8, lc = (threadIdx.x % 8) * 8;  // loader: batch row lr of the stage, 8 columns at lc
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  for (long long b0 = b_lo; b0 < b_hi; b0 += 32) {
+    const long long b = b0 + lr;
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      sA[lr][lc + c] = (b < b_hi && m0 + lc + c < p.M) ? p.A[b * p.M + m0 + lc + c] : 0.f;
+      sB[lr][lc + c] = (b < b_hi && n0 + lc + c < p.N) ? p.Bm[b * p.N + n0 + lc + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int bb = 0; bb < 32; ++bb) {
+      const float4 av = *reinterpret_cast<const float4*>(&sA[bb][4 * ty]);
+      const float4 bv = *reinterpret_cast<const float4*>(&sB[bb][4 * tx]);
+      const float am[4] = {av.x, av.y, av.z, av.w}, bn[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(am[i], bn[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int m = m0 + 4 * ty + i, n = n0 + 4 * tx + j;
+      if (m < p.M && n < p.N) atomicAdd(p.C + (size_t)m * p.N + n, acc[i][j]);
+    }
+}
+
+struct ColSumSplitArgs { ColSumProb p[3]; long long B; int nsplit; };
+__global__ void __launch_bounds__(256) mlp_colsum_split_kernel(ColSumSplitArgs a) {
+  const ColSumProb p = a.p[blockIdx.y];
+  const int c = blockIdx.x * 32 + threadIdx.x % 32;
+  const int part = threadIdx.x / 32;
+  const long long per = (a.B + a.nsplit - 1) / a.nsplit;
+  const long long b_lo = (long long)blockIdx.z * per, b_hi = min(a.B, b_lo + per);
+  __shared__ float red[8][33];
+  float s = 0.f;
+  if (c < p.N)
+    for (long long b = b_lo + part; b < b_hi; b += 8) s += p.D[b * p.N + c];
+  red[part][threadIdx.x % 32] = s;
+  __syncthreads();
+  if (part == 0 && c < p.N) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
+    atomicAdd(p.out + c, t);
+  }
+}
+
 }  // namespace nlbac

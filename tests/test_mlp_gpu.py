@@ -80,9 +80,11 @@ def test_mlps_match_reference_golden(tag, golden_dir):
     assert m2.shape == (obs.shape[0], n_u) and ls2.min() >= -20 and ls2.max() <= 2
 
 
-@pytest.mark.parametrize("B", [1, 7, 256, 1000])
+@pytest.mark.parametrize("B", [1, 7, 256, 1000, 4095, 4096, 70001])
 def test_mlp_ragged_batches_vs_oracle(B):
-    """Row tiles of 8: batches that are not a multiple of the tile, B=1, and more rows than one wave."""
+    """Row tiles of 8: batches that are not a multiple of the tile, B=1, and more rows than one wave; B >= 4096 takes
+    the split-over-the-batch parameter-gradient kernels (mlp_atb_split_kernel / mlp_colsum_split_kernel), with ragged
+    chunk ends."""
     import nlbac_b200
     torch.manual_seed(B)
     ref = nlbac_ref.LyaNetwork(11, 256)
@@ -101,9 +103,21 @@ def test_mlp_ragged_batches_vs_oracle(B):
     out = ours(xo)
     assert _rel(out, ref(x)) <= TOL
     (out * cot.cuda()).sum().backward()
-    assert _rel(xo.grad, xr.grad) <= TOL
-    for (k, p), (_, r) in zip(ours.named_parameters(), ref.named_parameters()):
-        assert _rel(p.grad, r.grad) <= TOL, k
+    if B < 4096:
+        assert _rel(xo.grad, xr.grad) <= TOL
+    else:   # kink rows (test_node_gpu._check): a pre-activation within fp32 round-off of zero flips that ROW's mask
+        d = (xo.grad.detach().cpu().double() - xr.grad.double()).abs().max(1).values
+        bad = int((d > TOL * xr.grad.abs().max().item()).sum())
+        assert bad <= max(2, B // 10000), ("kink rows", bad)
+    # fp64 tie-breaker (as in test_node_gpu._check): with tens of thousands of rows and a random cotangent the parameter
+    # gradients are cancelling sums, and the fp32 CPU oracle itself sits 1e-4 .. 1e-3 from fp64 (tools/diag_mlp_bigB.py:
+    # ours and the fp32 oracle are equally far from fp64) -- the kernel may not be further from fp64 than 2x the oracle is
+    r64 = nlbac_ref.LyaNetwork(11, 256).double()
+    r64.load_state_dict({k: v.double() for k, v in ref.state_dict().items()})
+    (r64(x.double()) * cot.double()).sum().backward()
+    for (k, p), (_, r), (_, d) in zip(ours.named_parameters(), ref.named_parameters(), r64.named_parameters()):
+        e32 = _rel(p.grad, r.grad)
+        assert e32 <= TOL or _rel(p.grad, d.grad) <= max(TOL, 2 * _rel(r.grad, d.grad)), (k, e32)
 
 
 def test_mlp_empty_batch_and_errors():
