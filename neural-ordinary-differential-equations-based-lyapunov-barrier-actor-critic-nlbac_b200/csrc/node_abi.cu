@@ -196,7 +196,7 @@ static int launch_tc_fwd(const FwdArgs& a, cudaStream_t st) {
 template <class C>
 static long long tc_bwd_chunk_tiles(long long n_tiles, long long n_se) {
   using G = TcBwdGeom<C>;
-  const long long per_pass = (long long)sm_count() * G::G;
+  const long long per_pass = (long long)sm_count() * G::G;     // (the TF32 tier's geometry: only it writes images so far)
   const long long cap = 24LL << 30;
   long long k = cap / (per_pass * n_se * ImgMap<C>::STRIDE);
   if (k < 1) k = 1;
@@ -204,13 +204,13 @@ static long long tc_bwd_chunk_tiles(long long n_tiles, long long n_se) {
   return n_tiles < chunk ? n_tiles : chunk;
 }
 
-template <class C>
+template <class C, bool SPLIT = false>
 static int run_tc_bwd(const BwdArgs& a, unsigned char* images, float* rep, cudaStream_t st) {
-  using G = TcBwdGeom<C>;
+  using G = TcBwdGeom<C, SPLIT>;
   using DG = DwGeom<C>;
   static DeviceOnce attr_once;
   if (attr_once.need()) {
-    NLBAC_CUDA(cudaFuncSetAttribute(node_tc_bwd_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM_BYTES));
+    NLBAC_CUDA(cudaFuncSetAttribute(node_tc_bwd_kernel<C, SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::SMEM_BYTES));
     NLBAC_CUDA(cudaFuncSetAttribute(node_tc_dw_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)DG::SMEM_BYTES));
   }
   const long long n_tiles = (a.B + 127) / 128;
@@ -223,7 +223,7 @@ static int run_tc_bwd(const BwdArgs& a, unsigned char* images, float* rep, cudaS
     const int grid = (int)(n_pairs < sm_count() ? n_pairs : sm_count());
     {
       KScope ks(1, st);
-      node_tc_bwd_kernel<C><<<grid, G::NT, G::SMEM_BYTES, st>>>(ta);
+      node_tc_bwd_kernel<C, SPLIT><<<grid, G::NT, G::SMEM_BYTES, st>>>(ta);
     }
     NLBAC_CUDA(cudaGetLastError());
     if (images) {
@@ -255,7 +255,8 @@ static int launch_pack_tc(const float* const* params, float* packed, cudaStream_
       if (l >= 1 && l <= C::nhc(c)) {
         const int h = C::hid_base(c) + (l - 1);
         pack_tc_kernel<C><<<16, 256, 0, st>>>(params[pi], params[pi + 1], packed + T::off_hi(h), packed + T::off_lo(h),
-                                              packed + T::off_tr(h), l == 1 ? packed + C::off_b0(c) + C::H : nullptr);
+                                              packed + T::off_tr(h), packed + T::off_trlo(h),
+                                              l == 1 ? packed + C::off_b0(c) + C::H : nullptr);
         NLBAC_CUDA(cudaGetLastError());
       }
   return 0;
@@ -512,9 +513,14 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
                          const float* ckpt, const float* grad_out, float* grad_y0, float* grad_params,
                          void* ws, void* stream) {
   NLBAC_REQUIRE(packed && y0 && t && grid && ckpt && grad_out && ws, "null pointer");
-  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32 || precision == NLBAC_PREC_TF32, "precision %d not compiled for the backward",
-                precision);
-  if (precision == NLBAC_PREC_TF32) {   // `packed` is the tensor-core image, `ws` sized by nlbac_node_tc_bwd_workspace_bytes
+  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32 || precision == NLBAC_PREC_TF32 || precision == NLBAC_PREC_3XTF32,
+                "precision %d not compiled for the backward", precision);
+  // 3xTF32 (fp32-class) reverse sweep on tcgen05: hi/lo operand images, three MMA sets per hidden layer.  Parameter
+  // gradients are not produced by this tier yet (dL/dy0 only: what the actor update needs, U sac_cbf_clf.py:453 -- the
+  // d-theta of that call is discarded by the reference); callers that want d-theta use the FP32 sweep.
+  NLBAC_REQUIRE(precision != NLBAC_PREC_3XTF32 || grad_params == nullptr,
+                "the 3xTF32 reverse sweep produces dL/dy0 only; request parameter gradients from the FP32 or TF32 tier");
+  if (precision == NLBAC_PREC_TF32 || precision == NLBAC_PREC_3XTF32) {   // `packed` is the tensor-core image, `ws` sized by nlbac_node_tc_bwd_workspace_bytes
     NLBAC_REQUIRE(method >= NLBAC_EULER && method <= NLBAC_RK4, "fixed-grid methods only (got %d)", method);
     NLBAC_REQUIRE(B >= 0, "negative batch");
     Schedule s;
@@ -538,7 +544,9 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
         NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
         images = reinterpret_cast<unsigned char*>(base + off_img);
       }
-      if (int rc = run_tc_bwd<C>(a, images, rep, st)) return rc;
+      if (precision == NLBAC_PREC_3XTF32) {
+        if (int rc = run_tc_bwd<C, true>(a, nullptr, rep, st)) return rc;
+      } else if (int rc = run_tc_bwd<C, false>(a, images, rep, st)) return rc;
       if (grad_params) {
         GradTable gt = build_grad_table<C>();
         KScope ks(3, st);

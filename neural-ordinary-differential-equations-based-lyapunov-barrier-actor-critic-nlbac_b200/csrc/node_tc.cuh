@@ -39,11 +39,13 @@ struct TcCfg {
   static constexpr bool FOLD = KP > C::H;
   static_assert(NP <= TCOLS && KP == C::HP, "tile shape");
   // packed image: [RES_ALL (thin layers fwd + bwd, node_cfg.cuh) | U_hi[NHID] | U_lo[NHID] | U_T[NHID]]
-  //   U_hi / U_lo: B operand of the forward GEMM  (rows j = out, K = in);  U_T: B operand of dX (rows k = in, K = out)
+  //   U_hi / U_lo: B operand of the forward GEMM  (rows j = out, K = in);  U_T / U_Tlo: B operand of dX (rows k = in, K = out)
   __host__ __device__ static constexpr int off_hi(int h) { return C::RES_ALL + h * W_FLOATS; }
   __host__ __device__ static constexpr int off_lo(int h) { return C::RES_ALL + (C::NHID + h) * W_FLOATS; }
   __host__ __device__ static constexpr int off_tr(int h) { return C::RES_ALL + (2 * C::NHID + h) * W_FLOATS; }
-  static constexpr int PACKED = C::RES_ALL + 3 * C::NHID * W_FLOATS;
+  // U_Tlo: residual of the transposed image (3xTF32 reverse sweep: dX = d_hi W_hi + d_lo W_hi + d_hi W_lo)
+  __host__ __device__ static constexpr int off_trlo(int h) { return C::RES_ALL + (3 * C::NHID + h) * W_FLOATS; }
+  static constexpr int PACKED = C::RES_ALL + 4 * C::NHID * W_FLOATS;
 };
 
 // round-to-nearest TF32 (the MMA itself truncates the low 13 mantissa bits: rounding first halves the error and
@@ -96,7 +98,8 @@ __device__ __forceinline__ float pair_sum(unsigned long long a) { float lo, hi; 
 // weight image of one hidden matrix: W[j][k] (nn.Linear [out][in]) -> float index (k/4)*NP*4 + j*4 + k%4
 template <class C>
 __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restrict__ b, float* __restrict__ hi,
-                               float* __restrict__ lo, float* __restrict__ tr, float* __restrict__ b0_one) {
+                               float* __restrict__ lo, float* __restrict__ tr, float* __restrict__ trlo,
+                               float* __restrict__ b0_one) {
   using T = TcCfg<C>;
   if (T::FOLD && b0_one != nullptr && blockIdx.x == 0 && threadIdx.x == 0) *b0_one = 1.f;   // a_1[H] = relu(1) = 1
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < T::W_FLOATS; i += gridDim.x * blockDim.x) {
@@ -107,14 +110,17 @@ __global__ void pack_tc_kernel(const float* __restrict__ W, const float* __restr
     const float h = tf32_hi(w);
     hi[i] = h;
     lo[i] = w - h;
-    tr[i] = in ? tf32_hi(W[k * C::H + j]) : 0.f;                         // row j of the image = column j of W
+    const float wt = in ? W[k * C::H + j] : 0.f;                         // row j of the image = column j of W
+    const float ht = tf32_hi(wt);
+    tr[i] = ht;
+    trlo[i] = wt - ht;
   }
 }
 
 // TMEM columns of a CTA: one 128-column accumulator per group + one 128-column operand block per TMEM-operand group
 // (allocations are powers of two)
-__host__ __device__ constexpr int tmem_cols(int groups, int tmem_groups) {
-  const int need = (groups + tmem_groups) * 128;
+__host__ __device__ constexpr int tmem_cols(int groups, int tmem_groups, int nimg = 1) {
+  const int need = (groups + tmem_groups * nimg) * 128;
   return need <= 128 ? 128 : (need <= 256 ? 256 : 512);
 }
 
@@ -270,11 +276,19 @@ struct TcGroupCtx {
 template <class C, bool SPLIT>
 __device__ __forceinline__ void act_store8(const TcGroupCtx& cx, int g8, const float (&v)[8]) {
   using T = TcCfg<C>;
-  if (!SPLIT && cx.tmemA) {
-    float r[8];
+  if (cx.tmemA) {
+    if (SPLIT) {   // hi block at ta_row, lo block 128 columns further (TcBwdGeom<C, true>)
+      float h[8], l[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) r[i] = tf32_bias(v[i]);
-    umma::st8(cx.ta_row + 8 * g8, r);
+      for (int i = 0; i < 8; ++i) { h[i] = tf32_rn(v[i]); l[i] = v[i] - h[i]; }
+      umma::st8(cx.ta_row + 8 * g8, h);
+      umma::st8(cx.ta_row + T::TCOLS + 8 * g8, l);
+    } else {
+      float r[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) r[i] = tf32_bias(v[i]);
+      umma::st8(cx.ta_row + 8 * g8, r);
+    }
   } else {
     store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, cx.lt, 8 * g8, v[0], v[1], v[2], v[3]);
     store_act4<SPLIT, T::ACH, T::A_BYTES>(cx.sA, cx.lt, 8 * g8 + 4, v[4], v[5], v[6], v[7]);
@@ -295,7 +309,7 @@ __device__ __forceinline__ void act_store8_raw(const TcGroupCtx& cx, int g8, con
 // operand written -> visible to the MMA the group's elected thread issues next
 template <bool SPLIT>
 __device__ __forceinline__ void act_publish(const TcGroupCtx& cx) {
-  if (!SPLIT && cx.tmemA) umma::wait_st();
+  if (cx.tmemA) umma::wait_st();
   else fence_proxy_async();
   umma::fence_before_sync();
   group_sync(cx.g);
@@ -350,12 +364,12 @@ __device__ __forceinline__ void tc_wait_done(TcGroupCtx& cx) {
 }
 
 template <class C>
-__device__ __noinline__ void tc_issue_ts(uint32_t tmma, uint32_t ta, uint64_t wd) {   // A operand in tensor memory
+__device__ __noinline__ void tc_issue_ts(uint32_t tmma, uint32_t ta, uint64_t wd, uint32_t acc0 = 0u) {   // A operand in tensor memory
   using T = TcCfg<C>;
   constexpr uint32_t idesc = umma::make_idesc_tf32(128, T::NP, false, false);
 #pragma unroll
   for (int ks = 0; ks < T::KSTEPS; ++ks)
-    umma::mma_tf32_ts(tmma, ta + 8 * ks, wd + (uint64_t)(ks * ((2 * T::WCH) >> 4)), idesc, ks > 0 ? 1u : 0u);
+    umma::mma_tf32_ts(tmma, ta + 8 * ks, wd + (uint64_t)(ks * ((2 * T::WCH) >> 4)), idesc, ks > 0 ? 1u : acc0);
 }
 
 // Right-hand side for the group's tile: owner thread passes x / constants, receives k = dx/dt.

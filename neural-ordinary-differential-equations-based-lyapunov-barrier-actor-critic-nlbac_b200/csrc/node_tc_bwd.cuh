@@ -70,31 +70,44 @@ __device__ __forceinline__ void store_img8_relu(unsigned char* img, int t, int c
   *reinterpret_cast<uint4*>(img + (c0 >> 3) * 2048 + (t >> 3) * 128 + (t & 7) * 16) = p;
 }
 
-template <class C>
+// SPLIT = 3xTF32 reverse sweep (fp32-class): every operand image exists twice (hi = TF32-rounded, lo = residual) and a
+// hidden-layer product is hi*hi + lo*hi + hi*lo, i.e. three MMA sets over TWO ring packets (W_hi then W_lo).  One group
+// keeps its hi / lo operand images in shared memory (2 x 53 KB), one keeps them in tensor memory (2 x 128 columns):
+// 2 accumulators + 2 operand blocks = all 512 TMEM columns.
+template <class C, bool SPLIT = false>
 struct TcBwdGeom {
   using T = TcCfg<C>;
   static constexpr int NSLOT = 2;
+  static constexpr int NIMG = SPLIT ? 2 : 1;
   static constexpr int fixed_bytes = NSLOT * T::W_BYTES + C::RES_ALL * 4 + 256;
-  static constexpr int GS = (fixed_bytes + 2 * T::A_BYTES <= 227 * 1024) ? 2 : 1;   // operand image in shared memory
-  static constexpr int GT = 1;                                                        // operand in tensor memory
+  static constexpr int GS = (!SPLIT && fixed_bytes + 2 * T::A_BYTES <= 227 * 1024) ? 2 : 1;   // operand image(s) in shared memory
+  static constexpr int GT = 1;                                                                  // operand in tensor memory
   static constexpr int G = GS + GT;
   static constexpr int NT = G * 128;
-  static constexpr int TMEM_COLS = tmem_cols(G, GT);
+  static constexpr int TMEM_COLS = tmem_cols(G, GT, NIMG);
   static constexpr int OFF_A = 0;
-  static constexpr int OFF_W = OFF_A + GS * T::A_BYTES;
+  static constexpr int OFF_W = OFF_A + GS * NIMG * T::A_BYTES;
   static constexpr int OFF_RES = OFF_W + NSLOT * T::W_BYTES;
   static constexpr int OFF_BAR = OFF_RES + C::RES_ALL * 4;
   static constexpr int NBAR = 2 * NSLOT + G + 1;
   static constexpr size_t SMEM_BYTES = OFF_BAR + NBAR * 8 + 16;
-  static constexpr int PKT_PER_EVAL = 2 * C::NHID;   // every hidden matrix once forward, once transposed
+  static constexpr int PKT_PER_LAYER = SPLIT ? 2 : 1;
+  static constexpr int PKT_PER_EVAL = 2 * C::NHID * PKT_PER_LAYER;   // every hidden matrix once forward, once transposed
   static constexpr int NLAY = C::NL_MAX - 1;         // activations per chain (masks kept in registers)
   static_assert(OFF_W % 128 == 0 && OFF_RES % 16 == 0 && OFF_BAR % 8 == 0, "alignment");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
+  static_assert(TMEM_COLS <= 512, "tensor memory budget");
   __device__ static int pkt_off(uint32_t p) {
     int q = p % PKT_PER_EVAL, c = 0;
-    if (C::NCH == 2 && q >= 2 * C::nhc(0)) { c = 1; q -= 2 * C::nhc(0); }
+    constexpr int per0 = 2 * C::nhc(0) * PKT_PER_LAYER;
+    if (C::NCH == 2 && q >= per0) { c = 1; q -= per0; }
     const int n = C::nhc(c);
-    return q < n ? T::off_hi(C::hid_base(c) + q) : T::off_tr(C::hid_base(c) + (n - 1 - (q - n)));
+    const int lo = SPLIT ? (q & 1) : 0;      // second packet of a layer = the residual image
+    q /= PKT_PER_LAYER;
+    const int hb = C::hid_base(c);
+    if (q < n) return lo ? T::off_lo(hb + q) : T::off_hi(hb + q);
+    const int h = hb + (n - 1 - (q - n));
+    return lo ? T::off_trlo(h) : T::off_tr(h);
   }
 };
 
@@ -108,11 +121,14 @@ __device__ __forceinline__ void finish_act_img(unsigned char* img, int t) {
 }
 
 // one hidden-layer GEMM of the group's tile: A = the group's activation image, B = next ring packet
-template <class C, class GEO>
+template <class C, class GEO, bool SPLIT = false>
 __device__ __forceinline__ void tc_layer_mma(TcGroupCtx& cx) {
   using T = TcCfg<C>;
   constexpr int NSLOT = GEO::NSLOT;
-  if (cx.keeper) ring_prefetch<GEO>(cx, cx.seq + NSLOT - 1);
+  if (cx.keeper) {
+    ring_prefetch<GEO>(cx, cx.seq + NSLOT - 1);
+    if (SPLIT) ring_prefetch<GEO>(cx, cx.seq + NSLOT);
+  }
 #ifdef NLBAC_TC_PROF
   long long p0 = clock64(), p1 = p0, p2 = p0;
   cx.pf_epi += p0 - cx.pf_t;
@@ -126,15 +142,29 @@ __device__ __forceinline__ void tc_layer_mma(TcGroupCtx& cx) {
     p1 = clock64();
 #endif
     const uint64_t wd = cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4));
-    if (cx.tmemA) tc_issue_ts<C>(cx.tmma, cx.ta_mma, wd);
-    else tc_issue<C>(cx.tmma, cx.adesc, wd, 0u);
+    if (cx.tmemA) {
+      tc_issue_ts<C>(cx.tmma, cx.ta_mma, wd, 0u);                                       // A_hi W_hi
+      if (SPLIT) tc_issue_ts<C>(cx.tmma, cx.ta_mma + T::TCOLS, wd, 1u);                 // A_lo W_hi
+    } else {
+      tc_issue<C>(cx.tmma, cx.adesc, wd, 0u);
+      if (SPLIT) tc_issue<C>(cx.tmma, cx.adesc + (uint64_t)(T::A_BYTES >> 4), wd, 1u);
+    }
     umma::commit(&cx.empty[slot]);
+    if (SPLIT) {                                                                         // A_hi W_lo
+      const uint32_t s2 = cx.seq + 1, slot2 = s2 % NSLOT;
+      mbar_wait(&cx.full[slot2], (s2 / NSLOT) & 1);
+      umma::fence_after_sync();
+      const uint64_t wd2 = cx.wdesc + (uint64_t)(slot2 * (T::W_BYTES >> 4));
+      if (cx.tmemA) tc_issue_ts<C>(cx.tmma, cx.ta_mma, wd2, 1u);
+      else tc_issue<C>(cx.tmma, cx.adesc, wd2, 1u);
+      umma::commit(&cx.empty[slot2]);
+    }
     umma::commit(cx.done);
 #ifdef NLBAC_TC_PROF
     p2 = clock64();
 #endif
   }
-  ++cx.seq;
+  cx.seq += SPLIT ? 2 : 1;
   tc_wait_done(cx);
 #ifdef NLBAC_TC_PROF
   cx.pf_t = clock64();
@@ -171,26 +201,32 @@ __device__ __forceinline__ uint32_t pos_bits8(const float (&v)[8]) {
 // activation -> the group's MMA operand (ReLU + TF32 rounding in one integer instruction) and, rounded to bf16 with
 // the ReLU folded into the conversion, -> the HBM image.  The ones column of the image (bias gradients, column H)
 // needs no special case where the bias is folded (TcCfg::FOLD): the pre-activation of column H is the constant 1.
-template <class C>
+template <class C, bool SPLIT = false>
 __device__ __forceinline__ void relu_publish8(const TcGroupCtx& cx, uint32_t& mword, int u, int g8,
                                               float (&v)[8], unsigned char* ia) {
   using T = TcCfg<C>;
   mword |= pos_bits8(v) << (8 * u);     // the batch's mask word; the caller files it once per batch (or4)
   if (ia != nullptr) store_img8_relu(ia, cx.lt, 8 * g8, v);
   float r[8];
+  if (SPLIT) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i) r[i] = relu_tf32_bias(v[i]);
-  act_store8_raw<C>(cx, g8, r);
+    for (int i = 0; i < 8; ++i) r[i] = fmaxf(v[i], 0.f);
+    act_store8<C, true>(cx, g8, r);
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = relu_tf32_bias(v[i]);
+    act_store8_raw<C>(cx, g8, r);
+  }
 }
 
 // One stage of the reverse sweep for the group's tile (mirrors vjp_rhs_tile of node_bwd.cuh).
 // img: global image block of this (tile, stage evaluation) or nullptr (no parameter gradients wanted).
-template <class C>
+template <class C, bool SPLIT = false>
 __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, const float (&x)[C::NS],
                                            const float (&cst)[C::NCONST], const float (&dk)[C::NS],
                                            float (&dx)[C::NS], float (&dcst)[C::NCONST]) {
   using T = TcCfg<C>;
-  using G = TcBwdGeom<C>;
+  using G = TcBwdGeom<C, SPLIT>;
   using IM = ImgMap<C>;
   constexpr int NG8 = T::KP / 8;
   static_assert(NG8 <= 16, "mask words");
@@ -237,7 +273,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
                    *reinterpret_cast<const float4*>(Wt0 + d * C::HP + 8 * g8 + 4));
         }
         acc8_get(acc, v);
-        relu_publish8<C>(cx, mword, u, g8, v, wimg ? ia : nullptr);
+        relu_publish8<C, SPLIT>(cx, mword, u, g8, v, wimg ? ia : nullptr);
       }, [&](int q) { or4(mk[0], q, mword); mword = 0u; });
       if (wimg) finish_act_img<C>(ia, lt);
     }
@@ -272,7 +308,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
 #pragma unroll
     for (int l = 1; l <= G::NLAY - 1; ++l) {
       if (l <= n) {
-        tc_layer_mma<C, G>(cx);
+        tc_layer_mma<C, G, SPLIT>(cx);
         const float* bias = cx.sRes + C::off_bh(c, l);
         unsigned char* ia = img + IM::off_act(c, l + 1);
         if (l < n) {
@@ -282,7 +318,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
               const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
               v[0] += ba.x; v[1] += ba.y; v[2] += ba.z; v[3] += ba.w; v[4] += bb.x; v[5] += bb.y; v[6] += bb.z; v[7] += bb.w;
             }
-            relu_publish8<C>(cx, mword, u, g8, v, wimg ? ia : nullptr);
+            relu_publish8<C, SPLIT>(cx, mword, u, g8, v, wimg ? ia : nullptr);
           }, [&](int q) { or4(mk[l], q, mword); mword = 0u; });
         } else {
           // last hidden activation: forward value of g(x) (action gradient) and d_{n+1} = relu' * WL^T dOut
@@ -330,7 +366,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
             acc8_get(da, dl);
 #pragma unroll
             for (int i = 0; i < 8; ++i) dl[i] = (v[i] > 0.f && 8 * g8 + i < C::H) ? dl[i] : 0.f;
-            act_store8<C, false>(cx, g8, dl);
+            act_store8<C, SPLIT>(cx, g8, dl);
             if (wimg) {
               store_img8(id, lt, 8 * g8, dl);
                           store_img8_relu(ia, lt, 8 * g8, v);
@@ -355,7 +391,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
 #pragma unroll
     for (int l = G::NLAY - 1; l >= 1; --l) {
       if (l <= n) {
-        tc_layer_mma<C, G>(cx);
+        tc_layer_mma<C, G, SPLIT>(cx);
         const float* Wt0 = cx.sRes + C::off_wt0(c);
         unsigned char* id = img + IM::off_del(c, l);
         tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
@@ -364,7 +400,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
           for (int i = 0; i < 8; ++i) v[i] = ((bits >> i) & 1u) ? v[i] : 0.f;
           if (wimg) store_img8(id, lt, 8 * g8, v);
           if (l > 1) {
-            act_store8<C, false>(cx, g8, v);
+            act_store8<C, SPLIT>(cx, g8, v);
           } else {   // d_1: thin first layer, dx = W0^T d_1 (rows of the transposed image; padded columns are zero)
             unsigned long long d2[4];
 #pragma unroll
@@ -528,10 +564,10 @@ struct TcBwdArgs {
   long long n_tiles;      // tiles in this chunk
 };
 
-template <class C>
-__global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdArgs ta) {
+template <class C, bool SPLIT = false>
+__global__ void __launch_bounds__(TcBwdGeom<C, SPLIT>::NT, 1) node_tc_bwd_kernel(TcBwdArgs ta) {
   using T = TcCfg<C>;
-  using G = TcBwdGeom<C>;
+  using G = TcBwdGeom<C, SPLIT>;
   using IM = ImgMap<C>;
   const BwdArgs& a = ta.b;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -569,13 +605,13 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
     cx.g = tid / 128;
     cx.lt = tid % 128;
     cx.tmemA = cx.g >= G::GS;
-    cx.sA = smem_raw + G::OFF_A + (cx.tmemA ? 0 : cx.g) * T::A_BYTES;
+    cx.sA = smem_raw + G::OFF_A + (cx.tmemA ? 0 : cx.g) * G::NIMG * T::A_BYTES;
     cx.sW = smem_raw + G::OFF_W;
     cx.sRes = sRes;
     cx.full = full; cx.empty = empty; cx.done = &done[cx.g];
     cx.tmma = tbase + cx.g * T::TCOLS;
     cx.tacc = cx.tmma + ((uint32_t)((warp % 4) * 32) << 16);
-    cx.ta_mma = tbase + (G::G + (cx.tmemA ? cx.g - G::GS : 0)) * T::TCOLS;
+    cx.ta_mma = tbase + (G::G + (cx.tmemA ? cx.g - G::GS : 0) * G::NIMG) * T::TCOLS;
     cx.ta_row = cx.ta_mma + ((uint32_t)((warp % 4) * 32) << 16);
     cx.seq = 0; cx.nd = 0;
     cx.adesc = umma::make_desc(smem_u32(cx.sA), T::ACH, 128);
@@ -652,7 +688,7 @@ __global__ void __launch_bounds__(TcBwdGeom<C>::NT, 1) node_tc_bwd_kernel(TcBwdA
             for (int d = 0; d < C::NS; ++d) dk[d] = 0.f;
           }
           unsigned char* img = timg ? timg + (size_t)((long long)step * S + i) * IM::STRIDE : nullptr;
-          vjp_rhs_tc<C>(cx, img, x, cst, dk, dx, dcst);
+          vjp_rhs_tc<C, SPLIT>(cx, img, x, cst, dk, dx, dcst);
 #pragma unroll
           for (int d = 0; d < C::NS; ++d) ay[d] += dx[d];
 #pragma unroll

@@ -19,7 +19,7 @@ import torch.nn as nn
 from . import _lib
 
 METHODS = {"euler": 0, "midpoint": 1, "rk4": 2, "dopri5": 3}
-PRECISIONS = {"fp32": 0, "tf32": 2, "3xtf32": 3}   # tensor-core tiers: forward on tcgen05, backward FP32
+PRECISIONS = {"fp32": 0, "tf32": 2, "3xtf32": 3}   # tensor-core tiers: forward (and, see _FixedSolve, backward) on tcgen05
 _FIXED = ("euler", "midpoint", "rk4")
 
 
@@ -141,9 +141,12 @@ class _FixedSolve(torch.autograd.Function):
                                           n_grid, method, precision, y_out.data_ptr(),
                                           ckpt.data_ptr() if want_ckpt else None, ws.data_ptr(), st), "node_solve_fwd")
         if want_ckpt:
-            # backward tier: TF32 -> tensor-core reverse sweep (takes the tensor-core image); others -> FP32 sweep
-            bprec = 2 if precision == 2 else 0
-            ctx.save_for_backward(y0c, packed_fwd if bprec == 2 else packed, ckpt)
+            # backward tier: TF32 -> tensor-core reverse sweep (takes the tensor-core image); 3xTF32 -> the split
+            # tensor-core sweep when only dL/dy0 is wanted (the actor update), the FP32 sweep when a parameter needs a
+            # gradient (that tier produces no d-theta yet); FP32 -> FP32 sweep
+            need_p_ = any(ctx.needs_input_grad[9:])
+            bprec = 2 if precision == 2 else (3 if (precision == 3 and not need_p_) else 0)
+            ctx.save_for_backward(y0c, packed_fwd if bprec in (2, 3) else packed, ckpt)
             ctx.meta = (desc, t_np, grid_np, method, bprec, bwd.value, [p.shape for p in params],
                         [p.numel() for p in params])
         return y_out
@@ -160,7 +163,7 @@ class _FixedSolve(torch.autograd.Function):
         go = grad_out.contiguous()
         _, tp = _farr(t_np)
         _, gp = _farr(grid_np)
-        if precision == 2:
+        if precision in (2, 3):
             nb = ctypes.c_size_t()
             _lib.check(L.nlbac_node_tc_bwd_workspace_bytes(ctypes.byref(desc), B, len(grid_np), len(t_np), method,
                                                            1 if need_p else 0, ctypes.byref(nb)), "tc_bwd_workspace")

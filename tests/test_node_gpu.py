@@ -423,3 +423,60 @@ def test_tf32_tier_declared_bars(tag, B, method, steps):
     assert m["gy0_l2"] <= TF32_BARS["gy0_l2"] and m["gy0_max"] <= TF32_BARS["gy0_max"], m
     assert m["dtheta_flat"] <= TF32_BARS["dtheta_flat_large" if B >= 4096 else "dtheta_flat_small"], m
     assert m["dtheta_tensor_l2"] <= TF32_BARS["dtheta_tensor_l2"], m
+
+
+@pytest.mark.parametrize("tag,B", [("U", 128), ("U", 1000), ("P", 256), ("C", 256), ("Q", 37), ("U", 40000)])
+@pytest.mark.parametrize("method", ["euler", "rk4"])
+def test_3xtf32_reverse_sweep_dy0_on_tensor_cores(tag, B, method):
+    """precision='3xtf32' with frozen parameters (the actor-update call, U sac_cbf_clf.py:453: only the gradient to the
+    action columns is used): forward AND reverse sweep on tcgen05 with hi/lo split operands (hi*hi + lo*hi + hi*lo),
+    fp32-class -- dL/dy0 against the oracle at 2e-5 (max-norm; a few kink rows allowed at B > 8192 as in _check)."""
+    import nlbac_b200
+    ref, ours = _models(tag)
+    for p in ours.parameters():
+        p.requires_grad_(False)
+    y0 = _y0(tag, B)
+    steps = 1 if method == "euler" else 3
+    t = 0.02 * torch.arange(steps + 1, dtype=torch.float32)
+    g = torch.Generator().manual_seed(5)
+    cot = torch.randn(len(t), B, y0.shape[1], generator=g)
+    ya = y0.clone().double().requires_grad_(True)
+    sa = oracle_odeint(ref.double(), ya, t.double(), method=method)
+    (sa * cot.double()).sum().backward()
+    ref.float()
+    yb = y0.cuda().requires_grad_(True)
+    sb = nlbac_b200.odeint(ours, yb, t, method=method, precision="3xtf32")
+    (sb * cot.cuda()).sum().backward()
+    assert _rel(sb, sa) <= TOL, _rel(sb, sa)
+    if B <= 8192:
+        assert _rel(yb.grad, ya.grad) <= 2 * TOL, _rel(yb.grad, ya.grad)
+    else:
+        d = (yb.grad.detach().double().cpu() - ya.grad).abs().max(1).values
+        bad = int((d > 2 * TOL * ya.grad.abs().max()).sum())
+        # kink rows: the split products drop lo*lo (2^-22 relative), so pre-activations within ~4 ulp of zero can take
+        # the other ReLU branch than fp64 does: measured 8 rows of 40 000 x 3 rk4 steps x 1.5-scaled weights
+        assert bad <= max(2, B // 4000), ("kink rows", bad)
+
+
+def test_3xtf32_reverse_sweep_20_steps_and_param_grad_fallback():
+    """20 rk4 steps through the split sweep; and with parameters that need gradients the tier falls back to the FP32
+    sweep (the 3xTF32 sweep produces dL/dy0 only) -- both against the fp64 oracle at 1e-4: 80 chained VJPs on the
+    x1.5-scaled PVTOL model (measured 5.6e-5 for the FP32 sweep; test_rk4_20_steps_all_outputs uses the fp64 tie-breaker)."""
+    import nlbac_b200
+    ref, ours = _models("P")
+    y0 = _y0("P", 300)
+    t = 0.02 * torch.arange(21, dtype=torch.float32)
+    ya = y0.clone().double().requires_grad_(True)
+    oracle_odeint(ref.double(), ya, t.double(), method="rk4")[-1].pow(2).sum().backward()
+    want_p = [p.grad.clone() for p in ref.parameters()]
+    ref.float()
+    yb = y0.cuda().requires_grad_(True)
+    nlbac_b200.odeint(ours, yb, t, method="rk4", precision="3xtf32")[-1].pow(2).sum().backward()     # d-theta wanted
+    assert _rel(yb.grad, ya.grad) <= 10 * TOL
+    for p, q in zip(ours.parameters(), want_p):
+        assert _rel(p.grad, q) <= KINK_TOL      # summed over 300 rows x 80 evaluations: ReLU kink flips (see _check)
+    for p in ours.parameters():
+        p.requires_grad_(False)
+    yc = y0.cuda().requires_grad_(True)
+    nlbac_b200.odeint(ours, yc, t, method="rk4", precision="3xtf32")[-1].pow(2).sum().backward()     # split TC sweep
+    assert _rel(yc.grad, ya.grad) <= 10 * TOL, _rel(yc.grad, ya.grad)
