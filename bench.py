@@ -35,7 +35,7 @@ def ncu_traffic(precision):
     the `ncu --set full` summary committed under profiles/ (None when no capture exists for that tier)."""
     import re
     f, kern = {"tf32": ("r1_ncu_bench_tc_tf32.txt", "node_tc_bwd_kernel"),
-               "fp32": (None, None), "3xtf32": (None, None)}[precision]
+               "fp32": (None, None), "3xtf32": (None, None)}[precision]   # no ncu --set full capture of the other tiers
     path = os.path.join(ROOT, "profiles", f) if f else None
     if not path or not os.path.exists(path):
         return None, None
@@ -66,7 +66,7 @@ def parse():
     ap.add_argument("--log2m-total", type=int, default=23, help="log2 of the total trajectories under --scaling strong")
     ap.add_argument("--precision", default="tf32", choices=["fp32", "tf32", "3xtf32"],
                     help="tf32: tcgen05 kind::tf32 forward + reverse sweep, dW in bf16 (the 1e-2 tier of north_star); "
-                         "fp32: exact FP32 FMA path (1e-5 tier); 3xtf32: split-TF32 forward (fp32-class) + FP32 backward")
+                         "fp32: exact FP32 FMA path (1e-5 tier); 3xtf32: tcgen05 with hi/lo split operands end to end")
     ap.add_argument("--cpu-sample", type=int, default=65536,
                     help="trajectories in the CPU baseline sample (2^20 x 25 passes does not fit a bench run: ~40 s per "
                          "pass on 16 cores; the CPU rate still grows with the sample -- 1.5e5 at 2^10, 4.8e5 at 2^14 --, "
@@ -214,7 +214,7 @@ def kernel_timing_read(nlbac_b200):
     return list(ms), list(n)
 
 
-def image_bytes_per_tile_eval(nlbac_b200, model, D, method="rk4"):
+def image_bytes_per_tile_eval(nlbac_b200, model, D, method="rk4", prec=2):
     """bf16 image bytes pass A writes (and pass B reads) per 128-trajectory tile per stage evaluation."""
     import ctypes
     from nlbac_b200.odeint import describe, METHODS
@@ -223,7 +223,7 @@ def image_bytes_per_tile_eval(nlbac_b200, model, D, method="rk4"):
     out = []
     for B in (128, 256):
         nb = ctypes.c_size_t()
-        nlbac_b200._lib.check(L.nlbac_node_tc_bwd_workspace_bytes(ctypes.byref(desc), B, 2, 2, METHODS[method], 1,
+        nlbac_b200._lib.check(L.nlbac_node_tc_bwd_workspace_bytes(ctypes.byref(desc), B, 2, 2, METHODS[method], prec, 1,
                                                                   ctypes.byref(nb)), "tc_ws")
         out.append(nb.value)
     return (out[1] - out[0]) / 4.0           # one rk4 step = 4 stage evaluations
@@ -326,10 +326,23 @@ def run_ours(args):
         barrier()
         fp32_ms = f0.elapsed_time(f1) / 2
 
-    tms = torch.tensor([ms_total, e2e_ms, fp32_ms], device=dev, dtype=torch.float64)
+    # the 3xTF32 tier (forward, reverse sweep and dW all on tcgen05 with hi/lo split operands), same workload
+    x3_ms = 0.0
+    if args.precision != "3xtf32":
+        fwd_bwd(y0, precision="3xtf32")
+        barrier()
+        f0, f1 = ev(), ev()
+        f0.record()
+        for _ in range(2):
+            fwd_bwd(y0, precision="3xtf32")
+        f1.record()
+        barrier()
+        x3_ms = f0.elapsed_time(f1) / 2
+
+    tms = torch.tensor([ms_total, e2e_ms, fp32_ms, x3_ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms, fp32_ms = tms.tolist()
+    ms_total, e2e_ms, fp32_ms, x3_ms = tms.tolist()
     peak32 = fp32_peak_tflops(nlbac_b200) if rank == 0 else 0.0
     if rank == 0:
         traj_steps = float((1 << args.log2m_total) if args.scaling == "strong" else world * M) * N_STEPS
@@ -340,7 +353,7 @@ def run_ours(args):
             os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         evals = M * N_STEPS * 4.0                               # stage evaluations per pass (rk4)
         sweep_ms, sweep_n = k_ms[1] / K, k_n[1] // K            # reverse sweep: the dominant kernel in both tiers
-        if args.precision == "tf32":
+        if args.precision in ("tf32", "3xtf32"):
             # algorithmic work of pass A = the dX products (1 x forward FLOPs); it also re-computes the forward
             # hidden layers from the stage checkpoints (another 1 x), reported as "executed"
             sweep_flops, executed = evals * FLOP_EVAL_FWD[env], evals * 2 * FLOP_EVAL_FWD[env]
@@ -349,8 +362,11 @@ def run_ours(args):
                 "MEASURED_PEAKS.json bf16_tflops_sustained / 2 (kind::tf32 issues at half the bf16 rate; sustained "
                 "figure because the kernel is timed inside a long step)" if peaks else
                 "B200_PROFILING.md fallback: sustained bf16 1403.6 / 2")
-            roof = {"bound": "tensor", "kernel": "node_tc_bwd_kernel (pass A: tcgen05 TF32 recompute + dX sweep)"}
-            img = image_bytes_per_tile_eval(nlbac_b200, model, 5 if env == "U" else 8)
+            if args.precision == "3xtf32":      # three MMAs per algorithmic product (TF32 peak / 3)
+                peak, peak_src = peak / 3.0, peak_src + "; / 3 for the 3xTF32 split (hi*hi + lo*hi + hi*lo)"
+            roof = {"bound": "tensor", "kernel": "node_tc_bwd_kernel (pass A: tcgen05 %s recompute + dX sweep)" % (
+                "3xTF32" if args.precision == "3xtf32" else "TF32")}
+            img = image_bytes_per_tile_eval(nlbac_b200, model, 5 if env == "U" else 8, prec=2 if args.precision == "tf32" else 3)
             dw_bytes = (M / 128.0) * N_STEPS * 4 * img
             hbm = peaks.get("hbm_gbs") or 6453.1
             dw_gbs = dw_bytes / (k_ms[2] / K * 1e-3) / 1e9 if k_ms[2] else None
@@ -420,7 +436,7 @@ def run_ours(args):
                                        ("2^%d in total, sharded M/world per GPU" % args.log2m_total)
                                        if args.scaling == "strong" else ("2^%d per GPU" % args.log2m),
                                        "Unicycle" if env == "U" else "PVTOL"),
-                       "trajectories_per_gpu": M, "solver_steps": N_STEPS, "method": "rk4", "precision": {"fp32": "fwd fp32 / bwd fp32", "tf32": "fwd tf32 / bwd tf32 (dW bf16 operands, fp32 accumulate)", "3xtf32": "fwd 3xtf32 / bwd fp32"}[args.precision],
+                       "trajectories_per_gpu": M, "solver_steps": N_STEPS, "method": "rk4", "precision": {"fp32": "fwd fp32 / bwd fp32", "tf32": "fwd tf32 / bwd tf32 (dW bf16 operands, fp32 accumulate)", "3xtf32": "fwd 3xtf32 / bwd 3xtf32 (dW from bf16 hi/lo image pairs, fp32 accumulate, drained per block)"}[args.precision],
                        "l2": "per-step working set (stage checkpoints + outputs, %.1f GB) exceeds the 126 MB L2; no explicit flush" % (
                            M * (N_STEPS * 4 * n_s + (N_STEPS + 1) * (n_s + 2) * 2) * 4 / 1e9)},
             "fwd_ms": fwd_ms, "bwd_ms": bwd_ms,
@@ -429,6 +445,10 @@ def run_ours(args):
             "roofline": roof, "roofline_secondary": secondary,
             "fp32_tier": {"value": traj_steps / (fp32_ms * 1e-3), "ms_per_step": fp32_ms,
                           "note": "exact FP32 FMA path (1e-5 tier), same workload, 2 timed passes"} if fp32_ms else None,
+            "tier_3xtf32": {"value": traj_steps / (x3_ms * 1e-3), "ms_per_step": x3_ms,
+                            "note": "3xTF32 tier: forward, reverse sweep and dW on tcgen05 with hi/lo split operands "
+                                    "(dL/dy0 2e-5, d-theta 2e-5 per tensor at B <= 8192, 5e-5 flat beyond), same workload, "
+                                    "2 timed passes"} if x3_ms else None,
             "cpu_baseline": cpu_base, "eager_gpu_baseline": eager_gpu,
             "e2e": {"value": traj_steps / (e2e_ms / args.steps * 1e-3), "unit": "trajectory-steps/s",
                     "h2d_bytes_per_step": y0_host.numel() * 4, "d2h_bytes_per_step": 4 + flat_h.numel() * 4},

@@ -84,15 +84,18 @@ int nlbac_node_pack(const nlbac_node_desc* desc, const float* const* params, flo
 
 /* Packed image for the tensor-core tiers (NLBAC_PREC_TF32 / NLBAC_PREC_3XTF32): thin layers + one UMMA K-major
  * core-matrix image (hi and lo halves) per hidden matrix.  Pass THIS image as `packed` to nlbac_node_solve_fwd
- * when precision is a tensor-core tier; the backward always takes the FP32 image of nlbac_node_pack. */
+ * when precision is a tensor-core tier, and to nlbac_node_solve_bwd with the same tier (its reverse sweep then runs on
+ * tcgen05 too: TF32 = 1e-2 tier, 3XTF32 = fp32-class); a backward with NLBAC_PREC_FP32 takes the FP32 image of
+ * nlbac_node_pack whatever the forward's tier was. */
 int64_t nlbac_node_tc_packed_floats(const nlbac_node_desc* desc);
 int nlbac_node_tc_pack(const nlbac_node_desc* desc, const float* const* params, float* packed, void* stream);
 
-/* Workspace of the tensor-core backward (precision NLBAC_PREC_TF32 in nlbac_node_solve_bwd, `packed` = the
- * tensor-core image): schedule tables + gradient replicas + (when parameter gradients are wanted) the bf16
- * activation / cotangent images of one chunk of trajectories (<= 24 GB; the call loops over chunks). */
+/* Workspace of the tensor-core backward (precision NLBAC_PREC_TF32 or NLBAC_PREC_3XTF32 in nlbac_node_solve_bwd,
+ * `packed` = the tensor-core image): schedule tables + gradient replicas + (when parameter gradients are wanted) the
+ * bf16 activation / cotangent images of one chunk of trajectories (<= 24 GB; the call loops over chunks; the 3xTF32
+ * tier writes every image as a hi / lo pair, twice the bytes per trajectory). */
 int nlbac_node_tc_bwd_workspace_bytes(const nlbac_node_desc* desc, int64_t B, int n_grid, int n_t, int method,
-                                      int want_param_grads, size_t* bwd_bytes);
+                                      int precision, int want_param_grads, size_t* bwd_bytes);
 
 /* Workspace sizes in bytes for a solve over `n_grid` integration grid points (n_grid-1 steps). */
 int nlbac_node_workspace_bytes(const nlbac_node_desc* desc, int64_t B, int n_grid, int n_t, int method,

@@ -96,7 +96,7 @@ def _declare(lib):
     lib.nlbac_node_tc_packed_floats.argtypes = [dp]
     lib.nlbac_node_tc_packed_floats.restype = c.c_int64
     lib.nlbac_node_tc_pack.argtypes = [dp, c.POINTER(vp), vp, vp]
-    lib.nlbac_node_tc_bwd_workspace_bytes.argtypes = [dp, c.c_int64, c.c_int, c.c_int, c.c_int, c.c_int,
+    lib.nlbac_node_tc_bwd_workspace_bytes.argtypes = [dp, c.c_int64, c.c_int, c.c_int, c.c_int, c.c_int, c.c_int,
                                                       c.POINTER(c.c_size_t)]
     lib.nlbac_node_workspace_bytes.argtypes = [dp, c.c_int64, c.c_int, c.c_int, c.c_int,
                                                c.POINTER(c.c_size_t), c.POINTER(c.c_size_t), c.POINTER(c.c_size_t)]

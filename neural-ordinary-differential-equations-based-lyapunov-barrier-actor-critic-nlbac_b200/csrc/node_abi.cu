@@ -193,12 +193,12 @@ static int launch_tc_fwd(const FwdArgs& a, cudaStream_t st) {
 // CTA is latency-bound at ~65 GB/s with its 165 KB of TMA loads in flight, so it takes ~all SMs to drain the image
 // stream at HBM speed; and the longer TMEM accumulation chains raised the d-theta error from 3e-4 to 4e-3 -- the
 // tensor core accumulates with truncation, ~6e-8 relative bias per accumulate.  Dropped)
-template <class C>
+template <class C, bool SPLIT = false>
 static long long tc_bwd_chunk_tiles(long long n_tiles, long long n_se) {
-  using G = TcBwdGeom<C>;
-  const long long per_pass = (long long)sm_count() * G::G;     // (the TF32 tier's geometry: only it writes images so far)
+  using G = TcBwdGeom<C, SPLIT>;
+  const long long per_pass = (long long)sm_count() * G::G;
   const long long cap = 24LL << 30;
-  long long k = cap / (per_pass * n_se * ImgMap<C>::STRIDE);
+  long long k = cap / (per_pass * n_se * ImgMap<C, SPLIT>::STRIDE);
   if (k < 1) k = 1;
   const long long chunk = k * per_pass;
   return n_tiles < chunk ? n_tiles : chunk;
@@ -215,7 +215,7 @@ static int run_tc_bwd(const BwdArgs& a, unsigned char* images, float* rep, cudaS
   }
   const long long n_tiles = (a.B + 127) / 128;
   const long long n_se = (long long)a.n_steps * method_stages(a.method);
-  const long long chunk = images ? tc_bwd_chunk_tiles<C>(n_tiles, n_se) : n_tiles;
+  const long long chunk = images ? tc_bwd_chunk_tiles<C, SPLIT>(n_tiles, n_se) : n_tiles;
   for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
     TcBwdArgs ta;
     ta.b = a; ta.images = images; ta.tile0 = t0; ta.n_tiles = (n_tiles - t0 < chunk) ? n_tiles - t0 : chunk;
@@ -232,7 +232,16 @@ static int run_tc_bwd(const BwdArgs& a, unsigned char* images, float* rep, cudaS
       if (slabs < 1) slabs = 1;
       if (slabs > items) slabs = items;
       KScope ks(2, st);
-      node_tc_dw_kernel<C><<<dim3((unsigned)slabs, ImgMap<C>::NPAIR), DG::NT, DG::SMEM_BYTES, st>>>(images, items, rep);
+      if (SPLIT) {
+        using DS = DwSplitGeom<C>;
+        static DeviceOnce split_once;
+        if (split_once.need())
+          NLBAC_CUDA(cudaFuncSetAttribute(node_tc_dw_split_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)DS::SMEM_BYTES));
+        node_tc_dw_split_kernel<C><<<dim3((unsigned)slabs, ImgMap<C>::NPAIR), DS::NT, DS::SMEM_BYTES, st>>>(images, items, rep);
+      } else {
+        node_tc_dw_kernel<C><<<dim3((unsigned)slabs, ImgMap<C>::NPAIR), DG::NT, DG::SMEM_BYTES, st>>>(images, items, rep);
+      }
       NLBAC_CUDA(cudaGetLastError());
     }
   }
@@ -494,7 +503,8 @@ int nlbac_node_solve_fwd(const nlbac_node_desc* desc, const float* packed, const
 }
 
 int nlbac_node_tc_bwd_workspace_bytes(const nlbac_node_desc* desc, int64_t B, int n_grid, int n_t, int method,
-                                      int want_param_grads, size_t* bwd_bytes) {
+                                      int precision, int want_param_grads, size_t* bwd_bytes) {
+  NLBAC_REQUIRE(precision == NLBAC_PREC_TF32 || precision == NLBAC_PREC_3XTF32, "tensor-core tiers only (got %d)", precision);
   NLBAC_REQUIRE(B >= 0 && n_grid >= 2 && n_t >= 1 && bwd_bytes, "bad sizes");
   NLBAC_REQUIRE(method >= NLBAC_EULER && method <= NLBAC_RK4, "fixed-grid methods only (got %d)", method);
   return dispatch(desc, [&]<class C>() {
@@ -502,7 +512,10 @@ int nlbac_node_tc_bwd_workspace_bytes(const nlbac_node_desc* desc, int64_t B, in
     const long long n_se = (long long)n_steps * method_stages(method);
     const long long n_tiles = (B + 127) / 128;
     size_t bytes = round_up((int)sched_bytes(n_steps, n_t), 1024) + (size_t)round_up(NREP * C::NGRAD * 4, 1024);
-    if (want_param_grads) bytes += (size_t)tc_bwd_chunk_tiles<C>(n_tiles, n_se) * n_se * ImgMap<C>::STRIDE;
+    if (want_param_grads)
+      bytes += precision == NLBAC_PREC_3XTF32
+                   ? (size_t)tc_bwd_chunk_tiles<C, true>(n_tiles, n_se) * n_se * ImgMap<C, true>::STRIDE
+                   : (size_t)tc_bwd_chunk_tiles<C, false>(n_tiles, n_se) * n_se * ImgMap<C, false>::STRIDE;
     *bwd_bytes = bytes;
     return 0;
   });
@@ -515,11 +528,8 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
   NLBAC_REQUIRE(packed && y0 && t && grid && ckpt && grad_out && ws, "null pointer");
   NLBAC_REQUIRE(precision == NLBAC_PREC_FP32 || precision == NLBAC_PREC_TF32 || precision == NLBAC_PREC_3XTF32,
                 "precision %d not compiled for the backward", precision);
-  // 3xTF32 (fp32-class) reverse sweep on tcgen05: hi/lo operand images, three MMA sets per hidden layer.  Parameter
-  // gradients are not produced by this tier yet (dL/dy0 only: what the actor update needs, U sac_cbf_clf.py:453 -- the
-  // d-theta of that call is discarded by the reference); callers that want d-theta use the FP32 sweep.
-  NLBAC_REQUIRE(precision != NLBAC_PREC_3XTF32 || grad_params == nullptr,
-                "the 3xTF32 reverse sweep produces dL/dy0 only; request parameter gradients from the FP32 or TF32 tier");
+  // 3xTF32 (fp32-class) reverse sweep on tcgen05: hi/lo operand images, three MMA sets per hidden layer; parameter
+  // gradients from hi/lo bf16 image pairs (node_tc_dw_split_kernel)
   if (precision == NLBAC_PREC_TF32 || precision == NLBAC_PREC_3XTF32) {   // `packed` is the tensor-core image, `ws` sized by nlbac_node_tc_bwd_workspace_bytes
     NLBAC_REQUIRE(method >= NLBAC_EULER && method <= NLBAC_RK4, "fixed-grid methods only (got %d)", method);
     NLBAC_REQUIRE(B >= 0, "negative batch");
@@ -545,7 +555,7 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
         images = reinterpret_cast<unsigned char*>(base + off_img);
       }
       if (precision == NLBAC_PREC_3XTF32) {
-        if (int rc = run_tc_bwd<C, true>(a, nullptr, rep, st)) return rc;
+        if (int rc = run_tc_bwd<C, true>(a, images, rep, st)) return rc;
       } else if (int rc = run_tc_bwd<C, false>(a, images, rep, st)) return rc;
       if (grad_params) {
         GradTable gt = build_grad_table<C>();

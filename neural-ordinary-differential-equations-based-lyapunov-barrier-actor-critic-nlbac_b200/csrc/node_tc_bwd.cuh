@@ -24,7 +24,9 @@ namespace nlbac {
 //   thin images           xin [128 x 16] (stage input incl. constants for black-box nets, ones column at IN0),
 //                         dOut_c [128 x 16] (cotangent of the chain output)
 // element (t, c) of an image lives at (c / 8) * 2048 + (t / 8) * 128 + (t % 8) * 16 + (c % 8) * 2.
-template <class C>
+// SPLIT (3xTF32 tier): every image exists twice, bf16 hi and bf16 lo = bf16(v - hi) (16 mantissa bits together), the lo
+// block LO bytes after the hi block; pass B then forms d_hi a_hi + d_hi a_lo + d_lo a_hi.
+template <class C, bool SPLIT = false>
 struct ImgMap {
   using T = TcCfg<C>;
   static constexpr int IMGW = round_up(C::H + 1, 16);              // MMA N of an activation image (multiple of 16)
@@ -41,7 +43,9 @@ struct ImgMap {
   __host__ __device__ static constexpr int off_act(int c, int i /*1..nl1*/) { return chain_base(c) + (i - 1) * ACT_B; }
   __host__ __device__ static constexpr int off_del(int c, int i) { return chain_base(c) + nl1(c) * ACT_B + (i - 1) * DEL_B; }
   __host__ __device__ static constexpr int off_dout(int c) { return chain_base(c) + nl1(c) * (ACT_B + DEL_B); }
-  static constexpr int STRIDE = XIN_B + chain_bytes(0) + (C::NCH == 2 ? chain_bytes(1) : 0);
+  static constexpr int STRIDE1 = XIN_B + chain_bytes(0) + (C::NCH == 2 ? chain_bytes(1) : 0);
+  static constexpr int LO = STRIDE1;                         // byte offset of the lo block
+  static constexpr int STRIDE = (SPLIT ? 2 : 1) * STRIDE1;
   // GEMM pairs of pass B: per chain  (d_1 | xin), (d_{l+1} | a_l) l = 1..nhc, (dOut | a_{nl1})
   __host__ __device__ static constexpr int npairs(int c) { return C::nhc(c) + 2; }
   static constexpr int NPAIR = npairs(0) + (C::NCH == 2 ? npairs(1) : 0);
@@ -68,6 +72,38 @@ __device__ __forceinline__ void store_img8_relu(unsigned char* img, int t, int c
   p.x = pack_relu_bf16x2(v[0], v[1]); p.y = pack_relu_bf16x2(v[2], v[3]);
   p.z = pack_relu_bf16x2(v[4], v[5]); p.w = pack_relu_bf16x2(v[6], v[7]);
   *reinterpret_cast<uint4*>(img + (c0 >> 3) * 2048 + (t >> 3) * 128 + (t & 7) * 16) = p;
+}
+
+// hi / lo bf16 pair of eight values: hi = bf16(v), lo = bf16(v - hi)
+__device__ __forceinline__ void split_bf16x8(const float (&v)[8], uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    const __nv_bfloat162 hb = __floats2bfloat162_rn(v[2 * p], v[2 * p + 1]);
+    const float2 hf = __bfloat1622float2(hb);
+    const __nv_bfloat162 lb = __floats2bfloat162_rn(v[2 * p] - hf.x, v[2 * p + 1] - hf.y);
+    h[p] = *reinterpret_cast<const uint32_t*>(&hb);
+    l[p] = *reinterpret_cast<const uint32_t*>(&lb);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+// image store of either tier: SPLIT writes the hi block and, LO bytes further, the lo block; RELU applies max(v, 0) first
+template <bool SPLIT, bool RELU, int LO>
+__device__ __forceinline__ void img_store8(unsigned char* img, int t, int c0, const float (&v)[8]) {
+  if (!SPLIT) {
+    if (RELU) store_img8_relu(img, t, c0, v);
+    else store_img8(img, t, c0, v);
+  } else {
+    float r[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) r[i] = RELU ? fmaxf(v[i], 0.f) : v[i];
+    uint4 hi, lo;
+    split_bf16x8(r, hi, lo);
+    unsigned char* p = img + (c0 >> 3) * 2048 + (t >> 3) * 128 + (t & 7) * 16;
+    *reinterpret_cast<uint4*>(p) = hi;
+    *reinterpret_cast<uint4*>(p + LO) = lo;
+  }
 }
 
 // SPLIT = 3xTF32 reverse sweep (fp32-class): every operand image exists twice (hi = TF32-rounded, lo = residual) and a
@@ -112,11 +148,11 @@ struct TcBwdGeom {
 };
 
 // the ones column of an activation image (bias gradients) sits at column H
-template <class C>
+template <class C, bool SPLIT = false>
 __device__ __forceinline__ void finish_act_img(unsigned char* img, int t) {
   if (C::H == TcCfg<C>::KP) {   // no padding column inside the K extent: the ones column opens a new chunk
     float v[8] = {1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    store_img8(img, t, C::H, v);
+    img_store8<SPLIT, false, ImgMap<C, SPLIT>::LO>(img, t, C::H, v);
   }
 }
 
@@ -206,7 +242,7 @@ __device__ __forceinline__ void relu_publish8(const TcGroupCtx& cx, uint32_t& mw
                                               float (&v)[8], unsigned char* ia) {
   using T = TcCfg<C>;
   mword |= pos_bits8(v) << (8 * u);     // the batch's mask word; the caller files it once per batch (or4)
-  if (ia != nullptr) store_img8_relu(ia, cx.lt, 8 * g8, v);
+  if (ia != nullptr) img_store8<SPLIT, true, ImgMap<C, SPLIT>::LO>(ia, cx.lt, 8 * g8, v);
   float r[8];
   if (SPLIT) {
 #pragma unroll
@@ -227,7 +263,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
                                            float (&dx)[C::NS], float (&dcst)[C::NCONST]) {
   using T = TcCfg<C>;
   using G = TcBwdGeom<C, SPLIT>;
-  using IM = ImgMap<C>;
+  using IM = ImgMap<C, SPLIT>;
   constexpr int NG8 = T::KP / 8;
   static_assert(NG8 <= 16, "mask words");
   const int lt = cx.lt;
@@ -245,8 +281,8 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
       else if (d == C::IN0) val = 1.f;
       if (d < 8) v0[d] = val; else v1[d - 8] = val;
     }
-    store_img8(img + IM::off_xin(), lt, 0, v0);
-    if (IM::XIN_CH > 1) store_img8(img + IM::off_xin(), lt, 8, v1);
+    img_store8<SPLIT, false, IM::LO>(img + IM::off_xin(), lt, 0, v0);
+    if (IM::XIN_CH > 1) img_store8<SPLIT, false, IM::LO>(img + IM::off_xin(), lt, 8, v1);
   }
 #pragma unroll
   for (int c = 0; c < C::NCH; ++c) {
@@ -275,7 +311,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
         acc8_get(acc, v);
         relu_publish8<C, SPLIT>(cx, mword, u, g8, v, wimg ? ia : nullptr);
       }, [&](int q) { or4(mk[0], q, mword); mword = 0u; });
-      if (wimg) finish_act_img<C>(ia, lt);
+      if (wimg) finish_act_img<C, SPLIT>(ia, lt);
     }
     tc_publish(cx);
     // cotangent of the chain output
@@ -301,8 +337,8 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
         const float val = o < C::OUTP_MAX ? dout[o < C::OUTP_MAX ? o : 0] : 0.f;
         if (o < 8) v0[o] = val; else v1[o - 8] = val;
       }
-      store_img8(img + IM::off_dout(c), lt, 0, v0);
-      if (IM::DOUT_CH > 1) store_img8(img + IM::off_dout(c), lt, 8, v1);
+      img_store8<SPLIT, false, IM::LO>(img + IM::off_dout(c), lt, 0, v0);
+      if (IM::DOUT_CH > 1) img_store8<SPLIT, false, IM::LO>(img + IM::off_dout(c), lt, 8, v1);
     }
     // ---------------- hidden layers forward: a_{l+1} = relu(H_l a_l + b_l) ----------------
 #pragma unroll
@@ -368,12 +404,12 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
             for (int i = 0; i < 8; ++i) dl[i] = (v[i] > 0.f && 8 * g8 + i < C::H) ? dl[i] : 0.f;
             act_store8<C, SPLIT>(cx, g8, dl);
             if (wimg) {
-              store_img8(id, lt, 8 * g8, dl);
-                          store_img8_relu(ia, lt, 8 * g8, v);
+              img_store8<SPLIT, false, IM::LO>(id, lt, 8 * g8, dl);
+              img_store8<SPLIT, true, IM::LO>(ia, lt, 8 * g8, v);
             }
           });
         }
-        if (wimg) finish_act_img<C>(ia, lt);
+        if (wimg) finish_act_img<C, SPLIT>(ia, lt);
         tc_publish(cx);
       }
     }
@@ -398,7 +434,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
           const uint32_t bits = (sel4(mk[l - 1], q) >> (8 * u)) & 0xFFu;
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[i] = ((bits >> i) & 1u) ? v[i] : 0.f;
-          if (wimg) store_img8(id, lt, 8 * g8, v);
+          if (wimg) img_store8<SPLIT, false, IM::LO>(id, lt, 8 * g8, v);
           if (l > 1) {
             act_store8<C, SPLIT>(cx, g8, v);
           } else {   // d_1: thin first layer, dx = W0^T d_1 (rows of the transposed image; padded columns are zero)
@@ -557,6 +593,147 @@ __global__ void __launch_bounds__(DwGeom<C>::NT, 1) node_tc_dw_kernel(const unsi
   dw_role<C>(smem_raw, images, n_items, grad_rep, (int)blockIdx.y, (int)blockIdx.x, (int)gridDim.x);
 }
 
+// ------------------------------------------------------------------------------------------------
+// pass B of the 3xTF32 tier: dW = sum d^T a from hi / lo bf16 image pairs (d_hi a_hi + d_hi a_lo + d_lo a_hi, 16 mantissa
+// bits per operand), fp32-class.  The tensor core accumulates into TMEM with truncation (measured, DESIGN.md 5: the
+// d-theta error of the TF32 tier's pass B grows linearly with the length of the accumulation chain), so here a chain is
+// ONE image block long (24 MMAs): two TMEM accumulators alternate, and four drain warps add each finished block into
+// fp32 registers (round-to-nearest) while the MMAs of the next block run.  Warp 4 = TMA producer, warp 5 = MMA issuer.
+// ------------------------------------------------------------------------------------------------
+template <class C>
+struct DwSplitGeom {
+  using IM = ImgMap<C, true>;
+  static constexpr int NST = 2;
+  static constexpr int STAGE = 2 * IM::DEL_B + 2 * IM::ACT_B + 4096;   // d_hi | d_lo | a_hi | a_lo, packed; the MMA's
+  // address ranges (16 chunks of d, IMGW / 8 chunks of a) overrun into the neighbour / the pad: rows and columns that
+  // the epilogue drops (every output row / column depends only on its own operand row)
+  static constexpr int OFF_BAR = NST * STAGE;
+  static constexpr int NBAR = 2 * NST + 4;
+  static constexpr size_t SMEM_BYTES = OFF_BAR + NBAR * 8 + 16;
+  static constexpr int NT = 192;
+  static constexpr int NG8 = IM::IMGW / 8;
+  static_assert(STAGE % 128 == 0 && SMEM_BYTES <= 227 * 1024, "pass-B staging (split)");
+  static_assert(2 * IM::DEL_B + 16 * 2048 - IM::DEL_B <= STAGE, "d_lo address range stays inside the stage");
+};
+
+template <class C>
+__global__ void __launch_bounds__(DwSplitGeom<C>::NT, 1) node_tc_dw_split_kernel(const unsigned char* __restrict__ images,
+                                                                                 long long n_items,
+                                                                                 float* __restrict__ grad_rep) {
+  using G = DwSplitGeom<C>;
+  using IM = ImgMap<C, true>;
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + G::OFF_BAR);
+  uint64_t* full = bars;
+  uint64_t* empty = bars + G::NST;
+  uint64_t* accf = bars + 2 * G::NST;       // accumulator b holds a finished block
+  uint64_t* acce = bars + 2 * G::NST + 2;   // accumulator b has been drained
+  uint32_t* tslot = reinterpret_cast<uint32_t*>(bars + G::NBAR);
+  const int tid = threadIdx.x, warp = tid / 32;
+  const DwPair pr = dw_pair<C>(blockIdx.y);
+  const int slab = blockIdx.x, nslab = gridDim.x;
+  long long my_items = 0;
+  if ((long long)slab < n_items) my_items = (n_items - slab + nslab - 1) / nslab;
+
+  if (tid == 0) {
+    for (int i = 0; i < G::NST; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&accf[i], 1); mbar_init(&acce[i], 128); }
+    fence_barrier_init();
+  }
+  if (warp == 0) umma::tmem_alloc(tslot, 256);
+  umma::fence_before_sync();
+  __syncthreads();
+  umma::fence_after_sync();
+  const uint32_t tbase = *tslot;
+  const int oDlo = pr.bytesD, oAhi = 2 * pr.bytesD, oAlo = 2 * pr.bytesD + pr.bytesA;
+
+  if (my_items > 0) {
+    if (warp == 4) {
+      if (tid % 32 == 0) {   // TMA producer: four images per block
+        for (long long i = 0; i < my_items; ++i) {
+          const int s = (int)(i % G::NST);
+          if (i >= G::NST) mbar_wait(&empty[s], (uint32_t)((i / G::NST) - 1) & 1);
+          const unsigned char* blk = images + (size_t)(slab + i * nslab) * IM::STRIDE;
+          unsigned char* st = smem_raw + s * G::STAGE;
+          mbar_expect_tx(&full[s], 2 * (pr.bytesD + pr.bytesA));
+          tma_load_1d(st, blk + pr.offD, pr.bytesD, &full[s]);
+          tma_load_1d(st + oDlo, blk + IM::LO + pr.offD, pr.bytesD, &full[s]);
+          tma_load_1d(st + oAhi, blk + pr.offA, pr.bytesA, &full[s]);
+          tma_load_1d(st + oAlo, blk + IM::LO + pr.offA, pr.bytesA, &full[s]);
+        }
+      }
+      __syncwarp();
+    } else if (warp == 5) {
+      if (tid % 32 == 0) {   // MMA issuer: per block  D = d_hi a_hi + d_hi a_lo + d_lo a_hi,  K = 128 trajectories
+        const uint32_t idesc = umma::make_idesc_bf16(128, pr.N, true, true);
+        for (long long i = 0; i < my_items; ++i) {
+          const int s = (int)(i % G::NST), b = (int)(i & 1);
+          if (i >= 2) mbar_wait(&acce[b], (uint32_t)((i >> 1) - 1) & 1);
+          mbar_wait(&full[s], (uint32_t)(i / G::NST) & 1);
+          umma::fence_after_sync();
+          const uint32_t s0 = smem_u32(smem_raw + s * G::STAGE);
+          const uint32_t dh = s0, dl = s0 + oDlo, ah = s0 + oAhi, al = s0 + oAlo;
+          const uint32_t acc = tbase + b * 128;
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma::mma_bf16(acc, umma::make_desc(dh + ks * 256, 128, 2048), umma::make_desc(ah + ks * 256, 128, 2048), idesc,
+                           ks > 0 ? 1u : 0u);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma::mma_bf16(acc, umma::make_desc(dh + ks * 256, 128, 2048), umma::make_desc(al + ks * 256, 128, 2048), idesc, 1u);
+#pragma unroll
+          for (int ks = 0; ks < 8; ++ks)
+            umma::mma_bf16(acc, umma::make_desc(dl + ks * 256, 128, 2048), umma::make_desc(ah + ks * 256, 128, 2048), idesc, 1u);
+          umma::commit(&empty[s]);
+          umma::commit(&accf[b]);
+        }
+      }
+      __syncwarp();
+    } else {   // drain warps: row j of the result = feature j of the cotangent image
+      float racc[G::NG8][8];
+#pragma unroll
+      for (int g = 0; g < G::NG8; ++g)
+#pragma unroll
+        for (int k = 0; k < 8; ++k) racc[g][k] = 0.f;
+      const int ng8 = pr.N / 8;
+      for (long long i = 0; i < my_items; ++i) {
+        const int b = (int)(i & 1);
+        mbar_wait(&accf[b], (uint32_t)(i >> 1) & 1);
+        umma::fence_after_sync();
+        const uint32_t trow = tbase + b * 128 + ((uint32_t)(warp * 32) << 16);
+#pragma unroll
+        for (int g = 0; g < G::NG8; ++g)
+          if (g < ng8) {
+            float v[8];
+            umma::ld8f(trow + 8 * g, v);
+            umma::wait_ld8(v);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) racc[g][k] += v[k];
+          }
+        umma::fence_before_sync();
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&acce[b])) : "memory");
+      }
+      const int j = tid;
+      float* grep = grad_rep + (size_t)(slab % NREP) * C::NGRAD;
+      if (j < pr.rows) {
+#pragma unroll
+        for (int g = 0; g < G::NG8; ++g)
+          if (g < ng8) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+              const int col = 8 * g + k;
+              if (col < pr.cols) atomicAdd(grep + pr.goff_w + j * pr.ldw + col, racc[g][k]);
+              else if (col == pr.cols) atomicAdd(grep + pr.goff_b + j, racc[g][k]);
+            }
+          }
+      }
+    }
+  }
+  umma::fence_before_sync();
+  __syncthreads();
+  if (warp == 0) umma::tmem_dealloc(tbase, 256);
+}
+
 struct TcBwdArgs {
   BwdArgs b;              // same meaning as node_bwd.cuh (grad_rep unused here)
   unsigned char* images;  // [n_tiles_in_chunk][n_steps * S][ImgMap::STRIDE] or null
@@ -568,7 +745,7 @@ template <class C, bool SPLIT = false>
 __global__ void __launch_bounds__(TcBwdGeom<C, SPLIT>::NT, 1) node_tc_bwd_kernel(TcBwdArgs ta) {
   using T = TcCfg<C>;
   using G = TcBwdGeom<C, SPLIT>;
-  using IM = ImgMap<C>;
+  using IM = ImgMap<C, SPLIT>;
   const BwdArgs& a = ta.b;
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   float* sRes = reinterpret_cast<float*>(smem_raw + G::OFF_RES);

@@ -117,6 +117,12 @@ __device__ __forceinline__ void ld8f(uint32_t taddr, float (&v)[8]) {
                : "r"(taddr)
                : "memory");
 }
+__device__ __forceinline__ void wait_ld8(float (&a)[8]) {   // wait::ld that names the registers of ONE earlier ld8f
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7])
+               :
+               : "memory");
+}
 // wait::ld that NAMES the registers two earlier ld8 wrote: later reads of v0 / v1 cannot be scheduled above the wait
 // (needed once loads are software-pipelined: another tcgen05.ld is already in flight when these values are consumed)
 __device__ __forceinline__ void wait_ld16(float (&a)[8], float (&b)[8]) {

@@ -141,11 +141,9 @@ class _FixedSolve(torch.autograd.Function):
                                           n_grid, method, precision, y_out.data_ptr(),
                                           ckpt.data_ptr() if want_ckpt else None, ws.data_ptr(), st), "node_solve_fwd")
         if want_ckpt:
-            # backward tier: TF32 -> tensor-core reverse sweep (takes the tensor-core image); 3xTF32 -> the split
-            # tensor-core sweep when only dL/dy0 is wanted (the actor update), the FP32 sweep when a parameter needs a
-            # gradient (that tier produces no d-theta yet); FP32 -> FP32 sweep
-            need_p_ = any(ctx.needs_input_grad[9:])
-            bprec = 2 if precision == 2 else (3 if (precision == 3 and not need_p_) else 0)
+            # backward tier = forward tier: TF32 / 3xTF32 -> tensor-core reverse sweep (takes the tensor-core image),
+            # FP32 -> FP32 sweep
+            bprec = precision if precision in (2, 3) else 0
             ctx.save_for_backward(y0c, packed_fwd if bprec in (2, 3) else packed, ckpt)
             ctx.meta = (desc, t_np, grid_np, method, bprec, bwd.value, [p.shape for p in params],
                         [p.numel() for p in params])
@@ -166,7 +164,8 @@ class _FixedSolve(torch.autograd.Function):
         if precision in (2, 3):
             nb = ctypes.c_size_t()
             _lib.check(L.nlbac_node_tc_bwd_workspace_bytes(ctypes.byref(desc), B, len(grid_np), len(t_np), method,
-                                                           1 if need_p else 0, ctypes.byref(nb)), "tc_bwd_workspace")
+                                                           precision, 1 if need_p else 0, ctypes.byref(nb)),
+                       "tc_bwd_workspace")
             bwd_bytes = nb.value
         ws = torch.empty(max(bwd_bytes, 16), dtype=torch.uint8, device=dev)
         gy0 = torch.empty((B, D), dtype=torch.float32, device=dev) if need_y0 else None
@@ -227,7 +226,7 @@ def odeint(func, y0, t, *, rtol=1e-7, atol=1e-9, method=None, options=None, even
     if method in _FIXED:
         step_size = options.pop("step_size", None)
         grid_np = t_np if step_size is None else _grid_from_step_size(t_np, float(step_size))
-        packed = _packed(func, desc, params) if (prec == 0 or (need_grad and prec == 3)) else None
+        packed = _packed(func, desc, params) if prec == 0 else None
         packed_fwd = _packed(func, desc, params, tc=True) if prec != 0 else packed
         return _FixedSolve.apply(y0, desc, packed, packed_fwd, t_np, grid_np, METHODS[method], prec, need_grad, *params)
     if prec != 0:

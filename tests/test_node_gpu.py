@@ -458,10 +458,10 @@ def test_3xtf32_reverse_sweep_dy0_on_tensor_cores(tag, B, method):
         assert bad <= max(2, B // 4000), ("kink rows", bad)
 
 
-def test_3xtf32_reverse_sweep_20_steps_and_param_grad_fallback():
-    """20 rk4 steps through the split sweep; and with parameters that need gradients the tier falls back to the FP32
-    sweep (the 3xTF32 sweep produces dL/dy0 only) -- both against the fp64 oracle at 1e-4: 80 chained VJPs on the
-    x1.5-scaled PVTOL model (measured 5.6e-5 for the FP32 sweep; test_rk4_20_steps_all_outputs uses the fp64 tie-breaker)."""
+def test_3xtf32_tier_20_steps_with_parameter_gradients():
+    """20 rk4 steps, forward + reverse sweep + parameter gradients all on tcgen05 in the 3xTF32 tier, against the fp64
+    oracle at 1e-4 (dL/dy0; 80 chained VJPs on the x1.5-scaled PVTOL model -- the FP32 tier measures 5.6e-5 here) and
+    KINK_TOL on the summed parameter gradients (300 rows x 80 evaluations: ReLU kink flips, see _check)."""
     import nlbac_b200
     ref, ours = _models("P")
     y0 = _y0("P", 300)
@@ -471,12 +471,40 @@ def test_3xtf32_reverse_sweep_20_steps_and_param_grad_fallback():
     want_p = [p.grad.clone() for p in ref.parameters()]
     ref.float()
     yb = y0.cuda().requires_grad_(True)
-    nlbac_b200.odeint(ours, yb, t, method="rk4", precision="3xtf32")[-1].pow(2).sum().backward()     # d-theta wanted
-    assert _rel(yb.grad, ya.grad) <= 10 * TOL
+    nlbac_b200.odeint(ours, yb, t, method="rk4", precision="3xtf32")[-1].pow(2).sum().backward()
+    assert _rel(yb.grad, ya.grad) <= 10 * TOL, _rel(yb.grad, ya.grad)
     for p, q in zip(ours.parameters(), want_p):
-        assert _rel(p.grad, q) <= KINK_TOL      # summed over 300 rows x 80 evaluations: ReLU kink flips (see _check)
-    for p in ours.parameters():
-        p.requires_grad_(False)
-    yc = y0.cuda().requires_grad_(True)
-    nlbac_b200.odeint(ours, yc, t, method="rk4", precision="3xtf32")[-1].pow(2).sum().backward()     # split TC sweep
-    assert _rel(yc.grad, ya.grad) <= 10 * TOL, _rel(yc.grad, ya.grad)
+        assert _rel(p.grad, q) <= KINK_TOL, _rel(p.grad, q)
+
+
+@pytest.mark.parametrize("tag,B", [("U", 128), ("U", 1000), ("P", 256), ("C", 256), ("Q", 37), ("U", 40000)])
+@pytest.mark.parametrize("method", ["euler", "rk4"])
+def test_3xtf32_tier_parameter_gradients(tag, B, method):
+    """d-theta of the 3xTF32 tier: split reverse sweep + dW from hi / lo bf16 image pairs (d_hi a_hi + d_hi a_lo + d_lo a_hi,
+    accumulator drained into fp32 registers after every image block).  2e-5 per tensor (max-norm) against the fp64 oracle
+    at the reference's batch sizes; at 40 000 rows 5e-5 in the flat max-norm over all parameters, 5e-3 per tensor."""
+    import nlbac_b200
+    ref, ours = _models(tag)
+    y0 = _y0(tag, B)
+    steps = 1 if method == "euler" else 3
+    t = 0.02 * torch.arange(steps + 1, dtype=torch.float32)
+    ya = y0.clone().double().requires_grad_(True)
+    oracle_odeint(ref.double(), ya, t.double(), method=method).pow(2).sum().backward()
+    want = [p.grad.clone() for p in ref.parameters()]
+    ref.float()
+    yb = y0.cuda().requires_grad_(True)
+    ours.zero_grad()
+    nlbac_b200.odeint(ours, yb, t, method=method, precision="3xtf32").pow(2).sum().backward()
+    errs = [_rel(p.grad, q) for p, q in zip(ours.parameters(), want)]
+    flat = _rel(torch.cat([p.grad.reshape(-1) for p in ours.parameters()]), torch.cat([q.reshape(-1) for q in want]))
+    print("3xtf32 dtheta", tag, B, method, "per tensor %.1e  flat %.1e" % (max(errs), flat))
+    if B <= 8192:
+        assert max(errs) <= 2 * TOL, errs
+        assert _rel(yb.grad, ya.grad) <= 2 * TOL
+    else:
+        # the dW operands carry 16 mantissa bits (bf16 hi + lo): a product is exact to 2^-17, 100x coarser than fp32.  Summed
+        # over 40 000 rows that shows on the tensors whose gradient is a strongly cancelling sum (g_net.0/.2: |g| ~ 1-4
+        # against 165-257 for f_net; tools/diag_3x.py: 1.4e-3 there, 1e-5 elsewhere, while the FP32 tier sits at 1e-7 --
+        # so this is the tier, not kink flips).  Declared: flat max-norm 5e-5, per tensor 5e-3 beyond 8192 rows.
+        assert flat <= 5 * TOL, flat
+        assert max(errs) <= 5e-3, errs
