@@ -71,6 +71,9 @@ def parse():
                     help="trajectories in the CPU baseline sample (2^20 x 25 passes does not fit a bench run: ~40 s per "
                          "pass on 16 cores; the CPU rate still grows with the sample -- 1.5e5 at 2^10, 4.8e5 at 2^14 --, "
                          "cpu_baseline.flatness reports a second point)")
+    ap.add_argument("--sweep-only", action="store_true",
+                    help="time the headline tier only (no FP32 / 3xTF32 tiers, no baselines, no peak probe): for the "
+                         "1M-64M sweep of BASELINE config 5")
     ap.add_argument("--suite", default="headline", choices=["headline", "configs"],
                     help="configs: latencies of the reference's real small-batch configurations 1-3 (SURVEY.md §8d) "
                          "next to the same code run eagerly by PyTorch on the GPU and on the host cores")
@@ -315,7 +318,7 @@ def run_ours(args):
 
     # the exact FP32 tier on the same workload (1 warm-up + 2 timed passes), reported beside the headline
     fp32_ms = 0.0
-    if args.precision != "fp32":
+    if args.precision != "fp32" and not args.sweep_only:
         fwd_bwd(y0, precision="fp32")
         barrier()
         f0, f1 = ev(), ev()
@@ -328,7 +331,7 @@ def run_ours(args):
 
     # the 3xTF32 tier (forward, reverse sweep and dW all on tcgen05 with hi/lo split operands), same workload
     x3_ms = 0.0
-    if args.precision != "3xtf32":
+    if args.precision != "3xtf32" and not args.sweep_only:
         fwd_bwd(y0, precision="3xtf32")
         barrier()
         f0, f1 = ev(), ev()
@@ -396,7 +399,7 @@ def run_ours(args):
         roof["whole_step"] = {"achieved": whole, "unit": "TFLOP/s", "frac": whole / peak if peak else None}
         cores = os.cpu_count()
         cpu_base = eager_gpu = None
-        if world == 1:
+        if world == 1 and not args.sweep_only:
             del y_dev
             torch.cuda.empty_cache()
             cs = args.cpu_sample
@@ -414,7 +417,7 @@ def run_ours(args):
             eager_gpu = {"value": gv, "unit": "trajectory-steps/s", "kind": gkind, "ms_per_pass": gms,
                          "sample": "%d trajectories x 20 rk4 steps fwd+bwd: the same reference classes + restated "
                                    "torchdiffeq run eagerly by PyTorch on this B200 (fp32, TF32 off)" % gs}
-        if args.precision == "tf32":
+        if args.precision == "tf32" and not args.sweep_only:
             sys.path.insert(0, os.path.join(ROOT, "tools"))
             import umma_peak
             pk = umma_peak.measure(1.5, modes=(1, 3))

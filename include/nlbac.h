@@ -26,6 +26,14 @@
  * asynchronously on the given stream (a cudaStream_t passed as void*).  No hidden allocation:
  * workspaces are sized by the *_workspace_bytes queries and supplied by the caller.  Time grids
  * are HOST pointers (they are tiny and drive the launch schedule).
+ * Threading: entry points may be called concurrently from several host threads on DISTINCT streams; the library keeps
+ * no per-call state.  Process-wide state is limited to: per-device caches of kernel attributes / SM count / the
+ * no-alloc scratch address (set once, under a lock or idempotently), the dlopen'ed NCCL table, and -- DEBUG ONLY --
+ * the event list of nlbac_kernel_timing, which is NOT thread-safe: enable it from one thread with no other thread
+ * inside the library (bench.py does), never in production.  nlbac_node_solve_bwd_noalloc shares one scratch array per
+ * device: calls that overlap on one GPU race.  Shapes: the NODE entry points have compiled instances for the four
+ * shapes of node_cfg.cuh only (anything else returns -2 "no compiled kernel instance"); the MLP entry points accept
+ * n_in <= 32, n_out <= 8 and any hidden width that is a multiple of 32 in [32, 1024] (--hidden_size), else -1.
  */
 #ifndef NLBAC_H_
 #define NLBAC_H_

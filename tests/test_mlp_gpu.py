@@ -147,3 +147,27 @@ def test_policy_log_std_clamp_blocks_gradient():
     lp_ref = (-((x - m[:, :1]) ** 2) / (2 * ls.exp() ** 2) - ls - 0.5 * np.log(2 * np.pi) - torch.log(1 - y ** 2 + 1e-6))
     (y.sum() + lp_ref.sum()).backward()
     assert _rel(ml.grad, m.grad) <= 5e-5   # saturated tanh: 1 - y^2 cancels, tanhf is ~2 ulp
+
+
+@pytest.mark.parametrize("H", [64, 128, 512])
+def test_mlp_other_hidden_sizes(H):
+    """--hidden_size other than the default 256 (U main.py:216): any multiple of 32 in [32, 1024] is accepted."""
+    import nlbac_b200
+    torch.manual_seed(H)
+    ref = nlbac_ref.QNetwork(11, 2, H)
+    ours = nlbac_b200.QNetwork(11, 2, H)
+    ours.load_state_dict(ref.state_dict())
+    ours.cuda()
+    obs, act = torch.randn(200, 11), torch.randn(200, 2)
+    ar = act.clone().requires_grad_()
+    r1, r2 = ref(obs, ar)
+    (r1.sum() + 2 * r2.sum()).backward()
+    ao = act.cuda().requires_grad_()
+    q1, q2 = ours(obs.cuda(), ao)
+    assert _rel(q1, r1) <= TOL and _rel(q2, r2) <= TOL
+    (q1.sum() + 2 * q2.sum()).backward()
+    assert _rel(ao.grad, ar.grad) <= TOL
+    for (k, p), (_, r) in zip(ours.named_parameters(), ref.named_parameters()):
+        assert _rel(p.grad, r.grad) <= TOL, k
+    with pytest.raises(RuntimeError):
+        nlbac_b200.QNetwork(11, 2, 100).cuda()(obs.cuda(), act.cuda())      # 100 is not a multiple of 32
