@@ -33,7 +33,8 @@ class GraphedUpdate:
                  gamma=0.99, tau=0.005, alpha=0.2, lr=3e-4, critic_lyapunov_lr=4e-4, node_lr=1e-3,
                  target_update_interval=1, automatic_entropy_tuning=True, multiplier_interval=8, lambda_max=400.0,
                  ratio_floor=None, use_ratio=True, backup_update_interval=1, separate_backup_rho=False,
-                 node_solver="euler", dt=0.02, node_n_s=3, node_n_u=2, node_graph_batch=32768):
+                 node_solver="euler", dt=0.02, node_n_s=3, node_n_u=2, node_graph_batch=32768, with_time=False,
+                 n_extra_eps=0):
         dev = next(critic.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("GraphedUpdate: the networks must live on a CUDA device (no CPU fallback)")
@@ -68,7 +69,14 @@ class GraphedUpdate:
         self.buf = {"state": z(B, obs_dim), "action": z(B, act_dim), "reward": z(B, 1), "constraint": z(B, 1),
                     "center_pos": z(B, center_pos_num), "next_center_pos": z(B, center_pos_num),
                     "next_state": z(B, obs_dim), "mask": z(B, 1)}
-        self.eps = [z(B, act_dim) for _ in range(3)]                            # next-state sample, pi, backup pi
+        # SimulatedCars (C sac_cbf_clf.py:49-51, :98-102): the time columns of the minibatch reach the constraint blocks, and
+        # those re-sample the policies inside their rollouts -> `with_time` adds t / next_t buffers that are passed to the
+        # closures as primary(state, pi, V, t, next_t) / backup(state, pi, t, next_t); `n_extra_eps` adds noise buffers
+        # self.eps[3:] for the closures' policy.sample calls (in the reference's call order)
+        self.with_time = bool(with_time)
+        if self.with_time:
+            self.buf["t"], self.buf["next_t"] = z(B, 1), z(B, 1)
+        self.eps = [z(B, act_dim) for _ in range(3 + n_extra_eps)]              # next-state sample, pi, backup pi, extras
         self.out = z(6)
         # NODE fit (its own optimiser state; eager fused step until the batch reaches node_graph_batch, a graph after)
         self.node_optim = FusedAdam(neural_ode_model.parameters(), lr=node_lr, capturable=True)
@@ -111,8 +119,9 @@ class GraphedUpdate:
         if isinstance(state, tuple):
             state = state[0]
         V = self.lyapunovNet(b["center_pos"]).detach()                                           # :382-383
-        policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V), st)            # :384 -> :408-530
-        backup_loss_2 = C.backup_augmented_lagrangian_device(self.backup(state, bpi), st)        # :279 -> :532-640
+        targs = (b["t"], b["next_t"]) if self.with_time else ()
+        policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V, *targs), st)    # :384 -> :408-530
+        backup_loss_2 = C.backup_augmented_lagrangian_device(self.backup(state, bpi, *targs), st)  # :279 -> :532-640
         self._step(self.policy_optim, policy_loss_1 + policy_loss_2, list(self.policy.parameters()))         # :284-286
         self._step(self.backup_policy_optim, backup_policy_loss_1 + backup_loss_2,
                    list(self.backup_policy.parameters()))                                                    # :288-290
@@ -184,10 +193,12 @@ class GraphedUpdate:
         next_state, mask, ...) as CUDA tensors or host arrays; ``eps`` = three [B, n_u] noise tensors or None (drawn
         from torch's CUDA generator, like ``Normal.rsample`` in the reference)."""
         names = ("state", "action", "reward", "constraint", "center_pos", "next_center_pos", "next_state", "mask")
+        if self.with_time:
+            names = names + ("t", "next_t")
         for n, v in zip(names, batch):
             t = v if torch.is_tensor(v) else torch.as_tensor(v, dtype=torch.float32)
             self.buf[n].copy_(t.reshape(self.buf[n].shape), non_blocking=True)
-        for i in range(3):
+        for i in range(len(self.eps)):
             if eps is None:
                 self.eps[i].normal_()
             else:
@@ -207,22 +218,23 @@ class GraphedUpdate:
         return self.out
 
     # ------------------------------------------------------------------------------------------------
-    def _node_body(self, state, action, next_state):
-        y0 = torch.cat((state, action), dim=-1)
+    def _node_body(self, state, action, next_state, time_batch=None):
+        y0 = torch.cat((state, action) if time_batch is None else (state, action, time_batch), dim=-1)
         pred = odeint(self.neural_ode_model, y0, [0.0, self.dt], method=self.node_solver, atol=1e-7, rtol=1e-5)[-1]
         loss = torch.nn.functional.mse_loss(pred[:, :state.shape[1]], next_state)
         self._step(self.node_optim, loss, list(self.neural_ode_model.parameters()))
         return loss
 
-    def node_fit(self, state, action, next_state):
+    def node_fit(self, state, action, next_state, time_batch=None):
         """The NODE model fit of U sac_cbf_clf.py:205-219 (``train_step``): eager fused step, or -- once the batch has the
         steady size ``node_graph_batch`` -- one graph replay.  One Adam state (device step counter) serves both."""
         N = state.shape[0]
+        srcs = (state, action, next_state) + (() if time_batch is None else (time_batch,))
         if N != self.node_graph_batch:
-            return self._node_body(state, action, next_state)
+            return self._node_body(*srcs)
         if self._node_graph is None:
-            self._nb = [torch.empty_like(state), torch.empty_like(action), torch.empty_like(next_state)]
-            for d, s_ in zip(self._nb, (state, action, next_state)):
+            self._nb = [torch.empty_like(x) for x in srcs]
+            for d, s_ in zip(self._nb, srcs):
                 d.copy_(s_)
             self._node_body(*self._nb)          # eager: this update itself (also warms the allocator)
             torch.cuda.synchronize()
@@ -231,7 +243,7 @@ class GraphedUpdate:
                 self._node_loss = self._node_body(*self._nb)
             self._node_graph = g
             return self._node_loss
-        for d, s_ in zip(self._nb, (state, action, next_state)):
+        for d, s_ in zip(self._nb, srcs):
             d.copy_(s_, non_blocking=True)
         self._node_graph.replay()
         for p in self.neural_ode_model.parameters():
@@ -250,7 +262,8 @@ class GraphedUpdate:
             s0, s1 = dm.get_state(to_dev(nb[0])), dm.get_state(to_dev(nb[6]))
             if isinstance(s0, tuple):           # Pvtol: (state7, state6) -- the NODE is fitted on the six dynamic states
                 s0, s1 = s0[1], s1[1]
-            self.node_fit(s0, to_dev(nb[1]), s1)
+            tb = to_dev(nb[8]).reshape(-1, 1) if self.with_time else None          # C :32: node_t_batch.unsqueeze(1)
+            self.node_fit(s0, to_dev(nb[1]), s1, tb)
         with torch.no_grad():
             self.updates_dev.fill_(int(updates))
         return self.step(batch, eps)

@@ -20,7 +20,7 @@ sys.path.insert(0, HERE)
 from make_golden import _Box  # noqa: E402
 from make_golden_constraints import import_variant, _Env, _Args, _perturb_biases, _sd  # noqa: E402
 
-N_UPDATES, B, NODE_N = 12, 128, 512
+N_UPDATES, NODE_N = 12, 512
 
 
 class _Memory:
@@ -63,27 +63,61 @@ def _batch(gen, n):
     return (f32(obs), f32(act), f32(reward), f32(cons), f32(cp), f32(ncp), f32(nobs), f32(mask), None, None)
 
 
-def main():
-    model, agent_mod, dyn_mod = import_variant("U")
+def _batch_C(gen, n):
+    """SimulatedCars minibatch (C replay layout: obs 10, action 1, reward, constraint, previous_positions 4,
+    next_positions 4, next_obs 10, mask, t, next_t)."""
+    r = lambda *s: torch.rand(*s, generator=gen, dtype=torch.float64)  # noqa: E731
+    pos = torch.tensor([42.0, 36, 31, 26, 21], dtype=torch.float64) + (r(n, 5) * 4 - 2)
+    vel = 3 + 0.5 * torch.randn(n, 5, generator=gen, dtype=torch.float64)
+    act = r(n, 1) * 6 - 3
+    pos2 = pos + 0.02 * vel
+    vel2 = vel + 0.02 * torch.randn(n, 5, generator=gen, dtype=torch.float64)
+    vel2[:, 3] = vel2[:, 3] + 0.02 * act[:, 0]
+    st = torch.stack([pos, vel], 2).reshape(n, 10)
+    st2 = torch.stack([pos2, vel2], 2).reshape(n, 10)
+    scale = torch.tensor([100.0, 30.0] * 5, dtype=torch.float64)
+    obs, nobs = st / scale, st2 / scale
+    reward = -(act[:, 0] ** 2) * 0.05
+    cons = (st2[:, 4] - st2[:, 6] - 9.5).abs()
+    mask = (r(n) > 0.02).double()
+    t = torch.floor(r(n) * 300) * 0.02
+    f32 = lambda x: x.float().double().numpy()  # noqa: E731
+    return (f32(obs), f32(act), f32(reward), f32(cons), f32(st[:, 4:8]), f32(st2[:, 4:8]), f32(nobs), f32(mask), f32(t),
+            f32(t + 0.02))
+
+
+VARIANT = {
+    "U": dict(B=128, obs=7, act=2, lya_in=2, node=(3, 3, 6), low=[-3.5, -12.0], high=[3.5, 12.0], gamma_b=50.0, n_eps=3,
+              num_cbfs=7, mode="Unicycle"),
+    "C": dict(B=256, obs=10, act=1, lya_in=4, node=(12, 10), low=[-3.0], high=[3.0], gamma_b=0.5, n_eps=5, num_cbfs=2,
+              mode="SimulatedCars"),
+}
+
+
+def main(tag="U"):
+    V = VARIANT[tag]
+    B = V["B"]
+    model, agent_mod, dyn_mod = import_variant(tag)
     gen = torch.Generator().manual_seed(777)
     torch.manual_seed(11)
     env = _Env()
-    env.dynamics_mode, env.dt, env.hazards_radius = "Unicycle", 0.02, 0.5
+    env.dynamics_mode, env.dt, env.hazards_radius = V["mode"], 0.02, 0.5
     env.hazards_locations = np.array([[0., 0.], [0., 1.], [0., -1.], [-1., 1.], [-1., -1.], [1., -1.], [1., 1.]]) * 1.5
-    space = _Box([-3.5, -12.0], [3.5, 12.0])
+    space = _Box(V["low"], V["high"])
     a = object.__new__(agent_mod.SAC_CBF_CLF)
     dev = torch.device("cpu")
     a.env, a.device, a.solver = env, dev, "euler"
-    a.gamma, a.gamma_b, a.tau, a.alpha, a.backup_alpha = 0.99, 50.0, 0.005, 0.2, 0.2
-    a.center_pos_num, a.policy_type, a.batch_size = 2, "Gaussian", B
+    a.gamma, a.gamma_b, a.tau, a.alpha, a.backup_alpha = 0.99, V["gamma_b"], 0.005, 0.2, 0.2
+    a.center_pos_num, a.policy_type, a.batch_size = V["lya_in"], "Gaussian", B
     a.target_update_interval, a.Lagrangian_multiplier_update_interval = 1, 8
     a.automatic_entropy_tuning, a.critic_lyapunov_lr = True, 0.0004
-    a.critic = model.QNetwork(7, 2, 256)
-    a.critic_target = model.QNetwork(7, 2, 256)
-    a.lyapunovNet = model.LyaNetwork(2, 256)
-    a.lyapunovNet_target = model.LyaNetwork(2, 256)
-    a.policy = model.GaussianPolicy(7, 2, 256, space)
-    a.backup_policy = model.GaussianPolicy(7, 2, 256, space)
+    no, na = V["obs"], V["act"]
+    a.critic = model.QNetwork(no, na, 256)
+    a.critic_target = model.QNetwork(no, na, 256)
+    a.lyapunovNet = model.LyaNetwork(V["lya_in"], 256)
+    a.lyapunovNet_target = model.LyaNetwork(V["lya_in"], 256)
+    a.policy = model.GaussianPolicy(no, na, 256, space)
+    a.backup_policy = model.GaussianPolicy(no, na, 256, space)
     for net in (a.critic, a.lyapunovNet, a.policy, a.backup_policy):
         _perturb_biases(net, gen)
     agent_mod.hard_update(a.critic_target, a.critic)
@@ -92,25 +126,26 @@ def main():
     a.lyaNet_optim = torch.optim.Adam(a.lyapunovNet.parameters(), lr=a.critic_lyapunov_lr)
     a.policy_optim = torch.optim.Adam(a.policy.parameters(), lr=3e-4)
     a.backup_policy_optim = torch.optim.Adam(a.backup_policy.parameters(), lr=3e-4)
-    a.target_entropy = -2.0
+    a.target_entropy = -float(na)
     a.log_alpha = torch.zeros(1, requires_grad=True)
     a.alpha_optim = torch.optim.Adam([a.log_alpha], lr=3e-4)
     a.backup_log_alpha = torch.zeros(1, requires_grad=True)
     a.backup_alpha_optim = torch.optim.Adam([a.backup_log_alpha], lr=3e-4)
     a.cost_limit, a.augmented_term, a.augmented_ratio = 0.0, 1.0, 1.0005
-    a.num_cbfs, a.l_p, a.action_dim, a.num_constraints = 7, 0.03, 2, 8
-    a.lambda_values = [0.0] * 8
-    a.backup_lambda_values = [0.0] * 7
-    a.neural_ode_model = model.NeuralODEModel(3, 3, 6)
+    a.num_cbfs, a.l_p, a.action_dim, a.num_constraints = V["num_cbfs"], 0.03, na, V["num_cbfs"] + 1
+    a.lambda_values = [0.0] * (V["num_cbfs"] + 1)
+    a.backup_lambda_values = [0.0] * V["num_cbfs"]
+    a.neural_ode_model = model.NeuralODEModel(*V["node"])
     a.neural_ode_model_optimizer = torch.optim.Adam(a.neural_ode_model.parameters(), lr=1e-3)
     a.model_loss_func = agent_mod.PoseLoss()
     dm = dyn_mod.DynamicsModel(env, _Args())
 
     init = {k: _sd(getattr(a, k)) for k in ("critic", "lyapunovNet", "policy", "backup_policy", "neural_ode_model")}
-    batches = [_batch(gen, B) for _ in range(N_UPDATES)]
+    mkb = _batch if tag == "U" else _batch_C
+    batches = [mkb(gen, B) for _ in range(N_UPDATES)]
     updates_list = list(range(8, 8 + N_UPDATES))                      # 8, 16: multipliers due; 10: NODE fit due
-    node_batches = [_batch(gen, NODE_N) for u in updates_list if u % 10 == 0]
-    eps = [[torch.randn(B, 2, generator=gen) for _ in range(3)] for _ in range(N_UPDATES)]
+    node_batches = [mkb(gen, NODE_N) for u in updates_list if u % 10 == 0]
+    eps = [[torch.randn(B, na, generator=gen) for _ in range(V["n_eps"])] for _ in range(N_UPDATES)]
     mem, node_mem = _Memory(batches, B * 4), _Memory(node_batches, NODE_N)
 
     import torch.distributions.normal as tdn
@@ -126,7 +161,7 @@ def main():
     returns, lam_trace, blam_trace, rho_trace = [], [], [], []
     try:
         for i, u in enumerate(updates_list):
-            queue.extend(eps[i])                                      # next_state sample, pi, backup_pi
+            queue.extend(eps[i])             # next_state sample, pi, backup_pi (+ C: the two re-samples inside the rollouts)
             returns.append(a.update_parameters(mem, B, u, dm, node_mem, 10))
             lam_trace.append([float(v) for v in a.lambda_values])
             blam_trace.append([float(v) for v in a.backup_lambda_values])
@@ -152,14 +187,15 @@ def main():
         "lambda_trace": torch.tensor(lam_trace, dtype=torch.float64),
         "backup_lambda_trace": torch.tensor(blam_trace, dtype=torch.float64),
         "rho_trace": torch.tensor(rho_trace, dtype=torch.float64), "after_first": after_first,
-        "consts": {"dt": 0.02, "gamma_b": 50.0, "hazards": env.hazards_locations, "hazards_radius": 0.5, "l_p": 0.03,
-                   "gamma": 0.99, "tau": 0.005, "alpha": 0.2, "target_entropy": -2.0, "lr": 3e-4, "critic_lr": 4e-4,
-                   "node_lr": 1e-3, "action_low": [-3.5, -12.0], "action_high": [3.5, 12.0]},
+        "consts": {"dt": 0.02, "gamma_b": V["gamma_b"], "hazards": env.hazards_locations, "hazards_radius": 0.5,
+                   "l_p": 0.03, "gamma": 0.99, "tau": 0.005, "alpha": 0.2, "target_entropy": -float(na), "lr": 3e-4,
+                   "critic_lr": 4e-4, "node_lr": 1e-3, "action_low": V["low"], "action_high": V["high"]},
     }
-    torch.save(out, os.path.join(HERE, "update_U.pt"))
-    print("update_U.pt: returns\n", out["returns"])
+    torch.save(out, os.path.join(HERE, "update_%s.pt" % tag))
+    print("update_%s.pt: returns\n" % tag, out["returns"])
     print("lambda", out["lambda_values"], "rho", out["augmented_term"])
 
 
 if __name__ == "__main__":
-    main()
+    for tag_ in (sys.argv[1:] or ["U", "C"]):
+        main(tag_)

@@ -40,16 +40,22 @@ class _Mem:
 
 
 class _Env:
-    dynamics_mode = "Unicycle"
+    def __init__(self, mode):
+        self.dynamics_mode = mode
 
 
-def _build(g, nb):
-    k = g["consts"]
+SHAPES = {"U": dict(obs=7, act=2, lya=2, node=(3, 3, 6), mode="Unicycle"),
+          "C": dict(obs=10, act=1, lya=4, node=(12, 10), mode="SimulatedCars")}
+
+
+def _build(g, nb, tag):
+    k, S = g["consts"], SHAPES[tag]
     sp = _Space(k["action_low"], k["action_high"])
-    nets = {"critic": nb.QNetwork(7, 2, 256), "critic_target": nb.QNetwork(7, 2, 256),
-            "lyapunovNet": nb.LyaNetwork(2, 256), "lyapunovNet_target": nb.LyaNetwork(2, 256),
-            "policy": nb.GaussianPolicy(7, 2, 256, sp), "backup_policy": nb.GaussianPolicy(7, 2, 256, sp),
-            "neural_ode_model": nb.NeuralODEModel(3, 3, 6)}
+    no, na = S["obs"], S["act"]
+    nets = {"critic": nb.QNetwork(no, na, 256), "critic_target": nb.QNetwork(no, na, 256),
+            "lyapunovNet": nb.LyaNetwork(S["lya"], 256), "lyapunovNet_target": nb.LyaNetwork(S["lya"], 256),
+            "policy": nb.GaussianPolicy(no, na, 256, sp), "backup_policy": nb.GaussianPolicy(no, na, 256, sp),
+            "neural_ode_model": nb.NeuralODEModel(*S["node"])}
     for name in ("critic", "lyapunovNet", "policy", "backup_policy", "neural_ode_model"):
         nets[name].load_state_dict(g["init"][name])
     nets["critic_target"].load_state_dict(g["init"]["critic"])
@@ -57,22 +63,38 @@ def _build(g, nb):
     return {n: m.to("cuda") for n, m in nets.items()}
 
 
-def test_graphed_update_matches_reference_update_parameters(golden_dir):
+@pytest.mark.parametrize("tag", ["U", "C"])
+def test_graphed_update_matches_reference_update_parameters(tag, golden_dir):
     import nlbac_b200 as nb
     C = nb.constraints
-    g = torch.load(os.path.join(golden_dir, "update_U.pt"), weights_only=False)
-    k, B = g["consts"], g["B"]
-    nets = _build(g, nb)
-    kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_locations=k["hazards"], hazards_radius=k["hazards_radius"],
-              l_p=k["l_p"], batch_size=B)
+    g = torch.load(os.path.join(golden_dir, "update_%s.pt" % tag), weights_only=False)
+    k, B, S = g["consts"], g["B"], SHAPES[tag]
+    nets = _build(g, nb, tag)
     node, lya = nets["neural_ode_model"], nets["lyapunovNet"]
-    upd = nb.GraphedUpdate(
-        nets["critic"], nets["critic_target"], lya, nets["lyapunovNet_target"], nets["policy"], nets["backup_policy"],
-        node, nb.DynamicsModel(_Env()), B,
-        primary=lambda s, pi, V: C.unicycle_required_matrix(node, lya, s, pi, V, **kw),
-        backup=lambda s, pi: C.unicycle_required_matrix(node, None, s, pi, None, **kw),
-        num_constraints=8, obs_dim=7, act_dim=2, center_pos_num=2, gamma=k["gamma"], tau=k["tau"], alpha=k["alpha"],
-        lr=k["lr"], critic_lyapunov_lr=k["critic_lr"], node_lr=k["node_lr"], node_graph_batch=g["node_N"])
+    dm = nb.DynamicsModel(_Env(S["mode"]))
+    common = dict(obs_dim=S["obs"], act_dim=S["act"], center_pos_num=S["lya"], gamma=k["gamma"], tau=k["tau"],
+                  alpha=k["alpha"], lr=k["lr"], critic_lyapunov_lr=k["critic_lr"], node_lr=k["node_lr"],
+                  node_graph_batch=g["node_N"])
+    args = (nets["critic"], nets["critic_target"], lya, nets["lyapunovNet_target"], nets["policy"], nets["backup_policy"],
+            node, dm, B)
+    if tag == "U":
+        kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_locations=k["hazards"], hazards_radius=k["hazards_radius"],
+                  l_p=k["l_p"], batch_size=B)
+        upd = nb.GraphedUpdate(
+            *args, primary=lambda s, pi, V: C.unicycle_required_matrix(node, lya, s, pi, V, **kw),
+            backup=lambda s, pi: C.unicycle_required_matrix(node, None, s, pi, None, **kw), num_constraints=8, **common)
+    else:   # SimulatedCars: time columns into the blocks, the policies re-sampled inside them (eps[3], eps[4])
+        kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], batch_size=B)
+        h = {}
+        upd = nb.GraphedUpdate(
+            *args,
+            primary=lambda s, pi, V, t, nt: C.cars_required_matrix(node, lya, nets["policy"], dm, s, pi, V, t, nt,
+                                                                   eps_next=h["u"].eps[3], **kw),
+            backup=lambda s, pi, t, nt: C.cars_required_matrix(node, None, nets["backup_policy"], dm, s, pi, None, t, nt,
+                                                               eps_next=h["u"].eps[4], **kw),
+            num_constraints=3, lambda_max=300.0, ratio_floor=0.002, node_n_s=10, node_n_u=1, with_time=True,
+            n_extra_eps=2, **common)
+        h["u"] = upd
     cu = lambda b: tuple(None if x is None else x.cuda() for x in b)  # noqa: E731
     mem = _Mem([cu(b) for b in g["batches"]], 4 * B)
     node_mem = _Mem([cu(b) for b in g["node_batches"]], g["node_N"])
@@ -109,7 +131,7 @@ def test_graphed_update_matches_reference_update_parameters(golden_dir):
             worst[name] = max(worst.get(name, 0.0), _rel(v, sd[key]))
     print("final parameters: worst per-tensor rel error", {n: "%.1e" % v for n, v in worst.items()})
     lam8 = ((upd.cstate.lambda_values.cpu() - lam).abs() / lam.abs().max()).tolist()
-    print("lambda per-row error", ["%.0e" % v for v in lam8], "reference", ["%.3f" % v for v in lam.tolist()])
+    print(tag, "lambda per-row error", ["%.0e" % v for v in lam8], "reference", ["%.3f" % v for v in lam.tolist()])
     # after 12 updates the two policies have drifted: their loss contains the where(> 0) filter of the CBF rows
     # (gamma_b = 50): a sample that crosses zero on one side only changes a row sum discretely, and Adam turns that into
     # an O(lr) difference per step.  They are held at 5e-2, everything else at 2e-3; the first update above is the
