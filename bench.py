@@ -686,6 +686,50 @@ def run_configs(args):
                         "the restated reference update (6 .item() + float() read-backs, numpy get_state round trip)"}
     rows += [update_case()]
 
+    # the Pvtol update (P sac_cbf_clf.py:181-331: 3 chained NODE predictions + 2 policy re-samples + get_obs + the 10-row
+    # constraint kernel inside the actor loss): the same body launched eagerly through the fused kernels vs one graph replay
+    def update_case_P():
+        import numpy as np
+        g = torch.load(os.path.join(ROOT, "tests", "golden", "update_P.pt"), weights_only=False)
+        k, B = g["consts"], g["B"]
+        C = nlbac_b200.constraints
+        sp = type("S", (), {"low": np.array(k["action_low"], dtype="float32"), "high": np.array(k["action_high"], dtype="float32")})
+        nets = {"critic": nlbac_b200.QNetwork(11, 2, 256), "critic_target": nlbac_b200.QNetwork(11, 2, 256),
+                "lya": nlbac_b200.LyaNetwork(11, 256), "lya_t": nlbac_b200.LyaNetwork(11, 256),
+                "policy": nlbac_b200.GaussianPolicy(11, 2, 256, sp), "backup": nlbac_b200.GaussianPolicy(11, 2, 256, sp),
+                "node": nlbac_b200.NeuralODEModel(6, 6, 12)}
+        for n, key in (("critic", "critic"), ("critic_target", "critic"), ("lya", "lyapunovNet"), ("lya_t", "lyapunovNet"),
+                       ("policy", "policy"), ("backup", "backup_policy"), ("node", "neural_ode_model")):
+            nets[n].load_state_dict(g["init"][key])
+            nets[n].to(dev)
+        kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazard_locations=k["hazards"], hazards_radius=k["hazards_radius"],
+                  safety_operator_follow=k["safety_operator_follow"], operator_dist=k["operator_dist"], y_max=k["y_max"],
+                  y_min=k["y_min"], batch_size=B)
+        node, lya = nets["node"], nets["lya"]
+        dm = nlbac_b200.DynamicsModel(type("E", (), {"dynamics_mode": "Pvtol"}))
+        h = {}
+        upd = nlbac_b200.GraphedUpdate(
+            nets["critic"], nets["critic_target"], lya, nets["lya_t"], nets["policy"], nets["backup"], node, dm, B,
+            primary=lambda s_, pi, V: C.pvtol_required_matrix(node, lya, nets["policy"], dm, s_, pi, V,
+                                                              eps_next=h["u"].eps[3], eps_next_next=h["u"].eps[4], **kw),
+            backup=lambda s_, pi: C.pvtol_required_matrix(node, None, nets["backup"], dm, s_, pi, None,
+                                                          eps_next=h["u"].eps[5], eps_next_next=h["u"].eps[6], **kw),
+            num_constraints=10, obs_dim=11, act_dim=2, center_pos_num=11, ratio_floor=0.002, node_n_s=6, node_n_u=2,
+            n_extra_eps=4, lya_on_obs=True, backup_update_interval=4, separate_backup_rho=True)
+        h["u"] = upd
+        batch = tuple(None if x is None else x.to(dev) for x in g["batches"][0])
+        upd.step(batch)
+        o_full = lat_gpu(lambda: upd.step(batch, with_backup=True))
+        o_nob = lat_gpu(lambda: upd.step(batch, with_backup=False))
+        e_full = lat_gpu(lambda: upd._body(True), iters=20, warm=3)
+        e_nob = lat_gpu(lambda: upd._body(False), iters=20, warm=3)
+        return {"case": "config3-shaped Pvtol full update_parameters (3-step rollout in the actor loss): graph replay vs the "
+                        "same fused launches issued eagerly", "batch": B, "ours_us": o_nob, "ours_with_backup_update_us": o_full,
+                "ours_eager_launches_us": e_nob, "ours_eager_launches_with_backup_us": e_full, "torch_eager_gpu_us": None,
+                "torch_cpu_us": None, "speedup_vs_eager_gpu": None, "speedup_vs_cpu": None,
+                "graph_speedup_vs_own_eager": e_nob / o_nob}
+    rows += [update_case_P()]
+
     # replay sampling: the reference's list-of-tuples memory + np.stack + H2D vs the device ring
     from oracle.replay import ReplayMemory as RefReplay
     import numpy as np

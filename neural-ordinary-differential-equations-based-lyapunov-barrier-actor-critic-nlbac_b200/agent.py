@@ -34,7 +34,7 @@ class GraphedUpdate:
                  target_update_interval=1, automatic_entropy_tuning=True, multiplier_interval=8, lambda_max=400.0,
                  ratio_floor=None, use_ratio=True, backup_update_interval=1, separate_backup_rho=False,
                  node_solver="euler", dt=0.02, node_n_s=3, node_n_u=2, node_graph_batch=32768, with_time=False,
-                 n_extra_eps=0):
+                 n_extra_eps=0, lya_on_obs=False, node_fit_max_episode=None):
         dev = next(critic.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("GraphedUpdate: the networks must live on a CUDA device (no CPU fallback)")
@@ -73,6 +73,13 @@ class GraphedUpdate:
         # those re-sample the policies inside their rollouts -> `with_time` adds t / next_t buffers that are passed to the
         # closures as primary(state, pi, V, t, next_t) / backup(state, pi, t, next_t); `n_extra_eps` adds noise buffers
         # self.eps[3:] for the closures' policy.sample calls (in the reference's call order)
+        # Pvtol (P sac_cbf_clf.py:239-247, :282-300, :205): the Lyapunov TD loss is on the observations (V(x_t) still on the
+        # replay's lya_pre_term field = the center_pos slot), the backup policy / its temperature are updated only every
+        # `backup_update_interval` updates -> TWO captured graphs (with / without the backup branch) share all state and
+        # the host picks one per call from `updates`; the NODE fit stops after episode `node_fit_max_episode`
+        self.lya_on_obs, self.backup_update_interval = bool(lya_on_obs), int(backup_update_interval)
+        self.node_fit_max_episode = node_fit_max_episode
+        self.graph_nobackup = None
         self.with_time = bool(with_time)
         if self.with_time:
             self.buf["t"], self.buf["next_t"] = z(B, 1), z(B, 1)
@@ -93,8 +100,9 @@ class GraphedUpdate:
             p.grad = g
         optim.step()
 
-    def _body(self):
-        """U sac_cbf_clf.py:221-319, statement for statement, on the static buffers."""
+    def _body(self, with_backup=True):
+        """U sac_cbf_clf.py:221-319, statement for statement, on the static buffers (P :221-331 with `lya_on_obs` and, on
+        the updates that skip the backup controller, `with_backup=False`)."""
         b, F = self.buf, torch.nn.functional
         st = self.cstate
         st.set_updates_device(self.updates_dev)
@@ -103,36 +111,41 @@ class GraphedUpdate:
             q1t, q2t = self.critic_target(b["next_state"], next_a)
             min_q = torch.min(q1t, q2t) - self.alpha * next_logp
             next_q = b["reward"] + b["mask"] * self.gamma * min_q
-            next_l = b["constraint"] + b["mask"] * self.gamma * self.lyapunovNet_target(b["next_center_pos"])
+            next_l = b["constraint"] + b["mask"] * self.gamma * self.lyapunovNet_target(
+                b["next_state"] if self.lya_on_obs else b["next_center_pos"])
         qf1, qf2 = self.critic(b["state"], b["action"])                                          # :240-246
         qf1_loss, qf2_loss = F.mse_loss(qf1, next_q), F.mse_loss(qf2, next_q)
-        lf_loss = F.mse_loss(self.lyapunovNet(b["center_pos"]), next_l)
+        lf_loss = F.mse_loss(self.lyapunovNet(b["state"] if self.lya_on_obs else b["center_pos"]), next_l)
         self._step(self.critic_optim, qf1_loss + qf2_loss, list(self.critic.parameters()))       # :249-251
         self._step(self.lyaNet_optim, lf_loss, list(self.lyapunovNet.parameters()))              # :253-255
         pi, log_pi, _ = self.policy.sample(b["state"], self.eps[1])                              # :258-261
         min_qf_pi = torch.min(*self.critic(b["state"], pi))
-        bpi, blog_pi, _ = self.backup_policy.sample(b["state"], self.eps[2])                     # :264-267
-        bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
         policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                                 # :270
-        backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()                 # :273
         state = self.dynamics_model.get_state(b["state"])                                        # :380 (get_cbf_clf_part)
         if isinstance(state, tuple):
             state = state[0]
         V = self.lyapunovNet(b["center_pos"]).detach()                                           # :382-383
         targs = (b["t"], b["next_t"]) if self.with_time else ()
         policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V, *targs), st)    # :384 -> :408-530
-        backup_loss_2 = C.backup_augmented_lagrangian_device(self.backup(state, bpi, *targs), st)  # :279 -> :532-640
+        if with_backup:
+            bpi, blog_pi, _ = self.backup_policy.sample(b["state"], self.eps[2])                 # :264-267
+            bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
+            backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()             # :273
+            backup_loss_2 = C.backup_augmented_lagrangian_device(self.backup(state, bpi, *targs), st)  # :279 -> :532-640
         self._step(self.policy_optim, policy_loss_1 + policy_loss_2, list(self.policy.parameters()))         # :284-286
-        self._step(self.backup_policy_optim, backup_policy_loss_1 + backup_loss_2,
-                   list(self.backup_policy.parameters()))                                                    # :288-290
+        if with_backup:
+            self._step(self.backup_policy_optim, backup_policy_loss_1 + backup_loss_2,
+                       list(self.backup_policy.parameters()))                                                # :288-290
         if self.automatic_entropy_tuning:                                                        # :292-308
             alpha_loss = -(self.log_alpha * (log_pi + self.target_entropy).detach()).mean()
             self._step(self.alpha_optim, alpha_loss, [self.log_alpha])
-            balpha_loss = -(self.backup_log_alpha * (blog_pi + self.target_entropy).detach()).mean()
-            self._step(self.backup_alpha_optim, balpha_loss, [self.backup_log_alpha])
+            if with_backup:
+                balpha_loss = -(self.backup_log_alpha * (blog_pi + self.target_entropy).detach()).mean()
+                self._step(self.backup_alpha_optim, balpha_loss, [self.backup_log_alpha])
             with torch.no_grad():
                 self.alpha.copy_(self.log_alpha.exp())
-                self.backup_alpha.copy_(self.backup_log_alpha.exp())
+                if with_backup:
+                    self.backup_alpha.copy_(self.backup_log_alpha.exp())
         else:
             alpha_loss = torch.zeros((), device=self.device)
         if self.target_update_interval == 1:                                                     # :315-317
@@ -166,7 +179,9 @@ class GraphedUpdate:
         side = torch.cuda.Stream()
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):
-            self._body()
+            self._body(True)
+            if self.backup_update_interval > 1:
+                self._body(False)
         torch.cuda.current_stream().wait_stream(side)
         with torch.no_grad():
             for t, v in zip(self._state_tensors(), snap):
@@ -184,7 +199,11 @@ class GraphedUpdate:
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(self.graph):
-            self._body()
+            self._body(True)
+        if self.backup_update_interval > 1:      # the updates that skip the backup controller: a second graph, same state
+            self.graph_nobackup = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph_nobackup):
+                self._body(False)
         return self
 
     @torch.no_grad()
@@ -204,13 +223,13 @@ class GraphedUpdate:
             else:
                 self.eps[i].copy_(eps[i], non_blocking=True)
 
-    def step(self, batch=None, eps=None):
+    def step(self, batch=None, eps=None, with_backup=True):
         """One update: load the minibatch into the static buffers and replay the graph.  No host synchronisation."""
         if batch is not None:
             self.load_batch(batch, eps)
         if self.graph is None:
             self.capture()
-        self.graph.replay()
+        (self.graph if (with_backup or self.graph_nobackup is None) else self.graph_nobackup).replay()
         for net in (self.critic, self.critic_target, self.lyapunovNet, self.lyapunovNet_target, self.policy,
                     self.backup_policy):
             for p in net.parameters():          # written through raw pointers inside the graph
@@ -251,10 +270,14 @@ class GraphedUpdate:
         return self._node_loss
 
     def update_parameters(self, memory, batch_size, updates, dynamics_model=None, NODE_memory=None,
-                          NODE_model_update_interval=10, eps=None):
-        """The reference's call (U sac_cbf_clf.py:181) on a device-resident ``nlbac_b200.ReplayMemory``."""
+                          NODE_model_update_interval=10, i_episode=None, eps=None):
+        """The reference's call (U sac_cbf_clf.py:181; P :181 with ``i_episode``) on a device-resident
+        ``nlbac_b200.ReplayMemory``."""
         batch = memory.sample(batch_size=batch_size)
-        if NODE_memory is not None and updates % NODE_model_update_interval == 0:
+        fit = NODE_memory is not None and updates % NODE_model_update_interval == 0
+        if fit and self.node_fit_max_episode is not None and i_episode is not None:
+            fit = i_episode <= self.node_fit_max_episode                                  # P :205
+        if fit:
             n = min(NODE_memory.position, 32768)
             nb = NODE_memory.sample(batch_size=n)
             dm = dynamics_model or self.dynamics_model
@@ -266,4 +289,4 @@ class GraphedUpdate:
             self.node_fit(s0, to_dev(nb[1]), s1, tb)
         with torch.no_grad():
             self.updates_dev.fill_(int(updates))
-        return self.step(batch, eps)
+        return self.step(batch, eps, with_backup=updates % self.backup_update_interval == 0)

@@ -86,7 +86,34 @@ def _batch_C(gen, n):
             f32(t + 0.02))
 
 
+def _batch_P(gen, n, dm):
+    """Pvtol minibatch (P replay layout: obs 11, action 2, reward, constraint, lya_pre_term 11, lya_next_term 11,
+    next_obs 11, mask, None, None); observations through the reference's own DynamicsModel.get_obs."""
+    r = lambda *s: torch.rand(*s, generator=gen)  # noqa: E731
+    hz = torch.tensor([[-2.5, -2.5], [-2.5, 2.5], [0.0, -3.5], [0.0, 3.5], [-4.5, 0.0]])
+    x, y = r(n) * 14 - 7, r(n) * 12 - 6
+    k = torch.randint(0, 5, (n,), generator=gen)
+    near = r(n) < 0.34
+    x = torch.where(near, hz[k, 0] + (r(n) * 0.7 - 0.35), x)
+    y = torch.where(near, hz[k, 1] + (r(n) * 0.7 - 0.35), y)
+    th, vx, vy, thr = (r(n) * 2 - 1) * np.pi, r(n) * 4 - 2, r(n) * 4 - 2, r(n) * 2
+    st = torch.stack([x, y, th, vx, vy, thr, x + (r(n) * 3 - 1.5)], 1)
+    act = torch.stack([r(n) * 7 - 3.5, r(n) * 30 - 15], 1)
+    st2 = torch.stack([x + 0.02 * vx, y + 0.02 * vy, th + 0.02 * act[:, 1] * 0.1, vx + 0.02 * torch.randn(n, generator=gen),
+                       vy + 0.02 * torch.randn(n, generator=gen), (thr + 0.02 * act[:, 0]).clamp(0, 2),
+                       st[:, 6] + 0.7 * (x + 0.02 * vx - st[:, 6])], 1)
+    obs = dm.get_obs(st.unsqueeze(-1), torch.device("cpu")).squeeze(-1).detach()
+    nobs = dm.get_obs(st2.unsqueeze(-1), torch.device("cpu")).squeeze(-1).detach()
+    reward = -0.1 * (st2[:, :2] - 4.5).norm(dim=1)
+    cons = (st2[:, :2] - 4.5).norm(dim=1)
+    mask = (r(n) > 0.02).float()
+    f = lambda t: t.float().double().numpy()  # noqa: E731
+    return (f(obs), f(act), f(reward), f(cons), f(obs), f(nobs), f(nobs), f(mask), None, None)
+
+
 VARIANT = {
+    "P": dict(B=256, obs=11, act=2, lya_in=11, node=(6, 6, 12), low=[-3.5, -15.0], high=[3.5, 15.0], gamma_b=0.6, n_eps=7,
+              num_cbfs=9, mode="Pvtol"),
     "U": dict(B=128, obs=7, act=2, lya_in=2, node=(3, 3, 6), low=[-3.5, -12.0], high=[3.5, 12.0], gamma_b=50.0, n_eps=3,
               num_cbfs=7, mode="Unicycle"),
     "C": dict(B=256, obs=10, act=1, lya_in=4, node=(12, 10), low=[-3.0], high=[3.0], gamma_b=0.5, n_eps=5, num_cbfs=2,
@@ -138,14 +165,24 @@ def main(tag="U"):
     a.neural_ode_model = model.NeuralODEModel(*V["node"])
     a.neural_ode_model_optimizer = torch.optim.Adam(a.neural_ode_model.parameters(), lr=1e-3)
     a.model_loss_func = agent_mod.PoseLoss()
+    if tag == "P":   # the env attributes P's constraint block reads (as in make_golden_constraints.case_P) + P's own knobs
+        env.hazards_radius = 0.25
+        env.hazard_locations = np.array([[-2.5, -2.5], [-2.5, 2.5], [0.0, -3.5], [0.0, 3.5], [-4.5, 0.0]])
+        env.safety_operator_follow, env.operator_dist = 0.7, 0.001
+        env.y_max, env.y_min = 13.0, -13.0
+        a.backup_update_interval, a.backup_augmented_term = 4, 1.0      # default 20: 4 puts three backup updates in the trace
     dm = dyn_mod.DynamicsModel(env, _Args())
 
     init = {k: _sd(getattr(a, k)) for k in ("critic", "lyapunovNet", "policy", "backup_policy", "neural_ode_model")}
-    mkb = _batch if tag == "U" else _batch_C
+    mkb = {"U": _batch, "C": _batch_C, "P": lambda g_, n_: _batch_P(g_, n_, dm)}[tag]
     batches = [mkb(gen, B) for _ in range(N_UPDATES)]
-    updates_list = list(range(8, 8 + N_UPDATES))                      # 8, 16: multipliers due; 10: NODE fit due
+    # U / C: 8, 16: multipliers due; 10: NODE fit due.  P: 28, 32, 36 update the backup controller (interval 4), 32: both
+    # multiplier sets due (backup: every 8 * 4), 30: NODE fit
+    first = 28 if tag == "P" else 8
+    updates_list = list(range(first, first + N_UPDATES))
     node_batches = [mkb(gen, NODE_N) for u in updates_list if u % 10 == 0]
-    eps = [[torch.randn(B, na, generator=gen) for _ in range(V["n_eps"])] for _ in range(N_UPDATES)]
+    n_eps = lambda u: (7 if u % 4 == 0 else 4) if tag == "P" else V["n_eps"]  # noqa: E731
+    eps = [[torch.randn(B, na, generator=gen) for _ in range(n_eps(u))] for u in updates_list]
     mem, node_mem = _Memory(batches, B * 4), _Memory(node_batches, NODE_N)
 
     import torch.distributions.normal as tdn
@@ -162,7 +199,8 @@ def main(tag="U"):
     try:
         for i, u in enumerate(updates_list):
             queue.extend(eps[i])             # next_state sample, pi, backup_pi (+ C: the two re-samples inside the rollouts)
-            returns.append(a.update_parameters(mem, B, u, dm, node_mem, 10))
+            returns.append(a.update_parameters(mem, B, u, dm, node_mem, 10, 1) if tag == "P" else
+                           a.update_parameters(mem, B, u, dm, node_mem, 10))
             lam_trace.append([float(v) for v in a.lambda_values])
             blam_trace.append([float(v) for v in a.backup_lambda_values])
             rho_trace.append(float(a.augmented_term))
@@ -184,10 +222,14 @@ def main(tag="U"):
         "lambda_values": [float(v) for v in a.lambda_values],
         "backup_lambda_values": [float(v) for v in a.backup_lambda_values],
         "augmented_term": float(a.augmented_term),
+        "backup_augmented_term": float(getattr(a, "backup_augmented_term", 0.0)),
         "lambda_trace": torch.tensor(lam_trace, dtype=torch.float64),
         "backup_lambda_trace": torch.tensor(blam_trace, dtype=torch.float64),
         "rho_trace": torch.tensor(rho_trace, dtype=torch.float64), "after_first": after_first,
-        "consts": {"dt": 0.02, "gamma_b": V["gamma_b"], "hazards": env.hazards_locations, "hazards_radius": 0.5,
+        "consts": {"dt": 0.02, "gamma_b": V["gamma_b"],
+                   "hazards": env.hazard_locations if tag == "P" else env.hazards_locations,
+                   "hazards_radius": env.hazards_radius, "safety_operator_follow": 0.7, "operator_dist": 0.001,
+                   "y_max": 13.0, "y_min": -13.0, "backup_update_interval": 4,
                    "l_p": 0.03, "gamma": 0.99, "tau": 0.005, "alpha": 0.2, "target_entropy": -float(na), "lr": 3e-4,
                    "critic_lr": 4e-4, "node_lr": 1e-3, "action_low": V["low"], "action_high": V["high"]},
     }
@@ -197,5 +239,5 @@ def main(tag="U"):
 
 
 if __name__ == "__main__":
-    for tag_ in (sys.argv[1:] or ["U", "C"]):
+    for tag_ in (sys.argv[1:] or ["U", "C", "P"]):
         main(tag_)

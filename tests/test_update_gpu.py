@@ -44,7 +44,8 @@ class _Env:
         self.dynamics_mode = mode
 
 
-SHAPES = {"U": dict(obs=7, act=2, lya=2, node=(3, 3, 6), mode="Unicycle"),
+SHAPES = {"P": dict(obs=11, act=2, lya=11, node=(6, 6, 12), mode="Pvtol"),
+          "U": dict(obs=7, act=2, lya=2, node=(3, 3, 6), mode="Unicycle"),
           "C": dict(obs=10, act=1, lya=4, node=(12, 10), mode="SimulatedCars")}
 
 
@@ -63,7 +64,7 @@ def _build(g, nb, tag):
     return {n: m.to("cuda") for n, m in nets.items()}
 
 
-@pytest.mark.parametrize("tag", ["U", "C"])
+@pytest.mark.parametrize("tag", ["U", "C", "P"])
 def test_graphed_update_matches_reference_update_parameters(tag, golden_dir):
     import nlbac_b200 as nb
     C = nb.constraints
@@ -83,6 +84,22 @@ def test_graphed_update_matches_reference_update_parameters(tag, golden_dir):
         upd = nb.GraphedUpdate(
             *args, primary=lambda s, pi, V: C.unicycle_required_matrix(node, lya, s, pi, V, **kw),
             backup=lambda s, pi: C.unicycle_required_matrix(node, None, s, pi, None, **kw), num_constraints=8, **common)
+    elif tag == "P":   # Pvtol: Lyapunov TD loss on the observations, backup controller every 4th update (two graphs), its own
+        # rho; both rollouts re-sample their policy twice (eps[3:5] primary, eps[5:7] backup)
+        kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazard_locations=k["hazards"], hazards_radius=k["hazards_radius"],
+                  safety_operator_follow=k["safety_operator_follow"], operator_dist=k["operator_dist"], y_max=k["y_max"],
+                  y_min=k["y_min"], batch_size=B)
+        h = {}
+        upd = nb.GraphedUpdate(
+            *args,
+            primary=lambda s, pi, V: C.pvtol_required_matrix(node, lya, nets["policy"], dm, s, pi, V,
+                                                             eps_next=h["u"].eps[3], eps_next_next=h["u"].eps[4], **kw),
+            backup=lambda s, pi: C.pvtol_required_matrix(node, None, nets["backup_policy"], dm, s, pi, None,
+                                                         eps_next=h["u"].eps[5], eps_next_next=h["u"].eps[6], **kw),
+            num_constraints=10, ratio_floor=0.002, node_n_s=6, node_n_u=2, n_extra_eps=4, lya_on_obs=True,
+            backup_update_interval=k["backup_update_interval"], separate_backup_rho=True, node_fit_max_episode=100,
+            **common)
+        h["u"] = upd
     else:   # SimulatedCars: time columns into the blocks, the policies re-sampled inside them (eps[3], eps[4])
         kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], batch_size=B)
         h = {}
@@ -100,7 +117,11 @@ def test_graphed_update_matches_reference_update_parameters(tag, golden_dir):
     node_mem = _Mem([cu(b) for b in g["node_batches"]], g["node_N"])
     got, lam_err = [], []
     for i, u in enumerate(g["updates"]):
-        out = upd.update_parameters(mem, B, u, None, node_mem, 10, eps=[e.cuda() for e in g["eps"][i]])
+        e = [x.cuda() for x in g["eps"][i]]
+        if tag == "P":   # reference call order [next, pi, prim1, prim2 (, backup pi, b1, b2)] -> buffer order of GraphedUpdate
+            zz = torch.zeros_like(e[0])
+            e = [e[0], e[1], e[4] if len(e) == 7 else zz, e[2], e[3]] + ([e[5], e[6]] if len(e) == 7 else [zz, zz])
+        out = upd.update_parameters(mem, B, u, None, node_mem, 10, i_episode=1, eps=e)
         got.append(out.clone())
         lam_err.append(max(_rel(upd.cstate.lambda_values, g["lambda_trace"][i]),
                            _rel(upd.cstate.backup_lambda_values, g["backup_lambda_trace"][i])))
