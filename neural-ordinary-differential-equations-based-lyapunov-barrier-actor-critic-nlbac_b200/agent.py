@@ -34,14 +34,17 @@ class GraphedUpdate:
                  target_update_interval=1, automatic_entropy_tuning=True, multiplier_interval=8, lambda_max=400.0,
                  ratio_floor=None, use_ratio=True, backup_update_interval=1, separate_backup_rho=False,
                  node_solver="euler", dt=0.02, node_n_s=3, node_n_u=2, node_graph_batch=32768, with_time=False,
-                 n_extra_eps=0, lya_on_obs=False, node_fit_max_episode=None):
+                 n_extra_eps=0, lya_on_obs=False, node_fit_max_episode=None, barrier=None, barrier_target=None):
         dev = next(critic.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("GraphedUpdate: the networks must live on a CUDA device (no CPU fallback)")
         self.device, self.B = dev, int(batch_size)
         self.critic, self.critic_target = critic, critic_target
         self.lyapunovNet, self.lyapunovNet_target = lyapunovNet, lyapunovNet_target
-        self.policy, self.backup_policy = policy, backup_policy
+        self.policy, self.backup_policy = policy, backup_policy      # backup_policy None: no backup controller (BU / BP)
+        # learned-barrier variants (BU sac_cbf_clf.py:181-186, 214-216, 225-227, 237-240, 277): a barrier network with its
+        # own target, TD loss on the replay's barrier_signal field (11-field layout), optimiser and Polyak update
+        self.barrier, self.barrier_target = barrier, barrier_target
         self.neural_ode_model, self.dynamics_model = neural_ode_model, dynamics_model
         self.primary, self.backup = primary, backup
         self.gamma, self.tau, self.target_update_interval = gamma, tau, target_update_interval
@@ -56,7 +59,8 @@ class GraphedUpdate:
         self.critic_optim = mk(critic.parameters(), critic_lyapunov_lr)
         self.lyaNet_optim = mk(lyapunovNet.parameters(), critic_lyapunov_lr)
         self.policy_optim = mk(policy.parameters(), lr)
-        self.backup_policy_optim = mk(backup_policy.parameters(), lr)
+        self.backup_policy_optim = mk(backup_policy.parameters(), lr) if backup_policy is not None else None
+        self.barrier_optim = mk(barrier.parameters(), critic_lyapunov_lr) if barrier is not None else None
         self.alpha_optim = mk([self.log_alpha], lr)
         self.backup_alpha_optim = mk([self.backup_log_alpha], lr)
         self.cstate = C.DeviceConstraintState(num_constraints, batch_size, dev, lambda_max=lambda_max,
@@ -83,6 +87,8 @@ class GraphedUpdate:
         self.with_time = bool(with_time)
         if self.with_time:
             self.buf["t"], self.buf["next_t"] = z(B, 1), z(B, 1)
+        if barrier is not None:
+            self.buf["barrier_signal"] = z(B, 1)
         self.eps = [z(B, act_dim) for _ in range(3 + n_extra_eps)]              # next-state sample, pi, backup pi, extras
         self.out = z(6)
         # NODE fit (its own optimiser state; eager fused step until the batch reaches node_graph_batch, a graph after)
@@ -113,11 +119,16 @@ class GraphedUpdate:
             next_q = b["reward"] + b["mask"] * self.gamma * min_q
             next_l = b["constraint"] + b["mask"] * self.gamma * self.lyapunovNet_target(
                 b["next_state"] if self.lya_on_obs else b["next_center_pos"])
+            if self.barrier is not None:                                                         # BU :214-216
+                next_b = b["barrier_signal"] + b["mask"] * self.gamma * self.barrier_target(b["next_state"], next_a)
         qf1, qf2 = self.critic(b["state"], b["action"])                                          # :240-246
         qf1_loss, qf2_loss = F.mse_loss(qf1, next_q), F.mse_loss(qf2, next_q)
         lf_loss = F.mse_loss(self.lyapunovNet(b["state"] if self.lya_on_obs else b["center_pos"]), next_l)
         self._step(self.critic_optim, qf1_loss + qf2_loss, list(self.critic.parameters()))       # :249-251
         self._step(self.lyaNet_optim, lf_loss, list(self.lyapunovNet.parameters()))              # :253-255
+        if self.barrier is not None:                                                             # BU :225-227, :237-240
+            barrier_loss = F.mse_loss(self.barrier(b["state"], b["action"]), next_b)
+            self._step(self.barrier_optim, barrier_loss, list(self.barrier.parameters()))
         pi, log_pi, _ = self.policy.sample(b["state"], self.eps[1])                              # :258-261
         min_qf_pi = torch.min(*self.critic(b["state"], pi))
         policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                                 # :270
@@ -127,6 +138,7 @@ class GraphedUpdate:
         V = self.lyapunovNet(b["center_pos"]).detach()                                           # :382-383
         targs = (b["t"], b["next_t"]) if self.with_time else ()
         policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V, *targs), st)    # :384 -> :408-530
+        with_backup = with_backup and self.backup_policy is not None
         if with_backup:
             bpi, blog_pi, _ = self.backup_policy.sample(b["state"], self.eps[2])                 # :264-267
             bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
@@ -151,6 +163,8 @@ class GraphedUpdate:
         if self.target_update_interval == 1:                                                     # :315-317
             soft_update(self.critic_target, self.critic, self.tau)
             soft_update(self.lyapunovNet_target, self.lyapunovNet, self.tau)
+            if self.barrier is not None:
+                soft_update(self.barrier_target, self.barrier, self.tau)                         # BU :277
         with torch.no_grad():
             self.out.copy_(torch.stack([qf1_loss.reshape(()), qf2_loss.reshape(()), lf_loss.reshape(()),
                                         policy_loss_1.reshape(()), alpha_loss.reshape(()), self.alpha.reshape(())]))
@@ -158,10 +172,13 @@ class GraphedUpdate:
         return self.out
 
     # ------------------------------------------------------------------------------------------------
+    def _nets(self):
+        return [n for n in (self.critic, self.critic_target, self.lyapunovNet, self.lyapunovNet_target, self.policy,
+                            self.backup_policy, self.barrier, self.barrier_target) if n is not None]
+
     def _state_tensors(self):
         ts = []
-        for net in (self.critic, self.critic_target, self.lyapunovNet, self.lyapunovNet_target, self.policy,
-                    self.backup_policy):
+        for net in self._nets():
             ts += list(net.parameters())
         ts += [self.log_alpha, self.backup_log_alpha, self.alpha, self.backup_alpha, self.updates_dev,
                self.cstate.lambda_values, self.cstate.backup_lambda_values, self.cstate.augmented_term,
@@ -169,8 +186,8 @@ class GraphedUpdate:
         return ts
 
     def _optims(self):
-        return (self.critic_optim, self.lyaNet_optim, self.policy_optim, self.backup_policy_optim, self.alpha_optim,
-                self.backup_alpha_optim)
+        return [o for o in (self.critic_optim, self.lyaNet_optim, self.policy_optim, self.backup_policy_optim,
+                            self.alpha_optim, self.backup_alpha_optim, self.barrier_optim) if o is not None]
 
     def capture(self):
         """Warm-up on a side stream (lazy kernel attributes, allocator, Adam state), restore every tensor the update
@@ -192,8 +209,7 @@ class GraphedUpdate:
                     s_["exp_avg_sq"].zero_()
                 for v in opt._step_dev.values():
                     v.zero_()
-        for net in (self.critic, self.critic_target, self.lyapunovNet, self.lyapunovNet_target, self.policy,
-                    self.backup_policy):
+        for net in self._nets():
             for p in net.parameters():
                 torch.autograd.graph.increment_version(p)
         torch.cuda.synchronize()
@@ -212,6 +228,8 @@ class GraphedUpdate:
         next_state, mask, ...) as CUDA tensors or host arrays; ``eps`` = three [B, n_u] noise tensors or None (drawn
         from torch's CUDA generator, like ``Normal.rsample`` in the reference)."""
         names = ("state", "action", "reward", "constraint", "center_pos", "next_center_pos", "next_state", "mask")
+        if self.barrier is not None:     # BU / BP replay layout: barrier_signal after constraint (replay_memory.py:12)
+            names = names[:4] + ("barrier_signal",) + names[4:]
         if self.with_time:
             names = names + ("t", "next_t")
         for n, v in zip(names, batch):
@@ -230,8 +248,7 @@ class GraphedUpdate:
         if self.graph is None:
             self.capture()
         (self.graph if (with_backup or self.graph_nobackup is None) else self.graph_nobackup).replay()
-        for net in (self.critic, self.critic_target, self.lyapunovNet, self.lyapunovNet_target, self.policy,
-                    self.backup_policy):
+        for net in self._nets():
             for p in net.parameters():          # written through raw pointers inside the graph
                 torch.autograd.graph.increment_version(p)
         return self.out
@@ -282,10 +299,11 @@ class GraphedUpdate:
             nb = NODE_memory.sample(batch_size=n)
             dm = dynamics_model or self.dynamics_model
             to_dev = lambda v: v if torch.is_tensor(v) else torch.as_tensor(v, dtype=torch.float32, device=self.device)  # noqa: E731
-            s0, s1 = dm.get_state(to_dev(nb[0])), dm.get_state(to_dev(nb[6]))
+            off = 1 if self.barrier is not None else 0
+            s0, s1 = dm.get_state(to_dev(nb[0])), dm.get_state(to_dev(nb[6 + off]))
             if isinstance(s0, tuple):           # Pvtol: (state7, state6) -- the NODE is fitted on the six dynamic states
                 s0, s1 = s0[1], s1[1]
-            tb = to_dev(nb[8]).reshape(-1, 1) if self.with_time else None          # C :32: node_t_batch.unsqueeze(1)
+            tb = to_dev(nb[8 + off]).reshape(-1, 1) if self.with_time else None    # C :32: node_t_batch.unsqueeze(1)
             self.node_fit(s0, to_dev(nb[1]), s1, tb)
         with torch.no_grad():
             self.updates_dev.fill_(int(updates))

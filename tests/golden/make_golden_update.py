@@ -111,7 +111,25 @@ def _batch_P(gen, n, dm):
     return (f(obs), f(act), f(reward), f(cons), f(obs), f(nobs), f(nobs), f(mask), None, None)
 
 
+def _batch_BU(gen, n):
+    """BU minibatch: the Unicycle fields with barrier_signal (0 / -20 per hazard hit, BU unicycle_env.py:51-52) after
+    constraint (BU replay_memory.py:12)."""
+    b = list(_batch(gen, n))
+    sig = -20.0 * (torch.rand(n, generator=gen) < 0.15).double().numpy()
+    return tuple(b[:4] + [sig] + b[4:])
+
+
+def _batch_BP(gen, n, dm):
+    b = list(_batch_P(gen, n, dm))
+    sig = -0.1 * (torch.rand(n, generator=gen) < 0.15).double().numpy()       # BP pvtol_env.py:28-29
+    return tuple(b[:4] + [sig] + b[4:])
+
+
 VARIANT = {
+    "BP": dict(B=256, obs=11, act=2, lya_in=11, node=(6, 6, 12), low=[-3.5, -15.0], high=[3.5, 15.0], gamma_b=0.6, n_eps=3,
+               num_cbfs=1, mode="Pvtol"),
+    "BU": dict(B=128, obs=7, act=2, lya_in=2, node=(3, 3, 6), low=[-3.5, -12.0], high=[3.5, 12.0], gamma_b=5.0, n_eps=3,
+               num_cbfs=1, mode="Unicycle"),
     "P": dict(B=256, obs=11, act=2, lya_in=11, node=(6, 6, 12), low=[-3.5, -15.0], high=[3.5, 15.0], gamma_b=0.6, n_eps=7,
               num_cbfs=9, mode="Pvtol"),
     "U": dict(B=128, obs=7, act=2, lya_in=2, node=(3, 3, 6), low=[-3.5, -12.0], high=[3.5, 12.0], gamma_b=50.0, n_eps=3,
@@ -147,6 +165,15 @@ def main(tag="U"):
     a.backup_policy = model.GaussianPolicy(no, na, 256, space)
     for net in (a.critic, a.lyapunovNet, a.policy, a.backup_policy):
         _perturb_biases(net, gen)
+    nets_names = ["critic", "lyapunovNet", "policy", "backup_policy", "neural_ode_model"]
+    targets = ["critic_target", "lyapunovNet_target"]
+    if tag in ("BU", "BP"):      # learned barrier: its own net / target / optimiser (BU sac_cbf_clf.py:52-61); no backup controller
+        a.BarrierNet, a.BarrierNet_target = model.BarrierNetwork(no, na, 256), model.BarrierNetwork(no, na, 256)
+        _perturb_biases(a.BarrierNet, gen)
+        agent_mod.hard_update(a.BarrierNet_target, a.BarrierNet)
+        a.BarrierNet_optim = torch.optim.Adam(a.BarrierNet.parameters(), lr=a.critic_lyapunov_lr)
+        nets_names = ["critic", "lyapunovNet", "policy", "BarrierNet", "neural_ode_model"]
+        targets = ["critic_target", "lyapunovNet_target", "BarrierNet_target"]
     agent_mod.hard_update(a.critic_target, a.critic)
     agent_mod.hard_update(a.lyapunovNet_target, a.lyapunovNet)
     a.critic_optim = torch.optim.Adam(a.critic.parameters(), lr=a.critic_lyapunov_lr)
@@ -165,6 +192,8 @@ def main(tag="U"):
     a.neural_ode_model = model.NeuralODEModel(*V["node"])
     a.neural_ode_model_optimizer = torch.optim.Adam(a.neural_ode_model.parameters(), lr=1e-3)
     a.model_loss_func = agent_mod.PoseLoss()
+    if tag == "BP":
+        env.safety_operator_follow = 0.7
     if tag == "P":   # the env attributes P's constraint block reads (as in make_golden_constraints.case_P) + P's own knobs
         env.hazards_radius = 0.25
         env.hazard_locations = np.array([[-2.5, -2.5], [-2.5, 2.5], [0.0, -3.5], [0.0, 3.5], [-4.5, 0.0]])
@@ -173,8 +202,9 @@ def main(tag="U"):
         a.backup_update_interval, a.backup_augmented_term = 4, 1.0      # default 20: 4 puts three backup updates in the trace
     dm = dyn_mod.DynamicsModel(env, _Args())
 
-    init = {k: _sd(getattr(a, k)) for k in ("critic", "lyapunovNet", "policy", "backup_policy", "neural_ode_model")}
-    mkb = {"U": _batch, "C": _batch_C, "P": lambda g_, n_: _batch_P(g_, n_, dm)}[tag]
+    init = {k: _sd(getattr(a, k)) for k in nets_names}
+    mkb = {"U": _batch, "BU": _batch_BU, "C": _batch_C, "P": lambda g_, n_: _batch_P(g_, n_, dm),
+           "BP": lambda g_, n_: _batch_BP(g_, n_, dm)}[tag]
     batches = [mkb(gen, B) for _ in range(N_UPDATES)]
     # U / C: 8, 16: multipliers due; 10: NODE fit due.  P: 28, 32, 36 update the backup controller (interval 4), 32: both
     # multiplier sets due (backup: every 8 * 4), 30: NODE fit
@@ -199,14 +229,13 @@ def main(tag="U"):
     try:
         for i, u in enumerate(updates_list):
             queue.extend(eps[i])             # next_state sample, pi, backup_pi (+ C: the two re-samples inside the rollouts)
-            returns.append(a.update_parameters(mem, B, u, dm, node_mem, 10, 1) if tag == "P" else
+            returns.append(a.update_parameters(mem, B, u, dm, node_mem, 10, 1) if tag in ("P", "BP") else
                            a.update_parameters(mem, B, u, dm, node_mem, 10))
             lam_trace.append([float(v) for v in a.lambda_values])
-            blam_trace.append([float(v) for v in a.backup_lambda_values])
+            blam_trace.append([float(v) for v in a.backup_lambda_values] if tag not in ("BU", "BP") else [0.0])
             rho_trace.append(float(a.augmented_term))
             if i == 0:
-                after_first = {k: _sd(getattr(a, k)) for k in ("critic", "critic_target", "lyapunovNet", "policy",
-                                                               "backup_policy")}
+                after_first = {k: _sd(getattr(a, k)) for k in nets_names[:-1] + ["critic_target"]}
             assert not queue
     finally:
         tdn._standard_normal = orig
@@ -216,18 +245,17 @@ def main(tag="U"):
         "B": B, "node_N": NODE_N, "updates": updates_list, "init": init, "batches": [to_t(b) for b in batches],
         "node_batches": [to_t(b) for b in node_batches], "eps": eps,
         "returns": torch.tensor(returns, dtype=torch.float64),        # qf1, qf2, lf, policy_loss_1, alpha_loss, alpha
-        "final": {k: _sd(getattr(a, k)) for k in ("critic", "critic_target", "lyapunovNet", "lyapunovNet_target", "policy",
-                                                   "backup_policy", "neural_ode_model")},
+        "final": {k: _sd(getattr(a, k)) for k in nets_names + targets},
         "log_alpha": a.log_alpha.detach().clone(), "backup_log_alpha": a.backup_log_alpha.detach().clone(),
         "lambda_values": [float(v) for v in a.lambda_values],
-        "backup_lambda_values": [float(v) for v in a.backup_lambda_values],
+        "backup_lambda_values": [float(v) for v in getattr(a, "backup_lambda_values", [])],
         "augmented_term": float(a.augmented_term),
         "backup_augmented_term": float(getattr(a, "backup_augmented_term", 0.0)),
         "lambda_trace": torch.tensor(lam_trace, dtype=torch.float64),
         "backup_lambda_trace": torch.tensor(blam_trace, dtype=torch.float64),
         "rho_trace": torch.tensor(rho_trace, dtype=torch.float64), "after_first": after_first,
         "consts": {"dt": 0.02, "gamma_b": V["gamma_b"],
-                   "hazards": env.hazard_locations if tag == "P" else env.hazards_locations,
+                   "hazards": env.hazard_locations if tag == "P" else getattr(env, "hazards_locations", None),
                    "hazards_radius": env.hazards_radius, "safety_operator_follow": 0.7, "operator_dist": 0.001,
                    "y_max": 13.0, "y_min": -13.0, "backup_update_interval": 4,
                    "l_p": 0.03, "gamma": 0.99, "tau": 0.005, "alpha": 0.2, "target_entropy": -float(na), "lr": 3e-4,
@@ -239,5 +267,5 @@ def main(tag="U"):
 
 
 if __name__ == "__main__":
-    for tag_ in (sys.argv[1:] or ["U", "C", "P"]):
+    for tag_ in (sys.argv[1:] or ["U", "C", "P", "BU", "BP"]):
         main(tag_)

@@ -44,7 +44,9 @@ class _Env:
         self.dynamics_mode = mode
 
 
-SHAPES = {"P": dict(obs=11, act=2, lya=11, node=(6, 6, 12), mode="Pvtol"),
+SHAPES = {"BP": dict(obs=11, act=2, lya=11, node=(6, 6, 12), mode="Pvtol"),
+          "BU": dict(obs=7, act=2, lya=2, node=(3, 3, 6), mode="Unicycle"),
+          "P": dict(obs=11, act=2, lya=11, node=(6, 6, 12), mode="Pvtol"),
           "U": dict(obs=7, act=2, lya=2, node=(3, 3, 6), mode="Unicycle"),
           "C": dict(obs=10, act=1, lya=4, node=(12, 10), mode="SimulatedCars")}
 
@@ -57,14 +59,18 @@ def _build(g, nb, tag):
             "lyapunovNet": nb.LyaNetwork(S["lya"], 256), "lyapunovNet_target": nb.LyaNetwork(S["lya"], 256),
             "policy": nb.GaussianPolicy(no, na, 256, sp), "backup_policy": nb.GaussianPolicy(no, na, 256, sp),
             "neural_ode_model": nb.NeuralODEModel(*S["node"])}
-    for name in ("critic", "lyapunovNet", "policy", "backup_policy", "neural_ode_model"):
+    if tag in ("BU", "BP"):
+        del nets["backup_policy"]
+        nets["BarrierNet"], nets["BarrierNet_target"] = nb.BarrierNetwork(no, na, 256), nb.BarrierNetwork(no, na, 256)
+        nets["BarrierNet_target"].load_state_dict(g["init"]["BarrierNet"])
+    for name in g["init"]:
         nets[name].load_state_dict(g["init"][name])
     nets["critic_target"].load_state_dict(g["init"]["critic"])
     nets["lyapunovNet_target"].load_state_dict(g["init"]["lyapunovNet"])
     return {n: m.to("cuda") for n, m in nets.items()}
 
 
-@pytest.mark.parametrize("tag", ["U", "C", "P"])
+@pytest.mark.parametrize("tag", ["U", "C", "P", "BU", "BP"])
 def test_graphed_update_matches_reference_update_parameters(tag, golden_dir):
     import nlbac_b200 as nb
     C = nb.constraints
@@ -76,14 +82,35 @@ def test_graphed_update_matches_reference_update_parameters(tag, golden_dir):
     common = dict(obs_dim=S["obs"], act_dim=S["act"], center_pos_num=S["lya"], gamma=k["gamma"], tau=k["tau"],
                   alpha=k["alpha"], lr=k["lr"], critic_lyapunov_lr=k["critic_lr"], node_lr=k["node_lr"],
                   node_graph_batch=g["node_N"])
-    args = (nets["critic"], nets["critic_target"], lya, nets["lyapunovNet_target"], nets["policy"], nets["backup_policy"],
-            node, dm, B)
+    args = (nets["critic"], nets["critic_target"], lya, nets["lyapunovNet_target"], nets["policy"],
+            nets.get("backup_policy"), node, dm, B)
     if tag == "U":
         kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_locations=k["hazards"], hazards_radius=k["hazards_radius"],
                   l_p=k["l_p"], batch_size=B)
         upd = nb.GraphedUpdate(
             *args, primary=lambda s, pi, V: C.unicycle_required_matrix(node, lya, s, pi, V, **kw),
             backup=lambda s, pi: C.unicycle_required_matrix(node, None, s, pi, None, **kw), num_constraints=8, **common)
+    elif tag == "BU":   # learned barrier: no backup controller, barrier net + target, no CBF/CLF ratio, one re-sample (eps[3])
+        kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], l_p=k["l_p"], batch_size=B)
+        h = {}
+        upd = nb.GraphedUpdate(
+            *args,
+            primary=lambda s, pi, V: C.barrier_unicycle_required_matrix(
+                node, lya, nets["BarrierNet"], nets["policy"], dm, h["u"].buf["state"], s, pi, V, eps_next=h["u"].eps[3], **kw),
+            backup=None, num_constraints=2, use_ratio=False, n_extra_eps=1, barrier=nets["BarrierNet"],
+            barrier_target=nets["BarrierNet_target"], **common)
+        h["u"] = upd
+    elif tag == "BP":   # learned barrier on Pvtol: BU's structure + the Lyapunov TD loss on observations, ratio floor 0.002
+        kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], safety_operator_follow=k["safety_operator_follow"], batch_size=B)
+        h = {}
+        upd = nb.GraphedUpdate(
+            *args,
+            primary=lambda s, pi, V: C.barrier_pvtol_required_matrix(
+                node, lya, nets["BarrierNet"], nets["policy"], dm, h["u"].buf["state"], s, pi, V, eps_next=h["u"].eps[3], **kw),
+            backup=None, num_constraints=2, ratio_floor=0.002, n_extra_eps=1, barrier=nets["BarrierNet"],
+            barrier_target=nets["BarrierNet_target"], lya_on_obs=True, node_n_s=6, node_n_u=2, node_fit_max_episode=100,
+            **common)
+        h["u"] = upd
     elif tag == "P":   # Pvtol: Lyapunov TD loss on the observations, backup controller every 4th update (two graphs), its own
         # rho; both rollouts re-sample their policy twice (eps[3:5] primary, eps[5:7] backup)
         kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazard_locations=k["hazards"], hazards_radius=k["hazards_radius"],
@@ -118,6 +145,8 @@ def test_graphed_update_matches_reference_update_parameters(tag, golden_dir):
     got, lam_err = [], []
     for i, u in enumerate(g["updates"]):
         e = [x.cuda() for x in g["eps"][i]]
+        if tag in ("BU", "BP"):  # [next, pi, re-sample inside the block] -> buffers 0, 1, (2 unused), 3
+            e = [e[0], e[1], torch.zeros_like(e[0]), e[2]]
         if tag == "P":   # reference call order [next, pi, prim1, prim2 (, backup pi, b1, b2)] -> buffer order of GraphedUpdate
             zz = torch.zeros_like(e[0])
             e = [e[0], e[1], e[4] if len(e) == 7 else zz, e[2], e[3]] + ([e[5], e[6]] if len(e) == 7 else [zz, zz])
