@@ -1,6 +1,7 @@
 // Shared device/host helpers for the sm_100a NLBAC kernels.
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <stdint.h>
 #include <stdio.h>
 
@@ -25,6 +26,15 @@ int cuda_fail(cudaError_t e, const char* what);
       return -1;                          \
     }                                     \
   } while (0)
+
+// NVTX range around an entry point / a kernel launch: shows up on an Nsight timeline, a no-op (one
+// branch on a null function pointer) when no tool is attached.  Header-only NVTX3: resolved with dlopen at first use.
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 __host__ __device__ constexpr int round_up(int x, int m) { return (x + m - 1) / m * m; }
 

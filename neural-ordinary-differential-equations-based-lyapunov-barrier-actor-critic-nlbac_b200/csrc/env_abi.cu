@@ -285,6 +285,7 @@ extern "C" {
 
 int nlbac_env_unicycle_reset(double* state, double* last_goal_dist, int32_t* episode_step, const uint8_t* mask,
                              int64_t E, double* obs, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:env_unicycle_reset");
   NLBAC_REQUIRE(state && last_goal_dist && episode_step && E >= 0, "bad arguments");
   if (E == 0) return 0;
   env_unicycle_reset_kernel<<<env_grid(E, 256), 256, 0, (cudaStream_t)stream>>>(state, last_goal_dist, episode_step,
@@ -297,6 +298,7 @@ int nlbac_env_unicycle_step(double* state, double* last_goal_dist, int32_t* epis
                             int64_t E, double* obs, double* reward, double* constraint, double* center,
                             double* next_center, uint8_t* done, uint8_t* goal_met, int32_t* num_safety_violation,
                             double* safety_cost, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:env_unicycle_step");
   NLBAC_REQUIRE(state && last_goal_dist && episode_step && action && obs && reward && constraint && center &&
                     next_center && done && goal_met && num_safety_violation && safety_cost && E >= 0,
                 "bad arguments");
@@ -310,6 +312,7 @@ int nlbac_env_unicycle_step(double* state, double* last_goal_dist, int32_t* epis
 
 int nlbac_env_cars_reset(double* state, double* t, int32_t* episode_step, const double* vel_noise, const uint8_t* mask,
                          int64_t E, double* obs, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:env_cars_reset");
   NLBAC_REQUIRE(state && t && episode_step && vel_noise && E >= 0, "bad arguments");
   if (E == 0) return 0;
   env_cars_reset_kernel<<<env_grid(E, 256), 256, 0, (cudaStream_t)stream>>>(state, t, episode_step, vel_noise, mask, E,
@@ -322,6 +325,7 @@ int nlbac_env_cars_step(double* state, double* t, int32_t* episode_step, const d
                         double* reward, double* constraint, double* previous_positions, double* next_positions,
                         uint8_t* done, uint8_t* reached, int32_t* num_safety_violation, double* safety_cost,
                         void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:env_cars_step");
   NLBAC_REQUIRE(state && t && episode_step && action && obs && reward && constraint && previous_positions &&
                     next_positions && done && reached && num_safety_violation && safety_cost && E >= 0,
                 "bad arguments");
@@ -335,6 +339,7 @@ int nlbac_env_cars_step(double* state, double* t, int32_t* episode_step, const d
 
 int nlbac_env_pvtol_reset(double* state, int32_t* episode_step, const uint8_t* mask, int64_t E, double* obs,
                           void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:env_pvtol_reset");
   NLBAC_REQUIRE(state && episode_step && E >= 0, "bad arguments");
   if (E == 0) return 0;
   env_pvtol_reset_kernel<<<env_grid(E, 256), 256, 0, (cudaStream_t)stream>>>(state, episode_step, mask, E, obs);
@@ -345,6 +350,7 @@ int nlbac_env_pvtol_reset(double* state, int32_t* episode_step, const uint8_t* m
 int nlbac_env_pvtol_step(double* state, int32_t* episode_step, const double* action, int64_t E, double* obs,
                          double* reward, double* constraint, double* lya_pre_term, uint8_t* done, uint8_t* goal_met,
                          int32_t* num_safety_violation, double* safety_cost, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:env_pvtol_step");
   NLBAC_REQUIRE(state && episode_step && action && obs && reward && constraint && lya_pre_term && done && goal_met &&
                     num_safety_violation && safety_cost && E >= 0,
                 "bad arguments");

@@ -101,6 +101,7 @@ int nlbac_mlp_workspace_bytes(const nlbac_mlp_desc* desc, int64_t B, size_t* act
 
 int nlbac_mlp_fwd(const nlbac_mlp_desc* desc, const float* const* params, const float* x, int64_t B, float* out,
                   float* act, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:mlp_fwd");
   if (int rc = check_mlp(desc)) return rc;
   NLBAC_REQUIRE(B >= 0, "negative batch");
   if (B == 0) return 0;
@@ -108,16 +109,22 @@ int nlbac_mlp_fwd(const nlbac_mlp_desc* desc, const float* const* params, const 
   MlpArgs a;
   a.W1 = params[0]; a.b1 = params[1]; a.W2 = params[2]; a.b2 = params[3]; a.W3 = params[4]; a.b3 = params[5];
   a.x = x; a.out = out; a.act = act; a.B = B; a.n_in = desc->n_in; a.H = desc->hidden; a.n_out = desc->n_out;
-  const size_t smem = (size_t)(MLP_TM * MLP_MAX_IN + 2 * MLP_TM * a.H) * 4;
-  NLBAC_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const unsigned grid = (unsigned)((B + MLP_TM - 1) / MLP_TM);
-  mlp_fwd_kernel<<<grid, MLP_NT, smem, (cudaStream_t)stream>>>(a);
-  NLBAC_CUDA(cudaGetLastError());
+  // row tile: 8 rows per CTA once that fills the SMs, 2 rows per CTA below (B = 128 -> 64 CTAs instead of 16)
+  auto launch = [&]<int TM>() -> int {
+    const size_t smem = (size_t)(TM * MLP_MAX_IN + 2 * TM * a.H) * 4;
+    NLBAC_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<TM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mlp_fwd_kernel<TM><<<(unsigned)((B + TM - 1) / TM), MLP_NT, smem, (cudaStream_t)stream>>>(a);
+    NLBAC_CUDA(cudaGetLastError());
+    return 0;
+  };
+  if (int rc = (B < MLP_SMALL_B) ? launch.template operator()<MLP_TM_SMALL>() : launch.template operator()<MLP_TM_LARGE>())
+    return rc;
   return 0;
 }
 
 int nlbac_mlp_bwd(const nlbac_mlp_desc* desc, const float* const* params, const float* x, int64_t B, const float* act,
                   const float* grad_out, float* grad_x, float* const* grad_params, void* ws, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:mlp_bwd");
   if (int rc = check_mlp(desc)) return rc;
   NLBAC_REQUIRE(B >= 0, "negative batch");
   NLBAC_REQUIRE(B == 0 || (params && x && act && grad_out && ws), "null pointer");
@@ -135,10 +142,15 @@ int nlbac_mlp_bwd(const nlbac_mlp_desc* desc, const float* const* params, const 
   a.act = act; a.grad_out = grad_out; a.grad_x = grad_x; a.B = B; a.n_in = NI; a.H = H; a.n_out = NO;
   a.d1 = static_cast<float*>(ws);
   a.d2 = a.d1 + (size_t)B * H;
-  const size_t smem = (size_t)(MLP_TM * MLP_MAX_OUT + 2 * MLP_TM * H) * 4;
-  NLBAC_CUDA(cudaFuncSetAttribute(mlp_bwd_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  mlp_bwd_rows_kernel<<<(unsigned)((B + MLP_TM - 1) / MLP_TM), MLP_NT, smem, st>>>(a);
-  NLBAC_CUDA(cudaGetLastError());
+  auto launch = [&]<int TM>() -> int {
+    const size_t smem = (size_t)(TM * MLP_MAX_OUT + 2 * TM * H) * 4;
+    NLBAC_CUDA(cudaFuncSetAttribute(mlp_bwd_rows_kernel<TM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mlp_bwd_rows_kernel<TM><<<(unsigned)((B + TM - 1) / TM), MLP_NT, smem, st>>>(a);
+    NLBAC_CUDA(cudaGetLastError());
+    return 0;
+  };
+  if (int rc = (B < MLP_SMALL_B) ? launch.template operator()<MLP_TM_SMALL>() : launch.template operator()<MLP_TM_LARGE>())
+    return rc;
   if (grad_params) {
     const float* h1 = act;
     const float* h2 = act + (size_t)B * H;
@@ -181,6 +193,7 @@ int nlbac_mlp_bwd(const nlbac_mlp_desc* desc, const float* const* params, const 
 int nlbac_policy_head_fwd(const float* mean_logstd, const float* eps, const float* action_scale,
                           const float* action_bias, int64_t B, int n_u, float* action, float* log_prob,
                           float* mean_out, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:policy_head_fwd");
   NLBAC_REQUIRE(mean_logstd && eps && action_scale && action_bias && action && log_prob && mean_out, "null pointer");
   NLBAC_REQUIRE(B >= 0 && n_u >= 1 && 2 * n_u <= MLP_MAX_OUT, "bad sizes (B=%lld n_u=%d)", (long long)B, n_u);
   if (B == 0) return 0;
@@ -193,6 +206,7 @@ int nlbac_policy_head_fwd(const float* mean_logstd, const float* eps, const floa
 int nlbac_policy_head_bwd(const float* mean_logstd, const float* eps, const float* action_scale, int64_t B, int n_u,
                           const float* grad_action, const float* grad_log_prob, const float* grad_mean_out,
                           float* grad_mean_logstd, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:policy_head_bwd");
   NLBAC_REQUIRE(mean_logstd && eps && action_scale && grad_mean_logstd, "null pointer");
   NLBAC_REQUIRE(B >= 0 && n_u >= 1 && 2 * n_u <= MLP_MAX_OUT, "bad sizes (B=%lld n_u=%d)", (long long)B, n_u);
   if (B == 0) return 0;

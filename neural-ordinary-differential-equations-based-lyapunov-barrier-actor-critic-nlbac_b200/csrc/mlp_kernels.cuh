@@ -12,7 +12,9 @@
 
 namespace nlbac {
 
-constexpr int MLP_TM = 8;         // rows per CTA
+constexpr int MLP_TM_LARGE = 8;   // rows per CTA (large batches); small batches use MLP_TM_SMALL so that B = 128 / 256
+constexpr int MLP_TM_SMALL = 2;   // still spreads over 64 / 128 of the 148 SMs instead of 16 / 32
+constexpr long long MLP_SMALL_B = 148 * 8;   // below this many rows the 8-row tiling leaves SMs idle
 constexpr int MLP_NT = 256;       // threads per CTA
 constexpr int MLP_MAX_OUT = 8;    // output columns (twin-Q: 1, policy: 2*n_u <= 4)
 constexpr int MLP_MAX_IN = 32;
@@ -27,6 +29,7 @@ struct MlpArgs {
 };
 
 // dynamic smem: x[TM][n_in] | h1[TM][H] | h2[TM][H]
+template <int MLP_TM>
 __global__ void __launch_bounds__(MLP_NT) mlp_fwd_kernel(MlpArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int H = a.H, NI = a.n_in, NO = a.n_out;
@@ -57,15 +60,19 @@ __global__ void __launch_bounds__(MLP_NT) mlp_fwd_kernel(MlpArgs a) {
     for (int r = 0; r < MLP_TM; ++r) h1[r * H + j] = fmaxf(acc[r], 0.f);
   }
   __syncthreads();
-  // layer 2: thread j walks row j of W2 (each 128-byte line is fetched once and consumed from L1)
+  // layer 2: thread j walks row j of W2 (each 128-byte line is fetched once and consumed from L1).  Measured at B = 128
+  // (torch.profiler on a GraphedUpdate replay, round 2): 8-row tiles 18.7 us -> 2-row tiles 14.2 us; deeper unrolling
+  // neutral; one WARP per output with coalesced row reads + shuffle reductions 25.7 us (32 dependent reductions per
+  // warp cost more than the wavefronts they save) -- dropped.
   for (int j = tid; j < H; j += MLP_NT) {
     float acc[MLP_TM];
     const float bj = a.b2[j];
 #pragma unroll
     for (int r = 0; r < MLP_TM; ++r) acc[r] = bj;
     const float4* w = reinterpret_cast<const float4*>(a.W2 + (size_t)j * H);
+#pragma unroll 8
     for (int k4 = 0; k4 < H / 4; ++k4) {
-      const float4 wv = w[k4];
+      const float4 wv = __ldg(w + k4);
 #pragma unroll
       for (int r = 0; r < MLP_TM; ++r) {
         const float4 hv = *reinterpret_cast<const float4*>(h1 + r * H + 4 * k4);
@@ -109,6 +116,7 @@ struct MlpBwdArgs {
 };
 
 // dynamic smem: g[TM][MAX_OUT] | d2[TM][H] | d1[TM][H]
+template <int MLP_TM>
 __global__ void __launch_bounds__(MLP_NT) mlp_bwd_rows_kernel(MlpBwdArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int H = a.H, NI = a.n_in, NO = a.n_out;
@@ -151,8 +159,9 @@ __global__ void __launch_bounds__(MLP_NT) mlp_bwd_rows_kernel(MlpBwdArgs a) {
     float acc[MLP_TM];
 #pragma unroll
     for (int r = 0; r < MLP_TM; ++r) acc[r] = 0.f;
+#pragma unroll 8
     for (int j = 0; j < H; ++j) {
-      const float wv = a.W2[(size_t)j * H + k];
+      const float wv = __ldg(a.W2 + (size_t)j * H + k);
 #pragma unroll
       for (int r = 0; r < MLP_TM; ++r) acc[r] = fmaf(s2[r * H + j], wv, acc[r]);
     }

@@ -57,9 +57,12 @@ struct KTimer {
   std::vector<Rec> recs;
 };
 static KTimer g_kt;
+static const char* const KSLOT_NAME[4] = {"nlbac:node_solve_fwd", "nlbac:node_reverse_sweep", "nlbac:node_dw_gemm",
+                                          "nlbac:node_grad_fold"};
 struct KScope {
   int slot; cudaStream_t st; cudaEvent_t e0 = nullptr, e1 = nullptr; bool on;
-  KScope(int slot_, cudaStream_t st_) : slot(slot_), st(st_), on(g_kt.on) {
+  NvtxRange nvtx;
+  KScope(int slot_, cudaStream_t st_) : slot(slot_), st(st_), on(g_kt.on), nvtx(KSLOT_NAME[slot_ & 3]) {
     if (on) {
       on = cudaEventCreate(&e0) == cudaSuccess && cudaEventCreate(&e1) == cudaSuccess;
       if (on) cudaEventRecord(e0, st);

@@ -410,6 +410,7 @@ extern "C" {
 
 int nlbac_constraints4_fwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
                            const float* e, const float* V, const float* Vnext, int64_t B, float* req, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:constraints4_fwd");
   if (int rc = check_constraint(desc)) return rc;
   NLBAC_REQUIRE(a && b && V && Vnext && req, "null pointer");
   NLBAC_REQUIRE((desc->kind != NLBAC_CONSTRAINT_CARS && desc->kind != NLBAC_CONSTRAINT_PVTOL) || c,
@@ -427,6 +428,7 @@ int nlbac_constraints4_fwd(const nlbac_constraint_desc* desc, const float* a, co
 int nlbac_constraints4_bwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
                            const float* e, const float* V, const float* Vnext, int64_t B, const float* grad_req,
                            float* grad_b, float* grad_c, float* grad_e, float* grad_Vnext, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:constraints4_bwd");
   if (int rc = check_constraint(desc)) return rc;
   NLBAC_REQUIRE(a && b && V && Vnext && grad_req && grad_b && grad_Vnext, "null pointer");
   NLBAC_REQUIRE((desc->kind != NLBAC_CONSTRAINT_CARS && desc->kind != NLBAC_CONSTRAINT_PVTOL) || (c && grad_c),
@@ -441,6 +443,7 @@ int nlbac_constraints4_bwd(const nlbac_constraint_desc* desc, const float* a, co
 
 int nlbac_constraints_fwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
                           const float* V, const float* Vnext, int64_t B, float* req, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:constraints_fwd");
   NLBAC_REQUIRE(desc == nullptr || desc->kind != NLBAC_CONSTRAINT_PVTOL, "pvtol constraints take four states: use nlbac_constraints4_fwd");
   return nlbac_constraints4_fwd(desc, a, b, c, nullptr, V, Vnext, B, req, stream);
 }
@@ -448,11 +451,13 @@ int nlbac_constraints_fwd(const nlbac_constraint_desc* desc, const float* a, con
 int nlbac_constraints_bwd(const nlbac_constraint_desc* desc, const float* a, const float* b, const float* c,
                           const float* V, const float* Vnext, int64_t B, const float* grad_req, float* grad_b,
                           float* grad_c, float* grad_Vnext, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:constraints_bwd");
   NLBAC_REQUIRE(desc == nullptr || desc->kind != NLBAC_CONSTRAINT_PVTOL, "pvtol constraints take four states: use nlbac_constraints4_bwd");
   return nlbac_constraints4_bwd(desc, a, b, c, nullptr, V, Vnext, B, grad_req, grad_b, grad_c, nullptr, grad_Vnext, stream);
 }
 
 int nlbac_lookahead_fwd(const float* state, int n_s, float l_p, int64_t B, float* p, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:lookahead_fwd");
   NLBAC_REQUIRE(state && p && n_s >= 3 && B >= 0, "bad arguments");
   if (B == 0) return 0;
   lookahead_fwd_kernel<<<tail_grid(B, 256), 256, 0, (cudaStream_t)stream>>>(state, n_s, l_p, B, p);
@@ -461,6 +466,7 @@ int nlbac_lookahead_fwd(const float* state, int n_s, float l_p, int64_t B, float
 }
 int nlbac_lookahead_bwd(const float* state, int n_s, float l_p, int64_t B, const float* grad_p, float* grad_state,
                         void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:lookahead_bwd");
   NLBAC_REQUIRE(state && grad_p && grad_state && n_s >= 3 && B >= 0, "bad arguments");
   if (B == 0) return 0;
   lookahead_bwd_kernel<<<tail_grid(B, 256), 256, 0, (cudaStream_t)stream>>>(state, n_s, l_p, B, grad_p, grad_state);
@@ -469,6 +475,7 @@ int nlbac_lookahead_bwd(const float* state, int n_s, float l_p, int64_t B, const
 }
 
 int nlbac_get_state(int env, const float* obs, int64_t B, float* state, float* state_dyn, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:get_state");
   NLBAC_REQUIRE(env >= NLBAC_ENV_UNICYCLE && env <= NLBAC_ENV_PVTOL, "unknown env %d", env);
   NLBAC_REQUIRE(obs && state && B >= 0, "bad arguments");
   if (B == 0) return 0;
@@ -477,6 +484,7 @@ int nlbac_get_state(int env, const float* obs, int64_t B, float* state, float* s
   return 0;
 }
 int nlbac_get_obs_fwd(int env, const float* state, int64_t B, float* obs, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:get_obs_fwd");
   NLBAC_REQUIRE(env >= NLBAC_ENV_UNICYCLE && env <= NLBAC_ENV_PVTOL, "unknown env %d", env);
   NLBAC_REQUIRE(state && obs && B >= 0, "bad arguments");
   if (B == 0) return 0;
@@ -485,6 +493,7 @@ int nlbac_get_obs_fwd(int env, const float* state, int64_t B, float* obs, void* 
   return 0;
 }
 int nlbac_get_obs_bwd(int env, const float* state, int64_t B, const float* grad_obs, float* grad_state, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:get_obs_bwd");
   NLBAC_REQUIRE(env >= NLBAC_ENV_UNICYCLE && env <= NLBAC_ENV_PVTOL, "unknown env %d", env);
   NLBAC_REQUIRE(state && grad_obs && grad_state && B >= 0, "bad arguments");
   if (B == 0) return 0;
@@ -495,6 +504,7 @@ int nlbac_get_obs_bwd(int env, const float* state, int64_t B, const float* grad_
 
 int nlbac_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n, int step, float lr,
                     float beta1, float beta2, float eps, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:adam_step");
   NLBAC_REQUIRE(param && grad && exp_avg && exp_avg_sq && n >= 0 && step >= 1, "bad arguments");
   if (n == 0) return 0;
   const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
@@ -504,6 +514,7 @@ int nlbac_adam_step(float* param, const float* grad, float* exp_avg, float* exp_
   return 0;
 }
 int nlbac_replay_gather(const float* ring, int width, const int64_t* idx, int64_t B, float* out, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:replay_gather");
   NLBAC_REQUIRE(width >= 1 && B >= 0, "bad sizes");
   if (B == 0) return 0;
   NLBAC_REQUIRE(ring && idx && out, "null pointer");
@@ -516,6 +527,7 @@ int nlbac_replay_gather(const float* ring, int width, const int64_t* idx, int64_
 int nlbac_adam_step_multi(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
                           float* const* exp_avg_sq, const int64_t* numels, int step, float lr, float beta1,
                           float beta2, float eps, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:adam_step_multi");
   NLBAC_REQUIRE(n_tensors >= 0 && n_tensors <= NLBAC_MAX_TENSORS, "n_tensors=%d (max %d)", n_tensors, NLBAC_MAX_TENSORS);
   NLBAC_REQUIRE(params && grads && exp_avg && exp_avg_sq && numels && step >= 1, "bad arguments");
   if (n_tensors == 0) return 0;
@@ -537,6 +549,7 @@ int nlbac_adam_step_multi(int n_tensors, float* const* params, const float* cons
 int nlbac_adam_step_multi_dev(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
                               float* const* exp_avg_sq, const int64_t* numels, int* step_dev, int bump, float lr,
                               float beta1, float beta2, float eps, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:adam_step_multi_dev");
   NLBAC_REQUIRE(n_tensors >= 0 && n_tensors <= NLBAC_MAX_TENSORS, "n_tensors=%d (max %d)", n_tensors, NLBAC_MAX_TENSORS);
   NLBAC_REQUIRE(params && grads && exp_avg && exp_avg_sq && numels && step_dev, "bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
@@ -560,6 +573,7 @@ int nlbac_adam_step_multi_dev(int n_tensors, float* const* params, const float* 
 }
 int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* const* sources, const int64_t* numels,
                             float tau, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:soft_update_multi");
   NLBAC_REQUIRE(n_tensors >= 0 && n_tensors <= NLBAC_MAX_TENSORS, "n_tensors=%d (max %d)", n_tensors, NLBAC_MAX_TENSORS);
   NLBAC_REQUIRE(targets && sources && numels, "bad arguments");
   if (n_tensors == 0) return 0;
@@ -576,6 +590,7 @@ int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* c
   return 0;
 }
 int nlbac_soft_update(float* target, const float* source, int64_t n, float tau, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:soft_update");
   NLBAC_REQUIRE(target && source && n >= 0, "bad arguments");
   if (n == 0) return 0;
   soft_update_kernel<<<tail_grid(n, 256), 256, 0, (cudaStream_t)stream>>>(target, source, n, tau);
