@@ -45,7 +45,7 @@
 extern "C" {
 #endif
 
-#define NLBAC_ABI_VERSION 1
+#define NLBAC_ABI_VERSION 2   /* 2: nlbac_node_tc_bwd_workspace_bytes takes the precision tier; nlbac_comm_*, *_noalloc, umma_peak_probe */
 
 /* model kinds */
 #define NLBAC_KIND_AFFINE   0   /* x' = f_net(x) + g_net(x) u      (U, P, BU, BP) */

@@ -19,7 +19,7 @@ def test_library_exports_every_declared_symbol(pkg):
     assert len(names) >= 10
     for n in names:
         assert hasattr(L, n), n
-    assert L.nlbac_abi_version() == 1
+    assert L.nlbac_abi_version() == 2
 
 
 def test_descriptor_queries_match_reference_shapes(pkg):
