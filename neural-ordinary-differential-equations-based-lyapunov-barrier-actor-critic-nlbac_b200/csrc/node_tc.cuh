@@ -127,13 +127,14 @@ __host__ __device__ constexpr int tmem_cols(int groups, int tmem_groups, int nim
 template <class C, bool SPLIT>
 struct TcFwdGeom {
   using T = TcCfg<C>;
-  static constexpr int GS = SPLIT ? 1 : 2;         // groups whose activation image lives in shared memory
-  static constexpr int GT = SPLIT ? 0 : 1;         // groups whose activation operand lives in tensor memory
+  static constexpr int GS = SPLIT ? 1 : 2;         // groups whose activation image(s) live in shared memory
+  static constexpr int GT = 1;                     // groups whose activation operand(s) live in tensor memory (3xTF32: the
+                                                   // hi and lo blocks, 2 x 128 columns -> 2 accumulators + 2 blocks = 512)
   static constexpr int G = GS + GT;                // groups (tiles in flight) per CTA
   static constexpr int NT = G * 128;               // no producer warp: see ring_prefetch
-  static constexpr int TMEM_COLS = tmem_cols(G, GT);
-  static constexpr int NSLOT = 2;
   static constexpr int NIMG = SPLIT ? 2 : 1;       // activation images per group (hi, lo)
+  static constexpr int TMEM_COLS = tmem_cols(G, GT, NIMG);
+  static constexpr int NSLOT = 2;
   static constexpr int OFF_A = 0;                                   // bytes
   static constexpr int OFF_W = OFF_A + GS * NIMG * T::A_BYTES;
   static constexpr int OFF_RES = OFF_W + NSLOT * T::W_BYTES;
@@ -246,6 +247,52 @@ __device__ __forceinline__ void tc_batches(uint32_t tacc, F&& body, P&& post = P
     for (int u = 0; u < REM; ++u) body(NFULL, u, 4 * NFULL + u, v[u]);
     post(NFULL);
   }
+  }
+}
+
+// Compact form of tc_batches for kernels bound by INSTRUCTION FETCH (the 3xTF32 reverse sweep: 193 KB of SASS, ncu
+// stalled_no_instruction 5.7 per issued instruction): a rolled loop over PAIRS of column groups, so every epilogue body
+// is inlined twice (+ once for an odd tail) instead of five times.  Same body / post contract: q = g8 / 4 (mask word),
+// u = g8 % 4 (byte inside it), post(q) once after the last group of word q.
+template <int NG8, bool LOAD, class F, class P = NoPost>
+__device__ __forceinline__ void tc_pairs(uint32_t tacc, F&& body, P&& post = P()) {
+  constexpr int NPAIR = NG8 / 2;
+#pragma unroll 1
+  for (int p = 0; p < NPAIR; ++p) {
+    float v0[8], v1[8];
+    if (LOAD) {
+      umma::ld8f(tacc + 16 * p, v0);
+      umma::ld8f(tacc + 16 * p + 8, v1);
+      umma::wait_ld16(v0, v1);
+    }
+    const int g = 2 * p;
+    body(g >> 2, g & 3, g, v0);
+    body(g >> 2, (g & 3) + 1, g + 1, v1);
+    if ((g & 3) == 2) post(g >> 2);
+  }
+  if (NG8 & 1) {
+    float v0[8];
+    if (LOAD) {
+      umma::ld8f(tacc + 8 * (NG8 - 1), v0);
+      umma::wait_ld8(v0);
+    }
+    body((NG8 - 1) >> 2, (NG8 - 1) & 3, NG8 - 1, v0);
+  }
+  if ((NG8 & 3) != 0) post((NG8 - 1) >> 2);
+}
+
+// ... and ONE column group per iteration (every body inlined exactly once; one exposed TMEM-load wait per 8 columns)
+template <int NG8, bool LOAD, class F, class P = NoPost>
+__device__ __forceinline__ void tc_singles(uint32_t tacc, F&& body, P&& post = P()) {
+#pragma unroll 1
+  for (int g = 0; g < NG8; ++g) {
+    float v0[8];
+    if (LOAD) {
+      umma::ld8f(tacc + 8 * g, v0);
+      umma::wait_ld8(v0);
+    }
+    body(g >> 2, g & 3, g, v0);
+    if ((g & 3) == 3 || g == NG8 - 1) post(g >> 2);
   }
 }
 
@@ -425,9 +472,13 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
           mbar_wait(&cx.full[slot], (cx.seq / G::NSLOT) & 1);
           umma::fence_after_sync();
           const uint64_t wd = cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4));
-          if (!SPLIT && cx.tmemA) tc_issue_ts<C>(cx.tmma, cx.ta_mma, wd);
-          else tc_issue<C>(cx.tmma, cx.adesc, wd, 0u);
-          if (SPLIT) tc_issue<C>(cx.tmma, cx.adesc + (uint64_t)(T::A_BYTES >> 4), wd, 1u);
+          if (cx.tmemA) {
+            tc_issue_ts<C>(cx.tmma, cx.ta_mma, wd, 0u);                                   // A_hi W_hi
+            if (SPLIT) tc_issue_ts<C>(cx.tmma, cx.ta_mma + T::TCOLS, wd, 1u);             // A_lo W_hi
+          } else {
+            tc_issue<C>(cx.tmma, cx.adesc, wd, 0u);
+            if (SPLIT) tc_issue<C>(cx.tmma, cx.adesc + (uint64_t)(T::A_BYTES >> 4), wd, 1u);
+          }
           umma::commit(&cx.empty[slot]);
         }
         if (SPLIT) {
@@ -435,7 +486,9 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
           const uint32_t slot = s2 % G::NSLOT;
           mbar_wait(&cx.full[slot], (s2 / G::NSLOT) & 1);
           umma::fence_after_sync();
-          tc_issue<C>(cx.tmma, cx.adesc, cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4)), 1u);
+          const uint64_t wd2 = cx.wdesc + (uint64_t)(slot * (T::W_BYTES >> 4));                                  // A_hi W_lo
+          if (cx.tmemA) tc_issue_ts<C>(cx.tmma, cx.ta_mma, wd2, 1u);
+          else tc_issue<C>(cx.tmma, cx.adesc, wd2, 1u);
           umma::commit(&cx.empty[slot]);
         }
         umma::commit(cx.done);
@@ -562,7 +615,7 @@ __global__ void __launch_bounds__(TcFwdGeom<C, SPLIT>::NT, 1) node_tc_fwd_kernel
     cx.full = full; cx.empty = empty; cx.done = &done[cx.g];
     cx.tmma = tbase + cx.g * T::TCOLS;
     cx.tacc = cx.tmma + ((uint32_t)((warp % 4) * 32) << 16);
-    cx.ta_mma = tbase + (G::G + (cx.tmemA ? cx.g - G::GS : 0)) * T::TCOLS;
+    cx.ta_mma = tbase + (G::G + (cx.tmemA ? cx.g - G::GS : 0) * G::NIMG) * T::TCOLS;
     cx.ta_row = cx.ta_mma + ((uint32_t)((warp % 4) * 32) << 16);
     cx.seq = 0; cx.nd = 0;
     cx.adesc = umma::make_desc(smem_u32(cx.sA), T::ACH, 128);

@@ -257,6 +257,27 @@ __device__ __forceinline__ void relu_publish8(const TcGroupCtx& cx, uint32_t& mw
 
 // One stage of the reverse sweep for the group's tile (mirrors vjp_rhs_tile of node_bwd.cuh).
 // img: global image block of this (tile, stage evaluation) or nullptr (no parameter gradients wanted).
+#ifndef NLBAC_TC_ROLL_CHAINS
+#define NLBAC_TC_ROLL_CHAINS 1
+#endif
+constexpr bool TC_ROLL_CHAINS = NLBAC_TC_ROLL_CHAINS != 0;   // (macros are not expanded inside #pragma unroll)
+#ifndef NLBAC_TC_SPLIT_COMPACT
+#define NLBAC_TC_SPLIT_COMPACT 1   // the 3xTF32 sweep visits the accumulator with tc_pairs (instruction-fetch bound)
+#endif
+template <int NG8, bool LOAD, bool COMPACT>
+struct TcVisit {
+  template <class F, class P = NoPost>
+  __device__ __forceinline__ void operator()(uint32_t tacc, F&& body, P&& post = P()) const {
+    if constexpr (COMPACT && NLBAC_TC_SPLIT_COMPACT == 2) tc_singles<NG8, LOAD>(tacc, body, post);
+    else if constexpr (COMPACT) tc_pairs<NG8, LOAD>(tacc, body, post);
+    else tc_batches<NG8, LOAD>(tacc, body, post);
+  }
+};
+#ifndef NLBAC_TC_COMPACT_ALL
+#define NLBAC_TC_COMPACT_ALL 0
+#endif
+#define TC_VISIT(LOAD) TcVisit<NG8, LOAD, ((SPLIT && NLBAC_TC_SPLIT_COMPACT) || NLBAC_TC_COMPACT_ALL)>()
+
 template <class C, bool SPLIT = false>
 __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, const float (&x)[C::NS],
                                            const float (&cst)[C::NCONST], const float (&dk)[C::NS],
@@ -284,7 +305,10 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
     img_store8<SPLIT, false, IM::LO>(img + IM::off_xin(), lt, 0, v0);
     if (IM::XIN_CH > 1) img_store8<SPLIT, false, IM::LO>(img + IM::off_xin(), lt, 8, v1);
   }
-#pragma unroll
+  // 3xTF32 sweep (NLBAC_TC_ROLL_CHAINS): the f / g chains as a ROLLED loop (per-chain sizes and offsets become run-time
+  // values): 141 -> 102 KB of SASS and 237 -> 224 ms at the bench size, because that sweep is instruction-fetch bound
+  // (DESIGN.md 5).  The TF32 sweep (104 -> 79 KB) measured neutral (103.6 vs 102.3 ms) and stays unrolled.
+#pragma unroll((SPLIT && TC_ROLL_CHAINS) ? 1 : 2)
   for (int c = 0; c < C::NCH; ++c) {
     const int n = C::nhc(c);
     const int OUT = C::out(c), OUTP = C::outp(c);
@@ -299,7 +323,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
       const float* Wt0 = cx.sRes + C::off_wt0(c);
       const float* b0 = cx.sRes + C::off_b0(c);
       unsigned char* ia = img + IM::off_act(c, 1);
-      tc_batches<NG8, false>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
+      TC_VISIT(false)(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
         Acc8 acc;
         acc8_init(acc, *reinterpret_cast<const float4*>(b0 + 8 * g8), *reinterpret_cast<const float4*>(b0 + 8 * g8 + 4));
 #pragma unroll
@@ -348,7 +372,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
         const float* bias = cx.sRes + C::off_bh(c, l);
         unsigned char* ia = img + IM::off_act(c, l + 1);
         if (l < n) {
-          tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
+          TC_VISIT(true)(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
             if (!T::FOLD) {
               const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
               const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
@@ -360,7 +384,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
           // last hidden activation: forward value of g(x) (action gradient) and d_{n+1} = relu' * WL^T dOut
           const float* WnL = cx.sRes + C::off_wnl(c);
           unsigned char* id = img + IM::off_del(c, n + 1);
-          tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
+          TC_VISIT(true)(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
             if (!T::FOLD) {
               const float4 ba = *reinterpret_cast<const float4*>(bias + 8 * g8);
               const float4 bb = *reinterpret_cast<const float4*>(bias + 8 * g8 + 4);
@@ -430,7 +454,7 @@ __device__ __forceinline__ void vjp_rhs_tc(TcGroupCtx& cx, unsigned char* img, c
         tc_layer_mma<C, G, SPLIT>(cx);
         const float* Wt0 = cx.sRes + C::off_wt0(c);
         unsigned char* id = img + IM::off_del(c, l);
-        tc_batches<NG8, true>(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
+        TC_VISIT(true)(cx.tacc, [&](int q, int u, int g8, float (&v)[8]) {
           const uint32_t bits = (sel4(mk[l - 1], q) >> (8 * u)) & 0xFFu;
 #pragma unroll
           for (int i = 0; i < 8; ++i) v[i] = ((bits >> i) & 1u) ? v[i] : 0.f;
