@@ -8,6 +8,18 @@
 
 namespace nlbac {
 
+// Chain loop (f_net, g_net) of the FP32 kernels rolled (1) or unrolled (0): rolled halves the code of the kernel
+// (instruction-cache footprint: 55 -> 38 KB for the backward), unrolled keeps every per-chain size a compile-time
+// constant.  Measured at 2^20 x 20 rk4 (round 2, same box A/B): backward 782 ms unrolled vs 843 ms rolled, forward equal
+// -> unrolled.  (The tcgen05 3xTF32 sweep, 193 KB, is the kernel where rolling pays: node_tc_bwd.cuh.)
+#ifndef NLBAC_ROLL_CHAINS_BWD
+#define NLBAC_ROLL_CHAINS_BWD 0
+#endif
+#ifndef NLBAC_ROLL_CHAINS_FWD
+#define NLBAC_ROLL_CHAINS_FWD 0
+#endif
+constexpr bool NODE_ROLL_CHAINS_BWD = NLBAC_ROLL_CHAINS_BWD != 0, NODE_ROLL_CHAINS_FWD = NLBAC_ROLL_CHAINS_FWD != 0;
+
 // ---------------------------------------------------------------------------------------------
 // Weight ring: the hidden HxH matrices cycle through NSLOT shared-memory slots.  One thread
 // issues cp.async.bulk (TMA, UBLKCP) for packet seq+NSLOT as soon as the CTA has finished reading

@@ -147,7 +147,7 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
   for (int d = 0; d < INP0; ++d) dxa[d] = 0.f;
   __syncthreads();
 
-#pragma unroll
+#pragma unroll(NODE_ROLL_CHAINS_BWD ? 1 : 2)
   for (int c = 0; c < C::NCH; ++c) {
     const int n = C::nhc(c);
     const int OUT = C::out(c), OUTP = C::outp(c);

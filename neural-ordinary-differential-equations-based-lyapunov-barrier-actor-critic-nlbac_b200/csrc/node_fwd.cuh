@@ -68,7 +68,7 @@ __device__ __forceinline__ void eval_rhs_tile(const float* __restrict__ packed, 
   __syncthreads();
 
   float fo[C::outp(0)];
-#pragma unroll
+#pragma unroll(NODE_ROLL_CHAINS_FWD ? 1 : 2)
   for (int c = 0; c < C::NCH; ++c) {
     float acc[G::TT][ColMap<C::HP>::NN];
     // first layer: sX -> sA
