@@ -162,6 +162,28 @@ int nlbac_node_dopri5_bwd(const nlbac_node_desc* desc, const float* packed, cons
                           int precision, const float* ckpt, const float* grad_out, float* grad_y0,
                           float* grad_params, void* ws, void* stream);
 
+/* The same solve with the step-size controller ON THE DEVICE: accept / reject, the next step size, the output
+ * bookkeeping and the error flags live in `state` (device memory, nlbac_node_dopri5_state_bytes, 8-byte aligned) and
+ * are advanced by a one-thread kernel after each attempt in the same double arithmetic as the host loop above, so
+ * the step sequence is identical.  Nothing is read back and nothing is allocated: forward and backward can be
+ * captured in a CUDA graph (torchdiffeq cannot: it reads error_ratio on the host, rk_common.py
+ * _adaptive_step).  `attempts` attempts (3 launches each) are enqueued; once the last output time has been passed
+ * the remaining ones return at once.  resume = 1 enqueues `attempts` more on the same `ws` / `state` / `ckpt`.
+ * nlbac_node_dopri5_state_read synchronises and reports; err: 0 ok, 1 non-finite error ratio, 2 max_steps accepted
+ * steps exhausted, 3 stalled (100 * max_steps attempts), 4 step-size underflow, 5 not finished within the attempts
+ * enqueued so far (enqueue more with resume = 1).  The backward takes the step table from `state`; after err != 0
+ * its results are meaningless (but it stays in bounds).  ws / ckpt sizes: nlbac_node_dopri5_workspace_bytes. */
+int nlbac_node_dopri5_state_bytes(int n_t, int max_steps, size_t* bytes);
+int nlbac_node_dopri5_fwd_dev(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B,
+                              const float* t, int n_t, float rtol, float atol, int max_steps, int attempts,
+                              int resume, int precision, float* y_out, float* ckpt, void* ws, void* state,
+                              void* stream);
+int nlbac_node_dopri5_state_read(const void* state, int n_t, int max_steps, int* n_accepted, int* n_rejected,
+                                 int* done, int* err, float* step_dt, void* stream);
+int nlbac_node_dopri5_bwd_dev(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B, int n_t,
+                              int max_steps, const void* state, int precision, const float* ckpt,
+                              const float* grad_out, float* grad_y0, float* grad_params, void* ws, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Actor / critic / Lyapunov / barrier MLPs: in -> hidden -> hidden -> out, ReLU (QNetwork is two of
  * them, U sac_cbf_clf/model.py:37-64; LyaNetwork :67-83; BarrierNetwork BU model.py:67-86;

@@ -112,6 +112,12 @@ def _declare(lib):
                                           vp, vp, vp, ip, ip, fp, ip, fp, vp]
     lib.nlbac_node_dopri5_bwd.argtypes = [dp, vp, vp, c.c_int64, c.c_int, c.c_int, fp, ip, fp, c.c_int,
                                           vp, vp, vp, vp, vp, vp]
+    lib.nlbac_node_dopri5_state_bytes.argtypes = [c.c_int, c.c_int, szp]
+    lib.nlbac_node_dopri5_fwd_dev.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, c.c_float, c.c_float, c.c_int,
+                                              c.c_int, c.c_int, c.c_int, vp, vp, vp, vp, vp]
+    lib.nlbac_node_dopri5_state_read.argtypes = [vp, c.c_int, c.c_int, ip, ip, ip, ip, fp, vp]
+    lib.nlbac_node_dopri5_bwd_dev.argtypes = [dp, vp, vp, c.c_int64, c.c_int, c.c_int, vp, c.c_int, vp, vp, vp, vp,
+                                              vp, vp]
     mp, cp, i64 = c.POINTER(MlpDesc), c.POINTER(ConstraintDesc), c.c_int64
     lib.nlbac_mlp_workspace_bytes.argtypes = [mp, i64, szp, szp]
     lib.nlbac_mlp_fwd.argtypes = [mp, c.POINTER(vp), vp, i64, vp, vp, vp]

@@ -667,6 +667,7 @@ int nlbac_node_dopri5_fwd(const nlbac_node_desc* desc, const float* packed, cons
     NLBAC_CUDA(cudaMemcpy2DAsync(ybuf[0], C::NS * 4, y0, C::D * 4, C::NS * 4, B, cudaMemcpyDeviceToDevice, st));
     Dp5Args a;
     a.packed = packed; a.y0 = y0; a.B = B; a.rtol = rtol; a.atol = atol; a.krec = krec; a.acc = acc;
+    a.dev = nullptr;
     int cur = 0;
     // f0 and the norms of _select_initial_step
     NLBAC_CUDA(cudaMemsetAsync(acc, 0, 3 * sizeof(double), st));
@@ -746,13 +747,134 @@ int nlbac_node_dopri5_bwd(const nlbac_node_desc* desc, const float* packed, cons
     NLBAC_CUDA(cudaMemcpyAsync(p + n_accepted * 4 + n_t * 4, out_x, n_t * 4, cudaMemcpyHostToDevice, st));
     Dp5BwdArgs a;
     a.packed = packed; a.y0 = y0; a.xrec = ckpt; a.grad_out = grad_out; a.grad_y0 = grad_y0; a.B = B;
-    a.n_acc = n_accepted; a.n_t = n_t;
+    a.n_acc = n_accepted; a.n_t = n_t; a.n_acc_dev = nullptr;
     a.dts = reinterpret_cast<const float*>(p);
     a.out_step = reinterpret_cast<const int*>(p + n_accepted * 4);
     a.out_x = reinterpret_cast<const float*>(p + n_accepted * 4 + n_t * 4);
     float* rep = nullptr;
     if (grad_params) {
       rep = reinterpret_cast<float*>(p + round_up(n_accepted * 4 + n_t * 8, 16));
+      NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
+    }
+    a.grad_rep = rep;
+    int rc = ((B + 63) / 64 >= sm_count()) ? launch_dp5_bwd<C, 64>(a, st) : launch_dp5_bwd<C, 32>(a, st);
+    if (rc) return rc;
+    if (grad_params) {
+      GradTable gt = build_grad_table<C>();
+      KScope ks(3, st);
+      fold_grad_kernel<<<dim3(8, gt.n), 256, 0, st>>>(gt, rep, C::NGRAD, grad_params);
+      NLBAC_CUDA(cudaGetLastError());
+    }
+    return 0;
+  });
+}
+
+// Device-driven solve: the controller state stays in device memory, nothing is read back, so the whole solve (and its
+// backward) can be captured in a CUDA graph.  `attempts` step attempts are enqueued; attempts after the last output
+// time has been passed are no-op launches.
+int nlbac_node_dopri5_state_bytes(int n_t, int max_steps, size_t* bytes) {
+  NLBAC_REQUIRE(bytes && n_t >= 2 && max_steps >= 1, "bad arguments");
+  *bytes = dp5_dev_bytes(n_t, max_steps);
+  return 0;
+}
+
+int nlbac_node_dopri5_fwd_dev(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B,
+                              const float* t, int n_t, float rtol, float atol, int max_steps, int attempts,
+                              int resume, int precision, float* y_out, float* ckpt, void* ws, void* state,
+                              void* stream) {
+  NLBAC_REQUIRE(packed && y0 && t && y_out && ws && state, "null pointer");
+  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32, "precision %d not compiled", precision);
+  NLBAC_REQUIRE(B > 0 && n_t >= 2 && max_steps >= 1 && attempts >= 0, "bad sizes");
+  NLBAC_REQUIRE(reinterpret_cast<uintptr_t>(state) % 8 == 0, "state must be 8-byte aligned");
+  for (int j = 1; j < n_t; ++j) NLBAC_REQUIRE(t[j] > t[j - 1], "t must be strictly increasing");
+  cudaStream_t st = (cudaStream_t)stream;
+  return dispatch(desc, [&]<class C>() {
+    const size_t n = (size_t)B * C::NS;
+    float* base = static_cast<float*>(ws);
+    Dp5Dev* dev = static_cast<Dp5Dev*>(state);
+    Dp5DevArrays arr = dp5_dev_arrays(state, n_t, max_steps);
+    Dp5CtrlArgs c;
+    c.s = dev;
+    c.acc = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + ((11 * n * 4 + 15) / 16) * 16);
+    c.cnt = (double)B * C::D; c.n_t = n_t; c.max_steps = max_steps; c.t_off = 0; c.t_cnt = 0;
+    auto ctrl = [&](int phase) -> int {
+      c.phase = phase;
+      dopri5_ctrl_kernel<<<1, 32, 0, st>>>(c);
+      NLBAC_CUDA(cudaGetLastError());
+      return 0;
+    };
+    Dp5Args a;
+    a.packed = packed; a.y0 = y0; a.B = B; a.rtol = rtol; a.atol = atol; a.krec = base + 4 * n; a.acc = c.acc;
+    a.dt = 0.f;
+    if (!resume) {
+      NLBAC_CUDA(cudaMemcpyAsync(y_out, y0, (size_t)B * C::D * 4, cudaMemcpyDeviceToDevice, st));
+      NLBAC_CUDA(cudaMemcpy2DAsync(base, C::NS * 4, y0, C::D * 4, C::NS * 4, B, cudaMemcpyDeviceToDevice, st));
+      for (int off = 0; off < n_t; off += 16) {
+        c.t_off = off; c.t_cnt = n_t - off < 16 ? n_t - off : 16;
+        for (int i = 0; i < c.t_cnt; ++i) c.t_chunk[i] = (double)t[off + i];
+        if (int rc = ctrl(-1)) return rc;
+      }
+      a.dev = nullptr;
+      a.mode = 0; a.y = base; a.k1 = nullptr; a.y1 = nullptr; a.k7 = base + 2 * n; a.xrec = nullptr;
+      if (int rc = launch_dp5_any<C>(a, st)) return rc;
+      if (int rc = ctrl(0)) return rc;
+      a.dev = dev;
+      a.mode = 1; a.k1 = base + 2 * n; a.k7 = nullptr;
+      if (int rc = launch_dp5_any<C>(a, st)) return rc;
+      if (int rc = ctrl(1)) return rc;
+    }
+    a.dev = dev;
+    a.mode = 2; a.y = base; a.k1 = nullptr; a.y1 = nullptr; a.k7 = nullptr; a.xrec = ckpt;
+    Dp5InterpDevArgs ia;
+    ia.y0 = y0; ia.base = base; ia.y_out = y_out; ia.dev = dev; ia.pend_j = arr.pend_j; ia.pend_x = arr.pend_x;
+    ia.B = B; ia.ns = C::NS; ia.d = C::D;
+    const long long tot = (long long)B * C::D;
+    for (int k = 0; k < attempts; ++k) {
+      if (int rc = launch_dp5_any<C>(a, st)) return rc;
+      if (int rc = ctrl(2)) return rc;
+      dopri5_interp_dev_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, st>>>(ia);
+      NLBAC_CUDA(cudaGetLastError());
+    }
+    return ctrl(3);
+  });
+}
+
+int nlbac_node_dopri5_state_read(const void* state, int n_t, int max_steps, int* n_accepted, int* n_rejected,
+                                 int* done, int* err, float* step_dt, void* stream) {
+  NLBAC_REQUIRE(state && n_t >= 2 && max_steps >= 1, "bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  Dp5Dev h;
+  NLBAC_CUDA(cudaMemcpyAsync(&h, state, sizeof(h), cudaMemcpyDeviceToHost, st));
+  NLBAC_CUDA(cudaStreamSynchronize(st));
+  if (n_accepted) *n_accepted = h.n_acc;
+  if (n_rejected) *n_rejected = h.n_rej;
+  if (done) *done = h.done;
+  if (err) *err = h.err;
+  if (step_dt && h.n_acc > 0) {
+    Dp5DevArrays arr = dp5_dev_arrays(const_cast<void*>(state), n_t, max_steps);
+    const int k = h.n_acc < max_steps ? h.n_acc : max_steps;
+    NLBAC_CUDA(cudaMemcpyAsync(step_dt, arr.step_dt, (size_t)k * 4, cudaMemcpyDeviceToHost, st));
+    NLBAC_CUDA(cudaStreamSynchronize(st));
+  }
+  return 0;
+}
+
+int nlbac_node_dopri5_bwd_dev(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B, int n_t,
+                              int max_steps, const void* state, int precision, const float* ckpt,
+                              const float* grad_out, float* grad_y0, float* grad_params, void* ws, void* stream) {
+  NLBAC_REQUIRE(packed && y0 && state && ckpt && grad_out && ws, "null pointer");
+  NLBAC_REQUIRE(precision == NLBAC_PREC_FP32, "precision %d not compiled", precision);
+  NLBAC_REQUIRE(B > 0 && n_t >= 2 && max_steps >= 1, "bad sizes");
+  cudaStream_t st = (cudaStream_t)stream;
+  return dispatch(desc, [&]<class C>() {
+    Dp5DevArrays arr = dp5_dev_arrays(const_cast<void*>(state), n_t, max_steps);
+    Dp5BwdArgs a;
+    a.packed = packed; a.y0 = y0; a.xrec = ckpt; a.grad_out = grad_out; a.grad_y0 = grad_y0; a.B = B;
+    a.n_acc = 0; a.n_t = n_t; a.n_acc_dev = &static_cast<const Dp5Dev*>(state)->n_acc;
+    a.dts = arr.step_dt; a.out_step = arr.out_step; a.out_x = arr.out_x;
+    float* rep = nullptr;
+    if (grad_params) {
+      rep = static_cast<float*>(ws);
       NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
     }
     a.grad_rep = rep;

@@ -30,6 +30,37 @@ __device__ constexpr float DP_CMID[7] = {(float)(6025192743.0 / 30085553152.0 / 
                                          (float)(-1776094331.0 / 19743644256.0 / 2),
                                          (float)(11237099.0 / 235043384.0 / 2)};
 
+// Controller state of the device-driven solve (nlbac_node_dopri5_fwd_dev): one instance in device memory, followed
+// by the arrays t_out[n_t] (double), step_dt[max_steps], out_step[n_t], out_x[n_t], pend_j[n_t], pend_x[n_t].
+struct Dp5Dev {
+  double dt, t_cur, t_prev, h0, d1;
+  float dt_last;
+  int cur, n_acc, n_rej, j, done, err, n_pend;
+};
+struct Dp5DevArrays {
+  double* t_out;
+  float* step_dt;
+  int* out_step;
+  float* out_x;
+  int* pend_j;
+  float* pend_x;
+};
+__host__ __device__ inline size_t dp5_dev_bytes(int n_t, int max_steps) {
+  return 128 + (size_t)n_t * 8 + ((size_t)max_steps + 4 * (size_t)n_t) * 4 + 64;
+}
+__host__ __device__ inline Dp5DevArrays dp5_dev_arrays(void* state, int n_t, int max_steps) {
+  char* p = static_cast<char*>(state) + 128;
+  Dp5DevArrays r;
+  r.t_out = reinterpret_cast<double*>(p); p += (size_t)n_t * 8;
+  r.step_dt = reinterpret_cast<float*>(p); p += (size_t)max_steps * 4;
+  r.out_step = reinterpret_cast<int*>(p); p += (size_t)n_t * 4;
+  r.out_x = reinterpret_cast<float*>(p); p += (size_t)n_t * 4;
+  r.pend_j = reinterpret_cast<int*>(p); p += (size_t)n_t * 4;
+  r.pend_x = reinterpret_cast<float*>(p);
+  return r;
+}
+static_assert(sizeof(Dp5Dev) <= 128, "Dp5Dev header");
+
 struct Dp5Args {
   const float* packed;
   const float* y0;     // [B, D] (constants of the flow)
@@ -43,6 +74,9 @@ struct Dp5Args {
   long long B;
   float dt, rtol, atol;
   int mode;            // 0: f0 = f(y0) + norms; 1: initial-step probe; 2: one attempted step
+  // device-driven solve: dt, the ping-pong parity and the checkpoint slot come from *dev (y = ybuf[0] = ws base,
+  // xrec = the checkpoint BASE); a finished solve makes the launch a no-op
+  const Dp5Dev* dev;
 };
 
 template <class C, int T>
@@ -55,6 +89,22 @@ __global__ void __launch_bounds__(FwdGeom<C, T>::NT, 1) dopri5_kernel(Dp5Args a)
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + G::OFF_BAR);
   __shared__ double sred[3][8];
   const int tid = threadIdx.x;
+  const float *yp = a.y, *k1p = a.k1;
+  float *y1p = a.y1, *k7p = a.k7, *xrecp = a.xrec;
+  float dtv = a.dt;
+  if (a.dev != nullptr) {
+    if (a.mode == 1) dtv = (float)a.dev->h0;
+    if (a.mode == 2) {
+      if (a.dev->done) return;
+      const size_t n = (size_t)a.B * C::NS;
+      const int cur = a.dev->cur;
+      float* base = const_cast<float*>(a.y);
+      yp = base + (size_t)cur * n; y1p = base + (size_t)(cur ^ 1) * n;
+      k1p = base + (size_t)(2 + cur) * n; k7p = base + (size_t)(2 + (cur ^ 1)) * n;
+      if (xrecp != nullptr) xrecp += (size_t)a.dev->n_acc * 6 * n;
+      dtv = (float)a.dev->dt;
+    }
+  }
   const long long n_tiles = (a.B + T - 1) / T;
   const int nev = a.mode == 2 ? 6 : 1;
   long long my_tiles = 0;
@@ -91,10 +141,10 @@ __global__ void __launch_bounds__(FwdGeom<C, T>::NT, 1) dopri5_kernel(Dp5Args a)
 #pragma unroll
       for (int d = 0; d < C::NCONST; ++d) cst[d] = a.y0[b * C::D + C::NS + d];
 #pragma unroll
-      for (int d = 0; d < C::NS; ++d) y[d] = a.y[b * C::NS + d];
+      for (int d = 0; d < C::NS; ++d) y[d] = yp[b * C::NS + d];
       if (a.mode != 0) {
 #pragma unroll
-        for (int d = 0; d < C::NS; ++d) k[0][d] = a.k1[b * C::NS + d];
+        for (int d = 0; d < C::NS; ++d) k[0][d] = k1p[b * C::NS + d];
       }
     }
     // one call site of the right-hand side for all three modes
@@ -105,19 +155,19 @@ __global__ void __launch_bounds__(FwdGeom<C, T>::NT, 1) dopri5_kernel(Dp5Args a)
         for (int d = 0; d < C::NS; ++d) x[d] = y[d];
       } else if (a.mode == 1) {
 #pragma unroll
-        for (int d = 0; d < C::NS; ++d) x[d] = y[d] + a.dt * k[0][d];
+        for (int d = 0; d < C::NS; ++d) x[d] = y[d] + dtv * k[0][d];
       } else {
 #pragma unroll
         for (int d = 0; d < C::NS; ++d) {
           float s = 0.f;
 #pragma unroll
           for (int j = 0; j < 6; ++j)
-            if (j < i) s = fmaf(k[j][d], DP_BETA[i - 1][j] * a.dt, s);
+            if (j < i) s = fmaf(k[j][d], DP_BETA[i - 1][j] * dtv, s);
           x[d] = y[d] + s;
         }
-        if (a.xrec != nullptr && live) {
+        if (xrecp != nullptr && live) {
 #pragma unroll
-          for (int d = 0; d < C::NS; ++d) a.xrec[((long long)(i - 1) * a.B + b) * C::NS + d] = x[d];
+          for (int d = 0; d < C::NS; ++d) xrecp[((long long)(i - 1) * a.B + b) * C::NS + d] = x[d];
         }
       }
       eval_rhs_tile<C, T>(a.packed, sA, sX, sRes, ring, x, cst, kn);
@@ -128,7 +178,7 @@ __global__ void __launch_bounds__(FwdGeom<C, T>::NT, 1) dopri5_kernel(Dp5Args a)
       if (a.mode == 0) {
 #pragma unroll
         for (int d = 0; d < C::NS; ++d) {
-          a.k7[b * C::NS + d] = kn[d];
+          k7p[b * C::NS + d] = kn[d];
           const float sc = a.atol + fabsf(y[d]) * a.rtol;
           const float q0 = y[d] / sc, q1 = kn[d] / sc;
           s0 += (double)q0 * q0;
@@ -148,11 +198,11 @@ __global__ void __launch_bounds__(FwdGeom<C, T>::NT, 1) dopri5_kernel(Dp5Args a)
       } else {  // x == y1 (Dormand–Prince: c_sol equals the last beta row), kn == f(y1)
 #pragma unroll
         for (int d = 0; d < C::NS; ++d) {
-          a.y1[b * C::NS + d] = x[d];
-          a.k7[b * C::NS + d] = kn[d];
+          y1p[b * C::NS + d] = x[d];
+          k7p[b * C::NS + d] = kn[d];
           float e = 0.f;
 #pragma unroll
-          for (int j = 0; j < 7; ++j) e = fmaf(k[j][d], DP_CERR[j] * a.dt, e);
+          for (int j = 0; j < 7; ++j) e = fmaf(k[j][d], DP_CERR[j] * dtv, e);
           const float tol = a.atol + a.rtol * fmaxf(fabsf(y[d]), fabsf(x[d]));
           const float q = e / tol;
           s0 += (double)q * q;
@@ -189,19 +239,13 @@ struct Dp5InterpArgs {
   float dt, xf;
   int ns, d;
 };
-__global__ void dopri5_interp_kernel(Dp5InterpArgs a) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= a.B * a.d) return;
-  const long long b = i / a.d;
-  const int c = (int)(i - b * a.d);
-  if (c >= a.ns) { a.out[i] = a.y0[i]; return; }
-  const long long o = b * a.ns + c, st = a.B * a.ns;
-  const float y0 = a.ya[o], y1 = a.yb[o], f0 = a.krec[o], f1 = a.krec[6 * st + o];
+__device__ __forceinline__ float dp5_dense(const float* ya, const float* yb, const float* krec, long long o,
+                                           long long st, float dt, float x) {
+  const float y0 = ya[o], y1 = yb[o], f0 = krec[o], f1 = krec[6 * st + o];
   float ymid = 0.f;
 #pragma unroll
-  for (int j = 0; j < 7; ++j) ymid = fmaf(a.krec[j * st + o], DP_CMID[j] * a.dt, ymid);
+  for (int j = 0; j < 7; ++j) ymid = fmaf(krec[j * st + o], DP_CMID[j] * dt, ymid);
   ymid += y0;
-  const float dt = a.dt, x = a.xf;
   const float ca = 2 * dt * (f1 - f0) - 8 * (y1 + y0) + 16 * ymid;
   const float cb = dt * (5 * f0 - 3 * f1) + 18 * y0 + 14 * y1 - 32 * ymid;
   const float cc = dt * (f1 - 4 * f0) - 11 * y0 - 5 * y1 + 16 * ymid;
@@ -211,7 +255,127 @@ __global__ void dopri5_interp_kernel(Dp5InterpArgs a) {
   xp *= x; tot += xp * cc;
   xp *= x; tot += xp * cb;
   xp *= x; tot += xp * ca;
-  a.out[i] = tot;
+  return tot;
+}
+__global__ void dopri5_interp_kernel(Dp5InterpArgs a) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.B * a.d) return;
+  const long long b = i / a.d;
+  const int c = (int)(i - b * a.d);
+  if (c >= a.ns) { a.out[i] = a.y0[i]; return; }
+  a.out[i] = dp5_dense(a.ya, a.yb, a.krec, b * a.ns + c, a.B * a.ns, a.dt, a.xf);
+}
+
+// Device-driven variant: writes every output time the LAST attempt passed (none after a rejected step).
+struct Dp5InterpDevArgs {
+  const float* y0;     // [B, D]
+  const float* base;   // workspace base: ybuf[0], ybuf[1], kbuf[0], kbuf[1], krec
+  float* y_out;        // [n_t, B, D]
+  const Dp5Dev* dev;
+  const int* pend_j;
+  const float* pend_x;
+  long long B;
+  int ns, d;
+};
+__global__ void dopri5_interp_dev_kernel(Dp5InterpDevArgs a) {
+  const int n_pend = a.dev->n_pend;
+  if (n_pend == 0) return;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= a.B * a.d) return;
+  const long long b = i / a.d;
+  const int c = (int)(i - b * a.d);
+  const size_t n = (size_t)a.B * a.ns;
+  const int cur = a.dev->cur;
+  const float* ya = a.base + (size_t)(cur ^ 1) * n;
+  const float* yb = a.base + (size_t)cur * n;
+  const float* krec = a.base + 4 * n;
+  const float dt = a.dev->dt_last;
+  for (int p = 0; p < n_pend; ++p) {
+    float* out = a.y_out + (size_t)a.pend_j[p] * a.B * a.d;
+    out[i] = c >= a.ns ? a.y0[i] : dp5_dense(ya, yb, krec, b * a.ns + c, (long long)n, dt, a.pend_x[p]);
+  }
+}
+
+// The step-size controller as ONE device thread, in the same double arithmetic as the host-driven loop of
+// nlbac_node_dopri5_fwd (torchdiffeq rk_common._adaptive_step / misc._select_initial_step / _optimal_step_size).
+// phase -1: reset (t_chunk holds up to 16 output times starting at t_off); 0 / 1: the two norms of the initial step;
+// 2: accept / reject of one attempt; 3: close (flags an exhausted attempt budget).
+struct Dp5CtrlArgs {
+  Dp5Dev* s;
+  double* acc;
+  double cnt;
+  double t_chunk[16];
+  int phase, n_t, max_steps, t_off, t_cnt;
+};
+__global__ void dopri5_ctrl_kernel(Dp5CtrlArgs a) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  Dp5Dev* s = a.s;
+  Dp5DevArrays A = dp5_dev_arrays(s, a.n_t, a.max_steps);
+  if (a.phase == -1) {
+    for (int i = 0; i < a.t_cnt; ++i) A.t_out[a.t_off + i] = a.t_chunk[i];
+    if (a.t_off == 0) {
+      s->dt = 0.0; s->t_cur = s->t_prev = a.t_chunk[0]; s->h0 = 0.0; s->d1 = 0.0; s->dt_last = 0.f;
+      s->cur = 0; s->n_acc = 0; s->n_rej = 0; s->j = 1; s->done = 0; s->err = 0; s->n_pend = 0;
+      a.acc[0] = a.acc[1] = a.acc[2] = 0.0;
+    }
+    for (int i = 0; i < a.t_cnt; ++i) { A.out_step[a.t_off + i] = -1; A.out_x[a.t_off + i] = 0.f; }
+    return;
+  }
+  if (a.phase == 0) {
+    const double d0 = sqrt(a.acc[0] / a.cnt), d1 = sqrt(a.acc[1] / a.cnt);
+    s->h0 = (d0 < 1e-5 || d1 < 1e-5) ? 1e-6 : 0.01 * d0 / d1;
+    s->d1 = d1;
+    a.acc[0] = a.acc[1] = a.acc[2] = 0.0;
+    return;
+  }
+  if (a.phase == 1) {
+    const double h0 = s->h0, d1 = s->d1, d2 = sqrt(a.acc[2] / a.cnt) / h0;
+    const double h1 = (d1 <= 1e-15 && d2 <= 1e-15) ? fmax(1e-6, h0 * 1e-3) : pow(0.01 / fmax(d1, d2), 1.0 / 5.0);
+    s->dt = fmin(100.0 * h0, h1);
+    a.acc[0] = a.acc[1] = a.acc[2] = 0.0;
+    return;
+  }
+  if (a.phase == 3) {
+    s->n_pend = 0;
+    if (!s->done) { s->err = 5; }
+    return;
+  }
+  s->n_pend = 0;
+  if (s->done) return;
+  if (s->err == 5) s->err = 0;   // resumed after an exhausted attempt budget
+  const double ratio = sqrt(a.acc[0] / a.cnt);
+  a.acc[0] = 0.0;
+  if (!isfinite(ratio)) { s->err = 1; s->done = 1; return; }
+  double dt = s->dt;
+  if (ratio <= 1.0) {
+    A.step_dt[s->n_acc] = (float)dt;
+    s->dt_last = (float)dt;
+    s->n_acc += 1;
+    s->t_prev = s->t_cur;
+    s->t_cur = s->t_cur + dt;
+    s->cur ^= 1;
+    int j = s->j, np = 0;
+    while (j < a.n_t && !(A.t_out[j] > s->t_cur)) {
+      const float xf = (float)((A.t_out[j] - s->t_prev) / (s->t_cur - s->t_prev));
+      A.pend_j[np] = j; A.pend_x[np] = xf; A.out_step[j] = s->n_acc - 1; A.out_x[j] = xf;
+      ++np; ++j;
+    }
+    s->j = j; s->n_pend = np;
+    if (j == a.n_t) s->done = 1;
+  } else {
+    s->n_rej += 1;
+  }
+  if (ratio == 0.0) dt *= 10.0;
+  else {
+    const double dfactor = ratio < 1.0 ? 1.0 : 0.2;
+    dt *= fmin(10.0, fmax(0.9 / pow(ratio, 0.2), dfactor));
+  }
+  s->dt = dt;
+  if (!s->done) {
+    if (s->n_acc >= a.max_steps) { s->err = 2; s->done = 1; }
+    else if (s->n_acc + s->n_rej >= 100 * a.max_steps) { s->err = 3; s->done = 1; }
+    else if (!(s->t_cur + dt > s->t_cur)) { s->err = 4; s->done = 1; }
+  }
 }
 
 struct Dp5BwdArgs {
@@ -226,6 +390,7 @@ struct Dp5BwdArgs {
   const float* out_x;     // [n_t] fraction inside that step
   long long B;
   int n_acc, n_t;
+  const int* n_acc_dev;   // device-driven solve: the accepted-step count lives in Dp5Dev
 };
 
 // Reverse sweep.  Per accepted step: k1 = f(y) is shared with the previous step's k7 (FSAL), so its
@@ -244,7 +409,8 @@ __global__ void __launch_bounds__(BwdGeom<C, TB>::NT, 1) dopri5_bwd_kernel(Dp5Bw
   ring.slots = smem + G::OFF_RING;
   ring.full = bars;
   ring.seq = 0;
-  ring.total = (uint32_t)(my_tiles * (6 * a.n_acc + 1) * G::CYC);
+  const int n_acc = a.n_acc_dev != nullptr ? *a.n_acc_dev : a.n_acc;
+  ring.total = (uint32_t)(my_tiles * (6 * n_acc + 1) * G::CYC);
   if (tid == 0) {
     for (int i = 0; i <= G::NSLOT; ++i) mbar_init(&bars[i], 1);
     fence_barrier_init();
@@ -274,7 +440,7 @@ __global__ void __launch_bounds__(BwdGeom<C, TB>::NT, 1) dopri5_bwd_kernel(Dp5Bw
     }
     int jo = a.n_t - 1;
 #pragma unroll 1
-    for (int s = a.n_acc - 1; s >= -1; --s) {
+    for (int s = n_acc - 1; s >= -1; --s) {
       float dt = 0.f;
       int i_hi = 0, i_lo = 0;
       if (s >= 0) {

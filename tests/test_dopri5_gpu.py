@@ -111,3 +111,89 @@ def test_default_method_is_dopri5_and_capacity_error():
     with pytest.raises(RuntimeError):
         nlbac_b200.odeint(ours, y0, torch.tensor([0.0, 5.0]), method="dopri5", rtol=1e-7, atol=1e-9,
                           options={"max_num_steps": 2})
+
+
+@pytest.mark.parametrize("tag,t", [("U", [0.0, 0.02]), ("P", [0.0, 0.3, 0.5, 1.0]), ("C", [0.0, 0.1, 0.7])])
+def test_device_and_host_controllers_take_the_same_steps(tag, t):
+    """The on-device controller repeats the host loop's double arithmetic: identical step sizes, and therefore
+    bit-identical solutions and gradients."""
+    import nlbac_b200
+    _, ours = _models(tag)
+    y0 = _y0(tag, 96)
+    cot = torch.randn(len(t), 96, y0.shape[1], generator=torch.Generator().manual_seed(3)).cuda()
+    res = {}
+    for ctl in ("host", "device"):
+        st = {}
+        yg = y0.clone().cuda().requires_grad_(True)
+        ours.zero_grad()
+        sol = nlbac_b200.odeint(ours, yg, torch.tensor(t), method="dopri5", rtol=1e-5, atol=1e-7,
+                                options={"_stats": st, "controller": ctl})
+        (sol * cot).sum().backward()
+        res[ctl] = (sol.detach().clone(), yg.grad.clone(), [p.grad.clone() for p in ours.parameters()], st)
+    h, d = res["host"], res["device"]
+    assert (h[3]["n_accepted"], h[3]["n_rejected"]) == (d[3]["n_accepted"], d[3]["n_rejected"])
+    assert (h[3]["step_dt"] == d[3]["step_dt"]).all()
+    assert torch.equal(h[0], d[0]) and torch.equal(h[1], d[1])
+    for a, b in zip(h[2], d[2]):       # the dW fold uses float atomics across CTAs: order-dependent round-off only
+        assert _rel(a, b) <= 1e-6
+
+
+def test_dopri5_forward_and_backward_captured_in_one_cuda_graph():
+    """Nothing in the device-driven solve touches the host: forward + backward replay as one CUDA graph on new
+    inputs and match the eager solve of the same inputs (which takes a DIFFERENT number of steps)."""
+    import nlbac_b200
+    _, ours = _models("P")
+    B, t = 128, torch.tensor([0.0, 0.25, 0.6])
+    y_static = _y0("P", B).cuda().requires_grad_(True)
+    cot = torch.randn(3, B, y_static.shape[1], generator=torch.Generator().manual_seed(5)).cuda()
+    params = list(ours.parameters())
+    st = {}
+
+    def run():
+        sol = nlbac_b200.odeint(ours, y_static, t, method="dopri5", rtol=1e-5, atol=1e-7,
+                                options={"_stats": st, "max_attempts": 24})
+        grads = torch.autograd.grad((sol * cot).sum(), [y_static] + params)
+        return sol, grads
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(2):
+            run()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        sol_g, grads_g = run()
+    steps = []
+    for seed, scale in ((21, 1.0), (22, 3.0)):
+        y_new = _y0("P", B, seed=seed).cuda() * scale
+        with torch.no_grad():
+            y_static.copy_(y_new)
+        graph.replay()
+        info = st["read"]()
+        assert info["done"] == 1 and info["err"] == 0
+        steps.append((info["n_accepted"], info["n_rejected"]))
+        ye = y_new.clone().requires_grad_(True)
+        st_e = {}
+        sol_e = nlbac_b200.odeint(ours, ye, t, method="dopri5", rtol=1e-5, atol=1e-7, options={"_stats": st_e})
+        grads_e = torch.autograd.grad((sol_e * cot).sum(), [ye] + params)
+        assert (st_e["n_accepted"], st_e["n_rejected"]) == steps[-1]
+        assert torch.equal(sol_g, sol_e) and torch.equal(grads_g[0], grads_e[0])
+        for a, b in zip(grads_g[1:], grads_e[1:]):
+            assert _rel(a, b) <= 1e-6
+
+
+def test_dopri5_capture_reports_exhausted_attempt_budget():
+    import nlbac_b200
+    _, ours = _models("U")
+    y0 = _y0("U", 16).cuda()
+    t = torch.tensor([0.0, 1.0])
+    nlbac_b200.odeint(ours, y0, t, method="dopri5", rtol=1e-6, atol=1e-8)            # warm-up outside capture
+    st = {}
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        nlbac_b200.odeint(ours, y0, t, method="dopri5", rtol=1e-6, atol=1e-8,
+                          options={"_stats": st, "max_attempts": 1})
+    graph.replay()
+    info = st["read"]()
+    assert info["done"] == 0 and info["err"] == 5

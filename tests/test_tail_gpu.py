@@ -424,3 +424,49 @@ def test_config4_quadrotor_shaped_horizon10_rollout():
     assert _rel(ub.grad, ua.grad) <= 5e-5, _rel(ub.grad, ua.grad)
     for p, q in zip(node.parameters(), ref_node.parameters()):
         assert _rel(p.grad, q.grad) <= 5e-5, _rel(p.grad, q.grad)
+
+
+def test_config3_learned_barrier_block_with_dopri5_inside_a_cuda_graph(golden_dir):
+    """BASELINE config 3 as named (Pvtol + learned barrier, dopri5 adaptive solve): the required matrix and its action
+    gradient with ``solver="dopri5"``, recorded ONCE into a CUDA graph (the device-side step controller needs no host
+    read-back) and replayed, against the CPU oracle running the restated torchdiffeq dopri5."""
+    import nlbac_b200
+    C = nlbac_b200.constraints
+    g = torch.load(os.path.join(golden_dir, "constraints_BP.pt"), weights_only=False)
+    k, B = g["consts"], g["B"]
+    nets, onets = build(g, nlbac_b200, "cuda"), build(g, nlbac_ref, "cpu")
+    dyn = nlbac_b200.DynamicsModel(_Env("Pvtol"))
+    w = torch.linspace(0.5, 1.5, 2).reshape(2, 1)
+    kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], batch_size=B, solver="dopri5")
+
+    act_o = g["action"].clone().requires_grad_(True)
+    req_o = OC.barrier_pvtol_required_matrix(onets["node"], onets["lya"], onets["barrier"], onets["policy"], g["obs"],
+                                             g["state"], act_o, g["V"], follow=k["safety_operator_follow"],
+                                             eps_next=g["eps"], **kw)
+    (req_o * w).sum().backward()
+
+    obs, state, V, eps = (g[n].cuda() for n in ("obs", "state", "V", "eps"))
+    act = torch.zeros_like(g["action"]).cuda().requires_grad_(True)
+    wc = w.cuda()
+
+    def run():
+        req = C.barrier_pvtol_required_matrix(nets["node"], nets["lya"], nets["barrier"], nets["policy"], dyn, obs, state,
+                                              act, V, safety_operator_follow=k["safety_operator_follow"], eps_next=eps,
+                                              **kw)
+        (ga,) = torch.autograd.grad((req * wc).sum(), act)
+        return req, ga
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for _ in range(2):
+            run()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        req_g, ga_g = run()
+    with torch.no_grad():
+        act.copy_(g["action"].cuda())          # the graph was recorded on zeros: the replay must see the new input
+    graph.replay()
+    assert _rel(req_g, req_o) <= 2 * TOL
+    assert _rel(ga_g, act_o.grad) <= 10 * TOL
