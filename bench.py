@@ -525,7 +525,7 @@ def run_configs(args):
             ts.append((time.perf_counter() - t0) * 1e6)
         return statistics.median(ts)
 
-    def node_case(name, mk_ref, mk_ours, B, D, n_s, method, steps=1):
+    def node_case(name, mk_ref, mk_ours, B, D, n_s, method, steps=1, options=None, graphed=False):
         torch.manual_seed(0)
         ref = mk_ref()
         ours = mk_ours()
@@ -540,8 +540,25 @@ def run_configs(args):
         tt = torch.tensor(t)
 
         def ours_fn():
-            sol = nlbac_b200.odeint(ours, y_gpu, t, method=method, atol=1e-7, rtol=1e-5)
-            torch.autograd.grad(sol[-1][:, :n_s].sum(), list(ours.parameters()))
+            sol = nlbac_b200.odeint(ours, y_gpu, t, method=method, atol=1e-7, rtol=1e-5,
+                                    options=dict(options) if options else None)
+            return torch.autograd.grad(sol[-1][:, :n_s].sum(), list(ours.parameters()))
+
+        if graphed:      # the whole forward + backward recorded once; a call is one cudaGraphLaunch
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    ours_fn()
+            torch.cuda.current_stream().wait_stream(side)
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                keep = ours_fn()                                              # noqa: F841 (outputs live in the graph pool)
+            eager_ours, ours_fn = ours_fn, graph.replay                       # noqa: F841
+            if options and "_stats" in options:
+                graph.replay()
+                info = options["_stats"]["read"]()
+                assert info["done"] == 1 and info["err"] == 0, info
 
         def eager_fn(model, y, tv):
             def f():
@@ -563,6 +580,10 @@ def run_configs(args):
             node_case("config1 Unicycle NODE batch", *U, 32768, 5, 3, "euler"),
             node_case("config2 SimulatedCars predict", *Cc, 256, 12, 10, "euler"),
             node_case("config3 PVTOL predict", *P, 256, 8, 6, "dopri5"),
+            node_case("config3 PVTOL predict (host-side step controller)", *P, 256, 8, 6, "dopri5",
+                      options={"controller": "host"}),
+            node_case("config3 PVTOL predict (one CUDA-graph replay)", *P, 256, 8, 6, "dopri5",
+                      options={"max_attempts": 4, "_stats": {}}, graphed=True),
             node_case("config3 PVTOL predict", *P, 256, 8, 6, "rk4", 20)]
 
     def mlp_case(name, mk_ref, mk_ours, B, n_in):
@@ -736,6 +757,44 @@ def run_configs(args):
                 "torch_cpu_us": None, "speedup_vs_eager_gpu": None, "speedup_vs_cpu": None,
                 "graph_speedup_vs_own_eager": e_nob / o_nob}
     rows += [update_case_P()]
+
+    # BASELINE config 3 as named: Pvtol with the learned barrier certificate (BP sac_cbf_clf.py), batch 256, the NODE
+    # predictions inside the actor loss solved with adaptive dopri5 (device-side step controller -> capturable) vs euler
+    def update_case_BP(solver):
+        import numpy as np
+        g = torch.load(os.path.join(ROOT, "tests", "golden", "update_BP.pt"), weights_only=False)
+        k, B = g["consts"], g["B"]
+        C = nlbac_b200.constraints
+        sp = type("S", (), {"low": np.array(k["action_low"], dtype="float32"), "high": np.array(k["action_high"], dtype="float32")})
+        nets = {"critic": nlbac_b200.QNetwork(11, 2, 256), "critic_target": nlbac_b200.QNetwork(11, 2, 256),
+                "lya": nlbac_b200.LyaNetwork(11, 256), "lya_t": nlbac_b200.LyaNetwork(11, 256),
+                "policy": nlbac_b200.GaussianPolicy(11, 2, 256, sp), "node": nlbac_b200.NeuralODEModel(6, 6, 12),
+                "bar": nlbac_b200.BarrierNetwork(11, 2, 256), "bar_t": nlbac_b200.BarrierNetwork(11, 2, 256)}
+        for n, key in (("critic", "critic"), ("critic_target", "critic"), ("lya", "lyapunovNet"), ("lya_t", "lyapunovNet"),
+                       ("policy", "policy"), ("node", "neural_ode_model"), ("bar", "BarrierNet"), ("bar_t", "BarrierNet")):
+            nets[n].load_state_dict(g["init"][key])
+            nets[n].to(dev)
+        node, lya = nets["node"], nets["lya"]
+        dm = nlbac_b200.DynamicsModel(type("E", (), {"dynamics_mode": "Pvtol"}))
+        kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], safety_operator_follow=k["safety_operator_follow"], batch_size=B,
+                  solver=solver)
+        h = {}
+        upd = nlbac_b200.GraphedUpdate(
+            nets["critic"], nets["critic_target"], lya, nets["lya_t"], nets["policy"], None, node, dm, B,
+            primary=lambda s_, pi, V: C.barrier_pvtol_required_matrix(
+                node, lya, nets["bar"], nets["policy"], dm, h["u"].buf["state"], s_, pi, V, eps_next=h["u"].eps[3], **kw),
+            backup=None, num_constraints=2, ratio_floor=0.002, n_extra_eps=1, barrier=nets["bar"],
+            barrier_target=nets["bar_t"], lya_on_obs=True, node_n_s=6, node_n_u=2, obs_dim=11, act_dim=2,
+            center_pos_num=11)
+        h["u"] = upd
+        batch = tuple(None if x is None else x.to(dev) for x in g["batches"][0])
+        upd.step(batch)
+        o = lat_gpu(lambda: upd.step(batch))
+        e = lat_gpu(lambda: upd._body(False), iters=20, warm=3)
+        return {"case": "config3 Pvtol + learned barrier full update_parameters, NODE solver = %s" % solver, "batch": B,
+                "ours_us": o, "ours_eager_launches_us": e, "torch_eager_gpu_us": None, "torch_cpu_us": None,
+                "speedup_vs_eager_gpu": None, "speedup_vs_cpu": None, "graph_speedup_vs_own_eager": e / o}
+    rows += [update_case_BP("euler"), update_case_BP("dopri5")]
 
     # replay sampling: the reference's list-of-tuples memory + np.stack + H2D vs the device ring
     from oracle.replay import ReplayMemory as RefReplay

@@ -47,6 +47,8 @@ extern "C" {
 
 #define NLBAC_ABI_VERSION 2   /* 2: nlbac_node_tc_bwd_workspace_bytes takes the precision tier; nlbac_comm_*, *_noalloc, umma_peak_probe */
 
+typedef struct nlbac_comm nlbac_comm;   /* NCCL communicator handle, see nlbac_comm_init below */
+
 /* model kinds */
 #define NLBAC_KIND_AFFINE   0   /* x' = f_net(x) + g_net(x) u      (U, P, BU, BP) */
 #define NLBAC_KIND_BLACKBOX 1   /* x' = net([x, u, const])          (C, quadrotor)  */
@@ -172,12 +174,15 @@ int nlbac_node_dopri5_bwd(const nlbac_node_desc* desc, const float* packed, cons
  * nlbac_node_dopri5_state_read synchronises and reports; err: 0 ok, 1 non-finite error ratio, 2 max_steps accepted
  * steps exhausted, 3 stalled (100 * max_steps attempts), 4 step-size underflow, 5 not finished within the attempts
  * enqueued so far (enqueue more with resume = 1).  The backward takes the step table from `state`; after err != 0
- * its results are meaningless (but it stays in bounds).  ws / ckpt sizes: nlbac_node_dopri5_workspace_bytes. */
+ * its results are meaningless (but it stays in bounds).  ws / ckpt sizes: nlbac_node_dopri5_workspace_bytes.
+ * Sharded batch: with `comm` non-NULL the three squared-norm sums are all-reduced over the ranks
+ * (3 doubles, on `stream`) before every controller step and divided by B_global * D, so every rank takes the step
+ * sequence of the unsharded batch; every rank must enqueue the same number of attempts.  comm = NULL: B_global unused. */
 int nlbac_node_dopri5_state_bytes(int n_t, int max_steps, size_t* bytes);
 int nlbac_node_dopri5_fwd_dev(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B,
                               const float* t, int n_t, float rtol, float atol, int max_steps, int attempts,
                               int resume, int precision, float* y_out, float* ckpt, void* ws, void* state,
-                              void* stream);
+                              nlbac_comm* comm, int64_t B_global, void* stream);
 int nlbac_node_dopri5_state_read(const void* state, int n_t, int max_steps, int* n_accepted, int* n_rejected,
                                  int* done, int* err, float* step_dt, void* stream);
 int nlbac_node_dopri5_bwd_dev(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B, int n_t,
@@ -346,10 +351,10 @@ int nlbac_env_pvtol_step(double* state, int32_t* episode_step, const double* act
  * rank 0 that the caller broadcasts to the other ranks (any transport) before nlbac_comm_init, with the rank's GPU
  * current.  Returns 0, < 0 for bad arguments, 1000 + ncclResult_t for NCCL errors (text via nlbac_last_error).  NCCL is
  * resolved at run time (dlopen of libnccl.so.2); the handle is the only state the library keeps. */
-typedef struct nlbac_comm nlbac_comm;
 int nlbac_comm_unique_id(void* id128);
 int nlbac_comm_init(int world, int rank, const void* id128, nlbac_comm** comm);
 int nlbac_allreduce_grads(nlbac_comm* comm, float* flat, size_t n, void* stream);
+int nlbac_allreduce_sum_f64(nlbac_comm* comm, double* buf, size_t n, void* stream);
 int nlbac_comm_destroy(nlbac_comm* comm);
 
 /* Self-test of the tcgen05 operand layouts the tensor-core NODE kernels use (csrc/umma.cuh): one 128x112 tile.

@@ -114,7 +114,7 @@ def _declare(lib):
                                           vp, vp, vp, vp, vp, vp]
     lib.nlbac_node_dopri5_state_bytes.argtypes = [c.c_int, c.c_int, szp]
     lib.nlbac_node_dopri5_fwd_dev.argtypes = [dp, vp, vp, c.c_int64, fp, c.c_int, c.c_float, c.c_float, c.c_int,
-                                              c.c_int, c.c_int, c.c_int, vp, vp, vp, vp, vp]
+                                              c.c_int, c.c_int, c.c_int, vp, vp, vp, vp, vp, c.c_int64, vp]
     lib.nlbac_node_dopri5_state_read.argtypes = [vp, c.c_int, c.c_int, ip, ip, ip, ip, fp, vp]
     lib.nlbac_node_dopri5_bwd_dev.argtypes = [dp, vp, vp, c.c_int64, c.c_int, c.c_int, vp, c.c_int, vp, vp, vp, vp,
                                               vp, vp]
@@ -151,6 +151,7 @@ def _declare(lib):
     lib.nlbac_comm_unique_id.argtypes = [vp]
     lib.nlbac_comm_init.argtypes = [c.c_int, c.c_int, vp, c.POINTER(vp)]
     lib.nlbac_allreduce_grads.argtypes = [vp, vp, c.c_size_t, vp]
+    lib.nlbac_allreduce_sum_f64.argtypes = [vp, vp, c.c_size_t, vp]
     lib.nlbac_comm_destroy.argtypes = [vp]
     lib.nlbac_umma_selftest.argtypes = [c.c_int, vp, vp, vp, vp]
     lib.nlbac_kernel_timing.argtypes = [c.c_int]

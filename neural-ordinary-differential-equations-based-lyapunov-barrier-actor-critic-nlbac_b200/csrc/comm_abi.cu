@@ -85,6 +85,15 @@ int nlbac_allreduce_grads(nlbac_comm* comm, float* flat, size_t n, void* stream)
   return 0;
 }
 
+int nlbac_allreduce_sum_f64(nlbac_comm* comm, double* buf, size_t n, void* stream) {
+  NLBAC_REQUIRE(comm != nullptr && (buf != nullptr || n == 0), "null communicator or buffer");
+  if (n == 0) return 0;
+  // ncclFloat64 = 8, ncclSum = 0 (nccl.h); in place
+  if (int rc = g_nccl.AllReduce(buf, buf, n, 8, 0, comm->comm, (cudaStream_t)stream))
+    return nccl_fail(rc, "ncclAllReduce(f64)");
+  return 0;
+}
+
 int nlbac_comm_destroy(nlbac_comm* comm) {
   if (comm == nullptr) return 0;
   int rc = g_nccl.ok ? g_nccl.CommDestroy(comm->comm) : 0;

@@ -781,8 +781,9 @@ int nlbac_node_dopri5_state_bytes(int n_t, int max_steps, size_t* bytes) {
 int nlbac_node_dopri5_fwd_dev(const nlbac_node_desc* desc, const float* packed, const float* y0, int64_t B,
                               const float* t, int n_t, float rtol, float atol, int max_steps, int attempts,
                               int resume, int precision, float* y_out, float* ckpt, void* ws, void* state,
-                              void* stream) {
+                              nlbac_comm* comm, int64_t B_global, void* stream) {
   NLBAC_REQUIRE(packed && y0 && t && y_out && ws && state, "null pointer");
+  NLBAC_REQUIRE(comm == nullptr || B_global >= B, "B_global %lld < local B %lld", (long long)B_global, (long long)B);
   NLBAC_REQUIRE(precision == NLBAC_PREC_FP32, "precision %d not compiled", precision);
   NLBAC_REQUIRE(B > 0 && n_t >= 2 && max_steps >= 1 && attempts >= 0, "bad sizes");
   NLBAC_REQUIRE(reinterpret_cast<uintptr_t>(state) % 8 == 0, "state must be 8-byte aligned");
@@ -796,8 +797,11 @@ int nlbac_node_dopri5_fwd_dev(const nlbac_node_desc* desc, const float* packed, 
     Dp5CtrlArgs c;
     c.s = dev;
     c.acc = reinterpret_cast<double*>(reinterpret_cast<char*>(ws) + ((11 * n * 4 + 15) / 16) * 16);
-    c.cnt = (double)B * C::D; c.n_t = n_t; c.max_steps = max_steps; c.t_off = 0; c.t_cnt = 0;
+    c.cnt = (double)(comm ? B_global : B) * C::D; c.n_t = n_t; c.max_steps = max_steps; c.t_off = 0; c.t_cnt = 0;
     auto ctrl = [&](int phase) -> int {
+      // sharded batch: the norms are sums over ALL ranks' rows (torchdiffeq's one step size for the whole batch)
+      if (comm != nullptr && phase >= 0 && phase <= 2)
+        if (int rc = nlbac_allreduce_sum_f64(comm, c.acc, 3, stream)) return rc;
       c.phase = phase;
       dopri5_ctrl_kernel<<<1, 32, 0, st>>>(c);
       NLBAC_CUDA(cudaGetLastError());

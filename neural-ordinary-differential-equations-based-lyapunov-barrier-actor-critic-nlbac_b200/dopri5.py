@@ -8,6 +8,8 @@ Two controllers with the identical step sequence (same double arithmetic):
   * ``device`` (default): accept / reject and the next step size are decided by a one-thread kernel after each
     attempt; the host reads the state back ONCE per batch of enqueued attempts (eager) or never (under CUDA-graph
     capture, where ``options["max_attempts"]`` attempts are recorded and the surplus ones are no-op launches).
+    Sharded batch (one process per GPU): ``options={"comm": parallel.Comm, "rows_global": N}`` all-reduces the three
+    squared-norm sums before every controller step, so every rank takes the step sequence of the unsharded batch.
   * ``host`` (``options={"controller": "host"}``): one scalar read-back per attempted step, exactly where
     torchdiffeq itself synchronises (rk_common._adaptive_step).
 """
@@ -21,6 +23,7 @@ from . import _lib
 DEFAULT_STEP_CAPACITY = 128
 FIRST_ATTEMPT_BATCH = 8          # eager device controller: attempts enqueued before the first read-back
 DEFAULT_CAPTURE_ATTEMPTS = 16    # under graph capture nothing can be read back: a fixed attempt budget
+_ATTEMPT_HINT = {}               # (B, D, t, rtol, atol) -> attempts the last eager solve of that problem needed
 ERRORS = {1: "non-finite error ratio in dopri5", 2: "dopri5 exceeded max_steps accepted steps",
           3: "dopri5 stalled (rejected steps)", 4: "underflow in dt",
           5: "dopri5 did not finish within the enqueued attempts"}
@@ -54,7 +57,8 @@ class DeviceStats(dict):
 
 class _Dopri5DeviceSolve(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, y0, desc, packed, t_np, rtol, atol, precision, want_ckpt, max_steps, stats, attempts, *params):
+    def forward(ctx, y0, desc, packed, t_np, rtol, atol, precision, want_ckpt, max_steps, stats, attempts, shard,
+                *params):
         L = _lib.lib()
         B, D = y0.shape
         n_t = len(t_np)
@@ -71,18 +75,24 @@ class _Dopri5DeviceSolve(torch.autograd.Function):
         t_arr = np.ascontiguousarray(t_np, dtype=np.float32)
         fp = ctypes.POINTER(ctypes.c_float)
         capturing = torch.cuda.is_current_stream_capturing()
+        comm_h, rows_global = (shard[0]._h, int(shard[1])) if shard is not None else (None, B)
 
         def enqueue(n_attempts, resume):
             _lib.check(L.nlbac_node_dopri5_fwd_dev(
                 ctypes.byref(desc), packed.data_ptr(), y0c.data_ptr(), B, t_arr.ctypes.data_as(fp), n_t, rtol, atol,
                 max_steps, n_attempts, resume, precision, y_out.data_ptr(), ckpt.data_ptr() if want_ckpt else None,
-                ws.data_ptr(), state.data_ptr(), _lib.raw_stream()), "node_dopri5_fwd_dev")
+                ws.data_ptr(), state.data_ptr(), comm_h, rows_global, _lib.raw_stream()), "node_dopri5_fwd_dev")
 
         info = DeviceStats(_state=state, _n_t=n_t, _cap=max_steps)
+        hint_key = (rows_global, D, tuple(float(v) for v in t_arr), rtol, atol)
         if capturing:
-            enqueue(attempts if attempts > 0 else DEFAULT_CAPTURE_ATTEMPTS, 0)
+            # nothing can be read back while recording: a fixed budget -- the caller's, else twice what the eager
+            # warm-up calls of the same problem needed (+2), else the default.  Surplus attempts are no-op launches.
+            hint = _ATTEMPT_HINT.get(hint_key)
+            enqueue(attempts if attempts > 0 else (2 * hint + 2 if hint else DEFAULT_CAPTURE_ATTEMPTS), 0)
         else:
-            batch = attempts if attempts > 0 else FIRST_ATTEMPT_BATCH
+            hint = _ATTEMPT_HINT.get(hint_key)
+            batch = attempts if attempts > 0 else (hint + 1 if hint else FIRST_ATTEMPT_BATCH)
             enqueue(batch, 0)
             while True:
                 info.read()
@@ -90,6 +100,7 @@ class _Dopri5DeviceSolve(torch.autograd.Function):
                     break
                 batch = min(2 * batch, 64)
                 enqueue(batch, 1)
+            _ATTEMPT_HINT[hint_key] = info["n_accepted"] + info["n_rejected"]
             if info["err"]:
                 raise RuntimeError(f"{ERRORS.get(info['err'], 'dopri5 error')} (max_num_steps={max_steps}, "
                                    f"accepted {info['n_accepted']}, rejected {info['n_rejected']})")
@@ -113,7 +124,7 @@ class _Dopri5DeviceSolve(torch.autograd.Function):
         B, D = y0c.shape
         dev = y0c.device
         need_y0 = ctx.needs_input_grad[0]
-        need_p = any(ctx.needs_input_grad[11:])
+        need_p = any(ctx.needs_input_grad[12:])
         go = grad_out.contiguous()
         ws = torch.empty(max(bwd_bytes, 16), dtype=torch.uint8, device=dev)
         gy0 = torch.empty((B, D), dtype=torch.float32, device=dev) if need_y0 else None
@@ -124,7 +135,7 @@ class _Dopri5DeviceSolve(torch.autograd.Function):
             ckpt.data_ptr(), go.data_ptr(), gy0.data_ptr() if need_y0 else None,
             gflat.data_ptr() if need_p else None, ws.data_ptr(), _lib.raw_stream()), "node_dopri5_bwd_dev")
         grads = _grads_from_flat(gflat, shapes) if need_p else [None] * len(shapes)
-        return (gy0, None, None, None, None, None, None, None, None, None, None, *grads)
+        return (gy0, None, None, None, None, None, None, None, None, None, None, None, *grads)
 
 
 class _Dopri5Solve(torch.autograd.Function):
@@ -198,7 +209,13 @@ def dopri5_solve(func, y0, desc, packed, params, t_np, rtol, atol, precision, ne
     attempts = int(options.pop("max_attempts", 0))
     if controller not in ("device", "host"):
         raise ValueError(f"dopri5 controller {controller!r}: 'device' or 'host'")
+    comm, rows_global = options.pop("comm", None), options.pop("rows_global", None)
+    if (comm is None) != (rows_global is None):
+        raise ValueError("dopri5 on a sharded batch needs both options: comm (parallel.Comm) and rows_global")
     if controller == "device":
+        shard = (comm, rows_global) if comm is not None else None
         return _Dopri5DeviceSolve.apply(y0, desc, packed, t_np, rtol, atol, precision, need_grad, cap, stats, attempts,
-                                        *params)
+                                        shard, *params)
+    if comm is not None:
+        raise ValueError("dopri5 on a sharded batch runs with the device-side controller only")
     return _Dopri5Solve.apply(y0, desc, packed, t_np, rtol, atol, precision, need_grad, cap, stats, *params)

@@ -13,6 +13,7 @@ import torch.multiprocessing as mp
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 B = 5000
+DP5_T = torch.tensor([0.0, 0.3, 0.7])
 
 
 def _inputs():
@@ -50,9 +51,17 @@ def _worker(rank, world, port, q):
         losses.append(parallel.train_step_dp(model, y0[lo:hi, :3].cuda().contiguous(), y0[lo:hi, 3:].cuda().contiguous(),
                                              nxt[lo:hi].cuda(), opt, torch.nn.MSELoss(), B, "euler", 0.02,
                                              rows_global=B, comm=comm))
+    # adaptive dopri5 on the sharded batch: the error norms are all-reduced, every rank takes the global step sequence
+    model2 = _model(nb).cuda()
+    st = {}
+    sol5 = nb.odeint(model2, y0[lo:hi].cuda(), DP5_T, method="dopri5", rtol=1e-5, atol=1e-7,
+                     options={"_stats": st, "comm": comm, "rows_global": B})
+    g5 = torch.autograd.grad(sol5[1:, :, :3].pow(2).sum(), list(model2.parameters()))
+    flat5 = parallel.allreduce_grad_tensors(g5, comm).clone()
     torch.cuda.synchronize()
     if rank == 0:
-        q.put((flat.cpu().tolist(), losses, torch.cat([p.detach().reshape(-1) for p in model.parameters()]).cpu().tolist()))
+        q.put((flat.cpu().tolist(), losses, torch.cat([p.detach().reshape(-1) for p in model.parameters()]).cpu().tolist(),
+               (st["n_accepted"], st["n_rejected"], st["step_dt"].tolist(), sol5.cpu().tolist(), flat5.cpu().tolist())))
     dist.barrier()
     comm.close()
     dist.destroy_process_group()
@@ -68,7 +77,7 @@ def test_n_rank_allreduced_dtheta_matches_one_rank():
     procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
-    flat, losses, params = q.get(timeout=600)
+    flat, losses, params, dp5 = q.get(timeout=600)
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
@@ -86,3 +95,14 @@ def test_n_rank_allreduced_dtheta_matches_one_rank():
         assert abs(l1 - losses[i]) <= 1e-5 * abs(l1)
     p1 = torch.cat([p.detach().reshape(-1) for p in model.parameters()]).cpu()
     assert rel(torch.tensor(params), p1) <= 1e-5, rel(torch.tensor(params), p1)
+    # sharded dopri5 == the single-rank solve of the whole batch (same steps; sums in a different order)
+    n_acc, n_rej, dts, sol_shard, flat5 = dp5
+    model2 = _model(nb).cuda()
+    st = {}
+    sol = nb.odeint(model2, y0.cuda(), DP5_T, method="dopri5", rtol=1e-5, atol=1e-7, options={"_stats": st})
+    want5 = torch.cat([g.reshape(-1) for g in torch.autograd.grad(sol[1:, :, :3].pow(2).sum(), list(model2.parameters()))])
+    assert (n_acc, n_rej) == (st["n_accepted"], st["n_rejected"]) and n_acc >= 3
+    assert rel(torch.tensor(dts), torch.tensor(st["step_dt"].tolist())) <= 1e-5
+    lo, hi = nb.parallel.shard_rows(B, 2, 0)
+    assert rel(torch.tensor(sol_shard), sol[:, lo:hi].detach().cpu()) <= 1e-5
+    assert rel(torch.tensor(flat5), want5.cpu()) <= 5e-5, rel(torch.tensor(flat5), want5.cpu())
