@@ -9,7 +9,8 @@ the published algorithm of rtqichen/torchdiffeq (``_impl/odeint.py``,
 ``fixed_grid.py``, ``rk_common.py``, ``dopri5.py``, ``interp.py``, ``misc.py``)
 as summarised in SURVEY.md Appendix A.  Parity of the solver is therefore
 "unpinned upstream"; it is anchored in tests/test_oracle_solver.py by analytic
-known answers.
+known answers and, for the dopri5 tableau / error weights (up to torchdiffeq's
+2/3 scale) / dense output / initial step, by scipy's independent RK45.
 
 Differentiable by ordinary autograd through the tensor ops (discretise-then-
 optimise), exactly like plain ``odeint`` (the reference never uses

@@ -137,3 +137,65 @@ def test_gradcheck_fixed_and_adaptive():
     t = torch.tensor([0.0, 0.1, 0.3], dtype=torch.float64)
     for m in ("euler", "rk4"):
         assert torch.autograd.gradcheck(lambda y: odeint(f, y, t, method=m), (y0,), atol=1e-7)
+
+
+def test_dopri5_step_arithmetic_matches_scipy_rk45():
+    """An INDEPENDENT implementation of the published Dormand-Prince 5(4) pair (scipy.integrate.RK45; Hairer et al.
+    / Shampine's continuous extension) pins what it can of the dopri5 restatement, with the NLBAC control-affine
+    network as the right-hand side (float64):
+      * the tableau: y1 and f(y1) of one step from the same (y0, f0, h) agree to round-off;
+      * the error weights: torchdiffeq's c_error is scipy's E scaled by -2/3 (torchdiffeq subtracts a differently
+        normalised 4th-order solution: -1/60 on k7 where Hairer's pair has 1/40) -- all 7 entries proportional;
+      * the dense output: the quartic through (y0, y1, y_mid, f0, f1) with torchdiffeq's DPS_C_MID is the same
+        polynomial as scipy's (5 conditions fix a quartic), compared at 5 interior points;
+      * _select_initial_step (Hairer's rule, order 4 -> exponent 1/5): identical first step size.
+    NOT pinned by this (torchdiffeq-specific, restated from its published source): the 2/3 scale itself, the step
+    controller's no-shrink-after-accept rule, and not clipping the last step."""
+    import numpy as np
+    from scipy.integrate import RK45
+    from scipy.integrate._ivp.rk import rk_step
+    from oracle import nlbac_ref
+    from oracle import torchdiffeq_restated as R
+    torch.manual_seed(3)
+    m = nlbac_ref.AffineNODE(3, 3, 6).double()
+    for p in m.parameters():
+        p.data.mul_(1.5)
+    B = 16
+    y0 = torch.randn(B, 5, dtype=torch.float64)
+
+    def fun(t, y):
+        with torch.no_grad():
+            return m(torch.tensor(t), torch.from_numpy(np.ascontiguousarray(y)).reshape(B, 5)).reshape(-1).numpy()
+
+    t0, h = 0.0, 0.13
+    with torch.no_grad():
+        f0 = m(torch.tensor(t0), y0)
+        y1, f1, err, k = R._runge_kutta_step(m, y0, f0, torch.tensor(t0, dtype=torch.float64),
+                                             torch.tensor(h, dtype=torch.float64), torch.tensor(t0 + h, dtype=torch.float64))
+    K = np.empty((7, B * 5))
+    y1_s, f1_s = rk_step(fun, t0, y0.reshape(-1).numpy(), f0.reshape(-1).numpy(), h, RK45.A, RK45.B, RK45.C, K)
+    assert np.abs(y1.reshape(-1).numpy() - y1_s).max() < 1e-13
+    assert np.abs(f1.reshape(-1).numpy() - f1_s).max() < 1e-12
+    for i in range(7):
+        assert np.abs(k[i].reshape(-1).numpy() - K[i]).max() < 1e-12
+    ratios = [c / e for c, e in zip(R.DP_C_ERR, RK45.E) if e != 0]
+    assert len(ratios) == 6 and all(abs(r + 2.0 / 3.0) < 1e-12 for r in ratios), ratios
+    assert R.DP_C_ERR[1] == 0 and RK45.E[1] == 0
+    err_s = K.T.dot(RK45.E) * h
+    assert np.abs(err.reshape(-1).numpy() + (2.0 / 3.0) * err_s).max() < 1e-15 + 1e-9 * np.abs(err_s).max()
+    # dense output
+    y_mid = y0 + sum(kj * (c * h) for c, kj in zip(R.DP_C_MID, k))
+    coeffs = R._interp_fit(y0, y1, y_mid, f0, f1, torch.tensor(h, dtype=torch.float64))
+    Q = K.T.dot(RK45.P)
+    for theta in (0.1, 0.3, 0.5, 0.77, 0.95):
+        want = y0.reshape(-1).numpy() + h * theta * Q.dot(np.cumprod(np.full(4, theta)) / theta)
+        got = R._interp_evaluate(coeffs, torch.tensor(t0, dtype=torch.float64), torch.tensor(t0 + h, dtype=torch.float64),
+                                 torch.tensor(t0 + theta * h, dtype=torch.float64)).reshape(-1).numpy()
+        assert np.abs(got - want).max() < 1e-9 * max(1.0, np.abs(want).max()), theta
+    # initial step
+    rtol, atol = 1e-6, 1e-8
+    st = {}
+    with torch.no_grad():
+        R.odeint(m, y0, torch.tensor([0.0, 3.0], dtype=torch.float64), method="dopri5", rtol=rtol, atol=atol, _stats=st)
+    s = RK45(fun, 0.0, y0.reshape(-1).numpy(), 3.0, rtol=rtol, atol=atol)
+    assert abs(st["step_dt"][0] - s.h_abs) <= 1e-12 * s.h_abs, (st["step_dt"][0], s.h_abs)
