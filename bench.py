@@ -694,13 +694,18 @@ def run_configs(args):
                   l_p=k["l_p"], batch_size=B)
         node, lya = nets["node"], nets["lya"]
         env = type("E", (), {"dynamics_mode": "Unicycle"})
-        upd = nlbac_b200.GraphedUpdate(
-            nets["critic"], nets["critic_target"], lya, nets["lya_t"], nets["policy"], nets["backup"], node,
-            nlbac_b200.DynamicsModel(env), B,
-            primary=lambda s_, pi, V: C.unicycle_required_matrix(node, lya, s_, pi, V, **kw),
-            backup=lambda s_, pi: C.unicycle_required_matrix(node, None, s_, pi, None, **kw),
-            num_constraints=8, obs_dim=7, act_dim=2, center_pos_num=2)
+        def make(concurrent):
+            return nlbac_b200.GraphedUpdate(
+                nets["critic"], nets["critic_target"], lya, nets["lya_t"], nets["policy"], nets["backup"], node,
+                nlbac_b200.DynamicsModel(env), B,
+                primary=lambda s_, pi, V: C.unicycle_required_matrix(node, lya, s_, pi, V, **kw),
+                backup=lambda s_, pi: C.unicycle_required_matrix(node, None, s_, pi, None, **kw),
+                num_constraints=8, obs_dim=7, act_dim=2, center_pos_num=2, concurrent=concurrent)
         batch = tuple(None if x is None else x.to(dev) for x in g["batches"][0])
+        upd1 = make(False)
+        upd1.step(batch)
+        o_single = lat_gpu(lambda: upd1.graph.replay())                  # every launch on one stream: a linear graph
+        upd = make(True)
         upd.step(batch)                                                  # capture
         o = lat_gpu(lambda: upd.step(batch))
         o_replay = lat_gpu(lambda: upd.graph.replay())
@@ -708,7 +713,8 @@ def run_configs(args):
         e = lat_gpu(lambda: ag_gpu.update_parameters(batch, 9), iters=20, warm=3)
         c = lat_cpu(lambda: ag_cpu.update_parameters(g["batches"][0], 9))
         return {"case": "config1 full update_parameters (critic + Lyapunov + actor + backup actor + alpha + Polyak)",
-                "batch": B, "ours_us": o, "ours_graph_replay_only_us": o_replay, "torch_eager_gpu_us": e, "torch_cpu_us": c,
+                "batch": B, "ours_us": o, "ours_graph_replay_only_us": o_replay,
+                "ours_graph_replay_single_stream_us": o_single, "torch_eager_gpu_us": e, "torch_cpu_us": c,
                 "speedup_vs_eager_gpu": e / o, "speedup_vs_cpu": c / o,
                 "note": "ours = load the minibatch into the static buffers + ONE CUDA-graph replay, no host sync; eager = "
                         "the restated reference update (6 .item() + float() read-backs, numpy get_state round trip)"}
@@ -735,17 +741,24 @@ def run_configs(args):
                   y_min=k["y_min"], batch_size=B)
         node, lya = nets["node"], nets["lya"]
         dm = nlbac_b200.DynamicsModel(type("E", (), {"dynamics_mode": "Pvtol"}))
-        h = {}
-        upd = nlbac_b200.GraphedUpdate(
-            nets["critic"], nets["critic_target"], lya, nets["lya_t"], nets["policy"], nets["backup"], node, dm, B,
-            primary=lambda s_, pi, V: C.pvtol_required_matrix(node, lya, nets["policy"], dm, s_, pi, V,
-                                                              eps_next=h["u"].eps[3], eps_next_next=h["u"].eps[4], **kw),
-            backup=lambda s_, pi: C.pvtol_required_matrix(node, None, nets["backup"], dm, s_, pi, None,
-                                                          eps_next=h["u"].eps[5], eps_next_next=h["u"].eps[6], **kw),
-            num_constraints=10, obs_dim=11, act_dim=2, center_pos_num=11, ratio_floor=0.002, node_n_s=6, node_n_u=2,
-            n_extra_eps=4, lya_on_obs=True, backup_update_interval=4, separate_backup_rho=True)
-        h["u"] = upd
+        def make(concurrent):
+            h = {}
+            u_ = nlbac_b200.GraphedUpdate(
+                nets["critic"], nets["critic_target"], lya, nets["lya_t"], nets["policy"], nets["backup"], node, dm, B,
+                primary=lambda s_, pi, V: C.pvtol_required_matrix(node, lya, nets["policy"], dm, s_, pi, V,
+                                                                  eps_next=h["u"].eps[3], eps_next_next=h["u"].eps[4], **kw),
+                backup=lambda s_, pi: C.pvtol_required_matrix(node, None, nets["backup"], dm, s_, pi, None,
+                                                              eps_next=h["u"].eps[5], eps_next_next=h["u"].eps[6], **kw),
+                num_constraints=10, obs_dim=11, act_dim=2, center_pos_num=11, ratio_floor=0.002, node_n_s=6, node_n_u=2,
+                n_extra_eps=4, lya_on_obs=True, backup_update_interval=4, separate_backup_rho=True, concurrent=concurrent)
+            h["u"] = u_
+            return u_
         batch = tuple(None if x is None else x.to(dev) for x in g["batches"][0])
+        upd1 = make(False)
+        upd1.step(batch)
+        o1_full = lat_gpu(lambda: upd1.step(batch, with_backup=True))
+        o1_nob = lat_gpu(lambda: upd1.step(batch, with_backup=False))
+        upd = make(True)
         upd.step(batch)
         o_full = lat_gpu(lambda: upd.step(batch, with_backup=True))
         o_nob = lat_gpu(lambda: upd.step(batch, with_backup=False))
@@ -753,6 +766,7 @@ def run_configs(args):
         e_nob = lat_gpu(lambda: upd._body(False), iters=20, warm=3)
         return {"case": "config3-shaped Pvtol full update_parameters (3-step rollout in the actor loss): graph replay vs the "
                         "same fused launches issued eagerly", "batch": B, "ours_us": o_nob, "ours_with_backup_update_us": o_full,
+                "ours_single_stream_graph_us": o1_nob, "ours_single_stream_graph_with_backup_us": o1_full,
                 "ours_eager_launches_us": e_nob, "ours_eager_launches_with_backup_us": e_full, "torch_eager_gpu_us": None,
                 "torch_cpu_us": None, "speedup_vs_eager_gpu": None, "speedup_vs_cpu": None,
                 "graph_speedup_vs_own_eager": e_nob / o_nob}

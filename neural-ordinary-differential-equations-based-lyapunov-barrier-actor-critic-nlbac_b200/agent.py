@@ -34,7 +34,8 @@ class GraphedUpdate:
                  target_update_interval=1, automatic_entropy_tuning=True, multiplier_interval=8, lambda_max=400.0,
                  ratio_floor=None, use_ratio=True, backup_update_interval=1, separate_backup_rho=False,
                  node_solver="euler", dt=0.02, node_n_s=3, node_n_u=2, node_graph_batch=32768, with_time=False,
-                 n_extra_eps=0, lya_on_obs=False, node_fit_max_episode=None, barrier=None, barrier_target=None):
+                 n_extra_eps=0, lya_on_obs=False, node_fit_max_episode=None, barrier=None, barrier_target=None,
+                 concurrent=True):
         dev = next(critic.parameters()).device
         if dev.type != "cuda":
             raise RuntimeError("GraphedUpdate: the networks must live on a CUDA device (no CPU fallback)")
@@ -97,6 +98,11 @@ class GraphedUpdate:
         self.node_n_s, self.node_n_u, self.node_graph_batch = node_n_s, node_n_u, node_graph_batch
         self._node_graph = None
         self.graph = None
+        self.concurrent = bool(concurrent)
+        self._streams = (torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev))
+        self._lag_event = torch.cuda.Event()
+        if self.concurrent:
+            critic.twin_streams = critic_target.twin_streams = True
 
     # ------------------------------------------------------------------------------------------------
     @staticmethod
@@ -112,54 +118,88 @@ class GraphedUpdate:
         b, F = self.buf, torch.nn.functional
         st = self.cstate
         st.set_updates_device(self.updates_dev)
-        with torch.no_grad():                                                                    # :231-238
+        # Independent pieces of the update run on forked streams (B = 128 / 256 kernels fill < half of the SMs, and
+        # every launch gap of one branch hides behind the other): {critic | Lyapunov | barrier} updates, then
+        # {actor | backup actor}.  Captured, the forks become parallel branches of the graph.  `concurrent=False`
+        # issues the same statements on one stream.
+        main = torch.cuda.current_stream()
+        s1, s2 = (self._streams if self.concurrent else (main, main))
+
+        forked = set()
+
+        def fork(s):
+            if s is not main:
+                s.wait_stream(main)
+                forked.add(s)
+            return torch.cuda.stream(s)
+
+        def join(*ss):          # only streams forked since their last join (a capture may not wait on foreign work)
+            for s in ss:
+                if s in forked:
+                    main.wait_stream(s)
+                    forked.discard(s)
+
+        with fork(s1):                                                                           # :236-238, :244, :253-255
+            with torch.no_grad():
+                next_l = b["constraint"] + b["mask"] * self.gamma * self.lyapunovNet_target(
+                    b["next_state"] if self.lya_on_obs else b["next_center_pos"])
+            lf_loss = F.mse_loss(self.lyapunovNet(b["state"] if self.lya_on_obs else b["center_pos"]), next_l)
+            self._step(self.lyaNet_optim, lf_loss, list(self.lyapunovNet.parameters()))
+        with torch.no_grad():                                                                    # :231-235
             next_a, next_logp, _ = self.policy.sample(b["next_state"], self.eps[0])
+            if self.barrier is not None:
+                with fork(s2):                                                                   # BU :214-216, :225-227, :237-240
+                    next_b = b["barrier_signal"] + b["mask"] * self.gamma * self.barrier_target(b["next_state"], next_a)
             q1t, q2t = self.critic_target(b["next_state"], next_a)
             min_q = torch.min(q1t, q2t) - self.alpha * next_logp
             next_q = b["reward"] + b["mask"] * self.gamma * min_q
-            next_l = b["constraint"] + b["mask"] * self.gamma * self.lyapunovNet_target(
-                b["next_state"] if self.lya_on_obs else b["next_center_pos"])
-            if self.barrier is not None:                                                         # BU :214-216
-                next_b = b["barrier_signal"] + b["mask"] * self.gamma * self.barrier_target(b["next_state"], next_a)
+        if self.barrier is not None:
+            with torch.cuda.stream(s2):
+                barrier_loss = F.mse_loss(self.barrier(b["state"], b["action"]), next_b)
+                self._step(self.barrier_optim, barrier_loss, list(self.barrier.parameters()))
         qf1, qf2 = self.critic(b["state"], b["action"])                                          # :240-246
         qf1_loss, qf2_loss = F.mse_loss(qf1, next_q), F.mse_loss(qf2, next_q)
-        lf_loss = F.mse_loss(self.lyapunovNet(b["state"] if self.lya_on_obs else b["center_pos"]), next_l)
         self._step(self.critic_optim, qf1_loss + qf2_loss, list(self.critic.parameters()))       # :249-251
-        self._step(self.lyaNet_optim, lf_loss, list(self.lyapunovNet.parameters()))              # :253-255
-        if self.barrier is not None:                                                             # BU :225-227, :237-240
-            barrier_loss = F.mse_loss(self.barrier(b["state"], b["action"]), next_b)
-            self._step(self.barrier_optim, barrier_loss, list(self.barrier.parameters()))
-        pi, log_pi, _ = self.policy.sample(b["state"], self.eps[1])                              # :258-261
-        min_qf_pi = torch.min(*self.critic(b["state"], pi))
-        policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                                 # :270
+        join(s1, s2)
         state = self.dynamics_model.get_state(b["state"])                                        # :380 (get_cbf_clf_part)
         if isinstance(state, tuple):
             state = state[0]
         V = self.lyapunovNet(b["center_pos"]).detach()                                           # :382-383
         targs = (b["t"], b["next_t"]) if self.with_time else ()
-        policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V, *targs), st)    # :384 -> :408-530
         with_backup = with_backup and self.backup_policy is not None
         if with_backup:
-            bpi, blog_pi, _ = self.backup_policy.sample(b["state"], self.eps[2])                 # :264-267
-            bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
-            backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()             # :273
-            backup_loss_2 = C.backup_augmented_lagrangian_device(self.backup(state, bpi, *targs), st)  # :279 -> :532-640
-        self._step(self.policy_optim, policy_loss_1 + policy_loss_2, list(self.policy.parameters()))         # :284-286
+            with fork(s1):
+                bpi, blog_pi, _ = self.backup_policy.sample(b["state"], self.eps[2])             # :264-267
+                bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
+                backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()         # :273
+                backup_req = self.backup(state, bpi, *targs)                                     # :279 -> :532-608
+        pi, log_pi, _ = self.policy.sample(b["state"], self.eps[1])                              # :258-261
+        min_qf_pi = torch.min(*self.critic(b["state"], pi))
+        policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                                 # :270
+        policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V, *targs), st)    # :384 -> :408-530
         if with_backup:
-            self._step(self.backup_policy_optim, backup_policy_loss_1 + backup_loss_2,
-                       list(self.backup_policy.parameters()))                                                # :288-290
-        if self.automatic_entropy_tuning:                                                        # :292-308
+            # the backup Lagrangian reads (and, where rho is shared, advances) what the primary one just wrote
+            if s1 is not main:
+                self._lag_event.record(main)
+                s1.wait_event(self._lag_event)
+            with torch.cuda.stream(s1):
+                backup_loss_2 = C.backup_augmented_lagrangian_device(backup_req, st)             # :611-640
+                self._step(self.backup_policy_optim, backup_policy_loss_1 + backup_loss_2,
+                           list(self.backup_policy.parameters()))                                # :288-290
+                if self.automatic_entropy_tuning:                                                # :302-308
+                    balpha_loss = -(self.backup_log_alpha * (blog_pi + self.target_entropy).detach()).mean()
+                    self._step(self.backup_alpha_optim, balpha_loss, [self.backup_log_alpha])
+                    with torch.no_grad():
+                        self.backup_alpha.copy_(self.backup_log_alpha.exp())
+        self._step(self.policy_optim, policy_loss_1 + policy_loss_2, list(self.policy.parameters()))         # :284-286
+        if self.automatic_entropy_tuning:                                                        # :292-300
             alpha_loss = -(self.log_alpha * (log_pi + self.target_entropy).detach()).mean()
             self._step(self.alpha_optim, alpha_loss, [self.log_alpha])
-            if with_backup:
-                balpha_loss = -(self.backup_log_alpha * (blog_pi + self.target_entropy).detach()).mean()
-                self._step(self.backup_alpha_optim, balpha_loss, [self.backup_log_alpha])
             with torch.no_grad():
                 self.alpha.copy_(self.log_alpha.exp())
-                if with_backup:
-                    self.backup_alpha.copy_(self.backup_log_alpha.exp())
         else:
             alpha_loss = torch.zeros((), device=self.device)
+        join(s1)
         if self.target_update_interval == 1:                                                     # :315-317
             soft_update(self.critic_target, self.critic, self.tau)
             soft_update(self.lyapunovNet_target, self.lyapunovNet, self.tau)

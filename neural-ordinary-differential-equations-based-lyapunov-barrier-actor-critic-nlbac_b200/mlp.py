@@ -108,6 +108,17 @@ class _PolicyHead(torch.autograd.Function):
         return g, None, None, None
 
 
+_TWIN_STREAMS = {}
+
+
+def _twin_side_stream(cur):
+    """One side stream per caller stream (two branches of a captured update may evaluate the same critic at once)."""
+    key = (cur.device_index, cur.cuda_stream)
+    if key not in _TWIN_STREAMS:
+        _TWIN_STREAMS[key] = torch.cuda.Stream(device=cur.device)
+    return _TWIN_STREAMS[key]
+
+
 class QNetwork(nn.Module):
     """Twin critics (U model.py:37-64): ``forward(state, action) -> (q1, q2)``."""
 
@@ -121,9 +132,23 @@ class QNetwork(nn.Module):
         self.linear6 = nn.Linear(hidden_dim, 1)
         self.apply(weights_init_)
 
+    # The two critics are independent: with ``twin_streams`` the second one runs on a side stream forked from the
+    # caller's (its backward follows it there: autograd replays each node on its forward stream).  At B = 128 / 256
+    # one critic fills < half of the SMs; GraphedUpdate switches this on, where the fork costs nothing at replay.
+    twin_streams = False
+
     def forward(self, state, action):
         xu = torch.cat([state, action], 1)
-        return mlp3(xu, self.linear1, self.linear2, self.linear3), mlp3(xu, self.linear4, self.linear5, self.linear6)
+        if not (self.twin_streams and xu.is_cuda):
+            return mlp3(xu, self.linear1, self.linear2, self.linear3), mlp3(xu, self.linear4, self.linear5, self.linear6)
+        cur = torch.cuda.current_stream()
+        side = _twin_side_stream(cur)
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            q2 = mlp3(xu, self.linear4, self.linear5, self.linear6)
+        q1 = mlp3(xu, self.linear1, self.linear2, self.linear3)
+        cur.wait_stream(side)
+        return q1, q2
 
 
 class LyaNetwork(nn.Module):
