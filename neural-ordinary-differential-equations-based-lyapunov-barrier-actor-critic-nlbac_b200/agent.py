@@ -99,7 +99,7 @@ class GraphedUpdate:
         self._node_graph = None
         self.graph = None
         self.concurrent = bool(concurrent)
-        self._streams = (torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev))
+        self._streams = tuple(torch.cuda.Stream(device=dev) for _ in range(4))
         self._lag_event = torch.cuda.Event()
         if self.concurrent:
             critic.twin_streams = critic_target.twin_streams = True
@@ -123,21 +123,19 @@ class GraphedUpdate:
         # {actor | backup actor}.  Captured, the forks become parallel branches of the graph.  `concurrent=False`
         # issues the same statements on one stream.
         main = torch.cuda.current_stream()
-        s1, s2 = (self._streams if self.concurrent else (main, main))
+        s1, s2, s3, s4 = (self._streams if self.concurrent else (main,) * 4)
+        forked = {}
 
-        forked = set()
-
-        def fork(s):
-            if s is not main:
-                s.wait_stream(main)
-                forked.add(s)
+        def fork(s, parent=main):
+            if s is not parent:
+                s.wait_stream(parent)
+                forked[s] = parent
             return torch.cuda.stream(s)
 
         def join(*ss):          # only streams forked since their last join (a capture may not wait on foreign work)
             for s in ss:
                 if s in forked:
-                    main.wait_stream(s)
-                    forked.discard(s)
+                    forked.pop(s).wait_stream(s)
 
         with fork(s1):                                                                           # :236-238, :244, :253-255
             with torch.no_grad():
@@ -168,21 +166,25 @@ class GraphedUpdate:
         targs = (b["t"], b["next_t"]) if self.with_time else ()
         with_backup = with_backup and self.backup_policy is not None
         if with_backup:
-            with fork(s1):
+            with fork(s1):       # inside each actor branch the SAC term (critic) and the Lagrangian term (NODE) fork again
                 bpi, blog_pi, _ = self.backup_policy.sample(b["state"], self.eps[2])             # :264-267
-                bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
-                backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()         # :273
+                with fork(s4, s1):
+                    bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
+                    backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()     # :273
                 backup_req = self.backup(state, bpi, *targs)                                     # :279 -> :532-608
         pi, log_pi, _ = self.policy.sample(b["state"], self.eps[1])                              # :258-261
-        min_qf_pi = torch.min(*self.critic(b["state"], pi))
-        policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                                 # :270
+        with fork(s3):
+            min_qf_pi = torch.min(*self.critic(b["state"], pi))
+            policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                             # :270
         policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V, *targs), st)    # :384 -> :408-530
+        join(s3)
         if with_backup:
             # the backup Lagrangian reads (and, where rho is shared, advances) what the primary one just wrote
             if s1 is not main:
                 self._lag_event.record(main)
                 s1.wait_event(self._lag_event)
             with torch.cuda.stream(s1):
+                join(s4)
                 backup_loss_2 = C.backup_augmented_lagrangian_device(backup_req, st)             # :611-640
                 self._step(self.backup_policy_optim, backup_policy_loss_1 + backup_loss_2,
                            list(self.backup_policy.parameters()))                                # :288-290
