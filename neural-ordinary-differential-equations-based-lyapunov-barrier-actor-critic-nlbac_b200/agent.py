@@ -100,7 +100,6 @@ class GraphedUpdate:
         self.graph = None
         self.concurrent = bool(concurrent)
         self._streams = tuple(torch.cuda.Stream(device=dev) for _ in range(4))
-        self._lag_event = torch.cuda.Event()
         if self.concurrent:
             critic.twin_streams = critic_target.twin_streams = True
 
@@ -118,73 +117,70 @@ class GraphedUpdate:
         b, F = self.buf, torch.nn.functional
         st = self.cstate
         st.set_updates_device(self.updates_dev)
-        # Independent pieces of the update run on forked streams (B = 128 / 256 kernels fill < half of the SMs, and
-        # every launch gap of one branch hides behind the other): {critic | Lyapunov | barrier} updates, then
-        # {actor | backup actor}.  Captured, the forks become parallel branches of the graph.  `concurrent=False`
-        # issues the same statements on one stream.
+        # The statements of the reference's update, issued as a dependency graph instead of a sequence (captured, the
+        # forked streams become parallel branches of the CUDA graph; at B = 128 / 256 a kernel fills < half of the SMs
+        # and every launch gap of one branch hides behind another).  What depends on what in :221-319:
+        #   main  TD targets -> critic update -> SAC term of the actor loss (needs the UPDATED critic) -> actor step
+        #   sA    Lyapunov update -> V, pi = policy.sample, the actor's Lagrangian term (NODE rollout + constraint sums:
+        #         needs the updated Lyapunov / barrier nets, NOT the critic)
+        #   sB    backup actor: sample + NODE rollout need nothing that this update writes; its SAC term waits for the
+        #         critic update, its Lagrangian for the primary one (U / C share rho)
+        #   sC    barrier-certificate update (BU / BP)
+        # `concurrent=False` issues the same statements on one stream.
         main = torch.cuda.current_stream()
-        s1, s2, s3, s4 = (self._streams if self.concurrent else (main,) * 4)
-        forked = {}
+        sA, sB, sC, _ = (self._streams if self.concurrent else (main,) * 4)
+        forked = []
 
-        def fork(s, parent=main):
-            if s is not parent:
-                s.wait_stream(parent)
-                forked[s] = parent
+        def fork(s):
+            if s is not main:
+                s.wait_stream(main)
+                forked.append(s)
             return torch.cuda.stream(s)
 
-        def join(*ss):          # only streams forked since their last join (a capture may not wait on foreign work)
-            for s in ss:
-                if s in forked:
-                    forked.pop(s).wait_stream(s)
+        def after(s, *deps):        # stream s continues only once the work issued so far on deps is done
+            for d in deps:
+                if d is not s:
+                    s.wait_stream(d)
+            return torch.cuda.stream(s)
 
-        with fork(s1):                                                                           # :236-238, :244, :253-255
+        with_backup = with_backup and self.backup_policy is not None
+        targs = (b["t"], b["next_t"]) if self.with_time else ()
+        state = self.dynamics_model.get_state(b["state"])                                        # :380 (get_cbf_clf_part)
+        if isinstance(state, tuple):
+            state = state[0]
+        with fork(sA):                                                                           # :236-238, :244, :253-255
             with torch.no_grad():
                 next_l = b["constraint"] + b["mask"] * self.gamma * self.lyapunovNet_target(
                     b["next_state"] if self.lya_on_obs else b["next_center_pos"])
             lf_loss = F.mse_loss(self.lyapunovNet(b["state"] if self.lya_on_obs else b["center_pos"]), next_l)
             self._step(self.lyaNet_optim, lf_loss, list(self.lyapunovNet.parameters()))
+        if with_backup:
+            with fork(sB):
+                bpi, blog_pi, _ = self.backup_policy.sample(b["state"], self.eps[2])             # :264-267
+                backup_req = self.backup(state, bpi, *targs)                                     # :279 -> :532-608
         with torch.no_grad():                                                                    # :231-235
             next_a, next_logp, _ = self.policy.sample(b["next_state"], self.eps[0])
             if self.barrier is not None:
-                with fork(s2):                                                                   # BU :214-216, :225-227, :237-240
+                with fork(sC):                                                                   # BU :214-216, :225-227, :237-240
                     next_b = b["barrier_signal"] + b["mask"] * self.gamma * self.barrier_target(b["next_state"], next_a)
             q1t, q2t = self.critic_target(b["next_state"], next_a)
             min_q = torch.min(q1t, q2t) - self.alpha * next_logp
             next_q = b["reward"] + b["mask"] * self.gamma * min_q
         if self.barrier is not None:
-            with torch.cuda.stream(s2):
+            with torch.cuda.stream(sC):
                 barrier_loss = F.mse_loss(self.barrier(b["state"], b["action"]), next_b)
                 self._step(self.barrier_optim, barrier_loss, list(self.barrier.parameters()))
+        with after(sA, *([sC] if self.barrier is not None else [])):
+            V = self.lyapunovNet(b["center_pos"]).detach()                                       # :382-383
+            pi, log_pi, _ = self.policy.sample(b["state"], self.eps[1])                          # :258-261
+            policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V, *targs), st)    # :384 -> :408-530
         qf1, qf2 = self.critic(b["state"], b["action"])                                          # :240-246
         qf1_loss, qf2_loss = F.mse_loss(qf1, next_q), F.mse_loss(qf2, next_q)
         self._step(self.critic_optim, qf1_loss + qf2_loss, list(self.critic.parameters()))       # :249-251
-        join(s1, s2)
-        state = self.dynamics_model.get_state(b["state"])                                        # :380 (get_cbf_clf_part)
-        if isinstance(state, tuple):
-            state = state[0]
-        V = self.lyapunovNet(b["center_pos"]).detach()                                           # :382-383
-        targs = (b["t"], b["next_t"]) if self.with_time else ()
-        with_backup = with_backup and self.backup_policy is not None
         if with_backup:
-            with fork(s1):       # inside each actor branch the SAC term (critic) and the Lagrangian term (NODE) fork again
-                bpi, blog_pi, _ = self.backup_policy.sample(b["state"], self.eps[2])             # :264-267
-                with fork(s4, s1):
-                    bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
-                    backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()     # :273
-                backup_req = self.backup(state, bpi, *targs)                                     # :279 -> :532-608
-        pi, log_pi, _ = self.policy.sample(b["state"], self.eps[1])                              # :258-261
-        with fork(s3):
-            min_qf_pi = torch.min(*self.critic(b["state"], pi))
-            policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                             # :270
-        policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V, *targs), st)    # :384 -> :408-530
-        join(s3)
-        if with_backup:
-            # the backup Lagrangian reads (and, where rho is shared, advances) what the primary one just wrote
-            if s1 is not main:
-                self._lag_event.record(main)
-                s1.wait_event(self._lag_event)
-            with torch.cuda.stream(s1):
-                join(s4)
+            with after(sB, main, sA):        # the updated critic (main) and the primary Lagrangian's rho (sA)
+                bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
+                backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()         # :273
                 backup_loss_2 = C.backup_augmented_lagrangian_device(backup_req, st)             # :611-640
                 self._step(self.backup_policy_optim, backup_policy_loss_1 + backup_loss_2,
                            list(self.backup_policy.parameters()))                                # :288-290
@@ -193,15 +189,19 @@ class GraphedUpdate:
                     self._step(self.backup_alpha_optim, balpha_loss, [self.backup_log_alpha])
                     with torch.no_grad():
                         self.backup_alpha.copy_(self.backup_log_alpha.exp())
-        self._step(self.policy_optim, policy_loss_1 + policy_loss_2, list(self.policy.parameters()))         # :284-286
-        if self.automatic_entropy_tuning:                                                        # :292-300
-            alpha_loss = -(self.log_alpha * (log_pi + self.target_entropy).detach()).mean()
-            self._step(self.alpha_optim, alpha_loss, [self.log_alpha])
-            with torch.no_grad():
-                self.alpha.copy_(self.log_alpha.exp())
-        else:
-            alpha_loss = torch.zeros((), device=self.device)
-        join(s1)
+        with after(main, sA):
+            min_qf_pi = torch.min(*self.critic(b["state"], pi))
+            policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                             # :270
+            self._step(self.policy_optim, policy_loss_1 + policy_loss_2, list(self.policy.parameters()))     # :284-286
+            if self.automatic_entropy_tuning:                                                    # :292-300
+                alpha_loss = -(self.log_alpha * (log_pi + self.target_entropy).detach()).mean()
+                self._step(self.alpha_optim, alpha_loss, [self.log_alpha])
+                with torch.no_grad():
+                    self.alpha.copy_(self.log_alpha.exp())
+            else:
+                alpha_loss = torch.zeros((), device=self.device)
+        for s_ in forked:           # join every branch before the Polyak updates and the returned values
+            main.wait_stream(s_)
         if self.target_update_interval == 1:                                                     # :315-317
             soft_update(self.critic_target, self.critic, self.tau)
             soft_update(self.lyapunovNet_target, self.lyapunovNet, self.tau)
