@@ -99,6 +99,13 @@ int nlbac_mlp_workspace_bytes(const nlbac_mlp_desc* desc, int64_t B, size_t* act
   return 0;
 }
 
+#ifndef NLBAC_MLP_STAGE
+#define NLBAC_MLP_STAGE 1         // layer 2 of the forward through the transposing shared-memory stage
+#endif
+#ifndef NLBAC_MLP_STAGE_LARGE
+#define NLBAC_MLP_STAGE_LARGE 1   // the staged layer 2 for the 8-row (large-batch) tiles too (B = 65536: 748 -> 513 us)
+#endif
+
 int nlbac_mlp_fwd(const nlbac_mlp_desc* desc, const float* const* params, const float* x, int64_t B, float* out,
                   float* act, void* stream) {
   ::nlbac::NvtxRange nvtx_range_("nlbac:mlp_fwd");
@@ -111,7 +118,10 @@ int nlbac_mlp_fwd(const nlbac_mlp_desc* desc, const float* const* params, const 
   a.x = x; a.out = out; a.act = act; a.B = B; a.n_in = desc->n_in; a.H = desc->hidden; a.n_out = desc->n_out;
   // row tile: 8 rows per CTA once that fills the SMs, 2 rows per CTA below (B = 128 -> 64 CTAs instead of 16)
   auto launch = [&]<int TM>() -> int {
-    const size_t smem = (size_t)(TM * MLP_MAX_IN + 2 * TM * a.H) * 4;
+    size_t smem = (size_t)(TM * MLP_MAX_IN + 2 * TM * a.H) * 4;
+    a.stage = (NLBAC_MLP_STAGE && a.H <= 2 * MLP_NT && a.H % MLP_KC == 0 && reinterpret_cast<uintptr_t>(a.W2) % 16 == 0 && (TM == MLP_TM_SMALL || NLBAC_MLP_STAGE_LARGE) &&
+               smem + mlp_stage_floats(a.H) * 4 <= 200 * 1024) ? 1 : 0;
+    if (a.stage) smem += mlp_stage_floats(a.H) * 4;
     NLBAC_CUDA(cudaFuncSetAttribute(mlp_fwd_kernel<TM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     mlp_fwd_kernel<TM><<<(unsigned)((B + TM - 1) / TM), MLP_NT, smem, (cudaStream_t)stream>>>(a);
     NLBAC_CUDA(cudaGetLastError());
@@ -143,7 +153,10 @@ int nlbac_mlp_bwd(const nlbac_mlp_desc* desc, const float* const* params, const 
   a.d1 = static_cast<float*>(ws);
   a.d2 = a.d1 + (size_t)B * H;
   auto launch = [&]<int TM>() -> int {
-    const size_t smem = (size_t)(TM * MLP_MAX_OUT + 2 * TM * H) * 4;
+    size_t smem = (size_t)(TM * MLP_MAX_OUT + 2 * TM * H) * 4;
+    a.stage = (NLBAC_MLP_STAGE && H <= 2 * MLP_NT && H % MLP_KC == 0 && reinterpret_cast<uintptr_t>(a.W2) % 16 == 0 &&
+               (TM == MLP_TM_SMALL || NLBAC_MLP_STAGE_LARGE) && smem + mlp_bwd_stage_floats(H) * 4 <= 200 * 1024) ? 1 : 0;
+    if (a.stage) smem += mlp_bwd_stage_floats(H) * 4;
     NLBAC_CUDA(cudaFuncSetAttribute(mlp_bwd_rows_kernel<TM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     mlp_bwd_rows_kernel<TM><<<(unsigned)((B + TM - 1) / TM), MLP_NT, smem, st>>>(a);
     NLBAC_CUDA(cudaGetLastError());
@@ -156,9 +169,9 @@ int nlbac_mlp_bwd(const nlbac_mlp_desc* desc, const float* const* params, const 
     const float* h2 = act + (size_t)B * H;
     AtbArgs g;
     g.B = B;
-    g.p[0] = {a.d1, x, grad_params[0], H, NI};        // dW1 = d1^T x
-    g.p[1] = {a.d2, h1, grad_params[2], H, H};        // dW2 = d2^T h1
-    g.p[2] = {grad_out, h2, grad_params[4], NO, H};   // dW3 = g^T h2
+    g.p[0] = {a.d1, x, grad_params[0], H, NI, grad_params[1]};        // dW1 = d1^T x,   db1 = colsum d1
+    g.p[1] = {a.d2, h1, grad_params[2], H, H, grad_params[3]};        // dW2 = d2^T h1,  db2 = colsum d2
+    g.p[2] = {grad_out, h2, grad_params[4], NO, H, grad_params[5]};   // dW3 = g^T h2,   db3 = colsum g
     ColSumArgs c;
     c.B = B;
     c.p[0] = {a.d1, grad_params[1], H};
@@ -182,9 +195,7 @@ int nlbac_mlp_bwd(const nlbac_mlp_desc* desc, const float* const* params, const 
       NLBAC_CUDA(cudaGetLastError());
       return 0;
     }
-    mlp_atb_kernel<<<dim3((H + 31) / 32, (H + 31) / 32, 3), 256, 0, st>>>(g);
-    NLBAC_CUDA(cudaGetLastError());
-    mlp_colsum_kernel<<<dim3((H + 31) / 32, 3), 256, 0, st>>>(c);
+    mlp_atb_kernel<<<dim3((H + 31) / 32, (H + 31) / 32, 3), 256, 0, st>>>(g);   // weight AND bias gradients
     NLBAC_CUDA(cudaGetLastError());
   }
   return 0;

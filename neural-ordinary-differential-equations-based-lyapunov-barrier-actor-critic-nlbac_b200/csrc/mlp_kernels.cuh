@@ -26,9 +26,30 @@ struct MlpArgs {
   float* act;        // [2, B, H] post-ReLU activations (saved for the backward) or null
   long long B;
   int n_in, H, n_out;
+  int stage;         // layer 2 reads W2 through a transposing shared-memory stage (host: H <= 512 and it fits)
 };
 
-// dynamic smem: x[TM][n_in] | h1[TM][H] | h2[TM][H]
+constexpr int MLP_KC = 32;        // W2 columns per staged chunk (one coalesced 128-byte row segment per warp load)
+#ifndef NLBAC_MLP_NBUF
+#define NLBAC_MLP_NBUF 2
+#endif
+#ifndef NLBAC_MLP_ROTATE
+#define NLBAC_MLP_ROTATE 0   // measured: 12.7 -> 13.5 us at B = 128 (the modulo costs more than lock-step L2 reads)
+#endif
+constexpr int MLP_NBUF = NLBAC_MLP_NBUF;   // chunks in flight: every CTA pulls all of W2 (256 KB at H = 256) from L2, latency-bound
+__host__ __device__ inline size_t mlp_stage_floats(int H) { return (size_t)MLP_NBUF * H * (MLP_KC + 4); }
+
+__device__ __forceinline__ void cp_async4(float* smem_dst, const float* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async16(float* smem_dst, const float* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// dynamic smem: x[TM][n_in] | h1[TM][H] | h2[TM][H] | (stage) W2 chunks [MLP_NBUF][H][MLP_KC + 4]
 template <int MLP_TM>
 __global__ void __launch_bounds__(MLP_NT) mlp_fwd_kernel(MlpArgs a) {
   extern __shared__ __align__(16) float sm[];
@@ -60,30 +81,97 @@ __global__ void __launch_bounds__(MLP_NT) mlp_fwd_kernel(MlpArgs a) {
     for (int r = 0; r < MLP_TM; ++r) h1[r * H + j] = fmaxf(acc[r], 0.f);
   }
   __syncthreads();
-  // layer 2: thread j walks row j of W2 (each 128-byte line is fetched once and consumed from L1).  Measured at B = 128
-  // (torch.profiler on a GraphedUpdate replay, round 2): 8-row tiles 18.7 us -> 2-row tiles 14.2 us; deeper unrolling
-  // neutral; one WARP per output with coalesced row reads + shuffle reductions 25.7 us (32 dependent reductions per
-  // warp cost more than the wavefronts they save) -- dropped.
-  for (int j = tid; j < H; j += MLP_NT) {
-    float acc[MLP_TM];
-    const float bj = a.b2[j];
+  if (a.stage) {
+    // layer 2, staged: W2 is nn.Linear layout [out j][in k], so "thread j walks row j" makes every warp load touch 32
+    // different 128-byte lines.  Here the 32-column chunk W2[:, k0 .. k0+32) is copied with 16-byte cp.async into a
+    // row-major tile sW[j][32 + 4] (8 lanes per 128-byte row segment: coalesced; the 144-byte row stride keeps the
+    // destination 16-byte aligned and makes thread j's LDS.128 reads conflict-free), MLP_NBUF chunks in flight.
+    // ncu at B = 128 (profiles/r2_ncu_mlp_b128.txt): the kernel is instruction-latency bound (2 warps per scheduler),
+    // so what counts is instructions per thread: 8 copies + 8 LDS.128 per chunk instead of 32 + 32.
+    float* sW = h2 + MLP_TM * H;
+    constexpr int WS = MLP_KC + 4;                 // row stride of the staged tile (floats)
+    const int nchunk = H / MLP_KC;
+    const int c_rot = NLBAC_MLP_ROTATE ? (int)(blockIdx.x % (unsigned)nchunk) : 0;
+    auto issue = [&](int c) {
+      float* dst = sW + (size_t)(c % MLP_NBUF) * H * WS + (tid & 7) * 4;
+      const float* src = a.W2 + ((c + c_rot) % nchunk) * MLP_KC + (tid & 7) * 4;
+      for (int j = tid >> 3; j < H; j += MLP_NT / 8) cp_async16(dst + j * WS, src + (size_t)j * H);
+      cp_async_commit();
+    };
+    float acc[2][MLP_TM];
 #pragma unroll
-    for (int r = 0; r < MLP_TM; ++r) acc[r] = bj;
-    const float4* w = reinterpret_cast<const float4*>(a.W2 + (size_t)j * H);
-#pragma unroll 8
-    for (int k4 = 0; k4 < H / 4; ++k4) {
-      const float4 wv = __ldg(w + k4);
+    for (int m = 0; m < 2; ++m) {
+      const int j = tid + m * MLP_NT;
+      const float bj = j < H ? a.b2[j] : 0.f;
 #pragma unroll
-      for (int r = 0; r < MLP_TM; ++r) {
-        const float4 hv = *reinterpret_cast<const float4*>(h1 + r * H + 4 * k4);
-        acc[r] = fmaf(hv.x, wv.x, acc[r]);
-        acc[r] = fmaf(hv.y, wv.y, acc[r]);
-        acc[r] = fmaf(hv.z, wv.z, acc[r]);
-        acc[r] = fmaf(hv.w, wv.w, acc[r]);
+      for (int r = 0; r < MLP_TM; ++r) acc[m][r] = bj;
+    }
+    // MLP_NBUF - 1 chunks in flight; one (possibly empty) commit group per iteration keeps the wait count constant
+#pragma unroll
+    for (int c = 0; c < MLP_NBUF - 1; ++c) {
+      if (c < nchunk) issue(c);
+      else cp_async_commit();
+    }
+    for (int c = 0; c < nchunk; ++c) {
+      cp_async_wait<MLP_NBUF - 2>();
+      __syncthreads();           // chunk c landed for every thread; everyone is done with chunk c - 1's buffer
+      if (c + MLP_NBUF - 1 < nchunk) issue(c + MLP_NBUF - 1);
+      else cp_async_commit();
+      const float* w = sW + (size_t)(c % MLP_NBUF) * H * WS;
+      const float* hc = h1 + ((c + c_rot) % nchunk) * MLP_KC;
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        const int j = tid + m * MLP_NT;
+        if (j < H) {
+#pragma unroll
+          for (int k4 = 0; k4 < MLP_KC / 4; ++k4) {
+            const float4 wv = *reinterpret_cast<const float4*>(w + j * WS + 4 * k4);
+#pragma unroll
+            for (int r = 0; r < MLP_TM; ++r) {
+              const float4 hv = *reinterpret_cast<const float4*>(hc + r * H + 4 * k4);
+              acc[m][r] = fmaf(hv.x, wv.x, acc[m][r]);
+              acc[m][r] = fmaf(hv.y, wv.y, acc[m][r]);
+              acc[m][r] = fmaf(hv.z, wv.z, acc[m][r]);
+              acc[m][r] = fmaf(hv.w, wv.w, acc[m][r]);
+            }
+          }
+        }
       }
     }
 #pragma unroll
-    for (int r = 0; r < MLP_TM; ++r) h2[r * H + j] = fmaxf(acc[r], 0.f);
+    for (int m = 0; m < 2; ++m) {
+      const int j = tid + m * MLP_NT;
+      if (j < H) {
+#pragma unroll
+        for (int r = 0; r < MLP_TM; ++r) h2[r * H + j] = fmaxf(acc[m][r], 0.f);
+      }
+    }
+  } else {
+    // layer 2 (H > 512): thread j walks row j of W2 (each 128-byte line is fetched once and consumed from L1).  Measured at B = 128
+    // (torch.profiler on a GraphedUpdate replay, round 2): 8-row tiles 18.7 us -> 2-row tiles 14.2 us; deeper unrolling
+    // neutral; one WARP per output with coalesced row reads + shuffle reductions 25.7 us (32 dependent reductions per
+    // warp cost more than the wavefronts they save) -- dropped.
+    for (int j = tid; j < H; j += MLP_NT) {
+      float acc[MLP_TM];
+      const float bj = a.b2[j];
+#pragma unroll
+      for (int r = 0; r < MLP_TM; ++r) acc[r] = bj;
+      const float4* w = reinterpret_cast<const float4*>(a.W2 + (size_t)j * H);
+#pragma unroll 8
+      for (int k4 = 0; k4 < H / 4; ++k4) {
+        const float4 wv = __ldg(w + k4);
+#pragma unroll
+        for (int r = 0; r < MLP_TM; ++r) {
+          const float4 hv = *reinterpret_cast<const float4*>(h1 + r * H + 4 * k4);
+          acc[r] = fmaf(hv.x, wv.x, acc[r]);
+          acc[r] = fmaf(hv.y, wv.y, acc[r]);
+          acc[r] = fmaf(hv.z, wv.z, acc[r]);
+          acc[r] = fmaf(hv.w, wv.w, acc[r]);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < MLP_TM; ++r) h2[r * H + j] = fmaxf(acc[r], 0.f);
+    }
   }
   __syncthreads();
   if (a.act != nullptr) {
@@ -113,9 +201,15 @@ struct MlpBwdArgs {
   float* grad_x;          // [B, n_in] or null
   long long B;
   int n_in, H, n_out;
+  int stage;              // the d1 pass reads W2 through a shared-memory stage (host: H <= 512 and it fits)
 };
+#ifndef NLBAC_MLP_BWD_NBUF
+#define NLBAC_MLP_BWD_NBUF 3
+#endif
+constexpr int MLP_BWD_NBUF = NLBAC_MLP_BWD_NBUF;
+__host__ __device__ inline size_t mlp_bwd_stage_floats(int H) { return (size_t)MLP_BWD_NBUF * MLP_KC * H; }
 
-// dynamic smem: g[TM][MAX_OUT] | d2[TM][H] | d1[TM][H]
+// dynamic smem: g[TM][MAX_OUT] | d2[TM][H] | d1[TM][H] | (stage) W2 row blocks [MLP_BWD_NBUF][MLP_KC][H]
 template <int MLP_TM>
 __global__ void __launch_bounds__(MLP_NT) mlp_bwd_rows_kernel(MlpBwdArgs a) {
   extern __shared__ __align__(16) float sm[];
@@ -155,6 +249,72 @@ __global__ void __launch_bounds__(MLP_NT) mlp_bwd_rows_kernel(MlpBwdArgs a) {
   }
   __syncthreads();
   // d1[r][k] = relu'(h1) * sum_j d2[r][j] W2[j][k]   (W2 rows read coalesced across threads k)
+  if (a.stage) {
+    // 256 dependent L2 round trips per thread at 2 warps per scheduler made this loop latency-bound (ncu at B = 128:
+    // 16 long-scoreboard stall cycles per issue).  Staged: W2 rows j0 .. j0+32 are one contiguous 32 * H block --
+    // 16-byte cp.async, MLP_BWD_NBUF blocks in flight, thread k reads sW[jj][k] (consecutive banks).
+    float* sW = s1 + MLP_TM * H;
+    const int nchunk = H / MLP_KC, per_chunk4 = MLP_KC * H / 4;
+    auto issue = [&](int c) {
+      float* dst = sW + (size_t)(c % MLP_BWD_NBUF) * MLP_KC * H;
+      const float* src = a.W2 + (size_t)c * MLP_KC * H;
+      for (int i = tid; i < per_chunk4; i += MLP_NT) cp_async16(dst + 4 * i, src + 4 * i);
+      cp_async_commit();
+    };
+    float acc[2][MLP_TM];
+#pragma unroll
+    for (int m = 0; m < 2; ++m)
+#pragma unroll
+      for (int r = 0; r < MLP_TM; ++r) acc[m][r] = 0.f;
+#pragma unroll
+    for (int c = 0; c < MLP_BWD_NBUF - 1; ++c) {
+      if (c < nchunk) issue(c);
+      else cp_async_commit();
+    }
+    for (int c = 0; c < nchunk; ++c) {
+      cp_async_wait<MLP_BWD_NBUF - 2>();
+      __syncthreads();
+      if (c + MLP_BWD_NBUF - 1 < nchunk) issue(c + MLP_BWD_NBUF - 1);
+      else cp_async_commit();
+      const float* w = sW + (size_t)(c % MLP_BWD_NBUF) * MLP_KC * H;
+#pragma unroll
+      for (int j4 = 0; j4 < MLP_KC / 4; ++j4) {
+        float4 dv[MLP_TM];
+#pragma unroll
+        for (int r = 0; r < MLP_TM; ++r) dv[r] = *reinterpret_cast<const float4*>(s2 + r * H + c * MLP_KC + 4 * j4);
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          const int k = tid + m * MLP_NT;
+          if (k < H) {
+            const float w0 = w[(4 * j4 + 0) * H + k], w1 = w[(4 * j4 + 1) * H + k];
+            const float w2 = w[(4 * j4 + 2) * H + k], w3 = w[(4 * j4 + 3) * H + k];
+#pragma unroll
+            for (int r = 0; r < MLP_TM; ++r) {
+              acc[m][r] = fmaf(dv[r].x, w0, acc[m][r]);
+              acc[m][r] = fmaf(dv[r].y, w1, acc[m][r]);
+              acc[m][r] = fmaf(dv[r].z, w2, acc[m][r]);
+              acc[m][r] = fmaf(dv[r].w, w3, acc[m][r]);
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int m = 0; m < 2; ++m) {
+      const int k = tid + m * MLP_NT;
+      if (k < H) {
+#pragma unroll
+        for (int r = 0; r < MLP_TM; ++r) {
+          float v = 0.f;
+          if (r < rows) {
+            v = h1[(row0 + r) * H + k] > 0.f ? acc[m][r] : 0.f;
+            a.d1[(row0 + r) * H + k] = v;
+          }
+          s1[r * H + k] = v;
+        }
+      }
+    }
+  } else {
   for (int k = tid; k < H; k += MLP_NT) {
     float acc[MLP_TM];
 #pragma unroll
@@ -175,6 +335,7 @@ __global__ void __launch_bounds__(MLP_NT) mlp_bwd_rows_kernel(MlpBwdArgs a) {
       s1[r * H + k] = v;
     }
   }
+  }
   __syncthreads();
   if (a.grad_x != nullptr) {
     const int warp = tid / 32, lane = tid % 32;
@@ -189,26 +350,34 @@ __global__ void __launch_bounds__(MLP_NT) mlp_bwd_rows_kernel(MlpBwdArgs a) {
 }
 
 // C[M,N] = A^T B over the batch:  C[m][n] = sum_b A[b][m] * Bm[b][n];  three problems per launch (blockIdx.z)
-struct AtbProb { const float* A; const float* Bm; float* C; int M, N; };
+struct AtbProb { const float* A; const float* Bm; float* C; int M, N; float* cs; };   // cs: column sums of A (bias gradient) or null
 struct AtbArgs { AtbProb p[3]; long long B; };
+// Small batches (B < MLP_SPLIT_MIN_B).  The batch is consumed 128 rows per step -- at B = 128 ONE global round trip per
+// CTA instead of four dependent ones (ncu: 12 long-scoreboard stall cycles per issue with 32-row steps) -- and the n = 0
+// CTAs of every M tile also reduce the column sums of A (the bias gradients), which removes mlp_colsum_kernel's launch.
+constexpr int ATB_BK = 128;
 __global__ void __launch_bounds__(256) mlp_atb_kernel(AtbArgs a) {
   const AtbProb p = a.p[blockIdx.z];
   const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
   if (m0 >= p.M || n0 >= p.N) return;
-  __shared__ float sA[32][33], sB[32][33];
+  __shared__ float sA[ATB_BK][33], sB[ATB_BK][33];
   const int tx = threadIdx.x % 32, ty = threadIdx.x / 32;  // 32 x 8; each thread 4 rows of the 32x32 tile
   float acc[4] = {0.f, 0.f, 0.f, 0.f};
-  for (long long b0 = 0; b0 < a.B; b0 += 32) {
+  float csum = 0.f;
+  const bool am = m0 + tx < p.M, bn = n0 + tx < p.N;
+  for (long long b0 = 0; b0 < a.B; b0 += ATB_BK) {
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < ATB_BK / 8; ++i) {
       const int bb = ty + 8 * i;
       const long long b = b0 + bb;
-      sA[bb][tx] = (b < a.B && m0 + tx < p.M) ? p.A[b * p.M + m0 + tx] : 0.f;
-      sB[bb][tx] = (b < a.B && n0 + tx < p.N) ? p.Bm[b * p.N + n0 + tx] : 0.f;
+      const float av = (b < a.B && am) ? p.A[b * p.M + m0 + tx] : 0.f;
+      sA[bb][tx] = av;
+      csum += av;
+      sB[bb][tx] = (b < a.B && bn) ? p.Bm[b * p.N + n0 + tx] : 0.f;
     }
     __syncthreads();
 #pragma unroll 8
-    for (int bb = 0; bb < 32; ++bb) {
+    for (int bb = 0; bb < ATB_BK; ++bb) {
       const float bv = sB[bb][tx];
 #pragma unroll
       for (int i = 0; i < 4; ++i) acc[i] = fmaf(sA[bb][ty + 8 * i], bv, acc[i]);
@@ -219,6 +388,16 @@ __global__ void __launch_bounds__(256) mlp_atb_kernel(AtbArgs a) {
   for (int i = 0; i < 4; ++i) {
     const int m = m0 + ty + 8 * i, n = n0 + tx;
     if (m < p.M && n < p.N) p.C[(size_t)m * p.N + n] = acc[i];
+  }
+  if (p.cs != nullptr && n0 == 0) {      // fixed-order reduction of the 8 partials: bit-reproducible
+    sB[ty][tx] = csum;
+    __syncthreads();
+    if (ty == 0 && am) {
+      float t = 0.f;
+#pragma unroll
+      for (int q = 0; q < 8; ++q) t += sB[q][tx];
+      p.cs[m0 + tx] = t;
+    }
   }
 }
 
