@@ -4,8 +4,8 @@
 // (U sac_cbf_clf/model.py:37-64, :67-83, :86-115; BU model.py:67-86) and autograd through them.
 // The real minibatches are B = 128 / 256 rows: the whole forward is ONE launch
 // of ceil(B/TM) CTAs that keep the row tile's activations in shared memory; weights (<= 0.27 MB)
-// are read through L1/L2.  The backward is one row-tile kernel (deltas, dX) + one batched
-// A^T B kernel for the three weight gradients + one column-sum kernel for the biases; no atomics,
+// are staged through shared memory with cp.async (the 256 x 256 layer) or read through L1/L2.  The backward is one row-tile kernel (deltas, dX) + one batched
+// A^T B kernel for the three weight gradients with the bias column sums folded in; no atomics,
 // so gradients are bit-reproducible run to run.
 #pragma once
 #include "common.cuh"
@@ -354,7 +354,7 @@ struct AtbProb { const float* A; const float* Bm; float* C; int M, N; float* cs;
 struct AtbArgs { AtbProb p[3]; long long B; };
 // Small batches (B < MLP_SPLIT_MIN_B).  The batch is consumed 128 rows per step -- at B = 128 ONE global round trip per
 // CTA instead of four dependent ones (ncu: 12 long-scoreboard stall cycles per issue with 32-row steps) -- and the n = 0
-// CTAs of every M tile also reduce the column sums of A (the bias gradients), which removes mlp_colsum_kernel's launch.
+// CTAs of every M tile also reduce the column sums of A (the bias gradients), which removes the separate column-sum launch.
 constexpr int ATB_BK = 128;
 __global__ void __launch_bounds__(256) mlp_atb_kernel(AtbArgs a) {
   const AtbProb p = a.p[blockIdx.z];
@@ -401,26 +401,9 @@ __global__ void __launch_bounds__(256) mlp_atb_kernel(AtbArgs a) {
   }
 }
 
-// db[c] = sum_b D[b][c]; three problems per launch (blockIdx.y)
+// db[c] = sum_b D[b][c] for the batch-split path (small batches: folded into mlp_atb_kernel)
 struct ColSumProb { const float* D; float* out; int N; };
 struct ColSumArgs { ColSumProb p[3]; long long B; };
-__global__ void __launch_bounds__(256) mlp_colsum_kernel(ColSumArgs a) {
-  const ColSumProb p = a.p[blockIdx.y];
-  const int c = blockIdx.x * 32 + threadIdx.x % 32;
-  const int part = threadIdx.x / 32;
-  __shared__ float red[8][33];
-  float s = 0.f;
-  if (c < p.N)
-    for (long long b = part; b < a.B; b += 8) s += p.D[b * p.N + c];
-  red[part][threadIdx.x % 32] = s;
-  __syncthreads();
-  if (part == 0 && c < p.N) {
-    float t = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; ++i) t += red[i][threadIdx.x];
-    p.out[c] = t;
-  }
-}
 
 // ------------------------------------------------------------------------------------------------
 // Large-batch forms of the two reductions above (B >= MLP_SPLIT_MIN_B: the vectorised environments of SURVEY 8f.4 feed
