@@ -301,6 +301,20 @@ int nlbac_adam_step_multi_dev(int n_tensors, float* const* params, const float* 
 int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* const* sources, const int64_t* numels,
                             float tau, void* stream);
 
+/* The tail of get_policy_loss_2 / backup_get_policy_loss_2 (U sac_cbf_clf.py:506-530, :611-640) on DEVICE-resident
+ * bookkeeping: multiplier update when *due > 0 (lambda_i <- clamp(lambda_i + rho req_i, 0.01,
+ * lambda_max)), rho <- min(rho * aug_ratio, 200), the CBF/CLF ratio |mean(c[:-1])| / |c[-1]| (clf_last: the last row is
+ * the CLF row; use_ratio / has_floor + ratio_floor as the variants set them) and
+ * loss = sum_i lambda_i w_i c_i + rho / 2 w_i^2 c_i^2, c = req - cost_limit, in ONE single-thread launch; float64
+ * scalars like the reference's Python floats.  req [m] float (m <= 32), lambda [m] / rho / due double, loss [1], coef
+ * [2m] (saved for the backward: d loss / d req_i = coef_i + 2 coef_{m+i} c_i; the ratio is a constant, as in the
+ * reference's float(ratio)). */
+int nlbac_lagrangian_fwd(const float* req, int m, int clf_last, double* lambda, double* rho, const double* due,
+                         double cost_limit, double lambda_max, double aug_ratio, int use_ratio, int has_floor,
+                         double ratio_floor, float* loss, float* coef, void* stream);
+int nlbac_lagrangian_bwd(const float* req, const float* coef, int m, double cost_limit, const float* grad_loss,
+                         float* grad_req, void* stream);
+
 /* Device-resident replay memory (U replay_memory.py:4-28, U sac_cbf_clf.py:201-229): transitions live
  * as float32 rows [capacity, width] on the device; a minibatch is ONE gather launch, out[i] = ring[idx[i]].
  * idx: DEVICE array of B row indices (int64), chosen by the host with the reference's own `random.sample`. */

@@ -150,6 +150,9 @@ def _declare(lib):
     lib.nlbac_env_pvtol_step.argtypes = [vp, vp, vp, i64] + [vp] * 9
     lib.nlbac_comm_unique_id.argtypes = [vp]
     lib.nlbac_comm_init.argtypes = [c.c_int, c.c_int, vp, c.POINTER(vp)]
+    lib.nlbac_lagrangian_fwd.argtypes = [vp, c.c_int, c.c_int, vp, vp, vp, c.c_double, c.c_double, c.c_double, c.c_int,
+                                         c.c_int, c.c_double, vp, vp, vp]
+    lib.nlbac_lagrangian_bwd.argtypes = [vp, vp, c.c_int, c.c_double, vp, vp, vp]
     lib.nlbac_allreduce_grads.argtypes = [vp, vp, c.c_size_t, vp]
     lib.nlbac_allreduce_sum_f64.argtypes = [vp, vp, c.c_size_t, vp]
     lib.nlbac_comm_destroy.argtypes = [vp]

@@ -8,6 +8,7 @@ the host exactly as written there (python floats, App. D.3).
 """
 import torch
 
+from . import _lib
 from .odeint import odeint
 from .tail import constraint_sums, lookahead, make_constraint_desc
 
@@ -116,9 +117,51 @@ class DeviceConstraintState:
         self.backup_due.copy_((updates_dev % (k * self.backup_update_interval) == 0).reshape(()).double())
 
 
+class _FusedLagrangian(torch.autograd.Function):
+    """``nlbac_lagrangian_fwd / _bwd``: the whole bookkeeping + loss as one launch per direction."""
+
+    @staticmethod
+    def forward(ctx, req, st, backup):
+        L = _lib.lib()
+        r = req.detach().contiguous()
+        m = r.numel()
+        loss = torch.empty(1, dtype=torch.float32, device=r.device)
+        coef = torch.empty(2 * m, dtype=torch.float32, device=r.device)
+        if backup:
+            lam, due = st.backup_lambda_values, st.backup_due
+            rho = st.backup_augmented_term if st.separate_backup_rho else st.augmented_term
+        else:
+            lam, rho, due = st.lambda_values, st.augmented_term, st.due
+        _lib.check(L.nlbac_lagrangian_fwd(
+            r.data_ptr(), m, 0 if backup else 1, lam.data_ptr(), rho.data_ptr(), due.data_ptr(), float(st.cost_limit),
+            float(st.lambda_max), float(st.augmented_ratio), int(bool(st.use_ratio)), int(st.ratio_floor is not None),
+            float(st.ratio_floor or 0.0), loss.data_ptr(), coef.data_ptr(), _lib.raw_stream()), "lagrangian_fwd")
+        ctx.save_for_backward(r, coef)
+        ctx.cost_limit = float(st.cost_limit)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        r, coef = ctx.saved_tensors
+        greq = torch.empty_like(r)
+        _lib.check(_lib.lib().nlbac_lagrangian_bwd(r.data_ptr(), coef.data_ptr(), r.numel(), ctx.cost_limit,
+                                                  g.contiguous().data_ptr(), greq.data_ptr(), _lib.raw_stream()),
+                   "lagrangian_bwd")
+        return greq, None, None
+
+
+def _fused_lagrangian_ok(req, st):
+    return (req.is_cuda and req.dtype == torch.float32 and req.numel() <= 32 and st.lambda_values.is_cuda and
+            st.lambda_values.dtype == torch.float64)
+
+
 def augmented_lagrangian_device(required_matrix, st):
     """``augmented_lagrangian`` (U sac_cbf_clf.py:506-530) with the multipliers, rho and the ratio kept as device
-    tensors: same arithmetic (float64 scalars like the Python floats), no host synchronisation, capturable."""
+    tensors: same arithmetic (float64 scalars like the Python floats), no host synchronisation, capturable.  On CUDA
+    the whole thing is ONE launch (``nlbac_lagrangian_fwd``); the torch statements below are the same arithmetic and
+    remain as the path for anything the kernel does not take."""
+    if _fused_lagrangian_ok(required_matrix.reshape(-1), st):
+        return _FusedLagrangian.apply(required_matrix.reshape(-1), st, False).reshape(1)
     req = required_matrix.reshape(-1)
     c = req - st.cost_limit
     cd = c.detach().double()
@@ -141,6 +184,8 @@ def augmented_lagrangian_device(required_matrix, st):
 
 def backup_augmented_lagrangian_device(backup_required_matrix, st):
     """``backup_augmented_lagrangian`` (U sac_cbf_clf.py:611-640, C :657-681, P :1022-1045) on a DeviceConstraintState."""
+    if _fused_lagrangian_ok(backup_required_matrix.reshape(-1), st):
+        return _FusedLagrangian.apply(backup_required_matrix.reshape(-1), st, True).reshape(1)
     req = backup_required_matrix.reshape(-1)
     c = req - st.cost_limit
     rho_t = st.backup_augmented_term if st.separate_backup_rho else st.augmented_term

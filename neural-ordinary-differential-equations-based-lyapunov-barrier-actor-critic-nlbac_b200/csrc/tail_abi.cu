@@ -402,6 +402,60 @@ static int check_constraint(const nlbac_constraint_desc* d) {
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Augmented Lagrangian of get_policy_loss_2 / backup_get_policy_loss_2 on device-resident state:
+// the multiplier update, the rho schedule, the CBF/CLF ratio and the loss in ONE single-thread launch (m <= 32
+// constraint rows) instead of ~25 scalar float64 torch ops; same arithmetic and the same float64 / float32 types as
+// constraints.augmented_lagrangian_device (which follows U sac_cbf_clf.py:506-530, :611-640 statement by statement).
+// ------------------------------------------------------------------------------------------------
+struct LagArgs {
+  const float* req;   // [m] required_matrix (sums over the batch)
+  double* lambda;     // [m] multipliers (updated when *due > 0)
+  double* rho;        // augmented term (advanced every call)
+  const double* due;
+  float* loss;        // [1]
+  float* coef;        // [2m]: lin_i, quad_i  (d loss / d req_i = lin_i + 2 quad_i c_i)
+  double cost_limit, lambda_max, aug_ratio, ratio_floor;
+  int m, use_ratio, has_floor, clf_last;   // clf_last: the last row is the CLF row (primary loss); 0 for the backup loss
+};
+__global__ void lagrangian_fwd_kernel(LagArgs a) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const int m = a.m;
+  const float cl = (float)a.cost_limit;
+  double ratio = 1.0;
+  if (a.clf_last && a.use_ratio) {
+    double s = 0.0;
+    for (int i = 0; i < m - 1; ++i) s += (double)(a.req[i] - cl);
+    ratio = fabs(s / (double)(m - 1)) / fabs((double)(a.req[m - 1] - cl));
+    if (a.has_floor) ratio = fmax(ratio, a.ratio_floor);
+  }
+  const double rho0 = *a.rho, due = *a.due;
+  const double rho = fmin(rho0 * a.aug_ratio, 200.0);
+  *a.rho = rho;
+  float tot = 0.f;
+  for (int i = 0; i < m; ++i) {
+    double lam = a.lambda[i];
+    if (due > 0.0) {
+      lam = fmin(fmax(lam + rho0 * (double)a.req[i], 0.01), a.lambda_max);
+      a.lambda[i] = lam;
+    }
+    const double w = (a.clf_last && i == m - 1) ? ratio : 1.0;
+    const float lin = (float)(lam * w), quad = (float)(rho / 2.0 * w * w);
+    const float c = a.req[i] - cl;
+    a.coef[i] = lin;
+    a.coef[m + i] = quad;
+    tot += lin * c + quad * c * c;
+  }
+  a.loss[0] = tot;
+}
+__global__ void lagrangian_bwd_kernel(const float* req, const float* coef, int m, float cl, const float* gloss,
+                                      float* greq) {
+  const int i = threadIdx.x;
+  if (i >= m) return;
+  const float c = req[i] - cl;
+  greq[i] = gloss[0] * (coef[i] + 2.f * coef[m + i] * c);
+}
+
 }  // namespace nlbac
 
 using namespace nlbac;
@@ -589,6 +643,27 @@ int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* c
   NLBAC_CUDA(cudaGetLastError());
   return 0;
 }
+int nlbac_lagrangian_fwd(const float* req, int m, int clf_last, double* lambda, double* rho, const double* due,
+                         double cost_limit, double lambda_max, double aug_ratio, int use_ratio, int has_floor,
+                         double ratio_floor, float* loss, float* coef, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:lagrangian_fwd");
+  NLBAC_REQUIRE(req && lambda && rho && due && loss && coef, "null pointer");
+  NLBAC_REQUIRE(m >= 1 && m <= 32 && (!clf_last || m >= 2), "bad number of constraint rows %d", m);
+  LagArgs a{req, lambda, rho, due, loss, coef, cost_limit, lambda_max, aug_ratio, ratio_floor, m, use_ratio, has_floor,
+            clf_last};
+  lagrangian_fwd_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_lagrangian_bwd(const float* req, const float* coef, int m, double cost_limit, const float* grad_loss,
+                         float* grad_req, void* stream) {
+  NLBAC_REQUIRE(req && coef && grad_loss && grad_req && m >= 1 && m <= 32, "bad arguments");
+  lagrangian_bwd_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(req, coef, m, (float)cost_limit, grad_loss, grad_req);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int nlbac_soft_update(float* target, const float* source, int64_t n, float tau, void* stream) {
   ::nlbac::NvtxRange nvtx_range_("nlbac:soft_update");
   NLBAC_REQUIRE(target && source && n >= 0, "bad arguments");
