@@ -301,8 +301,26 @@ int nlbac_adam_step_multi_dev(int n_tensors, float* const* params, const float* 
 int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* const* sources, const int64_t* numels,
                             float tau, void* stream);
 
+/* Scalar glue of update_parameters as single launches, float32, same operation order as the reference:
+ *   nlbac_td_target        out = reward + mask * gamma * (min(q1, q2) - alpha * logp)   (U sac_cbf_clf.py:234-236; q2 / logp
+ *                          NULL: the Lyapunov / barrier target reward + mask * gamma * q1, :237-238); alpha: DEVICE [1]
+ *   nlbac_mse_mean_*       F.mse_loss(pred, target) (mean over n elements) and its gradient w.r.t. pred (:244-246)
+ *   nlbac_sac_actor_term_* mean(alpha * logp - min(q1, q2)) (:270) and its gradients (torch.min semantics: the smaller
+ *                          input takes the gradient, a tie splits it).  The mean kernels are one 256-thread CTA: meant
+ *                          for the reference's B = 128 / 256 minibatches (any n is correct). */
+int nlbac_td_target(const float* q1, const float* q2, const float* logp, const float* alpha, const float* reward,
+                    const float* mask, float gamma, int64_t B, float* out, void* stream);
+int nlbac_mse_mean_fwd(const float* pred, const float* target, int64_t n, float* loss, void* stream);
+int nlbac_mse_mean_bwd(const float* pred, const float* target, int64_t n, const float* grad_loss, float* grad_pred,
+                       void* stream);
+int nlbac_sac_actor_term_fwd(const float* logp, const float* q1, const float* q2, const float* alpha, int64_t B,
+                             float* loss, void* stream);
+int nlbac_sac_actor_term_bwd(const float* q1, const float* q2, const float* alpha, int64_t B, const float* grad_loss,
+                             float* grad_logp, float* grad_q1, float* grad_q2, void* stream);
+
 /* The tail of get_policy_loss_2 / backup_get_policy_loss_2 (U sac_cbf_clf.py:506-530, :611-640) on DEVICE-resident
- * bookkeeping: multiplier update when *due > 0 (lambda_i <- clamp(lambda_i + rho req_i, 0.01,
+ * bookkeeping: multiplier update when due (updates != NULL: the device-resident update counter,
+ * due = *updates % interval == 0; else *due > 0) (lambda_i <- clamp(lambda_i + rho req_i, 0.01,
  * lambda_max)), rho <- min(rho * aug_ratio, 200), the CBF/CLF ratio |mean(c[:-1])| / |c[-1]| (clf_last: the last row is
  * the CLF row; use_ratio / has_floor + ratio_floor as the variants set them) and
  * loss = sum_i lambda_i w_i c_i + rho / 2 w_i^2 c_i^2, c = req - cost_limit, in ONE single-thread launch; float64
@@ -310,7 +328,7 @@ int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* c
  * [2m] (saved for the backward: d loss / d req_i = coef_i + 2 coef_{m+i} c_i; the ratio is a constant, as in the
  * reference's float(ratio)). */
 int nlbac_lagrangian_fwd(const float* req, int m, int clf_last, double* lambda, double* rho, const double* due,
-                         double cost_limit, double lambda_max, double aug_ratio, int use_ratio, int has_floor,
+                         const int64_t* updates, int interval, double cost_limit, double lambda_max, double aug_ratio, int use_ratio, int has_floor,
                          double ratio_floor, float* loss, float* coef, void* stream);
 int nlbac_lagrangian_bwd(const float* req, const float* coef, int m, double cost_limit, const float* grad_loss,
                          float* grad_req, void* stream);

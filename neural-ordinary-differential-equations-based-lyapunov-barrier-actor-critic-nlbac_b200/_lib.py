@@ -150,7 +150,12 @@ def _declare(lib):
     lib.nlbac_env_pvtol_step.argtypes = [vp, vp, vp, i64] + [vp] * 9
     lib.nlbac_comm_unique_id.argtypes = [vp]
     lib.nlbac_comm_init.argtypes = [c.c_int, c.c_int, vp, c.POINTER(vp)]
-    lib.nlbac_lagrangian_fwd.argtypes = [vp, c.c_int, c.c_int, vp, vp, vp, c.c_double, c.c_double, c.c_double, c.c_int,
+    lib.nlbac_td_target.argtypes = [vp, vp, vp, vp, vp, vp, c.c_float, c.c_int64, vp, vp]
+    lib.nlbac_mse_mean_fwd.argtypes = [vp, vp, c.c_int64, vp, vp]
+    lib.nlbac_mse_mean_bwd.argtypes = [vp, vp, c.c_int64, vp, vp, vp]
+    lib.nlbac_sac_actor_term_fwd.argtypes = [vp, vp, vp, vp, c.c_int64, vp, vp]
+    lib.nlbac_sac_actor_term_bwd.argtypes = [vp, vp, vp, c.c_int64, vp, vp, vp, vp, vp]
+    lib.nlbac_lagrangian_fwd.argtypes = [vp, c.c_int, c.c_int, vp, vp, vp, vp, c.c_int, c.c_double, c.c_double, c.c_double, c.c_int,
                                          c.c_int, c.c_double, vp, vp, vp]
     lib.nlbac_lagrangian_bwd.argtypes = [vp, vp, c.c_int, c.c_double, vp, vp, vp]
     lib.nlbac_allreduce_grads.argtypes = [vp, vp, c.c_size_t, vp]

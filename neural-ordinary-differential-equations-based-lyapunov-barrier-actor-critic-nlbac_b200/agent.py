@@ -13,7 +13,7 @@ import torch
 
 from . import constraints as C
 from .odeint import odeint
-from .tail import FusedAdam, soft_update
+from .tail import FusedAdam, mse_mean, sac_actor_term, soft_update, td_target
 
 
 class GraphedUpdate:
@@ -114,7 +114,7 @@ class GraphedUpdate:
     def _body(self, with_backup=True):
         """U sac_cbf_clf.py:221-319, statement for statement, on the static buffers (P :221-331 with `lya_on_obs` and, on
         the updates that skip the backup controller, `with_backup=False`)."""
-        b, F = self.buf, torch.nn.functional
+        b = self.buf
         st = self.cstate
         st.set_updates_device(self.updates_dev)
         # The statements of the reference's update, issued as a dependency graph instead of a sequence (captured, the
@@ -150,9 +150,9 @@ class GraphedUpdate:
             state = state[0]
         with fork(sA):                                                                           # :236-238, :244, :253-255
             with torch.no_grad():
-                next_l = b["constraint"] + b["mask"] * self.gamma * self.lyapunovNet_target(
-                    b["next_state"] if self.lya_on_obs else b["next_center_pos"])
-            lf_loss = F.mse_loss(self.lyapunovNet(b["state"] if self.lya_on_obs else b["center_pos"]), next_l)
+                next_l = td_target(b["constraint"], b["mask"], self.gamma, self.lyapunovNet_target(
+                    b["next_state"] if self.lya_on_obs else b["next_center_pos"]))
+            lf_loss = mse_mean(self.lyapunovNet(b["state"] if self.lya_on_obs else b["center_pos"]), next_l)
             self._step(self.lyaNet_optim, lf_loss, list(self.lyapunovNet.parameters()))
         if with_backup:
             with fork(sB):
@@ -162,25 +162,24 @@ class GraphedUpdate:
             next_a, next_logp, _ = self.policy.sample(b["next_state"], self.eps[0])
             if self.barrier is not None:
                 with fork(sC):                                                                   # BU :214-216, :225-227, :237-240
-                    next_b = b["barrier_signal"] + b["mask"] * self.gamma * self.barrier_target(b["next_state"], next_a)
+                    next_b = td_target(b["barrier_signal"], b["mask"], self.gamma,
+                                       self.barrier_target(b["next_state"], next_a))
             q1t, q2t = self.critic_target(b["next_state"], next_a)
-            min_q = torch.min(q1t, q2t) - self.alpha * next_logp
-            next_q = b["reward"] + b["mask"] * self.gamma * min_q
+            next_q = td_target(b["reward"], b["mask"], self.gamma, q1t, q2t, next_logp, self.alpha)
         if self.barrier is not None:
             with torch.cuda.stream(sC):
-                barrier_loss = F.mse_loss(self.barrier(b["state"], b["action"]), next_b)
+                barrier_loss = mse_mean(self.barrier(b["state"], b["action"]), next_b)
                 self._step(self.barrier_optim, barrier_loss, list(self.barrier.parameters()))
         with after(sA, *([sC] if self.barrier is not None else [])):
             V = self.lyapunovNet(b["center_pos"]).detach()                                       # :382-383
             pi, log_pi, _ = self.policy.sample(b["state"], self.eps[1])                          # :258-261
             policy_loss_2 = C.augmented_lagrangian_device(self.primary(state, pi, V, *targs), st)    # :384 -> :408-530
         qf1, qf2 = self.critic(b["state"], b["action"])                                          # :240-246
-        qf1_loss, qf2_loss = F.mse_loss(qf1, next_q), F.mse_loss(qf2, next_q)
+        qf1_loss, qf2_loss = mse_mean(qf1, next_q), mse_mean(qf2, next_q)
         self._step(self.critic_optim, qf1_loss + qf2_loss, list(self.critic.parameters()))       # :249-251
         if with_backup:
             with after(sB, main, sA):        # the updated critic (main) and the primary Lagrangian's rho (sA)
-                bmin_qf_pi = torch.min(*self.critic(b["state"], bpi))
-                backup_policy_loss_1 = (self.backup_alpha * blog_pi - bmin_qf_pi).mean()         # :273
+                backup_policy_loss_1 = sac_actor_term(blog_pi, *self.critic(b["state"], bpi), self.backup_alpha)  # :273
                 backup_loss_2 = C.backup_augmented_lagrangian_device(backup_req, st)             # :611-640
                 self._step(self.backup_policy_optim, backup_policy_loss_1 + backup_loss_2,
                            list(self.backup_policy.parameters()))                                # :288-290
@@ -190,8 +189,7 @@ class GraphedUpdate:
                     with torch.no_grad():
                         self.backup_alpha.copy_(self.backup_log_alpha.exp())
         with after(main, sA):
-            min_qf_pi = torch.min(*self.critic(b["state"], pi))
-            policy_loss_1 = (self.alpha * log_pi - min_qf_pi).mean()                             # :270
+            policy_loss_1 = sac_actor_term(log_pi, *self.critic(b["state"], pi), self.alpha)     # :270
             self._step(self.policy_optim, policy_loss_1 + policy_loss_2, list(self.policy.parameters()))     # :284-286
             if self.automatic_entropy_tuning:                                                    # :292-300
                 alpha_loss = -(self.log_alpha * (log_pi + self.target_entropy).detach()).mean()

@@ -106,15 +106,23 @@ class DeviceConstraintState:
         self.ratio_floor, self.use_ratio = ratio_floor, use_ratio
 
     def set_updates(self, updates):
+        self._updates_dev = None
         self.due.fill_(1.0 if updates % self.Lagrangian_multiplier_update_interval == 0 else 0.0)
         self.backup_due.fill_(1.0 if updates % (self.Lagrangian_multiplier_update_interval *
                                                  self.backup_update_interval) == 0 else 0.0)
 
     def set_updates_device(self, updates_dev):
-        """Same from a device-resident update counter (int64 tensor): no host input at all, capturable."""
-        k = self.Lagrangian_multiplier_update_interval
-        self.due.copy_((updates_dev % k == 0).reshape(()).double())
-        self.backup_due.copy_((updates_dev % (k * self.backup_update_interval) == 0).reshape(()).double())
+        """Same from a device-resident update counter (int64 tensor): no host input at all, capturable.  Nothing is
+        launched here: the fused Lagrangian kernel reads the counter itself; the torch path refreshes the flags."""
+        assert updates_dev.dtype == torch.int64 and updates_dev.is_contiguous()
+        self._updates_dev = updates_dev
+
+    def refresh_due(self):
+        ud = getattr(self, "_updates_dev", None)
+        if ud is not None:
+            k = self.Lagrangian_multiplier_update_interval
+            self.due.copy_((ud % k == 0).reshape(()).double())
+            self.backup_due.copy_((ud % (k * self.backup_update_interval) == 0).reshape(()).double())
 
 
 class _FusedLagrangian(torch.autograd.Function):
@@ -132,8 +140,11 @@ class _FusedLagrangian(torch.autograd.Function):
             rho = st.backup_augmented_term if st.separate_backup_rho else st.augmented_term
         else:
             lam, rho, due = st.lambda_values, st.augmented_term, st.due
+        ud = getattr(st, "_updates_dev", None)
+        interval = st.Lagrangian_multiplier_update_interval * (st.backup_update_interval if backup else 1)
         _lib.check(L.nlbac_lagrangian_fwd(
-            r.data_ptr(), m, 0 if backup else 1, lam.data_ptr(), rho.data_ptr(), due.data_ptr(), float(st.cost_limit),
+            r.data_ptr(), m, 0 if backup else 1, lam.data_ptr(), rho.data_ptr(), due.data_ptr(),
+            ud.data_ptr() if ud is not None else None, interval, float(st.cost_limit),
             float(st.lambda_max), float(st.augmented_ratio), int(bool(st.use_ratio)), int(st.ratio_floor is not None),
             float(st.ratio_floor or 0.0), loss.data_ptr(), coef.data_ptr(), _lib.raw_stream()), "lagrangian_fwd")
         ctx.save_for_backward(r, coef)
@@ -162,6 +173,7 @@ def augmented_lagrangian_device(required_matrix, st):
     remain as the path for anything the kernel does not take."""
     if _fused_lagrangian_ok(required_matrix.reshape(-1), st):
         return _FusedLagrangian.apply(required_matrix.reshape(-1), st, False).reshape(1)
+    st.refresh_due()
     req = required_matrix.reshape(-1)
     c = req - st.cost_limit
     cd = c.detach().double()
@@ -186,6 +198,7 @@ def backup_augmented_lagrangian_device(backup_required_matrix, st):
     """``backup_augmented_lagrangian`` (U sac_cbf_clf.py:611-640, C :657-681, P :1022-1045) on a DeviceConstraintState."""
     if _fused_lagrangian_ok(backup_required_matrix.reshape(-1), st):
         return _FusedLagrangian.apply(backup_required_matrix.reshape(-1), st, True).reshape(1)
+    st.refresh_due()
     req = backup_required_matrix.reshape(-1)
     c = req - st.cost_limit
     rho_t = st.backup_augmented_term if st.separate_backup_rho else st.augmented_term

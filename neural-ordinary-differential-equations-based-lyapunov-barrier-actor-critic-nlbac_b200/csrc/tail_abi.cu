@@ -413,9 +413,11 @@ struct LagArgs {
   double* lambda;     // [m] multipliers (updated when *due > 0)
   double* rho;        // augmented term (advanced every call)
   const double* due;
+  const long long* updates;   // device-resident update counter: due = (*updates % interval == 0); null -> *due
   float* loss;        // [1]
   float* coef;        // [2m]: lin_i, quad_i  (d loss / d req_i = lin_i + 2 quad_i c_i)
   double cost_limit, lambda_max, aug_ratio, ratio_floor;
+  int interval;
   int m, use_ratio, has_floor, clf_last;   // clf_last: the last row is the CLF row (primary loss); 0 for the backup loss
 };
 __global__ void lagrangian_fwd_kernel(LagArgs a) {
@@ -429,7 +431,8 @@ __global__ void lagrangian_fwd_kernel(LagArgs a) {
     ratio = fabs(s / (double)(m - 1)) / fabs((double)(a.req[m - 1] - cl));
     if (a.has_floor) ratio = fmax(ratio, a.ratio_floor);
   }
-  const double rho0 = *a.rho, due = *a.due;
+  const double rho0 = *a.rho;
+  const double due = a.updates != nullptr ? ((*a.updates % a.interval == 0) ? 1.0 : 0.0) : *a.due;
   const double rho = fmin(rho0 * a.aug_ratio, 200.0);
   *a.rho = rho;
   float tot = 0.f;
@@ -454,6 +457,73 @@ __global__ void lagrangian_bwd_kernel(const float* req, const float* coef, int m
   if (i >= m) return;
   const float c = req[i] - cl;
   greq[i] = gloss[0] * (coef[i] + 2.f * coef[m + i] * c);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Scalar glue of update_parameters as single launches: the TD target (U sac_cbf_clf.py:234-238),
+// F.mse_loss with mean reduction (:244-246) and the SAC term of the actor loss (:270).  Each replaces 4-10 one-op
+// torch launches per call inside the captured update; same float32 operation order as the reference's expressions
+// (no FMA contraction across its separate ops).
+// ------------------------------------------------------------------------------------------------
+__global__ void td_target_kernel(const float* q1, const float* q2, const float* logp, const float* alpha,
+                                 const float* reward, const float* mask, float gamma, long long B, float* out) {
+  const long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  float v = q1[b];
+  if (q2 != nullptr) v = fminf(v, q2[b]);
+  if (logp != nullptr) v = __fsub_rn(v, __fmul_rn(alpha[0], logp[b]));
+  out[b] = __fadd_rn(reward[b], __fmul_rn(__fmul_rn(mask[b], gamma), v));
+}
+
+__device__ __forceinline__ float block_sum_256(float v, float* red) {
+  v = warp_sum(v);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = 0.f;
+  if (threadIdx.x < 32) {
+    t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+  }
+  return t;   // valid in warp 0
+}
+__global__ void __launch_bounds__(256) mse_mean_fwd_kernel(const float* pred, const float* target, long long n,
+                                                           float* loss) {
+  __shared__ float red[8];
+  float s = 0.f;
+  for (long long i = threadIdx.x; i < n; i += 256) {
+    const float d = __fsub_rn(pred[i], target[i]);
+    s = __fadd_rn(s, __fmul_rn(d, d));
+  }
+  s = block_sum_256(s, red);
+  if (threadIdx.x == 0) loss[0] = s / (float)n;
+}
+__global__ void mse_mean_bwd_kernel(const float* pred, const float* target, long long n, const float* gloss,
+                                    float* gpred) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  gpred[i] = gloss[0] * (2.f / (float)n) * (pred[i] - target[i]);
+}
+// loss = mean(alpha * logp - min(q1, q2))
+__global__ void __launch_bounds__(256) sac_actor_fwd_kernel(const float* logp, const float* q1, const float* q2,
+                                                            const float* alpha, long long B, float* loss) {
+  __shared__ float red[8];
+  const float al = alpha[0];
+  float s = 0.f;
+  for (long long i = threadIdx.x; i < B; i += 256)
+    s = __fadd_rn(s, __fsub_rn(__fmul_rn(al, logp[i]), fminf(q1[i], q2[i])));
+  s = block_sum_256(s, red);
+  if (threadIdx.x == 0) loss[0] = s / (float)B;
+}
+// torch.min(a, b) backward: the smaller input takes the gradient, a tie splits it in halves
+__global__ void sac_actor_bwd_kernel(const float* q1, const float* q2, const float* alpha, long long B,
+                                     const float* gloss, float* glogp, float* gq1, float* gq2) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B) return;
+  const float g = gloss[0] / (float)B;
+  glogp[i] = g * alpha[0];
+  const float a = q1[i], b = q2[i];
+  gq1[i] = a < b ? -g : (a == b ? -0.5f * g : 0.f);
+  gq2[i] = b < a ? -g : (a == b ? -0.5f * g : 0.f);
 }
 
 }  // namespace nlbac
@@ -643,14 +713,59 @@ int nlbac_soft_update_multi(int n_tensors, float* const* targets, const float* c
   NLBAC_CUDA(cudaGetLastError());
   return 0;
 }
+int nlbac_td_target(const float* q1, const float* q2, const float* logp, const float* alpha, const float* reward,
+                    const float* mask, float gamma, int64_t B, float* out, void* stream) {
+  NLBAC_REQUIRE(q1 && reward && mask && out && (logp == nullptr || alpha != nullptr), "null pointer");
+  NLBAC_REQUIRE(B >= 0, "negative batch");
+  if (B == 0) return 0;
+  td_target_kernel<<<(unsigned)((B + 255) / 256), 256, 0, (cudaStream_t)stream>>>(q1, q2, logp, alpha, reward, mask,
+                                                                                  gamma, B, out);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_mse_mean_fwd(const float* pred, const float* target, int64_t n, float* loss, void* stream) {
+  NLBAC_REQUIRE(pred && target && loss && n >= 1, "bad arguments");
+  mse_mean_fwd_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(pred, target, n, loss);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_mse_mean_bwd(const float* pred, const float* target, int64_t n, const float* grad_loss, float* grad_pred,
+                       void* stream) {
+  NLBAC_REQUIRE(pred && target && grad_loss && grad_pred && n >= 1, "bad arguments");
+  mse_mean_bwd_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(pred, target, n, grad_loss,
+                                                                                     grad_pred);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_sac_actor_term_fwd(const float* logp, const float* q1, const float* q2, const float* alpha, int64_t B,
+                             float* loss, void* stream) {
+  NLBAC_REQUIRE(logp && q1 && q2 && alpha && loss && B >= 1, "bad arguments");
+  sac_actor_fwd_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(logp, q1, q2, alpha, B, loss);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_sac_actor_term_bwd(const float* q1, const float* q2, const float* alpha, int64_t B, const float* grad_loss,
+                             float* grad_logp, float* grad_q1, float* grad_q2, void* stream) {
+  NLBAC_REQUIRE(q1 && q2 && alpha && grad_loss && grad_logp && grad_q1 && grad_q2 && B >= 1, "bad arguments");
+  sac_actor_bwd_kernel<<<(unsigned)((B + 255) / 256), 256, 0, (cudaStream_t)stream>>>(q1, q2, alpha, B, grad_loss,
+                                                                                      grad_logp, grad_q1, grad_q2);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
 int nlbac_lagrangian_fwd(const float* req, int m, int clf_last, double* lambda, double* rho, const double* due,
-                         double cost_limit, double lambda_max, double aug_ratio, int use_ratio, int has_floor,
+                         const int64_t* updates, int interval, double cost_limit, double lambda_max, double aug_ratio, int use_ratio, int has_floor,
                          double ratio_floor, float* loss, float* coef, void* stream) {
   ::nlbac::NvtxRange nvtx_range_("nlbac:lagrangian_fwd");
-  NLBAC_REQUIRE(req && lambda && rho && due && loss && coef, "null pointer");
+  NLBAC_REQUIRE(req && lambda && rho && (due || updates) && loss && coef, "null pointer");
+  NLBAC_REQUIRE(updates == nullptr || interval >= 1, "bad multiplier interval %d", interval);
   NLBAC_REQUIRE(m >= 1 && m <= 32 && (!clf_last || m >= 2), "bad number of constraint rows %d", m);
-  LagArgs a{req, lambda, rho, due, loss, coef, cost_limit, lambda_max, aug_ratio, ratio_floor, m, use_ratio, has_floor,
-            clf_last};
+  LagArgs a{req, lambda, rho, due, reinterpret_cast<const long long*>(updates), loss, coef, cost_limit, lambda_max,
+            aug_ratio, ratio_floor, interval, m, use_ratio, has_floor, clf_last};
   lagrangian_fwd_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(a);
   NLBAC_CUDA(cudaGetLastError());
   return 0;

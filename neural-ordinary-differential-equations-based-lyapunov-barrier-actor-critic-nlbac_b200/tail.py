@@ -315,3 +315,79 @@ def soft_update(target, source, tau):
 def hard_update(target, source):
     for tp, sp in zip(target.parameters(), source.parameters()):
         tp.copy_(sp)
+
+
+# ------------------------------------------------------------------------------------------------
+# scalar glue of update_parameters as single launches
+# ------------------------------------------------------------------------------------------------
+def _f32c(x):
+    if not (x.is_cuda and x.dtype == torch.float32):
+        raise RuntimeError("float32 CUDA tensor expected")
+    return x.detach().contiguous()
+
+
+def td_target(reward, mask, gamma, q1, q2=None, logp=None, alpha=None):
+    """``reward + mask * gamma * (min(q1, q2) - alpha * logp)`` (U sac_cbf_clf.py:234-236) in one launch; with ``q2`` /
+    ``logp`` omitted the Lyapunov / barrier target ``reward + mask * gamma * q1`` (:237-238).  No gradient (the
+    reference computes it under ``no_grad``).  ``alpha``: float32 CUDA tensor [1]."""
+    r, m, a = _f32c(reward), _f32c(mask), _f32c(q1)
+    b2 = _f32c(q2) if q2 is not None else None
+    lp = _f32c(logp) if logp is not None else None
+    al = _f32c(alpha) if logp is not None else None
+    out = torch.empty_like(a)
+    _lib.check(_lib.lib().nlbac_td_target(a.data_ptr(), b2.data_ptr() if b2 is not None else None,
+                                          lp.data_ptr() if lp is not None else None,
+                                          al.data_ptr() if al is not None else None, r.data_ptr(), m.data_ptr(),
+                                          float(gamma), a.numel(), out.data_ptr(), _stream()), "td_target")
+    return out
+
+
+class _MseMean(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, pred, target):
+        p, t = _f32c(pred), _f32c(target)
+        assert p.shape == t.shape
+        loss = torch.empty((), dtype=torch.float32, device=p.device)
+        _lib.check(_lib.lib().nlbac_mse_mean_fwd(p.data_ptr(), t.data_ptr(), p.numel(), loss.data_ptr(), _stream()),
+                   "mse_mean_fwd")
+        ctx.save_for_backward(p, t)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        p, t = ctx.saved_tensors
+        gp = torch.empty_like(p)
+        _lib.check(_lib.lib().nlbac_mse_mean_bwd(p.data_ptr(), t.data_ptr(), p.numel(), g.contiguous().data_ptr(),
+                                                 gp.data_ptr(), _stream()), "mse_mean_bwd")
+        return gp, None
+
+
+def mse_mean(pred, target):
+    """``F.mse_loss(pred, target)`` (mean reduction; the target is a constant) as one launch per direction."""
+    return _MseMean.apply(pred, target)
+
+
+class _SacActorTerm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, log_pi, q1, q2, alpha):
+        lp, a, b, al = _f32c(log_pi), _f32c(q1), _f32c(q2), _f32c(alpha)
+        loss = torch.empty((), dtype=torch.float32, device=lp.device)
+        _lib.check(_lib.lib().nlbac_sac_actor_term_fwd(lp.data_ptr(), a.data_ptr(), b.data_ptr(), al.data_ptr(),
+                                                       lp.numel(), loss.data_ptr(), _stream()), "sac_actor_term_fwd")
+        ctx.save_for_backward(a, b, al)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        a, b, al = ctx.saved_tensors
+        glp, ga, gb = torch.empty_like(a), torch.empty_like(a), torch.empty_like(b)
+        _lib.check(_lib.lib().nlbac_sac_actor_term_bwd(a.data_ptr(), b.data_ptr(), al.data_ptr(), a.numel(),
+                                                       g.contiguous().data_ptr(), glp.data_ptr(), ga.data_ptr(),
+                                                       gb.data_ptr(), _stream()), "sac_actor_term_bwd")
+        return glp, ga, gb, None
+
+
+def sac_actor_term(log_pi, q1, q2, alpha):
+    """``(alpha * log_pi - torch.min(q1, q2)).mean()`` (U sac_cbf_clf.py:270) as one launch per direction; ``alpha`` is a
+    constant float32 CUDA tensor [1] (a Python float in the reference)."""
+    return _SacActorTerm.apply(log_pi, q1, q2, alpha)

@@ -470,3 +470,35 @@ def test_config3_learned_barrier_block_with_dopri5_inside_a_cuda_graph(golden_di
     graph.replay()
     assert _rel(req_g, req_o) <= 2 * TOL
     assert _rel(ga_g, act_o.grad) <= 10 * TOL
+
+
+@pytest.mark.parametrize("B", [1, 128, 256, 1000])
+def test_scalar_glue_kernels_match_torch_expressions(B):
+    """nlbac_td_target / nlbac_mse_mean_* / nlbac_sac_actor_term_* against the reference's own expressions
+    (U sac_cbf_clf.py:234-238, :244-246, :270), forward and backward, incl. an exact tie in min(q1, q2)."""
+    from nlbac_b200 import tail
+    g = torch.Generator().manual_seed(B)
+    r, q1, q2, lp = (torch.randn(B, 1, generator=g).cuda() for _ in range(4))
+    mask = (torch.rand(B, 1, generator=g) > 0.1).float().cuda()
+    alpha = torch.tensor([0.2], device="cuda")
+    q2[0] = q1[0]                                                   # a tie
+    want = r + mask * 0.99 * (torch.min(q1, q2) - alpha * lp)
+    assert torch.equal(tail.td_target(r, mask, 0.99, q1, q2, lp, alpha), want)
+    assert torch.equal(tail.td_target(r, mask, 0.99, q1), r + mask * 0.99 * q1)
+    # mse mean
+    p1 = q1.clone().requires_grad_(True)
+    p2 = q1.clone().requires_grad_(True)
+    l1, l2 = tail.mse_mean(p1, want), torch.nn.functional.mse_loss(p2, want)
+    (3.0 * l1).backward()
+    (3.0 * l2).backward()
+    assert l1.shape == l2.shape and _rel(l1, l2) <= 1e-6 and _rel(p1.grad, p2.grad) <= 1e-6
+    # SAC actor term
+    a = [t.clone().requires_grad_(True) for t in (lp, q1, q2)]
+    b = [t.clone().requires_grad_(True) for t in (lp, q1, q2)]
+    s1 = tail.sac_actor_term(a[0], a[1], a[2], alpha)
+    s2 = (alpha * b[0] - torch.min(b[1], b[2])).mean()
+    (2.0 * s1).backward()
+    (2.0 * s2).backward()
+    assert _rel(s1, s2) <= 1e-6
+    for x, y in zip(a, b):
+        assert _rel(x.grad, y.grad) <= 1e-6
