@@ -18,6 +18,28 @@ namespace nlbac {
 #ifndef NLBAC_ROLL_CHAINS_FWD
 #define NLBAC_ROLL_CHAINS_FWD 0
 #endif
+// k-loop of gemm_tile (4 k per iteration, 26 iterations at K = 104), per call site.  Measured at 2^20 x 20 rk4 (round 2,
+// same box): backward sweep 791 ms rolled -> 747 (x2) -> 736 (x4); forward 170 ms rolled -> 176 (x2) -> 175 (x4): the
+// backward's loads had nothing to overlap with at 2 warps per scheduler, the forward prefers the smaller loop body.
+#ifndef NLBAC_GEMM_UNROLL_FWD
+#define NLBAC_GEMM_UNROLL_FWD 1
+#endif
+#ifndef NLBAC_GEMM_UNROLL_BWD
+#define NLBAC_GEMM_UNROLL_BWD 4
+#endif
+#ifndef NLBAC_DW_UNROLL
+#define NLBAC_DW_UNROLL 8      // t-loop of dw_tile_reduce (one tile row per iteration): sweep 737 (x2) -> 731 (x4) -> 714 (x8) -> 717 ms (x16)
+#endif
+constexpr int NODE_DW_UNROLL = NLBAC_DW_UNROLL;
+#ifndef NLBAC_THIN_UNROLL
+#define NLBAC_THIN_UNROLL 16   // t-loops of the thin first / last layer dW and the bias sums in vjp_rhs_tile: sweep 714 (x2) -> 696 (x8) -> 692 ms (x16)
+#endif
+constexpr int NODE_THIN_UNROLL = NLBAC_THIN_UNROLL;
+#ifndef NLBAC_THINOUT_UNROLL
+#define NLBAC_THINOUT_UNROLL 4  // k-loop of thin_out (the H -> n_out last layer, one thread per trajectory): step 861 (x1) -> 855 ms (x4)
+#endif
+constexpr int NODE_THINOUT_UNROLL = NLBAC_THINOUT_UNROLL;
+constexpr int NODE_GEMM_UNROLL_FWD = NLBAC_GEMM_UNROLL_FWD, NODE_GEMM_UNROLL_BWD = NLBAC_GEMM_UNROLL_BWD;
 constexpr bool NODE_ROLL_CHAINS_BWD = NLBAC_ROLL_CHAINS_BWD != 0, NODE_ROLL_CHAINS_FWD = NLBAC_ROLL_CHAINS_FWD != 0;
 
 // ---------------------------------------------------------------------------------------------
@@ -84,7 +106,7 @@ struct ColMap {
 
 // acc[i][j] = bias[col j] + sum_{k<K} in[row_i][k] * W[k][col j],   row_i = tg + TG*i,  K % 4 == 0
 // Inner product runs on packed FFMA2: the 4*NV4 vector columns as pairs, the remainder column scalar.
-template <int TT, int TG, int HP>
+template <int TT, int TG, int HP, int UNR = NODE_GEMM_UNROLL_FWD>
 __device__ __forceinline__ void gemm_tile(const float* __restrict__ in, int ldi, const float* __restrict__ W,
                                           const float* __restrict__ bias, int K, int tg, int ng,
                                           float (&acc)[TT][ColMap<HP>::NN]) {
@@ -107,7 +129,7 @@ __device__ __forceinline__ void gemm_tile(const float* __restrict__ in, int ldi,
   }
   const float* inp = in + tg * ldi;
   const float* wp = W + 4 * ng;
-#pragma unroll 1
+#pragma unroll(UNR)
   for (int k = 0; k < K; k += 4) {
     float a[TT][4];
 #pragma unroll
@@ -188,7 +210,7 @@ __device__ __forceinline__ void thin_out(const float* __restrict__ arow, const f
                                          const float* __restrict__ bL, float (&o)[OUTP]) {
 #pragma unroll
   for (int j = 0; j < OUTP; ++j) o[j] = bL[j];
-#pragma unroll 1
+#pragma unroll(NODE_THINOUT_UNROLL)
   for (int k = 0; k < H; k += 4) {
     const float4 v = *reinterpret_cast<const float4*>(arow + k);
     const float a[4] = {v.x, v.y, v.z, v.w};

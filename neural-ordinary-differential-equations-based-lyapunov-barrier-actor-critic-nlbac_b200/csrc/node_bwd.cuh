@@ -73,7 +73,7 @@ __device__ __forceinline__ void dw_tile_reduce(const float* __restrict__ delta, 
     for (int p = 0; p < NP; ++p) acc2[j][p] = 0ull;
     accr[j] = 0.f;
   }
-#pragma unroll 2
+#pragma unroll(NODE_DW_UNROLL)
   for (int t = 0; t < TB; ++t) {
     const float4 dv = *reinterpret_cast<const float4*>(delta + t * RS + 4 * jg);
     const float d[4] = {dv.x, dv.y, dv.z, dv.w};
@@ -153,13 +153,13 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
     const int OUT = C::out(c), OUTP = C::outp(c);
     float acc[G::TT][ColMap<HP>::NN];
     // ---------------- forward with stored activations ----------------
-    gemm_tile<G::TT, G::TG, HP>(sX, INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), INP0, tg, ng, acc);
+    gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD>(sX, INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), INP0, tg, ng, acc);
     store_relu<G::TT, G::TG, HP>(sAct, RS, tg, ng, acc);
     __syncthreads();
 #pragma unroll 1
     for (int l = 1; l <= n; ++l) {
       const float* W = ring.acquire();
-      gemm_tile<G::TT, G::TG, HP>(sAct + (l - 1) * TB * RS, RS, W, sRes + C::off_bh(c, l), H, tg, ng, acc);
+      gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD>(sAct + (l - 1) * TB * RS, RS, W, sRes + C::off_bh(c, l), H, tg, ng, acc);
       store_relu<G::TT, G::TG, HP>(sAct + l * TB * RS, RS, tg, ng, acc);
       __syncthreads();
       ring.release(packed, off);
@@ -192,7 +192,7 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
         float s[C::OUTP_MAX];
 #pragma unroll
         for (int o = 0; o < C::OUTP_MAX; ++o) s[o] = 0.f;
-#pragma unroll 2
+#pragma unroll(NODE_THIN_UNROLL)
         for (int t = 0; t < TB; ++t) {
           const float av = aL[t * RS + tid];
 #pragma unroll
@@ -209,7 +209,7 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
         atomicAdd(grep + C::goff_b(c, n + 1) + o, s);
       }
     }
-    gemm_tile<G::TT, G::TG, HP>(sD, C::OUTP_MAX, sRes + C::off_wnl(c), nullptr, OUTP, tg, ng, acc);
+    gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD>(sD, C::OUTP_MAX, sRes + C::off_wnl(c), nullptr, OUTP, tg, ng, acc);
     __syncthreads();
     store_masked<G::TT, G::TG, HP>(aL, RS, tg, ng, acc);
     __syncthreads();
@@ -222,13 +222,13 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
         if (wactive) dw_tile_reduce<TB, RS, HP, H>(dl, ain, wjg, wkg, grep + C::goff_w(c, l));
         if (tid < H) {
           float s = 0.f;
-#pragma unroll 4
+#pragma unroll(NODE_THIN_UNROLL < 4 ? 4 : NODE_THIN_UNROLL)
           for (int t = 0; t < TB; ++t) s += dl[t * RS + tid];
           atomicAdd(grep + C::goff_b(c, l) + tid, s);
         }
       }
       const float* W = ring.acquire();
-      gemm_tile<G::TT, G::TG, HP>(dl, RS, W, nullptr, H, tg, ng, acc);
+      gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD>(dl, RS, W, nullptr, H, tg, ng, acc);
       __syncthreads();
       ring.release(packed, off);
       store_masked<G::TT, G::TG, HP>(ain, RS, tg, ng, acc);
@@ -239,7 +239,7 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
       float s[INP0], sb = 0.f;
 #pragma unroll
       for (int k = 0; k < INP0; ++k) s[k] = 0.f;
-#pragma unroll 2
+#pragma unroll(NODE_THIN_UNROLL)
       for (int t = 0; t < TB; ++t) {
         const float dv = sAct[t * RS + tid];
         sb += dv;
