@@ -39,6 +39,10 @@ constexpr int NODE_THIN_UNROLL = NLBAC_THIN_UNROLL;
 #define NLBAC_THINOUT_UNROLL 4  // k-loop of thin_out (the H -> n_out last layer, one thread per trajectory): step 861 (x1) -> 855 ms (x4)
 #endif
 constexpr int NODE_THINOUT_UNROLL = NLBAC_THINOUT_UNROLL;
+#ifndef NLBAC_DX0_UNROLL
+#define NLBAC_DX0_UNROLL 4      // j-loop of the first-layer dx (owner threads) in vjp_rhs_tile: step 855 (x1) -> 847 ms (x4)
+#endif
+constexpr int NODE_DX0_UNROLL = NLBAC_DX0_UNROLL;
 constexpr int NODE_GEMM_UNROLL_FWD = NLBAC_GEMM_UNROLL_FWD, NODE_GEMM_UNROLL_BWD = NLBAC_GEMM_UNROLL_BWD;
 constexpr bool NODE_ROLL_CHAINS_BWD = NLBAC_ROLL_CHAINS_BWD != 0, NODE_ROLL_CHAINS_FWD = NLBAC_ROLL_CHAINS_FWD != 0;
 

@@ -254,7 +254,7 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
     if (owner) {
       const float* drow = sAct + tid * RS;
       const float* Wn0 = sRes + C::off_wn0(c);
-#pragma unroll 1
+#pragma unroll(NODE_DX0_UNROLL)
       for (int j = 0; j < H; j += 4) {
         const float4 dv = *reinterpret_cast<const float4*>(drow + j);
         const float d4[4] = {dv.x, dv.y, dv.z, dv.w};

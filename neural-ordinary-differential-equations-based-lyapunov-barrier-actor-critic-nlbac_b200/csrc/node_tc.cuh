@@ -20,6 +20,12 @@
 
 namespace nlbac {
 
+#ifndef NLBAC_TC_L0_UNROLL
+#define NLBAC_TC_L0_UNROLL 1   // column-group loop of the thin first layer in the tensor-core kernels
+#endif
+constexpr int TC_L0_UNROLL = NLBAC_TC_L0_UNROLL;
+
+
 template <class C>
 struct TcCfg {
   static constexpr int ROWS = 128;                 // trajectories per tile = MMA M
@@ -433,7 +439,7 @@ __device__ __forceinline__ void eval_rhs_tc(TcGroupCtx& cx, const float (&x)[C::
     {
       const float* Wt0 = cx.sRes + C::off_wt0(c);
       const float* b0 = cx.sRes + C::off_b0(c);
-#pragma unroll 1
+#pragma unroll(TC_L0_UNROLL)
       for (int g8 = 0; g8 < T::KP / 8; ++g8) {
         Acc8 acc;
         acc8_init(acc, *reinterpret_cast<const float4*>(b0 + 8 * g8), *reinterpret_cast<const float4*>(b0 + 8 * g8 + 4));
