@@ -43,6 +43,10 @@ constexpr int NODE_THINOUT_UNROLL = NLBAC_THINOUT_UNROLL;
 #define NLBAC_DX0_UNROLL 4      // j-loop of the first-layer dx (owner threads) in vjp_rhs_tile: step 855 (x1) -> 847 ms (x4)
 #endif
 constexpr int NODE_DX0_UNROLL = NLBAC_DX0_UNROLL;
+#ifndef NLBAC_GEMM_UNROLL_FWD_SMALL
+#define NLBAC_GEMM_UNROLL_FWD_SMALL 4   // forward tiles with <= NODE_FWD_SMALL_TT rows per thread (small batches: latency-bound)
+#endif
+constexpr int NODE_GEMM_UNROLL_FWD_SMALL = NLBAC_GEMM_UNROLL_FWD_SMALL, NODE_FWD_SMALL_TT = 2;
 constexpr int NODE_GEMM_UNROLL_FWD = NLBAC_GEMM_UNROLL_FWD, NODE_GEMM_UNROLL_BWD = NLBAC_GEMM_UNROLL_BWD;
 constexpr bool NODE_ROLL_CHAINS_BWD = NLBAC_ROLL_CHAINS_BWD != 0, NODE_ROLL_CHAINS_FWD = NLBAC_ROLL_CHAINS_FWD != 0;
 

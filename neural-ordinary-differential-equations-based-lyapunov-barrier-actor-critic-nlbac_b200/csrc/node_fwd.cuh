@@ -72,14 +72,14 @@ __device__ __forceinline__ void eval_rhs_tile(const float* __restrict__ packed, 
   for (int c = 0; c < C::NCH; ++c) {
     float acc[G::TT][ColMap<C::HP>::NN];
     // first layer: sX -> sA
-    gemm_tile<G::TT, G::TG, C::HP>(sX, C::INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), C::INP0, tg, ng, acc);
+    gemm_tile<G::TT, G::TG, C::HP, (G::TT <= NODE_FWD_SMALL_TT ? NODE_GEMM_UNROLL_FWD_SMALL : NODE_GEMM_UNROLL_FWD)>(sX, C::INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), C::INP0, tg, ng, acc);
     store_relu<G::TT, G::TG, C::HP>(sA, C::RS, tg, ng, acc);
     __syncthreads();
     // hidden layers, in place
 #pragma unroll 1
     for (int l = 1; l <= C::nhc(c); ++l) {
       const float* W = ring.acquire();
-      gemm_tile<G::TT, G::TG, C::HP>(sA, C::RS, W, sRes + C::off_bh(c, l), C::H, tg, ng, acc);
+      gemm_tile<G::TT, G::TG, C::HP, (G::TT <= NODE_FWD_SMALL_TT ? NODE_GEMM_UNROLL_FWD_SMALL : NODE_GEMM_UNROLL_FWD)>(sA, C::RS, W, sRes + C::off_bh(c, l), C::H, tg, ng, acc);
       __syncthreads();
       ring.release(packed, off_t);
       store_relu<G::TT, G::TG, C::HP>(sA, C::RS, tg, ng, acc);
