@@ -290,6 +290,10 @@ static int launch_bwd(const BwdArgs& a, cudaStream_t st) {
   return 0;
 }
 
+#ifndef NLBAC_NODE_SMALL_TILE
+#define NLBAC_NODE_SMALL_TILE 1   // 8-row tiles with the narrow column map when they fit one wave (B <= 8 * SMs)
+#endif
+
 template <class C, int T>
 static int launch_dp5(const Dp5Args& a, cudaStream_t st) {
   using G = FwdGeom<C, T>;
@@ -310,6 +314,7 @@ static int launch_dp5_any(const Dp5Args& a, cudaStream_t st) {
   if ((a.B + 255) / 256 >= sms) return launch_dp5<C, 256>(a, st);
   if ((a.B + 127) / 128 >= sms) return launch_dp5<C, 128>(a, st);
   if ((a.B + 63) / 64 >= sms) return launch_dp5<C, 64>(a, st);
+  if (NLBAC_NODE_SMALL_TILE && (a.B + NODE_SMALL_TILE - 1) / NODE_SMALL_TILE <= sms) return launch_dp5<C, NODE_SMALL_TILE>(a, st);
   return launch_dp5<C, 32>(a, st);
 }
 template <class C, int TB>
@@ -501,6 +506,7 @@ int nlbac_node_solve_fwd(const nlbac_node_desc* desc, const float* packed, const
     if ((B + 255) / 256 >= sms) return launch_fwd<C, 256>(a, st);
     if ((B + 127) / 128 >= sms) return launch_fwd<C, 128>(a, st);
     if ((B + 63) / 64 >= sms) return launch_fwd<C, 64>(a, st);
+    if (NLBAC_NODE_SMALL_TILE && (B + NODE_SMALL_TILE - 1) / NODE_SMALL_TILE <= sms) return launch_fwd<C, NODE_SMALL_TILE>(a, st);
     return launch_fwd<C, 32>(a, st);
   });
 }
@@ -589,7 +595,9 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
       NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
     }
     a.grad_rep = rep;
-    int rc = ((B + 63) / 64 >= sm_count()) ? launch_bwd<C, 64>(a, st) : launch_bwd<C, 32>(a, st);
+    int rc = ((B + 63) / 64 >= sm_count()) ? launch_bwd<C, 64>(a, st)
+             : (NLBAC_NODE_SMALL_TILE && (B + NODE_SMALL_TILE - 1) / NODE_SMALL_TILE <= sm_count())
+                 ? launch_bwd<C, NODE_SMALL_TILE>(a, st) : launch_bwd<C, 32>(a, st);
     if (rc) return rc;
     if (grad_params) {
       GradTable gt = build_grad_table<C>();
@@ -757,7 +765,9 @@ int nlbac_node_dopri5_bwd(const nlbac_node_desc* desc, const float* packed, cons
       NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
     }
     a.grad_rep = rep;
-    int rc = ((B + 63) / 64 >= sm_count()) ? launch_dp5_bwd<C, 64>(a, st) : launch_dp5_bwd<C, 32>(a, st);
+    int rc = ((B + 63) / 64 >= sm_count()) ? launch_dp5_bwd<C, 64>(a, st)
+             : (NLBAC_NODE_SMALL_TILE && (B + NODE_SMALL_TILE - 1) / NODE_SMALL_TILE <= sm_count())
+                 ? launch_dp5_bwd<C, NODE_SMALL_TILE>(a, st) : launch_dp5_bwd<C, 32>(a, st);
     if (rc) return rc;
     if (grad_params) {
       GradTable gt = build_grad_table<C>();
@@ -882,7 +892,9 @@ int nlbac_node_dopri5_bwd_dev(const nlbac_node_desc* desc, const float* packed, 
       NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
     }
     a.grad_rep = rep;
-    int rc = ((B + 63) / 64 >= sm_count()) ? launch_dp5_bwd<C, 64>(a, st) : launch_dp5_bwd<C, 32>(a, st);
+    int rc = ((B + 63) / 64 >= sm_count()) ? launch_dp5_bwd<C, 64>(a, st)
+             : (NLBAC_NODE_SMALL_TILE && (B + NODE_SMALL_TILE - 1) / NODE_SMALL_TILE <= sm_count())
+                 ? launch_dp5_bwd<C, NODE_SMALL_TILE>(a, st) : launch_dp5_bwd<C, 32>(a, st);
     if (rc) return rc;
     if (grad_params) {
       GradTable gt = build_grad_table<C>();

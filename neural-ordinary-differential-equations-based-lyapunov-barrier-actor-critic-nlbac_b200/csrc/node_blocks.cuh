@@ -4,6 +4,8 @@
 // Activation layout in shared memory: row = trajectory, RS floats per row (RS/4 odd), so a warp
 // reading 32 consecutive rows with LDS.128 is bank-conflict free, and weight rows are broadcast.
 #pragma once
+#include <type_traits>
+
 #include "node_cfg.cuh"
 
 namespace nlbac {
@@ -112,13 +114,28 @@ struct ColMap {
   __device__ __forceinline__ static int col(int ng, int j) { return j < 4 * NV4 ? 32 * (j / 4) + 4 * ng + (j % 4) : 32 * NV4 + ng; }
 };
 
+constexpr int NODE_SMALL_TILE = 8;    // rows per CTA of the small-batch geometry (ColMapN)
+
+// Narrow map for the small-batch geometry (8-row tiles, B <= ~1200): HP / 4 column groups of ONE float4 each, i.e. 4
+// columns per thread instead of 13 -- the per-layer latency of the register-tiled GEMM is its k-loop over a thread's
+// columns, and at B = 128 / 256 latency is all there is (4 / 8 CTAs with the wide map).  Same index formulas as ColMap
+// (32 * v + 4 * ng with v = 0), so gemm_tile / store_relu / store_masked take it as a template argument.
+template <int HP>
+struct ColMapN {
+  static constexpr int NV4 = 1;
+  static constexpr int NREM = 0;
+  static constexpr int NN = 4;
+  static constexpr int NGRP = HP / 4;
+  static_assert(HP % 4 == 0, "narrow column map: HP = 4m");
+  __device__ __forceinline__ static int col(int ng, int j) { return 4 * ng + j; }
+};
+
 // acc[i][j] = bias[col j] + sum_{k<K} in[row_i][k] * W[k][col j],   row_i = tg + TG*i,  K % 4 == 0
 // Inner product runs on packed FFMA2: the 4*NV4 vector columns as pairs, the remainder column scalar.
-template <int TT, int TG, int HP, int UNR = NODE_GEMM_UNROLL_FWD>
+template <int TT, int TG, int HP, int UNR = NODE_GEMM_UNROLL_FWD, class CM = ColMap<HP>>
 __device__ __forceinline__ void gemm_tile(const float* __restrict__ in, int ldi, const float* __restrict__ W,
                                           const float* __restrict__ bias, int K, int tg, int ng,
-                                          float (&acc)[TT][ColMap<HP>::NN]) {
-  using CM = ColMap<HP>;
+                                          float (&acc)[TT][CM::NN]) {
   constexpr int NP = 2 * CM::NV4;  // column pairs
   unsigned long long acc2[TT][NP];
   float accr[TT];
@@ -175,10 +192,9 @@ __device__ __forceinline__ void gemm_tile(const float* __restrict__ in, int ldi,
 }
 
 // out[row_i][col j] = relu(acc[i][j])
-template <int TT, int TG, int HP>
+template <int TT, int TG, int HP, class CM = ColMap<HP>>
 __device__ __forceinline__ void store_relu(float* __restrict__ out, int ldo, int tg, int ng,
-                                           const float (&acc)[TT][ColMap<HP>::NN]) {
-  using CM = ColMap<HP>;
+                                           const float (&acc)[TT][CM::NN]) {
 #pragma unroll
   for (int i = 0; i < TT; ++i) {
     float* o = out + (size_t)(tg + TG * i) * ldo;
@@ -192,9 +208,8 @@ __device__ __forceinline__ void store_relu(float* __restrict__ out, int ldo, int
 }
 
 // out[row_i][col j] = acc[i][j] where out[row_i][col j] > 0 else 0   (ReLU backward, in place over the activation)
-template <int TT, int TG, int HP>
-__device__ __forceinline__ void store_masked(float* out, int ldo, int tg, int ng, const float (&acc)[TT][ColMap<HP>::NN]) {
-  using CM = ColMap<HP>;
+template <int TT, int TG, int HP, class CM = ColMap<HP>>
+__device__ __forceinline__ void store_masked(float* out, int ldo, int tg, int ng, const float (&acc)[TT][CM::NN]) {
 #pragma unroll
   for (int i = 0; i < TT; ++i) {
     float* o = out + (size_t)(tg + TG * i) * ldo;

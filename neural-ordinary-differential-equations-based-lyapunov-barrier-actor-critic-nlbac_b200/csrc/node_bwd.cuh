@@ -31,10 +31,13 @@ struct BwdArgs {
 
 template <class C, int TB>
 struct BwdGeom {
-  static constexpr int TG = 32;
+  static constexpr bool SMALL = (TB == NODE_SMALL_TILE);
+  static constexpr int TG = SMALL ? NODE_SMALL_TILE : 32;
   static constexpr int TT = TB / TG;
-  static constexpr int NGRP = 8;
-  static constexpr int NT = TG * NGRP;
+  using CM = std::conditional_t<SMALL, ColMapN<C::HP>, ColMap<C::HP>>;
+  static constexpr int NGRP = SMALL ? C::HP / 4 : 8;      // column groups of the GEMM / store mapping
+  static constexpr int NGRP_DW = 8;                        // dw_tile_reduce keeps the wide map (its loop is over the tile rows)
+  static constexpr int NT = (TG * NGRP + 31) / 32 * 32;
   static_assert(TB % TG == 0 && TT >= 1, "tile size");
   static constexpr int CYC = 2 * C::NHID;  // packets per stage: forward (transposed) + backward (natural)
   static constexpr int NSLOT = (CYC * C::HID_BYTES <= 64 * 1024) ? CYC : 2;
@@ -46,7 +49,7 @@ struct BwdGeom {
   static constexpr int OFF_RING = OFF_RES + C::RES_ALL;
   static constexpr int OFF_BAR = OFF_RING + NSLOT * C::HID_FLOATS;
   static constexpr size_t SMEM_BYTES = (size_t)OFF_BAR * 4 + (NSLOT + 1) * 8;
-  static_assert(NT >= TB && NT >= (C::H / 4) * NGRP && NT >= C::H + C::OUTP_MAX, "thread roles");
+  static_assert(NT >= TB && NT >= (C::H / 4) * NGRP_DW && NT >= C::H + C::OUTP_MAX, "thread roles");
   static_assert(SMEM_BYTES <= 227 * 1024, "shared memory budget");
 
   // packet offset for ring sequence number s
@@ -128,7 +131,9 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
   const int tid = threadIdx.x;
   const bool owner = tid < TB;
   const int tg = tid % G::TG, ng = tid / G::TG;
-  const int wjg = tid / G::NGRP, wkg = tid % G::NGRP;  // dW tile of this thread: rows 4*wjg.., column group wkg
+  const int wjg = tid / G::NGRP_DW, wkg = tid % G::NGRP_DW;  // dW tile of this thread: rows 4*wjg.., column group wkg
+  const bool gact = ng < G::NGRP;
+  using CM = typename G::CM;
   const bool wactive = 4 * wjg < H;
   auto off = [](uint32_t s) { return G::pkt_off(s); };
 
@@ -151,16 +156,16 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
   for (int c = 0; c < C::NCH; ++c) {
     const int n = C::nhc(c);
     const int OUT = C::out(c), OUTP = C::outp(c);
-    float acc[G::TT][ColMap<HP>::NN];
+    float acc[G::TT][CM::NN];
     // ---------------- forward with stored activations ----------------
-    gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD>(sX, INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), INP0, tg, ng, acc);
-    store_relu<G::TT, G::TG, HP>(sAct, RS, tg, ng, acc);
+    if (gact) gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD, CM>(sX, INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), INP0, tg, ng, acc);
+    if (gact) store_relu<G::TT, G::TG, HP, CM>(sAct, RS, tg, ng, acc);
     __syncthreads();
 #pragma unroll 1
     for (int l = 1; l <= n; ++l) {
       const float* W = ring.acquire();
-      gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD>(sAct + (l - 1) * TB * RS, RS, W, sRes + C::off_bh(c, l), H, tg, ng, acc);
-      store_relu<G::TT, G::TG, HP>(sAct + l * TB * RS, RS, tg, ng, acc);
+      if (gact) gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD, CM>(sAct + (l - 1) * TB * RS, RS, W, sRes + C::off_bh(c, l), H, tg, ng, acc);
+      if (gact) store_relu<G::TT, G::TG, HP, CM>(sAct + l * TB * RS, RS, tg, ng, acc);
       __syncthreads();
       ring.release(packed, off);
     }
@@ -209,9 +214,9 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
         atomicAdd(grep + C::goff_b(c, n + 1) + o, s);
       }
     }
-    gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD>(sD, C::OUTP_MAX, sRes + C::off_wnl(c), nullptr, OUTP, tg, ng, acc);
+    if (gact) gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD, CM>(sD, C::OUTP_MAX, sRes + C::off_wnl(c), nullptr, OUTP, tg, ng, acc);
     __syncthreads();
-    store_masked<G::TT, G::TG, HP>(aL, RS, tg, ng, acc);
+    if (gact) store_masked<G::TT, G::TG, HP, CM>(aL, RS, tg, ng, acc);
     __syncthreads();
     // ---------------- hidden layers, reverse ----------------
 #pragma unroll 1
@@ -228,10 +233,10 @@ __device__ __forceinline__ void vjp_rhs_tile(const float* __restrict__ packed, f
         }
       }
       const float* W = ring.acquire();
-      gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD>(dl, RS, W, nullptr, H, tg, ng, acc);
+      if (gact) gemm_tile<G::TT, G::TG, HP, NODE_GEMM_UNROLL_BWD, CM>(dl, RS, W, nullptr, H, tg, ng, acc);
       __syncthreads();
       ring.release(packed, off);
-      store_masked<G::TT, G::TG, HP>(ain, RS, tg, ng, acc);
+      if (gact) store_masked<G::TT, G::TG, HP, CM>(ain, RS, tg, ng, acc);
       __syncthreads();
     }
     // ---------------- first layer: dW0, db0 (thin), dx ----------------

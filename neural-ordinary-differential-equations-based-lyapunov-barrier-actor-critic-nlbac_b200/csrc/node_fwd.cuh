@@ -27,10 +27,12 @@ struct FwdArgs {
 
 template <class C, int T>
 struct FwdGeom {
-  static constexpr int TG = 32;       // row-threads per column group = one warp
+  static constexpr bool SMALL = (T == NODE_SMALL_TILE);
+  static constexpr int TG = SMALL ? NODE_SMALL_TILE : 32;   // row-threads per column group (regular: one warp)
   static constexpr int TT = T / TG;   // trajectories per thread
-  static constexpr int NGRP = 8;      // column groups (ColMap)
-  static constexpr int NT = TG * NGRP;
+  using CM = std::conditional_t<SMALL, ColMapN<C::HP>, ColMap<C::HP>>;
+  static constexpr int NGRP = SMALL ? C::HP / 4 : 8;        // column groups
+  static constexpr int NT = (TG * NGRP + 31) / 32 * 32;     // small: 8 x 26 = 208 -> 224 (threads past NGRP idle in the GEMMs)
   static_assert(T % TG == 0 && TT >= 1, "tile size");
   static constexpr int NSLOT = C::NHID <= 2 ? C::NHID : 2;
   static constexpr int OFF_A = 0;
@@ -53,6 +55,8 @@ __device__ __forceinline__ void eval_rhs_tile(const float* __restrict__ packed, 
   const int tid = threadIdx.x;
   const bool owner = tid < T;
   const int tg = tid % G::TG, ng = tid / G::TG;
+  const bool gact = ng < G::NGRP;
+  using CM = typename G::CM;
   auto off_t = [](uint32_t s) { return C::off_hid_t(s % C::NHID); };
 
   if (owner) {
@@ -70,19 +74,21 @@ __device__ __forceinline__ void eval_rhs_tile(const float* __restrict__ packed, 
   float fo[C::outp(0)];
 #pragma unroll(NODE_ROLL_CHAINS_FWD ? 1 : 2)
   for (int c = 0; c < C::NCH; ++c) {
-    float acc[G::TT][ColMap<C::HP>::NN];
+    float acc[G::TT][CM::NN];
     // first layer: sX -> sA
-    gemm_tile<G::TT, G::TG, C::HP, (G::TT <= NODE_FWD_SMALL_TT ? NODE_GEMM_UNROLL_FWD_SMALL : NODE_GEMM_UNROLL_FWD)>(sX, C::INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), C::INP0, tg, ng, acc);
-    store_relu<G::TT, G::TG, C::HP>(sA, C::RS, tg, ng, acc);
+    if (gact) {
+      gemm_tile<G::TT, G::TG, C::HP, (G::TT <= NODE_FWD_SMALL_TT ? NODE_GEMM_UNROLL_FWD_SMALL : NODE_GEMM_UNROLL_FWD), CM>(sX, C::INP0, sRes + C::off_wt0(c), sRes + C::off_b0(c), C::INP0, tg, ng, acc);
+      store_relu<G::TT, G::TG, C::HP, CM>(sA, C::RS, tg, ng, acc);
+    }
     __syncthreads();
     // hidden layers, in place
 #pragma unroll 1
     for (int l = 1; l <= C::nhc(c); ++l) {
       const float* W = ring.acquire();
-      gemm_tile<G::TT, G::TG, C::HP, (G::TT <= NODE_FWD_SMALL_TT ? NODE_GEMM_UNROLL_FWD_SMALL : NODE_GEMM_UNROLL_FWD)>(sA, C::RS, W, sRes + C::off_bh(c, l), C::H, tg, ng, acc);
+      if (gact) gemm_tile<G::TT, G::TG, C::HP, (G::TT <= NODE_FWD_SMALL_TT ? NODE_GEMM_UNROLL_FWD_SMALL : NODE_GEMM_UNROLL_FWD), CM>(sA, C::RS, W, sRes + C::off_bh(c, l), C::H, tg, ng, acc);
       __syncthreads();
       ring.release(packed, off_t);
-      store_relu<G::TT, G::TG, C::HP>(sA, C::RS, tg, ng, acc);
+      if (gact) store_relu<G::TT, G::TG, C::HP, CM>(sA, C::RS, tg, ng, acc);
       __syncthreads();
     }
     // thin last layer, one thread per trajectory
