@@ -290,6 +290,10 @@ static int launch_bwd(const BwdArgs& a, cudaStream_t st) {
   return 0;
 }
 
+#ifndef NLBAC_BWD_LARGE_TB
+#define NLBAC_BWD_LARGE_TB 64      // rows per CTA of the backward at large batches (a multiple of 32: wide map; else narrow).
+                                   // Measured at 2^20 x 20 rk4: sweep 688 ms (64, wide) vs 731 (56, narrow) vs 789 (40, narrow)
+#endif
 #ifndef NLBAC_NODE_SMALL_TILE
 #define NLBAC_NODE_SMALL_TILE 1   // 8-row tiles with the narrow column map when they fit one wave (B <= 8 * SMs)
 #endif
@@ -595,7 +599,7 @@ int nlbac_node_solve_bwd(const nlbac_node_desc* desc, const float* packed, const
       NLBAC_CUDA(cudaMemsetAsync(rep, 0, (size_t)NREP * C::NGRAD * 4, st));
     }
     a.grad_rep = rep;
-    int rc = ((B + 63) / 64 >= sm_count()) ? launch_bwd<C, 64>(a, st)
+    int rc = ((B + 63) / 64 >= sm_count()) ? launch_bwd<C, NLBAC_BWD_LARGE_TB>(a, st)
              : (NLBAC_NODE_SMALL_TILE && (B + NODE_SMALL_TILE - 1) / NODE_SMALL_TILE <= sm_count())
                  ? launch_bwd<C, NODE_SMALL_TILE>(a, st) : launch_bwd<C, 32>(a, st);
     if (rc) return rc;

@@ -31,7 +31,7 @@ struct BwdArgs {
 
 template <class C, int TB>
 struct BwdGeom {
-  static constexpr bool SMALL = (TB == NODE_SMALL_TILE);
+  static constexpr bool SMALL = (TB % 32 != 0);              // narrow geometry: 8 row-threads x HP/4 column groups
   static constexpr int TG = SMALL ? NODE_SMALL_TILE : 32;
   static constexpr int TT = TB / TG;
   using CM = std::conditional_t<SMALL, ColMapN<C::HP>, ColMap<C::HP>>;

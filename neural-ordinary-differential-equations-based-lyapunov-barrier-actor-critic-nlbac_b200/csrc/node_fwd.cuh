@@ -27,7 +27,7 @@ struct FwdArgs {
 
 template <class C, int T>
 struct FwdGeom {
-  static constexpr bool SMALL = (T == NODE_SMALL_TILE);
+  static constexpr bool SMALL = (T % 32 != 0);               // narrow geometry: 8 row-threads x HP/4 column groups
   static constexpr int TG = SMALL ? NODE_SMALL_TILE : 32;   // row-threads per column group (regular: one warp)
   static constexpr int TT = T / TG;   // trajectories per thread
   using CM = std::conditional_t<SMALL, ColMapN<C::HP>, ColMap<C::HP>>;
