@@ -439,14 +439,27 @@ __global__ void __launch_bounds__(256) mlp_atb_split_kernel(AtbSplitArgs a) {
   for (int i = 0; i < 4; ++i)
 #pragma unroll
     for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
-  for (long long b0 = b_lo; b0 < b_hi; b0 += 32) {
+  // Operands of a 32-row step go through registers: all 16 global loads are issued together (generic pointers: a store
+  // to sA / sB between two loads would have to be assumed to alias them and serialise the round trips), and the NEXT
+  // step's loads are in flight while this step's products are formed.
+  float ra[8], rb[8];
+  auto gload = [&](long long b0) {
     const long long b = b0 + lr;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
-      sA[lr][lc + c] = (b < b_hi && m0 + lc + c < p.M) ? p.A[b * p.M + m0 + lc + c] : 0.f;
-      sB[lr][lc + c] = (b < b_hi && n0 + lc + c < p.N) ? p.Bm[b * p.N + n0 + lc + c] : 0.f;
+      ra[c] = (b < b_hi && m0 + lc + c < p.M) ? __ldg(p.A + b * p.M + m0 + lc + c) : 0.f;
+      rb[c] = (b < b_hi && n0 + lc + c < p.N) ? __ldg(p.Bm + b * p.N + n0 + lc + c) : 0.f;
+    }
+  };
+  gload(b_lo);
+  for (long long b0 = b_lo; b0 < b_hi; b0 += 32) {
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      sA[lr][lc + c] = ra[c];
+      sB[lr][lc + c] = rb[c];
     }
     __syncthreads();
+    if (b0 + 32 < b_hi) gload(b0 + 32);
 #pragma unroll 8
     for (int bb = 0; bb < 32; ++bb) {
       const float4 av = *reinterpret_cast<const float4*>(&sA[bb][4 * ty]);
