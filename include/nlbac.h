@@ -292,9 +292,11 @@ int nlbac_soft_update(float* target, const float* source, int64_t n, float tau, 
 int nlbac_adam_step_multi(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
                           float* const* exp_avg_sq, const int64_t* numels, int step, float lr, float beta1,
                           float beta2, float eps, void* stream);
-/* Same update with the step counter kept ON THE DEVICE (*step_dev, int32; incremented first when `bump` != 0, then
- * read by the update kernel, which forms the bias corrections itself): nothing depends on host state, so the call
- * can be captured in a CUDA graph and replayed. */
+/* Same update with the step counter kept ON THE DEVICE: step_dev = DEVICE int32[2], zero-initialised by the caller --
+ * [0] the step count, [1] a ticket word the kernel uses and leaves at zero.  With `bump` != 0 the launch works with
+ * step_dev[0] + 1 and writes it back from its last block (no separate increment launch); with bump = 0 (further chunks
+ * of the same optimiser step) it reads step_dev[0].  The kernel forms the bias corrections itself: nothing depends on
+ * host state, so the call can be captured in a CUDA graph and replayed. */
 int nlbac_adam_step_multi_dev(int n_tensors, float* const* params, const float* const* grads, float* const* exp_avg,
                               float* const* exp_avg_sq, const int64_t* numels, int* step_dev, int bump, float lr,
                               float beta1, float beta2, float eps, void* stream);

@@ -353,23 +353,46 @@ __global__ void adam_multi_kernel(const __grid_constant__ AdamTable tb, float lr
   }
 }
 // Adam with the step counter ON THE DEVICE (graph-capturable: nothing about the update depends on host state).
-// Launched after bump_step_kernel; every thread forms the two bias corrections from *step itself.
-__global__ void bump_step_kernel(int* step) { *step += 1; }
-__global__ void adam_multi_dev_kernel(const __grid_constant__ AdamTable tb, const int* __restrict__ step_ptr, float lr,
+// step_ctl[0] = step counter, step_ctl[1] = ticket word (both zero-initialised by the caller).  With `bump` the launch
+// works with step = step_ctl[0] + 1 and the LAST block to finish (ticket) writes it back: every other block has read the
+// counter by then, so no separate increment launch is needed.
+__global__ void adam_multi_dev_kernel(const __grid_constant__ AdamTable tb, int* step_ctl, int bump, float lr,
                                       float b1, float b2, float eps) {
   const int k = blockIdx.y;
   float* p = tb.p[k]; const float* g = tb.g[k]; float* m = tb.m[k]; float* v = tb.v[k];
   const long long n = tb.n[k];
-  const int step = *step_ptr;
-  const float bc1 = (float)(1.0 - pow((double)b1, (double)step));
-  const float bc2_sqrt = (float)sqrt(1.0 - pow((double)b2, (double)step));
+  // the two bias corrections are the same for the whole launch: ONE thread per block forms them (two double-precision
+  // pow() per THREAD were most of this kernel's 8-9 us at 70-140 k parameters)
+  __shared__ float s_bc[2];
+  __shared__ int s_step;
+  const bool work = (long long)blockIdx.x * blockDim.x < n;   // small tensors of the group: most blocks have nothing to do
+  if (threadIdx.x == 0) {
+    const int step = *reinterpret_cast<volatile int*>(step_ctl) + (bump ? 1 : 0);
+    s_step = step;
+    if (work) {
+      s_bc[0] = (float)(1.0 - pow((double)b1, (double)step));
+      s_bc[1] = (float)sqrt(1.0 - pow((double)b2, (double)step));
+    }
+  }
+  __syncthreads();
+  if (work) {
+  const float bc1 = s_bc[0], bc2_sqrt = s_bc[1];
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
-    const float gi = g[i];
-    const float mi = m[i] + (gi - m[i]) * (1.f - b1);
-    const float vi = fmaf(v[i], b2, (1.f - b2) * gi * gi);
+    const float gi = g[i], m0 = m[i], v0 = v[i], p0 = p[i];   // all loads before the first store
+    const float mi = m0 + (gi - m0) * (1.f - b1);
+    const float vi = fmaf(v0, b2, (1.f - b2) * gi * gi);
     m[i] = mi; v[i] = vi;
     const float denom = sqrtf(vi) / bc2_sqrt + eps;
-    p[i] = p[i] - (lr / bc1) * (mi / denom);
+    p[i] = p0 - (lr / bc1) * (mi / denom);
+  }
+  }
+  if (bump && threadIdx.x == 0) {
+    const unsigned total = gridDim.x * gridDim.y;
+    const unsigned t = atomicAdd(reinterpret_cast<unsigned*>(step_ctl + 1), 1u);
+    if (t == total - 1) {            // every block has read step_ctl[0] (it took its ticket after doing so)
+      step_ctl[0] = s_step;
+      step_ctl[1] = 0;
+    }
   }
 }
 __global__ void soft_update_multi_kernel(const __grid_constant__ PolyakTable tb, float tau) {
@@ -677,10 +700,7 @@ int nlbac_adam_step_multi_dev(int n_tensors, float* const* params, const float* 
   NLBAC_REQUIRE(n_tensors >= 0 && n_tensors <= NLBAC_MAX_TENSORS, "n_tensors=%d (max %d)", n_tensors, NLBAC_MAX_TENSORS);
   NLBAC_REQUIRE(params && grads && exp_avg && exp_avg_sq && numels && step_dev, "bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
-  if (bump) {
-    bump_step_kernel<<<1, 1, 0, st>>>(step_dev);
-    NLBAC_CUDA(cudaGetLastError());
-  }
+  NLBAC_REQUIRE(n_tensors > 0 || !bump, "bump needs at least one tensor (the update kernel advances the counter)");
   if (n_tensors == 0) return 0;
   AdamTable tb;
   long long nmax = 0;
@@ -690,8 +710,8 @@ int nlbac_adam_step_multi_dev(int n_tensors, float* const* params, const float* 
     tb.p[k] = params[k]; tb.g[k] = grads[k]; tb.m[k] = exp_avg[k]; tb.v[k] = exp_avg_sq[k]; tb.n[k] = numels[k];
     if (numels[k] > nmax) nmax = numels[k];
   }
-  if (nmax == 0) return 0;
-  adam_multi_dev_kernel<<<dim3(tail_grid(nmax, 256), n_tensors), 256, 0, st>>>(tb, step_dev, lr, beta1, beta2, eps);
+  if (nmax == 0) nmax = 1;   // the launch still advances the counter
+  adam_multi_dev_kernel<<<dim3(tail_grid(nmax, 256), n_tensors), 256, 0, st>>>(tb, step_dev, bump, lr, beta1, beta2, eps);
   NLBAC_CUDA(cudaGetLastError());
   return 0;
 }

@@ -37,7 +37,7 @@ class GraphedTrainStep:
         self.time = torch.zeros(B, 1, device=dev) if has_time else None
         self.exp_avg = [torch.zeros_like(p) for p in self.params]
         self.exp_avg_sq = [torch.zeros_like(p) for p in self.params]
-        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.step_dev = torch.zeros(2, dtype=torch.int32, device=dev)      # step count, ticket word of the Adam kernel
         if len(self.params) > _lib.MAX_TENSORS:
             raise RuntimeError("GraphedTrainStep: at most %d parameter tensors" % _lib.MAX_TENSORS)
         # eager warm-up on a side stream (lazy kernel attributes, allocator), then put everything back

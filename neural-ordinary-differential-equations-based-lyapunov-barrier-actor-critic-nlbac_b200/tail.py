@@ -273,7 +273,7 @@ def _fused_adam_step_capturable(self, L, group, b1, b2):
         return
     key = id(group)
     if key not in self._step_dev:
-        self._step_dev[key] = torch.zeros(1, dtype=torch.int32, device=items[0][0].device)
+        self._step_dev[key] = torch.zeros(2, dtype=torch.int32, device=items[0][0].device)   # step, ticket word
     step_dev = self._step_dev[key]
     for lo in range(0, len(items), _lib.MAX_TENSORS):
         chunk = items[lo:lo + _lib.MAX_TENSORS]
