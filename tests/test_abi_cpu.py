@@ -64,3 +64,16 @@ def test_forward_api_matches_oracle_rhs(pkg):
         m.load_state_dict(ref.state_dict())
         s = torch.randn(7, D)
         assert torch.allclose(m(None, s), ref(None, s), atol=1e-6)
+
+
+def test_import_shim_aliases_submodules():
+    """``from nlbac_b200.odeint import ...`` must reuse the already-loaded submodule: a second copy would carry its own
+    caches and rebind ``nlbac_b200.odeint`` (the function) to the module (regression: round 2)."""
+    import sys
+    import nlbac_b200
+    from nlbac_b200.odeint import describe            # noqa: F401
+    from nlbac_b200 import tail, parallel, dopri5      # noqa: F401
+    assert callable(nlbac_b200.odeint) and not isinstance(nlbac_b200.odeint, type(sys))
+    long_name = nlbac_b200.__name__
+    for sub in ("odeint", "tail", "constraints", "agent", "parallel", "dopri5", "_lib"):
+        assert sys.modules["nlbac_b200." + sub] is sys.modules[long_name + "." + sub], sub
