@@ -339,6 +339,13 @@ int nlbac_lagrangian_bwd(const float* req, const float* coef, int m, double cost
  * as float32 rows [capacity, width] on the device; a minibatch is ONE gather launch, out[i] = ring[idx[i]].
  * idx: DEVICE array of B row indices (int64), chosen by the host with the reference's own `random.sample`. */
 int nlbac_replay_gather(const float* ring, int width, const int64_t* idx, int64_t B, float* out, void* stream);
+/* The same gather with every field (columns [offsets[f], offsets[f] + widths[f]) of a row, ascending) written to its own
+ * contiguous [B, widths[f]] buffer outs[f] (NULL: field skipped) -- e.g. straight into the static input buffers of a
+ * captured update, instead of one strided copy per field.  offsets / widths / outs: HOST arrays, n_fields <=
+ * NLBAC_REPLAY_MAX_FIELDS. */
+#define NLBAC_REPLAY_MAX_FIELDS 16
+int nlbac_replay_gather_split(const float* ring, int width, const int64_t* idx, int64_t B, int n_fields,
+                              const int* offsets, const int* widths, float* const* outs, void* stream);
 
 /* Vectorised environment stepping: E independent copies of the reference's UnicycleEnv advanced in
  * one launch, float64 like the reference's numpy state.  Replaces, per environment, UnicycleEnv.reset

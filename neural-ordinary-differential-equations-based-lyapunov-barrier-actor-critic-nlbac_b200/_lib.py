@@ -150,6 +150,7 @@ def _declare(lib):
     lib.nlbac_env_pvtol_step.argtypes = [vp, vp, vp, i64] + [vp] * 9
     lib.nlbac_comm_unique_id.argtypes = [vp]
     lib.nlbac_comm_init.argtypes = [c.c_int, c.c_int, vp, c.POINTER(vp)]
+    lib.nlbac_replay_gather_split.argtypes = [vp, c.c_int, vp, c.c_int64, c.c_int, ip, ip, pvp, vp]
     lib.nlbac_td_target.argtypes = [vp, vp, vp, vp, vp, vp, c.c_float, c.c_int64, vp, vp]
     lib.nlbac_mse_mean_fwd.argtypes = [vp, vp, c.c_int64, vp, vp]
     lib.nlbac_mse_mean_bwd.argtypes = [vp, vp, c.c_int64, vp, vp, vp]

@@ -262,19 +262,27 @@ class GraphedUpdate:
                 self._body(False)
         return self
 
-    @torch.no_grad()
-    def load_batch(self, batch, eps=None):
-        """``batch`` = the reference's sampled tuple (state, action, reward, constraint, center_pos, next_center_pos,
-        next_state, mask, ...) as CUDA tensors or host arrays; ``eps`` = three [B, n_u] noise tensors or None (drawn
-        from torch's CUDA generator, like ``Normal.rsample`` in the reference)."""
+    def _batch_names(self):
+        """Static-buffer names in the order of the reference's sampled tuple."""
         names = ("state", "action", "reward", "constraint", "center_pos", "next_center_pos", "next_state", "mask")
         if self.barrier is not None:     # BU / BP replay layout: barrier_signal after constraint (replay_memory.py:12)
             names = names[:4] + ("barrier_signal",) + names[4:]
         if self.with_time:
             names = names + ("t", "next_t")
-        for n, v in zip(names, batch):
+        return names
+
+    @torch.no_grad()
+    def load_batch(self, batch, eps=None):
+        """``batch`` = the reference's sampled tuple (state, action, reward, constraint, center_pos, next_center_pos,
+        next_state, mask, ...) as CUDA tensors or host arrays; ``eps`` = three [B, n_u] noise tensors or None (drawn
+        from torch's CUDA generator, like ``Normal.rsample`` in the reference)."""
+        for n, v in zip(self._batch_names(), batch):
             t = v if torch.is_tensor(v) else torch.as_tensor(v, dtype=torch.float32)
             self.buf[n].copy_(t.reshape(self.buf[n].shape), non_blocking=True)
+        self.load_eps(eps)
+
+    @torch.no_grad()
+    def load_eps(self, eps=None):
         for i in range(len(self.eps)):
             if eps is None:
                 self.eps[i].normal_()
@@ -330,7 +338,13 @@ class GraphedUpdate:
                           NODE_model_update_interval=10, i_episode=None, eps=None):
         """The reference's call (U sac_cbf_clf.py:181; P :181 with ``i_episode``) on a device-resident
         ``nlbac_b200.ReplayMemory``."""
-        batch = memory.sample(batch_size=batch_size)
+        if hasattr(memory, "sample_into") and batch_size == self.B:
+            # gather straight into the static inputs of the captured update (same indices as memory.sample)
+            memory.sample_into(batch_size, [self.buf[n] for n in self._batch_names()])
+            self.load_eps(eps)
+            batch = None
+        else:
+            batch = memory.sample(batch_size=batch_size)
         fit = NODE_memory is not None and updates % NODE_model_update_interval == 0
         if fit and self.node_fit_max_episode is not None and i_episode is not None:
             fit = i_episode <= self.node_fit_max_episode                                  # P :205

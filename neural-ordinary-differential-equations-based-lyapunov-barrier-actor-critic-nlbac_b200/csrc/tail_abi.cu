@@ -414,6 +414,25 @@ __global__ void replay_gather_kernel(const float* __restrict__ ring, int width, 
   }
 }
 
+// the same gather, every field written to its OWN contiguous buffer (the static input buffers of a captured update):
+// saves the strided -> contiguous copy per field that splitting a [B, width] row matrix costs
+struct GatherSplit {
+  float* out[NLBAC_REPLAY_MAX_FIELDS];
+  int off[NLBAC_REPLAY_MAX_FIELDS], w[NLBAC_REPLAY_MAX_FIELDS];
+  int n_fields;
+};
+__global__ void replay_gather_split_kernel(const float* __restrict__ ring, int width, const long long* __restrict__ idx,
+                                           long long B, const __grid_constant__ GatherSplit g) {
+  const long long n = B * width;
+  for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+    const long long i = e / width;
+    const int c = (int)(e - i * width);
+    int f = 0;
+    while (f + 1 < g.n_fields && c >= g.off[f + 1]) ++f;
+    if (g.out[f] != nullptr && c < g.off[f] + g.w[f]) g.out[f][i * g.w[f] + (c - g.off[f])] = ring[idx[i] * width + c];
+  }
+}
+
 static int check_constraint(const nlbac_constraint_desc* d) {
   NLBAC_REQUIRE(d != nullptr, "null constraint descriptor");
   NLBAC_REQUIRE(d->kind >= NLBAC_CONSTRAINT_UNICYCLE && d->kind <= NLBAC_CONSTRAINT_PVTOL, "unknown constraint kind %d", d->kind);
@@ -667,6 +686,27 @@ int nlbac_replay_gather(const float* ring, int width, const int64_t* idx, int64_
   NLBAC_REQUIRE(ring && idx && out, "null pointer");
   replay_gather_kernel<<<tail_grid(B * width, 256), 256, 0, (cudaStream_t)stream>>>(
       ring, width, reinterpret_cast<const long long*>(idx), B, out);
+  NLBAC_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int nlbac_replay_gather_split(const float* ring, int width, const int64_t* idx, int64_t B, int n_fields,
+                              const int* offsets, const int* widths, float* const* outs, void* stream) {
+  ::nlbac::NvtxRange nvtx_range_("nlbac:replay_gather_split");
+  NLBAC_REQUIRE(ring && idx && offsets && widths && outs, "null pointer");
+  NLBAC_REQUIRE(B >= 0 && width >= 1 && n_fields >= 1 && n_fields <= NLBAC_REPLAY_MAX_FIELDS, "bad sizes");
+  if (B == 0) return 0;
+  GatherSplit g;
+  g.n_fields = n_fields;
+  int prev_end = 0;
+  for (int f = 0; f < n_fields; ++f) {
+    NLBAC_REQUIRE(offsets[f] >= prev_end && widths[f] >= 0 && offsets[f] + widths[f] <= width,
+                  "field %d: columns [%d, %d) out of order or outside the row", f, offsets[f], offsets[f] + widths[f]);
+    g.out[f] = outs[f]; g.off[f] = offsets[f]; g.w[f] = widths[f];
+    prev_end = offsets[f] + widths[f];
+  }
+  replay_gather_split_kernel<<<tail_grid(B * width, 256), 256, 0, (cudaStream_t)stream>>>(
+      ring, width, reinterpret_cast<const long long*>(idx), B, g);
   NLBAC_CUDA(cudaGetLastError());
   return 0;
 }

@@ -134,6 +134,32 @@ class ReplayMemory:
             if r is not None:
                 start = prev = r
 
+    def sample_into(self, batch_size, outs):
+        """``sample`` straight into caller-owned contiguous float32 CUDA buffers (``outs``: one per field in layout
+        order, ``None`` or a missing tail = skip): the same indices ``sample`` would draw, ONE launch, no per-field
+        copies.  ``GraphedUpdate.update_parameters`` uses it to fill the static inputs of the captured update."""
+        import ctypes
+        if batch_size > self._n:
+            raise ValueError("Sample larger than population or is negative")
+        idx = random.sample(range(self._n), batch_size)
+        self._flush()
+        idx_dev = torch.tensor(idx, dtype=torch.int64).pin_memory().to(self.device, non_blocking=True)
+        lay = [(off, w) for _, off, w, _ in self._layout if w > 0]
+        fields = [i for i, (_, _, w, _) in enumerate(self._layout) if w > 0]
+        n = len(lay)
+        ptrs = []
+        for k, fi in enumerate(fields):
+            o = outs[fi] if fi < len(outs) else None
+            if o is not None:
+                if not (o.is_cuda and o.dtype == torch.float32 and o.is_contiguous() and o.numel() == batch_size * lay[k][1]):
+                    raise ValueError("sample_into: buffer %d must be contiguous float32 CUDA with %d x %d elements" % (
+                        fi, batch_size, lay[k][1]))
+            ptrs.append(o.data_ptr() if o is not None else None)
+        _lib.check(_lib.lib().nlbac_replay_gather_split(
+            self._ring.data_ptr(), self._width, idx_dev.data_ptr(), batch_size, n,
+            (ctypes.c_int * n)(*[o for o, _ in lay]), (ctypes.c_int * n)(*[w for _, w in lay]),
+            (ctypes.c_void_p * n)(*ptrs), _lib.raw_stream()), "replay_gather_split")
+
     def sample(self, batch_size, as_numpy=False):
         if batch_size > self._n:
             raise ValueError("Sample larger than population or is negative")     # random.sample's own error

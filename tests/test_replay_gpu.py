@@ -56,3 +56,30 @@ def test_replay_large_batch_and_numpy_mode():
     assert a[0].shape == (32768, 7) and a[2].shape == (32768,)
     with pytest.raises(ValueError):
         ours.sample(cap + 1)
+
+
+def test_sample_into_fills_caller_buffers_like_sample():
+    """``sample_into`` (one gather launch straight into caller-owned contiguous buffers, the static inputs of a captured
+    update) draws the same indices and delivers the same values as ``sample``; skipped fields stay untouched."""
+    import random
+    import numpy as np
+    import nlbac_b200
+    rng = np.random.default_rng(0)
+    for barrier in (False, True):
+        mem = nlbac_b200.ReplayMemory(500, 3)
+        for _ in range(300):
+            tr = [rng.normal(size=7), rng.normal(size=2), rng.normal(), rng.normal()]
+            if barrier:
+                tr.append(rng.normal())
+            tr += [rng.normal(size=2), rng.normal(size=2), rng.normal(size=7), 1.0]
+            mem.push(*tr)
+        B = 64
+        state = random.getstate()
+        want = mem.sample(B)
+        random.setstate(state)
+        outs = [torch.full((B, max(1, int(np.prod(w.shape[1:])))), 7.0, device="cuda") if w is not None else None for w in want]
+        outs[1] = None                                   # skip the action field
+        mem.sample_into(B, outs)
+        for i, (o, w) in enumerate(zip(outs, want)):
+            if o is not None:
+                assert torch.equal(o.reshape(w.shape), w), i

@@ -189,3 +189,52 @@ def test_graphed_update_matches_reference_update_parameters(tag, golden_dir):
     assert all(v <= (5e-2 if "policy" in n else 2e-3) for n, v in worst.items()), worst
     assert lam_err[-1] <= 5e-2
     assert upd.graph is not None and int(upd.updates_dev.item()) == g["updates"][-1] + 1
+
+
+def test_update_parameters_gathers_straight_into_the_static_buffers(golden_dir):
+    """With a ``nlbac_b200.ReplayMemory`` the minibatch is gathered straight into the captured update's static inputs
+    (``sample_into``: one launch, no per-field copies); the result must equal the sample-then-copy path."""
+    import random
+    import nlbac_b200 as nb
+    C = nb.constraints
+    g = torch.load(os.path.join(golden_dir, "update_U.pt"), weights_only=False)
+    k, B, S = g["consts"], g["B"], SHAPES["U"]
+
+    class _SampleOnly:                      # hides sample_into: forces the sample-then-copy path
+        def __init__(self, mem):
+            self.mem = mem
+
+        @property
+        def position(self):
+            return self.mem.position
+
+        def sample(self, batch_size):
+            return self.mem.sample(batch_size)
+
+    def run(direct):
+        nets = _build(g, nb, "U")
+        node, lya = nets["neural_ode_model"], nets["lyapunovNet"]
+        kw = dict(dt=k["dt"], gamma_b=k["gamma_b"], hazards_locations=k["hazards"], hazards_radius=k["hazards_radius"],
+                  l_p=k["l_p"], batch_size=B)
+        upd = nb.GraphedUpdate(
+            nets["critic"], nets["critic_target"], lya, nets["lyapunovNet_target"], nets["policy"], nets["backup_policy"],
+            node, nb.DynamicsModel(_Env("Unicycle")), B,
+            primary=lambda s, pi, V: C.unicycle_required_matrix(node, lya, s, pi, V, **kw),
+            backup=lambda s, pi: C.unicycle_required_matrix(node, None, s, pi, None, **kw), num_constraints=8,
+            obs_dim=S["obs"], act_dim=S["act"], center_pos_num=S["lya"], gamma=k["gamma"], tau=k["tau"], alpha=k["alpha"],
+            lr=k["lr"], critic_lyapunov_lr=k["critic_lr"], node_lr=k["node_lr"])
+        mem = nb.ReplayMemory(4 * B, 5)
+        for b in g["batches"][:3]:
+            cols = [x.numpy() for x in b[:8]]
+            for i in range(B):
+                mem.push(*[c[i] for c in cols])
+        random.seed(11)
+        outs = []
+        for u in range(3):
+            e = [x.cuda() for x in g["eps"][u]]
+            outs.append(upd.update_parameters(mem if direct else _SampleOnly(mem), B, u + 1, None, None, 10, eps=e).clone())
+        return torch.stack(outs), torch.cat([p.detach().reshape(-1) for p in nets["policy"].parameters()])
+
+    o1, p1 = run(True)
+    o2, p2 = run(False)
+    assert _rel(o1, o2) <= 1e-6 and _rel(p1, p2) <= 1e-5, (_rel(o1, o2), _rel(p1, p2))
