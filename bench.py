@@ -709,12 +709,29 @@ def run_configs(args):
         upd.step(batch)                                                  # capture
         o = lat_gpu(lambda: upd.step(batch))
         o_replay = lat_gpu(lambda: upd.graph.replay())
+        # the call the training loop makes: sample the device-resident replay memory + update (one gather straight into
+        # the static buffers) vs sample-then-copy
+        mem = nlbac_b200.ReplayMemory(4 * B, 0)
+        for b_ in g["batches"][:4]:
+            cols = [x.numpy() for x in b_[:8]]
+            for i in range(B):
+                mem.push(*[c_[i] for c_ in cols])
+
+        class SampleOnly:
+            position = mem.position
+
+            @staticmethod
+            def sample(batch_size):
+                return mem.sample(batch_size)
+        o_mem = lat_gpu(lambda: upd.update_parameters(mem, B, 9, None, None, 10))
+        o_mem_copy = lat_gpu(lambda: upd.update_parameters(SampleOnly, B, 9, None, None, 10))
         ag_gpu, ag_cpu = UnicycleAgent(k, B, g["init"], "cuda"), UnicycleAgent(k, B, g["init"], "cpu")
         e = lat_gpu(lambda: ag_gpu.update_parameters(batch, 9), iters=20, warm=3)
         c = lat_cpu(lambda: ag_cpu.update_parameters(g["batches"][0], 9))
         return {"case": "config1 full update_parameters (critic + Lyapunov + actor + backup actor + alpha + Polyak)",
                 "batch": B, "ours_us": o, "ours_graph_replay_only_us": o_replay,
-                "ours_graph_replay_single_stream_us": o_single, "torch_eager_gpu_us": e, "torch_cpu_us": c,
+                "ours_graph_replay_single_stream_us": o_single, "ours_sample_and_update_us": o_mem,
+                "ours_sample_copy_and_update_us": o_mem_copy, "torch_eager_gpu_us": e, "torch_cpu_us": c,
                 "speedup_vs_eager_gpu": e / o, "speedup_vs_cpu": c / o,
                 "note": "ours = load the minibatch into the static buffers + ONE CUDA-graph replay, no host sync; eager = "
                         "the restated reference update (6 .item() + float() read-backs, numpy get_state round trip)"}
